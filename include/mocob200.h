@@ -1,0 +1,197 @@
+/* mocob200.h — C ABI of the B200-native direct-collocation evaluator.
+ *
+ * This is the drop-in boundary for the hot path of OpenSim Moco's MocoCasADiSolver:
+ * the per-grid-point multibody + muscle evaluation (the CasOC point functions) and
+ * the finite-difference sparse Jacobian that IPOPT asks for every iteration.
+ *
+ * Every entry point below names the reference interface it replaces
+ * (paths relative to the reference tree):
+ *
+ *   mocob200_create            <- CasOC::Problem::initialize + Transcription ctor
+ *                                 (Moco/Moco/MocoCasADiSolver/CasOCProblem.h:384-468,
+ *                                  CasOCTranscription.cpp:83-251)
+ *   mocob200_eval_points       <- CasOC::MultibodySystemExplicit/Implicit::eval,
+ *                                 CostIntegrand::eval mapped over the grid
+ *                                 (CasOCFunction.cpp:232-245,317-331,145-151;
+ *                                  CasOCTranscription.cpp:1179-1212)
+ *   mocob200_eval_f / _g       <- nlp_f / nlp_g of casadi::nlpsol
+ *                                 (CasOCTranscription.cpp:448-585, 253-446; .h:219-313)
+ *   mocob200_eval_grad_f       <- nlp_grad_f (CasADi FD through the callbacks)
+ *   mocob200_jac_g_structure   <- CSC sparsity of nlp_jac_g (optim_write_sparsity,
+ *                                 CasOCTranscription.cpp:661-677)
+ *   mocob200_eval_jac_g        <- nlp_jac_g (CasOCFunction.h:38-44 enable_fd/fd_method)
+ *   mocob200_set_fd            <- optim_finite_difference_scheme (MocoCasADiSolver.cpp:255-257)
+ *
+ * Conventions: plain C, POD only, caller owns every buffer, every call returns an
+ * int status (0 = ok), nothing throws across the boundary, NaN/Inf pass through.
+ * One handle is driven by one host thread (IPOPT is serial); concurrency is inside
+ * (CUDA streams, NCCL).  All floating point is FP64.
+ */
+#ifndef MOCOB200_H
+#define MOCOB200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MOCOB200_OK 0
+#define MOCOB200_ERR_ARG 1
+#define MOCOB200_ERR_UNSUPPORTED 2
+#define MOCOB200_ERR_CUDA 3
+#define MOCOB200_ERR_IO 4
+#define MOCOB200_ERR_NCCL 5
+
+/* joint (mobilizer) kinds; conventions of Simbody mobilizers used by
+ * opensim-core/OpenSim/Simulation/SimbodyEngine/{Pin,Slider,Planar,Weld}Joint.cpp */
+enum { MOCOB200_JOINT_WELD = 0, MOCOB200_JOINT_PIN = 1, MOCOB200_JOINT_SLIDER = 2,
+       MOCOB200_JOINT_PLANAR = 3 };
+/* path point kinds (PathPoint / ConditionalPathPoint / MovingPathPoint) */
+enum { MOCOB200_PP_FIXED = 0, MOCOB200_PP_CONDITIONAL = 1, MOCOB200_PP_MOVING = 2 };
+/* goal kinds (Moco/Moco/MocoGoal) */
+enum { MOCOB200_GOAL_CONTROL = 0, MOCOB200_GOAL_STATE_TRACKING = 1,
+       MOCOB200_GOAL_CONTACT_TRACKING = 2, MOCOB200_GOAL_FINAL_TIME = 3,
+       MOCOB200_GOAL_AVERAGE_SPEED = 4, MOCOB200_GOAL_PERIODICITY = 5,
+       MOCOB200_GOAL_INITIAL_ACTIVATION = 6, MOCOB200_GOAL_INITIAL_VELOCITY_EQUILIBRIUM_DGF = 7,
+       MOCOB200_GOAL_SUM_SQUARED_STATE = 8, MOCOB200_GOAL_CONTROL_TRACKING = 9 };
+enum { MOCOB200_MODE_COST = 0, MOCOB200_MODE_ENDPOINT_CONSTRAINT = 1 };
+enum { MOCOB200_SCHEME_TRAPEZOIDAL = 0, MOCOB200_SCHEME_HERMITE_SIMPSON = 1 };
+enum { MOCOB200_DYNAMICS_EXPLICIT = 0, MOCOB200_DYNAMICS_IMPLICIT = 1 };
+enum { MOCOB200_FD_FORWARD = 0, MOCOB200_FD_CENTRAL = 1, MOCOB200_FD_BACKWARD = 2 };
+/* what mocob200_eval_points returns */
+enum { MOCOB200_POINTS_OUTPUTS = 0 /* [n_grid][n_out] */, MOCOB200_POINTS_JACOBIAN = 1 /* [n_grid][n_out][n_in] */ };
+
+/* Layout of per-entity records inside the pools.  All strides are in elements. */
+#define MOCOB200_BODY_DSTRIDE 34   /* X_PF R(9) p(3) | X_BM R(9) p(3) | mass | com(3) | inertia about origin xx yy zz xy xz yz (6) */
+#define MOCOB200_BODY_ISTRIDE 4    /* parent (-1 ground) | joint kind | first q | ndof */
+#define MOCOB200_PP_DSTRIDE 5      /* loc(3) in body frame | range lo | range hi */
+#define MOCOB200_PP_ISTRIDE 8      /* body | kind | cond coord q | spline x,y,z | coord x (q idx) | coord y | -- z is idx[7] */
+#define MOCOB200_MUS_DSTRIDE 14    /* Fmax lopt lslack alpha vmax tau_a tau_d damping eT e0 width_scale min_ctl max_ctl kT */
+#define MOCOB200_MUS_ISTRIDE 10    /* pp_first | pp_count | control | act state(z idx or -1) | tendon-force state (z idx or -1) | flags | deriv idx (in derivatives, -1) | auxres idx (-1) | 0 | 0 */
+#define MOCOB200_MUS_FLAG_IGNORE_TENDON_COMPLIANCE 1
+#define MOCOB200_MUS_FLAG_IGNORE_ACTIVATION_DYNAMICS 2
+#define MOCOB200_MUS_FLAG_IGNORE_PASSIVE 4
+#define MOCOB200_MUS_FLAG_TENDON_IMPLICIT 8
+#define MOCOB200_CONTACT_DSTRIDE 28 /* sphere centre(3) radius | halfspace R(9) p(3) | stiffness dissipation mu_s mu_d mu_v v_t c_f b_d b_v | pad(3) */
+#define MOCOB200_CONTACT_ISTRIDE 2  /* sphere body | half-space body (-1 ground) */
+#define MOCOB200_CACT_DSTRIDE 1     /* optimal force */
+#define MOCOB200_CACT_ISTRIDE 2     /* speed index u | control */
+#define MOCOB200_SPLINE_ISTRIDE 3   /* first knot offset (into dbl, relative to o_spline_data) | n knots | 0 */
+#define MOCOB200_GOAL_ISTRIDE 8     /* kind | mode | n_outputs | has_integrand | ioff (into idx) | doff (into dbl) | ni | nd */
+#define MOCOB200_PPOLY_ISTRIDE 3    /* first break offset (rel. o_ppoly_data) | n pieces | order (coeffs per piece) */
+
+/* A fixed-topology model + optimal control problem flattened into two pools.
+ * Filled by the host flattener (the reference analogue is MocoProblemRep,
+ * Moco/Moco/MocoProblemRep.cpp:36-559, read by MocoCasOCProblem.cpp:30-256). */
+typedef struct mocob200_tables {
+    int n_dbl, n_int;
+    const double* dbl;
+    const int* idx;
+    /* sizes */
+    int nb;          /* mobilized bodies (ground excluded), Simbody tree (breadth-first) order */
+    int nq;          /* coordinates == speeds */
+    int nz;          /* auxiliary states (activation, normalized tendon force) */
+    int nc;          /* controls */
+    int nderiv_aux;  /* implicit auxiliary derivative variables */
+    int nmus, npp, nspline, ncontact, ncact, ngoal, nppoly;
+    /* offsets into dbl */
+    int o_body_d, o_gravity, o_pp_d, o_mus_d, o_contact_d, o_cact_d, o_spline_data, o_ppoly_data;
+    int o_bounds;    /* 6 doubles per variable: lo hi init_lo init_hi final_lo final_hi ; states (nq+nq+nz) then controls (nc) */
+    int o_time_bounds; /* t0 lo,hi ; tf lo,hi */
+    /* offsets into idx */
+    int o_body_i, o_pp_i, o_mus_i, o_contact_i, o_cact_i, o_spline_i, o_goal_i, o_ppoly_i;
+} mocob200_tables;
+
+/* Solver-side settings: mirrors the properties of MocoDirectCollocationSolver /
+ * MocoCasADiSolver that shape the NLP (MocoDirectCollocationSolver.h:90-168,
+ * MocoCasADiSolver.h:115-159). */
+typedef struct mocob200_transcription {
+    int scheme;                        /* MOCOB200_SCHEME_* (default hermite-simpson) */
+    int dynamics_mode;                 /* MOCOB200_DYNAMICS_* */
+    int n_mesh;                        /* mesh points = intervals + 1 */
+    const double* mesh;                /* [n_mesh], 0..1 increasing; NULL = uniform */
+    int interpolate_control_midpoints; /* default 1 */
+    int fd_scheme;                     /* MOCOB200_FD_* ; solver default central */
+    double accel_bounds[2];            /* implicit_multibody_acceleration_bounds */
+    double auxderiv_bounds[2];         /* implicit_auxiliary_derivative_bounds */
+    int minimize_accelerations;  double accelerations_weight;
+    int minimize_auxiliary_derivatives; double auxiliary_derivatives_weight;
+} mocob200_transcription;
+
+typedef struct mocob200_dims {
+    int n_grid, n_mesh, n_var, n_con, nnz_jac;
+    int ns, nc, nd, n_in, n_out;       /* point function: n_in = 1+ns+nc+nd ; n_out = nu + nz + n_auxres + n_integrands */
+    int n_dyn_out, n_integrand;
+    int n_cost_terms;
+    int first_interval, n_intervals_local; /* this rank's shard of mesh intervals */
+    int rank, world;
+} mocob200_dims;
+
+typedef struct mocob200_handle mocob200_handle;
+typedef struct mocob200_problem mocob200_problem; /* host-side: owns a tables + transcription pair */
+
+/* ---- host side: flatten models / build the reference's example problems ---- */
+/* name: "sliding_mass" (exampleSlidingMass.cpp / testMocoInterface.cpp:66-83),
+ *       "hanging_muscle" (testMocoActuators.cpp:1050-1175), "pendulum:<N>" (ModelFactory::createNLinkPendulum),
+ *       "gait2d_tracking", "gait2d_prediction" (example2DWalking.cpp:58-340; need data_dir with 2D_gait.osim etc.).
+ * options: "key=value;..." — num_mesh_intervals, scheme, dynamics_mode, fd_scheme, ... (NULL = the example's own). */
+int mocob200_problem_create_example(const char* name, const char* data_dir, const char* options,
+                                    mocob200_problem** out, char* err, int errlen);
+/* Load a flattened problem written by mocob200_problem_save (so a GPU box needs no .osim). */
+int mocob200_problem_load(const char* path, mocob200_problem** out, char* err, int errlen);
+/* options (may be NULL) override the stored transcription: "num_mesh_intervals=800;fd_scheme=central;..." */
+int mocob200_problem_load_opts(const char* path, const char* options, mocob200_problem** out, char* err, int errlen);
+int mocob200_problem_save(const mocob200_problem*, const char* path);
+/* '\n'-joined names in NLP order; which = 0 states, 1 controls, 2 auxiliary derivative variables */
+int mocob200_problem_names(const mocob200_problem*, int which, char* buf, int buflen);
+const mocob200_tables* mocob200_problem_tables(const mocob200_problem*);
+const mocob200_transcription* mocob200_problem_transcription(const mocob200_problem*);
+void mocob200_problem_destroy(mocob200_problem*);
+/* NLP layout computed on the host only (no GPU needed). bounds arrays may be NULL. */
+int mocob200_layout(const mocob200_tables*, const mocob200_transcription*, mocob200_dims* dims);
+int mocob200_layout_bounds(const mocob200_tables*, const mocob200_transcription*,
+                           double* x_lo, double* x_hi, double* g_lo, double* g_hi);
+int mocob200_layout_structure(const mocob200_tables*, const mocob200_transcription*,
+                              int* colptr /*[n_var+1]*/, int* rowidx /*[nnz]*/);
+/* A deterministic iterate: guess from bounds midpoints (createInitialGuessFromBounds,
+ * CasOCTranscription.cpp:1123-1149) when seed<0, else uniform within bounds scaled by `spread`
+ * about the midpoint (createRandomIterateWithinBounds, :1151-1177). */
+int mocob200_make_iterate(const mocob200_tables*, const mocob200_transcription*, long seed, double spread, double* x);
+
+/* ---- device side ---- */
+/* rank/world: this process's shard of mesh intervals (world=1: everything).
+ * nccl_unique_id: 128 bytes shared by all ranks (NULL when world==1). */
+int mocob200_create(const mocob200_tables*, const mocob200_transcription*, int device,
+                    int rank, int world, const void* nccl_unique_id, mocob200_handle** out);
+int mocob200_nccl_unique_id(void* id128);
+void mocob200_destroy(mocob200_handle*);
+const char* mocob200_last_error(const mocob200_handle*);
+int mocob200_get_dims(const mocob200_handle*, mocob200_dims*);
+int mocob200_set_fd(mocob200_handle*, int scheme, double h /*<=0: CasADi default*/, int h_iter /*<0 default*/,
+                    double u_aim /*<=0 default 100*/);
+int mocob200_jac_g_structure(const mocob200_handle*, int* colptr, int* rowidx);
+/* x, outputs: HOST pointers (pinned or pageable). Full-size arrays on every rank;
+ * after the call rank 0 holds the gathered result (all ranks for eval_f). */
+int mocob200_eval_points(mocob200_handle*, int what, const double* x, double* out);
+int mocob200_eval_f(mocob200_handle*, const double* x, double* f, double* f_terms /*[n_cost_terms] or NULL*/);
+int mocob200_eval_g(mocob200_handle*, const double* x, double* g);
+int mocob200_eval_grad_f(mocob200_handle*, const double* x, double* grad);
+int mocob200_eval_jac_g(mocob200_handle*, const double* x, double* values);
+/* Same evaluations with x already resident on the device and results left there
+ * (device pointers; used by bench.py's device-resident timing and by callers that chain kernels). */
+int mocob200_eval_jac_g_device(mocob200_handle*, const double* d_x, double* d_values, void* cuda_stream);
+int mocob200_eval_g_device(mocob200_handle*, const double* d_x, double* d_g, void* cuda_stream);
+/* the *_device calls only enqueue work on the handle's stream: */
+int mocob200_sync(mocob200_handle*);
+int mocob200_mark(mocob200_handle*, int which /*0 start, 1 stop*/); /* CUDA-event stopwatch on that stream */
+int mocob200_elapsed_ms(mocob200_handle*, float* ms);
+/* bookkeeping for bench.py */
+long mocob200_launch_count(const mocob200_handle*);           /* kernels launched so far */
+int mocob200_last_kernel_ms(const mocob200_handle*, float* point_kernel_ms, float* assemble_kernel_ms);
+long mocob200_point_evals_per_jacobian(const mocob200_handle*);
+/* FP64 FMA saturation microbenchmark: returns measured TFLOP/s (the FP64 roofline peak). */
+int mocob200_measure_fp64_peak(int device, double* tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,510 @@
+// Device half of the C ABI: handle life cycle, evaluation pipelines, NCCL gather of the point blocks.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "kernels.cuh"
+#include "layout.h"
+
+using namespace mocob200;
+
+namespace {
+
+// ---- minimal NCCL binding, resolved at run time so single-GPU use needs no NCCL at all
+typedef struct ncclComm* ncclComm_t;
+struct NcclUid { char internal[128]; };
+struct NcclApi {
+    void* lib = nullptr;
+    int (*GetUniqueId)(NcclUid*) = nullptr;
+    int (*CommInitRank)(ncclComm_t*, int, NcclUid, int) = nullptr;
+    int (*CommDestroy)(ncclComm_t) = nullptr;
+    int (*Broadcast)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*Send)(const void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    bool load(std::string& err) {
+        if (lib) return true;
+        const char* names[] = {"libnccl.so.2", "libnccl.so"};
+        for (const char* n : names) { lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (lib) break; }
+        if (!lib) { err = std::string("cannot load NCCL: ") + dlerror(); return false; }
+#define NCCL_SYM(field, sym) field = (decltype(field))dlsym(lib, sym); if (!field) { err = std::string("NCCL symbol missing: ") + sym; return false; }
+        NCCL_SYM(GetUniqueId, "ncclGetUniqueId");
+        NCCL_SYM(CommInitRank, "ncclCommInitRank");
+        NCCL_SYM(CommDestroy, "ncclCommDestroy");
+        NCCL_SYM(Broadcast, "ncclBroadcast");
+        NCCL_SYM(Send, "ncclSend");
+        NCCL_SYM(Recv, "ncclRecv");
+        NCCL_SYM(GroupStart, "ncclGroupStart");
+        NCCL_SYM(GroupEnd, "ncclGroupEnd");
+        NCCL_SYM(GetErrorString, "ncclGetErrorString");
+#undef NCCL_SYM
+        return true;
+    }
+};
+NcclApi g_nccl;
+const int kNcclDouble = 8; // ncclFloat64
+
+template <class T>
+T* devAlloc(size_t n) {
+    T* p = nullptr;
+    if (n == 0) n = 1;
+    if (cudaMalloc(&p, n * sizeof(T)) != cudaSuccess) return nullptr;
+    return p;
+}
+template <class T>
+T* devUpload(const std::vector<T>& v) {
+    T* p = devAlloc<T>(v.size());
+    if (p && !v.empty()) cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
+    return p;
+}
+
+} // namespace
+
+struct mocob200_handle {
+    std::string err;
+    int device = 0, rank = 0, world = 1;
+    Layout L;
+    DevTables DT{};
+    DevLayout DL{};
+    FdSettings fd{};
+    std::vector<void*> owned;
+    double *d_x = nullptr, *d_Y = nullptr, *d_J = nullptr, *d_I = nullptr, *d_G = nullptr, *d_E = nullptr;
+    double *d_g = nullptr, *d_vals = nullptr, *d_grad = nullptr, *d_f = nullptr;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    long launches = 0;
+    int p0 = 0, p1 = 0; // this rank's grid points
+    std::vector<int> shard; // world+1 boundaries
+    ncclComm_t comm = nullptr;
+    // host-side memo: IPOPT asks for grad_f and jac_g at the same x
+    std::vector<double> x_cached;
+    bool haveJ = false;
+
+    bool ck(cudaError_t e, const char* what) {
+        if (e == cudaSuccess) return true;
+        err = std::string(what) + ": " + cudaGetErrorString(e);
+        return false;
+    }
+};
+
+namespace {
+
+bool ncclOk(mocob200_handle* h, int rc, const char* what) {
+    if (rc == 0) return true;
+    h->err = std::string(what) + ": " + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "nccl error");
+    return false;
+}
+
+void defaultFd(FdSettings& fd, int scheme) {
+    const double eps = 2.220446049250313e-16;
+    fd.scheme = scheme;
+    fd.reltol = eps;
+    fd.abstol = eps;
+    fd.u_aim = 100.0;
+    if (scheme == MOCOB200_FD_CENTRAL) { fd.h = cbrt(eps); fd.h_iter = 1; }
+    else { fd.h = sqrt(eps); fd.h_iter = 0; }
+}
+
+// x on the device (rank 0 holds the caller's x; other ranks receive it)
+bool stageX(mocob200_handle* h, const double* x_host) {
+    if (h->rank == 0) {
+        if (!x_host) { h->err = "x is NULL"; return false; }
+        if (!h->ck(cudaMemcpyAsync(h->d_x, x_host, sizeof(double) * h->L.n_var, cudaMemcpyHostToDevice, h->stream), "H2D x")) return false;
+    }
+    return true;
+}
+bool bcastX(mocob200_handle* h, const double* d_src) {
+    if (h->world > 1) {
+        if (!ncclOk(h, g_nccl.Broadcast(d_src, h->d_x, (size_t)h->L.n_var, kNcclDouble, 0, h->comm, h->stream), "ncclBroadcast")) return false;
+    } else if (d_src != h->d_x) {
+        if (!h->ck(cudaMemcpyAsync(h->d_x, d_src, sizeof(double) * h->L.n_var, cudaMemcpyDeviceToDevice, h->stream), "D2D x")) return false;
+    }
+    return true;
+}
+// gather per-point blocks (stride doubles per grid point) to rank 0
+bool gatherBlocks(mocob200_handle* h, double* d_buf, size_t stride) {
+    if (h->world == 1) return true;
+    if (!ncclOk(h, g_nccl.GroupStart(), "ncclGroupStart")) return false;
+    if (h->rank == 0) {
+        for (int r = 1; r < h->world; ++r) {
+            const size_t n = (size_t)(h->shard[r + 1] - h->shard[r]) * stride;
+            if (n) g_nccl.Recv(d_buf + (size_t)h->shard[r] * stride, n, kNcclDouble, r, h->comm, h->stream);
+        }
+    } else {
+        const size_t n = (size_t)(h->p1 - h->p0) * stride;
+        if (n) g_nccl.Send(d_buf + (size_t)h->p0 * stride, n, kNcclDouble, 0, h->comm, h->stream);
+    }
+    return ncclOk(h, g_nccl.GroupEnd(), "ncclGroupEnd");
+}
+
+// stages shared by the pipelines; x must already be in d_x
+bool runNominal(mocob200_handle* h) {
+    launch_points_nominal(h->DT, h->DL, h->d_x, h->d_Y, h->p0, h->p1 - h->p0, h->stream);
+    h->launches++;
+    if (!gatherBlocks(h, h->d_Y, (size_t)h->L.n_out)) return false;
+    if (h->rank == 0) {
+        launch_integrals(h->DL, h->d_x, h->d_Y, h->d_J, h->d_I, false, h->stream);
+        launch_endpoint(h->DT, h->DL, h->fd, h->d_x, h->d_I, h->d_G, h->d_E, false, h->stream);
+        h->launches += (h->L.n_integrand > 0) + (h->DL.n_eout_total > 0);
+    }
+    return true;
+}
+bool runFd(mocob200_handle* h) {
+    cudaEventRecord(h->ev[0], h->stream);
+    launch_points_fd(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream);
+    cudaEventRecord(h->ev[1], h->stream);
+    h->launches++;
+    if (!gatherBlocks(h, h->d_Y, (size_t)h->L.n_out)) return false;
+    if (!gatherBlocks(h, h->d_J, (size_t)h->L.n_out * h->L.n_in)) return false;
+    if (h->rank == 0) {
+        launch_integrals(h->DL, h->d_x, h->d_Y, h->d_J, h->d_I, true, h->stream);
+        launch_endpoint(h->DT, h->DL, h->fd, h->d_x, h->d_I, h->d_G, h->d_E, true, h->stream);
+        h->launches += (h->L.n_integrand > 0) + (h->DL.n_eout_total > 0);
+    }
+    return true;
+}
+bool finish(mocob200_handle* h, const char* what) {
+    if (!h->ck(cudaStreamSynchronize(h->stream), what)) return false;
+    return h->ck(cudaGetLastError(), what);
+}
+bool sameX(mocob200_handle* h, const double* x) {
+    return h->rank == 0 && x && h->x_cached.size() == (size_t)h->L.n_var &&
+           std::memcmp(h->x_cached.data(), x, sizeof(double) * h->L.n_var) == 0;
+}
+void rememberX(mocob200_handle* h, const double* x, bool withJ) {
+    if (h->rank != 0 || !x) return;
+    h->x_cached.assign(x, x + h->L.n_var);
+    h->haveJ = withJ;
+}
+
+} // namespace
+
+extern "C" {
+
+int mocob200_nccl_unique_id(void* id128) {
+    std::string err;
+    if (!id128 || !g_nccl.load(err)) return MOCOB200_ERR_NCCL;
+    NcclUid uid;
+    if (g_nccl.GetUniqueId(&uid) != 0) return MOCOB200_ERR_NCCL;
+    std::memcpy(id128, &uid, 128);
+    return MOCOB200_OK;
+}
+
+void mocob200_destroy(mocob200_handle* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
+    for (void* p : h->owned) cudaFree(p);
+    for (auto& e : h->ev) if (e) cudaEventDestroy(e);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+static thread_local std::string g_create_err;
+const char* mocob200_last_error(const mocob200_handle* h) { return h ? h->err.c_str() : g_create_err.c_str(); }
+
+int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, int device, int rank, int world,
+                    const void* nccl_unique_id, mocob200_handle** out) {
+    if (!T || !R || !out || world < 1 || rank < 0 || rank >= world) { g_create_err = "bad argument"; return MOCOB200_ERR_ARG; }
+    auto h = new mocob200_handle;
+    h->device = device; h->rank = rank; h->world = world;
+    auto fail = [&](int code, const std::string& m) { g_create_err = m.empty() ? h->err : m; mocob200_destroy(h); return code; };
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0)
+        return fail(MOCOB200_ERR_CUDA, "no CUDA device: the evaluator has no CPU path");
+    if (!h->ck(cudaSetDevice(device), "cudaSetDevice")) return fail(MOCOB200_ERR_CUDA, "");
+    try {
+        h->L = buildLayout(*T, *R, true);
+    } catch (const std::exception& e) { return fail(MOCOB200_ERR_UNSUPPORTED, e.what()); }
+    Layout& L = h->L;
+    if (T->nb > MOCOB200_MAXB || T->nq > MOCOB200_MAXQ || T->ncontact > MOCOB200_MAXCONTACT)
+        return fail(MOCOB200_ERR_UNSUPPORTED, "model exceeds the compiled limits (bodies/coordinates/contacts)");
+    if (L.n_in > MOCOB200_MAX_IN || L.n_out > MOCOB200_MAX_OUT || L.n_in + 1 > 256 || L.n_ein + 1 > 1024)
+        return fail(MOCOB200_ERR_UNSUPPORTED, "point function exceeds the compiled input/output limits");
+    for (int m = 0; m < T->nmus; ++m)
+        if (T->idx[T->o_mus_i + m * MOCOB200_MUS_ISTRIDE + 1] > MOCOB200_MAXPPM)
+            return fail(MOCOB200_ERR_UNSUPPORTED, "a muscle has more path points than the compiled limit");
+    for (int g = 0; g < T->ngoal; ++g)
+        if (T->idx[T->o_goal_i + g * MOCOB200_GOAL_ISTRIDE + 2] > MOCOB200_MAX_EOUT)
+            return fail(MOCOB200_ERR_UNSUPPORTED, "a goal has more outputs than the compiled limit");
+    if (L.n_integrand > 30) return fail(MOCOB200_ERR_UNSUPPORTED, "too many integrand goals");
+
+    auto own = [&](void* p) { h->owned.push_back(p); return p; };
+    // tables
+    DevTables& D = h->DT;
+    std::vector<double> dbl(T->dbl, T->dbl + T->n_dbl);
+    std::vector<int> idx(T->idx, T->idx + T->n_int);
+    D.dbl = (const double*)own(devUpload(dbl));
+    D.idx = (const int*)own(devUpload(idx));
+    D.nb = T->nb; D.nq = T->nq; D.nz = T->nz; D.nc = T->nc; D.nderiv_aux = T->nderiv_aux; D.nmus = T->nmus; D.npp = T->npp;
+    D.nspline = T->nspline; D.ncontact = T->ncontact; D.ncact = T->ncact; D.ngoal = T->ngoal; D.nppoly = T->nppoly;
+    D.o_body_d = T->o_body_d; D.o_gravity = T->o_gravity; D.o_pp_d = T->o_pp_d; D.o_mus_d = T->o_mus_d;
+    D.o_contact_d = T->o_contact_d; D.o_cact_d = T->o_cact_d; D.o_spline_data = T->o_spline_data; D.o_ppoly_data = T->o_ppoly_data;
+    D.o_body_i = T->o_body_i; D.o_pp_i = T->o_pp_i; D.o_mus_i = T->o_mus_i; D.o_contact_i = T->o_contact_i; D.o_cact_i = T->o_cact_i;
+    D.o_spline_i = T->o_spline_i; D.o_goal_i = T->o_goal_i; D.o_ppoly_i = T->o_ppoly_i;
+    D.implicit = L.implicit; D.n_auxres = L.n_auxres; D.n_integrand = L.n_integrand;
+    // layout
+    DevLayout& G = h->DL;
+    G.scheme = L.scheme; G.implicit = L.implicit; G.nq = L.nq; G.nz = L.nz; G.ns = L.ns; G.nc = L.nc; G.nd = L.nd; G.n_in = L.n_in;
+    G.n_auxres = L.n_auxres; G.n_integrand = L.n_integrand; G.n_dyn_out = L.n_dyn_out; G.n_out = L.n_out;
+    G.n_mesh = L.n_mesh; G.n_grid = L.n_grid; G.n_intervals = L.n_intervals; G.n_var = L.n_var; G.n_con = L.n_con; G.nnz = L.nnz;
+    G.off_states = L.off_states; G.off_controls = L.off_controls; G.off_derivs = L.off_derivs;
+    G.n_endpoint_rows = L.n_endpoint_rows; G.n_resid_rows_per_point = L.n_resid_rows_per_point; G.n_defect_rows = L.n_defect_rows;
+    G.n_interp_rows = L.n_interp_rows; G.n_ein = L.n_ein; G.n_cost_terms = L.n_cost_terms;
+    G.minimize_accel = R->minimize_accelerations; G.minimize_auxderiv = R->minimize_auxiliary_derivatives;
+    G.accel_weight = R->accelerations_weight; G.auxderiv_weight = R->auxiliary_derivatives_weight;
+    std::vector<int> eoff(T->ngoal + 1, 0);
+    for (int g = 0; g < T->ngoal; ++g) eoff[g + 1] = eoff[g] + T->idx[T->o_goal_i + g * MOCOB200_GOAL_ISTRIDE + 2];
+    G.n_eout_total = eoff[T->ngoal];
+    G.mesh = (const double*)own(devUpload(L.mesh));
+    G.grid = (const double*)own(devUpload(L.grid));
+    G.quad = (const double*)own(devUpload(L.quad));
+    G.row_resid = (const int*)own(devUpload(L.row_resid));
+    G.row_defect = (const int*)own(devUpload(L.row_defect));
+    G.row_interp = (const int*)own(devUpload(L.row_interp));
+    G.goal_row = (const int*)own(devUpload(L.goal_row));
+    G.goal_integrand = (const int*)own(devUpload(L.goal_integrand));
+    G.goal_eoff = (const int*)own(devUpload(eoff));
+    static_assert(sizeof(RowMeta) == sizeof(RowMetaD) && sizeof(ColMeta) == sizeof(ColMetaD), "meta layouts");
+    {
+        RowMetaD* p = devAlloc<RowMetaD>(L.rows.size());
+        if (p) cudaMemcpy(p, L.rows.data(), L.rows.size() * sizeof(RowMeta), cudaMemcpyHostToDevice);
+        G.rows = (const RowMetaD*)own(p);
+        ColMetaD* c = devAlloc<ColMetaD>(L.cols.size());
+        if (c) cudaMemcpy(c, L.cols.data(), L.cols.size() * sizeof(ColMeta), cudaMemcpyHostToDevice);
+        G.cols = (const ColMetaD*)own(c);
+    }
+    G.colptr = (const int*)own(devUpload(L.colptr));
+    G.rowidx = (const int*)own(devUpload(L.rowidx));
+    G.nnzcol = (const int*)own(devUpload(L.nnzcol));
+    // work buffers
+    h->d_x = (double*)own(devAlloc<double>(L.n_var));
+    h->d_Y = (double*)own(devAlloc<double>((size_t)L.n_grid * L.n_out));
+    h->d_J = (double*)own(devAlloc<double>((size_t)L.n_grid * L.n_out * L.n_in));
+    h->d_I = (double*)own(devAlloc<double>(3 * (size_t)L.n_integrand + 1));
+    h->d_G = (double*)own(devAlloc<double>(G.n_eout_total + 1));
+    h->d_E = (double*)own(devAlloc<double>((size_t)(G.n_eout_total + 1) * L.n_ein));
+    h->d_g = (double*)own(devAlloc<double>(L.n_con));
+    h->d_vals = (double*)own(devAlloc<double>(L.nnz));
+    h->d_grad = (double*)own(devAlloc<double>(L.n_var));
+    h->d_f = (double*)own(devAlloc<double>(2 + L.n_cost_terms));
+    for (void* p : h->owned)
+        if (!p) return fail(MOCOB200_ERR_CUDA, "device allocation failed");
+    if (!h->ck(cudaGetLastError(), "upload")) return fail(MOCOB200_ERR_CUDA, "");
+    if (!h->ck(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "stream")) return fail(MOCOB200_ERR_CUDA, "");
+    for (auto& e : h->ev) cudaEventCreate(&e);
+    defaultFd(h->fd, R->fd_scheme);
+    // shard grid points evenly over ranks
+    h->shard.resize(world + 1);
+    for (int r = 0; r <= world; ++r) h->shard[r] = (int)((long long)L.n_grid * r / world);
+    h->p0 = h->shard[rank];
+    h->p1 = h->shard[rank + 1];
+    if (world > 1) {
+        if (!nccl_unique_id) return fail(MOCOB200_ERR_ARG, "world > 1 needs a NCCL unique id");
+        std::string e;
+        if (!g_nccl.load(e)) return fail(MOCOB200_ERR_NCCL, e);
+        NcclUid uid;
+        std::memcpy(&uid, nccl_unique_id, 128);
+        if (!ncclOk(h, g_nccl.CommInitRank(&h->comm, world, uid, rank), "ncclCommInitRank")) return fail(MOCOB200_ERR_NCCL, "");
+    }
+    *out = h;
+    return MOCOB200_OK;
+}
+
+int mocob200_get_dims(const mocob200_handle* h, mocob200_dims* d) {
+    if (!h || !d) return MOCOB200_ERR_ARG;
+    const Layout& L = h->L;
+    std::memset(d, 0, sizeof *d);
+    d->n_grid = L.n_grid; d->n_mesh = L.n_mesh; d->n_var = L.n_var; d->n_con = L.n_con; d->nnz_jac = L.nnz;
+    d->ns = L.ns; d->nc = L.nc; d->nd = L.nd; d->n_in = L.n_in; d->n_out = L.n_out;
+    d->n_dyn_out = L.n_dyn_out; d->n_integrand = L.n_integrand; d->n_cost_terms = L.n_cost_terms;
+    d->first_interval = h->p0; d->n_intervals_local = h->p1 - h->p0; d->rank = h->rank; d->world = h->world;
+    return MOCOB200_OK;
+}
+
+int mocob200_set_fd(mocob200_handle* h, int scheme, double step, int h_iter, double u_aim) {
+    if (!h || scheme < 0 || scheme > 2) return MOCOB200_ERR_ARG;
+    defaultFd(h->fd, scheme);
+    if (step > 0) h->fd.h = step;
+    if (h_iter >= 0) h->fd.h_iter = h_iter;
+    if (u_aim > 0) h->fd.u_aim = u_aim;
+    h->x_cached.clear();
+    return MOCOB200_OK;
+}
+
+int mocob200_jac_g_structure(const mocob200_handle* h, int* colptr, int* rowidx) {
+    if (!h || !colptr || !rowidx) return MOCOB200_ERR_ARG;
+    std::memcpy(colptr, h->L.colptr.data(), sizeof(int) * (h->L.n_var + 1));
+    std::memcpy(rowidx, h->L.rowidx.data(), sizeof(int) * h->L.nnz);
+    return MOCOB200_OK;
+}
+
+int mocob200_eval_points(mocob200_handle* h, int what, const double* x, double* out) {
+    if (!h) return MOCOB200_ERR_ARG;
+    cudaSetDevice(h->device);
+    if (!stageX(h, x) || !bcastX(h, h->d_x)) return MOCOB200_ERR_CUDA;
+    const Layout& L = h->L;
+    if (what == MOCOB200_POINTS_OUTPUTS) {
+        if (!runNominal(h)) return MOCOB200_ERR_CUDA;
+        if (h->rank == 0 && out) cudaMemcpyAsync(out, h->d_Y, sizeof(double) * L.n_grid * L.n_out, cudaMemcpyDeviceToHost, h->stream);
+        rememberX(h, nullptr, false);
+        h->x_cached.clear();
+    } else {
+        if (!runFd(h)) return MOCOB200_ERR_CUDA;
+        if (h->rank == 0 && out) cudaMemcpyAsync(out, h->d_J, sizeof(double) * L.n_grid * L.n_out * L.n_in, cudaMemcpyDeviceToHost, h->stream);
+        h->x_cached.clear();
+    }
+    return finish(h, "eval_points") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
+}
+
+int mocob200_eval_g(mocob200_handle* h, const double* x, double* g) {
+    if (!h) return MOCOB200_ERR_ARG;
+    cudaSetDevice(h->device);
+    if (!stageX(h, x) || !bcastX(h, h->d_x) || !runNominal(h)) return MOCOB200_ERR_CUDA;
+    if (h->rank == 0) {
+        launch_assemble_g(h->DL, h->d_x, h->d_Y, h->d_G, h->d_g, h->stream);
+        h->launches++;
+        if (g) cudaMemcpyAsync(g, h->d_g, sizeof(double) * h->L.n_con, cudaMemcpyDeviceToHost, h->stream);
+    }
+    h->x_cached.clear();
+    return finish(h, "eval_g") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
+}
+
+int mocob200_eval_f(mocob200_handle* h, const double* x, double* f, double* f_terms) {
+    if (!h) return MOCOB200_ERR_ARG;
+    cudaSetDevice(h->device);
+    if (!stageX(h, x) || !bcastX(h, h->d_x) || !runNominal(h)) return MOCOB200_ERR_CUDA;
+    std::vector<double> host(1 + h->L.n_cost_terms, 0.0);
+    if (h->rank == 0) {
+        launch_assemble_f(h->DT, h->DL, h->d_x, h->d_G, h->d_f, h->stream);
+        h->launches++;
+        cudaMemcpyAsync(host.data(), h->d_f, sizeof(double) * host.size(), cudaMemcpyDeviceToHost, h->stream);
+    }
+    h->x_cached.clear();
+    if (!finish(h, "eval_f")) return MOCOB200_ERR_CUDA;
+    if (h->rank == 0) {
+        if (f) *f = host[0];
+        if (f_terms) for (int k = 0; k < h->L.n_cost_terms; ++k) f_terms[k] = host[1 + k];
+    }
+    return MOCOB200_OK;
+}
+
+int mocob200_eval_grad_f(mocob200_handle* h, const double* x, double* grad) {
+    if (!h) return MOCOB200_ERR_ARG;
+    cudaSetDevice(h->device);
+    const bool reuse = h->world == 1 && h->haveJ && sameX(h, x);
+    if (!reuse) {
+        if (!stageX(h, x) || !bcastX(h, h->d_x) || !runFd(h)) return MOCOB200_ERR_CUDA;
+    }
+    if (h->rank == 0) {
+        launch_assemble_grad(h->DT, h->DL, h->d_x, h->d_Y, h->d_J, h->d_I, h->d_E, h->d_grad, h->stream);
+        h->launches++;
+        if (grad) cudaMemcpyAsync(grad, h->d_grad, sizeof(double) * h->L.n_var, cudaMemcpyDeviceToHost, h->stream);
+    }
+    if (!finish(h, "eval_grad_f")) return MOCOB200_ERR_CUDA;
+    rememberX(h, x, true);
+    return MOCOB200_OK;
+}
+
+static bool jacPipeline(mocob200_handle* h, double* d_vals) {
+    if (!runFd(h)) return false;
+    if (h->rank == 0) {
+        cudaEventRecord(h->ev[2], h->stream);
+        launch_assemble_jac(h->DL, h->d_x, h->d_Y, h->d_J, h->d_I, h->d_E, d_vals, h->stream);
+        cudaEventRecord(h->ev[3], h->stream);
+        h->launches++;
+    }
+    return true;
+}
+
+int mocob200_eval_jac_g(mocob200_handle* h, const double* x, double* values) {
+    if (!h) return MOCOB200_ERR_ARG;
+    cudaSetDevice(h->device);
+    const bool reuse = h->world == 1 && h->haveJ && sameX(h, x);
+    if (!reuse) {
+        if (!stageX(h, x) || !bcastX(h, h->d_x)) return MOCOB200_ERR_CUDA;
+        if (!jacPipeline(h, h->d_vals)) return MOCOB200_ERR_CUDA;
+    } else {
+        launch_assemble_jac(h->DL, h->d_x, h->d_Y, h->d_J, h->d_I, h->d_E, h->d_vals, h->stream);
+        h->launches++;
+    }
+    if (h->rank == 0 && values)
+        cudaMemcpyAsync(values, h->d_vals, sizeof(double) * h->L.nnz, cudaMemcpyDeviceToHost, h->stream);
+    if (!finish(h, "eval_jac_g")) return MOCOB200_ERR_CUDA;
+    rememberX(h, x, true);
+    return MOCOB200_OK;
+}
+
+int mocob200_eval_jac_g_device(mocob200_handle* h, const double* d_x, double* d_values, void* cuda_stream) {
+    if (!h || !d_x) return MOCOB200_ERR_ARG;
+    cudaSetDevice(h->device);
+    (void)cuda_stream; // the handle's own stream orders the work; the caller synchronises through mocob200_sync
+    h->x_cached.clear();
+    if (!bcastX(h, d_x)) return MOCOB200_ERR_CUDA;
+    if (!jacPipeline(h, d_values ? d_values : h->d_vals)) return MOCOB200_ERR_CUDA;
+    return h->ck(cudaGetLastError(), "eval_jac_g_device") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
+}
+
+int mocob200_eval_g_device(mocob200_handle* h, const double* d_x, double* d_g, void* cuda_stream) {
+    if (!h || !d_x) return MOCOB200_ERR_ARG;
+    cudaSetDevice(h->device);
+    (void)cuda_stream;
+    h->x_cached.clear();
+    if (!bcastX(h, d_x) || !runNominal(h)) return MOCOB200_ERR_CUDA;
+    if (h->rank == 0) { launch_assemble_g(h->DL, h->d_x, h->d_Y, h->d_G, d_g ? d_g : h->d_g, h->stream); h->launches++; }
+    return h->ck(cudaGetLastError(), "eval_g_device") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
+}
+
+// wait for everything queued on the handle's stream; elapsed_ms (optional) = time between two marks
+int mocob200_sync(mocob200_handle* h) {
+    if (!h) return MOCOB200_ERR_ARG;
+    cudaSetDevice(h->device);
+    return finish(h, "sync") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
+}
+// CUDA-event stopwatch on the handle's stream: mark(0) ... mark(1), then elapsed
+static cudaEvent_t g_marks[2] = {nullptr, nullptr};
+int mocob200_mark(mocob200_handle* h, int which) {
+    if (!h || which < 0 || which > 1) return MOCOB200_ERR_ARG;
+    cudaSetDevice(h->device);
+    if (!g_marks[which]) cudaEventCreate(&g_marks[which]);
+    return h->ck(cudaEventRecord(g_marks[which], h->stream), "mark") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
+}
+int mocob200_elapsed_ms(mocob200_handle* h, float* ms) {
+    if (!h || !ms || !g_marks[0] || !g_marks[1]) return MOCOB200_ERR_ARG;
+    if (!h->ck(cudaEventSynchronize(g_marks[1]), "elapsed")) return MOCOB200_ERR_CUDA;
+    return h->ck(cudaEventElapsedTime(ms, g_marks[0], g_marks[1]), "elapsed") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
+}
+
+long mocob200_launch_count(const mocob200_handle* h) { return h ? h->launches : 0; }
+
+int mocob200_last_kernel_ms(const mocob200_handle* h, float* point_ms, float* asm_ms) {
+    if (!h) return MOCOB200_ERR_ARG;
+    if (point_ms) { *point_ms = 0; cudaEventElapsedTime(point_ms, h->ev[0], h->ev[1]); }
+    if (asm_ms) { *asm_ms = 0; if (h->rank == 0) cudaEventElapsedTime(asm_ms, h->ev[2], h->ev[3]); }
+    return MOCOB200_OK;
+}
+
+long mocob200_point_evals_per_jacobian(const mocob200_handle* h) {
+    if (!h) return 0;
+    const Layout& L = h->L;
+    // evaluations of the dynamics callback group only (integrand-only passes are not counted)
+    long per_dir = 1;
+    if (h->fd.scheme == MOCOB200_FD_CENTRAL) per_dir = 2L * (1 + h->fd.h_iter);
+    return (long)L.n_grid * (1 + per_dir * L.n_in);
+}
+
+int mocob200_measure_fp64_peak(int device, double* tflops) {
+    if (!tflops) return MOCOB200_ERR_ARG;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) return MOCOB200_ERR_CUDA;
+    *tflops = measure_fp64_peak_tflops(device);
+    return *tflops > 0 ? MOCOB200_OK : MOCOB200_ERR_CUDA;
+}
+
+} // extern "C"

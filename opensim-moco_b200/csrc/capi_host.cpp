@@ -1,0 +1,199 @@
+// Host-only half of the C ABI: example problems, save/load of flattened problems, NLP layout.
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <limits>
+#include <random>
+#include <stdexcept>
+
+#include "host_model.h"
+#include "layout.h"
+
+using namespace mocob200;
+
+struct mocob200_problem {
+    std::unique_ptr<FlatProblem> fp;
+};
+
+namespace {
+void setErr(char* err, int errlen, const std::string& m) {
+    if (err && errlen > 0) {
+        std::snprintf(err, (size_t)errlen, "%s", m.c_str());
+    }
+}
+const unsigned kMagic = 0x4d423230u; // "MB20"
+} // namespace
+
+extern "C" {
+
+int mocob200_problem_create_example(const char* name, const char* data_dir, const char* options, mocob200_problem** out,
+                                    char* err, int errlen) {
+    if (!name || !out) return MOCOB200_ERR_ARG;
+    try {
+        auto p = new mocob200_problem;
+        p->fp = buildExample(name, data_dir ? data_dir : ".", options ? options : "");
+        *out = p;
+        return MOCOB200_OK;
+    } catch (const std::exception& e) {
+        setErr(err, errlen, e.what());
+        return MOCOB200_ERR_UNSUPPORTED;
+    }
+}
+
+int mocob200_problem_save(const mocob200_problem* p, const char* path) {
+    if (!p || !path) return MOCOB200_ERR_ARG;
+    std::ofstream f(path, std::ios::binary);
+    if (!f) return MOCOB200_ERR_IO;
+    const FlatProblem& fp = *p->fp;
+    unsigned magic = kMagic, ver = 1;
+    f.write((const char*)&magic, 4);
+    f.write((const char*)&ver, 4);
+    mocob200_tables t = fp.tables;
+    t.dbl = nullptr; t.idx = nullptr;
+    mocob200_transcription r = fp.tr;
+    r.mesh = nullptr;
+    f.write((const char*)&t, sizeof t);
+    f.write((const char*)&r, sizeof r);
+    f.write((const char*)fp.dbl.data(), (std::streamsize)(fp.dbl.size() * sizeof(double)));
+    f.write((const char*)fp.idx.data(), (std::streamsize)(fp.idx.size() * sizeof(int)));
+    f.write((const char*)fp.mesh.data(), (std::streamsize)(fp.mesh.size() * sizeof(double)));
+    return f ? MOCOB200_OK : MOCOB200_ERR_IO;
+}
+
+// options (may be NULL): "num_mesh_intervals=..;scheme=..;dynamics_mode=..;fd_scheme=.." override the stored transcription
+int mocob200_problem_load_opts(const char* path, const char* options, mocob200_problem** out, char* err, int errlen) {
+    if (!path || !out) return MOCOB200_ERR_ARG;
+    try {
+        std::ifstream f(path, std::ios::binary);
+        if (!f) throw std::runtime_error(std::string("cannot open '") + path + "'");
+        unsigned magic = 0, ver = 0;
+        f.read((char*)&magic, 4);
+        f.read((char*)&ver, 4);
+        if (magic != kMagic || ver != 1) throw std::runtime_error("not a mocob200 problem file");
+        auto fp = std::make_unique<FlatProblem>();
+        f.read((char*)&fp->tables, sizeof fp->tables);
+        f.read((char*)&fp->tr, sizeof fp->tr);
+        if (fp->tables.n_dbl < 0 || fp->tables.n_int < 0 || fp->tr.n_mesh < 2) throw std::runtime_error("corrupt problem file");
+        fp->dbl.resize(fp->tables.n_dbl);
+        fp->idx.resize(fp->tables.n_int);
+        fp->mesh.resize(fp->tr.n_mesh);
+        f.read((char*)fp->dbl.data(), (std::streamsize)(fp->dbl.size() * sizeof(double)));
+        f.read((char*)fp->idx.data(), (std::streamsize)(fp->idx.size() * sizeof(int)));
+        f.read((char*)fp->mesh.data(), (std::streamsize)(fp->mesh.size() * sizeof(double)));
+        if (!f) throw std::runtime_error("truncated problem file");
+        if (options && *options) {
+            SolverSettings S; // only the keys present in `options` are applied
+            S.num_mesh_intervals = -1;
+            S.transcription_scheme = "";
+            S.multibody_dynamics_mode = "";
+            S.optim_finite_difference_scheme = "";
+            S.applyOptions(options);
+            if (!S.mesh.empty()) fp->mesh = S.mesh;
+            else if (S.num_mesh_intervals > 0) {
+                fp->mesh.clear();
+                for (int i = 0; i <= S.num_mesh_intervals; ++i) fp->mesh.push_back(i / (double)S.num_mesh_intervals);
+            }
+            if (S.transcription_scheme == "trapezoidal") fp->tr.scheme = MOCOB200_SCHEME_TRAPEZOIDAL;
+            else if (S.transcription_scheme == "hermite-simpson") fp->tr.scheme = MOCOB200_SCHEME_HERMITE_SIMPSON;
+            else if (!S.transcription_scheme.empty()) throw std::runtime_error("unknown transcription_scheme");
+            if (S.multibody_dynamics_mode == "explicit") fp->tr.dynamics_mode = MOCOB200_DYNAMICS_EXPLICIT;
+            else if (S.multibody_dynamics_mode == "implicit") fp->tr.dynamics_mode = MOCOB200_DYNAMICS_IMPLICIT;
+            else if (!S.multibody_dynamics_mode.empty()) throw std::runtime_error("unknown multibody_dynamics_mode");
+            if (S.optim_finite_difference_scheme == "central") fp->tr.fd_scheme = MOCOB200_FD_CENTRAL;
+            else if (S.optim_finite_difference_scheme == "forward") fp->tr.fd_scheme = MOCOB200_FD_FORWARD;
+            else if (S.optim_finite_difference_scheme == "backward") fp->tr.fd_scheme = MOCOB200_FD_BACKWARD;
+            else if (!S.optim_finite_difference_scheme.empty()) throw std::runtime_error("unknown fd scheme");
+        }
+        fp->rebind();
+        auto p = new mocob200_problem;
+        p->fp = std::move(fp);
+        *out = p;
+        return MOCOB200_OK;
+    } catch (const std::exception& e) {
+        setErr(err, errlen, e.what());
+        return MOCOB200_ERR_IO;
+    }
+}
+int mocob200_problem_load(const char* path, mocob200_problem** out, char* err, int errlen) {
+    return mocob200_problem_load_opts(path, nullptr, out, err, errlen);
+}
+
+const mocob200_tables* mocob200_problem_tables(const mocob200_problem* p) { return p ? &p->fp->tables : nullptr; }
+const mocob200_transcription* mocob200_problem_transcription(const mocob200_problem* p) { return p ? &p->fp->tr : nullptr; }
+void mocob200_problem_destroy(mocob200_problem* p) { delete p; }
+
+// names as '\n'-joined strings: which = 0 states, 1 controls, 2 derivatives(aux)
+int mocob200_problem_names(const mocob200_problem* p, int which, char* buf, int buflen) {
+    if (!p || !buf) return MOCOB200_ERR_ARG;
+    const auto& v = which == 0 ? p->fp->stateNames : which == 1 ? p->fp->controlNames : p->fp->derivativeNames;
+    std::string s;
+    for (auto& n : v) { s += n; s += '\n'; }
+    std::snprintf(buf, (size_t)buflen, "%s", s.c_str());
+    return MOCOB200_OK;
+}
+
+static void fillDims(const Layout& L, mocob200_dims* d) {
+    std::memset(d, 0, sizeof *d);
+    d->n_grid = L.n_grid; d->n_mesh = L.n_mesh; d->n_var = L.n_var; d->n_con = L.n_con; d->nnz_jac = L.nnz;
+    d->ns = L.ns; d->nc = L.nc; d->nd = L.nd; d->n_in = L.n_in; d->n_out = L.n_out;
+    d->n_dyn_out = L.n_dyn_out; d->n_integrand = L.n_integrand; d->n_cost_terms = L.n_cost_terms;
+    d->first_interval = 0; d->n_intervals_local = L.n_intervals; d->rank = 0; d->world = 1;
+}
+
+int mocob200_layout(const mocob200_tables* T, const mocob200_transcription* R, mocob200_dims* dims) {
+    if (!T || !R || !dims) return MOCOB200_ERR_ARG;
+    try {
+        Layout L = buildLayout(*T, *R, true);
+        fillDims(L, dims);
+        return MOCOB200_OK;
+    } catch (const std::exception&) { return MOCOB200_ERR_UNSUPPORTED; }
+}
+
+int mocob200_layout_bounds(const mocob200_tables* T, const mocob200_transcription* R, double* xlo, double* xhi, double* glo, double* ghi) {
+    if (!T || !R) return MOCOB200_ERR_ARG;
+    try {
+        Layout L = buildLayout(*T, *R, false);
+        layoutBounds(*T, *R, L, xlo, xhi, glo, ghi);
+        return MOCOB200_OK;
+    } catch (const std::exception&) { return MOCOB200_ERR_UNSUPPORTED; }
+}
+
+int mocob200_layout_structure(const mocob200_tables* T, const mocob200_transcription* R, int* colptr, int* rowidx) {
+    if (!T || !R || !colptr || !rowidx) return MOCOB200_ERR_ARG;
+    try {
+        Layout L = buildLayout(*T, *R, true);
+        std::memcpy(colptr, L.colptr.data(), sizeof(int) * (L.n_var + 1));
+        std::memcpy(rowidx, L.rowidx.data(), sizeof(int) * L.nnz);
+        return MOCOB200_OK;
+    } catch (const std::exception&) { return MOCOB200_ERR_UNSUPPORTED; }
+}
+
+int mocob200_make_iterate(const mocob200_tables* T, const mocob200_transcription* R, long seed, double spread, double* x) {
+    if (!T || !R || !x) return MOCOB200_ERR_ARG;
+    try {
+        Layout L = buildLayout(*T, *R, false);
+        std::vector<double> lo(L.n_var), hi(L.n_var);
+        layoutBounds(*T, *R, L, lo.data(), hi.data(), nullptr, nullptr);
+        std::mt19937_64 rng((unsigned long long)(seed < 0 ? 0 : seed));
+        std::uniform_real_distribution<double> U(-1.0, 1.0);
+        for (int i = 0; i < L.n_var; ++i) {
+            double l = lo[i], h = hi[i], mid;
+            if (!std::isinf(l) && !std::isinf(h)) mid = 0.5 * (l + h);
+            else if (!std::isinf(l)) mid = l;
+            else if (!std::isinf(h)) mid = h;
+            else mid = 0;
+            double v = mid;
+            if (seed >= 0) {
+                const double half = (!std::isinf(l) && !std::isinf(h)) ? 0.5 * (h - l) : 1.0;
+                v = mid + spread * half * U(rng);
+                if (v < l) v = l;
+                if (v > h) v = h;
+            }
+            x[i] = v;
+        }
+        return MOCOB200_OK;
+    } catch (const std::exception&) { return MOCOB200_ERR_UNSUPPORTED; }
+}
+
+} // extern "C"

@@ -1,0 +1,309 @@
+// The reference's example / test problems, set up through the host mirror of the
+// MocoProblem + MocoCasADiSolver surface.  Each builder cites the reference program it follows.
+#include <cmath>
+#include <stdexcept>
+
+#include "host_model.h"
+
+namespace mocob200 {
+namespace {
+
+const double kPi = 3.14159265358979323846;
+
+bool endsWith(const std::string& s, const std::string& e) {
+    return s.size() >= e.size() && s.compare(s.size() - e.size(), e.size(), e) == 0;
+}
+std::string swapSuffix(const std::string& path, const std::string& from, const std::string& to) {
+    // std::regex_replace(name, regex("_r"), "_l") of the reference replaces every occurrence
+    std::string o;
+    for (size_t i = 0; i < path.size();) {
+        if (path.compare(i, from.size(), from) == 0) { o += to; i += from.size(); }
+        else o += path[i++];
+    }
+    return o;
+}
+
+// exampleSlidingMass.cpp:42-66 (createSlidingMassModel)
+ModelSpec slidingMassModel() {
+    ModelSpec M;
+    M.name = "sliding_mass";
+    M.gravity = Vec3();
+    BodySpec b;
+    b.name = "body";
+    b.mass = 2.0;
+    M.bodies.push_back(b);
+    JointSpec j;
+    j.name = "slider";
+    j.container = "/";
+    j.kind = MOCOB200_JOINT_SLIDER;
+    j.parent.body = -1;
+    j.child.body = 0;
+    j.coords.push_back({"position", -10, 10});
+    M.joints.push_back(j);
+    CoordActSpec a;
+    a.path = "/actuator";
+    a.coord = "position";
+    a.optimalForce = 1;
+    M.coordActs.push_back(a);
+    M.actuatorOrder.emplace_back(0, 0);
+    return M;
+}
+
+// Examples/C++/exampleSlidingMass/exampleSlidingMass.cpp:68-116 ; trapezoidal variant testMocoInterface.cpp:66-83
+std::unique_ptr<FlatProblem> slidingMass(const std::string& options) {
+    Problem P;
+    P.model = slidingMassModel();
+    P.setTimeBounds(Bounds(0), Bounds(0, 5));
+    P.setStateInfo("/slider/position/value", Bounds(-5, 5), Bounds(0), Bounds(1));
+    P.setStateInfo("/slider/position/speed", Bounds(-50, 50), Bounds(0), Bounds(0));
+    P.setControlInfo("/actuator", Bounds(-50, 50));
+    P.addGoal(MOCOB200_GOAL_FINAL_TIME, "cost");
+    SolverSettings S;
+    S.num_mesh_intervals = 50;
+    S.applyOptions(options);
+    return flatten(P, S);
+}
+
+// Moco/Tests/testMocoActuators.cpp:1050-1085 (createHangingMuscleModel)
+ModelSpec hangingMuscleModel(bool ignoreActivationDynamics, bool ignoreTendonCompliance, bool tendonExplicit) {
+    ModelSpec M;
+    M.name = "isometric_muscle";
+    M.gravity = Vec3();
+    M.gravity.v[0] = 9.81;
+    BodySpec b;
+    b.name = "body";
+    b.mass = 0.5;
+    M.bodies.push_back(b);
+    JointSpec j;
+    j.name = "joint";
+    j.container = "/";
+    j.kind = MOCOB200_JOINT_SLIDER;
+    j.parent.body = -1;
+    j.child.body = 0;
+    j.coords.push_back({"height", -10, 10});
+    M.joints.push_back(j);
+    MuscleSpec mu;
+    mu.path = "/forceset/actuator";
+    mu.maxIsometricForce = 30.0;
+    mu.optimalFiberLength = 0.10;
+    mu.tendonSlackLength = 0.05;
+    mu.tendonStrainAtOneNormForce = 0.10;
+    mu.ignoreActivationDynamics = ignoreActivationDynamics;
+    mu.ignoreTendonCompliance = ignoreTendonCompliance;
+    mu.fiberDamping = 0.01;
+    mu.tendonImplicit = !tendonExplicit;
+    mu.maxContractionVelocity = 10;
+    mu.pennationAngleAtOptimal = 0.10;
+    PathPointSpec o, i;
+    o.body = -1;
+    i.body = 0;
+    mu.points = {o, i};
+    M.muscles.push_back(mu);
+    M.actuatorOrder.emplace_back(1, 0);
+    return M;
+}
+
+// "Hanging muscle minimum time", testMocoActuators.cpp:1087-1150
+std::unique_ptr<FlatProblem> hangingMuscle(const std::string& options, bool ignoreAct, bool ignoreTendon) {
+    Problem P;
+    P.model = hangingMuscleModel(ignoreAct, ignoreTendon, false);
+    P.setTimeBounds(Bounds(0), Bounds(0.05, 1.0));
+    P.setStateInfo("/joint/height/value", Bounds(0.14, 0.16), Bounds(0.15), Bounds(0.14));
+    P.setStateInfo("/joint/height/speed", Bounds(-1, 1), Bounds(0), Bounds(0));
+    P.setControlInfo("/forceset/actuator", Bounds(0.01, 1));
+    if (!ignoreAct) P.addGoal(MOCOB200_GOAL_INITIAL_ACTIVATION, "initial_activation");
+    if (!ignoreTendon) {
+        GoalSpec& g = P.addGoal(MOCOB200_GOAL_INITIAL_VELOCITY_EQUILIBRIUM_DGF, "initial_velocity_equilibrium", 0.001);
+        g.mode = MOCOB200_MODE_COST;
+    }
+    P.addGoal(MOCOB200_GOAL_FINAL_TIME, "cost");
+    SolverSettings S;
+    S.num_mesh_intervals = 25;
+    S.multibody_dynamics_mode = "implicit";
+    S.optim_convergence_tolerance = 1e-4;
+    S.optim_constraint_tolerance = 1e-4;
+    S.applyOptions(options);
+    return flatten(P, S);
+}
+
+// Moco/Moco/Components/ModelFactory.cpp:33-89 (createNLinkPendulum) with a swing-up problem
+// in the style of testImplicit.cpp:29-112.
+std::unique_ptr<FlatProblem> pendulum(int n, const std::string& options) {
+    if (n < 1) throw std::runtime_error("pendulum:<N> needs N >= 1");
+    Problem P;
+    ModelSpec& M = P.model;
+    M.name = std::to_string(n) + "_link_pendulum";
+    for (int i = 0; i < n; ++i) {
+        const std::string is = std::to_string(i);
+        BodySpec b;
+        b.name = "b" + is;
+        b.mass = 1;
+        b.inertiaCom[0] = b.inertiaCom[1] = b.inertiaCom[2] = 1;
+        M.bodies.push_back(b);
+        JointSpec j;
+        j.name = "j" + is;
+        j.kind = MOCOB200_JOINT_PIN;
+        j.parent.body = i - 1;
+        j.child.body = i;
+        j.child.X.p.v[0] = -1;
+        j.coords.push_back({"q" + is, -10, 10});
+        M.joints.push_back(j);
+        CoordActSpec a;
+        a.path = "/tau" + is;
+        a.coord = "q" + is;
+        M.coordActs.push_back(a);
+        M.actuatorOrder.emplace_back(0, i);
+    }
+    P.setTimeBounds(Bounds(0), Bounds(0.5, 5));
+    for (int i = 0; i < n; ++i) {
+        const std::string is = std::to_string(i);
+        P.setStateInfo("/jointset/j" + is + "/q" + is + "/value", Bounds(-10, 10), Bounds(0), Bounds(i == 0 ? kPi : 0.0));
+        P.setStateInfo("/jointset/j" + is + "/q" + is + "/speed", Bounds(-50, 50), Bounds(0), Bounds(0));
+        P.setControlInfo("/tau" + is, Bounds(-100, 100));
+    }
+    P.addGoal(MOCOB200_GOAL_CONTROL, "effort");
+    P.addGoal(MOCOB200_GOAL_FINAL_TIME, "time", 0.1);
+    SolverSettings S;
+    S.num_mesh_intervals = 20;
+    S.applyOptions(options);
+    return flatten(P, S);
+}
+
+// symmetry goal shared by gaitTracking / gaitPrediction (example2DWalking.cpp:80-126, 225-271)
+void addSymmetryGoal(Problem& P) {
+    GoalSpec& g = P.addGoal(MOCOB200_GOAL_PERIODICITY, "symmetryGoal");
+    for (const JointSpec& J : P.model.joints)
+        for (const CoordSpec& c : J.coords) {
+            const std::string base = J.container + J.name + "/" + c.name;
+            const std::string sv[2] = {base + "/value", base + "/speed"};
+            if (endsWith(c.name, "_r"))
+                for (auto& s : sv) g.statePairs.push_back({s, swapSuffix(s, "_r", "_l"), 1});
+            if (endsWith(c.name, "_l"))
+                for (auto& s : sv) g.statePairs.push_back({s, swapSuffix(s, "_l", "_r"), 1});
+            if (!endsWith(c.name, "_l") && !endsWith(c.name, "_r") && !endsWith(c.name, "_tx"))
+                for (auto& s : sv) g.statePairs.push_back({s, s, 1});
+        }
+    g.statePairs.push_back({"/jointset/groundPelvis/pelvis_tx/speed", "", 1});
+    g.controlPairs.push_back({"/lumbarAct", "", 1});
+    for (const MuscleSpec& mu : P.model.muscles) {
+        const std::string s = mu.path + "/activation";
+        if (endsWith(mu.path, "_r")) g.statePairs.push_back({s, swapSuffix(s, "_r", "_l"), 1});
+        if (endsWith(mu.path, "_l")) g.statePairs.push_back({s, swapSuffix(s, "_l", "_r"), 1});
+    }
+}
+void setGaitBounds(Problem& P) { // example2DWalking.cpp:151-169
+    const double d = kPi / 180;
+    P.setStateInfo("/jointset/groundPelvis/pelvis_tilt/value", Bounds(-20 * d, -10 * d));
+    P.setStateInfo("/jointset/groundPelvis/pelvis_tx/value", Bounds(0, 1));
+    P.setStateInfo("/jointset/groundPelvis/pelvis_ty/value", Bounds(0.75, 1.25));
+    P.setStateInfo("/jointset/hip_l/hip_flexion_l/value", Bounds(-10 * d, 60 * d));
+    P.setStateInfo("/jointset/hip_r/hip_flexion_r/value", Bounds(-10 * d, 60 * d));
+    P.setStateInfo("/jointset/knee_l/knee_angle_l/value", Bounds(-50 * d, 0));
+    P.setStateInfo("/jointset/knee_r/knee_angle_r/value", Bounds(-50 * d, 0));
+    P.setStateInfo("/jointset/ankle_l/ankle_angle_l/value", Bounds(-15 * d, 25 * d));
+    P.setStateInfo("/jointset/ankle_r/ankle_angle_r/value", Bounds(-15 * d, 25 * d));
+    P.setStateInfo("/jointset/lumbar/lumbar/value", Bounds(0, 20 * d));
+}
+
+// example2DWalking.cpp:58-204 (gaitTracking through MocoTrack, MocoTrack.cpp:54-233).
+// The reference low-pass filters the coordinate table at 6 Hz before splining
+// (TabOpLowPassFilter); table pre-processing is outside the evaluator and the
+// raw table is splined here.
+std::unique_ptr<FlatProblem> gaitTracking(const std::string& dir, const std::string& options) {
+    Problem P;
+    P.model = loadOsim(dir + "/2D_gait.osim");
+    StoTable ref = readSto(dir + "/referenceCoordinates.sto");
+    // state tracking goal: values from the table, speeds = derivative of the value spline at the
+    // table times (track_reference_position_derivatives, MocoTrack.cpp:180-191), all re-splined (degree 5)
+    GoalSpec& st = P.addGoal(MOCOB200_GOAL_STATE_TRACKING, "state_tracking", 1.0);
+    std::vector<GoalSpec::Ref> speeds;
+    for (size_t c = 0; c < ref.labels.size(); ++c) {
+        GoalSpec::Ref r;
+        r.name = ref.labels[c];
+        r.spline = fitNaturalSpline(ref.time, ref.cols[c], 5);
+        st.refs.push_back(r);
+    }
+    for (const JointSpec& J : P.model.joints)
+        for (const CoordSpec& c : J.coords) {
+            const std::string base = J.container + J.name + "/" + c.name;
+            const int ci = ref.col(base + "/value");
+            if (ci < 0 || ref.col(base + "/speed") >= 0) continue;
+            std::vector<double> sp(ref.time.size());
+            for (size_t k = 0; k < ref.time.size(); ++k) sp[k] = evalPiecewisePoly(st.refs[ci].spline, ref.time[k], 1);
+            GoalSpec::Ref r;
+            r.name = base + "/speed";
+            r.spline = fitNaturalSpline(ref.time, sp, 5);
+            speeds.push_back(r);
+        }
+    st.refs.insert(st.refs.end(), speeds.begin(), speeds.end());
+    P.addGoal(MOCOB200_GOAL_CONTROL, "control_effort", 10.0);
+    P.setTimeBounds(Bounds(0.0), Bounds(0.47008941));
+    addSymmetryGoal(P);
+    {
+        StoTable grf = readSto(dir + "/referenceGRF.sto");
+        GoalSpec& ct = P.addGoal(MOCOB200_GOAL_CONTACT_TRACKING, "contact", 1.0);
+        auto group = [&](std::vector<std::string> cs, const std::string& body, const std::string& id) {
+            GoalSpec::ContactGroup g;
+            g.contacts = cs;
+            g.appliedToBody = body;
+            const char* ax[3] = {"x", "y", "z"};
+            for (int a = 0; a < 3; ++a) {
+                const int ci = grf.col(id + ax[a]);
+                if (ci < 0) throw std::runtime_error("referenceGRF.sto lacks column " + id + ax[a]);
+                g.ref[a] = fitNaturalSpline(grf.time, grf.cols[ci], 5);
+            }
+            ct.groups.push_back(g);
+        };
+        // referenceGRF.xml: Right_GRF applied_to_body calcn_r, force_identifier ground_force_r_v
+        group({"contactHeel_r", "contactFront_r"}, "calcn_r", "ground_force_r_v");
+        group({"contactHeel_l", "contactFront_l"}, "calcn_l", "ground_force_l_v");
+        ct.projection = 2; // "plane"
+        ct.projectionVector.v[2] = 1;
+    }
+    setGaitBounds(P);
+    SolverSettings S;
+    S.num_mesh_intervals = 50;
+    S.multibody_dynamics_mode = "explicit";
+    S.optim_finite_difference_scheme = "forward"; // MocoTrack.cpp:112
+    S.optim_convergence_tolerance = 1e-4;
+    S.optim_constraint_tolerance = 1e-4;
+    S.optim_max_iterations = 1000;
+    S.applyOptions(options);
+    return flatten(P, S);
+}
+
+// example2DWalking.cpp:211-340 (gaitPrediction). BASELINE config 5 runs it at 800 mesh intervals.
+std::unique_ptr<FlatProblem> gaitPrediction(const std::string& dir, const std::string& options) {
+    Problem P;
+    P.model = loadOsim(dir + "/2D_gait.osim");
+    addSymmetryGoal(P);
+    GoalSpec& sp = P.addGoal(MOCOB200_GOAL_AVERAGE_SPEED, "speed");
+    sp.desiredAverageSpeed = 1.2;
+    GoalSpec& ef = P.addGoal(MOCOB200_GOAL_CONTROL, "effort", 10);
+    ef.exponent = 3;
+    ef.divideByDisplacement = true;
+    P.setTimeBounds(Bounds(0), Bounds(0.4, 0.6));
+    setGaitBounds(P);
+    SolverSettings S;
+    S.num_mesh_intervals = 50;
+    S.optim_convergence_tolerance = 1e-4;
+    S.optim_constraint_tolerance = 1e-4;
+    S.optim_max_iterations = 1000;
+    S.applyOptions(options);
+    return flatten(P, S);
+}
+
+} // namespace
+
+std::unique_ptr<FlatProblem> buildExample(const std::string& name, const std::string& dataDir, const std::string& options) {
+    if (name == "sliding_mass") return slidingMass(options);
+    if (name == "hanging_muscle") return hangingMuscle(options, false, false);
+    if (name == "hanging_muscle_rigidtendon") return hangingMuscle(options, false, true);
+    if (name == "hanging_muscle_noactdyn") return hangingMuscle(options, true, false);
+    if (name.rfind("pendulum:", 0) == 0) return pendulum(std::stoi(name.substr(9)), options);
+    if (name == "gait2d_tracking") return gaitTracking(dataDir, options);
+    if (name == "gait2d_prediction") return gaitPrediction(dataDir, options);
+    throw std::runtime_error("unknown example '" + name + "'");
+}
+
+} // namespace mocob200

@@ -1,0 +1,236 @@
+// Host-side description of a fixed-topology model + optimal control problem, and
+// its flattening into the POD pools of include/mocob200.h.
+//
+// The classes mirror, name for name, the slice of the reference's surface that the
+// BASELINE configs touch (MocoProblem::setTimeBounds/setStateInfo/setControlInfo/addGoal,
+// MocoCasADiSolver's properties) so that problem set-up code reads like the reference's
+// examples; they hold plain data and never evaluate dynamics.
+#pragma once
+#include <array>
+#include <cmath>
+#include <limits>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/mocob200.h"
+
+namespace mocob200 {
+
+struct Vec3 {
+    double v[3] = {0, 0, 0};
+    double& operator[](int i) { return v[i]; }
+    double operator[](int i) const { return v[i]; }
+};
+struct Mat3 { // row-major
+    double m[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+};
+struct Xform { // x_outer = R * x_inner + p
+    Mat3 R;
+    Vec3 p;
+};
+Mat3 mul(const Mat3& a, const Mat3& b);
+Vec3 mul(const Mat3& a, const Vec3& x);
+Xform compose(const Xform& a, const Xform& b); // a∘b
+Xform inverse(const Xform& a);
+Mat3 rotXYZ(double a, double b, double c); // body-fixed X-Y-Z (PhysicalOffsetFrame orientation)
+
+struct FrameRef { // a frame fixed on a body: body index (-1 = ground) + transform in the body's base frame
+    int body = -1;
+    Xform X;
+};
+
+struct BodySpec {
+    std::string name;
+    double mass = 0;
+    Vec3 com;
+    double inertiaCom[6] = {0, 0, 0, 0, 0, 0}; // xx yy zz xy xz yz about the mass centre
+};
+struct CoordSpec {
+    std::string name;
+    double lo = -10, hi = 10;
+};
+struct JointSpec {
+    std::string name;
+    std::string container = "/jointset/"; // "/" when added with Model::addComponent
+    int kind = MOCOB200_JOINT_WELD;
+    FrameRef parent, child;
+    std::vector<CoordSpec> coords;
+};
+struct SplineSpec { // SimmSpline wrapped in a MultiplierFunction
+    std::vector<double> x, y;
+    double scale = 1;
+};
+struct PathPointSpec {
+    int kind = MOCOB200_PP_FIXED;
+    int body = -1;
+    Vec3 location; // already expressed in the body's base frame
+    std::string condCoord;
+    double range[2] = {0, 0};
+    SplineSpec fn[3];
+    std::string coord[3];
+};
+struct MuscleSpec { // DeGrooteFregly2016Muscle properties (Components/DeGrooteFregly2016Muscle.cpp:52-63)
+    std::string path; // absolute path, e.g. "/hamstrings_r" or "/forceset/muscle"
+    double maxIsometricForce = 1000, optimalFiberLength = 0.1, tendonSlackLength = 0.2;
+    double pennationAngleAtOptimal = 0, maxContractionVelocity = 10;
+    double activationTimeConstant = 0.015, deactivationTimeConstant = 0.060;
+    double defaultActivation = 0.5, defaultNormalizedTendonForce = 0.5;
+    double activeForceWidthScale = 1.0, fiberDamping = 0.0;
+    double passiveFiberStrainAtOneNormForce = 0.6, tendonStrainAtOneNormForce = 0.049;
+    double minControl = 0, maxControl = 1;
+    bool ignoreTendonCompliance = false, ignoreActivationDynamics = false, ignorePassiveFiberForce = false;
+    bool tendonImplicit = false; // tendon_compliance_dynamics_mode == "implicit"
+    std::vector<PathPointSpec> points;
+};
+struct ContactSpec { // SmoothSphereHalfSpaceForce + its ContactSphere / ContactHalfSpace
+    std::string name;
+    FrameRef sphere; // X.p = sphere centre
+    double radius = 0.01;
+    FrameRef halfSpace;
+    double stiffness = 1, dissipation = 0, muS = 0, muD = 0, muV = 0, vT = 0.01, cF = 1e-5, bD = 300, bV = 50;
+};
+struct CoordActSpec {
+    std::string path;
+    std::string coord;
+    double optimalForce = 1, minControl = -std::numeric_limits<double>::infinity(),
+           maxControl = std::numeric_limits<double>::infinity();
+};
+
+struct ModelSpec {
+    std::string name;
+    Vec3 gravity;
+    std::vector<BodySpec> bodies;
+    std::vector<JointSpec> joints;
+    std::vector<MuscleSpec> muscles;
+    std::vector<ContactSpec> contacts;
+    std::vector<CoordActSpec> coordActs;
+    std::vector<std::pair<int, int>> actuatorOrder; // (0 = coordinate actuator, 1 = muscle ; index) in component order
+    ModelSpec() { gravity.v[1] = -9.80665; }
+    int bodyIndex(const std::string& n) const;
+};
+
+ModelSpec loadOsim(const std::string& path); // .osim document Version 40000 subset
+
+// ---- the optimal control problem (MocoProblem / MocoPhase surface) ----
+struct Bounds {
+    double lo = std::numeric_limits<double>::quiet_NaN(), hi = std::numeric_limits<double>::quiet_NaN();
+    Bounds() {}
+    Bounds(double v) : lo(v), hi(v) {}
+    Bounds(double a, double b) : lo(a), hi(b) {}
+    bool isSet() const { return !std::isnan(lo); }
+};
+struct VariableInfo {
+    Bounds bounds, initial, final;
+};
+struct PiecewisePoly { // value(t) on [breaks[k], breaks[k+1]) = sum_j coef[k*order+j] (t-breaks[k])^j
+    std::vector<double> breaks, coef;
+    int order = 0;
+};
+// natural interpolating spline of odd degree (what GCVSPL returns for zero smoothing), as a piecewise polynomial
+PiecewisePoly fitNaturalSpline(const std::vector<double>& t, const std::vector<double>& y, int degree);
+double evalPiecewisePoly(const PiecewisePoly& pp, double t, int deriv = 0);
+
+struct GoalSpec {
+    int kind = MOCOB200_GOAL_CONTROL;
+    std::string name;
+    double weight = 1;
+    int mode = -1; // -1: the goal's default mode
+    // control goal
+    std::map<std::string, double> controlWeights;
+    int exponent = 2;
+    bool divideByDisplacement = false;
+    // tracking goals: (state/control name, weight, reference)
+    struct Ref {
+        std::string name;
+        double weight = 1;
+        PiecewisePoly spline;
+    };
+    std::vector<Ref> refs;
+    // contact tracking
+    struct ContactGroup {
+        std::vector<std::string> contacts;
+        std::string appliedToBody;
+        PiecewisePoly ref[3];
+    };
+    std::vector<ContactGroup> groups;
+    int projection = 0; // 0 none, 1 vector, 2 plane
+    Vec3 projectionVector;
+    // periodicity: (initial name, final name, sign)
+    struct Pair {
+        std::string a, b;
+        double sign = 1;
+    };
+    std::vector<Pair> statePairs, controlPairs;
+    // average speed
+    double desiredAverageSpeed = 0;
+    // endpoint-constraint bounds (default 0,0)
+    Bounds ecBounds{0, 0};
+};
+
+struct Problem {
+    ModelSpec model;
+    Bounds timeInitial{0}, timeFinal{1};
+    std::map<std::string, VariableInfo> stateInfos, controlInfos;
+    Bounds defaultSpeedBounds{-50, 50};
+    bool boundActivationFromExcitation = true;
+    std::vector<GoalSpec> goals;
+
+    void setTimeBounds(Bounds i, Bounds f) { timeInitial = i; timeFinal = f; }
+    void setStateInfo(const std::string& n, Bounds b, Bounds i = {}, Bounds f = {}) { stateInfos[n] = {b, i, f}; }
+    void setControlInfo(const std::string& n, Bounds b, Bounds i = {}, Bounds f = {}) { controlInfos[n] = {b, i, f}; }
+    GoalSpec& addGoal(int kind, const std::string& name, double weight = 1) {
+        goals.emplace_back();
+        goals.back().kind = kind;
+        goals.back().name = name;
+        goals.back().weight = weight;
+        return goals.back();
+    }
+};
+
+// MocoCasADiSolver / MocoDirectCollocationSolver properties that shape the NLP.
+struct SolverSettings {
+    int num_mesh_intervals = 100;
+    std::vector<double> mesh;
+    std::string transcription_scheme = "hermite-simpson";
+    bool interpolate_control_midpoints = true;
+    std::string multibody_dynamics_mode = "explicit";
+    std::string optim_finite_difference_scheme = "central";
+    std::string optim_sparsity_detection = "none";
+    Bounds implicit_multibody_acceleration_bounds{-1000, 1000};
+    Bounds implicit_auxiliary_derivative_bounds{-1000, 1000};
+    bool minimize_implicit_multibody_accelerations = false;
+    double implicit_multibody_accelerations_weight = 1.0;
+    bool minimize_implicit_auxiliary_derivatives = false;
+    double implicit_auxiliary_derivatives_weight = 1.0;
+    // IPOPT-side properties are carried but unused by the evaluator
+    double optim_convergence_tolerance = -1, optim_constraint_tolerance = -1;
+    int optim_max_iterations = -1;
+    void applyOptions(const std::string& opts); // "key=value;key=value"
+};
+
+// Owner of one flattened problem (pools + transcription).
+struct FlatProblem {
+    std::vector<double> dbl;
+    std::vector<int> idx;
+    std::vector<double> mesh;
+    mocob200_tables tables{};
+    mocob200_transcription tr{};
+    std::vector<std::string> stateNames, controlNames, derivativeNames;
+    void rebind(); // re-point tables.dbl/idx and tr.mesh after a copy/load
+};
+
+std::unique_ptr<FlatProblem> flatten(const Problem& p, const SolverSettings& s);
+std::unique_ptr<FlatProblem> buildExample(const std::string& name, const std::string& dataDir, const std::string& options);
+
+// simple .sto/.mot table
+struct StoTable {
+    std::vector<std::string> labels; // without "time"
+    std::vector<double> time;
+    std::vector<std::vector<double>> cols; // [label][row]
+    int col(const std::string& l) const;
+};
+StoTable readSto(const std::string& path);
+
+} // namespace mocob200

@@ -1,0 +1,455 @@
+// Kernels: point functions over the grid (+ CasADi-style finite differences), endpoint functions,
+// and assembly of g, jac_g (CSC), f and grad_f.  FP64, sm_100a.
+#include <cstdio>
+
+#include "kernels.cuh"
+
+namespace mocob200 {
+
+// ---------------------------------------------------------------------------------------------
+// gather the inputs of grid point j from the NLP vector x (CasOCTranscription.h:192-199 layout)
+__device__ __forceinline__ void gather_inputs(const DevLayout& L, const double* __restrict__ x, int j, double* in) {
+    const double t0 = x[0], tf = x[1];
+    in[0] = t0 + (tf - t0) * L.grid[j]; // createTimes (CasOCTranscription.h: m_times)
+    const double* xs = x + L.off_states + (size_t)j * L.ns;
+    for (int k = 0; k < L.ns; ++k) in[1 + k] = xs[k];
+    const double* xc = x + L.off_controls + (size_t)j * L.nc;
+    for (int k = 0; k < L.nc; ++k) in[1 + L.ns + k] = xc[k];
+    const double* xd = x + L.off_derivs + (size_t)j * L.nd;
+    for (int k = 0; k < L.nd; ++k) in[1 + L.ns + L.nc + k] = xd[k];
+}
+
+__global__ void k_points_nominal(DevTables T, DevLayout L, const double* __restrict__ x, double* __restrict__ Y, int p0, int np) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= np) return;
+    const int j = p0 + t;
+    double in[MOCOB200_MAX_IN], out[MOCOB200_MAX_OUT];
+    gather_inputs(L, x, j, in);
+    eval_point(T, in, out, 0xffffffffu);
+    for (int o = 0; o < L.n_out; ++o) Y[(size_t)j * L.n_out + o] = out[o];
+}
+
+// One finite-difference column of one callback group, following CasADi's FiniteDiff
+// (casadi/core/finite_differences.cpp of the pinned fork; restated from its documented algorithm):
+//   forward : (f(x+h v) - f(x)) / h                       h = sqrt(abstol)
+//   backward: (f(x) - f(x-h v)) / h
+//   central : (f(x+h v) - f(x-h v)) / 2h, h = abstol^(1/3); after each of h_iter passes the ratio
+//             u = max_i |yf-2yc+yb| / (reltol/h max(|yf-yc|,|yc-yb|) + abstol) rescales h by
+//             sqrt(u_aim / max(1,u)) (or h /= u_aim if an output was not finite).
+// `lo,hi` select the output range of the group, `mask` the eval_point group bit.
+template <class F>
+__device__ inline void fd_group(F&& f, const FdSettings& fd, double* in, int a, const double* y0, int lo, int hi, double* yb,
+                                double* yf, double* Jcol) {
+    const double x0 = in[a];
+    if (fd.scheme != MOCOB200_FD_CENTRAL) {
+        const double h = fd.h;
+        const double pert = (fd.scheme == MOCOB200_FD_FORWARD) ? h : -h;
+        in[a] = x0 + pert;
+        f(in, yf);
+        in[a] = x0;
+        for (int o = lo; o < hi; ++o) Jcol[o] = (fd.scheme == MOCOB200_FD_FORWARD) ? (yf[o] - y0[o]) / h : (y0[o] - yf[o]) / h;
+        return;
+    }
+    double h = fd.h;
+    for (int iter = 0;; ++iter) {
+        in[a] = x0 - h;
+        f(in, yb);
+        in[a] = x0 + h;
+        f(in, yf);
+        in[a] = x0;
+        double u = 0;
+        for (int o = lo; o < hi; ++o) {
+            const double vf = yf[o], vc = y0[o], vb = yb[o];
+            if (!isfinite(vf) || !isfinite(vc) || !isfinite(vb)) { Jcol[o] = NAN; u = -1; continue; }
+            Jcol[o] = (vf - vb) / (2 * h);
+            const double et = vf - 2 * vc + vb;
+            const double er = fd.reltol / h * fmax(fabs(vf - vc), fabs(vc - vb)) + fd.abstol;
+            if (u >= 0) u = fmax(u, fabs(et / er));
+        }
+        if (iter == fd.h_iter) break;
+        if (u < 0) h /= fd.u_aim;
+        else h *= sqrt(fd.u_aim / fmax(1.0, u));
+    }
+}
+
+// block = one grid point; thread a < n_in = FD direction a; thread n_in = nominal evaluation.
+__global__ void __launch_bounds__(256)
+k_points_fd(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ x, double* __restrict__ Y, double* __restrict__ J, int p0) {
+    extern __shared__ double sh_y0[]; // [n_out]
+    const int j = p0 + blockIdx.x;
+    const int a = threadIdx.x;
+    double in[MOCOB200_MAX_IN];
+    double ya[MOCOB200_MAX_OUT], yb[MOCOB200_MAX_OUT], Jc[MOCOB200_MAX_OUT];
+    const bool active = a <= L.n_in;
+    if (active) gather_inputs(L, x, j, in);
+    if (a == L.n_in) {
+        eval_point(T, in, ya, 0xffffffffu);
+        for (int o = 0; o < L.n_out; ++o) { sh_y0[o] = ya[o]; Y[(size_t)j * L.n_out + o] = ya[o]; }
+    }
+    const bool central = fd.scheme == MOCOB200_FD_CENTRAL;
+    if (a < L.n_in && !central) {
+        // forward/backward need no nominal value until the difference: evaluate before the barrier
+        const double x0 = in[a];
+        const double pert = (fd.scheme == MOCOB200_FD_FORWARD) ? fd.h : -fd.h;
+        in[a] = x0 + pert;
+        eval_point(T, in, ya, 0xffffffffu);
+        in[a] = x0;
+    }
+    __syncthreads();
+    if (a >= L.n_in) return;
+    if (!central) {
+        const double h = fd.h;
+        for (int o = 0; o < L.n_out; ++o) Jc[o] = (fd.scheme == MOCOB200_FD_FORWARD) ? (ya[o] - sh_y0[o]) / h : (sh_y0[o] - ya[o]) / h;
+    } else {
+        // every reference callback refines its own step: group 0 = dynamics, group 1+k = integrand k
+        const int ngroups = 1 + L.n_integrand;
+        for (int gidx = 0; gidx < ngroups; ++gidx) {
+            const unsigned mask = 1u << gidx;
+            const int lo = gidx == 0 ? 0 : L.n_dyn_out + gidx - 1;
+            const int hi = gidx == 0 ? L.n_dyn_out : lo + 1;
+            fd_group([&](const double* xin, double* yout) { eval_point(T, xin, yout, mask); }, fd, in, a, sh_y0, lo, hi, yb, ya, Jc);
+        }
+    }
+    double* Jp = J + (size_t)j * L.n_out * L.n_in;
+    for (int o = 0; o < L.n_out; ++o) Jp[(size_t)o * L.n_in + a] = Jc[o];
+}
+
+// ---------------------------------------------------------------------------------------------
+// integrals of the goal integrands: I_k = T * sum_j quad_j * integrand_k(j)  (CasOCTranscription.cpp:489-493)
+// d_I = [I (n_integrand) | dI/dt0 | dI/dtf]
+__global__ void k_integrals(DevLayout L, const double* __restrict__ x, const double* __restrict__ Y, const double* __restrict__ J, double* I, int withJ) {
+    __shared__ double red[3][256];
+    const int k = blockIdx.x;
+    const double T = x[1] - x[0];
+    double s0 = 0, s1 = 0, s2 = 0;
+    const int row = L.n_dyn_out + k;
+    for (int j = threadIdx.x; j < L.n_grid; j += blockDim.x) {
+        const double qj = L.quad[j];
+        s0 += qj * Y[(size_t)j * L.n_out + row];
+        if (withJ) {
+            const double dydt = J[((size_t)j * L.n_out + row) * L.n_in];
+            s1 += qj * dydt * (1.0 - L.grid[j]);
+            s2 += qj * dydt * L.grid[j];
+        }
+    }
+    red[0][threadIdx.x] = s0; red[1][threadIdx.x] = s1; red[2][threadIdx.x] = s2;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a0 = 0, a1 = 0, a2 = 0;
+        for (int t = 0; t < blockDim.x; ++t) { a0 += red[0][t]; a1 += red[1][t]; a2 += red[2][t]; }
+        I[k] = T * a0;
+        I[L.n_integrand + k] = -a0 + T * a1;
+        I[2 * L.n_integrand + k] = a0 + T * a2;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// endpoint functions of all goals + their FD blocks. One block; thread a < n_ein = direction, thread n_ein = nominal.
+__device__ inline void gather_endpoint_inputs(const DevTables& T, const DevLayout& L, const double* x, int g, const double* I, double* ein) {
+    const int half = 1 + L.ns + L.nc + L.nd;
+    const int last = L.n_grid - 1;
+    ein[0] = x[0];
+    ein[half] = x[1];
+    for (int k = 0; k < L.ns; ++k) { ein[1 + k] = x[L.off_states + k]; ein[half + 1 + k] = x[L.off_states + (size_t)last * L.ns + k]; }
+    for (int k = 0; k < L.nc; ++k) { ein[1 + L.ns + k] = x[L.off_controls + k]; ein[half + 1 + L.ns + k] = x[L.off_controls + (size_t)last * L.nc + k]; }
+    for (int k = 0; k < L.nd; ++k) { ein[1 + L.ns + L.nc + k] = x[L.off_derivs + k]; ein[half + 1 + L.ns + L.nc + k] = x[L.off_derivs + (size_t)last * L.nd + k]; }
+    ein[2 * half] = (L.goal_integrand[g] >= 0) ? I[L.goal_integrand[g]] : NAN; // integral is NaN without an integrand (:495)
+}
+
+__global__ void k_endpoint(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ x, const double* __restrict__ I,
+                           double* __restrict__ G, double* __restrict__ E, int withFd) {
+    extern __shared__ double sh_g0[]; // [n_eout_total]
+    const int a = threadIdx.x;
+    if (a > L.n_ein) return;
+    double ein[2 * MOCOB200_MAX_IN + 8];
+    double v0[MOCOB200_MAX_EOUT], v1[MOCOB200_MAX_EOUT], Jc[MOCOB200_MAX_EOUT];
+    if (a == L.n_ein) {
+        for (int g = 0; g < T.ngoal; ++g) {
+            const int nout = T.idx[T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE + 2];
+            gather_endpoint_inputs(T, L, x, g, I, ein);
+            eval_endpoint(T, g, ein, L.ns, L.nc, L.nd, v0);
+            for (int o = 0; o < nout; ++o) { sh_g0[L.goal_eoff[g] + o] = v0[o]; G[L.goal_eoff[g] + o] = v0[o]; }
+        }
+    }
+    __syncthreads();
+    if (!withFd || a == L.n_ein) return;
+    for (int g = 0; g < T.ngoal; ++g) {
+        const int nout = T.idx[T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE + 2];
+        gather_endpoint_inputs(T, L, x, g, I, ein);
+        const bool nanIntegral = (a == L.n_ein - 1) && L.goal_integrand[g] < 0;
+        if (nanIntegral) { // perturbing a NaN input: the reference's FD yields NaN - NaN; the block entry is structurally unused
+            for (int o = 0; o < nout; ++o) E[(size_t)(L.goal_eoff[g] + o) * L.n_ein + a] = 0.0;
+            continue;
+        }
+        fd_group([&](const double* xin, double* yout) { eval_endpoint(T, g, xin, L.ns, L.nc, L.nd, yout); }, fd, ein, a,
+                 sh_g0 + L.goal_eoff[g], 0, nout, v0, v1, Jc);
+        for (int o = 0; o < nout; ++o) E[(size_t)(L.goal_eoff[g] + o) * L.n_ein + a] = Jc[o];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double xdot_val(const DevLayout& L, const double* x, const double* Y, int j, int s) {
+    if (s < L.nq) return x[L.off_states + (size_t)j * L.ns + L.nq + s];                     // qdot = u (:313-314)
+    if (s < 2 * L.nq && L.implicit) return x[L.off_derivs + (size_t)j * L.nd + (s - L.nq)]; // udot = w
+    return Y[(size_t)j * L.n_out + (s - L.nq)];
+}
+__device__ __forceinline__ double dxdot(const DevLayout& L, const double* J, int j, int s, const ColMetaD& c) {
+    if (s < L.nq) return (c.kind == COL_STATE_D && c.k == L.nq + s) ? 1.0 : 0.0;
+    if (s < 2 * L.nq && L.implicit) return (c.kind == COL_DERIV_D && c.k == s - L.nq) ? 1.0 : 0.0;
+    return J[((size_t)j * L.n_out + (s - L.nq)) * L.n_in + c.in];
+}
+__device__ __forceinline__ double dxdot_dt(const DevLayout& L, const double* J, int j, int s) {
+    if (s < L.nq) return 0.0;
+    if (s < 2 * L.nq && L.implicit) return 0.0;
+    return J[((size_t)j * L.n_out + (s - L.nq)) * L.n_in];
+}
+// defect coefficients: defect = sum_role lin_role * x_role,s + sum_role (wc_role * h) * xdot_role,s
+__device__ __forceinline__ void defect_coeffs(int kind, int role, double& lin, double& wc) {
+    if (kind == ROW_DEFECT_HERMITE_D) { // x_mid - (x_ip + x_i)/2 - h/8 (xdot_i - xdot_ip)
+        lin = role == 1 ? 1.0 : -0.5;
+        wc = role == 0 ? -1.0 / 8.0 : (role == 2 ? 1.0 / 8.0 : 0.0);
+    } else if (kind == ROW_DEFECT_SIMPSON_D) { // x_ip - x_i - h/6 (xdot_ip + 4 xdot_mid + xdot_i)
+        lin = role == 0 ? -1.0 : (role == 2 ? 1.0 : 0.0);
+        wc = role == 1 ? -4.0 / 6.0 : -1.0 / 6.0;
+    } else { // trapezoidal: x_ip - (x_i + h/2 (xdot_ip + xdot_i))
+        lin = role == 0 ? -1.0 : 1.0;
+        wc = -0.5;
+    }
+}
+
+__global__ void k_assemble_g(DevLayout L, const double* __restrict__ x, const double* __restrict__ Y, const double* __restrict__ G,
+                             double* __restrict__ g) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= L.n_con) return;
+    const RowMetaD rm = L.rows[r];
+    const bool hs = L.scheme == MOCOB200_SCHEME_HERMITE_SIMPSON;
+    double v = 0;
+    if (rm.kind == ROW_ENDPOINT_D) v = G[L.goal_eoff[rm.a] + rm.b];
+    else if (rm.kind == ROW_RESIDUAL_D) v = Y[(size_t)rm.a * L.n_out + rm.b];
+    else if (rm.kind == ROW_INTERP_D) {
+        const int m = rm.a, c = rm.b;
+        const double* xc = x + L.off_controls;
+        v = xc[(size_t)(2 * m + 1) * L.nc + c] - 0.5 * (xc[(size_t)(2 * m + 2) * L.nc + c] + xc[(size_t)(2 * m) * L.nc + c]);
+    } else {
+        const int m = rm.a, s = rm.b;
+        const double h = (x[1] - x[0]) * (L.mesh[m + 1] - L.mesh[m]);
+        const double* xs = x + L.off_states;
+        if (!hs) {
+            const double xi = xs[(size_t)m * L.ns + s], xp = xs[(size_t)(m + 1) * L.ns + s];
+            v = xp - (xi + 0.5 * h * (xdot_val(L, x, Y, m + 1, s) + xdot_val(L, x, Y, m, s)));
+        } else {
+            const int i = 2 * m, mid = 2 * m + 1, ip = 2 * m + 2;
+            const double xi = xs[(size_t)i * L.ns + s], xm = xs[(size_t)mid * L.ns + s], xp = xs[(size_t)ip * L.ns + s];
+            const double di = xdot_val(L, x, Y, i, s), dm = xdot_val(L, x, Y, mid, s), dp = xdot_val(L, x, Y, ip, s);
+            if (rm.kind == ROW_DEFECT_HERMITE_D) v = xm - 0.5 * (xp + xi) - (h / 8.0) * (di - dp);
+            else v = xp - xi - (h / 6.0) * (dp + 4.0 * dm + di);
+        }
+    }
+    g[r] = v;
+}
+
+// objective: sum of cost-mode goals (+ implicit penalties, CasOCTranscription.cpp:513-545). f[0] = total, f[1..] = terms.
+__global__ void k_assemble_f(DevTables T, DevLayout L, const double* __restrict__ x, const double* __restrict__ G, double* __restrict__ f) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    double total = 0;
+    int term = 0;
+    for (int g = 0; g < T.ngoal; ++g) {
+        const int* gr = T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
+        if (gr[1] != MOCOB200_MODE_COST) continue;
+        double s = 0;
+        for (int o = 0; o < gr[2]; ++o) s += G[L.goal_eoff[g] + o];
+        f[1 + term++] = s;
+        total += s;
+    }
+    const double dur = x[1] - x[0];
+    for (int which = 0; which < 2; ++which) {
+        const bool on = which == 0 ? (L.minimize_accel && L.implicit) : (L.minimize_auxderiv && L.n_auxres > 0);
+        if (!on) continue;
+        const int lo = which == 0 ? 0 : (L.implicit ? L.nq : 0), hi = which == 0 ? L.nq : L.nd;
+        double acc = 0;
+        for (int j = 0; j < L.n_grid; ++j) {
+            double sq = 0;
+            for (int k = lo; k < hi; ++k) { const double d = x[L.off_derivs + (size_t)j * L.nd + k]; sq += d * d; }
+            acc += L.quad[j] * sq;
+        }
+        const double s = (which == 0 ? L.accel_weight : L.auxderiv_weight) * dur * acc;
+        f[1 + term++] = s;
+        total += s;
+    }
+    f[0] = total;
+}
+
+// d(goal output)/d(variable of column c): endpoint block + chain through the integral
+__device__ __forceinline__ double endpoint_entry(const DevLayout& L, const double* x, const double* J, const double* I, const double* E,
+                                                 int g, int o, const ColMetaD& c) {
+    const double* Er = E + (size_t)(L.goal_eoff[g] + o) * L.n_ein;
+    const int half = 1 + L.ns + L.nc + L.nd;
+    const int slot = L.goal_integrand[g];
+    const double dGdI = slot >= 0 ? Er[L.n_ein - 1] : 0.0;
+    if (c.kind == COL_T0_D) return Er[0] + (slot >= 0 ? dGdI * I[L.n_integrand + slot] : 0.0);
+    if (c.kind == COL_TF_D) return Er[half] + (slot >= 0 ? dGdI * I[2 * L.n_integrand + slot] : 0.0);
+    double v = 0;
+    if (c.point == 0) v += Er[c.in];
+    if (c.point == L.n_grid - 1) v += Er[half + c.in];
+    if (slot >= 0) {
+        const double dur = x[1] - x[0];
+        v += dGdI * dur * L.quad[c.point] * J[((size_t)c.point * L.n_out + L.n_dyn_out + slot) * L.n_in + c.in];
+    }
+    return v;
+}
+
+__global__ void k_assemble_jac(DevLayout L, const double* __restrict__ x, const double* __restrict__ Y, const double* __restrict__ J,
+                               const double* __restrict__ I, const double* __restrict__ E, double* __restrict__ vals) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= L.nnz) return;
+    const RowMetaD rm = L.rows[L.rowidx[k]];
+    const ColMetaD c = L.cols[L.nnzcol[k]];
+    const bool hs = L.scheme == MOCOB200_SCHEME_HERMITE_SIMPSON;
+    const bool isTime = c.kind == COL_T0_D || c.kind == COL_TF_D;
+    double v = 0;
+    if (rm.kind == ROW_ENDPOINT_D) {
+        v = endpoint_entry(L, x, J, I, E, rm.a, rm.b, c);
+    } else if (rm.kind == ROW_RESIDUAL_D) {
+        const int j = rm.a;
+        const double* Jr = J + ((size_t)j * L.n_out + rm.b) * L.n_in;
+        if (isTime) v = Jr[0] * (c.kind == COL_TF_D ? L.grid[j] : 1.0 - L.grid[j]);
+        else v = Jr[c.in];
+    } else if (rm.kind == ROW_INTERP_D) {
+        v = (c.point == 2 * rm.a + 1) ? 1.0 : -0.5;
+    } else {
+        const int m = rm.a, s = rm.b;
+        const double dm = L.mesh[m + 1] - L.mesh[m];
+        const double h = (x[1] - x[0]) * dm;
+        const int base = hs ? 2 * m : m;
+        if (!isTime) {
+            const int role = hs ? (c.point - base) : 2 * (c.point - base);
+            double lin, wc;
+            defect_coeffs(rm.kind, role, lin, wc);
+            v = ((c.kind == COL_STATE_D && c.k == s) ? lin : 0.0);
+            if (wc != 0.0) v += wc * h * dxdot(L, J, c.point, s, c);
+        } else {
+            const double dhdt = (c.kind == COL_TF_D) ? dm : -dm;
+            const int npts = hs ? 3 : 2;
+            for (int p = 0; p < npts; ++p) {
+                const int role = hs ? p : 2 * p;
+                const int j = base + p;
+                double lin, wc;
+                defect_coeffs(rm.kind, role, lin, wc);
+                if (wc == 0.0) continue;
+                const double dtj = (c.kind == COL_TF_D) ? L.grid[j] : 1.0 - L.grid[j];
+                v += wc * (dhdt * xdot_val(L, x, Y, j, s) + h * dxdot_dt(L, J, j, s) * dtj);
+            }
+        }
+    }
+    vals[k] = v;
+}
+
+__global__ void k_assemble_grad(DevTables T, DevLayout L, const double* __restrict__ x, const double* __restrict__ Y, const double* __restrict__ J,
+                                const double* __restrict__ I, const double* __restrict__ E, double* __restrict__ grad) {
+    const int vi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (vi >= L.n_var) return;
+    const ColMetaD c = L.cols[vi];
+    double v = 0;
+    for (int g = 0; g < T.ngoal; ++g) {
+        const int* gr = T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
+        if (gr[1] != MOCOB200_MODE_COST) continue;
+        for (int o = 0; o < gr[2]; ++o) v += endpoint_entry(L, x, J, I, E, g, o, c);
+    }
+    const double dur = x[1] - x[0];
+    for (int which = 0; which < 2; ++which) {
+        const bool on = which == 0 ? (L.minimize_accel && L.implicit) : (L.minimize_auxderiv && L.n_auxres > 0);
+        if (!on) continue;
+        const int lo = which == 0 ? 0 : (L.implicit ? L.nq : 0), hi = which == 0 ? L.nq : L.nd;
+        const double w = which == 0 ? L.accel_weight : L.auxderiv_weight;
+        if (c.kind == COL_DERIV_D && c.k >= lo && c.k < hi) v += 2.0 * w * dur * L.quad[c.point] * x[vi];
+        if (c.kind == COL_T0_D || c.kind == COL_TF_D) {
+            double acc = 0;
+            for (int j = 0; j < L.n_grid; ++j) {
+                double sq = 0;
+                for (int k = lo; k < hi; ++k) { const double d = x[L.off_derivs + (size_t)j * L.nd + k]; sq += d * d; }
+                acc += L.quad[j] * sq;
+            }
+            v += (c.kind == COL_TF_D ? 1.0 : -1.0) * w * acc;
+        }
+    }
+    grad[vi] = v;
+}
+
+// ---------------------------------------------------------------------------------------------
+void launch_points_nominal(const DevTables& T, const DevLayout& L, const double* d_x, double* d_Y, int p0, int np, cudaStream_t s) {
+    if (np <= 0) return;
+    const int bs = 32;
+    k_points_nominal<<<(np + bs - 1) / bs, bs, 0, s>>>(T, L, d_x, d_Y, p0, np);
+}
+void launch_points_fd(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, double* d_Y, double* d_J, int p0,
+                      int np, cudaStream_t s) {
+    if (np <= 0) return;
+    const int bs = ((L.n_in + 1 + 31) / 32) * 32;
+    k_points_fd<<<np, bs, L.n_out * sizeof(double), s>>>(T, L, fd, d_x, d_Y, d_J, p0);
+}
+void launch_integrals(const DevLayout& L, const double* d_x, const double* d_Y, const double* d_J, double* d_I, bool withJ, cudaStream_t s) {
+    if (L.n_integrand <= 0) return;
+    k_integrals<<<L.n_integrand, 256, 0, s>>>(L, d_x, d_Y, d_J, d_I, withJ ? 1 : 0);
+}
+void launch_endpoint(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, const double* d_I, double* d_G,
+                     double* d_E, bool withFd, cudaStream_t s) {
+    if (L.n_eout_total <= 0) return;
+    const int bs = ((L.n_ein + 1 + 31) / 32) * 32;
+    k_endpoint<<<1, bs, (L.n_eout_total + 1) * sizeof(double), s>>>(T, L, fd, d_x, d_I, d_G, d_E, withFd ? 1 : 0);
+}
+void launch_assemble_g(const DevLayout& L, const double* d_x, const double* d_Y, const double* d_G, double* d_g, cudaStream_t s) {
+    if (L.n_con <= 0) return;
+    k_assemble_g<<<(L.n_con + 127) / 128, 128, 0, s>>>(L, d_x, d_Y, d_G, d_g);
+}
+void launch_assemble_f(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_G, double* d_f, cudaStream_t s) {
+    k_assemble_f<<<1, 32, 0, s>>>(T, L, d_x, d_G, d_f);
+}
+void launch_assemble_jac(const DevLayout& L, const double* d_x, const double* d_Y, const double* d_J, const double* d_I, const double* d_E,
+                         double* d_vals, cudaStream_t s) {
+    if (L.nnz <= 0) return;
+    k_assemble_jac<<<(L.nnz + 255) / 256, 256, 0, s>>>(L, d_x, d_Y, d_J, d_I, d_E, d_vals);
+}
+void launch_assemble_grad(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_Y, const double* d_J, const double* d_I,
+                          const double* d_E, double* d_grad, cudaStream_t s) {
+    k_assemble_grad<<<(L.n_var + 127) / 128, 128, 0, s>>>(T, L, d_x, d_Y, d_J, d_I, d_E, d_grad);
+}
+
+// ---------------------------------------------------------------------------------------------
+// FP64 FMA saturation: 8 independent chains per thread, many resident warps per SM.
+__global__ void k_fp64_peak(double* out, int iters) {
+    double a0 = threadIdx.x * 1e-9, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+    const double b = 1.0000001, c = 1e-9;
+    for (int i = 0; i < iters; ++i) {
+        a0 = fma(a0, b, c); a1 = fma(a1, b, c); a2 = fma(a2, b, c); a3 = fma(a3, b, c);
+        a4 = fma(a4, b, c); a5 = fma(a5, b, c); a6 = fma(a6, b, c); a7 = fma(a7, b, c);
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+double measure_fp64_peak_tflops(int device) {
+    cudaSetDevice(device);
+    cudaDeviceProp prop;
+    cudaGetDeviceProperties(&prop, device);
+    const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 1 << 15;
+    double* d = nullptr;
+    if (cudaMalloc(&d, sizeof(double) * blocks * threads) != cudaSuccess) return -1;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    double best = 0;
+    for (int rep = 0; rep < 6; ++rep) {
+        cudaEventRecord(e0);
+        k_fp64_peak<<<blocks, threads>>>(d, iters);
+        cudaEventRecord(e1);
+        cudaEventSynchronize(e1);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double flops = 2.0 * 8.0 * (double)iters * blocks * threads;
+        if (rep > 0) best = fmax(best, flops / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d);
+    return best;
+}
+
+} // namespace mocob200

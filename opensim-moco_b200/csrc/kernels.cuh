@@ -1,0 +1,58 @@
+// Kernels of the evaluator: point functions over the grid, their finite-difference blocks,
+// endpoint functions, and the assembly of g / jac_g (CSC) / grad_f.
+#pragma once
+#include "point_eval.cuh"
+
+namespace mocob200 {
+
+#define MOCOB200_MAX_IN 160
+#define MOCOB200_MAX_OUT 72
+#define MOCOB200_MAX_EOUT 64 /* outputs of one endpoint goal */
+
+struct FdSettings {
+    int scheme;    // MOCOB200_FD_*
+    double h;      // initial step
+    int h_iter;    // step-size refinement iterations (central)
+    double u_aim;  // target truncation/round-off ratio
+    double reltol, abstol;
+};
+
+enum { ROW_ENDPOINT_D = 0, ROW_RESIDUAL_D = 1, ROW_DEFECT_TRAP_D = 2, ROW_DEFECT_HERMITE_D = 3, ROW_DEFECT_SIMPSON_D = 4, ROW_INTERP_D = 5 };
+enum { COL_T0_D = 0, COL_TF_D = 1, COL_STATE_D = 2, COL_CONTROL_D = 3, COL_DERIV_D = 4 };
+struct RowMetaD { int kind, a, b, pad; };
+struct ColMetaD { int kind, point, k, in; };
+
+struct DevLayout {
+    int scheme, implicit, nq, nz, ns, nc, nd, n_in, n_auxres, n_integrand, n_dyn_out, n_out;
+    int n_mesh, n_grid, n_intervals, n_var, n_con, nnz;
+    int off_states, off_controls, off_derivs;
+    int n_endpoint_rows, n_resid_rows_per_point, n_defect_rows, n_interp_rows, n_ein, n_cost_terms;
+    int minimize_accel, minimize_auxderiv;
+    double accel_weight, auxderiv_weight;
+    const double* mesh;  // [n_mesh]
+    const double* grid;  // [n_grid]
+    const double* quad;  // [n_grid]
+    const int* row_resid; const int* row_defect; const int* row_interp;
+    const int* goal_row; const int* goal_integrand; const int* goal_eoff; // offset of goal g's block in E / G
+    const RowMetaD* rows; const ColMetaD* cols;
+    const int* colptr; const int* rowidx; const int* nnzcol;
+    int n_eout_total; // total outputs over all goals
+};
+
+void launch_points_nominal(const DevTables& T, const DevLayout& L, const double* d_x, double* d_Y, int p0, int np, cudaStream_t s);
+void launch_points_fd(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, double* d_Y, double* d_J,
+                      int p0, int np, cudaStream_t s);
+// integrals[n_integrand], dIdt0[n_integrand], dIdtf[n_integrand] (derivative parts need J)
+void launch_integrals(const DevLayout& L, const double* d_x, const double* d_Y, const double* d_J, double* d_I, bool withJ, cudaStream_t s);
+// G[n_eout_total] values and E[n_eout_total][n_ein] FD blocks of every goal's endpoint function
+void launch_endpoint(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, const double* d_I, double* d_G,
+                     double* d_E, bool withFd, cudaStream_t s);
+void launch_assemble_g(const DevLayout& L, const double* d_x, const double* d_Y, const double* d_G, double* d_g, cudaStream_t s);
+void launch_assemble_f(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_G, double* d_f /*[1+n_cost_terms]*/, cudaStream_t s);
+void launch_assemble_jac(const DevLayout& L, const double* d_x, const double* d_Y, const double* d_J, const double* d_I,
+                         const double* d_E, double* d_vals, cudaStream_t s);
+void launch_assemble_grad(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_Y, const double* d_J, const double* d_I,
+                          const double* d_E, double* d_grad, cudaStream_t s);
+double measure_fp64_peak_tflops(int device);
+
+} // namespace mocob200

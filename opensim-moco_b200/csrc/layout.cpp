@@ -1,0 +1,224 @@
+#include "layout.h"
+
+#include <algorithm>
+#include <limits>
+#include <stdexcept>
+
+namespace mocob200 {
+
+namespace {
+inline const int* goalRec(const mocob200_tables& T, int g) { return T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE; }
+}
+
+Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bool withStructure) {
+    Layout L{};
+    L.scheme = R.scheme;
+    L.implicit = R.dynamics_mode == MOCOB200_DYNAMICS_IMPLICIT;
+    L.nq = T.nq; L.nz = T.nz; L.ns = 2 * T.nq + T.nz; L.nc = T.nc;
+    L.nd = (L.implicit ? T.nq : 0) + T.nderiv_aux;
+    L.n_in = 1 + L.ns + L.nc + L.nd;
+    L.n_auxres = T.nderiv_aux;
+    L.goal_integrand.assign(T.ngoal, -1);
+    L.goal_row.assign(T.ngoal, -1);
+    L.n_integrand = 0; L.n_endpoint_rows = 0; L.n_cost_terms = 0;
+    for (int g = 0; g < T.ngoal; ++g) {
+        const int* gr = goalRec(T, g);
+        if (gr[3]) L.goal_integrand[g] = L.n_integrand++;
+        if (gr[1] == MOCOB200_MODE_ENDPOINT_CONSTRAINT) { L.goal_row[g] = L.n_endpoint_rows; L.n_endpoint_rows += gr[2]; }
+        else L.n_cost_terms++;
+    }
+    // endpoint constraints come first in goal order among themselves (createEndpointConstraintNames)
+    if (L.implicit && R.minimize_accelerations) L.n_cost_terms++;
+    if (L.n_auxres && R.minimize_auxiliary_derivatives) L.n_cost_terms++;
+    L.n_dyn_out = L.nq + L.nz + L.n_auxres;
+    L.n_out = L.n_dyn_out + L.n_integrand;
+    L.n_mesh = R.n_mesh;
+    if (L.n_mesh < 2) throw std::runtime_error("need at least one mesh interval");
+    L.n_intervals = L.n_mesh - 1;
+    L.mesh.resize(L.n_mesh);
+    for (int i = 0; i < L.n_mesh; ++i) L.mesh[i] = R.mesh ? R.mesh[i] : i / (double)L.n_intervals;
+    const bool hs = L.scheme == MOCOB200_SCHEME_HERMITE_SIMPSON;
+    L.n_grid = hs ? 2 * L.n_mesh - 1 : L.n_mesh;
+    L.grid.resize(L.n_grid);
+    L.quad.assign(L.n_grid, 0.0);
+    for (int i = 0; i < L.n_grid; ++i) {
+        if (!hs) L.grid[i] = L.mesh[i];
+        else L.grid[i] = (i % 2 == 0) ? L.mesh[i / 2] : .5 * (L.mesh[i / 2] + L.mesh[i / 2 + 1]);
+    }
+    for (int m = 0; m < L.n_intervals; ++m) {
+        const double dm = L.mesh[m + 1] - L.mesh[m];
+        if (hs) {
+            L.quad[2 * m] += (1.0 / 6.0) * dm;
+            L.quad[2 * m + 1] += (2.0 / 3.0) * dm;
+            L.quad[2 * m + 2] += (1.0 / 6.0) * dm;
+        } else {
+            L.quad[m] += 0.5 * dm;
+            L.quad[m + 1] += 0.5 * dm;
+        }
+    }
+    // variables: t0, tf, vec(states), vec(controls), [multipliers, slacks: none], vec(derivatives), [parameters: none]
+    L.off_states = 2;
+    L.off_controls = L.off_states + L.ns * L.n_grid;
+    L.off_derivs = L.off_controls + L.nc * L.n_grid;
+    L.n_var = L.off_derivs + L.nd * L.n_grid;
+    L.n_ein = 2 + 2 * (L.ns + L.nc + L.nd) + 1;
+    // constraints
+    L.n_resid_rows_per_point = (L.implicit ? L.nq : 0) + L.n_auxres;
+    L.n_defect_rows = (hs ? 2 : 1) * L.ns;
+    L.n_interp_rows = (hs && R.interpolate_control_midpoints) ? L.nc : 0;
+    L.row_resid.assign(L.n_grid, -1);
+    L.row_defect.assign(L.n_intervals, -1);
+    L.row_interp.assign(L.n_intervals, -1);
+    int row = L.n_endpoint_rows;
+    const int ppi = hs ? 2 : 1; // grid points whose residuals are grouped with interval m
+    for (int m = 0; m < L.n_intervals; ++m) {
+        for (int k = 0; k < ppi; ++k) { L.row_resid[ppi * m + k] = row; row += L.n_resid_rows_per_point; }
+        L.row_defect[m] = row; row += L.n_defect_rows;
+        L.row_interp[m] = row; row += L.n_interp_rows;
+    }
+    L.row_resid[L.n_grid - 1] = row; row += L.n_resid_rows_per_point;
+    L.n_con = row;
+    L.rows.assign(L.n_con, RowMeta{0, 0, 0, 0});
+    for (int g = 0; g < T.ngoal; ++g)
+        if (L.goal_row[g] >= 0)
+            for (int o = 0; o < goalRec(T, g)[2]; ++o) L.rows[L.goal_row[g] + o] = RowMeta{ROW_ENDPOINT, g, o, 0};
+    for (int j = 0; j < L.n_grid; ++j)
+        for (int o = 0; o < L.n_resid_rows_per_point; ++o) {
+            // out rows: implicit multibody residual [0,nq) then aux residuals at [nq+nz, ...)
+            const int outRow = (L.implicit && o < L.nq) ? o : L.nq + L.nz + (o - (L.implicit ? L.nq : 0));
+            L.rows[L.row_resid[j] + o] = RowMeta{ROW_RESIDUAL, j, outRow, 0};
+        }
+    for (int m = 0; m < L.n_intervals; ++m) {
+        for (int s = 0; s < L.ns; ++s) {
+            if (hs) {
+                L.rows[L.row_defect[m] + s] = RowMeta{ROW_DEFECT_HERMITE, m, s, 0};
+                L.rows[L.row_defect[m] + L.ns + s] = RowMeta{ROW_DEFECT_SIMPSON, m, s, 0};
+            } else
+                L.rows[L.row_defect[m] + s] = RowMeta{ROW_DEFECT_TRAP, m, s, 0};
+        }
+        for (int c = 0; c < L.n_interp_rows; ++c) L.rows[L.row_interp[m] + c] = RowMeta{ROW_INTERP, m, c, 0};
+    }
+    L.cols.assign(L.n_var, ColMeta{0, 0, 0, 0});
+    L.cols[0] = ColMeta{COL_T0, -1, 0, 0};
+    L.cols[1] = ColMeta{COL_TF, -1, 0, 0};
+    for (int j = 0; j < L.n_grid; ++j) {
+        for (int k = 0; k < L.ns; ++k) L.cols[L.off_states + j * L.ns + k] = ColMeta{COL_STATE, j, k, 1 + k};
+        for (int k = 0; k < L.nc; ++k) L.cols[L.off_controls + j * L.nc + k] = ColMeta{COL_CONTROL, j, k, 1 + L.ns + k};
+        for (int k = 0; k < L.nd; ++k) L.cols[L.off_derivs + j * L.nd + k] = ColMeta{COL_DERIV, j, k, 1 + L.ns + L.nc + k};
+    }
+    if (!withStructure) { L.nnz = -1; return L; }
+
+    // ---- CSC structure with CasADi's dense point-function blocks (optim_sparsity_detection "none")
+    bool anyGoalIntegrandEC = false;
+    std::vector<char> ecHasInt(T.ngoal, 0);
+    for (int g = 0; g < T.ngoal; ++g)
+        if (L.goal_row[g] >= 0 && goalRec(T, g)[3]) { ecHasInt[g] = 1; anyGoalIntegrandEC = true; }
+    (void)anyGoalIntegrandEC;
+    // does xdot_s (state s) at a point depend on input `in` of the same point?
+    auto xdotDepends = [&](int s, const ColMeta& c) -> bool {
+        if (s < L.nq) return c.kind == COL_STATE && c.k == L.nq + s; // qdot = u
+        if (s < 2 * L.nq && L.implicit) return c.kind == COL_DERIV && c.k == s - L.nq; // udot = w
+        return true; // dense callback block
+    };
+    L.colptr.assign(L.n_var + 1, 0);
+    L.rowidx.clear();
+    L.nnzcol.clear();
+    auto emit = [&](int col, int r) { L.rowidx.push_back(r); L.nnzcol.push_back(col); };
+    for (int col = 0; col < L.n_var; ++col) {
+        const ColMeta c = L.cols[col];
+        L.colptr[col] = (int)L.rowidx.size();
+        if (c.kind == COL_T0 || c.kind == COL_TF) {
+            for (int r = 0; r < L.n_endpoint_rows; ++r) emit(col, r);
+            for (int m = 0; m < L.n_intervals; ++m) {
+                for (int k = 0; k < ppi; ++k)
+                    for (int o = 0; o < L.n_resid_rows_per_point; ++o) emit(col, L.row_resid[ppi * m + k] + o);
+                for (int o = 0; o < L.n_defect_rows; ++o) emit(col, L.row_defect[m] + o);
+            }
+            for (int o = 0; o < L.n_resid_rows_per_point; ++o) emit(col, L.row_resid[L.n_grid - 1] + o);
+            continue;
+        }
+        const int j = c.point;
+        for (int g = 0; g < T.ngoal; ++g) {
+            if (L.goal_row[g] < 0) continue;
+            if (j == 0 || j == L.n_grid - 1 || ecHasInt[g])
+                for (int o = 0; o < goalRec(T, g)[2]; ++o) emit(col, L.goal_row[g] + o);
+        }
+        // intervals that contain grid point j, ascending
+        int ms[2], roles[2], nm = 0; // role: 0 = i (left), 1 = mid, 2 = ip (right)
+        if (hs) {
+            if (j % 2 == 1) { ms[nm] = j / 2; roles[nm++] = 1; }
+            else {
+                if (j / 2 - 1 >= 0) { ms[nm] = j / 2 - 1; roles[nm++] = 2; }
+                if (j / 2 < L.n_intervals) { ms[nm] = j / 2; roles[nm++] = 0; }
+            }
+        } else {
+            if (j - 1 >= 0) { ms[nm] = j - 1; roles[nm++] = 2; }
+            if (j < L.n_intervals) { ms[nm] = j; roles[nm++] = 0; }
+        }
+        for (int t = 0; t < nm; ++t) {
+            const int m = ms[t], role = roles[t];
+            if (role != 2) // residual rows of j sit in the block of the interval that starts at / contains j
+                for (int o = 0; o < L.n_resid_rows_per_point; ++o) emit(col, L.row_resid[j] + o);
+            for (int s = 0; s < L.ns; ++s) {
+                const bool dep = xdotDepends(s, c);
+                const bool direct = c.kind == COL_STATE && c.k == s;
+                if (hs) {
+                    // Hermite: x_mid - (x_ip + x_i)/2 - h/8 (xdot_i - xdot_ip) ; no xdot_mid
+                    if (direct || (dep && role != 1)) emit(col, L.row_defect[m] + s);
+                } else {
+                    if (direct || dep) emit(col, L.row_defect[m] + s);
+                }
+            }
+            if (hs)
+                for (int s = 0; s < L.ns; ++s) {
+                    // Simpson: x_ip - x_i - h/6 (xdot_ip + 4 xdot_mid + xdot_i) ; no x_mid
+                    const bool dep = xdotDepends(s, c);
+                    const bool direct = c.kind == COL_STATE && c.k == s && role != 1;
+                    if (direct || dep) emit(col, L.row_defect[m] + L.ns + s);
+                }
+            if (L.n_interp_rows && c.kind == COL_CONTROL) emit(col, L.row_interp[m] + c.k);
+        }
+        if (j == L.n_grid - 1)
+            for (int o = 0; o < L.n_resid_rows_per_point; ++o) emit(col, L.row_resid[j] + o);
+    }
+    L.colptr[L.n_var] = (int)L.rowidx.size();
+    L.nnz = (int)L.rowidx.size();
+    return L;
+}
+
+// Variable and constraint bounds (CasOCTranscription.cpp:175-250, 273-309, 429-443).
+void layoutBounds(const mocob200_tables& T, const mocob200_transcription& R, const Layout& L, double* xlo, double* xhi,
+                  double* glo, double* ghi) {
+    const double* tb = T.dbl + T.o_time_bounds;
+    const double* vb = T.dbl + T.o_bounds;
+    if (xlo && xhi) {
+        xlo[0] = tb[0]; xhi[0] = tb[1]; xlo[1] = tb[2]; xhi[1] = tb[3];
+        for (int j = 0; j < L.n_grid; ++j) {
+            const int which = j == 0 ? 2 : (j == L.n_grid - 1 ? 4 : 0);
+            for (int k = 0; k < L.ns; ++k) {
+                xlo[L.off_states + j * L.ns + k] = vb[6 * k + which];
+                xhi[L.off_states + j * L.ns + k] = vb[6 * k + which + 1];
+            }
+            for (int k = 0; k < L.nc; ++k) {
+                xlo[L.off_controls + j * L.nc + k] = vb[6 * (L.ns + k) + which];
+                xhi[L.off_controls + j * L.nc + k] = vb[6 * (L.ns + k) + which + 1];
+            }
+            for (int k = 0; k < L.nd; ++k) {
+                const bool accel = L.implicit && k < L.nq;
+                xlo[L.off_derivs + j * L.nd + k] = accel ? R.accel_bounds[0] : R.auxderiv_bounds[0];
+                xhi[L.off_derivs + j * L.nd + k] = accel ? R.accel_bounds[1] : R.auxderiv_bounds[1];
+            }
+        }
+    }
+    if (glo && ghi) {
+        for (int r = 0; r < L.n_con; ++r) { glo[r] = 0; ghi[r] = 0; }
+        for (int g = 0; g < T.ngoal; ++g) {
+            if (L.goal_row[g] < 0) continue;
+            const int* gr = T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
+            const double* dp = T.dbl + gr[5];
+            for (int o = 0; o < gr[2]; ++o) { glo[L.goal_row[g] + o] = dp[1]; ghi[L.goal_row[g] + o] = dp[2]; }
+        }
+    }
+}
+
+} // namespace mocob200

@@ -1,0 +1,44 @@
+// NLP layout of the transcribed problem: variable/constraint ordering and the CSC structure of
+// jac_g exactly as MocoCasADiSolver hands them to IPOPT
+// (CasOCIterate.h:28-45, CasOCTranscription.h:181-313, CasOCTranscription.cpp:83-446,
+//  CasOCTrapezoidal.cpp, CasOCHermiteSimpson.{h,cpp}).
+#pragma once
+#include <vector>
+
+#include "../../include/mocob200.h"
+
+namespace mocob200 {
+
+// row kinds
+enum { ROW_ENDPOINT = 0, ROW_RESIDUAL = 1, ROW_DEFECT_TRAP = 2, ROW_DEFECT_HERMITE = 3, ROW_DEFECT_SIMPSON = 4, ROW_INTERP = 5 };
+// column kinds
+enum { COL_T0 = 0, COL_TF = 1, COL_STATE = 2, COL_CONTROL = 3, COL_DERIV = 4 };
+
+struct RowMeta { int kind, a, b, pad; };  // ENDPOINT: a = goal, b = output ; RESIDUAL: a = grid point, b = out row ; DEFECT_*: a = interval, b = state ; INTERP: a = interval, b = control
+struct ColMeta { int kind, point, k, in; }; // in = index into the point-function input vector (0 = time)
+
+struct Layout {
+    int scheme, implicit;
+    int nq, nz, ns, nc, nd, n_in;
+    int n_auxres, n_integrand, n_dyn_out, n_out;
+    int n_mesh, n_grid, n_intervals;
+    int n_var, n_con, nnz;
+    int off_states, off_controls, off_derivs;
+    int n_endpoint_rows, n_resid_rows_per_point, n_defect_rows, n_interp_rows;
+    int n_cost_terms;
+    std::vector<double> mesh, grid, quad;      // normalised times and quadrature coefficients
+    std::vector<int> row_resid, row_defect, row_interp; // first row of each block (per grid point / interval)
+    std::vector<int> goal_row;                 // first endpoint-constraint row of goal g (or -1)
+    std::vector<int> goal_integrand;           // integrand slot of goal g (or -1)
+    std::vector<RowMeta> rows;
+    std::vector<ColMeta> cols;
+    std::vector<int> colptr, rowidx, nnzcol;
+    // endpoint function inputs: [t0, x0(ns), c0(nc), d0(nd), tf, xf, cf, df, integral]
+    int n_ein;
+};
+
+Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bool withStructure);
+void layoutBounds(const mocob200_tables& T, const mocob200_transcription& R, const Layout& L, double* xlo, double* xhi,
+                  double* glo, double* ghi);
+
+} // namespace mocob200

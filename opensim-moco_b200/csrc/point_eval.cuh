@@ -1,0 +1,912 @@
+// Device-side point function of the direct-collocation hot path (FP64, sm_100a).
+//
+// One call = one evaluation of the fused CasOC point functions at one grid point:
+//   (time, states, controls, derivatives) -> [udot | residual, zdot, aux residuals, integrands...]
+// i.e. what MultibodySystemExplicit/Implicit::eval + every CostIntegrand::eval compute in the
+// reference through SimTK::State + realizeAcceleration (MocoCasOCProblem.h:203-356).
+//
+// Formulation (not Simbody's code; written from the equations): ground-frame spatial quantities
+// referenced to each body's origin, spatial vectors [angular; linear]; articulated-body forward
+// dynamics (explicit mode) or recursive Newton–Euler residual (implicit mode); straight-line
+// muscle paths with conditional / moving points; De Groote–Fregly 2016 muscle curves; smooth
+// sphere–half-space contact; goal integrands.
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+
+#include "../../include/mocob200.h"
+
+namespace mocob200 {
+
+#ifndef MOCOB200_MAXB
+#define MOCOB200_MAXB 16 /* mobilized bodies */
+#endif
+#ifndef MOCOB200_MAXQ
+#define MOCOB200_MAXQ 16 /* coordinates */
+#endif
+#define MOCOB200_MAXCONTACT 8
+#define MOCOB200_MAXPPM 12 /* path points per muscle */
+
+struct DevTables { // mocob200_tables with device (or shared-memory) pool pointers
+    const double* dbl;
+    const int* idx;
+    int nb, nq, nz, nc, nderiv_aux, nmus, npp, nspline, ncontact, ncact, ngoal, nppoly;
+    int o_body_d, o_gravity, o_pp_d, o_mus_d, o_contact_d, o_cact_d, o_spline_data, o_ppoly_data;
+    int o_body_i, o_pp_i, o_mus_i, o_contact_i, o_cact_i, o_spline_i, o_goal_i, o_ppoly_i;
+    int implicit; // multibody dynamics mode
+    int n_auxres;
+    int n_integrand; // goals with an integrand, in goal order
+};
+
+struct V3 {
+    double x, y, z;
+};
+__device__ __forceinline__ V3 mk(double x, double y, double z) { return V3{x, y, z}; }
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ V3 operator*(double s, V3 a) { return mk(s * a.x, s * a.y, s * a.z); }
+__device__ __forceinline__ V3 cross(V3 a, V3 b) { return mk(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+__device__ __forceinline__ double dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ V3 ld3(const double* p) { return mk(p[0], p[1], p[2]); }
+// R row-major 3x3
+__device__ __forceinline__ V3 rmul(const double* R, V3 v) {
+    return mk(R[0] * v.x + R[1] * v.y + R[2] * v.z, R[3] * v.x + R[4] * v.y + R[5] * v.z, R[6] * v.x + R[7] * v.y + R[8] * v.z);
+}
+__device__ __forceinline__ V3 rtmul(const double* R, V3 v) {
+    return mk(R[0] * v.x + R[3] * v.y + R[6] * v.z, R[1] * v.x + R[4] * v.y + R[7] * v.z, R[2] * v.x + R[5] * v.y + R[8] * v.z);
+}
+__device__ __forceinline__ void mm3(const double* A, const double* B, double* C) { // C = A B
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) C[3 * i + j] = A[3 * i] * B[j] + A[3 * i + 1] * B[3 + j] + A[3 * i + 2] * B[6 + j];
+}
+__device__ __forceinline__ void mmt3(const double* A, const double* B, double* C) { // C = A B^T
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) C[3 * i + j] = A[3 * i] * B[3 * j] + A[3 * i + 1] * B[3 * j + 1] + A[3 * i + 2] * B[3 * j + 2];
+}
+
+// ---- SimmSpline evaluation (value / first derivative), semantics of
+// opensim-core/OpenSim/Common/SimmSpline.cpp:511-685: linear extrapolation outside the knots,
+// end-knot snapping within 2e-13, interval search, cubic in (x - x_k).
+__device__ inline double simm_spline(const DevTables& T, int id, double ax, int deriv) {
+    const int* rec = T.idx + T.o_spline_i + id * MOCOB200_SPLINE_ISTRIDE;
+    const int n = rec[1];
+    const double* x = T.dbl + T.o_spline_data + rec[0];
+    const double* y = x + n;
+    const double* b = y + n;
+    const double* c = b + n;
+    const double* d = c + n;
+    const double scale = d[n];
+    if (ax < x[0]) return scale * (deriv ? b[0] : y[0] + (ax - x[0]) * b[0]);
+    if (ax > x[n - 1]) return scale * (deriv ? b[n - 1] : y[n - 1] + (ax - x[n - 1]) * b[n - 1]);
+    if (fabs(ax - x[0]) <= 2e-13) return scale * (deriv ? b[0] : y[0]);
+    if (fabs(ax - x[n - 1]) <= 2e-13) return scale * (deriv ? b[n - 1] : y[n - 1]);
+    int k = 0;
+    if (n >= 3) {
+        int i = 0, j = n;
+        for (;;) {
+            k = (i + j) >> 1;
+            if (ax < x[k]) j = k;
+            else if (ax > x[k + 1]) i = k;
+            else break;
+        }
+    }
+    const double dx = ax - x[k];
+    if (deriv) return scale * (b[k] + dx * (2.0 * c[k] + 3.0 * dx * d[k]));
+    return scale * (y[k] + dx * (b[k] + dx * (c[k] + dx * d[k])));
+}
+
+// ---- piecewise polynomial (tracking references; natural spline fitted on the host)
+__device__ inline double ppoly_eval(const DevTables& T, int id, double t) {
+    const int* rec = T.idx + T.o_ppoly_i + id * MOCOB200_PPOLY_ISTRIDE;
+    const int np = rec[1], order = rec[2];
+    const double* br = T.dbl + T.o_ppoly_data + rec[0];
+    const double* co = br + np + 1;
+    int k = 0;
+    if (t >= br[np]) k = np - 1;
+    else if (t > br[0]) {
+        int lo = 0, hi = np;
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (t >= br[mid]) lo = mid; else hi = mid;
+        }
+        k = lo;
+    }
+    const double s = t - br[k];
+    const double* c = co + (size_t)k * order;
+    double v = c[order - 1];
+    for (int j = order - 2; j >= 0; --j) v = v * s + c[j];
+    return v;
+}
+
+// ---- De Groote–Fregly 2016 curves (Components/DeGrooteFregly2016Muscle.h:332-474, constants :769-815)
+__device__ __forceinline__ double dgf_gauss(double x, double b1, double b2, double b3, double b4) {
+    const double num = x - b2, den = b3 + b4 * x;
+    return b1 * exp(-0.5 * (num * num) / (den * den));
+}
+__device__ __forceinline__ double dgf_active_fl(double nfl, double scale) {
+    const double x = (nfl - 1.0) / scale + 1.0;
+    return dgf_gauss(x, 0.8150671134243542, 1.055033428970575, 0.162384573599574, 0.063303448465465) +
+           dgf_gauss(x, 0.433004984392647, 0.716775413397760, -0.029947116970696, 0.200356847296188) +
+           dgf_gauss(x, 0.1, 1.0, 0.353553390593274, 0.0);
+}
+__device__ __forceinline__ double dgf_gauss_d(double x, double b1, double b2, double b3, double b4) {
+    const double den = b3 + b4 * x;
+    return (b1 * exp(-((b2 - x) * (b2 - x)) / (2.0 * den * den)) * (b2 - x) * (b3 + b2 * b4)) / (den * den * den);
+}
+__device__ __forceinline__ double dgf_active_fl_d(double nfl, double scale) {
+    const double x = (nfl - 1.0) / scale + 1.0;
+    return (1.0 / scale) * (dgf_gauss_d(x, 0.8150671134243542, 1.055033428970575, 0.162384573599574, 0.063303448465465) +
+                            dgf_gauss_d(x, 0.433004984392647, 0.716775413397760, -0.029947116970696, 0.200356847296188) +
+                            dgf_gauss_d(x, 0.1, 1.0, 0.353553390593274, 0.0));
+}
+__device__ __forceinline__ double dgf_passive_fl(double nfl, double e0) {
+    const double kPE = 4.0;
+    const double offset = exp(kPE * (0.2 - 1.0) / e0);
+    const double denom = exp(kPE) - offset;
+    return (exp(kPE * (nfl - 1.0) / e0) - offset) / denom;
+}
+__device__ __forceinline__ double dgf_passive_fl_d(double nfl, double e0) {
+    const double kPE = 4.0;
+    const double offset = exp(kPE * (0.2 - 1.0) / e0);
+    return (kPE * exp((kPE * (nfl - 1.0)) / e0)) / (e0 * (exp(kPE) - offset));
+}
+__device__ __forceinline__ double dgf_fv(double nv) {
+    const double d1 = -0.3211346127989808, d2 = -8.149, d3 = -0.374, d4 = 0.8825327733249912;
+    const double tv = d2 * nv + d3;
+    return d1 * log(tv + sqrt(tv * tv + 1.0)) + d4;
+}
+__device__ __forceinline__ double dgf_fv_inv(double fv) {
+    const double d1 = -0.3211346127989808, d2 = -8.149, d3 = -0.374, d4 = 0.8825327733249912;
+    return (sinh(1.0 / d1 * (fv - d4)) - d3) / d2;
+}
+
+struct MuscleOut {
+    double tendonForce;  // actuation
+    double residual;     // implicit tendon: F_T - F_fiber cos(alpha)
+    double nfDeriv;      // d(normalized tendon force)/dt
+    double linResidDeriv; // getLinearizedEquilibriumResidualDerivative (for InitialVelocityEquilibriumDGF)
+};
+
+// DeGrooteFregly2016Muscle::calcMuscleLengthInfoHelper / calcFiberVelocityInfoHelper /
+// calcMuscleDynamicsInfoHelper (Components/DeGrooteFregly2016Muscle.cpp:240-372) reduced to what
+// reaches the outputs; wantStiffness adds the stiffness terms needed by the linearized residual.
+__device__ inline MuscleOut dgf_muscle(const double* p, int flags, double mtLength, double mtVelocity, double activation,
+                                      double normTendonForce, double normTendonForceDeriv, bool wantStiffness) {
+    const double Fmax = p[0], lopt = p[1], lslack = p[2], alpha0 = p[3], vmaxN = p[4], damping = p[7], e0 = p[9],
+                 wscale = p[10], kT = p[13];
+    const double c1 = 0.200, c2 = 1.0, c3 = 0.200;
+    const bool rigid = flags & MOCOB200_MUS_FLAG_IGNORE_TENDON_COMPLIANCE;
+    const bool implicitT = flags & MOCOB200_MUS_FLAG_TENDON_IMPLICIT;
+    const double fiberWidth = lopt * sin(alpha0);
+    const double vmax = vmaxN * lopt;
+    MuscleOut o;
+    // length info
+    const double normTendonLength = rigid ? 1.0 : log((1.0 / c1) * (normTendonForce + c3)) / kT + c2;
+    const double tendonLength = lslack * normTendonLength;
+    const double fibAlong = mtLength - tendonLength;
+    const double fiberLength = sqrt(fibAlong * fibAlong + fiberWidth * fiberWidth);
+    const double nfl = fiberLength / lopt;
+    const double cosA = fibAlong / fiberLength;
+    const double sinA = fiberWidth / fiberLength;
+    const double fpe = (flags & MOCOB200_MUS_FLAG_IGNORE_PASSIVE) ? 0.0 : dgf_passive_fl(nfl, e0);
+    const double fal = dgf_active_fl(nfl, wscale);
+    // velocity info
+    double normFiberVelocity, fv, fiberVelAlong, tendonVelocity;
+    if (!rigid && !implicitT) {
+        const double normFiberForce = normTendonForce / cosA;
+        fv = (normFiberForce - fpe) / (activation * fal);
+        normFiberVelocity = dgf_fv_inv(fv);
+        const double fiberVelocity = normFiberVelocity * vmax;
+        fiberVelAlong = fiberVelocity / cosA;
+        tendonVelocity = mtVelocity - fiberVelAlong;
+    } else {
+        const double normTendonVelocity =
+                rigid ? 0.0 : normTendonForceDeriv / (c1 * kT * exp(kT * (normTendonLength - c2)));
+        tendonVelocity = lslack * normTendonVelocity;
+        fiberVelAlong = mtVelocity - tendonVelocity;
+        const double fiberVelocity = fiberVelAlong * cosA;
+        normFiberVelocity = fiberVelocity / vmax;
+        fv = dgf_fv(normFiberVelocity);
+    }
+    // dynamics info
+    const double activeF = Fmax * (activation * fal * fv);
+    const double conPassiveF = Fmax * fpe;
+    const double nonConPassiveF = Fmax * damping * normFiberVelocity;
+    const double fiberForce = activeF + conPassiveF + nonConPassiveF;
+    const double fiberForceAlong = fiberForce * cosA;
+    o.tendonForce = rigid ? fiberForceAlong : Fmax * normTendonForce;
+    o.residual = rigid ? 0.0 : (implicitT ? o.tendonForce - fiberForceAlong : NAN);
+    if (rigid) o.nfDeriv = 0.0;
+    else if (implicitT) o.nfDeriv = normTendonForceDeriv;
+    else o.nfDeriv = (tendonVelocity / lslack) * (c1 * kT * exp(kT * (normTendonLength - c2)));
+    o.linResidDeriv = 0.0;
+    if (wantStiffness) {
+        // calcFiberStiffness, calcPartialPennationAnglePartialFiberLength,
+        // calcPartialFiberForceAlongTendonPartialFiberLength, calcFiberStiffnessAlongTendon,
+        // calcTendonStiffness (DeGrooteFregly2016Muscle.h:506-618)
+        const double fiberStiffness = Fmax * (activation * (1.0 / lopt) * dgf_active_fl_d(nfl, wscale) * fv +
+                                              ((flags & MOCOB200_MUS_FLAG_IGNORE_PASSIVE) ? 0.0 : (1.0 / lopt) * dgf_passive_fl_d(nfl, e0)));
+        const double dAlpha_dL = -fiberWidth / (fiberLength * fiberLength) / sqrt(1.0 - (fiberWidth / fiberLength) * (fiberWidth / fiberLength));
+        const double dFalong_dL = fiberStiffness * cosA - fiberForce * sinA * dAlpha_dL;
+        const double dLalong_dL = cosA - fiberLength * sinA * dAlpha_dL;
+        const double fiberStiffAlong = dFalong_dL * (1.0 / dLalong_dL);
+        const double tendonStiffness = rigid ? INFINITY : (Fmax / lslack) * (c1 * kT * exp(kT * (normTendonLength - c2)));
+        o.linResidDeriv = fiberStiffAlong * fiberVelAlong - tendonStiffness * (mtVelocity - fiberVelAlong);
+    }
+    return o;
+}
+
+// Scratch for one evaluation. Lives in thread-local memory.
+struct Scratch {
+    double R[MOCOB200_MAXB][9]; // R_GB
+    V3 p[MOCOB200_MAXB];        // body origin in ground
+    V3 w[MOCOB200_MAXB], v[MOCOB200_MAXB]; // spatial velocity of the body origin
+    V3 Fm[MOCOB200_MAXB], Ff[MOCOB200_MAXB]; // applied spatial force (moment about origin ; force)
+    double tau[MOCOB200_MAXQ];  // applied mobility forces
+    V3 contactF[MOCOB200_MAXCONTACT]; // force on the sphere body of each contact (ground frame)
+};
+
+// position + velocity kinematics, base to tip.
+__device__ inline void kinematics(const DevTables& T, const double* q, const double* u, Scratch& S) {
+    for (int b = 0; b < T.nb; ++b) {
+        const double* bd = T.dbl + T.o_body_d + b * MOCOB200_BODY_DSTRIDE;
+        const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
+        const int par = bi[0], kind = bi[1], q0 = bi[2];
+        double RGF[9];
+        V3 oF, wP = mk(0, 0, 0), vP = mk(0, 0, 0), pP = mk(0, 0, 0);
+        if (par >= 0) {
+            mm3(S.R[par], bd, RGF);
+            pP = S.p[par];
+            oF = pP + rmul(S.R[par], ld3(bd + 9));
+            wP = S.w[par];
+            vP = S.v[par];
+        } else {
+#pragma unroll
+            for (int k = 0; k < 9; ++k) RGF[k] = bd[k];
+            oF = ld3(bd + 9);
+        }
+        double RGM[9];
+        V3 oM = oF;
+        const V3 xF = mk(RGF[0], RGF[3], RGF[6]), yF = mk(RGF[1], RGF[4], RGF[7]), zF = mk(RGF[2], RGF[5], RGF[8]);
+        V3 wrel = mk(0, 0, 0), vtr = mk(0, 0, 0);
+        if (kind == MOCOB200_JOINT_PIN || kind == MOCOB200_JOINT_PLANAR) {
+            double s, c;
+            sincos(q[q0], &s, &c);
+            // R_GM = R_GF * Rz(theta)
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+                RGM[3 * i] = RGF[3 * i] * c + RGF[3 * i + 1] * s;
+                RGM[3 * i + 1] = -RGF[3 * i] * s + RGF[3 * i + 1] * c;
+                RGM[3 * i + 2] = RGF[3 * i + 2];
+            }
+            wrel = u[q0] * zF;
+            if (kind == MOCOB200_JOINT_PLANAR) {
+                oM = oF + q[q0 + 1] * xF + q[q0 + 2] * yF;
+                vtr = u[q0 + 1] * xF + u[q0 + 2] * yF;
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 9; ++k) RGM[k] = RGF[k];
+            if (kind == MOCOB200_JOINT_SLIDER) {
+                oM = oF + q[q0] * xF;
+                vtr = u[q0] * xF;
+            }
+        }
+        mmt3(RGM, bd + 12, S.R[b]); // R_GB = R_GM * R_BM^T
+        const V3 pB = oM - rmul(S.R[b], ld3(bd + 21));
+        S.p[b] = pB;
+        const V3 sv = pB - oM;
+        S.w[b] = wP + wrel;
+        S.v[b] = vP + cross(wP, pB - pP) + cross(wrel, sv) + vtr;
+        S.Fm[b] = mk(0, 0, 0);
+        S.Ff[b] = mk(0, 0, 0);
+    }
+}
+
+__device__ __forceinline__ void apply_point_force(Scratch& S, int b, V3 pointG, V3 f) {
+    if (b < 0) return; // ground
+    S.Ff[b] = S.Ff[b] + f;
+    S.Fm[b] = S.Fm[b] + cross(pointG - S.p[b], f);
+}
+__device__ __forceinline__ V3 point_velocity(const Scratch& S, int b, V3 pointG) {
+    if (b < 0) return mk(0, 0, 0);
+    return S.v[b] + cross(S.w[b], pointG - S.p[b]);
+}
+
+// SimTK::SmoothSphereHalfSpaceForce (Simbody 3.7; not in the reference tree). Written from the
+// model description in opensim-core/OpenSim/Simulation/Model/SmoothSphereHalfSpaceForce.h:28-66 and
+// Serrancoli et al. 2019: smoothed Hertz force, Hunt–Crossley dissipation,
+// smooth stick–slip friction. Returns the force on the sphere body; applies both sides.
+__device__ inline V3 contact_force(const DevTables& T, int ci, Scratch& S, bool apply) {
+    const double* cd = T.dbl + T.o_contact_d + ci * MOCOB200_CONTACT_DSTRIDE;
+    const int* cidx = T.idx + T.o_contact_i + ci * MOCOB200_CONTACT_ISTRIDE;
+    const int bs = cidx[0], bh = cidx[1];
+    const double radius = cd[3];
+    const double* pr = cd + 16;
+    const double stiffness = pr[0], diss = pr[1], us = pr[2], ud = pr[3], uv = pr[4], vt = pr[5], cf = pr[6], bd = pr[7], bv = pr[8];
+    // half-space frame in ground; the half space fills +x of its frame, so the outward normal is -x
+    V3 nrm, oH;
+    {
+        const V3 xh = mk(cd[4], cd[7], cd[10]);
+        V3 ph = ld3(cd + 13);
+        if (bh >= 0) { nrm = -1.0 * rmul(S.R[bh], xh); oH = S.p[bh] + rmul(S.R[bh], ph); }
+        else { nrm = -1.0 * xh; oH = ph; }
+    }
+    const V3 centre = (bs >= 0) ? S.p[bs] + rmul(S.R[bs], ld3(cd)) : ld3(cd);
+    const double indentation = radius - dot(centre - oH, nrm);
+    // contact point: sphere surface point nearest the plane, moved half the indentation back in
+    const V3 cp = centre - (radius - 0.5 * indentation) * nrm;
+    const V3 vrel = point_velocity(S, bs, cp) - point_velocity(S, bh, cp);
+    const double vnormal = dot(vrel, nrm);
+    const V3 vtan = vrel - vnormal * nrm;
+    const double indVel = -vnormal;
+    const double k = 0.5 * pow(stiffness, 2.0 / 3.0);
+    const double fH = (4.0 / 3.0) * k * sqrt(radius * k) * pow(sqrt(indentation * indentation + cf), 1.5);
+    const double fHs = fH * (0.5 + 0.5 * tanh(bd * indentation)) + cf;
+    const double fHC = fHs * (1.0 + 1.5 * diss * indVel);
+    const double fn = fHC * (0.5 + 0.5 * tanh(bv * (indVel + 2.0 / (3.0 * diss))));
+    V3 force = fn * nrm;
+    const double vslip = sqrt(dot(vtan, vtan) + cf);
+    const double vr = vslip / vt;
+    const double ff = fn * (fmin(vr, 1.0) * (ud + 2.0 * (us - ud) / (1.0 + vr * vr)) + uv * vslip);
+    force = force + (-ff / vslip) * vtan;
+    if (apply) {
+        apply_point_force(S, bs, cp, force);
+        apply_point_force(S, bh, cp, -1.0 * force);
+    }
+    return force;
+}
+
+// Muscle path geometry + muscle model + equivalent forces for muscle m
+// (GeometryPath.cpp:306-432, 817-864, 1117-1145; Point.cpp:130-140; ConditionalPathPoint.cpp:160-169;
+//  MovingPathPoint.cpp:216-315, 374-392; PathActuator.cpp:170-197).
+__device__ inline MuscleOut muscle_force(const DevTables& T, int m, const double* q, const double* u, const double* z,
+                                        const double* ctl, const double* deriv, Scratch& S, bool apply, bool wantStiffness) {
+    const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
+    const double* md = T.dbl + T.o_mus_d + m * MOCOB200_MUS_DSTRIDE;
+    const int first = mi[0], count = mi[1], flags = mi[5];
+    V3 pos[MOCOB200_MAXPPM], dPdq[MOCOB200_MAXPPM];
+    int body[MOCOB200_MAXPPM], mcoord[MOCOB200_MAXPPM];
+    int na = 0;
+    double length = 0, speed = 0;
+    V3 prevP = mk(0, 0, 0), prevV = mk(0, 0, 0);
+    for (int k = 0; k < count; ++k) {
+        const int* pi = T.idx + T.o_pp_i + (first + k) * MOCOB200_PP_ISTRIDE;
+        const double* pd = T.dbl + T.o_pp_d + (first + k) * MOCOB200_PP_DSTRIDE;
+        const int b = pi[0], kind = pi[1];
+        V3 loc = ld3(pd), vloc = mk(0, 0, 0), dp = mk(0, 0, 0);
+        int mc = -1;
+        if (kind == MOCOB200_PP_CONDITIONAL) {
+            const double val = q[pi[2]];
+            if (!(val >= pd[3] - 1e-5 && val <= pd[4] + 1e-5)) continue;
+        } else if (kind == MOCOB200_PP_MOVING) {
+            mc = pi[6];
+            const double qv = q[mc];
+            const double qc = fmin(fmax(qv, pd[3]), pd[4]); // location clamps the coordinate, derivatives do not
+            loc = mk(simm_spline(T, pi[3], qc, 0), simm_spline(T, pi[4], qc, 0), simm_spline(T, pi[5], qc, 0));
+            dp = mk(simm_spline(T, pi[3], qv, 1), simm_spline(T, pi[4], qv, 1), simm_spline(T, pi[5], qv, 1));
+            vloc = u[mc] * dp;
+        }
+        V3 pG, vG;
+        if (b >= 0) {
+            const V3 r = rmul(S.R[b], loc);
+            pG = S.p[b] + r;
+            vG = S.v[b] + cross(S.w[b], r);
+            if (mc >= 0) { vG = vG + rmul(S.R[b], vloc); dp = rmul(S.R[b], dp); }
+        } else {
+            pG = loc;
+            vG = vloc;
+        }
+        if (na > 0) {
+            const V3 r = prevP - pG, dv = prevV - vG;
+            const double d = sqrt(dot(r, r));
+            length += d;
+            speed += (d < 2.220446049250313e-16) ? sqrt(dot(dv, dv)) : dot(dv, (1.0 / d) * r);
+        }
+        prevP = pG;
+        prevV = vG;
+        if (na < MOCOB200_MAXPPM) { pos[na] = pG; body[na] = b; mcoord[na] = mc; dPdq[na] = dp; }
+        ++na;
+    }
+    double activation = (flags & MOCOB200_MUS_FLAG_IGNORE_ACTIVATION_DYNAMICS) ? ctl[mi[2]] : z[mi[3]];
+    const double ntf = (mi[4] >= 0) ? z[mi[4]] : NAN;
+    const double ntfd = (mi[6] >= 0) ? deriv[mi[6]] : NAN;
+    MuscleOut o = dgf_muscle(md, flags, length, speed, activation, ntf, ntfd, wantStiffness);
+    if (apply) {
+        const double tension = o.tendonForce;
+        for (int k = 0; k + 1 < na; ++k) {
+            if (body[k] == body[k + 1]) continue;
+            V3 dir = pos[k + 1] - pos[k];
+            const double nn = sqrt(dot(dir, dir));
+            // SimTK::SignificantReal = eps^(7/8)
+            dir = (nn < 1.9984014443252818e-14) ? (NAN * dir) : ((1.0 / nn) * dir);
+            const V3 f = tension * dir;
+            apply_point_force(S, body[k], pos[k], f);
+            apply_point_force(S, body[k + 1], pos[k + 1], -1.0 * f);
+            if (mcoord[k] >= 0) S.tau[mcoord[k]] += dot(dPdq[k], f);
+            if (mcoord[k + 1] >= 0) S.tau[mcoord[k + 1]] -= dot(dPdq[k + 1], f);
+        }
+    }
+    return o;
+}
+
+// activation dynamics (DeGrooteFregly2016Muscle.cpp:190-210)
+__device__ __forceinline__ double activation_dot(double e, double a, double tauA, double tauD) {
+    const double zf = 0.5 + 1.5 * a;
+    const double tempAct = 1.0 / (tauA * zf);
+    const double tempDeact = zf / tauD;
+    const double f = 0.5 * tanh(0.1 * (e - a));
+    const double timeConst = tempAct * (f + 0.5) + tempDeact * (-f + 0.5);
+    return timeConst * (e - a);
+}
+
+// 6x6 symmetric articulated inertia in blocks: A (ang-ang, sym, 6), B (ang-lin, full 9), C (lin-lin, sym, 6)
+struct ArtI {
+    double A[6], B[9], C[6]; // sym order: xx yy zz xy xz yz
+};
+__device__ __forceinline__ V3 symmul(const double* s, V3 v) {
+    return mk(s[0] * v.x + s[3] * v.y + s[4] * v.z, s[3] * v.x + s[1] * v.y + s[5] * v.z, s[4] * v.x + s[5] * v.y + s[2] * v.z);
+}
+__device__ __forceinline__ V3 bmul(const double* B, V3 v) { return rmul(B, v); }
+__device__ __forceinline__ V3 btmul(const double* B, V3 v) { return rtmul(B, v); }
+
+// spatial inertia of body b about its origin, in ground: I_o = R I R^T, c = R com
+__device__ inline void body_inertia_ground(const DevTables& T, int b, const Scratch& S, double* Io /*sym6*/, V3& mc, double& mass) {
+    const double* bd = T.dbl + T.o_body_d + b * MOCOB200_BODY_DSTRIDE;
+    mass = bd[24];
+    const V3 c = rmul(S.R[b], ld3(bd + 25));
+    mc = mass * c;
+    const double* in = bd + 28;
+    const double I[9] = {in[0], in[3], in[4], in[3], in[1], in[5], in[4], in[5], in[2]};
+    double RI[9], RIRt[9];
+    mm3(S.R[b], I, RI);
+    mmt3(RI, S.R[b], RIRt);
+    Io[0] = RIRt[0]; Io[1] = RIRt[4]; Io[2] = RIRt[8];
+    Io[3] = 0.5 * (RIRt[1] + RIRt[3]); Io[4] = 0.5 * (RIRt[2] + RIRt[6]); Io[5] = 0.5 * (RIRt[5] + RIRt[7]);
+}
+
+// hinge data of body b in ground: returns dof; axes as (angular, linear-at-B-origin) pairs
+__device__ inline int hinge(const DevTables& T, int b, const Scratch& S, V3* Ha, V3* Hl, V3& oMrel /* pB - oM */) {
+    const double* bd = T.dbl + T.o_body_d + b * MOCOB200_BODY_DSTRIDE;
+    const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
+    const int par = bi[0], kind = bi[1];
+    double RGF[9];
+    if (par >= 0) mm3(S.R[par], bd, RGF);
+    else {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) RGF[k] = bd[k];
+    }
+    const V3 xF = mk(RGF[0], RGF[3], RGF[6]), yF = mk(RGF[1], RGF[4], RGF[7]), zF = mk(RGF[2], RGF[5], RGF[8]);
+    oMrel = rmul(S.R[b], ld3(bd + 21)); // = pB - oM with a minus sign: pB = oM - R_GB p_BM
+    oMrel = -1.0 * oMrel;
+    if (kind == MOCOB200_JOINT_PIN) {
+        Ha[0] = zF; Hl[0] = cross(zF, oMrel);
+        return 1;
+    }
+    if (kind == MOCOB200_JOINT_SLIDER) {
+        Ha[0] = mk(0, 0, 0); Hl[0] = xF;
+        return 1;
+    }
+    if (kind == MOCOB200_JOINT_PLANAR) {
+        Ha[0] = zF; Hl[0] = cross(zF, oMrel);
+        Ha[1] = mk(0, 0, 0); Hl[1] = xF;
+        Ha[2] = mk(0, 0, 0); Hl[2] = yF;
+        return 3;
+    }
+    return 0;
+}
+
+// velocity-dependent (Coriolis) acceleration of body b relative to its parent, ground frame
+__device__ inline void coriolis(const DevTables& T, int b, const Scratch& S, const double* u, V3& ca, V3& cl) {
+    const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
+    const int par = bi[0], q0 = bi[2];
+    V3 Ha[3], Hl[3], sv;
+    const int nd = hinge(T, b, S, Ha, Hl, sv);
+    V3 wP = mk(0, 0, 0), pP = mk(0, 0, 0);
+    if (par >= 0) { wP = S.w[par]; pP = S.p[par]; }
+    V3 wrel = mk(0, 0, 0), vrel = mk(0, 0, 0);
+    for (int k = 0; k < nd; ++k) { wrel = wrel + u[q0 + k] * Ha[k]; vrel = vrel + u[q0 + k] * Hl[k]; }
+    const V3 r = S.p[b] - pP;
+    ca = cross(wP, wrel);
+    cl = cross(wP, cross(wP, r)) + 2.0 * cross(wP, vrel) + cross(wrel, cross(wrel, sv));
+}
+
+// Explicit mode: articulated-body algorithm. udot out.
+__device__ inline void forward_dynamics(const DevTables& T, const double* u, Scratch& S, double* udot) {
+    ArtI P[MOCOB200_MAXB];
+    V3 zm[MOCOB200_MAXB], zf[MOCOB200_MAXB]; // z (moment; force)
+    V3 Ga[MOCOB200_MAXQ], Gl[MOCOB200_MAXQ]; // G = P H D^-1 columns
+    double nu[MOCOB200_MAXQ];                 // D^-1 eps
+    const int nb = T.nb;
+    // initialise with rigid-body inertias and bias forces
+    for (int b = 0; b < nb; ++b) {
+        double Io[6], mass;
+        V3 mc;
+        body_inertia_ground(T, b, S, Io, mc, mass);
+        ArtI& a = P[b];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) a.A[k] = Io[k];
+        // B = m c× ; C = m 1
+        a.B[0] = 0; a.B[1] = -mc.z; a.B[2] = mc.y;
+        a.B[3] = mc.z; a.B[4] = 0; a.B[5] = -mc.x;
+        a.B[6] = -mc.y; a.B[7] = mc.x; a.B[8] = 0;
+        a.C[0] = a.C[1] = a.C[2] = mass; a.C[3] = a.C[4] = a.C[5] = 0;
+        const V3 w = S.w[b];
+        // gyroscopic moment and centrifugal force, then minus applied force
+        zm[b] = cross(w, symmul(Io, w)) - S.Fm[b];
+        zf[b] = cross(w, cross(w, mc)) - S.Ff[b];
+    }
+    // tip to base
+    for (int b = nb - 1; b >= 0; --b) {
+        const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
+        const int par = bi[0], q0 = bi[2];
+        V3 Ha[3], Hl[3], sv, ca, cl;
+        const int nd = hinge(T, b, S, Ha, Hl, sv);
+        coriolis(T, b, S, u, ca, cl);
+        ArtI& a = P[b];
+        // z += P * coriolis
+        zm[b] = zm[b] + symmul(a.A, ca) + bmul(a.B, cl);
+        zf[b] = zf[b] + btmul(a.B, ca) + symmul(a.C, cl);
+        // joint: U = P H (6 x nd), D = H^T U
+        V3 Ua[3], Ul[3];
+        double D[9], Di[9], eps[3];
+        for (int k = 0; k < nd; ++k) {
+            Ua[k] = symmul(a.A, Ha[k]) + bmul(a.B, Hl[k]);
+            Ul[k] = btmul(a.B, Ha[k]) + symmul(a.C, Hl[k]);
+            eps[k] = S.tau[q0 + k] - (dot(Ha[k], zm[b]) + dot(Hl[k], zf[b]));
+        }
+        for (int i = 0; i < nd; ++i)
+            for (int j = 0; j < nd; ++j) D[3 * i + j] = dot(Ha[i], Ua[j]) + dot(Hl[i], Ul[j]);
+        if (nd == 1) Di[0] = 1.0 / D[0];
+        else if (nd == 3) {
+            const double c00 = D[4] * D[8] - D[5] * D[7], c01 = D[5] * D[6] - D[3] * D[8], c02 = D[3] * D[7] - D[4] * D[6];
+            const double det = D[0] * c00 + D[1] * c01 + D[2] * c02, id = 1.0 / det;
+            Di[0] = c00 * id; Di[1] = (D[2] * D[7] - D[1] * D[8]) * id; Di[2] = (D[1] * D[5] - D[2] * D[4]) * id;
+            Di[3] = c01 * id; Di[4] = (D[0] * D[8] - D[2] * D[6]) * id; Di[5] = (D[2] * D[3] - D[0] * D[5]) * id;
+            Di[6] = c02 * id; Di[7] = (D[1] * D[6] - D[0] * D[7]) * id; Di[8] = (D[0] * D[4] - D[1] * D[3]) * id;
+        }
+        V3 zpm = zm[b], zpf = zf[b];
+        for (int i = 0; i < nd; ++i) {
+            V3 ga = mk(0, 0, 0), gl = mk(0, 0, 0);
+            double n = 0;
+            for (int j = 0; j < nd; ++j) {
+                ga = ga + Di[3 * j + i] * Ua[j];
+                gl = gl + Di[3 * j + i] * Ul[j];
+                n += Di[3 * i + j] * eps[j];
+            }
+            Ga[q0 + i] = ga; Gl[q0 + i] = gl; nu[q0 + i] = n;
+        }
+        for (int i = 0; i < nd; ++i) { zpm = zpm + eps[i] * Ga[q0 + i]; zpf = zpf + eps[i] * Gl[q0 + i]; }
+        if (par < 0) continue;
+        // P+ = P - G D G^T = P - sum_i G_i U_i^T ; then shift to the parent origin and accumulate
+        double A[9], B[9], C[9];
+        A[0] = a.A[0]; A[1] = a.A[3]; A[2] = a.A[4]; A[3] = a.A[3]; A[4] = a.A[1]; A[5] = a.A[5]; A[6] = a.A[4]; A[7] = a.A[5]; A[8] = a.A[2];
+        C[0] = a.C[0]; C[1] = a.C[3]; C[2] = a.C[4]; C[3] = a.C[3]; C[4] = a.C[1]; C[5] = a.C[5]; C[6] = a.C[4]; C[7] = a.C[5]; C[8] = a.C[2];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) B[k] = a.B[k];
+        for (int i = 0; i < nd; ++i) {
+            const double ga[3] = {Ga[q0 + i].x, Ga[q0 + i].y, Ga[q0 + i].z}, gl[3] = {Gl[q0 + i].x, Gl[q0 + i].y, Gl[q0 + i].z};
+            const double ua[3] = {Ua[i].x, Ua[i].y, Ua[i].z}, ul[3] = {Ul[i].x, Ul[i].y, Ul[i].z};
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    A[3 * r + c] -= ga[r] * ua[c];
+                    B[3 * r + c] -= ga[r] * ul[c];
+                    C[3 * r + c] -= gl[r] * ul[c];
+                }
+        }
+        // shift by r = pB - pP : A' = A + rx B^T + B rx^T + rx C rx^T ; B' = B + rx C ; C' = C
+        const V3 r = S.p[b] - S.p[par];
+        const double rx[9] = {0, -r.z, r.y, r.z, 0, -r.x, -r.y, r.x, 0};
+        double rxC[9], Bp[9], t1[9], t2[9];
+        mm3(rx, C, rxC);
+#pragma unroll
+        for (int k = 0; k < 9; ++k) Bp[k] = B[k] + rxC[k];
+        mmt3(rx, B, t1);  // rx B^T
+        mmt3(Bp, rx, t2); // (B + rx C) rx^T
+        ArtI& pa = P[par];
+        double Ap[9];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) Ap[k] = A[k] + t1[k] + t2[k];
+        pa.A[0] += Ap[0]; pa.A[1] += Ap[4]; pa.A[2] += Ap[8];
+        pa.A[3] += 0.5 * (Ap[1] + Ap[3]); pa.A[4] += 0.5 * (Ap[2] + Ap[6]); pa.A[5] += 0.5 * (Ap[5] + Ap[7]);
+#pragma unroll
+        for (int k = 0; k < 9; ++k) pa.B[k] += Bp[k];
+        pa.C[0] += C[0]; pa.C[1] += C[4]; pa.C[2] += C[8];
+        pa.C[3] += 0.5 * (C[1] + C[3]); pa.C[4] += 0.5 * (C[2] + C[6]); pa.C[5] += 0.5 * (C[5] + C[7]);
+        zm[par] = zm[par] + zpm + cross(r, zpf);
+        zf[par] = zf[par] + zpf;
+    }
+    // base to tip: accelerations. Reuse zm/zf as the spatial acceleration (alpha ; a_origin).
+    for (int b = 0; b < nb; ++b) {
+        const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
+        const int par = bi[0], q0 = bi[2];
+        V3 Ha[3], Hl[3], sv, ca, cl;
+        const int nd = hinge(T, b, S, Ha, Hl, sv);
+        coriolis(T, b, S, u, ca, cl);
+        V3 aa = mk(0, 0, 0), al = mk(0, 0, 0);
+        if (par >= 0) {
+            const V3 r = S.p[b] - S.p[par];
+            aa = zm[par];
+            al = zf[par] + cross(zm[par], r);
+        }
+        for (int i = 0; i < nd; ++i) udot[q0 + i] = nu[q0 + i] - (dot(Ga[q0 + i], aa) + dot(Gl[q0 + i], al));
+        aa = aa + ca;
+        al = al + cl;
+        for (int i = 0; i < nd; ++i) { aa = aa + udot[q0 + i] * Ha[i]; al = al + udot[q0 + i] * Hl[i]; }
+        zm[b] = aa;
+        zf[b] = al;
+    }
+}
+
+// Implicit mode: residual = f_app - M udot - f_inertial by recursive Newton–Euler
+// (what SimbodyMatterSubsystem::findMotionForces reports under AccelerationMotion,
+//  MocoCasOCProblem.h:245-297; sign per Moco/doc/MocoDeveloperGuide.dox:175-208).
+__device__ inline void inverse_dynamics_residual(const DevTables& T, const double* u, const double* udot, Scratch& S, double* resid) {
+    V3 fm[MOCOB200_MAXB], ff[MOCOB200_MAXB], aa[MOCOB200_MAXB], al[MOCOB200_MAXB];
+    const int nb = T.nb;
+    for (int b = 0; b < nb; ++b) {
+        const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
+        const int par = bi[0], q0 = bi[2];
+        V3 Ha[3], Hl[3], sv, ca, cl;
+        const int nd = hinge(T, b, S, Ha, Hl, sv);
+        coriolis(T, b, S, u, ca, cl);
+        V3 a = ca, l = cl;
+        if (par >= 0) {
+            const V3 r = S.p[b] - S.p[par];
+            a = a + aa[par];
+            l = l + al[par] + cross(aa[par], r);
+        }
+        for (int i = 0; i < nd; ++i) { a = a + udot[q0 + i] * Ha[i]; l = l + udot[q0 + i] * Hl[i]; }
+        aa[b] = a; al[b] = l;
+        double Io[6], mass;
+        V3 mc;
+        body_inertia_ground(T, b, S, Io, mc, mass);
+        const V3 w = S.w[b];
+        fm[b] = symmul(Io, a) + cross(mc, l) + cross(w, symmul(Io, w)) - S.Fm[b];
+        ff[b] = mass * l + cross(a, mc) + cross(w, cross(w, mc)) - S.Ff[b];
+    }
+    for (int b = nb - 1; b >= 0; --b) {
+        const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
+        const int par = bi[0], q0 = bi[2];
+        V3 Ha[3], Hl[3], sv;
+        const int nd = hinge(T, b, S, Ha, Hl, sv);
+        for (int i = 0; i < nd; ++i) resid[q0 + i] = S.tau[q0 + i] - (dot(Ha[i], fm[b]) + dot(Hl[i], ff[b]));
+        if (par >= 0) {
+            const V3 r = S.p[b] - S.p[par];
+            fm[par] = fm[par] + fm[b] + cross(r, ff[b]);
+            ff[par] = ff[par] + ff[b];
+        }
+    }
+}
+
+// whole-model mass centre in ground (Model::calcMassCenterPosition), needs kinematics()
+__device__ inline V3 mass_center(const DevTables& T, const Scratch& S) {
+    V3 acc = mk(0, 0, 0);
+    double mt = 0;
+    for (int b = 0; b < T.nb; ++b) {
+        const double* bd = T.dbl + T.o_body_d + b * MOCOB200_BODY_DSTRIDE;
+        const double m = bd[24];
+        acc = acc + m * (S.p[b] + rmul(S.R[b], ld3(bd + 25)));
+        mt += m;
+    }
+    return (1.0 / mt) * acc;
+}
+
+// The fused point function. in = [time, states(2nq+nz), controls(nc), derivatives(nd)], out[n_out].
+// mask selects output groups (one group per reference callback): bit 0 = dynamics
+// (udot|residual, zdot, aux residuals), bit 1+k = integrand k. Unselected outputs are left untouched.
+__device__ inline void eval_point(const DevTables& T, const double* in, double* out, unsigned mask) {
+    const int nq = T.nq, nz = T.nz, nc = T.nc;
+    const double time = in[0];
+    const double* q = in + 1;
+    const double* u = q + nq;
+    const double* z = u + nq;
+    const double* ctl = z + nz;
+    const double* der = ctl + nc; // implicit: udot[nq] then aux derivatives
+    const double* auxder = der + (T.implicit ? nq : 0);
+    const bool dyn_on = mask & 1u;
+    // which integrands are wanted, and do any of them need kinematics + contact forces?
+    bool need_contacts = dyn_on;
+    {
+        int gi = 0;
+        for (int g2 = 0; g2 < T.ngoal; ++g2) {
+            const int* gr = T.idx + T.o_goal_i + g2 * MOCOB200_GOAL_ISTRIDE;
+            if (!gr[3]) continue;
+            if (((mask >> (1 + gi)) & 1u) && gr[0] == MOCOB200_GOAL_CONTACT_TRACKING) need_contacts = true;
+            ++gi;
+        }
+    }
+    Scratch S;
+    if (need_contacts) {
+        kinematics(T, q, u, S);
+        for (int c = 0; c < T.ncontact; ++c) {
+            const V3 f = contact_force(T, c, S, dyn_on);
+            if (c < MOCOB200_MAXCONTACT) S.contactF[c] = f;
+        }
+    }
+    double* dyn = out;            // udot or residual [nq]
+    double* zdot = out + nq;      // [nz]
+    double* auxres = zdot + nz;   // [n_auxres]
+    if (dyn_on) {
+        for (int k = 0; k < nq; ++k) S.tau[k] = 0;
+        // gravity (Model.cpp:587-590)
+        const V3 g = ld3(T.dbl + T.o_gravity);
+        for (int b = 0; b < T.nb; ++b) {
+            const double* bd = T.dbl + T.o_body_d + b * MOCOB200_BODY_DSTRIDE;
+            const double m = bd[24];
+            const V3 c = rmul(S.R[b], ld3(bd + 25));
+            S.Ff[b] = S.Ff[b] + m * g;
+            S.Fm[b] = S.Fm[b] + cross(c, m * g);
+        }
+        for (int m = 0; m < T.nmus; ++m) {
+            const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
+            const double* md = T.dbl + T.o_mus_d + m * MOCOB200_MUS_DSTRIDE;
+            MuscleOut mo = muscle_force(T, m, q, u, z, ctl, auxder, S, true, false);
+            if (mi[3] >= 0) zdot[mi[3]] = activation_dot(ctl[mi[2]], z[mi[3]], md[5], md[6]);
+            if (mi[4] >= 0) zdot[mi[4]] = mo.nfDeriv;
+            if (mi[7] >= 0) auxres[mi[7]] = mo.residual;
+        }
+        // coordinate actuators (CoordinateActuator.cpp:185-204)
+        for (int a = 0; a < T.ncact; ++a) {
+            const int* ai = T.idx + T.o_cact_i + a * MOCOB200_CACT_ISTRIDE;
+            S.tau[ai[0]] += T.dbl[T.o_cact_d + a * MOCOB200_CACT_DSTRIDE] * ctl[ai[1]];
+        }
+        if (T.implicit) inverse_dynamics_residual(T, u, der, S, dyn);
+        else forward_dynamics(T, u, S, dyn);
+    }
+    // goal integrands (MocoGoal::calcIntegrand; MocoControlGoal.cpp:121-131,
+    // MocoStateTrackingGoal.cpp:103-117, MocoContactTrackingGoal.cpp:240-287)
+    double* integ = auxres + T.n_auxres;
+    int gi = 0;
+    for (int g2 = 0; g2 < T.ngoal; ++g2) {
+        const int* gr = T.idx + T.o_goal_i + g2 * MOCOB200_GOAL_ISTRIDE;
+        if (!gr[3]) continue;
+        const int slot = gi++;
+        if (!((mask >> (1 + slot)) & 1u)) continue;
+        const int* ip = T.idx + gr[4];
+        const double* dp = T.dbl + gr[5];
+        double val = 0;
+        switch (gr[0]) {
+        case MOCOB200_GOAL_CONTROL: {
+            const int expo = ip[0], n = ip[2];
+            for (int k = 0; k < n; ++k) {
+                const double c = ctl[ip[3 + k]];
+                val += dp[3 + k] * (expo == 2 ? c * c : pow(fabs(c), (double)expo));
+            }
+        } break;
+        case MOCOB200_GOAL_STATE_TRACKING: {
+            const int n = ip[0];
+            for (int k = 0; k < n; ++k) {
+                const double e = q[ip[1 + 2 * k]] - ppoly_eval(T, ip[2 + 2 * k], time);
+                val += dp[3 + k] * (e * e);
+            }
+        } break;
+        case MOCOB200_GOAL_CONTROL_TRACKING: {
+            const int n = ip[0];
+            for (int k = 0; k < n; ++k) {
+                const double e = ctl[ip[1 + 2 * k]] - ppoly_eval(T, ip[2 + 2 * k], time);
+                val += dp[3 + k] * e * e;
+            }
+        } break;
+        case MOCOB200_GOAL_SUM_SQUARED_STATE: {
+            const int n = ip[0];
+            for (int k = 0; k < n; ++k) {
+                const double e = q[ip[1 + 2 * k]];
+                val += dp[3 + k] * e * e;
+            }
+        } break;
+        case MOCOB200_GOAL_CONTACT_TRACKING: {
+            const int proj = ip[0], ng = ip[1];
+            const V3 pv = ld3(dp + 3);
+            const int* gp = ip + 2;
+            for (int k = 0; k < ng; ++k) {
+                const int ncon = gp[0];
+                V3 fm = mk(0, 0, 0);
+                for (int c = 0; c < ncon; ++c) {
+                    const V3 f = S.contactF[gp[1 + 2 * c]];
+                    fm = (gp[2 + 2 * c] == 0) ? fm + f : fm - f;
+                }
+                gp += 1 + 2 * ncon;
+                const V3 fr = mk(ppoly_eval(T, gp[0], time), ppoly_eval(T, gp[1], time), ppoly_eval(T, gp[2], time));
+                gp += 3;
+                const V3 e3 = fm - fr;
+                V3 e = e3;
+                if (proj == 1) e = dot(e3, pv) * pv;
+                else if (proj == 2) e = e3 - dot(e3, pv) * pv;
+                val += dot(e, e);
+            }
+        } break;
+        default: break;
+        }
+        integ[slot] = val;
+    }
+}
+
+// Endpoint function of goal g (MocoGoal::calcGoal, MocoGoal.h:215-247 and the calcGoalImpl of each
+// goal class): ein = [t0, x0(ns), c0(nc), d0(nd), tf, xf(ns), cf(nc), df(nd), integral] -> vals[n_outputs].
+__device__ inline void eval_endpoint(const DevTables& T, int g, const double* ein, int ns, int nc, int nd, double* vals) {
+    const int* gr = T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
+    const int* ip = T.idx + gr[4];
+    const double* dp = T.dbl + gr[5];
+    const int half = 1 + ns + nc + nd;
+    const double t0 = ein[0], tf = ein[half];
+    const double* x0 = ein + 1;
+    const double* c0 = x0 + ns;
+    const double* d0 = c0 + nc;
+    const double* xf = ein + half + 1;
+    const double* cf = xf + ns;
+    const double integral = ein[2 * half];
+    const double w = dp[0];
+    const bool cost = gr[1] == MOCOB200_MODE_COST;
+    const int nq = T.nq;
+    auto displacement = [&]() {
+        Scratch S;
+        kinematics(T, x0, x0 + nq, S);
+        const V3 ci = mass_center(T, S);
+        kinematics(T, xf, xf + nq, S);
+        const V3 cfn = mass_center(T, S);
+        const V3 d = cfn - ci;
+        return sqrt(dot(d, d));
+    };
+    switch (gr[0]) {
+    case MOCOB200_GOAL_CONTROL: {
+        double v = integral;
+        if (ip[1]) v /= displacement();
+        vals[0] = w * v;
+    } break;
+    case MOCOB200_GOAL_STATE_TRACKING:
+    case MOCOB200_GOAL_CONTROL_TRACKING:
+    case MOCOB200_GOAL_SUM_SQUARED_STATE:
+    case MOCOB200_GOAL_CONTACT_TRACKING: vals[0] = w * integral; break;
+    case MOCOB200_GOAL_FINAL_TIME: vals[0] = w * tf; break;
+    case MOCOB200_GOAL_AVERAGE_SPEED: {
+        double v = dp[3] - displacement() / (tf - t0);
+        if (cost) v = v * v;
+        vals[0] = w * v;
+    } break;
+    case MOCOB200_GOAL_PERIODICITY: {
+        const int nsp = ip[0], ncp = ip[1];
+        double acc = 0;
+        for (int k = 0; k < nsp; ++k) {
+            double v = x0[ip[2 + 2 * k]] * dp[3 + k] - xf[ip[3 + 2 * k]];
+            if (cost) acc += w * (v * v); else vals[k] = w * v;
+        }
+        for (int k = 0; k < ncp; ++k) {
+            double v = c0[ip[2 + 2 * nsp + 2 * k]] * dp[3 + nsp + k] - cf[ip[3 + 2 * nsp + 2 * k]];
+            if (cost) acc += w * (v * v); else vals[nsp + k] = w * v;
+        }
+        if (cost) vals[0] = acc;
+    } break;
+    case MOCOB200_GOAL_INITIAL_ACTIVATION: {
+        const int n = ip[0];
+        double acc = 0;
+        for (int k = 0; k < n; ++k) {
+            double v = c0[ip[1 + 2 * k]] - x0[ip[2 + 2 * k]];
+            if (cost) acc += w * (v * v); else vals[k] = w * v;
+        }
+        if (cost) vals[0] = acc;
+    } break;
+    case MOCOB200_GOAL_INITIAL_VELOCITY_EQUILIBRIUM_DGF: {
+        const int n = ip[0];
+        Scratch S;
+        kinematics(T, x0, x0 + nq, S);
+        double acc = 0;
+        const double* auxder = d0 + (T.implicit ? nq : 0);
+        for (int k = 0; k < n; ++k) {
+            MuscleOut mo = muscle_force(T, ip[1 + k], x0, x0 + nq, x0 + 2 * nq, c0, auxder, S, false, true);
+            const double v = mo.linResidDeriv;
+            if (cost) acc += w * (v * v); else vals[k] = w * v;
+        }
+        if (cost) vals[0] = acc;
+    } break;
+    default: vals[0] = NAN; break;
+    }
+}
+
+} // namespace mocob200
