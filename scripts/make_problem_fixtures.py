@@ -1,0 +1,30 @@
+"""Flatten the reference's example problems into tests/golden/*.mb20 (run in the build container,
+where /root/reference holds 2D_gait.osim and the reference .sto data; the GPU box has neither).
+The .mb20 files hold only numbers (device tables + transcription), no reference source."""
+import importlib.util
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+spec = importlib.util.spec_from_file_location("opensim_moco_b200", os.path.join(ROOT, "opensim-moco_b200", "__init__.py"))
+m = importlib.util.module_from_spec(spec)
+spec.loader.exec_module(m)
+
+REF = os.environ.get("MOCO_REFERENCE", "/root/reference")
+GAIT = os.path.join(REF, "Moco/Examples/C++/example2DWalking")
+OUT = os.path.join(ROOT, "tests", "golden")
+CASES = {
+    "sliding_mass": ("sliding_mass", None),
+    "sliding_mass_trap": ("sliding_mass", "num_mesh_intervals=19;transcription_scheme=trapezoidal"),
+    "hanging_muscle": ("hanging_muscle", None),
+    "hanging_muscle_rigidtendon": ("hanging_muscle_rigidtendon", None),
+    "pendulum2": ("pendulum:2", None),
+    "pendulum3_implicit": ("pendulum:3", "multibody_dynamics_mode=implicit"),
+    "gait2d_tracking": ("gait2d_tracking", None),
+    "gait2d_prediction": ("gait2d_prediction", None),
+}
+for out, (name, opts) in CASES.items():
+    p = m.Problem.example(name, GAIT, opts)
+    path = os.path.join(OUT, out + ".mb20")
+    p.save(path)
+    print(out, p.dims().asdict(), os.path.getsize(path))
