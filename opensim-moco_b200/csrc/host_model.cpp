@@ -638,6 +638,14 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
             goalI.push_back(g.projection);
             goalI.push_back((int)g.groups.size());
             for (int a = 0; a < 3; ++a) goalD.push_back(g.projectionVector.v[a]);
+            {   // m_denominator = total mass * |gravity| (MocoContactTrackingGoal.cpp:76-81)
+                double denom = 0;
+                for (auto& b : M.bodies) denom += b.mass;
+                const double gmag = std::sqrt(M.gravity.v[0] * M.gravity.v[0] + M.gravity.v[1] * M.gravity.v[1] +
+                                              M.gravity.v[2] * M.gravity.v[2]);
+                if (gmag > 1.9984014443252818e-14) denom *= gmag;
+                goalD.push_back(denom);
+            }
             for (auto& grp : g.groups) {
                 goalI.push_back((int)grp.contacts.size());
                 for (auto& cname : grp.contacts) {

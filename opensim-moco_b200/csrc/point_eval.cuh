@@ -862,48 +862,46 @@ __device__ inline void eval_endpoint(const DevTables& T, int g, const double* ei
     } break;
     case MOCOB200_GOAL_STATE_TRACKING:
     case MOCOB200_GOAL_CONTROL_TRACKING:
-    case MOCOB200_GOAL_SUM_SQUARED_STATE:
-    case MOCOB200_GOAL_CONTACT_TRACKING: vals[0] = w * integral; break;
+    case MOCOB200_GOAL_SUM_SQUARED_STATE: vals[0] = w * integral; break;
+    case MOCOB200_GOAL_CONTACT_TRACKING: vals[0] = w * (integral / dp[6]); break; // MocoContactTrackingGoal.h:220-223
     case MOCOB200_GOAL_FINAL_TIME: vals[0] = w * tf; break;
     case MOCOB200_GOAL_AVERAGE_SPEED: {
         double v = dp[3] - displacement() / (tf - t0);
         if (cost) v = v * v;
         vals[0] = w * v;
     } break;
-    case MOCOB200_GOAL_PERIODICITY: {
+    case MOCOB200_GOAL_PERIODICITY: { // MocoPeriodicityGoal.cpp:100-127
         const int nsp = ip[0], ncp = ip[1];
-        double acc = 0;
         for (int k = 0; k < nsp; ++k) {
             double v = x0[ip[2 + 2 * k]] * dp[3 + k] - xf[ip[3 + 2 * k]];
-            if (cost) acc += w * (v * v); else vals[k] = w * v;
+            if (cost) v = v * v;
+            vals[k] = w * v;
         }
         for (int k = 0; k < ncp; ++k) {
             double v = c0[ip[2 + 2 * nsp + 2 * k]] * dp[3 + nsp + k] - cf[ip[3 + 2 * nsp + 2 * k]];
-            if (cost) acc += w * (v * v); else vals[nsp + k] = w * v;
+            if (cost) v = v * v;
+            vals[nsp + k] = w * v;
         }
-        if (cost) vals[0] = acc;
     } break;
-    case MOCOB200_GOAL_INITIAL_ACTIVATION: {
+    case MOCOB200_GOAL_INITIAL_ACTIVATION: { // MocoInitialActivationGoal.cpp:41-60
         const int n = ip[0];
-        double acc = 0;
         for (int k = 0; k < n; ++k) {
             double v = c0[ip[1 + 2 * k]] - x0[ip[2 + 2 * k]];
-            if (cost) acc += w * (v * v); else vals[k] = w * v;
+            if (cost) v = v * v;
+            vals[k] = w * v;
         }
-        if (cost) vals[0] = acc;
     } break;
-    case MOCOB200_GOAL_INITIAL_VELOCITY_EQUILIBRIUM_DGF: {
+    case MOCOB200_GOAL_INITIAL_VELOCITY_EQUILIBRIUM_DGF: { // MocoInitialVelocityEquilibriumDGFGoal.cpp:36-55
         const int n = ip[0];
         Scratch S;
         kinematics(T, x0, x0 + nq, S);
-        double acc = 0;
         const double* auxder = d0 + (T.implicit ? nq : 0);
         for (int k = 0; k < n; ++k) {
             MuscleOut mo = muscle_force(T, ip[1 + k], x0, x0 + nq, x0 + 2 * nq, c0, auxder, S, false, true);
-            const double v = mo.linResidDeriv;
-            if (cost) acc += w * (v * v); else vals[k] = w * v;
+            double v = mo.linResidDeriv;
+            if (cost) v = v * v;
+            vals[k] = w * v;
         }
-        if (cost) vals[0] = acc;
     } break;
     default: vals[0] = NAN; break;
     }

@@ -1,0 +1,40 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+
+
+@pytest.fixture(scope="session")
+def pkg():
+    """The product's host harness (ctypes over libmocob200.so); builds the library if it is missing."""
+    import __graft_entry__ as ge
+
+    if not os.path.exists(os.path.join(ROOT, "opensim-moco_b200", "libmocob200.so")):
+        ge.build()
+    return ge.package()
+
+
+@pytest.fixture(scope="session")
+def orc(pkg):
+    """The CPU oracle (test infrastructure)."""
+    import oracle_py
+
+    oracle_py.lib()
+    return oracle_py
+
+
+def golden(name):
+    return os.path.join(GOLDEN, name)
+
+
+FIXTURES = ["sliding_mass", "sliding_mass_trap", "hanging_muscle", "hanging_muscle_rigidtendon", "pendulum2",
+            "pendulum3_implicit", "gait2d_tracking", "gait2d_prediction"]
