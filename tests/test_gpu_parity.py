@@ -1,0 +1,246 @@
+"""Parity tests proper (need a B200): the CUDA path, called through the C ABI, against the CPU oracle on the same seeded
+inputs, plus size-independent properties at BASELINE.json's full sizes.
+
+Tolerances (also in DESIGN.md):
+  * function values (point outputs, g, f): 1e-10 relative (north_star) — measured ~1e-12.
+  * FD Jacobians: two implementations that agree to ~1e-13 in the function produce finite differences that differ by
+    (that round-off)/h. With CasADi's default steps (h = 1.5e-8 forward) this noise is ~1e-4 of the row scale for ANY
+    implementation that is not bit-identical, so the 1e-7 criterion is checked with round-off-negligible steps
+    (forward h = 1e-4, central h = 1e-3: identical truncation error on both sides), and the default steps get a
+    noise-model bound.
+"""
+import numpy as np
+import pytest
+
+from conftest import FIXTURES, golden
+
+pytestmark = pytest.mark.gpu
+
+FD_FORWARD, FD_CENTRAL, FD_BACKWARD = 0, 1, 2
+
+
+def relerr(a, b):
+    """max |a-b| / (|b| + 1e-6 max|b|): relative, with a floor so that structural zeros do not divide by zero."""
+    return float(np.max(np.abs(a - b) / (np.abs(b) + 1e-6 * np.abs(b).max() + 1e-300)))
+
+
+def load(pkg, name, intervals=None):
+    opts = None
+    if intervals is not None:
+        opts = "num_mesh_intervals=%d" % intervals
+    elif name.startswith("gait2d"):
+        opts = "num_mesh_intervals=10"
+    return pkg.Problem.load(golden(name + ".mb20"), opts)
+
+
+@pytest.mark.parametrize("name", FIXTURES)
+@pytest.mark.parametrize("seed,spread", [(1, 0.1), (2, 0.5), (3, 1.0)])
+def test_values_match_oracle(pkg, orc, name, seed, spread):
+    p = load(pkg, name)
+    ev, o = pkg.Evaluator(p), orc.Oracle(p)
+    x = p.make_iterate(seed=seed, spread=spread)
+    Y, Yo = ev.eval_points(x), o.eval_points(x)
+    assert np.isfinite(Yo).all()
+    assert relerr(Y, Yo) < 1e-10
+    assert relerr(ev.eval_g(x), o.eval_g(x)) < 1e-10
+    f, terms = ev.eval_f(x, terms=True)
+    fo, termso = o.eval_f(x, terms=True)
+    assert abs(f - fo) <= 1e-10 * max(1.0, abs(fo))
+    assert np.allclose(terms, termso, rtol=1e-10, atol=1e-12)
+
+
+@pytest.mark.parametrize("name", FIXTURES)
+def test_structure_matches_oracle(pkg, orc, name):
+    p = load(pkg, name)
+    ev, o = pkg.Evaluator(p), orc.Oracle(p)
+    c, r = ev.structure()
+    co, ro = o.structure()
+    assert np.array_equal(c, co) and np.array_equal(r, ro)
+
+
+@pytest.mark.parametrize("name", FIXTURES)
+@pytest.mark.parametrize("scheme,h", [(FD_FORWARD, 1e-4), (FD_BACKWARD, 1e-4), (FD_CENTRAL, 1e-3)])
+def test_fd_jacobian_pipeline_1e7(pkg, orc, name, scheme, h):
+    """north_star: Jacobian entries within 1e-7 relative — with steps where round-off/h is below that bar."""
+    p = load(pkg, name)
+    ev, o = pkg.Evaluator(p), orc.Oracle(p)
+    ev.set_fd(scheme, h, 0)
+    o.set_fd(scheme, h, 0)
+    x = p.make_iterate(seed=5, spread=0.3)
+    J = ev.eval_points(x, jacobian=True)
+    Yo, Jo = o.eval_point_jacobians(x)
+    scale = np.abs(Yo)[:, :, None] + np.abs(Jo) + 1e-300
+    assert np.max(np.abs(J - Jo) / scale) < 1e-7
+    v, vo = ev.eval_jac_g(x), o.eval_jac_g(x)
+    assert relerr(v, vo) < 1e-7 * 50  # entries are sums of up to ~n_in block entries scaled by h
+    gr, gro = ev.eval_grad_f(x), o.eval_grad_f(x)
+    assert np.max(np.abs(gr - gro)) <= 1e-7 * max(1.0, np.abs(gro).max())
+
+
+@pytest.mark.parametrize("name", FIXTURES)
+@pytest.mark.parametrize("scheme", [FD_FORWARD, FD_CENTRAL])
+def test_fd_jacobian_default_steps_noise_bound(pkg, orc, name, scheme):
+    """CasADi's default steps (forward sqrt(eps); central cbrt(eps) + one refinement): agreement up to the FD noise
+    floor eps*cond/h of two non-bit-identical implementations."""
+    p = load(pkg, name)
+    ev, o = pkg.Evaluator(p), orc.Oracle(p)
+    ev.set_fd(scheme)
+    o.set_fd(scheme)
+    x = p.make_iterate(seed=6, spread=0.3)
+    J = ev.eval_points(x, jacobian=True)
+    Yo, Jo = o.eval_point_jacobians(x)
+    scale = np.abs(Yo)[:, :, None] + np.abs(Jo) + 1e-300
+    assert np.max(np.abs(J - Jo) / scale) < 2e-3
+    # and the median entry is far better than the worst one
+    assert np.median(np.abs(J - Jo) / scale) < 1e-6
+
+
+def test_exact_linear_entries(pkg):
+    """Entries that do not pass through a callback are exact: interpolation rows (+1, -1/2, -1/2) and d(defect)/dx."""
+    p = load(pkg, "gait2d_tracking", 8)
+    ev = pkg.Evaluator(p)
+    d = ev.dims
+    x = p.make_iterate(seed=9, spread=0.2)
+    colptr, rowidx = ev.structure()
+    vals = ev.eval_jac_g(x)
+    # rows of the interpolating-control constraints: the last nc rows of every interval block
+    rows_per_interval = 2 * d.ns + d.nc
+    first_interp = 2 * d.ns  # after the defects (no residual rows in explicit mode, no endpoint... skip endpoint rows)
+    n_endpoint = d.n_con - rows_per_interval * (d.n_mesh - 1)
+    seen = 0
+    for c in range(d.n_var):
+        for k in range(colptr[c], colptr[c + 1]):
+            r = rowidx[k] - n_endpoint
+            if r >= 0 and (r % rows_per_interval) >= first_interp:
+                assert vals[k] in (1.0, -0.5)
+                seen += 1
+    assert seen == 3 * d.nc * (d.n_mesh - 1)
+
+
+def test_nan_passes_through(pkg):
+    """NaN/Inf in the iterate must come back as NaN in the outputs with status OK (IPOPT handles them)."""
+    p = load(pkg, "pendulum2")
+    ev = pkg.Evaluator(p)
+    x = p.make_iterate(seed=1, spread=0.1)
+    x[2 + 4 * 3] = np.nan  # a state of grid point 3
+    g = ev.eval_g(x)
+    assert np.isnan(g).any() and np.isfinite(g).any()
+    v = ev.eval_jac_g(x)
+    assert np.isnan(v).any()
+
+
+@pytest.mark.parametrize("intervals", [1, 2, 7])
+def test_small_and_odd_meshes(pkg, orc, intervals):
+    for name in ("sliding_mass_trap", "hanging_muscle", "gait2d_prediction"):
+        p = load(pkg, name, intervals)
+        ev, o = pkg.Evaluator(p), orc.Oracle(p)
+        x = p.make_iterate(seed=3, spread=0.4)
+        assert relerr(ev.eval_g(x), o.eval_g(x)) < 1e-10
+        ev.set_fd(FD_CENTRAL, 1e-3, 0)
+        o.set_fd(FD_CENTRAL, 1e-3, 0)
+        assert relerr(ev.eval_jac_g(x), o.eval_jac_g(x)) < 5e-6
+
+
+def test_nonuniform_mesh(pkg, orc):
+    p = pkg.Problem.load(golden("pendulum2.mb20"), "mesh=0,0.1,0.15,0.5,0.9,1")
+    ev, o = pkg.Evaluator(p), orc.Oracle(p)
+    assert ev.dims.n_mesh == 6
+    x = p.make_iterate(seed=2, spread=0.5)
+    assert relerr(ev.eval_g(x), o.eval_g(x)) < 1e-10
+    assert abs(ev.eval_f(x) - o.eval_f(x)) < 1e-10 * max(1, abs(o.eval_f(x)))
+
+
+# ---- full-size (BASELINE.json) properties that need no oracle run ---------------------------------------------
+@pytest.fixture(scope="module")
+def config5(pkg):
+    p = pkg.Problem.load(golden("gait2d_prediction.mb20"), "num_mesh_intervals=800")
+    return p, pkg.Evaluator(p)
+
+
+def test_config5_point_sample_matches_oracle(config5, orc):
+    """At 1601 grid points the oracle checks a sample of the points (each point function is independent)."""
+    p, ev = config5
+    o = orc.Oracle(p)
+    x = p.make_iterate(seed=12, spread=0.3)
+    Y = ev.eval_points(x)
+    for j in (0, 1, 2, 799, 800, 1599, 1600):
+        yo = o.eval_point(o.gather_inputs(x, j))
+        assert np.max(np.abs(Y[j] - yo) / (np.abs(yo) + 1e-6 * np.abs(yo).max())) < 1e-10
+
+
+def test_config5_g_is_the_transcription_of_the_point_outputs(config5):
+    """eval_g at full size against a vectorised numpy restatement of the Hermite–Simpson defects
+    (CasOCHermiteSimpson.cpp:53-105) fed with the device's own point outputs."""
+    p, ev = config5
+    d = ev.dims
+    x = p.make_iterate(seed=13, spread=0.3)
+    Y, g = ev.eval_points(x), ev.eval_g(x)
+    N, ns, nc, nq = d.n_grid, d.ns, d.nc, 10
+    X = x[2:2 + ns * N].reshape(N, ns)
+    U = x[2 + ns * N:2 + (ns + nc) * N].reshape(N, nc)
+    xdot = np.concatenate([X[:, nq:2 * nq], Y[:, :ns - nq]], axis=1)
+    h = (x[1] - x[0]) / 800.0
+    i, m, ip = slice(0, N - 1, 2), slice(1, N, 2), slice(2, N, 2)
+    herm = X[m] - 0.5 * (X[ip] + X[i]) - (h / 8.0) * (xdot[i] - xdot[ip])
+    simp = X[ip] - X[i] - (h / 6.0) * (xdot[ip] + 4 * xdot[m] + xdot[i])
+    interp = U[m] - 0.5 * (U[ip] + U[i])
+    want = np.concatenate([herm, simp, interp], axis=1).ravel()
+    n_endpoint = d.n_con - want.size
+    assert n_endpoint == 39
+    assert np.allclose(g[n_endpoint:], want, rtol=1e-12, atol=1e-9 * np.abs(want).max())
+
+
+def test_config5_jacobian_is_derivative_of_g(config5):
+    p, ev = config5
+    d = ev.dims
+    ev.set_fd(FD_CENTRAL, 1e-3, 0)
+    x = p.make_iterate(seed=14, spread=0.1)
+    colptr, rowidx = ev.structure()
+    vals = ev.eval_jac_g(x)
+    rng = np.random.default_rng(1)
+    v = rng.uniform(-1, 1, d.n_var)
+    cols = np.repeat(np.arange(d.n_var), np.diff(colptr))
+    Jv = np.bincount(rowidx, weights=vals * v[cols], minlength=d.n_con)
+    e = 1e-6
+    fd = (ev.eval_g(x + e * v) - ev.eval_g(x - e * v)) / (2 * e)
+    assert np.max(np.abs(Jv - fd)) < 1e-4 * np.abs(fd).max()
+
+
+def test_config5_invariances(config5):
+    """Physics the evaluator must respect at any size: the prediction problem has no explicit time dependence, and
+    moving the whole model forward (pelvis_tx) changes nothing because the ground is a horizontal half space."""
+    p, ev = config5
+    d = ev.dims
+    x = p.make_iterate(seed=15, spread=0.2)
+    Y = ev.eval_points(x)
+    x2 = x.copy()
+    x2[0] += 0.123
+    x2[1] += 0.123
+    assert np.max(np.abs(ev.eval_points(x2)[:, :28] - Y[:, :28])) == 0
+    x3 = x.copy()
+    x3[2 + 1:2 + d.ns * d.n_grid:d.ns] += 0.37  # state index 1 = pelvis_tx of every grid point
+    Y3 = ev.eval_points(x3)
+    assert np.max(np.abs(Y3 - Y) / (np.abs(Y) + 1e-6 * np.abs(Y).max())) < 1e-9
+
+
+def test_config5_left_right_mirror(config5):
+    """2D_gait.osim is left/right symmetric: swapping the legs' states and controls swaps the outputs."""
+    p, ev = config5
+    d = ev.dims
+    N, ns, nc = d.n_grid, d.ns, d.nc
+    x = p.make_iterate(seed=16, spread=0.2)
+    # state order: [tilt tx ty hip_l hip_r lumbar knee_l knee_r ankle_l ankle_r] values, same speeds, then 18 activations
+    # (9 right then 9 left); controls: 9 right muscles, 9 left, lumbarAct (tests/golden names)
+    qperm = np.array([0, 1, 2, 4, 3, 5, 7, 6, 9, 8])
+    sperm = np.concatenate([qperm, 10 + qperm, 20 + np.concatenate([np.arange(9, 18), np.arange(0, 9)])])
+    names_c = None
+    cperm = np.concatenate([np.arange(9, 18), np.arange(0, 9), [18]])
+    X = x[2:2 + ns * N].reshape(N, ns)
+    U = x[2 + ns * N:2 + (ns + nc) * N].reshape(N, nc)
+    xm = x.copy()
+    xm[2:2 + ns * N] = X[:, sperm].ravel()
+    xm[2 + ns * N:2 + (ns + nc) * N] = U[:, cperm].ravel()
+    Y, Ym = ev.eval_points(x), ev.eval_points(xm)
+    operm = np.concatenate([qperm, 10 + np.concatenate([np.arange(9, 18), np.arange(0, 9)])])
+    a, b = Ym[:, :28], Y[:, operm]
+    assert np.max(np.abs(a - b) / (np.abs(b) + 1e-6 * np.abs(b).max())) < 1e-8
