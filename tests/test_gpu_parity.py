@@ -24,6 +24,13 @@ def relerr(a, b):
     return float(np.max(np.abs(a - b) / (np.abs(b) + 1e-6 * np.abs(b).max() + 1e-300)))
 
 
+def rowscaled_err(v, vo, rowidx, n_con):
+    """max |v-vo| / (|vo| + largest |entry| of the same constraint row): FD error scales with the row's output."""
+    rowmax = np.zeros(n_con)
+    np.maximum.at(rowmax, rowidx, np.abs(vo))
+    return float(np.max(np.abs(v - vo) / (np.abs(vo) + rowmax[rowidx] + 1e-300)))
+
+
 def load(pkg, name, intervals=None):
     opts = None
     if intervals is not None:
@@ -72,9 +79,12 @@ def test_fd_jacobian_pipeline_1e7(pkg, orc, name, scheme, h):
     scale = np.abs(Yo)[:, :, None] + np.abs(Jo) + 1e-300
     assert np.max(np.abs(J - Jo) / scale) < 1e-7
     v, vo = ev.eval_jac_g(x), o.eval_jac_g(x)
-    assert relerr(v, vo) < 1e-7 * 50  # entries are sums of up to ~n_in block entries scaled by h
+    # CSC entries: FD error scales with the magnitude of the row's callback output, so compare against the row scale
+    _, rowidx = o.structure()
+    assert rowscaled_err(v, vo, rowidx, o.n_con) < 5e-7
     gr, gro = ev.eval_grad_f(x), o.eval_grad_f(x)
-    assert np.max(np.abs(gr - gro)) <= 1e-7 * max(1.0, np.abs(gro).max())
+    gerr = np.max(np.abs(gr - gro)) / max(1.0, np.abs(gro).max())
+    assert gerr <= 1e-7, gerr
 
 
 @pytest.mark.parametrize("name", FIXTURES)
@@ -138,7 +148,7 @@ def test_small_and_odd_meshes(pkg, orc, intervals):
         assert relerr(ev.eval_g(x), o.eval_g(x)) < 1e-10
         ev.set_fd(FD_CENTRAL, 1e-3, 0)
         o.set_fd(FD_CENTRAL, 1e-3, 0)
-        assert relerr(ev.eval_jac_g(x), o.eval_jac_g(x)) < 5e-6
+        assert rowscaled_err(ev.eval_jac_g(x), o.eval_jac_g(x), o.structure()[1], o.n_con) < 5e-7
 
 
 def test_nonuniform_mesh(pkg, orc):
@@ -230,11 +240,10 @@ def test_config5_left_right_mirror(config5):
     N, ns, nc = d.n_grid, d.ns, d.nc
     x = p.make_iterate(seed=16, spread=0.2)
     # state order: [tilt tx ty hip_l hip_r lumbar knee_l knee_r ankle_l ankle_r] values, same speeds, then 18 activations
-    # (9 right then 9 left); controls: 9 right muscles, 9 left, lumbarAct (tests/golden names)
+    # (9 right then 9 left); controls: lumbarAct, 9 right muscles, 9 left (Problem.names of the example)
     qperm = np.array([0, 1, 2, 4, 3, 5, 7, 6, 9, 8])
     sperm = np.concatenate([qperm, 10 + qperm, 20 + np.concatenate([np.arange(9, 18), np.arange(0, 9)])])
-    names_c = None
-    cperm = np.concatenate([np.arange(9, 18), np.arange(0, 9), [18]])
+    cperm = np.concatenate([[0], np.arange(10, 19), np.arange(1, 10)])
     X = x[2:2 + ns * N].reshape(N, ns)
     U = x[2 + ns * N:2 + (ns + nc) * N].reshape(N, nc)
     xm = x.copy()
