@@ -3,6 +3,7 @@
 #include <dlfcn.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -73,6 +74,8 @@ struct mocob200_handle {
     DevTables DT{};
     DevLayout DL{};
     FdSettings fd{};
+    WarpAux WA{};
+    bool useWarp = true; // MOCOB200_KERNEL=thread selects the thread-per-evaluation articulated-body kernels
     std::vector<void*> owned;
     double *d_x = nullptr, *d_Y = nullptr, *d_J = nullptr, *d_I = nullptr, *d_G = nullptr, *d_E = nullptr;
     double *d_g = nullptr, *d_vals = nullptr, *d_grad = nullptr, *d_f = nullptr;
@@ -99,6 +102,81 @@ bool ncclOk(mocob200_handle* h, int rc, const char* what) {
     if (rc == 0) return true;
     h->err = std::string(what) + ": " + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "nccl error");
     return false;
+}
+
+// Topology tables + shared-memory layout of the warp-per-evaluation kernels.
+bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err) {
+    const Layout& L = h->L;
+    const int nb = T.nb, nq = T.nq, npp = T.npp;
+    auto bodyI = [&](int b) { return T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE; };
+    std::vector<int> level(nb, 0), levelStart{0}, childStart(nb + 1, 0), childList, dofBody(nq, -1);
+    for (int b = 0; b < nb; ++b) {
+        const int par = bodyI(b)[0];
+        if (par >= b) { err = "bodies are not stored parent-before-child"; return false; }
+        level[b] = par < 0 ? 0 : level[par] + 1;
+        if (b > 0 && level[b] < level[b - 1]) { err = "bodies are not stored level by level"; return false; }
+        if (b > 0 && level[b] != level[b - 1]) levelStart.push_back(b);
+        for (int k = 0; k < bodyI(b)[3]; ++k) dofBody[bodyI(b)[2] + k] = b;
+    }
+    levelStart.push_back(nb);
+    for (int b = 0; b < nb; ++b) {
+        childStart[b] = (int)childList.size();
+        for (int c = b + 1; c < nb; ++c) if (bodyI(c)[0] == b) childList.push_back(c);
+    }
+    childStart[nb] = (int)childList.size();
+    std::vector<int> bodyPpStart(nb + 1, 0), bodyPpList, ppMpp(npp > 0 ? npp : 1, -1), mppPp, mppCoord;
+    for (int b = 0; b < nb; ++b) {
+        bodyPpStart[b] = (int)bodyPpList.size();
+        for (int p = 0; p < npp; ++p) if (T.idx[T.o_pp_i + p * MOCOB200_PP_ISTRIDE] == b) bodyPpList.push_back(p);
+    }
+    bodyPpStart[nb] = (int)bodyPpList.size();
+    for (int p = 0; p < npp; ++p) {
+        const int* pi = T.idx + T.o_pp_i + p * MOCOB200_PP_ISTRIDE;
+        if (pi[1] == MOCOB200_PP_MOVING) { ppMpp[p] = (int)mppPp.size(); mppPp.push_back(p); mppCoord.push_back(pi[6]); }
+    }
+    std::vector<int> pairI, pairJ;
+    for (int i = 0; i < nq; ++i) {
+        int b = dofBody[i];
+        while (b >= 0) {
+            for (int k = 0; k < bodyI(b)[3]; ++k) {
+                const int j = bodyI(b)[2] + k;
+                if (j <= i) { pairI.push_back(i); pairJ.push_back(j); }
+            }
+            b = bodyI(b)[0];
+        }
+    }
+    auto up = [&](const std::vector<int>& v) {
+        const int* p = devUpload(v);
+        h->owned.push_back((void*)p);
+        return p;
+    };
+    WarpAux& A = h->WA;
+    A.nlevels = (int)levelStart.size() - 1;
+    A.level_start = up(levelStart);
+    A.child_start = up(childStart);
+    A.child_list = up(childList);
+    A.body_pp_start = up(bodyPpStart);
+    A.body_pp_list = up(bodyPpList);
+    A.dof_body = up(dofBody);
+    A.pp_mpp = up(ppMpp);
+    A.mpp_pp = up(mppPp);
+    A.mpp_coord = up(mppCoord);
+    A.nmpp = (int)mppPp.size();
+    A.npairs = (int)pairI.size();
+    A.pair_i = up(pairI);
+    A.pair_j = up(pairJ);
+    int o = 0;
+    auto take = [&](int n) { const int at = o; o += (n + 1) & ~1; return at; };
+    A.o_in = take(L.n_in); A.o_out = take(L.n_out); A.o_out2 = take(L.n_out);
+    A.o_R = take(9 * nb); A.o_p = take(3 * nb); A.o_w = take(3 * nb); A.o_v = take(3 * nb); A.o_cg = take(3 * nb);
+    A.o_oM = take(3 * nb); A.o_Io = take(6 * nb); A.o_F = take(3 * nb); A.o_N = take(3 * nb); A.o_al = take(3 * nb);
+    A.o_ac = take(3 * nb); A.o_cm = take(nb); A.o_ch = take(3 * nb); A.o_cJ = take(6 * nb);
+    A.o_a = take(3 * nq); A.o_l = take(3 * nq); A.o_tau = take(nq); A.o_taub = take(nq); A.o_lin = take(3 * nq);
+    A.o_ang = take(3 * nq); A.o_M = take(nq * nq);
+    A.o_ppos = take(3 * npp); A.o_pf = take(3 * npp); A.o_dp = take(3 * A.nmpp);
+    A.o_cF = take(3 * T.ncontact); A.o_cP = take(3 * T.ncontact);
+    A.ws_doubles = o;
+    return warp_kernels_configure(A, err);
 }
 
 void defaultFd(FdSettings& fd, int scheme) {
@@ -145,7 +223,8 @@ bool gatherBlocks(mocob200_handle* h, double* d_buf, size_t stride) {
 
 // stages shared by the pipelines; x must already be in d_x
 bool runNominal(mocob200_handle* h) {
-    launch_points_nominal(h->DT, h->DL, h->d_x, h->d_Y, h->p0, h->p1 - h->p0, h->stream);
+    if (h->useWarp) launch_wpoints_nominal(h->DT, h->WA, h->DL, h->d_x, h->d_Y, h->p0, h->p1 - h->p0, h->stream);
+    else launch_points_nominal(h->DT, h->DL, h->d_x, h->d_Y, h->p0, h->p1 - h->p0, h->stream);
     h->launches++;
     if (!gatherBlocks(h, h->d_Y, (size_t)h->L.n_out)) return false;
     if (h->rank == 0) {
@@ -157,9 +236,9 @@ bool runNominal(mocob200_handle* h) {
 }
 bool runFd(mocob200_handle* h) {
     cudaEventRecord(h->ev[0], h->stream);
-    launch_points_fd(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream);
+    if (h->useWarp) h->launches += launch_wpoints_fd(h->DT, h->WA, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream);
+    else { launch_points_fd(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream); h->launches++; }
     cudaEventRecord(h->ev[1], h->stream);
-    h->launches++;
     if (!gatherBlocks(h, h->d_Y, (size_t)h->L.n_out)) return false;
     if (!gatherBlocks(h, h->d_J, (size_t)h->L.n_out * h->L.n_in)) return false;
     if (h->rank == 0) {
@@ -283,6 +362,12 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     G.colptr = (const int*)own(devUpload(L.colptr));
     G.rowidx = (const int*)own(devUpload(L.rowidx));
     G.nnzcol = (const int*)own(devUpload(L.nnzcol));
+    {
+        const char* k = getenv("MOCOB200_KERNEL");
+        h->useWarp = !(k && std::string(k) == "thread");
+        std::string e;
+        if (h->useWarp && !buildWarpAux(h, *T, e)) return fail(MOCOB200_ERR_UNSUPPORTED, "warp kernels: " + e);
+    }
     // work buffers
     h->d_x = (double*)own(devAlloc<double>(L.n_var));
     h->d_Y = (double*)own(devAlloc<double>((size_t)L.n_grid * L.n_out));

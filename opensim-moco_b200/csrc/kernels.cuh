@@ -1,7 +1,10 @@
 // Kernels of the evaluator: point functions over the grid, their finite-difference blocks,
 // endpoint functions, and the assembly of g / jac_g (CSC) / grad_f.
 #pragma once
+#include <string>
+
 #include "point_eval.cuh"
+#include "point_warp.cuh"
 
 namespace mocob200 {
 
@@ -54,5 +57,12 @@ void launch_assemble_jac(const DevLayout& L, const double* d_x, const double* d_
 void launch_assemble_grad(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_Y, const double* d_J, const double* d_I,
                           const double* d_E, double* d_grad, cudaStream_t s);
 double measure_fp64_peak_tflops(int device);
+
+// warp-per-evaluation kernels (kernels_warp.cu)
+bool warp_kernels_configure(const WarpAux& A, std::string& err);
+void launch_wpoints_nominal(const DevTables& T, const WarpAux& A, const DevLayout& L, const double* d_x, double* d_Y, int p0, int np,
+                            cudaStream_t s);
+int launch_wpoints_fd(const DevTables& T, const WarpAux& A, const DevLayout& L, const FdSettings& fd, const double* d_x, double* d_Y,
+                      double* d_J, int p0, int np, cudaStream_t s);
 
 } // namespace mocob200

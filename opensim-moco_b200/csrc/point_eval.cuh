@@ -85,14 +85,11 @@ __device__ inline double simm_spline(const DevTables& T, int id, double ax, int 
     if (fabs(ax - x[0]) <= 2e-13) return scale * (deriv ? b[0] : y[0]);
     if (fabs(ax - x[n - 1]) <= 2e-13) return scale * (deriv ? b[n - 1] : y[n - 1]);
     int k = 0;
-    if (n >= 3) {
-        int i = 0, j = n;
-        for (;;) {
-            k = (i + j) >> 1;
-            if (ax < x[k]) j = k;
-            else if (ax > x[k + 1]) i = k;
-            else break;
-        }
+    if (n >= 3) { // x[k] <= ax <= x[k+1]: interpolation guess, then walk (the knots are sorted)
+        k = (int)((ax - x[0]) / (x[n - 1] - x[0]) * (double)(n - 1));
+        k = max(0, min(k, n - 2));
+        while (k > 0 && ax < x[k]) --k;
+        while (k < n - 2 && ax > x[k + 1]) ++k;
     }
     const double dx = ax - x[k];
     if (deriv) return scale * (b[k] + dx * (2.0 * c[k] + 3.0 * dx * d[k]));
@@ -107,13 +104,11 @@ __device__ inline double ppoly_eval(const DevTables& T, int id, double t) {
     const double* co = br + np + 1;
     int k = 0;
     if (t >= br[np]) k = np - 1;
-    else if (t > br[0]) {
-        int lo = 0, hi = np;
-        while (hi - lo > 1) {
-            const int mid = (lo + hi) >> 1;
-            if (t >= br[mid]) lo = mid; else hi = mid;
-        }
-        k = lo;
+    else if (t > br[0]) { // br[k] <= t < br[k+1]: interpolation guess, then walk
+        k = (int)((t - br[0]) / (br[np] - br[0]) * (double)np);
+        k = max(0, min(k, np - 1));
+        while (k > 0 && t < br[k]) --k;
+        while (k < np - 1 && t >= br[k + 1]) ++k;
     }
     const double s = t - br[k];
     const double* c = co + (size_t)k * order;

@@ -1,0 +1,255 @@
+// Warp-cooperative point function (FP64, sm_100a): ONE WARP evaluates the fused CasOC point function at one
+// (grid point, FD direction); all scratch lives in the warp's slice of shared memory and the 32 lanes are mapped to
+// the entities of each phase:
+//   kinematics        bodies of one tree level in parallel (one lane per body), level by level
+//   forces            one lane per muscle (path geometry, SimmSpline, De Groote–Fregly curves) and per contact
+//   gather            one lane per body / per coordinate: deterministic fixed-order sums of the point forces
+//   dynamics          recursive Newton–Euler bias forces + composite-rigid-body mass matrix (origin-referenced,
+//                     children pulled by their parent) + LDL^T solve (explicit) or the RNEA residual (implicit)
+//   integrands        lanes over the terms of each goal, shuffle-tree reduction (fixed order)
+// Same quantities as MocoCasOCProblem.h:203-356 computes through SimTK::State (see point_eval.cuh for the
+// per-equation citations; the scalar curve / spline functions are shared with it). The thread-per-evaluation
+// articulated-body version in point_eval.cuh is kept as an independent formulation for cross-checks.
+#pragma once
+#include "point_eval.cuh"
+
+namespace mocob200 {
+
+// Topology tables derived from mocob200_tables at create time (device pointers) + the per-warp scratch layout.
+struct WarpAux {
+    int nlevels;
+    const int* level_start;   // [nlevels+1]: bodies are stored level by level (Simbody tree order)
+    const int* child_start;   // [nb+1]
+    const int* child_list;
+    const int* body_pp_start; // [nb+1]: path points attached to each body
+    const int* body_pp_list;
+    const int* dof_body;      // [nq]
+    const int* pp_mpp;        // [npp]: ordinal among the moving path points, or -1
+    const int* mpp_pp;        // [nmpp]: path point index of each moving point
+    const int* mpp_coord;     // [nmpp]
+    int nmpp, npairs;
+    const int* pair_i;        // mass-matrix entries (i >= j, dof j on the path from dof i to ground)
+    const int* pair_j;
+    // scratch layout, offsets in doubles
+    int o_in, o_out, o_out2, o_R, o_p, o_w, o_v, o_cg, o_oM, o_Io, o_F, o_N, o_al, o_ac, o_cm, o_ch, o_cJ, o_a, o_l, o_tau,
+        o_taub, o_lin, o_ang, o_M, o_ppos, o_pf, o_dp, o_cF, o_cP;
+    int ws_doubles;
+};
+
+__device__ __forceinline__ V3 ldv(const double* p) { return mk(p[0], p[1], p[2]); }
+__device__ __forceinline__ void stv(double* p, V3 a) { p[0] = a.x; p[1] = a.y; p[2] = a.z; }
+
+struct WarpCtx {
+    const DevTables& T;
+    const WarpAux& A;
+    double* ws;
+    int lane;
+    __device__ double* at(int off) const { return ws + off; }
+};
+
+// ---- phase 1: position + velocity kinematics of body b (one lane) -----------------------------------------------
+__device__ inline void wk_body_kinematics(const WarpCtx& C, int b, const double* q, const double* u) {
+    const DevTables& T = C.T;
+    const WarpAux& A = C.A;
+    const double* bd = T.dbl + T.o_body_d + b * MOCOB200_BODY_DSTRIDE;
+    const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
+    const int par = bi[0], kind = bi[1], q0 = bi[2];
+    double RGF[9];
+    V3 oF, wP = mk(0, 0, 0), vP = mk(0, 0, 0), pP = mk(0, 0, 0);
+    if (par >= 0) {
+        const double* Rp = C.at(A.o_R) + 9 * par;
+        mm3(Rp, bd, RGF);
+        pP = ldv(C.at(A.o_p) + 3 * par);
+        oF = pP + rmul(Rp, ld3(bd + 9));
+        wP = ldv(C.at(A.o_w) + 3 * par);
+        vP = ldv(C.at(A.o_v) + 3 * par);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) RGF[k] = bd[k];
+        oF = ld3(bd + 9);
+    }
+    const V3 xF = mk(RGF[0], RGF[3], RGF[6]), yF = mk(RGF[1], RGF[4], RGF[7]), zF = mk(RGF[2], RGF[5], RGF[8]);
+    double RGM[9];
+    V3 oM = oF, wrel = mk(0, 0, 0), vrel = mk(0, 0, 0);
+    double* ax = C.at(A.o_a);
+    double* lx = C.at(A.o_l);
+    if (kind == MOCOB200_JOINT_PIN || kind == MOCOB200_JOINT_PLANAR) {
+        double s, c;
+        sincos(q[q0], &s, &c);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) { // R_GM = R_GF Rz(theta)
+            RGM[3 * i] = RGF[3 * i] * c + RGF[3 * i + 1] * s;
+            RGM[3 * i + 1] = -RGF[3 * i] * s + RGF[3 * i + 1] * c;
+            RGM[3 * i + 2] = RGF[3 * i + 2];
+        }
+        stv(ax + 3 * q0, zF);
+        stv(lx + 3 * q0, mk(0, 0, 0));
+        wrel = u[q0] * zF;
+        if (kind == MOCOB200_JOINT_PLANAR) {
+            oM = oF + q[q0 + 1] * xF + q[q0 + 2] * yF;
+            vrel = u[q0 + 1] * xF + u[q0 + 2] * yF;
+            stv(ax + 3 * (q0 + 1), mk(0, 0, 0));
+            stv(lx + 3 * (q0 + 1), xF);
+            stv(ax + 3 * (q0 + 2), mk(0, 0, 0));
+            stv(lx + 3 * (q0 + 2), yF);
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) RGM[k] = RGF[k];
+        if (kind == MOCOB200_JOINT_SLIDER) {
+            oM = oF + q[q0] * xF;
+            vrel = u[q0] * xF;
+            stv(ax + 3 * q0, mk(0, 0, 0));
+            stv(lx + 3 * q0, xF);
+        }
+    }
+    double* Rb = C.at(A.o_R) + 9 * b;
+    mmt3(RGM, bd + 12, Rb); // R_GB = R_GM R_BM^T
+    const V3 pB = oM - rmul(Rb, ld3(bd + 21));
+    const V3 wB = wP + wrel;
+    const V3 vM = vP + cross(wP, oM - pP) + vrel;
+    stv(C.at(A.o_p) + 3 * b, pB);
+    stv(C.at(A.o_oM) + 3 * b, oM);
+    stv(C.at(A.o_w) + 3 * b, wB);
+    stv(C.at(A.o_v) + 3 * b, vM + cross(wB, pB - oM));
+    stv(C.at(A.o_cg) + 3 * b, rmul(Rb, ld3(bd + 25)));
+    // inertia about the body origin, in ground: R I R^T (sym6: xx yy zz xy xz yz)
+    const double* in = bd + 28;
+    const double I[9] = {in[0], in[3], in[4], in[3], in[1], in[5], in[4], in[5], in[2]};
+    double RI[9], RIRt[9];
+    mm3(Rb, I, RI);
+    mmt3(RI, Rb, RIRt);
+    double* Io = C.at(A.o_Io) + 6 * b;
+    Io[0] = RIRt[0]; Io[1] = RIRt[4]; Io[2] = RIRt[8];
+    Io[3] = 0.5 * (RIRt[1] + RIRt[3]); Io[4] = 0.5 * (RIRt[2] + RIRt[6]); Io[5] = 0.5 * (RIRt[5] + RIRt[7]);
+}
+
+__device__ __forceinline__ V3 wk_point_velocity(const WarpCtx& C, int b, V3 pointG) {
+    if (b < 0) return mk(0, 0, 0);
+    return ldv(C.at(C.A.o_v) + 3 * b) + cross(ldv(C.at(C.A.o_w) + 3 * b), pointG - ldv(C.at(C.A.o_p) + 3 * b));
+}
+
+// ---- phase 2a: one contact (one lane): force on the sphere body + point of application ---------------------------
+__device__ inline void wk_contact(const WarpCtx& C, int ci) {
+    const DevTables& T = C.T;
+    const WarpAux& A = C.A;
+    const double* cd = T.dbl + T.o_contact_d + ci * MOCOB200_CONTACT_DSTRIDE;
+    const int* cidx = T.idx + T.o_contact_i + ci * MOCOB200_CONTACT_ISTRIDE;
+    const int bs = cidx[0], bh = cidx[1];
+    const double radius = cd[3];
+    const double* pr = cd + 16;
+    const double stiffness = pr[0], diss = pr[1], us = pr[2], ud = pr[3], uv = pr[4], vt = pr[5], cf = pr[6], bd = pr[7], bv = pr[8];
+    V3 nrm, oH;
+    {
+        const V3 xh = mk(cd[4], cd[7], cd[10]);
+        const V3 ph = ld3(cd + 13);
+        if (bh >= 0) {
+            const double* Rh = C.at(A.o_R) + 9 * bh;
+            nrm = -1.0 * rmul(Rh, xh);
+            oH = ldv(C.at(A.o_p) + 3 * bh) + rmul(Rh, ph);
+        } else { nrm = -1.0 * xh; oH = ph; }
+    }
+    const V3 centre = (bs >= 0) ? ldv(C.at(A.o_p) + 3 * bs) + rmul(C.at(A.o_R) + 9 * bs, ld3(cd)) : ld3(cd);
+    const double indentation = radius - dot(centre - oH, nrm);
+    const V3 cp = centre - (radius - 0.5 * indentation) * nrm;
+    const V3 vrel = wk_point_velocity(C, bs, cp) - wk_point_velocity(C, bh, cp);
+    const double vnormal = dot(vrel, nrm);
+    const V3 vtan = vrel - vnormal * nrm;
+    const double indVel = -vnormal;
+    const double k = 0.5 * pow(stiffness, 2.0 / 3.0);
+    const double fH = (4.0 / 3.0) * k * sqrt(radius * k) * pow(sqrt(indentation * indentation + cf), 1.5);
+    const double fHs = fH * (0.5 + 0.5 * tanh(bd * indentation)) + cf;
+    const double fHC = fHs * (1.0 + 1.5 * diss * indVel);
+    const double fn = fHC * (0.5 + 0.5 * tanh(bv * (indVel + 2.0 / (3.0 * diss))));
+    const double vslip = sqrt(dot(vtan, vtan) + cf);
+    const double vr = vslip / vt;
+    const double ff = fn * (fmin(vr, 1.0) * (ud + 2.0 * (us - ud) / (1.0 + vr * vr)) + uv * vslip);
+    stv(C.at(A.o_cF) + 3 * ci, fn * nrm + (-ff / vslip) * vtan);
+    stv(C.at(A.o_cP) + 3 * ci, cp);
+}
+
+// ---- phase 2b: one muscle (one lane): path geometry, muscle model, per-point forces ------------------------------
+__device__ inline MuscleOut wk_muscle(const WarpCtx& C, int m, const double* q, const double* u, const double* z, const double* ctl,
+                                      const double* auxder, bool apply, bool wantStiffness) {
+    const DevTables& T = C.T;
+    const WarpAux& A = C.A;
+    const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
+    const double* md = T.dbl + T.o_mus_d + m * MOCOB200_MUS_DSTRIDE;
+    const int first = mi[0], count = mi[1], flags = mi[5];
+    double* ppos = C.at(A.o_ppos);
+    double length = 0, speed = 0;
+    V3 prevP = mk(0, 0, 0), prevV = mk(0, 0, 0);
+    int na = 0;
+    unsigned active = 0; // bit k: point k of this muscle is on the current path
+    for (int k = 0; k < count; ++k) {
+        const int pp = first + k;
+        const int* pi = T.idx + T.o_pp_i + pp * MOCOB200_PP_ISTRIDE;
+        const double* pd = T.dbl + T.o_pp_d + pp * MOCOB200_PP_DSTRIDE;
+        const int b = pi[0], kind = pi[1];
+        V3 loc = ld3(pd), vloc = mk(0, 0, 0), dp = mk(0, 0, 0);
+        int mc = -1;
+        if (kind == MOCOB200_PP_CONDITIONAL) {
+            const double val = q[pi[2]];
+            if (!(val >= pd[3] - 1e-5 && val <= pd[4] + 1e-5)) continue;
+        } else if (kind == MOCOB200_PP_MOVING) {
+            mc = pi[6];
+            const double qv = q[mc];
+            const double qc = fmin(fmax(qv, pd[3]), pd[4]); // location clamps the coordinate, derivatives do not
+            loc = mk(simm_spline(T, pi[3], qc, 0), simm_spline(T, pi[4], qc, 0), simm_spline(T, pi[5], qc, 0));
+            dp = mk(simm_spline(T, pi[3], qv, 1), simm_spline(T, pi[4], qv, 1), simm_spline(T, pi[5], qv, 1));
+            vloc = u[mc] * dp;
+        }
+        V3 pG, vG;
+        if (b >= 0) {
+            const double* Rb = C.at(A.o_R) + 9 * b;
+            const V3 r = rmul(Rb, loc);
+            pG = ldv(C.at(A.o_p) + 3 * b) + r;
+            vG = ldv(C.at(A.o_v) + 3 * b) + cross(ldv(C.at(A.o_w) + 3 * b), r);
+            if (mc >= 0) { vG = vG + rmul(Rb, vloc); dp = rmul(Rb, dp); }
+        } else {
+            pG = loc;
+            vG = vloc;
+        }
+        if (na > 0) {
+            const V3 r = prevP - pG, dv = prevV - vG;
+            const double d = sqrt(dot(r, r));
+            length += d;
+            speed += (d < 2.220446049250313e-16) ? sqrt(dot(dv, dv)) : dot(dv, (1.0 / d) * r);
+        }
+        prevP = pG;
+        prevV = vG;
+        stv(ppos + 3 * pp, pG);
+        if (mc >= 0) stv(C.at(A.o_dp) + 3 * A.pp_mpp[pp], dp);
+        active |= 1u << k;
+        ++na;
+    }
+    const double activation = (flags & MOCOB200_MUS_FLAG_IGNORE_ACTIVATION_DYNAMICS) ? ctl[mi[2]] : z[mi[3]];
+    const double ntf = (mi[4] >= 0) ? z[mi[4]] : NAN;
+    const double ntfd = (mi[6] >= 0) ? auxder[mi[6]] : NAN;
+    MuscleOut o = dgf_muscle(md, flags, length, speed, activation, ntf, ntfd, wantStiffness);
+    if (apply) {
+        // net force of the path on the body at every active point (GeometryPath.cpp:306-432): +T dir at the start
+        // of a segment, -T dir at its end; segments between points of the same body carry no force
+        double* pf = C.at(A.o_pf);
+        int prev = -1;
+        for (int k = 0; k < count; ++k) {
+            if (!((active >> k) & 1u)) continue;
+            if (prev >= 0) {
+                const int pa = first + prev, pb = first + k;
+                const int ba = T.idx[T.o_pp_i + pa * MOCOB200_PP_ISTRIDE], bb = T.idx[T.o_pp_i + pb * MOCOB200_PP_ISTRIDE];
+                if (ba != bb) {
+                    V3 dir = ldv(ppos + 3 * pb) - ldv(ppos + 3 * pa);
+                    const double nn = sqrt(dot(dir, dir));
+                    dir = (nn < 1.9984014443252818e-14) ? (NAN * dir) : ((1.0 / nn) * dir);
+                    const V3 f = o.tendonForce * dir;
+                    stv(pf + 3 * pa, ldv(pf + 3 * pa) + f);
+                    stv(pf + 3 * pb, ldv(pf + 3 * pb) - f);
+                }
+            }
+            prev = k;
+        }
+    }
+    return o;
+}
+
+} // namespace mocob200

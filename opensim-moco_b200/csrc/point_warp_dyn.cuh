@@ -1,0 +1,352 @@
+// Warp-cooperative point function, part 2: gather of applied forces, dynamics, integrands, and the driver.
+#pragma once
+#include "point_warp.cuh"
+
+namespace mocob200 {
+
+__device__ __forceinline__ V3 sym6mul(const double* s, V3 v) { return symmul(s, v); }
+
+// ---- phase 3: applied wrench on body b about its origin (one lane per body), fixed summation order -------------
+__device__ inline void wk_gather_body(const WarpCtx& C, int b) {
+    const DevTables& T = C.T;
+    const WarpAux& A = C.A;
+    const double* bd = T.dbl + T.o_body_d + b * MOCOB200_BODY_DSTRIDE;
+    const V3 pB = ldv(C.at(A.o_p) + 3 * b);
+    const V3 g = ld3(T.dbl + T.o_gravity);
+    const double m = bd[24];
+    V3 F = m * g;                                        // gravity at the mass centre (Model.cpp:587-590)
+    V3 N = cross(ldv(C.at(A.o_cg) + 3 * b), m * g);
+    const double* pf = C.at(A.o_pf);
+    const double* ppos = C.at(A.o_ppos);
+    for (int k = A.body_pp_start[b]; k < A.body_pp_start[b + 1]; ++k) {
+        const int pp = A.body_pp_list[k];
+        const V3 f = ldv(pf + 3 * pp);
+        F = F + f;
+        N = N + cross(ldv(ppos + 3 * pp) - pB, f);
+    }
+    for (int c = 0; c < T.ncontact; ++c) {
+        const int* cidx = T.idx + T.o_contact_i + c * MOCOB200_CONTACT_ISTRIDE;
+        if (cidx[0] != b && cidx[1] != b) continue;
+        V3 f = ldv(C.at(A.o_cF) + 3 * c);
+        if (cidx[0] != b) f = -1.0 * f;
+        F = F + f;
+        N = N + cross(ldv(C.at(A.o_cP) + 3 * c) - pB, f);
+    }
+    stv(C.at(A.o_F) + 3 * b, F);
+    stv(C.at(A.o_N) + 3 * b, N);
+}
+// applied mobility force on coordinate k (one lane per coordinate)
+__device__ inline void wk_gather_coord(const WarpCtx& C, int k, const double* ctl) {
+    const DevTables& T = C.T;
+    const WarpAux& A = C.A;
+    double tau = 0;
+    for (int j = 0; j < A.nmpp; ++j) // moving path points driven by this coordinate: (dP/dq) . (force at the point)
+        if (A.mpp_coord[j] == k) tau += dot(ldv(C.at(A.o_dp) + 3 * j), ldv(C.at(A.o_pf) + 3 * A.mpp_pp[j]));
+    for (int a = 0; a < T.ncact; ++a) { // CoordinateActuator.cpp:185-204
+        const int* ai = T.idx + T.o_cact_i + a * MOCOB200_CACT_ISTRIDE;
+        if (ai[0] == k) tau += T.dbl[T.o_cact_d + a * MOCOB200_CACT_DSTRIDE] * ctl[ai[1]];
+    }
+    C.at(A.o_tau)[k] = tau;
+}
+
+// ---- phase 4a: RNEA outward pass for body b: accelerations, then the wrench (about the body origin) that the
+// joint must supply = inertial - applied. udot == nullptr means zero accelerations (bias forces).
+__device__ inline void wk_rnea_forward(const WarpCtx& C, int b, const double* u, const double* udot) {
+    const DevTables& T = C.T;
+    const WarpAux& A = C.A;
+    const double* bd = T.dbl + T.o_body_d + b * MOCOB200_BODY_DSTRIDE;
+    const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
+    const int par = bi[0], q0 = bi[2], nd = bi[3];
+    V3 alP = mk(0, 0, 0), aP = mk(0, 0, 0), wP = mk(0, 0, 0), pP = mk(0, 0, 0);
+    if (par >= 0) {
+        alP = ldv(C.at(A.o_al) + 3 * par);
+        aP = ldv(C.at(A.o_ac) + 3 * par);
+        wP = ldv(C.at(A.o_w) + 3 * par);
+        pP = ldv(C.at(A.o_p) + 3 * par);
+    }
+    V3 wrel = mk(0, 0, 0), vrel = mk(0, 0, 0), wrd = mk(0, 0, 0), vrd = mk(0, 0, 0);
+    for (int k = 0; k < nd; ++k) {
+        const V3 a = ldv(C.at(A.o_a) + 3 * (q0 + k)), l = ldv(C.at(A.o_l) + 3 * (q0 + k));
+        wrel = wrel + u[q0 + k] * a;
+        vrel = vrel + u[q0 + k] * l;
+        if (udot) { wrd = wrd + udot[q0 + k] * a; vrd = vrd + udot[q0 + k] * l; }
+    }
+    const V3 oM = ldv(C.at(A.o_oM) + 3 * b), pB = ldv(C.at(A.o_p) + 3 * b), w = ldv(C.at(A.o_w) + 3 * b);
+    const V3 r = oM - pP, s = pB - oM;
+    // joint axes are fixed in the parent: d(axis)/dt = wP x axis
+    const V3 al = alP + cross(wP, wrel) + wrd;
+    const V3 aM = aP + cross(alP, r) + cross(wP, cross(wP, r)) + 2.0 * cross(wP, vrel) + vrd;
+    const V3 aB = aM + cross(al, s) + cross(w, cross(w, s));
+    stv(C.at(A.o_al) + 3 * b, al);
+    stv(C.at(A.o_ac) + 3 * b, aB);
+    const double m = bd[24];
+    const V3 cg = ldv(C.at(A.o_cg) + 3 * b);
+    const double* Io = C.at(A.o_Io) + 6 * b;
+    const V3 F = m * (aB + cross(al, cg) + cross(w, cross(w, cg))) - ldv(C.at(A.o_F) + 3 * b);
+    const V3 N = sym6mul(Io, al) + cross(cg, m * aB) + cross(w, sym6mul(Io, w)) - ldv(C.at(A.o_N) + 3 * b);
+    stv(C.at(A.o_F) + 3 * b, F);
+    stv(C.at(A.o_N) + 3 * b, N);
+}
+
+// ---- phase 4b: inward pass for body b (its children are final): pull the children's wrenches and composite
+// inertias to this body's origin, then project the wrench on the joint axes.
+__device__ inline void wk_inward(const WarpCtx& C, int b, bool composite) {
+    const DevTables& T = C.T;
+    const WarpAux& A = C.A;
+    const double* bd = T.dbl + T.o_body_d + b * MOCOB200_BODY_DSTRIDE;
+    const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
+    const int q0 = bi[2], nd = bi[3];
+    const V3 pB = ldv(C.at(A.o_p) + 3 * b);
+    V3 F = ldv(C.at(A.o_F) + 3 * b), N = ldv(C.at(A.o_N) + 3 * b);
+    double cm = bd[24];
+    V3 ch = cm * ldv(C.at(A.o_cg) + 3 * b);
+    double cJ[6];
+    if (composite) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) cJ[k] = C.at(A.o_Io)[6 * b + k];
+    }
+    for (int k = A.child_start[b]; k < A.child_start[b + 1]; ++k) {
+        const int c = A.child_list[k];
+        const V3 r = ldv(C.at(A.o_p) + 3 * c) - pB;
+        const V3 Fc = ldv(C.at(A.o_F) + 3 * c);
+        F = F + Fc;
+        N = N + ldv(C.at(A.o_N) + 3 * c) + cross(r, Fc);
+        if (composite) {
+            // shift the child's composite (mass mc, first moment hc, inertia Jc about its origin) by r
+            const double mc = C.at(A.o_cm)[c];
+            const V3 hc = ldv(C.at(A.o_ch) + 3 * c);
+            const double* Jc = C.at(A.o_cJ) + 6 * c;
+            const double d = 2.0 * dot(hc, r) + mc * dot(r, r);
+            cJ[0] += Jc[0] + d - 2.0 * hc.x * r.x - mc * r.x * r.x;
+            cJ[1] += Jc[1] + d - 2.0 * hc.y * r.y - mc * r.y * r.y;
+            cJ[2] += Jc[2] + d - 2.0 * hc.z * r.z - mc * r.z * r.z;
+            cJ[3] += Jc[3] - (hc.x * r.y + r.x * hc.y) - mc * r.x * r.y;
+            cJ[4] += Jc[4] - (hc.x * r.z + r.x * hc.z) - mc * r.x * r.z;
+            cJ[5] += Jc[5] - (hc.y * r.z + r.y * hc.z) - mc * r.y * r.z;
+            ch = ch + hc + mc * r;
+            cm += mc;
+        }
+    }
+    stv(C.at(A.o_F) + 3 * b, F);
+    stv(C.at(A.o_N) + 3 * b, N);
+    if (composite) {
+        C.at(A.o_cm)[b] = cm;
+        stv(C.at(A.o_ch) + 3 * b, ch);
+#pragma unroll
+        for (int k = 0; k < 6; ++k) C.at(A.o_cJ)[6 * b + k] = cJ[k];
+    }
+    const V3 oM = ldv(C.at(A.o_oM) + 3 * b);
+    const V3 NM = N + cross(pB - oM, F); // moment about the joint point
+    for (int k = 0; k < nd; ++k)
+        C.at(A.o_taub)[q0 + k] = dot(ldv(C.at(A.o_a) + 3 * (q0 + k)), NM) + dot(ldv(C.at(A.o_l) + 3 * (q0 + k)), F);
+}
+
+// ---- phase 4c: momentum of dof i's composite body under a unit rate of dof i (about the body origin) ------------
+__device__ inline void wk_dof_momentum(const WarpCtx& C, int i) {
+    const WarpAux& A = C.A;
+    const int b = A.dof_body[i];
+    const V3 a = ldv(C.at(A.o_a) + 3 * i);
+    const V3 v0 = ldv(C.at(A.o_l) + 3 * i) + cross(a, ldv(C.at(A.o_p) + 3 * b) - ldv(C.at(A.o_oM) + 3 * b));
+    const double m = C.at(A.o_cm)[b];
+    const V3 h = ldv(C.at(A.o_ch) + 3 * b);
+    stv(C.at(A.o_lin) + 3 * i, m * v0 + cross(a, h));
+    stv(C.at(A.o_ang) + 3 * i, sym6mul(C.at(A.o_cJ) + 6 * b, a) + cross(h, v0));
+}
+__device__ inline void wk_mass_entry(const WarpCtx& C, int i, int j, int nq) {
+    const WarpAux& A = C.A;
+    const int bi = A.dof_body[i], bj = A.dof_body[j];
+    const V3 aj = ldv(C.at(A.o_a) + 3 * j);
+    const V3 vj = ldv(C.at(A.o_l) + 3 * j) + cross(aj, ldv(C.at(A.o_p) + 3 * bi) - ldv(C.at(A.o_oM) + 3 * bj));
+    const double mij = dot(aj, ldv(C.at(A.o_ang) + 3 * i)) + dot(vj, ldv(C.at(A.o_lin) + 3 * i));
+    C.at(A.o_M)[i * nq + j] = mij;
+    C.at(A.o_M)[j * nq + i] = mij;
+}
+
+// ---- phase 4d: solve M x = rhs by LDL^T in shared memory (whole warp). M is overwritten. ---------------------
+__device__ inline void wk_ldlt_solve(const WarpCtx& C, int n, const double* rhs, double* x) {
+    double* M = C.at(C.A.o_M);
+    const int lane = C.lane;
+    for (int j = 0; j < n; ++j) {
+        if (lane == 0) {
+            double d = M[j * n + j];
+            for (int k = 0; k < j; ++k) d -= M[j * n + k] * M[j * n + k] * M[k * n + k];
+            M[j * n + j] = d;
+        }
+        __syncwarp();
+        const double dj = M[j * n + j];
+        for (int i = j + 1 + lane; i < n; i += 32) {
+            double v = M[i * n + j];
+            for (int k = 0; k < j; ++k) v -= M[i * n + k] * M[j * n + k] * M[k * n + k];
+            M[i * n + j] = v / dj;
+        }
+        __syncwarp();
+    }
+    if (lane == 0) {
+        for (int i = 0; i < n; ++i) { // L y = rhs
+            double v = rhs[i];
+            for (int k = 0; k < i; ++k) v -= M[i * n + k] * x[k];
+            x[i] = v;
+        }
+        for (int i = 0; i < n; ++i) x[i] /= M[i * n + i];
+        for (int i = n - 1; i >= 0; --i) { // L^T x = z
+            double v = x[i];
+            for (int k = i + 1; k < n; ++k) v -= M[k * n + i] * x[k];
+            x[i] = v;
+        }
+    }
+    __syncwarp();
+}
+
+__device__ __forceinline__ double warp_sum(double v) { // fixed butterfly order => deterministic
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// The fused point function, evaluated by one warp. Inputs at ws[o_in..], outputs to ws[o_out..] (only the groups
+// selected by mask are written): bit 0 = dynamics (udot|residual, zdot, aux residuals), bit 1+k = integrand k.
+__device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, double* ws, unsigned mask) {
+    const WarpCtx C{T, A, ws, (int)(threadIdx.x & 31)};
+    const int lane = C.lane;
+    const int nq = T.nq, nz = T.nz, nc = T.nc, nb = T.nb;
+    const double* in = ws + A.o_in;
+    double* out = ws + A.o_out;
+    const double time = in[0];
+    const double* q = in + 1;
+    const double* u = q + nq;
+    const double* z = u + nq;
+    const double* ctl = z + nz;
+    const double* der = ctl + nc;
+    const double* auxder = der + (T.implicit ? nq : 0);
+    const bool dyn = mask & 1u;
+    bool need_contacts = dyn;
+    {
+        int gi = 0;
+        for (int g2 = 0; g2 < T.ngoal; ++g2) {
+            const int* gr = T.idx + T.o_goal_i + g2 * MOCOB200_GOAL_ISTRIDE;
+            if (!gr[3]) continue;
+            if (((mask >> (1 + gi)) & 1u) && gr[0] == MOCOB200_GOAL_CONTACT_TRACKING) need_contacts = true;
+            ++gi;
+        }
+    }
+    if (need_contacts) {
+        for (int L = 0; L < A.nlevels; ++L) {
+            for (int b = A.level_start[L] + lane; b < A.level_start[L + 1]; b += 32) wk_body_kinematics(C, b, q, u);
+            __syncwarp();
+        }
+        for (int k = lane; k < 3 * T.npp; k += 32) { ws[A.o_pf + k] = 0.0; ws[A.o_ppos + k] = 0.0; }
+        __syncwarp();
+        const int nent = (dyn ? T.nmus : 0) + T.ncontact;
+        for (int e = lane; e < nent; e += 32) {
+            if (e < T.ncontact) wk_contact(C, e);
+            else {
+                const int m = e - T.ncontact;
+                const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
+                const double* md = T.dbl + T.o_mus_d + m * MOCOB200_MUS_DSTRIDE;
+                const MuscleOut mo = wk_muscle(C, m, q, u, z, ctl, auxder, true, false);
+                double* zdot = out + nq;
+                double* auxres = zdot + nz;
+                if (mi[3] >= 0) zdot[mi[3]] = activation_dot(ctl[mi[2]], z[mi[3]], md[5], md[6]);
+                if (mi[4] >= 0) zdot[mi[4]] = mo.nfDeriv;
+                if (mi[7] >= 0) auxres[mi[7]] = mo.residual;
+            }
+        }
+        __syncwarp();
+    }
+    if (dyn) {
+        for (int b = lane; b < nb; b += 32) wk_gather_body(C, b);
+        for (int k = lane; k < nq; k += 32) wk_gather_coord(C, k, ctl);
+        __syncwarp();
+        const double* udot = T.implicit ? der : nullptr;
+        for (int L = 0; L < A.nlevels; ++L) {
+            for (int b = A.level_start[L] + lane; b < A.level_start[L + 1]; b += 32) wk_rnea_forward(C, b, u, udot);
+            __syncwarp();
+        }
+        for (int L = A.nlevels - 1; L >= 0; --L) {
+            for (int b = A.level_start[L] + lane; b < A.level_start[L + 1]; b += 32) wk_inward(C, b, !T.implicit);
+            __syncwarp();
+        }
+        if (T.implicit) {
+            for (int k = lane; k < nq; k += 32) out[k] = ws[A.o_tau + k] - ws[A.o_taub + k];
+        } else {
+            for (int k = lane; k < nq * nq; k += 32) ws[A.o_M + k] = 0.0;
+            for (int i = lane; i < nq; i += 32) {
+                wk_dof_momentum(C, i);
+                ws[A.o_tau + i] -= ws[A.o_taub + i]; // right-hand side
+            }
+            __syncwarp();
+            for (int e = lane; e < A.npairs; e += 32) wk_mass_entry(C, A.pair_i[e], A.pair_j[e], nq);
+            __syncwarp();
+            wk_ldlt_solve(C, nq, ws + A.o_tau, out);
+        }
+        __syncwarp();
+    }
+    // goal integrands (MocoControlGoal.cpp:121-131, MocoStateTrackingGoal.cpp:103-117, MocoContactTrackingGoal.cpp:240-287)
+    double* integ = out + nq + nz + T.n_auxres;
+    int gi = 0;
+    for (int g2 = 0; g2 < T.ngoal; ++g2) {
+        const int* gr = T.idx + T.o_goal_i + g2 * MOCOB200_GOAL_ISTRIDE;
+        if (!gr[3]) continue;
+        const int slot = gi++;
+        if (!((mask >> (1 + slot)) & 1u)) continue;
+        const int* ip = T.idx + gr[4];
+        const double* dp = T.dbl + gr[5];
+        double val = 0;
+        switch (gr[0]) {
+        case MOCOB200_GOAL_CONTROL: {
+            const int expo = ip[0], n = ip[2];
+            for (int k = lane; k < n; k += 32) {
+                const double c = ctl[ip[3 + k]];
+                val += dp[3 + k] * (expo == 2 ? c * c : pow(fabs(c), (double)expo));
+            }
+        } break;
+        case MOCOB200_GOAL_STATE_TRACKING:
+            for (int k = lane; k < ip[0]; k += 32) {
+                const double e = q[ip[1 + 2 * k]] - ppoly_eval(T, ip[2 + 2 * k], time);
+                val += dp[3 + k] * (e * e);
+            }
+            break;
+        case MOCOB200_GOAL_CONTROL_TRACKING:
+            for (int k = lane; k < ip[0]; k += 32) {
+                const double e = ctl[ip[1 + 2 * k]] - ppoly_eval(T, ip[2 + 2 * k], time);
+                val += dp[3 + k] * (e * e);
+            }
+            break;
+        case MOCOB200_GOAL_SUM_SQUARED_STATE:
+            for (int k = lane; k < ip[0]; k += 32) {
+                const double e = q[ip[1 + 2 * k]];
+                val += dp[3 + k] * (e * e);
+            }
+            break;
+        case MOCOB200_GOAL_CONTACT_TRACKING: {
+            const int proj = ip[0], ng = ip[1];
+            const V3 pv = ld3(dp + 3);
+            const int* gp = ip + 2;
+            for (int k = 0; k < ng; ++k) {
+                const int ncon = gp[0];
+                if ((k & 31) == lane) {
+                    V3 fm = mk(0, 0, 0);
+                    for (int c = 0; c < ncon; ++c) {
+                        const V3 f = ldv(ws + A.o_cF + 3 * gp[1 + 2 * c]);
+                        fm = (gp[2 + 2 * c] == 0) ? fm + f : fm - f;
+                    }
+                    const int* rp = gp + 1 + 2 * ncon;
+                    const V3 fr = mk(ppoly_eval(T, rp[0], time), ppoly_eval(T, rp[1], time), ppoly_eval(T, rp[2], time));
+                    const V3 e3 = fm - fr;
+                    V3 e = e3;
+                    if (proj == 1) e = dot(e3, pv) * pv;
+                    else if (proj == 2) e = e3 - dot(e3, pv) * pv;
+                    val += dot(e, e);
+                }
+                gp += 1 + 2 * ncon + 3;
+            }
+        } break;
+        default: break;
+        }
+        val = warp_sum(val);
+        if (lane == 0) integ[slot] = val;
+    }
+    __syncwarp();
+}
+
+} // namespace mocob200
