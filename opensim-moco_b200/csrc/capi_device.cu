@@ -134,6 +134,16 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
         const int* pi = T.idx + T.o_pp_i + p * MOCOB200_PP_ISTRIDE;
         if (pi[1] == MOCOB200_PP_MOVING) { ppMpp[p] = (int)mppPp.size(); mppPp.push_back(p); mppCoord.push_back(pi[6]); }
     }
+    std::vector<int> bodyFlags(nb, 0);
+    for (int b = 0; b < nb; ++b) {
+        const double* bd = T.dbl + T.o_body_d + b * MOCOB200_BODY_DSTRIDE;
+        auto isIdentity = [](const double* R) {
+            for (int k = 0; k < 9; ++k) if (R[k] != ((k % 4 == 0) ? 1.0 : 0.0)) return false;
+            return true;
+        };
+        if (isIdentity(bd)) bodyFlags[b] |= 1;
+        if (isIdentity(bd + 12)) bodyFlags[b] |= 2;
+    }
     std::vector<int> pairI, pairJ;
     for (int i = 0; i < nq; ++i) {
         int b = dofBody[i];
@@ -158,6 +168,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     A.body_pp_start = up(bodyPpStart);
     A.body_pp_list = up(bodyPpList);
     A.dof_body = up(dofBody);
+    A.body_flags = up(bodyFlags);
     A.pp_mpp = up(ppMpp);
     A.mpp_pp = up(mppPp);
     A.mpp_coord = up(mppCoord);

@@ -24,6 +24,7 @@ struct WarpAux {
     const int* body_pp_start; // [nb+1]: path points attached to each body
     const int* body_pp_list;
     const int* dof_body;      // [nq]
+    const int* body_flags;    // [nb]: bit 0 = R_PF is the identity, bit 1 = R_BM is the identity
     const int* pp_mpp;        // [npp]: ordinal among the moving path points, or -1
     const int* mpp_pp;        // [nmpp]: path point index of each moving point
     const int* mpp_coord;     // [nmpp]
@@ -48,21 +49,29 @@ struct WarpCtx {
 };
 
 // ---- phase 1: position + velocity kinematics of body b (one lane) -----------------------------------------------
-__device__ inline void wk_body_kinematics(const WarpCtx& C, int b, const double* q, const double* u) {
+// Also propagates the spatial acceleration (velocity-product terms, plus the joint accelerations udot when given):
+// it needs no forces, so the recursive part of the Newton-Euler outward pass rides along here.
+__device__ inline void wk_body_kinematics(const WarpCtx& C, int b, const double* q, const double* u, const double* udot) {
     const DevTables& T = C.T;
     const WarpAux& A = C.A;
     const double* bd = T.dbl + T.o_body_d + b * MOCOB200_BODY_DSTRIDE;
     const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
     const int par = bi[0], kind = bi[1], q0 = bi[2];
+    const int flags = A.body_flags[b];
     double RGF[9];
-    V3 oF, wP = mk(0, 0, 0), vP = mk(0, 0, 0), pP = mk(0, 0, 0);
+    V3 oF, wP = mk(0, 0, 0), vP = mk(0, 0, 0), pP = mk(0, 0, 0), alP = mk(0, 0, 0), aP = mk(0, 0, 0);
     if (par >= 0) {
         const double* Rp = C.at(A.o_R) + 9 * par;
-        mm3(Rp, bd, RGF);
+        if (flags & 1) {
+#pragma unroll
+            for (int k = 0; k < 9; ++k) RGF[k] = Rp[k];
+        } else mm3(Rp, bd, RGF);
         pP = ldv(C.at(A.o_p) + 3 * par);
         oF = pP + rmul(Rp, ld3(bd + 9));
         wP = ldv(C.at(A.o_w) + 3 * par);
         vP = ldv(C.at(A.o_v) + 3 * par);
+        alP = ldv(C.at(A.o_al) + 3 * par);
+        aP = ldv(C.at(A.o_ac) + 3 * par);
     } else {
 #pragma unroll
         for (int k = 0; k < 9; ++k) RGF[k] = bd[k];
@@ -70,7 +79,7 @@ __device__ inline void wk_body_kinematics(const WarpCtx& C, int b, const double*
     }
     const V3 xF = mk(RGF[0], RGF[3], RGF[6]), yF = mk(RGF[1], RGF[4], RGF[7]), zF = mk(RGF[2], RGF[5], RGF[8]);
     double RGM[9];
-    V3 oM = oF, wrel = mk(0, 0, 0), vrel = mk(0, 0, 0);
+    V3 oM = oF, wrel = mk(0, 0, 0), vrel = mk(0, 0, 0), wrd = mk(0, 0, 0), vrd = mk(0, 0, 0);
     double* ax = C.at(A.o_a);
     double* lx = C.at(A.o_l);
     if (kind == MOCOB200_JOINT_PIN || kind == MOCOB200_JOINT_PLANAR) {
@@ -85,9 +94,11 @@ __device__ inline void wk_body_kinematics(const WarpCtx& C, int b, const double*
         stv(ax + 3 * q0, zF);
         stv(lx + 3 * q0, mk(0, 0, 0));
         wrel = u[q0] * zF;
+        if (udot) wrd = udot[q0] * zF;
         if (kind == MOCOB200_JOINT_PLANAR) {
             oM = oF + q[q0 + 1] * xF + q[q0 + 2] * yF;
             vrel = u[q0 + 1] * xF + u[q0 + 2] * yF;
+            if (udot) vrd = udot[q0 + 1] * xF + udot[q0 + 2] * yF;
             stv(ax + 3 * (q0 + 1), mk(0, 0, 0));
             stv(lx + 3 * (q0 + 1), xF);
             stv(ax + 3 * (q0 + 2), mk(0, 0, 0));
@@ -99,21 +110,37 @@ __device__ inline void wk_body_kinematics(const WarpCtx& C, int b, const double*
         if (kind == MOCOB200_JOINT_SLIDER) {
             oM = oF + q[q0] * xF;
             vrel = u[q0] * xF;
+            if (udot) vrd = udot[q0] * xF;
             stv(ax + 3 * q0, mk(0, 0, 0));
             stv(lx + 3 * q0, xF);
         }
     }
     double* Rb = C.at(A.o_R) + 9 * b;
-    mmt3(RGM, bd + 12, Rb); // R_GB = R_GM R_BM^T
+    if (flags & 2) {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) Rb[k] = RGM[k];
+    } else mmt3(RGM, bd + 12, Rb); // R_GB = R_GM R_BM^T
     const V3 pB = oM - rmul(Rb, ld3(bd + 21));
     const V3 wB = wP + wrel;
-    const V3 vM = vP + cross(wP, oM - pP) + vrel;
+    const V3 r = oM - pP, sv = pB - oM;
+    const V3 vM = vP + cross(wP, r) + vrel;
     stv(C.at(A.o_p) + 3 * b, pB);
     stv(C.at(A.o_oM) + 3 * b, oM);
     stv(C.at(A.o_w) + 3 * b, wB);
-    stv(C.at(A.o_v) + 3 * b, vM + cross(wB, pB - oM));
+    stv(C.at(A.o_v) + 3 * b, vM + cross(wB, sv));
+    // accelerations: the joint axes are fixed in the parent, d(axis)/dt = wP x axis
+    const V3 al = alP + cross(wP, wrel) + wrd;
+    const V3 aM = aP + cross(alP, r) + cross(wP, cross(wP, r)) + 2.0 * cross(wP, vrel) + vrd;
+    stv(C.at(A.o_al) + 3 * b, al);
+    stv(C.at(A.o_ac) + 3 * b, aM + cross(al, sv) + cross(wB, cross(wB, sv)));
+}
+// non-recursive per-body quantities (all bodies in parallel): mass-centre offset and inertia about the origin, in ground
+__device__ inline void wk_body_inertia(const WarpCtx& C, int b) {
+    const DevTables& T = C.T;
+    const WarpAux& A = C.A;
+    const double* bd = T.dbl + T.o_body_d + b * MOCOB200_BODY_DSTRIDE;
+    const double* Rb = C.at(A.o_R) + 9 * b;
     stv(C.at(A.o_cg) + 3 * b, rmul(Rb, ld3(bd + 25)));
-    // inertia about the body origin, in ground: R I R^T (sym6: xx yy zz xy xz yz)
     const double* in = bd + 28;
     const double I[9] = {in[0], in[3], in[4], in[3], in[1], in[5], in[4], in[5], in[2]};
     double RI[9], RIRt[9];

@@ -32,8 +32,11 @@ __device__ inline void wk_gather_body(const WarpCtx& C, int b) {
         F = F + f;
         N = N + cross(ldv(C.at(A.o_cP) + 3 * c) - pB, f);
     }
-    stv(C.at(A.o_F) + 3 * b, F);
-    stv(C.at(A.o_N) + 3 * b, N);
+    // wrench (about the body origin) that the joint must supply = inertial - applied
+    const V3 cg = ldv(C.at(A.o_cg) + 3 * b), w = ldv(C.at(A.o_w) + 3 * b), al = ldv(C.at(A.o_al) + 3 * b), aB = ldv(C.at(A.o_ac) + 3 * b);
+    const double* Io = C.at(A.o_Io) + 6 * b;
+    stv(C.at(A.o_F) + 3 * b, m * (aB + cross(al, cg) + cross(w, cross(w, cg))) - F);
+    stv(C.at(A.o_N) + 3 * b, sym6mul(Io, al) + cross(cg, m * aB) + cross(w, sym6mul(Io, w)) - N);
 }
 // applied mobility force on coordinate k (one lane per coordinate)
 __device__ inline void wk_gather_coord(const WarpCtx& C, int k, const double* ctl) {
@@ -47,45 +50,6 @@ __device__ inline void wk_gather_coord(const WarpCtx& C, int k, const double* ct
         if (ai[0] == k) tau += T.dbl[T.o_cact_d + a * MOCOB200_CACT_DSTRIDE] * ctl[ai[1]];
     }
     C.at(A.o_tau)[k] = tau;
-}
-
-// ---- phase 4a: RNEA outward pass for body b: accelerations, then the wrench (about the body origin) that the
-// joint must supply = inertial - applied. udot == nullptr means zero accelerations (bias forces).
-__device__ inline void wk_rnea_forward(const WarpCtx& C, int b, const double* u, const double* udot) {
-    const DevTables& T = C.T;
-    const WarpAux& A = C.A;
-    const double* bd = T.dbl + T.o_body_d + b * MOCOB200_BODY_DSTRIDE;
-    const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
-    const int par = bi[0], q0 = bi[2], nd = bi[3];
-    V3 alP = mk(0, 0, 0), aP = mk(0, 0, 0), wP = mk(0, 0, 0), pP = mk(0, 0, 0);
-    if (par >= 0) {
-        alP = ldv(C.at(A.o_al) + 3 * par);
-        aP = ldv(C.at(A.o_ac) + 3 * par);
-        wP = ldv(C.at(A.o_w) + 3 * par);
-        pP = ldv(C.at(A.o_p) + 3 * par);
-    }
-    V3 wrel = mk(0, 0, 0), vrel = mk(0, 0, 0), wrd = mk(0, 0, 0), vrd = mk(0, 0, 0);
-    for (int k = 0; k < nd; ++k) {
-        const V3 a = ldv(C.at(A.o_a) + 3 * (q0 + k)), l = ldv(C.at(A.o_l) + 3 * (q0 + k));
-        wrel = wrel + u[q0 + k] * a;
-        vrel = vrel + u[q0 + k] * l;
-        if (udot) { wrd = wrd + udot[q0 + k] * a; vrd = vrd + udot[q0 + k] * l; }
-    }
-    const V3 oM = ldv(C.at(A.o_oM) + 3 * b), pB = ldv(C.at(A.o_p) + 3 * b), w = ldv(C.at(A.o_w) + 3 * b);
-    const V3 r = oM - pP, s = pB - oM;
-    // joint axes are fixed in the parent: d(axis)/dt = wP x axis
-    const V3 al = alP + cross(wP, wrel) + wrd;
-    const V3 aM = aP + cross(alP, r) + cross(wP, cross(wP, r)) + 2.0 * cross(wP, vrel) + vrd;
-    const V3 aB = aM + cross(al, s) + cross(w, cross(w, s));
-    stv(C.at(A.o_al) + 3 * b, al);
-    stv(C.at(A.o_ac) + 3 * b, aB);
-    const double m = bd[24];
-    const V3 cg = ldv(C.at(A.o_cg) + 3 * b);
-    const double* Io = C.at(A.o_Io) + 6 * b;
-    const V3 F = m * (aB + cross(al, cg) + cross(w, cross(w, cg))) - ldv(C.at(A.o_F) + 3 * b);
-    const V3 N = sym6mul(Io, al) + cross(cg, m * aB) + cross(w, sym6mul(Io, w)) - ldv(C.at(A.o_N) + 3 * b);
-    stv(C.at(A.o_F) + 3 * b, F);
-    stv(C.at(A.o_N) + 3 * b, N);
 }
 
 // ---- phase 4b: inward pass for body b (its children are final): pull the children's wrenches and composite
@@ -162,38 +126,72 @@ __device__ inline void wk_mass_entry(const WarpCtx& C, int i, int j, int nq) {
     C.at(A.o_M)[j * nq + i] = mij;
 }
 
-// ---- phase 4d: solve M x = rhs by LDL^T in shared memory (whole warp). M is overwritten. ---------------------
+// ---- phase 4d: solve M x = rhs by LDL^T (whole warp). Lane i keeps row i of M in registers; the right-looking
+// elimination broadcasts column entries with shuffles (M is symmetric: A_jk sits in register j of lane k).
+// The unit-lower factor is written back to shared memory for the transposed (backward) substitution.
+#define MOCOB200_LDLT_MAX 16
 __device__ inline void wk_ldlt_solve(const WarpCtx& C, int n, const double* rhs, double* x) {
     double* M = C.at(C.A.o_M);
     const int lane = C.lane;
-    for (int j = 0; j < n; ++j) {
+    const unsigned full = 0xffffffffu;
+    if (n > MOCOB200_LDLT_MAX) { // generic fallback for wide models: column-by-column in shared memory
+        for (int j = 0; j < n; ++j) {
+            if (lane == 0) {
+                double d = M[j * n + j];
+                for (int k = 0; k < j; ++k) d -= M[j * n + k] * M[j * n + k] * M[k * n + k];
+                M[j * n + j] = d;
+            }
+            __syncwarp();
+            const double dj = M[j * n + j];
+            for (int i = j + 1 + lane; i < n; i += 32) {
+                double v = M[i * n + j];
+                for (int k = 0; k < j; ++k) v -= M[i * n + k] * M[j * n + k] * M[k * n + k];
+                M[i * n + j] = v / dj;
+            }
+            __syncwarp();
+        }
         if (lane == 0) {
-            double d = M[j * n + j];
-            for (int k = 0; k < j; ++k) d -= M[j * n + k] * M[j * n + k] * M[k * n + k];
-            M[j * n + j] = d;
+            for (int i = 0; i < n; ++i) { double v = rhs[i]; for (int k = 0; k < i; ++k) v -= M[i * n + k] * x[k]; x[i] = v; }
+            for (int i = 0; i < n; ++i) x[i] /= M[i * n + i];
+            for (int i = n - 1; i >= 0; --i) { double v = x[i]; for (int k = i + 1; k < n; ++k) v -= M[k * n + i] * x[k]; x[i] = v; }
         }
         __syncwarp();
-        const double dj = M[j * n + j];
-        for (int i = j + 1 + lane; i < n; i += 32) {
-            double v = M[i * n + j];
-            for (int k = 0; k < j; ++k) v -= M[i * n + k] * M[j * n + k] * M[k * n + k];
-            M[i * n + j] = v / dj;
-        }
-        __syncwarp();
+        return;
     }
-    if (lane == 0) {
-        for (int i = 0; i < n; ++i) { // L y = rhs
-            double v = rhs[i];
-            for (int k = 0; k < i; ++k) v -= M[i * n + k] * x[k];
-            x[i] = v;
-        }
-        for (int i = 0; i < n; ++i) x[i] /= M[i * n + i];
-        for (int i = n - 1; i >= 0; --i) { // L^T x = z
-            double v = x[i];
-            for (int k = i + 1; k < n; ++k) v -= M[k * n + i] * x[k];
-            x[i] = v;
+    double m[MOCOB200_LDLT_MAX];
+    const int row = lane < n ? lane : 0;
+#pragma unroll
+    for (int c = 0; c < MOCOB200_LDLT_MAX; ++c) m[c] = (c < n) ? M[row * n + c] : 0.0;
+    double y = lane < n ? rhs[row] : 0.0;
+#pragma unroll
+    for (int j = 0; j < MOCOB200_LDLT_MAX; ++j) {
+        if (j < n) { // uniform
+            const double dj = __shfl_sync(full, m[j], j);
+            const double l = m[j] / dj; // L_ij for lanes i > j
+            const double yj = __shfl_sync(full, y, j);
+#pragma unroll
+            for (int k = j + 1; k < MOCOB200_LDLT_MAX; ++k) {
+                if (k < n) {
+                    const double akj = __shfl_sync(full, m[j], k); // A_kj = A_jk (still un-normalised on lane k)
+                    if (lane > j) m[k] -= l * akj;
+                }
+            }
+            if (lane > j) { m[j] = l; y -= l * yj; } // forward substitution rides along
         }
     }
+    // lane i: m[0..i) = L_i*, m[i] = D_i, y = (L^-1 rhs)_i
+    double d = 1.0;
+#pragma unroll
+    for (int c = 0; c < MOCOB200_LDLT_MAX; ++c) {
+        if (c < n && lane < n) { if (c == lane) d = m[c]; else if (c < lane) M[lane * n + c] = m[c]; }
+    }
+    double xv = y / d;
+    __syncwarp();
+    for (int j = n - 1; j > 0; --j) { // L^T x = z: x_j is final, eliminate it from rows i < j
+        const double xj = __shfl_sync(full, xv, j);
+        if (lane < j) xv -= M[j * n + lane] * xj;
+    }
+    if (lane < n) x[lane] = xv;
     __syncwarp();
 }
 
@@ -231,9 +229,11 @@ __device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, dou
     }
     if (need_contacts) {
         for (int L = 0; L < A.nlevels; ++L) {
-            for (int b = A.level_start[L] + lane; b < A.level_start[L + 1]; b += 32) wk_body_kinematics(C, b, q, u);
+            for (int b = A.level_start[L] + lane; b < A.level_start[L + 1]; b += 32)
+                wk_body_kinematics(C, b, q, u, T.implicit ? der : nullptr);
             __syncwarp();
         }
+        for (int b = lane; b < nb; b += 32) wk_body_inertia(C, b);
         for (int k = lane; k < 3 * T.npp; k += 32) { ws[A.o_pf + k] = 0.0; ws[A.o_ppos + k] = 0.0; }
         __syncwarp();
         const int nent = (dyn ? T.nmus : 0) + T.ncontact;
@@ -257,11 +257,6 @@ __device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, dou
         for (int b = lane; b < nb; b += 32) wk_gather_body(C, b);
         for (int k = lane; k < nq; k += 32) wk_gather_coord(C, k, ctl);
         __syncwarp();
-        const double* udot = T.implicit ? der : nullptr;
-        for (int L = 0; L < A.nlevels; ++L) {
-            for (int b = A.level_start[L] + lane; b < A.level_start[L + 1]; b += 32) wk_rnea_forward(C, b, u, udot);
-            __syncwarp();
-        }
         for (int L = A.nlevels - 1; L >= 0; --L) {
             for (int b = A.level_start[L] + lane; b < A.level_start[L + 1]; b += 32) wk_inward(C, b, !T.implicit);
             __syncwarp();
@@ -321,24 +316,33 @@ __device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, dou
         case MOCOB200_GOAL_CONTACT_TRACKING: {
             const int proj = ip[0], ng = ip[1];
             const V3 pv = ld3(dp + 3);
-            const int* gp = ip + 2;
-            for (int k = 0; k < ng; ++k) {
-                const int ncon = gp[0];
-                if ((k & 31) == lane) {
-                    V3 fm = mk(0, 0, 0);
-                    for (int c = 0; c < ncon; ++c) {
-                        const V3 f = ldv(ws + A.o_cF + 3 * gp[1 + 2 * c]);
-                        fm = (gp[2 + 2 * c] == 0) ? fm + f : fm - f;
-                    }
-                    const int* rp = gp + 1 + 2 * ncon;
-                    const V3 fr = mk(ppoly_eval(T, rp[0], time), ppoly_eval(T, rp[1], time), ppoly_eval(T, rp[2], time));
-                    const V3 e3 = fm - fr;
-                    V3 e = e3;
-                    if (proj == 1) e = dot(e3, pv) * pv;
-                    else if (proj == 2) e = e3 - dot(e3, pv) * pv;
-                    val += dot(e, e);
+            // lane t < 3 ng evaluates reference component t % 3 of group t / 3 (one parallel spline pass)
+            int myref = -1, mygrp = -1;
+            {
+                const int* gp = ip + 2;
+                for (int k = 0; k < ng; ++k) {
+                    const int ncon = gp[0];
+                    if (lane / 3 == k) myref = gp[1 + 2 * ncon + lane % 3];
+                    if (lane == k) mygrp = (int)(gp - ip);
+                    gp += 1 + 2 * ncon + 3;
                 }
-                gp += 1 + 2 * ncon + 3;
+            }
+            const double r = myref >= 0 ? ppoly_eval(T, myref, time) : 0.0;
+            const int src = 3 * min(lane, max(ng - 1, 0));
+            const V3 fr = mk(__shfl_sync(0xffffffffu, r, src), __shfl_sync(0xffffffffu, r, src + 1), __shfl_sync(0xffffffffu, r, src + 2));
+            if (mygrp >= 0) {
+                const int* gp = ip + mygrp;
+                const int ncon = gp[0];
+                V3 fm = mk(0, 0, 0);
+                for (int c = 0; c < ncon; ++c) {
+                    const V3 f = ldv(ws + A.o_cF + 3 * gp[1 + 2 * c]);
+                    fm = (gp[2 + 2 * c] == 0) ? fm + f : fm - f;
+                }
+                const V3 e3 = fm - fr;
+                V3 e = e3;
+                if (proj == 1) e = dot(e3, pv) * pv;
+                else if (proj == 2) e = e3 - dot(e3, pv) * pv;
+                val += dot(e, e);
             }
         } break;
         default: break;

@@ -85,7 +85,10 @@ def test_fd_jacobian_pipeline_1e7(pkg, orc, name, scheme, h):
     gr, gro = ev.eval_grad_f(x), o.eval_grad_f(x)
     # FD error of the integrand blocks scales with the integrand values themselves (~ the objective)
     gerr = np.max(np.abs(gr - gro)) / max(1.0, np.abs(gro).max(), abs(o.eval_f(x)))
-    assert gerr <= 1e-7, gerr
+    # the endpoint functions are differenced w.r.t. their `integral` input with an ABSOLUTE step (CasADi does not scale
+    # h): for a huge integral I the difference (I+h)-(I-h) itself carries ulp(I)/h relative round-off on either side
+    imax = (x[1] - x[0]) * np.abs(Yo[:, o.n_dyn_out:]).mean(axis=0).max() if o.n_integrand else 0.0
+    assert gerr <= 1e-7 + 4 * 2.2e-16 * imax / h, gerr
 
 
 @pytest.mark.parametrize("name", FIXTURES)
