@@ -75,7 +75,12 @@ struct mocob200_handle {
     DevLayout DL{};
     FdSettings fd{};
     WarpAux WA{};
-    bool useWarp = true; // MOCOB200_KERNEL=thread selects the thread-per-evaluation articulated-body kernels
+    // point-function kernels: warp-per-evaluation (latency: few evaluations) or thread-per-evaluation articulated-body
+    // (throughput: enough evaluations to fill the machine with threads). MOCOB200_KERNEL=warp|thread forces one.
+    bool useWarp = true;
+    int kernelMode = 0; // 0 auto, 1 warp, 2 thread
+    long warpMaxEvals = 48000;
+    bool warpFor(long evals) const { return kernelMode == 1 || (kernelMode == 0 && evals <= warpMaxEvals); }
     std::vector<void*> owned;
     double *d_x = nullptr, *d_Y = nullptr, *d_J = nullptr, *d_I = nullptr, *d_G = nullptr, *d_E = nullptr;
     double *d_g = nullptr, *d_vals = nullptr, *d_grad = nullptr, *d_f = nullptr;
@@ -95,6 +100,8 @@ struct mocob200_handle {
         return false;
     }
 };
+
+extern "C" long mocob200_point_evals_per_jacobian(const mocob200_handle* h);
 
 namespace {
 
@@ -234,7 +241,7 @@ bool gatherBlocks(mocob200_handle* h, double* d_buf, size_t stride) {
 
 // stages shared by the pipelines; x must already be in d_x
 bool runNominal(mocob200_handle* h) {
-    if (h->useWarp) launch_wpoints_nominal(h->DT, h->WA, h->DL, h->d_x, h->d_Y, h->p0, h->p1 - h->p0, h->stream);
+    if (h->warpFor(h->p1 - h->p0)) launch_wpoints_nominal(h->DT, h->WA, h->DL, h->d_x, h->d_Y, h->p0, h->p1 - h->p0, h->stream);
     else launch_points_nominal(h->DT, h->DL, h->d_x, h->d_Y, h->p0, h->p1 - h->p0, h->stream);
     h->launches++;
     if (!gatherBlocks(h, h->d_Y, (size_t)h->L.n_out)) return false;
@@ -247,7 +254,7 @@ bool runNominal(mocob200_handle* h) {
 }
 bool runFd(mocob200_handle* h) {
     cudaEventRecord(h->ev[0], h->stream);
-    if (h->useWarp) h->launches += launch_wpoints_fd(h->DT, h->WA, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream);
+    if (h->warpFor(mocob200_point_evals_per_jacobian(h) / h->world)) h->launches += launch_wpoints_fd(h->DT, h->WA, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream);
     else { launch_points_fd(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream); h->launches++; }
     cudaEventRecord(h->ev[1], h->stream);
     if (!gatherBlocks(h, h->d_Y, (size_t)h->L.n_out)) return false;
@@ -375,9 +382,9 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     G.nnzcol = (const int*)own(devUpload(L.nnzcol));
     {
         const char* k = getenv("MOCOB200_KERNEL");
-        h->useWarp = !(k && std::string(k) == "thread");
+        h->kernelMode = (k && std::string(k) == "thread") ? 2 : (k && std::string(k) == "warp") ? 1 : 0;
         std::string e;
-        if (h->useWarp && !buildWarpAux(h, *T, e)) return fail(MOCOB200_ERR_UNSUPPORTED, "warp kernels: " + e);
+        if (!buildWarpAux(h, *T, e)) return fail(MOCOB200_ERR_UNSUPPORTED, "warp kernels: " + e);
     }
     // work buffers
     h->d_x = (double*)own(devAlloc<double>(L.n_var));

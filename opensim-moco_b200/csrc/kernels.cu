@@ -145,46 +145,80 @@ __global__ void k_integrals(DevLayout L, const double* __restrict__ x, const dou
 
 // ---------------------------------------------------------------------------------------------
 // endpoint functions of all goals + their FD blocks. One block; thread a < n_ein = direction, thread n_ein = nominal.
-__device__ inline void gather_endpoint_inputs(const DevTables& T, const DevLayout& L, const double* x, int g, const double* I, double* ein) {
+// does the endpoint function of goal g read endpoint input a?  (columns it does not read are exactly zero under any
+// finite-difference formula, so they are written without evaluating anything)
+__device__ inline bool endpoint_reads(const DevTables& T, const DevLayout& L, int g, int a) {
+    const int* gr = T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
+    const int* ip = T.idx + gr[4];
     const int half = 1 + L.ns + L.nc + L.nd;
-    const int last = L.n_grid - 1;
-    ein[0] = x[0];
-    ein[half] = x[1];
-    for (int k = 0; k < L.ns; ++k) { ein[1 + k] = x[L.off_states + k]; ein[half + 1 + k] = x[L.off_states + (size_t)last * L.ns + k]; }
-    for (int k = 0; k < L.nc; ++k) { ein[1 + L.ns + k] = x[L.off_controls + k]; ein[half + 1 + L.ns + k] = x[L.off_controls + (size_t)last * L.nc + k]; }
-    for (int k = 0; k < L.nd; ++k) { ein[1 + L.ns + L.nc + k] = x[L.off_derivs + k]; ein[half + 1 + L.ns + L.nc + k] = x[L.off_derivs + (size_t)last * L.nd + k]; }
-    ein[2 * half] = (L.goal_integrand[g] >= 0) ? I[L.goal_integrand[g]] : NAN; // integral is NaN without an integrand (:495)
+    const bool isIntegral = a == 2 * half;
+    const int side = a >= half ? 1 : 0;          // 0 = initial, 1 = final
+    const int k = isIntegral ? -1 : a - side * half; // 0 = time, 1.. = states, controls, derivatives
+    const bool isTime = k == 0;
+    const bool isQ = k >= 1 && k <= L.nq;
+    const bool isState = k >= 1 && k <= L.ns;
+    const bool isControl = k > L.ns && k <= L.ns + L.nc;
+    switch (gr[0]) {
+    case MOCOB200_GOAL_CONTROL: return isIntegral || (ip[1] && isQ);
+    case MOCOB200_GOAL_STATE_TRACKING:
+    case MOCOB200_GOAL_CONTROL_TRACKING:
+    case MOCOB200_GOAL_SUM_SQUARED_STATE:
+    case MOCOB200_GOAL_CONTACT_TRACKING: return isIntegral;
+    case MOCOB200_GOAL_FINAL_TIME: return isTime && side == 1;
+    case MOCOB200_GOAL_AVERAGE_SPEED: return isTime || isQ;
+    case MOCOB200_GOAL_PERIODICITY: return isState || isControl;
+    case MOCOB200_GOAL_INITIAL_ACTIVATION: return side == 0 && (isState || isControl);
+    default: return !isIntegral || L.goal_integrand[g] >= 0;
+    }
 }
 
+// one block per goal; thread a < n_ein = FD direction, thread n_ein = nominal evaluation.
 __global__ void k_endpoint(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ x, const double* __restrict__ I,
                            double* __restrict__ G, double* __restrict__ E, int withFd) {
-    extern __shared__ double sh_g0[]; // [n_eout_total]
+    extern __shared__ double sh[]; // [n_ein] nominal inputs, then [nout] nominal outputs
+    const int g = blockIdx.x;
     const int a = threadIdx.x;
-    if (a > L.n_ein) return;
-    double ein[2 * MOCOB200_MAX_IN + 8];
-    double v0[MOCOB200_MAX_EOUT], v1[MOCOB200_MAX_EOUT], Jc[MOCOB200_MAX_EOUT];
-    if (a == L.n_ein) {
-        for (int g = 0; g < T.ngoal; ++g) {
-            const int nout = T.idx[T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE + 2];
-            gather_endpoint_inputs(T, L, x, g, I, ein);
-            eval_endpoint(T, g, ein, L.ns, L.nc, L.nd, v0);
-            for (int o = 0; o < nout; ++o) { sh_g0[L.goal_eoff[g] + o] = v0[o]; G[L.goal_eoff[g] + o] = v0[o]; }
+    const int nout = T.idx[T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE + 2];
+    double* sh_in = sh;
+    double* sh_g0 = sh + L.n_ein;
+    {   // cooperative gather of [t0, x0, c0, d0, tf, xf, cf, df, integral]
+        const int half = 1 + L.ns + L.nc + L.nd, last = L.n_grid - 1;
+        for (int i = threadIdx.x; i < L.n_ein; i += blockDim.x) {
+            double v;
+            if (i == 2 * half) v = (L.goal_integrand[g] >= 0) ? I[L.goal_integrand[g]] : NAN; // NaN without an integrand (:495)
+            else {
+                const int side = i >= half ? 1 : 0, k = i - side * half, j = side ? last : 0;
+                if (k == 0) v = x[side];
+                else if (k <= L.ns) v = x[L.off_states + (size_t)j * L.ns + (k - 1)];
+                else if (k <= L.ns + L.nc) v = x[L.off_controls + (size_t)j * L.nc + (k - 1 - L.ns)];
+                else v = x[L.off_derivs + (size_t)j * L.nd + (k - 1 - L.ns - L.nc)];
+            }
+            sh_in[i] = v;
         }
     }
     __syncthreads();
-    if (!withFd || a == L.n_ein) return;
-    for (int g = 0; g < T.ngoal; ++g) {
-        const int nout = T.idx[T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE + 2];
-        gather_endpoint_inputs(T, L, x, g, I, ein);
-        const bool nanIntegral = (a == L.n_ein - 1) && L.goal_integrand[g] < 0;
-        if (nanIntegral) { // perturbing a NaN input: the reference's FD yields NaN - NaN; the block entry is structurally unused
-            for (int o = 0; o < nout; ++o) E[(size_t)(L.goal_eoff[g] + o) * L.n_ein + a] = 0.0;
-            continue;
-        }
-        fd_group([&](const double* xin, double* yout) { eval_endpoint(T, g, xin, L.ns, L.nc, L.nd, yout); }, fd, ein, a,
-                 sh_g0 + L.goal_eoff[g], 0, nout, v0, v1, Jc);
-        for (int o = 0; o < nout; ++o) E[(size_t)(L.goal_eoff[g] + o) * L.n_ein + a] = Jc[o];
+    double ein[2 * MOCOB200_MAX_IN + 8];
+    double v0[MOCOB200_MAX_EOUT], v1[MOCOB200_MAX_EOUT], Jc[MOCOB200_MAX_EOUT];
+    if (a == L.n_ein) {
+        for (int i = 0; i < L.n_ein; ++i) ein[i] = sh_in[i];
+        eval_endpoint(T, g, ein, L.ns, L.nc, L.nd, v0);
+        for (int o = 0; o < nout; ++o) { sh_g0[o] = v0[o]; G[L.goal_eoff[g] + o] = v0[o]; }
     }
+    __syncthreads();
+    if (!withFd || a >= L.n_ein) return;
+    const bool nanIntegral = (a == L.n_ein - 1) && L.goal_integrand[g] < 0; // structurally unused entry
+    if (nanIntegral || !endpoint_reads(T, L, g, a)) {
+        for (int o = 0; o < nout; ++o) {
+            double z = 0.0;
+            if (!nanIntegral && !isfinite(sh_g0[o])) z = NAN; // a non-finite nominal poisons every difference
+            E[(size_t)(L.goal_eoff[g] + o) * L.n_ein + a] = z;
+        }
+        return;
+    }
+    for (int i = 0; i < L.n_ein; ++i) ein[i] = sh_in[i];
+    fd_group([&](const double* xin, double* yout) { eval_endpoint(T, g, xin, L.ns, L.nc, L.nd, yout); }, fd, ein, a, sh_g0, 0, nout,
+             v0, v1, Jc);
+    for (int o = 0; o < nout; ++o) E[(size_t)(L.goal_eoff[g] + o) * L.n_ein + a] = Jc[o];
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -395,7 +429,7 @@ void launch_endpoint(const DevTables& T, const DevLayout& L, const FdSettings& f
                      double* d_E, bool withFd, cudaStream_t s) {
     if (L.n_eout_total <= 0) return;
     const int bs = ((L.n_ein + 1 + 31) / 32) * 32;
-    k_endpoint<<<1, bs, (L.n_eout_total + 1) * sizeof(double), s>>>(T, L, fd, d_x, d_I, d_G, d_E, withFd ? 1 : 0);
+    k_endpoint<<<T.ngoal, bs, (L.n_ein + MOCOB200_MAX_EOUT) * sizeof(double), s>>>(T, L, fd, d_x, d_I, d_G, d_E, withFd ? 1 : 0);
 }
 void launch_assemble_g(const DevLayout& L, const double* d_x, const double* d_Y, const double* d_G, double* d_g, cudaStream_t s) {
     if (L.n_con <= 0) return;
