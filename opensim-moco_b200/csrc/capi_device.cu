@@ -82,6 +82,7 @@ struct mocob200_handle {
     long warpMaxEvals = 48000;
     bool warpFor(long evals) const { return kernelMode == 1 || (kernelMode == 0 && evals <= warpMaxEvals); }
     std::vector<void*> owned;
+    double* d_cfg = nullptr; // per-point blobs of the nominal evaluation (warp kernels)
     double *d_x = nullptr, *d_Y = nullptr, *d_J = nullptr, *d_I = nullptr, *d_G = nullptr, *d_E = nullptr;
     double *d_g = nullptr, *d_vals = nullptr, *d_grad = nullptr, *d_f = nullptr;
     cudaStream_t stream = nullptr;
@@ -186,13 +187,20 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     int o = 0;
     auto take = [&](int n) { const int at = o; o += (n + 1) & ~1; return at; };
     A.o_in = take(L.n_in); A.o_out = take(L.n_out); A.o_out2 = take(L.n_out);
-    A.o_R = take(9 * nb); A.o_p = take(3 * nb); A.o_w = take(3 * nb); A.o_v = take(3 * nb); A.o_cg = take(3 * nb);
-    A.o_oM = take(3 * nb); A.o_Io = take(6 * nb); A.o_F = take(3 * nb); A.o_N = take(3 * nb); A.o_al = take(3 * nb);
-    A.o_ac = take(3 * nb); A.o_cm = take(nb); A.o_ch = take(3 * nb); A.o_cJ = take(6 * nb);
-    A.o_a = take(3 * nq); A.o_l = take(3 * nq); A.o_tau = take(nq); A.o_taub = take(nq); A.o_lin = take(3 * nq);
-    A.o_ang = take(3 * nq); A.o_M = take(nq * nq);
-    A.o_ppos = take(3 * npp); A.o_pf = take(3 * npp); A.o_dp = take(3 * A.nmpp);
+    // position-dependent block (saved/reloaded as one range)
+    A.blob_begin = o;
+    A.o_R = take(9 * nb); A.o_p = take(3 * nb); A.o_oM = take(3 * nb); A.o_a = take(3 * nq); A.o_l = take(3 * nq);
+    A.o_cg = take(3 * nb); A.o_Io = take(6 * nb); A.o_ppos = take(3 * npp); A.o_prel = take(3 * npp);
+    A.o_dpl = take(3 * A.nmpp); A.o_mact = take(T.nmus); A.o_M = take(nq * nq);
+    A.blob_pos_end = o;
+    // velocity-dependent block
+    A.o_w = take(3 * nb); A.o_v = take(3 * nb); A.o_al = take(3 * nb); A.o_ac = take(3 * nb);
     A.o_cF = take(3 * T.ncontact); A.o_cP = take(3 * T.ncontact);
+    A.blob_end = o;
+    // per-evaluation scratch
+    A.o_F = take(3 * nb); A.o_N = take(3 * nb); A.o_cm = take(nb); A.o_ch = take(3 * nb); A.o_cJ = take(6 * nb);
+    A.o_tau = take(nq); A.o_taub = take(nq); A.o_lin = take(3 * nq); A.o_ang = take(3 * nq);
+    A.o_pf = take(3 * npp); A.o_dp = take(3 * A.nmpp);
     A.ws_doubles = o;
     return warp_kernels_configure(A, err);
 }
@@ -241,7 +249,7 @@ bool gatherBlocks(mocob200_handle* h, double* d_buf, size_t stride) {
 
 // stages shared by the pipelines; x must already be in d_x
 bool runNominal(mocob200_handle* h) {
-    if (h->warpFor(h->p1 - h->p0)) launch_wpoints_nominal(h->DT, h->WA, h->DL, h->d_x, h->d_Y, h->p0, h->p1 - h->p0, h->stream);
+    if (h->warpFor(h->p1 - h->p0)) launch_wpoints_nominal(h->DT, h->WA, h->DL, h->d_x, h->d_Y, nullptr, h->p0, h->p1 - h->p0, h->stream);
     else launch_points_nominal(h->DT, h->DL, h->d_x, h->d_Y, h->p0, h->p1 - h->p0, h->stream);
     h->launches++;
     if (!gatherBlocks(h, h->d_Y, (size_t)h->L.n_out)) return false;
@@ -254,7 +262,7 @@ bool runNominal(mocob200_handle* h) {
 }
 bool runFd(mocob200_handle* h) {
     cudaEventRecord(h->ev[0], h->stream);
-    if (h->warpFor(mocob200_point_evals_per_jacobian(h) / h->world)) h->launches += launch_wpoints_fd(h->DT, h->WA, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream);
+    if (h->warpFor(mocob200_point_evals_per_jacobian(h) / h->world)) h->launches += launch_wpoints_fd(h->DT, h->WA, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_cfg, h->p0, h->p1 - h->p0, h->stream);
     else { launch_points_fd(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream); h->launches++; }
     cudaEventRecord(h->ev[1], h->stream);
     if (!gatherBlocks(h, h->d_Y, (size_t)h->L.n_out)) return false;
@@ -390,6 +398,7 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     h->d_x = (double*)own(devAlloc<double>(L.n_var));
     h->d_Y = (double*)own(devAlloc<double>((size_t)L.n_grid * L.n_out));
     h->d_J = (double*)own(devAlloc<double>((size_t)L.n_grid * L.n_out * L.n_in));
+    h->d_cfg = (double*)own(devAlloc<double>((size_t)L.n_grid * (h->WA.blob_end - h->WA.blob_begin) + 1));
     h->d_I = (double*)own(devAlloc<double>(3 * (size_t)L.n_integrand + 1));
     h->d_G = (double*)own(devAlloc<double>(G.n_eout_total + 1));
     h->d_E = (double*)own(devAlloc<double>((size_t)(G.n_eout_total + 1) * L.n_ein));

@@ -60,9 +60,9 @@ double measure_fp64_peak_tflops(int device);
 
 // warp-per-evaluation kernels (kernels_warp.cu)
 bool warp_kernels_configure(const WarpAux& A, std::string& err);
-void launch_wpoints_nominal(const DevTables& T, const WarpAux& A, const DevLayout& L, const double* d_x, double* d_Y, int p0, int np,
-                            cudaStream_t s);
+void launch_wpoints_nominal(const DevTables& T, const WarpAux& A, const DevLayout& L, const double* d_x, double* d_Y, double* d_cfg,
+                            int p0, int np, cudaStream_t s);
 int launch_wpoints_fd(const DevTables& T, const WarpAux& A, const DevLayout& L, const FdSettings& fd, const double* d_x, double* d_Y,
-                      double* d_J, int p0, int np, cudaStream_t s);
+                      double* d_J, double* d_cfg, int p0, int np, cudaStream_t s);
 
 } // namespace mocob200

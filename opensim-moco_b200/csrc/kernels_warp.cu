@@ -17,8 +17,31 @@ __device__ __forceinline__ void warp_gather_inputs(const DevLayout& L, const dou
     __syncwarp();
 }
 
-// nominal evaluation of every grid point in [p0, p0+np): Y[j][:]
-__global__ void k_wpoints_nominal(DevTables T, WarpAux A, DevLayout L, const double* __restrict__ x, double* __restrict__ Y, int p0, int np) {
+__device__ __forceinline__ void blob_save(const WarpAux& A, const double* ws, double* __restrict__ cfg, int j, int lane) {
+    const int n = A.blob_end - A.blob_begin;
+    double* dst = cfg + (size_t)j * n;
+    for (int i = lane; i < n; i += 32) dst[i] = ws[A.blob_begin + i];
+}
+__device__ __forceinline__ void blob_load(const WarpAux& A, double* ws, const double* __restrict__ cfg, int j, int lane, int reuse) {
+    const int n = A.blob_end - A.blob_begin;
+    const int m = (reuse == 2 ? A.blob_end : A.blob_pos_end) - A.blob_begin;
+    const double* src = cfg + (size_t)j * n;
+    for (int i = lane; i < m; i += 32) ws[A.blob_begin + i] = src[i];
+    __syncwarp();
+}
+// which part of the nominal evaluation survives a perturbation of input `dir`:
+// 0 = nothing (a coordinate), 1 = poses / path geometry / mass-matrix factor (a speed, or an acceleration variable in
+// implicit mode), 2 = velocities and contact forces as well (time, auxiliary states, controls, auxiliary derivatives)
+__device__ __forceinline__ int reuse_level(const DevLayout& L, int dir) {
+    if (dir >= 1 && dir <= L.nq) return 0;
+    if (dir > L.nq && dir <= 2 * L.nq) return 1;
+    if (L.implicit && dir >= 1 + L.ns + L.nc && dir < 1 + L.ns + L.nc + L.nq) return 1;
+    return 2;
+}
+
+// nominal evaluation of every grid point in [p0, p0+np): Y[j][:] (+ the blob of each point when cfg != nullptr)
+__global__ void k_wpoints_nominal(DevTables T, WarpAux A, DevLayout L, const double* __restrict__ x, double* __restrict__ Y,
+                                  double* __restrict__ cfg, int p0, int np) {
     extern __shared__ double smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int item = blockIdx.x * (blockDim.x >> 5) + warp;
@@ -26,27 +49,35 @@ __global__ void k_wpoints_nominal(DevTables T, WarpAux A, DevLayout L, const dou
     double* ws = smem + (size_t)warp * A.ws_doubles;
     const int j = p0 + item;
     warp_gather_inputs(L, x, j, ws + A.o_in, lane);
-    warp_eval_point(T, A, ws, 0xffffffffu);
+    warp_eval_point(T, A, ws, 0xffffffffu, 0);
     for (int o = lane; o < L.n_out; o += 32) Y[(size_t)j * L.n_out + o] = ws[A.o_out + o];
+    if (cfg) blob_save(A, ws, cfg, j, lane);
 }
 
-// one-sided differences: item = point * (n_in + 1) + (dir + 1); dir = -1 is the nominal evaluation.
-// Writes Y (nominal) and the RAW perturbed outputs into J[j][o][dir]; k_fd1_finalize turns them into differences.
+// one-sided differences, two launches:
+//   phase 0: item = point * (1 + nq) + k; k = 0 is the nominal evaluation (writes Y and the blob), k >= 1 perturbs
+//            coordinate k (a full evaluation);
+//   phase 1: item = point * (n_in - nq) + t; t = 0 perturbs time, t >= 1 perturbs input nq + t; these reload the blob.
+// Perturbed evaluations write their RAW outputs into J[j][o][dir]; k_fd1_finalize turns them into differences.
 __global__ void k_wpoints_fd1(DevTables T, WarpAux A, DevLayout L, FdSettings fd, const double* __restrict__ x, double* __restrict__ Y,
-                              double* __restrict__ J, int p0, int np) {
+                              double* __restrict__ J, double* __restrict__ cfg, int p0, int np, int phase) {
     extern __shared__ double smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long item = (long)blockIdx.x * (blockDim.x >> 5) + warp;
-    const int per = L.n_in + 1;
+    const int per = phase == 0 ? 1 + L.nq : L.n_in - L.nq;
     if (item >= (long)np * per) return;
     double* ws = smem + (size_t)warp * A.ws_doubles;
-    const int j = p0 + (int)(item / per), dir = (int)(item % per) - 1;
+    const int j = p0 + (int)(item / per), t = (int)(item % per);
+    const int dir = phase == 0 ? (t == 0 ? -1 : t) : (t == 0 ? 0 : L.nq + t);
+    const int reuse = dir < 0 ? 0 : reuse_level(L, dir);
     warp_gather_inputs(L, x, j, ws + A.o_in, lane);
     if (dir >= 0 && lane == 0) ws[A.o_in + dir] += (fd.scheme == MOCOB200_FD_FORWARD) ? fd.h : -fd.h;
+    if (reuse) blob_load(A, ws, cfg, j, lane, reuse);
     __syncwarp();
-    warp_eval_point(T, A, ws, 0xffffffffu);
+    warp_eval_point(T, A, ws, 0xffffffffu, reuse);
     if (dir < 0) {
         for (int o = lane; o < L.n_out; o += 32) Y[(size_t)j * L.n_out + o] = ws[A.o_out + o];
+        blob_save(A, ws, cfg, j, lane);
     } else {
         double* Jp = J + (size_t)j * L.n_out * L.n_in;
         for (int o = lane; o < L.n_out; o += 32) Jp[(size_t)o * L.n_in + dir] = ws[A.o_out + o];
@@ -63,9 +94,10 @@ __global__ void k_fd1_finalize(DevLayout L, FdSettings fd, const double* __restr
     J[base + t] = (fd.scheme == MOCOB200_FD_FORWARD) ? (yp - y0) / fd.h : (y0 - yp) / fd.h;
 }
 
-// central differences with CasADi's step refinement; item = (point, dir, callback group). Needs Y (nominal).
+// central differences with CasADi's step refinement; item = (point, dir, callback group). Needs Y and the blobs of
+// the nominal evaluation.
 __global__ void k_wpoints_central(DevTables T, WarpAux A, DevLayout L, FdSettings fd, const double* __restrict__ x,
-                                  const double* __restrict__ Y, double* __restrict__ J, int p0, int np) {
+                                  const double* __restrict__ Y, double* __restrict__ J, const double* __restrict__ cfg, int p0, int np) {
     extern __shared__ double smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long item = (long)blockIdx.x * (blockDim.x >> 5) + warp;
@@ -80,7 +112,9 @@ __global__ void k_wpoints_central(DevTables T, WarpAux A, DevLayout L, FdSetting
     const int hi = gidx == 0 ? L.n_dyn_out : lo + 1;
     if (hi == lo) return;
     const unsigned mask = 1u << gidx;
+    const int reuse = reuse_level(L, dir);
     warp_gather_inputs(L, x, j, ws + A.o_in, lane);
+    if (reuse) blob_load(A, ws, cfg, j, lane, reuse);
     const double x0 = ws[A.o_in + dir];
     const double* y0 = Y + (size_t)j * L.n_out;
     double* yb = ws + A.o_out2;
@@ -90,11 +124,11 @@ __global__ void k_wpoints_central(DevTables T, WarpAux A, DevLayout L, FdSetting
     for (int iter = 0;; ++iter) {
         if (lane == 0) ws[A.o_in + dir] = x0 - h;
         __syncwarp();
-        warp_eval_point(T, A, ws, mask);
+        warp_eval_point(T, A, ws, mask, reuse);
         for (int o = lo + lane; o < hi; o += 32) yb[o] = yf[o];
         if (lane == 0) ws[A.o_in + dir] = x0 + h;
         __syncwarp();
-        warp_eval_point(T, A, ws, mask);
+        warp_eval_point(T, A, ws, mask, reuse);
         double u = 0;
         bool bad = false;
         for (int o = lo + lane; o < hi; o += 32) {
@@ -139,25 +173,26 @@ bool warp_kernels_configure(const WarpAux& A, std::string& err) {
     return true;
 }
 
-void launch_wpoints_nominal(const DevTables& T, const WarpAux& A, const DevLayout& L, const double* d_x, double* d_Y, int p0, int np,
-                            cudaStream_t s) {
+void launch_wpoints_nominal(const DevTables& T, const WarpAux& A, const DevLayout& L, const double* d_x, double* d_Y, double* d_cfg,
+                            int p0, int np, cudaStream_t s) {
     if (np <= 0) return;
-    k_wpoints_nominal<<<(np + g_wpb - 1) / g_wpb, g_wpb * 32, warpSmemBytes(A), s>>>(T, A, L, d_x, d_Y, p0, np);
+    k_wpoints_nominal<<<(np + g_wpb - 1) / g_wpb, g_wpb * 32, warpSmemBytes(A), s>>>(T, A, L, d_x, d_Y, d_cfg, p0, np);
 }
 // returns the number of kernels launched
 int launch_wpoints_fd(const DevTables& T, const WarpAux& A, const DevLayout& L, const FdSettings& fd, const double* d_x, double* d_Y,
-                      double* d_J, int p0, int np, cudaStream_t s) {
+                      double* d_J, double* d_cfg, int p0, int np, cudaStream_t s) {
     if (np <= 0) return 0;
     if (fd.scheme != MOCOB200_FD_CENTRAL) {
-        const long items = (long)np * (L.n_in + 1);
-        k_wpoints_fd1<<<(unsigned)((items + g_wpb - 1) / g_wpb), g_wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, p0, np);
+        const long items0 = (long)np * (1 + L.nq), items1 = (long)np * (L.n_in - L.nq);
+        k_wpoints_fd1<<<(unsigned)((items0 + g_wpb - 1) / g_wpb), g_wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np, 0);
+        k_wpoints_fd1<<<(unsigned)((items1 + g_wpb - 1) / g_wpb), g_wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np, 1);
         const long n = (long)np * L.n_out * L.n_in;
         k_fd1_finalize<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(L, fd, d_Y, d_J, p0, np);
-        return 2;
+        return 3;
     }
-    launch_wpoints_nominal(T, A, L, d_x, d_Y, p0, np, s);
+    launch_wpoints_nominal(T, A, L, d_x, d_Y, d_cfg, p0, np, s);
     const long items = (long)np * L.n_in * (1 + L.n_integrand);
-    k_wpoints_central<<<(unsigned)((items + g_wpb - 1) / g_wpb), g_wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, p0, np);
+    k_wpoints_central<<<(unsigned)((items + g_wpb - 1) / g_wpb), g_wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
     return 2;
 }
 

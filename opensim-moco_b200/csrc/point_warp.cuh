@@ -33,8 +33,12 @@ struct WarpAux {
     const int* pair_j;
     // scratch layout, offsets in doubles
     int o_in, o_out, o_out2, o_R, o_p, o_w, o_v, o_cg, o_oM, o_Io, o_F, o_N, o_al, o_ac, o_cm, o_ch, o_cJ, o_a, o_l, o_tau,
-        o_taub, o_lin, o_ang, o_M, o_ppos, o_pf, o_dp, o_cF, o_cP;
+        o_taub, o_lin, o_ang, o_M, o_ppos, o_prel, o_pf, o_dp, o_dpl, o_mact, o_cF, o_cP;
     int ws_doubles;
+    // The position-dependent part of the scratch [blob_begin, blob_pos_end) and the velocity-dependent part
+    // [blob_pos_end, blob_end) of the NOMINAL evaluation are saved per grid point ("blob") and reloaded by the
+    // evaluations of FD directions that leave q (or q and u) untouched.
+    int blob_begin, blob_pos_end, blob_end;
 };
 
 __device__ __forceinline__ V3 ldv(const double* p) { return mk(p[0], p[1], p[2]); }
@@ -48,10 +52,8 @@ struct WarpCtx {
     __device__ double* at(int off) const { return ws + off; }
 };
 
-// ---- phase 1: position + velocity kinematics of body b (one lane) -----------------------------------------------
-// Also propagates the spatial acceleration (velocity-product terms, plus the joint accelerations udot when given):
-// it needs no forces, so the recursive part of the Newton-Euler outward pass rides along here.
-__device__ inline void wk_body_kinematics(const WarpCtx& C, int b, const double* q, const double* u, const double* udot) {
+// ---- phase 1a: pose of body b (one lane): R_GB, origin, joint point oM, joint axes (angular a, linear l acting at oM)
+__device__ inline void wk_body_pose(const WarpCtx& C, int b, const double* q) {
     const DevTables& T = C.T;
     const WarpAux& A = C.A;
     const double* bd = T.dbl + T.o_body_d + b * MOCOB200_BODY_DSTRIDE;
@@ -59,19 +61,14 @@ __device__ inline void wk_body_kinematics(const WarpCtx& C, int b, const double*
     const int par = bi[0], kind = bi[1], q0 = bi[2];
     const int flags = A.body_flags[b];
     double RGF[9];
-    V3 oF, wP = mk(0, 0, 0), vP = mk(0, 0, 0), pP = mk(0, 0, 0), alP = mk(0, 0, 0), aP = mk(0, 0, 0);
+    V3 oF;
     if (par >= 0) {
         const double* Rp = C.at(A.o_R) + 9 * par;
         if (flags & 1) {
 #pragma unroll
             for (int k = 0; k < 9; ++k) RGF[k] = Rp[k];
         } else mm3(Rp, bd, RGF);
-        pP = ldv(C.at(A.o_p) + 3 * par);
-        oF = pP + rmul(Rp, ld3(bd + 9));
-        wP = ldv(C.at(A.o_w) + 3 * par);
-        vP = ldv(C.at(A.o_v) + 3 * par);
-        alP = ldv(C.at(A.o_al) + 3 * par);
-        aP = ldv(C.at(A.o_ac) + 3 * par);
+        oF = ldv(C.at(A.o_p) + 3 * par) + rmul(Rp, ld3(bd + 9));
     } else {
 #pragma unroll
         for (int k = 0; k < 9; ++k) RGF[k] = bd[k];
@@ -79,7 +76,7 @@ __device__ inline void wk_body_kinematics(const WarpCtx& C, int b, const double*
     }
     const V3 xF = mk(RGF[0], RGF[3], RGF[6]), yF = mk(RGF[1], RGF[4], RGF[7]), zF = mk(RGF[2], RGF[5], RGF[8]);
     double RGM[9];
-    V3 oM = oF, wrel = mk(0, 0, 0), vrel = mk(0, 0, 0), wrd = mk(0, 0, 0), vrd = mk(0, 0, 0);
+    V3 oM = oF;
     double* ax = C.at(A.o_a);
     double* lx = C.at(A.o_l);
     if (kind == MOCOB200_JOINT_PIN || kind == MOCOB200_JOINT_PLANAR) {
@@ -93,12 +90,8 @@ __device__ inline void wk_body_kinematics(const WarpCtx& C, int b, const double*
         }
         stv(ax + 3 * q0, zF);
         stv(lx + 3 * q0, mk(0, 0, 0));
-        wrel = u[q0] * zF;
-        if (udot) wrd = udot[q0] * zF;
         if (kind == MOCOB200_JOINT_PLANAR) {
             oM = oF + q[q0 + 1] * xF + q[q0 + 2] * yF;
-            vrel = u[q0 + 1] * xF + u[q0 + 2] * yF;
-            if (udot) vrd = udot[q0 + 1] * xF + udot[q0 + 2] * yF;
             stv(ax + 3 * (q0 + 1), mk(0, 0, 0));
             stv(lx + 3 * (q0 + 1), xF);
             stv(ax + 3 * (q0 + 2), mk(0, 0, 0));
@@ -109,8 +102,6 @@ __device__ inline void wk_body_kinematics(const WarpCtx& C, int b, const double*
         for (int k = 0; k < 9; ++k) RGM[k] = RGF[k];
         if (kind == MOCOB200_JOINT_SLIDER) {
             oM = oF + q[q0] * xF;
-            vrel = u[q0] * xF;
-            if (udot) vrd = udot[q0] * xF;
             stv(ax + 3 * q0, mk(0, 0, 0));
             stv(lx + 3 * q0, xF);
         }
@@ -120,15 +111,49 @@ __device__ inline void wk_body_kinematics(const WarpCtx& C, int b, const double*
 #pragma unroll
         for (int k = 0; k < 9; ++k) Rb[k] = RGM[k];
     } else mmt3(RGM, bd + 12, Rb); // R_GB = R_GM R_BM^T
-    const V3 pB = oM - rmul(Rb, ld3(bd + 21));
+    stv(C.at(A.o_p) + 3 * b, oM - rmul(Rb, ld3(bd + 21)));
+    stv(C.at(A.o_oM) + 3 * b, oM);
+}
+// ---- phase 1b: velocity and spatial acceleration of body b from the stored pose (one lane). The acceleration holds
+// the velocity-product terms plus the joint accelerations udot when given; it needs no forces, so the recursive part
+// of the Newton-Euler outward pass rides along here. Used unchanged by the full and the pose-reusing evaluations.
+__device__ inline void wk_body_velocity(const WarpCtx& C, int b, const double* u, const double* udot) {
+    const DevTables& T = C.T;
+    const WarpAux& A = C.A;
+    const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
+    const int par = bi[0], kind = bi[1], q0 = bi[2];
+    V3 wP = mk(0, 0, 0), vP = mk(0, 0, 0), pP = mk(0, 0, 0), alP = mk(0, 0, 0), aP = mk(0, 0, 0);
+    if (par >= 0) {
+        pP = ldv(C.at(A.o_p) + 3 * par);
+        wP = ldv(C.at(A.o_w) + 3 * par);
+        vP = ldv(C.at(A.o_v) + 3 * par);
+        alP = ldv(C.at(A.o_al) + 3 * par);
+        aP = ldv(C.at(A.o_ac) + 3 * par);
+    }
+    V3 wrel = mk(0, 0, 0), vrel = mk(0, 0, 0), wrd = mk(0, 0, 0), vrd = mk(0, 0, 0);
+    const double* ax = C.at(A.o_a) + 3 * q0;
+    const double* lx = C.at(A.o_l) + 3 * q0;
+    if (kind == MOCOB200_JOINT_PIN || kind == MOCOB200_JOINT_PLANAR) {
+        const V3 zF = ldv(ax);
+        wrel = u[q0] * zF;
+        if (udot) wrd = udot[q0] * zF;
+        if (kind == MOCOB200_JOINT_PLANAR) {
+            const V3 xF = ldv(lx + 3), yF = ldv(lx + 6);
+            vrel = u[q0 + 1] * xF + u[q0 + 2] * yF;
+            if (udot) vrd = udot[q0 + 1] * xF + udot[q0 + 2] * yF;
+        }
+    } else if (kind == MOCOB200_JOINT_SLIDER) {
+        const V3 xF = ldv(lx);
+        vrel = u[q0] * xF;
+        if (udot) vrd = udot[q0] * xF;
+    }
+    const V3 oM = ldv(C.at(A.o_oM) + 3 * b), pB = ldv(C.at(A.o_p) + 3 * b);
     const V3 wB = wP + wrel;
     const V3 r = oM - pP, sv = pB - oM;
     const V3 vM = vP + cross(wP, r) + vrel;
-    stv(C.at(A.o_p) + 3 * b, pB);
-    stv(C.at(A.o_oM) + 3 * b, oM);
     stv(C.at(A.o_w) + 3 * b, wB);
     stv(C.at(A.o_v) + 3 * b, vM + cross(wB, sv));
-    // accelerations: the joint axes are fixed in the parent, d(axis)/dt = wP x axis
+    // the joint axes are fixed in the parent: d(axis)/dt = wP x axis
     const V3 al = alP + cross(wP, wrel) + wrd;
     const V3 aM = aP + cross(alP, r) + cross(wP, cross(wP, r)) + 2.0 * cross(wP, vrel) + vrd;
     stv(C.at(A.o_al) + 3 * b, al);
@@ -195,47 +220,71 @@ __device__ inline void wk_contact(const WarpCtx& C, int ci) {
     stv(C.at(A.o_cP) + 3 * ci, cp);
 }
 
-// ---- phase 2b: one muscle (one lane): path geometry, muscle model, per-point forces ------------------------------
-__device__ inline MuscleOut wk_muscle(const WarpCtx& C, int m, const double* q, const double* u, const double* z, const double* ctl,
-                                      const double* auxder, bool apply, bool wantStiffness) {
+// ---- phase 2b: path geometry of one muscle (one lane): active points, their offsets from the body origin (prel),
+// ground positions (ppos) and, for moving points, dP/dq in the body frame (dpl). Position-dependent only.
+// (GeometryPath.cpp:817-846; ConditionalPathPoint.cpp:160-169; MovingPathPoint.cpp:216-315)
+__device__ inline void wk_muscle_geometry(const WarpCtx& C, int m, const double* q) {
     const DevTables& T = C.T;
     const WarpAux& A = C.A;
     const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
-    const double* md = T.dbl + T.o_mus_d + m * MOCOB200_MUS_DSTRIDE;
-    const int first = mi[0], count = mi[1], flags = mi[5];
-    double* ppos = C.at(A.o_ppos);
-    double length = 0, speed = 0;
-    V3 prevP = mk(0, 0, 0), prevV = mk(0, 0, 0);
-    int na = 0;
+    const int first = mi[0], count = mi[1];
     unsigned active = 0; // bit k: point k of this muscle is on the current path
     for (int k = 0; k < count; ++k) {
         const int pp = first + k;
         const int* pi = T.idx + T.o_pp_i + pp * MOCOB200_PP_ISTRIDE;
         const double* pd = T.dbl + T.o_pp_d + pp * MOCOB200_PP_DSTRIDE;
         const int b = pi[0], kind = pi[1];
-        V3 loc = ld3(pd), vloc = mk(0, 0, 0), dp = mk(0, 0, 0);
-        int mc = -1;
+        V3 loc = ld3(pd);
         if (kind == MOCOB200_PP_CONDITIONAL) {
             const double val = q[pi[2]];
             if (!(val >= pd[3] - 1e-5 && val <= pd[4] + 1e-5)) continue;
         } else if (kind == MOCOB200_PP_MOVING) {
-            mc = pi[6];
-            const double qv = q[mc];
+            const double qv = q[pi[6]];
             const double qc = fmin(fmax(qv, pd[3]), pd[4]); // location clamps the coordinate, derivatives do not
             loc = mk(simm_spline(T, pi[3], qc, 0), simm_spline(T, pi[4], qc, 0), simm_spline(T, pi[5], qc, 0));
-            dp = mk(simm_spline(T, pi[3], qv, 1), simm_spline(T, pi[4], qv, 1), simm_spline(T, pi[5], qv, 1));
-            vloc = u[mc] * dp;
+            stv(C.at(A.o_dpl) + 3 * A.pp_mpp[pp], mk(simm_spline(T, pi[3], qv, 1), simm_spline(T, pi[4], qv, 1), simm_spline(T, pi[5], qv, 1)));
         }
-        V3 pG, vG;
+        V3 r = loc, pG = loc;
         if (b >= 0) {
-            const double* Rb = C.at(A.o_R) + 9 * b;
-            const V3 r = rmul(Rb, loc);
+            r = rmul(C.at(A.o_R) + 9 * b, loc);
             pG = ldv(C.at(A.o_p) + 3 * b) + r;
-            vG = ldv(C.at(A.o_v) + 3 * b) + cross(ldv(C.at(A.o_w) + 3 * b), r);
-            if (mc >= 0) { vG = vG + rmul(Rb, vloc); dp = rmul(Rb, dp); }
-        } else {
-            pG = loc;
-            vG = vloc;
+        }
+        stv(C.at(A.o_prel) + 3 * pp, r);
+        stv(C.at(A.o_ppos) + 3 * pp, pG);
+        active |= 1u << k;
+    }
+    C.at(A.o_mact)[m] = (double)active;
+}
+// ---- phase 2c: one muscle (one lane) from its stored geometry: point velocities, length, lengthening speed, muscle
+// model, per-point forces (GeometryPath.cpp:848-864, 1117-1145, 306-432; Point.cpp:130-140)
+__device__ inline MuscleOut wk_muscle_dynamics(const WarpCtx& C, int m, const double* u, const double* z, const double* ctl,
+                                               const double* auxder, bool apply, bool wantStiffness) {
+    const DevTables& T = C.T;
+    const WarpAux& A = C.A;
+    const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
+    const double* md = T.dbl + T.o_mus_d + m * MOCOB200_MUS_DSTRIDE;
+    const int first = mi[0], count = mi[1], flags = mi[5];
+    const unsigned active = (unsigned)C.at(A.o_mact)[m];
+    const double* ppos = C.at(A.o_ppos);
+    double length = 0, speed = 0;
+    V3 prevP = mk(0, 0, 0), prevV = mk(0, 0, 0);
+    int na = 0;
+    for (int k = 0; k < count; ++k) {
+        if (!((active >> k) & 1u)) continue;
+        const int pp = first + k;
+        const int* pi = T.idx + T.o_pp_i + pp * MOCOB200_PP_ISTRIDE;
+        const int b = pi[0];
+        const int mc = (pi[1] == MOCOB200_PP_MOVING) ? pi[6] : -1;
+        const V3 pG = ldv(ppos + 3 * pp);
+        V3 vG = mk(0, 0, 0);
+        if (b >= 0) vG = ldv(C.at(A.o_v) + 3 * b) + cross(ldv(C.at(A.o_w) + 3 * b), ldv(C.at(A.o_prel) + 3 * pp));
+        if (mc >= 0) {
+            const int j = A.pp_mpp[pp];
+            const V3 dpl = ldv(C.at(A.o_dpl) + 3 * j);
+            V3 dpg = dpl, vloc = u[mc] * dpl;
+            if (b >= 0) { const double* Rb = C.at(A.o_R) + 9 * b; vloc = rmul(Rb, vloc); dpg = rmul(Rb, dpl); }
+            vG = vG + vloc;
+            stv(C.at(A.o_dp) + 3 * j, dpg);
         }
         if (na > 0) {
             const V3 r = prevP - pG, dv = prevV - vG;
@@ -245,9 +294,6 @@ __device__ inline MuscleOut wk_muscle(const WarpCtx& C, int m, const double* q, 
         }
         prevP = pG;
         prevV = vG;
-        stv(ppos + 3 * pp, pG);
-        if (mc >= 0) stv(C.at(A.o_dp) + 3 * A.pp_mpp[pp], dp);
-        active |= 1u << k;
         ++na;
     }
     const double activation = (flags & MOCOB200_MUS_FLAG_IGNORE_ACTIVATION_DYNAMICS) ? ctl[mi[2]] : z[mi[3]];
@@ -255,8 +301,8 @@ __device__ inline MuscleOut wk_muscle(const WarpCtx& C, int m, const double* q, 
     const double ntfd = (mi[6] >= 0) ? auxder[mi[6]] : NAN;
     MuscleOut o = dgf_muscle(md, flags, length, speed, activation, ntf, ntfd, wantStiffness);
     if (apply) {
-        // net force of the path on the body at every active point (GeometryPath.cpp:306-432): +T dir at the start
-        // of a segment, -T dir at its end; segments between points of the same body carry no force
+        // net force of the path on the body at every active point: +T dir at the start of a segment, -T dir at its
+        // end; segments between points of the same body carry no force
         double* pf = C.at(A.o_pf);
         int prev = -1;
         for (int k = 0; k < count; ++k) {

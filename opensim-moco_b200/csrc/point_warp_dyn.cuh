@@ -126,11 +126,12 @@ __device__ inline void wk_mass_entry(const WarpCtx& C, int i, int j, int nq) {
     C.at(A.o_M)[j * nq + i] = mij;
 }
 
-// ---- phase 4d: solve M x = rhs by LDL^T (whole warp). Lane i keeps row i of M in registers; the right-looking
-// elimination broadcasts column entries with shuffles (M is symmetric: A_jk sits in register j of lane k).
-// The unit-lower factor is written back to shared memory for the transposed (backward) substitution.
+// ---- phase 4d: LDL^T of the mass matrix (whole warp). Lane i keeps row i of M in registers; the right-looking
+// elimination broadcasts column entries with shuffles (M is symmetric: A_jk sits in register j of lane k). The
+// factor (unit-lower L below the diagonal, D on it) is written back over M in shared memory; it depends on q only,
+// so evaluations of FD directions that leave q untouched reuse the nominal factor and only run wk_ldlt_solve.
 #define MOCOB200_LDLT_MAX 16
-__device__ inline void wk_ldlt_solve(const WarpCtx& C, int n, const double* rhs, double* x) {
+__device__ inline void wk_ldlt_factor(const WarpCtx& C, int n) {
     double* M = C.at(C.A.o_M);
     const int lane = C.lane;
     const unsigned full = 0xffffffffu;
@@ -150,6 +151,39 @@ __device__ inline void wk_ldlt_solve(const WarpCtx& C, int n, const double* rhs,
             }
             __syncwarp();
         }
+        return;
+    }
+    double m[MOCOB200_LDLT_MAX];
+    const int row = lane < n ? lane : 0;
+#pragma unroll
+    for (int c = 0; c < MOCOB200_LDLT_MAX; ++c) m[c] = (c < n) ? M[row * n + c] : 0.0;
+#pragma unroll
+    for (int j = 0; j < MOCOB200_LDLT_MAX; ++j) {
+        if (j < n) { // uniform
+            const double dj = __shfl_sync(full, m[j], j);
+            const double l = m[j] / dj; // L_ij for lanes i > j
+#pragma unroll
+            for (int k = j + 1; k < MOCOB200_LDLT_MAX; ++k) {
+                if (k < n) {
+                    const double akj = __shfl_sync(full, m[j], k); // A_kj = A_jk (still un-normalised on lane k)
+                    if (lane > j) m[k] -= l * akj;
+                }
+            }
+            if (lane > j) m[j] = l;
+        }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int c = 0; c < MOCOB200_LDLT_MAX; ++c)
+        if (c < n && lane < n && c <= lane) M[lane * n + c] = m[c];
+    __syncwarp();
+}
+// x = M^-1 rhs from the stored factor (whole warp): L y = rhs, z = y / D, L^T x = z.
+__device__ inline void wk_ldlt_solve(const WarpCtx& C, int n, const double* rhs, double* x) {
+    const double* M = C.at(C.A.o_M);
+    const int lane = C.lane;
+    const unsigned full = 0xffffffffu;
+    if (n > 32) { // one lane, plain substitution
         if (lane == 0) {
             for (int i = 0; i < n; ++i) { double v = rhs[i]; for (int k = 0; k < i; ++k) v -= M[i * n + k] * x[k]; x[i] = v; }
             for (int i = 0; i < n; ++i) x[i] /= M[i * n + i];
@@ -158,36 +192,14 @@ __device__ inline void wk_ldlt_solve(const WarpCtx& C, int n, const double* rhs,
         __syncwarp();
         return;
     }
-    double m[MOCOB200_LDLT_MAX];
     const int row = lane < n ? lane : 0;
-#pragma unroll
-    for (int c = 0; c < MOCOB200_LDLT_MAX; ++c) m[c] = (c < n) ? M[row * n + c] : 0.0;
     double y = lane < n ? rhs[row] : 0.0;
-#pragma unroll
-    for (int j = 0; j < MOCOB200_LDLT_MAX; ++j) {
-        if (j < n) { // uniform
-            const double dj = __shfl_sync(full, m[j], j);
-            const double l = m[j] / dj; // L_ij for lanes i > j
-            const double yj = __shfl_sync(full, y, j);
-#pragma unroll
-            for (int k = j + 1; k < MOCOB200_LDLT_MAX; ++k) {
-                if (k < n) {
-                    const double akj = __shfl_sync(full, m[j], k); // A_kj = A_jk (still un-normalised on lane k)
-                    if (lane > j) m[k] -= l * akj;
-                }
-            }
-            if (lane > j) { m[j] = l; y -= l * yj; } // forward substitution rides along
-        }
+    for (int j = 0; j < n - 1; ++j) { // y_j is final; eliminate it from rows i > j
+        const double yj = __shfl_sync(full, y, j);
+        if (lane > j && lane < n) y -= M[lane * n + j] * yj;
     }
-    // lane i: m[0..i) = L_i*, m[i] = D_i, y = (L^-1 rhs)_i
-    double d = 1.0;
-#pragma unroll
-    for (int c = 0; c < MOCOB200_LDLT_MAX; ++c) {
-        if (c < n && lane < n) { if (c == lane) d = m[c]; else if (c < lane) M[lane * n + c] = m[c]; }
-    }
-    double xv = y / d;
-    __syncwarp();
-    for (int j = n - 1; j > 0; --j) { // L^T x = z: x_j is final, eliminate it from rows i < j
+    double xv = y / M[row * n + row];
+    for (int j = n - 1; j > 0; --j) { // x_j is final; eliminate it from rows i < j
         const double xj = __shfl_sync(full, xv, j);
         if (lane < j) xv -= M[j * n + lane] * xj;
     }
@@ -203,7 +215,11 @@ __device__ __forceinline__ double warp_sum(double v) { // fixed butterfly order 
 
 // The fused point function, evaluated by one warp. Inputs at ws[o_in..], outputs to ws[o_out..] (only the groups
 // selected by mask are written): bit 0 = dynamics (udot|residual, zdot, aux residuals), bit 1+k = integrand k.
-__device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, double* ws, unsigned mask) {
+// reuse: 0 = compute everything; 1 = the position-dependent scratch (poses, path geometry, mass-matrix factor) is
+// already in place (same q as the evaluation that produced it); 2 = the velocity-dependent scratch as well (same q, u
+// and, in implicit mode, the same accelerations). The reused and the recomputed quantities come from the same device
+// functions, so a reusing evaluation is bit-identical to a full one.
+__device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, double* ws, unsigned mask, int reuse) {
     const WarpCtx C{T, A, ws, (int)(threadIdx.x & 31)};
     const int lane = C.lane;
     const int nq = T.nq, nz = T.nz, nc = T.nc, nb = T.nb;
@@ -228,22 +244,30 @@ __device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, dou
         }
     }
     if (need_contacts) {
-        for (int L = 0; L < A.nlevels; ++L) {
-            for (int b = A.level_start[L] + lane; b < A.level_start[L + 1]; b += 32)
-                wk_body_kinematics(C, b, q, u, T.implicit ? der : nullptr);
-            __syncwarp();
+        if (reuse < 2) {
+            const double* udot = T.implicit ? der : nullptr;
+            for (int L = 0; L < A.nlevels; ++L) {
+                for (int b = A.level_start[L] + lane; b < A.level_start[L + 1]; b += 32) {
+                    if (reuse == 0) wk_body_pose(C, b, q);
+                    wk_body_velocity(C, b, u, udot);
+                }
+                __syncwarp();
+            }
         }
-        for (int b = lane; b < nb; b += 32) wk_body_inertia(C, b);
-        for (int k = lane; k < 3 * T.npp; k += 32) { ws[A.o_pf + k] = 0.0; ws[A.o_ppos + k] = 0.0; }
+        if (reuse == 0) {
+            for (int b = lane; b < nb; b += 32) wk_body_inertia(C, b);
+            if (dyn) for (int m = lane; m < T.nmus; m += 32) wk_muscle_geometry(C, m, q);
+        }
+        for (int k = lane; k < 3 * T.npp; k += 32) ws[A.o_pf + k] = 0.0;
         __syncwarp();
-        const int nent = (dyn ? T.nmus : 0) + T.ncontact;
+        const int nent = (dyn ? T.nmus : 0) + (reuse < 2 ? T.ncontact : 0);
         for (int e = lane; e < nent; e += 32) {
-            if (e < T.ncontact) wk_contact(C, e);
+            if (e >= (dyn ? T.nmus : 0)) wk_contact(C, e - (dyn ? T.nmus : 0));
             else {
-                const int m = e - T.ncontact;
+                const int m = e;
                 const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
                 const double* md = T.dbl + T.o_mus_d + m * MOCOB200_MUS_DSTRIDE;
-                const MuscleOut mo = wk_muscle(C, m, q, u, z, ctl, auxder, true, false);
+                const MuscleOut mo = wk_muscle_dynamics(C, m, u, z, ctl, auxder, true, false);
                 double* zdot = out + nq;
                 double* auxres = zdot + nz;
                 if (mi[3] >= 0) zdot[mi[3]] = activation_dot(ctl[mi[2]], z[mi[3]], md[5], md[6]);
@@ -257,20 +281,23 @@ __device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, dou
         for (int b = lane; b < nb; b += 32) wk_gather_body(C, b);
         for (int k = lane; k < nq; k += 32) wk_gather_coord(C, k, ctl);
         __syncwarp();
+        const bool composite = !T.implicit && reuse == 0;
         for (int L = A.nlevels - 1; L >= 0; --L) {
-            for (int b = A.level_start[L] + lane; b < A.level_start[L + 1]; b += 32) wk_inward(C, b, !T.implicit);
+            for (int b = A.level_start[L] + lane; b < A.level_start[L + 1]; b += 32) wk_inward(C, b, composite);
             __syncwarp();
         }
         if (T.implicit) {
             for (int k = lane; k < nq; k += 32) out[k] = ws[A.o_tau + k] - ws[A.o_taub + k];
         } else {
-            for (int k = lane; k < nq * nq; k += 32) ws[A.o_M + k] = 0.0;
-            for (int i = lane; i < nq; i += 32) {
-                wk_dof_momentum(C, i);
-                ws[A.o_tau + i] -= ws[A.o_taub + i]; // right-hand side
+            if (composite) {
+                for (int k = lane; k < nq * nq; k += 32) ws[A.o_M + k] = 0.0;
+                for (int i = lane; i < nq; i += 32) wk_dof_momentum(C, i);
+                __syncwarp();
+                for (int e = lane; e < A.npairs; e += 32) wk_mass_entry(C, A.pair_i[e], A.pair_j[e], nq);
+                __syncwarp();
+                wk_ldlt_factor(C, nq);
             }
-            __syncwarp();
-            for (int e = lane; e < A.npairs; e += 32) wk_mass_entry(C, A.pair_i[e], A.pair_j[e], nq);
+            for (int i = lane; i < nq; i += 32) ws[A.o_tau + i] -= ws[A.o_taub + i]; // right-hand side
             __syncwarp();
             wk_ldlt_solve(C, nq, ws + A.o_tau, out);
         }

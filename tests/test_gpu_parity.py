@@ -109,6 +109,26 @@ def test_fd_jacobian_default_steps_noise_bound(pkg, orc, name, scheme):
     assert np.median(np.abs(J - Jo) / scale) < 1e-6
 
 
+def test_fd_structural_zeros_are_exact(pkg):
+    """Perturbing an input that an output does not depend on must give an exactly zero difference (the evaluations that
+    reuse the nominal poses / velocities are bit-identical to full ones): muscle excitations do not enter udot, and an
+    activation only enters its own muscle's activation dynamics."""
+    p = load(pkg, "gait2d_tracking", 6)
+    ev = pkg.Evaluator(p)
+    d = ev.dims
+    x = p.make_iterate(seed=21, spread=0.3)
+    for scheme in (FD_FORWARD, FD_CENTRAL):
+        ev.set_fd(scheme)
+        J = ev.eval_points(x, jacobian=True)
+        nq, nz = 10, 18
+        ctl0 = 1 + d.ns  # first control input; control 0 is lumbarAct, 1..18 the muscle excitations
+        assert np.all(J[:, :nq, ctl0 + 1:ctl0 + 19] == 0.0)
+        zrows = J[:, nq:nq + nz, 1 + 2 * nq:1 + 2 * nq + nz]  # d zdot_m / d a_n
+        off = ~np.eye(nz, dtype=bool)
+        assert np.all(zrows[:, off] == 0.0)
+        assert np.all(J[:, :nq + nz, 0] == 0.0)  # the dynamics do not depend on time
+
+
 def test_exact_linear_entries(pkg):
     """Entries that do not pass through a callback are exact: interpolation rows (+1, -1/2, -1/2) and d(defect)/dx."""
     p = load(pkg, "gait2d_tracking", 8)
