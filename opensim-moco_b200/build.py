@@ -31,6 +31,8 @@ def build(force=False, verbose=False):
         objs.append(o)
         if force or _newer(o, [s] + headers):
             cmd = [NVCC, "-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC", "-c", s, "-o", o]
+            if os.environ.get("MOCOB200_PROFILE_PHASES"):  # development stopwatch, never set by build()/the driver
+                cmd += ["-DMOCOB200_PROFILE_PHASES"]
             if src.endswith(".cu"):
                 cmd += ARCH + ["-Xptxas", "-v"] if verbose else ARCH
             if verbose:

@@ -86,6 +86,11 @@ struct mocob200_handle {
     double *d_x = nullptr, *d_Y = nullptr, *d_J = nullptr, *d_I = nullptr, *d_G = nullptr, *d_E = nullptr;
     double *d_g = nullptr, *d_vals = nullptr, *d_grad = nullptr, *d_f = nullptr;
     cudaStream_t stream = nullptr;
+    // side stream: the endpoint functions (which need only x and the integrals of the nominal point outputs) run
+    // beside the FD evaluations of the point functions
+    cudaStream_t stream2 = nullptr;
+    cudaEvent_t evY = nullptr, evE = nullptr;
+    double* d_I2 = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     long launches = 0;
     int p0 = 0, p1 = 0; // this rank's grid points
@@ -163,27 +168,50 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
             b = bodyI(b)[0];
         }
     }
-    auto up = [&](const std::vector<int>& v) {
-        const int* p = devUpload(v);
-        h->owned.push_back((void*)p);
-        return p;
-    };
+    // all topology arrays live in one int pool so that a block can stage them with one copy loop
+    std::vector<int> pool;
+    std::vector<size_t> at;
+    auto put = [&](const std::vector<int>& v) { at.push_back(pool.size()); pool.insert(pool.end(), v.begin(), v.end()); pool.push_back(0); };
+    put(levelStart); put(childStart); put(childList); put(bodyPpStart); put(bodyPpList); put(dofBody); put(bodyFlags);
+    put(ppMpp); put(mppPp); put(mppCoord); put(pairI); put(pairJ);
+    const int* base = devUpload(pool);
+    h->owned.push_back((void*)base);
     WarpAux& A = h->WA;
+    A.aux_base = base;
+    A.st_naux = (int)pool.size();
     A.nlevels = (int)levelStart.size() - 1;
-    A.level_start = up(levelStart);
-    A.child_start = up(childStart);
-    A.child_list = up(childList);
-    A.body_pp_start = up(bodyPpStart);
-    A.body_pp_list = up(bodyPpList);
-    A.dof_body = up(dofBody);
-    A.body_flags = up(bodyFlags);
-    A.pp_mpp = up(ppMpp);
-    A.mpp_pp = up(mppPp);
-    A.mpp_coord = up(mppCoord);
+    A.level_start = base + at[0];
+    A.child_start = base + at[1];
+    A.child_list = base + at[2];
+    A.body_pp_start = base + at[3];
+    A.body_pp_list = base + at[4];
+    A.dof_body = base + at[5];
+    A.body_flags = base + at[6];
+    A.pp_mpp = base + at[7];
+    A.mpp_pp = base + at[8];
+    A.mpp_coord = base + at[9];
     A.nmpp = (int)mppPp.size();
     A.npairs = (int)pairI.size();
-    A.pair_i = up(pairI);
-    A.pair_j = up(pairJ);
+    A.pair_i = base + at[10];
+    A.pair_j = base + at[11];
+    // staged part of the pools: everything below the bounds block (host-only), plus the goal payload
+    {
+        int goal0 = T.n_dbl;
+        for (int g = 0; g < T.ngoal; ++g) {
+            const int* gr = T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
+            if (gr[7] > 0 && gr[5] < goal0) goal0 = gr[5];
+        }
+        const bool tail = goal0 >= T.o_ppoly_data && T.o_bounds <= T.o_ppoly_data && T.o_spline_data <= T.o_bounds &&
+                          T.o_body_d <= T.o_bounds && T.o_pp_d <= T.o_bounds && T.o_mus_d <= T.o_bounds && T.o_contact_d <= T.o_bounds &&
+                          T.o_cact_d <= T.o_bounds && T.o_gravity <= T.o_bounds;
+        if (!tail) { err = "unexpected pool order (model | bounds | references | goal payload)"; return false; }
+        A.st_ndbl = T.o_bounds;
+        A.st_goal0 = goal0;
+        A.st_ngoal = T.n_dbl - goal0;
+        A.st_nint = T.n_int;
+        const int ints = A.st_nint + A.st_naux;
+        A.st_doubles = ((A.st_ndbl + A.st_ngoal + 1) & ~1) + ((ints + 3) / 4) * 2;
+    }
     int o = 0;
     auto take = [&](int n) { const int at = o; o += (n + 1) & ~1; return at; };
     A.o_in = take(L.n_in); A.o_out = take(L.n_out); A.o_out2 = take(L.n_out);
@@ -191,7 +219,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     A.blob_begin = o;
     A.o_R = take(9 * nb); A.o_p = take(3 * nb); A.o_oM = take(3 * nb); A.o_a = take(3 * nq); A.o_l = take(3 * nq);
     A.o_cg = take(3 * nb); A.o_Io = take(6 * nb); A.o_ppos = take(3 * npp); A.o_prel = take(3 * npp);
-    A.o_dpl = take(3 * A.nmpp); A.o_mact = take(T.nmus); A.o_M = take(nq * nq);
+    A.o_dpl = take(3 * A.nmpp); A.o_mloc = take(3 * A.nmpp); A.o_ref = take(T.nppoly); A.o_mact = take(T.nmus); A.o_M = take(nq * nq);
     A.blob_pos_end = o;
     // velocity-dependent block
     A.o_w = take(3 * nb); A.o_v = take(3 * nb); A.o_al = take(3 * nb); A.o_ac = take(3 * nb);
@@ -202,6 +230,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     A.o_tau = take(nq); A.o_taub = take(nq); A.o_lin = take(3 * nq); A.o_ang = take(3 * nq);
     A.o_pf = take(3 * npp); A.o_dp = take(3 * A.nmpp);
     A.ws_doubles = o;
+    { const char* e = getenv("MOCOB200_POISON_SCRATCH"); A.poison = (e && e[0] == '1') ? 1 : 0; }
     return warp_kernels_configure(A, err);
 }
 
@@ -262,9 +291,26 @@ bool runNominal(mocob200_handle* h) {
 }
 bool runFd(mocob200_handle* h) {
     cudaEventRecord(h->ev[0], h->stream);
-    if (h->warpFor(mocob200_point_evals_per_jacobian(h) / h->world)) h->launches += launch_wpoints_fd(h->DT, h->WA, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_cfg, h->p0, h->p1 - h->p0, h->stream);
-    else { launch_points_fd(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream); h->launches++; }
+    const bool overlap = h->world == 1; // single rank: Y is complete as soon as the nominal evaluations are
+    if (h->warpFor(mocob200_point_evals_per_jacobian(h) / h->world))
+        h->launches += launch_wpoints_fd(h->DT, h->WA, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_cfg, h->p0, h->p1 - h->p0, h->stream,
+                                         overlap ? h->evY : nullptr);
+    else {
+        launch_points_fd(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream);
+        h->launches++;
+        if (overlap) cudaEventRecord(h->evY, h->stream);
+    }
     cudaEventRecord(h->ev[1], h->stream);
+    if (overlap) {
+        cudaStreamWaitEvent(h->stream2, h->evY, 0);
+        launch_integrals(h->DL, h->d_x, h->d_Y, h->d_J, h->d_I2, false, h->stream2);
+        launch_endpoint(h->DT, h->DL, h->fd, h->d_x, h->d_I2, h->d_G, h->d_E, true, h->stream2);
+        cudaEventRecord(h->evE, h->stream2);
+        launch_integrals(h->DL, h->d_x, h->d_Y, h->d_J, h->d_I, true, h->stream);
+        cudaStreamWaitEvent(h->stream, h->evE, 0);
+        h->launches += 2 * (h->L.n_integrand > 0) + (h->DL.n_eout_total > 0);
+        return true;
+    }
     if (!gatherBlocks(h, h->d_Y, (size_t)h->L.n_out)) return false;
     if (!gatherBlocks(h, h->d_J, (size_t)h->L.n_out * h->L.n_in)) return false;
     if (h->rank == 0) {
@@ -307,6 +353,9 @@ void mocob200_destroy(mocob200_handle* h) {
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     for (void* p : h->owned) cudaFree(p);
     for (auto& e : h->ev) if (e) cudaEventDestroy(e);
+    if (h->evY) cudaEventDestroy(h->evY);
+    if (h->evE) cudaEventDestroy(h->evE);
+    if (h->stream2) cudaStreamDestroy(h->stream2);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -347,6 +396,8 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     std::vector<int> idx(T->idx, T->idx + T->n_int);
     D.dbl = (const double*)own(devUpload(dbl));
     D.idx = (const int*)own(devUpload(idx));
+    D.dblP = D.dbl;
+    D.dblG = D.dbl;
     D.nb = T->nb; D.nq = T->nq; D.nz = T->nz; D.nc = T->nc; D.nderiv_aux = T->nderiv_aux; D.nmus = T->nmus; D.npp = T->npp;
     D.nspline = T->nspline; D.ncontact = T->ncontact; D.ncact = T->ncact; D.ngoal = T->ngoal; D.nppoly = T->nppoly;
     D.o_body_d = T->o_body_d; D.o_gravity = T->o_gravity; D.o_pp_d = T->o_pp_d; D.o_mus_d = T->o_mus_d;
@@ -400,6 +451,7 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     h->d_J = (double*)own(devAlloc<double>((size_t)L.n_grid * L.n_out * L.n_in));
     h->d_cfg = (double*)own(devAlloc<double>((size_t)L.n_grid * (h->WA.blob_end - h->WA.blob_begin) + 1));
     h->d_I = (double*)own(devAlloc<double>(3 * (size_t)L.n_integrand + 1));
+    h->d_I2 = (double*)own(devAlloc<double>(3 * (size_t)L.n_integrand + 1));
     h->d_G = (double*)own(devAlloc<double>(G.n_eout_total + 1));
     h->d_E = (double*)own(devAlloc<double>((size_t)(G.n_eout_total + 1) * L.n_ein));
     h->d_g = (double*)own(devAlloc<double>(L.n_con));
@@ -410,7 +462,10 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
         if (!p) return fail(MOCOB200_ERR_CUDA, "device allocation failed");
     if (!h->ck(cudaGetLastError(), "upload")) return fail(MOCOB200_ERR_CUDA, "");
     if (!h->ck(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "stream")) return fail(MOCOB200_ERR_CUDA, "");
+    if (!h->ck(cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking), "stream")) return fail(MOCOB200_ERR_CUDA, "");
     for (auto& e : h->ev) cudaEventCreate(&e);
+    cudaEventCreateWithFlags(&h->evY, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&h->evE, cudaEventDisableTiming);
     defaultFd(h->fd, R->fd_scheme);
     // shard grid points evenly over ranks
     h->shard.resize(world + 1);

@@ -59,10 +59,11 @@ void launch_assemble_grad(const DevTables& T, const DevLayout& L, const double* 
 double measure_fp64_peak_tflops(int device);
 
 // warp-per-evaluation kernels (kernels_warp.cu)
-bool warp_kernels_configure(const WarpAux& A, std::string& err);
+bool warp_kernels_configure(WarpAux& A, std::string& err);
 void launch_wpoints_nominal(const DevTables& T, const WarpAux& A, const DevLayout& L, const double* d_x, double* d_Y, double* d_cfg,
                             int p0, int np, cudaStream_t s);
+// after_nominal (may be null) is recorded on s once Y (the nominal point outputs) is complete
 int launch_wpoints_fd(const DevTables& T, const WarpAux& A, const DevLayout& L, const FdSettings& fd, const double* d_x, double* d_Y,
-                      double* d_J, double* d_cfg, int p0, int np, cudaStream_t s);
+                      double* d_J, double* d_cfg, int p0, int np, cudaStream_t s, cudaEvent_t after_nominal);
 
 } // namespace mocob200

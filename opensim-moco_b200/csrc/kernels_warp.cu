@@ -17,6 +17,43 @@ __device__ __forceinline__ void warp_gather_inputs(const DevLayout& L, const dou
     __syncwarp();
 }
 
+// Block prologue: copy the model tables and the topology arrays into shared memory (coalesced, all threads), and
+// return table descriptors whose pointers address the staged copies. Every thread of the block must call this.
+__device__ __forceinline__ double* stage_tables(const DevTables& T, const WarpAux& A, double* smem, DevTables& Ts, WarpAux& As) {
+    double* sd = smem;
+    const int nd = A.st_ndbl, ng = A.st_ngoal;
+    int* si = (int*)(smem + ((nd + ng + 1) & ~1));
+    int* sa = si + A.st_nint;
+    const int tid = threadIdx.x, nt = blockDim.x;
+    {
+        const double2* src = (const double2*)T.dbl;
+        double2* dst = (double2*)sd;
+        for (int i = tid; i < nd / 2; i += nt) dst[i] = src[i];
+        if ((nd & 1) && tid == 0) sd[nd - 1] = T.dbl[nd - 1];
+    }
+    for (int i = tid; i < ng; i += nt) sd[nd + i] = T.dbl[A.st_goal0 + i];
+    for (int i = tid; i < A.st_nint; i += nt) si[i] = T.idx[i];
+    for (int i = tid; i < A.st_naux; i += nt) sa[i] = A.aux_base[i];
+    __syncthreads();
+    Ts = T;
+    Ts.dblP = T.dbl;
+    Ts.dbl = sd;
+    Ts.dblG = sd + nd - A.st_goal0;
+    Ts.idx = si;
+    As = A;
+#define MOCOB200_RESTAGE(f) As.f = sa + (A.f - A.aux_base)
+    MOCOB200_RESTAGE(level_start); MOCOB200_RESTAGE(child_start); MOCOB200_RESTAGE(child_list); MOCOB200_RESTAGE(body_pp_start);
+    MOCOB200_RESTAGE(body_pp_list); MOCOB200_RESTAGE(dof_body); MOCOB200_RESTAGE(body_flags); MOCOB200_RESTAGE(pp_mpp);
+    MOCOB200_RESTAGE(mpp_pp); MOCOB200_RESTAGE(mpp_coord); MOCOB200_RESTAGE(pair_i); MOCOB200_RESTAGE(pair_j);
+#undef MOCOB200_RESTAGE
+    return smem + A.st_doubles;
+}
+
+__device__ __forceinline__ void poison_scratch(const WarpAux& A, double* ws, int lane) {
+    if (!A.poison) return;
+    for (int i = lane; i < A.ws_doubles; i += 32) ws[i] = NAN;
+    __syncwarp();
+}
 __device__ __forceinline__ void blob_save(const WarpAux& A, const double* ws, double* __restrict__ cfg, int j, int lane) {
     const int n = A.blob_end - A.blob_begin;
     double* dst = cfg + (size_t)j * n;
@@ -40,16 +77,20 @@ __device__ __forceinline__ int reuse_level(const DevLayout& L, int dir) {
 }
 
 // nominal evaluation of every grid point in [p0, p0+np): Y[j][:] (+ the blob of each point when cfg != nullptr)
-__global__ void k_wpoints_nominal(DevTables T, WarpAux A, DevLayout L, const double* __restrict__ x, double* __restrict__ Y,
+__global__ void k_wpoints_nominal(DevTables Tg, WarpAux Ag, DevLayout L, const double* __restrict__ x, double* __restrict__ Y,
                                   double* __restrict__ cfg, int p0, int np) {
     extern __shared__ double smem[];
+    DevTables T;
+    WarpAux A;
+    double* scratch = stage_tables(Tg, Ag, smem, T, A);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int item = blockIdx.x * (blockDim.x >> 5) + warp;
     if (item >= np) return;
-    double* ws = smem + (size_t)warp * A.ws_doubles;
+    double* ws = scratch + (size_t)warp * A.ws_doubles;
     const int j = p0 + item;
+    poison_scratch(A, ws, lane);
     warp_gather_inputs(L, x, j, ws + A.o_in, lane);
-    warp_eval_point(T, A, ws, 0xffffffffu, 0);
+    warp_eval_point(T, A, ws, 0xffffffffu, 0, false);
     for (int o = lane; o < L.n_out; o += 32) Y[(size_t)j * L.n_out + o] = ws[A.o_out + o];
     if (cfg) blob_save(A, ws, cfg, j, lane);
 }
@@ -59,22 +100,26 @@ __global__ void k_wpoints_nominal(DevTables T, WarpAux A, DevLayout L, const dou
 //            coordinate k (a full evaluation);
 //   phase 1: item = point * (n_in - nq) + t; t = 0 perturbs time, t >= 1 perturbs input nq + t; these reload the blob.
 // Perturbed evaluations write their RAW outputs into J[j][o][dir]; k_fd1_finalize turns them into differences.
-__global__ void k_wpoints_fd1(DevTables T, WarpAux A, DevLayout L, FdSettings fd, const double* __restrict__ x, double* __restrict__ Y,
+__global__ void k_wpoints_fd1(DevTables Tg, WarpAux Ag, DevLayout L, FdSettings fd, const double* __restrict__ x, double* __restrict__ Y,
                               double* __restrict__ J, double* __restrict__ cfg, int p0, int np, int phase) {
     extern __shared__ double smem[];
+    DevTables T;
+    WarpAux A;
+    double* scratch = stage_tables(Tg, Ag, smem, T, A);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long item = (long)blockIdx.x * (blockDim.x >> 5) + warp;
     const int per = phase == 0 ? 1 + L.nq : L.n_in - L.nq;
     if (item >= (long)np * per) return;
-    double* ws = smem + (size_t)warp * A.ws_doubles;
+    double* ws = scratch + (size_t)warp * A.ws_doubles;
     const int j = p0 + (int)(item / per), t = (int)(item % per);
     const int dir = phase == 0 ? (t == 0 ? -1 : t) : (t == 0 ? 0 : L.nq + t);
     const int reuse = dir < 0 ? 0 : reuse_level(L, dir);
+    poison_scratch(A, ws, lane);
     warp_gather_inputs(L, x, j, ws + A.o_in, lane);
     if (dir >= 0 && lane == 0) ws[A.o_in + dir] += (fd.scheme == MOCOB200_FD_FORWARD) ? fd.h : -fd.h;
     if (reuse) blob_load(A, ws, cfg, j, lane, reuse);
     __syncwarp();
-    warp_eval_point(T, A, ws, 0xffffffffu, reuse);
+    warp_eval_point(T, A, ws, 0xffffffffu, reuse, dir == 0);
     if (dir < 0) {
         for (int o = lane; o < L.n_out; o += 32) Y[(size_t)j * L.n_out + o] = ws[A.o_out + o];
         blob_save(A, ws, cfg, j, lane);
@@ -96,15 +141,18 @@ __global__ void k_fd1_finalize(DevLayout L, FdSettings fd, const double* __restr
 
 // central differences with CasADi's step refinement; item = (point, dir, callback group). Needs Y and the blobs of
 // the nominal evaluation.
-__global__ void k_wpoints_central(DevTables T, WarpAux A, DevLayout L, FdSettings fd, const double* __restrict__ x,
+__global__ void k_wpoints_central(DevTables Tg, WarpAux Ag, DevLayout L, FdSettings fd, const double* __restrict__ x,
                                   const double* __restrict__ Y, double* __restrict__ J, const double* __restrict__ cfg, int p0, int np) {
     extern __shared__ double smem[];
+    DevTables T;
+    WarpAux A;
+    double* scratch = stage_tables(Tg, Ag, smem, T, A);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long item = (long)blockIdx.x * (blockDim.x >> 5) + warp;
     const int ngroups = 1 + L.n_integrand;
     const long per = (long)L.n_in * ngroups;
     if (item >= (long)np * per) return;
-    double* ws = smem + (size_t)warp * A.ws_doubles;
+    double* ws = scratch + (size_t)warp * A.ws_doubles;
     const int j = p0 + (int)(item / per);
     const int rem = (int)(item % per);
     const int dir = rem / ngroups, gidx = rem % ngroups;
@@ -113,6 +161,7 @@ __global__ void k_wpoints_central(DevTables T, WarpAux A, DevLayout L, FdSetting
     if (hi == lo) return;
     const unsigned mask = 1u << gidx;
     const int reuse = reuse_level(L, dir);
+    poison_scratch(A, ws, lane);
     warp_gather_inputs(L, x, j, ws + A.o_in, lane);
     if (reuse) blob_load(A, ws, cfg, j, lane, reuse);
     const double x0 = ws[A.o_in + dir];
@@ -124,11 +173,11 @@ __global__ void k_wpoints_central(DevTables T, WarpAux A, DevLayout L, FdSetting
     for (int iter = 0;; ++iter) {
         if (lane == 0) ws[A.o_in + dir] = x0 - h;
         __syncwarp();
-        warp_eval_point(T, A, ws, mask, reuse);
+        warp_eval_point(T, A, ws, mask, reuse, dir == 0);
         for (int o = lo + lane; o < hi; o += 32) yb[o] = yf[o];
         if (lane == 0) ws[A.o_in + dir] = x0 + h;
         __syncwarp();
-        warp_eval_point(T, A, ws, mask, reuse);
+        warp_eval_point(T, A, ws, mask, reuse, dir == 0);
         double u = 0;
         bool bad = false;
         for (int o = lo + lane; o < hi; o += 32) {
@@ -154,15 +203,19 @@ __global__ void k_wpoints_central(DevTables T, WarpAux A, DevLayout L, FdSetting
 }
 
 // ---------------------------------------------------------------------------------------------
-static int g_wpb = 4; // warps per block
-static size_t warpSmemBytes(const WarpAux& A) { return (size_t)g_wpb * A.ws_doubles * sizeof(double); }
+static size_t warpSmemBytes(const WarpAux& A) { return ((size_t)A.st_doubles + (size_t)A.wpb * A.ws_doubles) * sizeof(double); }
 
-bool warp_kernels_configure(const WarpAux& A, std::string& err) {
+bool warp_kernels_configure(WarpAux& A, std::string& err) {
     // choose the number of warps per block so that a block's scratch fits and several blocks share an SM
-    g_wpb = 4;
-    while (g_wpb > 1 && warpSmemBytes(A) > 96 * 1024) g_wpb >>= 1;
+    A.wpb = 4;
+    while (A.wpb > 1 && warpSmemBytes(A) > 96 * 1024) A.wpb >>= 1;
     const size_t bytes = warpSmemBytes(A);
     if (bytes > 227 * 1024) { err = "per-warp scratch exceeds shared memory"; return false; }
+    // the attribute is per function, not per handle: only ever raise it
+    static size_t g_maxBytes[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 8 && bytes <= g_maxBytes[dev]) return true;
     cudaError_t e;
     if ((e = cudaFuncSetAttribute(k_wpoints_nominal, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
         (e = cudaFuncSetAttribute(k_wpoints_fd1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
@@ -170,30 +223,39 @@ bool warp_kernels_configure(const WarpAux& A, std::string& err) {
         err = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e);
         return false;
     }
+    if (dev >= 0 && dev < 8) g_maxBytes[dev] = bytes;
     return true;
 }
 
 void launch_wpoints_nominal(const DevTables& T, const WarpAux& A, const DevLayout& L, const double* d_x, double* d_Y, double* d_cfg,
                             int p0, int np, cudaStream_t s) {
     if (np <= 0) return;
-    k_wpoints_nominal<<<(np + g_wpb - 1) / g_wpb, g_wpb * 32, warpSmemBytes(A), s>>>(T, A, L, d_x, d_Y, d_cfg, p0, np);
+    k_wpoints_nominal<<<(np + A.wpb - 1) / A.wpb, A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, d_x, d_Y, d_cfg, p0, np);
 }
 // returns the number of kernels launched
 int launch_wpoints_fd(const DevTables& T, const WarpAux& A, const DevLayout& L, const FdSettings& fd, const double* d_x, double* d_Y,
-                      double* d_J, double* d_cfg, int p0, int np, cudaStream_t s) {
-    if (np <= 0) return 0;
+                      double* d_J, double* d_cfg, int p0, int np, cudaStream_t s, cudaEvent_t after_nominal) {
+    if (np <= 0) { if (after_nominal) cudaEventRecord(after_nominal, s); return 0; }
     if (fd.scheme != MOCOB200_FD_CENTRAL) {
         const long items0 = (long)np * (1 + L.nq), items1 = (long)np * (L.n_in - L.nq);
-        k_wpoints_fd1<<<(unsigned)((items0 + g_wpb - 1) / g_wpb), g_wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np, 0);
-        k_wpoints_fd1<<<(unsigned)((items1 + g_wpb - 1) / g_wpb), g_wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np, 1);
+        k_wpoints_fd1<<<(unsigned)((items0 + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np, 0);
+        if (after_nominal) cudaEventRecord(after_nominal, s);
+        k_wpoints_fd1<<<(unsigned)((items1 + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np, 1);
         const long n = (long)np * L.n_out * L.n_in;
         k_fd1_finalize<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(L, fd, d_Y, d_J, p0, np);
         return 3;
     }
     launch_wpoints_nominal(T, A, L, d_x, d_Y, d_cfg, p0, np, s);
+    if (after_nominal) cudaEventRecord(after_nominal, s);
     const long items = (long)np * L.n_in * (1 + L.n_integrand);
-    k_wpoints_central<<<(unsigned)((items + g_wpb - 1) / g_wpb), g_wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
+    k_wpoints_central<<<(unsigned)((items + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
     return 2;
 }
 
 } // namespace mocob200
+
+#ifdef MOCOB200_PROFILE_PHASES
+extern "C" int mocob200_debug_phase_clocks(long long* out32) {
+    return cudaMemcpyFromSymbol(out32, mocob200::g_phase_clk, sizeof(long long) * 32) == cudaSuccess ? 0 : 3;
+}
+#endif

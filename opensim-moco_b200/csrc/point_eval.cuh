@@ -30,6 +30,10 @@ namespace mocob200 {
 struct DevTables { // mocob200_tables with device (or shared-memory) pool pointers
     const double* dbl;
     const int* idx;
+    // The warp kernels stage the model part of the pools in shared memory; the (large) tracking-reference data stay in
+    // global memory behind dblP, and the goal payload is addressed through dblG (same absolute offsets as in dbl).
+    const double* dblP;
+    const double* dblG;
     int nb, nq, nz, nc, nderiv_aux, nmus, npp, nspline, ncontact, ncact, ngoal, nppoly;
     int o_body_d, o_gravity, o_pp_d, o_mus_d, o_contact_d, o_cact_d, o_spline_data, o_ppoly_data;
     int o_body_i, o_pp_i, o_mus_i, o_contact_i, o_cact_i, o_spline_i, o_goal_i, o_ppoly_i;
@@ -100,7 +104,7 @@ __device__ inline double simm_spline(const DevTables& T, int id, double ax, int 
 __device__ inline double ppoly_eval(const DevTables& T, int id, double t) {
     const int* rec = T.idx + T.o_ppoly_i + id * MOCOB200_PPOLY_ISTRIDE;
     const int np = rec[1], order = rec[2];
-    const double* br = T.dbl + T.o_ppoly_data + rec[0];
+    const double* br = T.dblP + T.o_ppoly_data + rec[0];
     const double* co = br + np + 1;
     int k = 0;
     if (t >= br[np]) k = np - 1;
@@ -765,7 +769,7 @@ __device__ inline void eval_point(const DevTables& T, const double* in, double* 
         const int slot = gi++;
         if (!((mask >> (1 + slot)) & 1u)) continue;
         const int* ip = T.idx + gr[4];
-        const double* dp = T.dbl + gr[5];
+        const double* dp = T.dblG + gr[5];
         double val = 0;
         switch (gr[0]) {
         case MOCOB200_GOAL_CONTROL: {
@@ -828,7 +832,7 @@ __device__ inline void eval_point(const DevTables& T, const double* in, double* 
 __device__ inline void eval_endpoint(const DevTables& T, int g, const double* ein, int ns, int nc, int nd, double* vals) {
     const int* gr = T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
     const int* ip = T.idx + gr[4];
-    const double* dp = T.dbl + gr[5];
+    const double* dp = T.dblG + gr[5];
     const int half = 1 + ns + nc + nd;
     const double t0 = ein[0], tf = ein[half];
     const double* x0 = ein + 1;

@@ -33,8 +33,15 @@ struct WarpAux {
     const int* pair_j;
     // scratch layout, offsets in doubles
     int o_in, o_out, o_out2, o_R, o_p, o_w, o_v, o_cg, o_oM, o_Io, o_F, o_N, o_al, o_ac, o_cm, o_ch, o_cJ, o_a, o_l, o_tau,
-        o_taub, o_lin, o_ang, o_M, o_ppos, o_prel, o_pf, o_dp, o_dpl, o_mact, o_cF, o_cP;
+        o_taub, o_lin, o_ang, o_M, o_ppos, o_prel, o_pf, o_dp, o_dpl, o_mloc, o_ref, o_mact, o_cF, o_cP;
+    // shared-memory staging of the tables (per block): dbl[0, st_ndbl) (bodies, path points, muscles, contacts,
+    // splines), the goal payload dbl[st_goal0, st_goal0 + st_ngoal), the whole int pool, and the topology arrays above
+    // (one int pool starting at aux_base). st_doubles = size of the staged region in doubles.
+    int st_ndbl, st_goal0, st_ngoal, st_nint, st_naux, st_doubles;
+    const int* aux_base;
+    int poison; // development switch (MOCOB200_POISON_SCRATCH=1): every evaluation starts from NaN-filled scratch
     int ws_doubles;
+    int wpb; // warps (= evaluations in flight) per block, chosen at create from the scratch size
     // The position-dependent part of the scratch [blob_begin, blob_pos_end) and the velocity-dependent part
     // [blob_pos_end, blob_end) of the NOMINAL evaluation are saved per grid point ("blob") and reloaded by the
     // evaluations of FD directions that leave q (or q and u) untouched.
@@ -220,6 +227,21 @@ __device__ inline void wk_contact(const WarpCtx& C, int ci) {
     stv(C.at(A.o_cP) + 3 * ci, cp);
 }
 
+// ---- phase 0: SimmSpline evaluations of the moving path points, one per lane: t = 6 * (moving point) + c, c < 3 the
+// location components at the clamped coordinate, c >= 3 the derivative components at the unclamped coordinate
+// (MovingPathPoint.cpp:216-315: the location clamps the coordinate to the spline's range, the derivatives do not)
+__device__ inline void wk_moving_point_spline(const WarpCtx& C, int t, const double* q) {
+    const DevTables& T = C.T;
+    const WarpAux& A = C.A;
+    const int j = t / 6, c = t - 6 * j;
+    const int pp = A.mpp_pp[j];
+    const int* pi = T.idx + T.o_pp_i + pp * MOCOB200_PP_ISTRIDE;
+    const double* pd = T.dbl + T.o_pp_d + pp * MOCOB200_PP_DSTRIDE;
+    const double qv = q[pi[6]];
+    if (c < 3) C.at(A.o_mloc)[3 * j + c] = simm_spline(T, pi[3 + c], fmin(fmax(qv, pd[3]), pd[4]), 0);
+    else C.at(A.o_dpl)[3 * j + c - 3] = simm_spline(T, pi[c], qv, 1);
+}
+
 // ---- phase 2b: path geometry of one muscle (one lane): active points, their offsets from the body origin (prel),
 // ground positions (ppos) and, for moving points, dP/dq in the body frame (dpl). Position-dependent only.
 // (GeometryPath.cpp:817-846; ConditionalPathPoint.cpp:160-169; MovingPathPoint.cpp:216-315)
@@ -235,14 +257,13 @@ __device__ inline void wk_muscle_geometry(const WarpCtx& C, int m, const double*
         const double* pd = T.dbl + T.o_pp_d + pp * MOCOB200_PP_DSTRIDE;
         const int b = pi[0], kind = pi[1];
         V3 loc = ld3(pd);
+        bool on = true;
         if (kind == MOCOB200_PP_CONDITIONAL) {
             const double val = q[pi[2]];
-            if (!(val >= pd[3] - 1e-5 && val <= pd[4] + 1e-5)) continue;
+            // an inactive point still gets a (finite) position: the per-body gather multiplies it by a zero force
+            on = (val >= pd[3] - 1e-5 && val <= pd[4] + 1e-5);
         } else if (kind == MOCOB200_PP_MOVING) {
-            const double qv = q[pi[6]];
-            const double qc = fmin(fmax(qv, pd[3]), pd[4]); // location clamps the coordinate, derivatives do not
-            loc = mk(simm_spline(T, pi[3], qc, 0), simm_spline(T, pi[4], qc, 0), simm_spline(T, pi[5], qc, 0));
-            stv(C.at(A.o_dpl) + 3 * A.pp_mpp[pp], mk(simm_spline(T, pi[3], qv, 1), simm_spline(T, pi[4], qv, 1), simm_spline(T, pi[5], qv, 1)));
+            loc = ldv(C.at(A.o_mloc) + 3 * A.pp_mpp[pp]); // evaluated by wk_moving_point_splines
         }
         V3 r = loc, pG = loc;
         if (b >= 0) {
@@ -251,7 +272,7 @@ __device__ inline void wk_muscle_geometry(const WarpCtx& C, int m, const double*
         }
         stv(C.at(A.o_prel) + 3 * pp, r);
         stv(C.at(A.o_ppos) + 3 * pp, pG);
-        active |= 1u << k;
+        if (on) active |= 1u << k;
     }
     C.at(A.o_mact)[m] = (double)active;
 }

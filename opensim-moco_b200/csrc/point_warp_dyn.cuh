@@ -6,6 +6,15 @@ namespace mocob200 {
 
 __device__ __forceinline__ V3 sym6mul(const double* s, V3 v) { return symmul(s, v); }
 
+// Phase stopwatch for development builds (-DMOCOB200_PROFILE_PHASES): warp 0 of block 0 records clock64() at the
+// phase boundaries of its evaluation. Compiled out of the product.
+#ifdef MOCOB200_PROFILE_PHASES
+__device__ long long g_phase_clk[32];
+#define PHASE_MARK(k) do { __syncwarp(); if (blockIdx.x == 0 && threadIdx.x == 0) g_phase_clk[k] = clock64(); } while (0)
+#else
+#define PHASE_MARK(k) do { } while (0)
+#endif
+
 // ---- phase 3: applied wrench on body b about its origin (one lane per body), fixed summation order -------------
 __device__ inline void wk_gather_body(const WarpCtx& C, int b) {
     const DevTables& T = C.T;
@@ -126,57 +135,32 @@ __device__ inline void wk_mass_entry(const WarpCtx& C, int i, int j, int nq) {
     C.at(A.o_M)[j * nq + i] = mij;
 }
 
-// ---- phase 4d: LDL^T of the mass matrix (whole warp). Lane i keeps row i of M in registers; the right-looking
-// elimination broadcasts column entries with shuffles (M is symmetric: A_jk sits in register j of lane k). The
-// factor (unit-lower L below the diagonal, D on it) is written back over M in shared memory; it depends on q only,
-// so evaluations of FD directions that leave q untouched reuse the nominal factor and only run wk_ldlt_solve.
-#define MOCOB200_LDLT_MAX 16
+// ---- phase 4d: LDL^T of the mass matrix (whole warp), in place in shared memory. Right-looking: at step j the lanes
+// first normalise column j (keeping the un-normalised entries in row j of the unused upper triangle), then update the
+// trailing lower triangle, one (row, column) pair per lane. The factor (unit-lower L below the diagonal, D on it)
+// depends on q only, so evaluations of FD directions that leave q untouched reuse the nominal factor and only run
+// wk_ldlt_solve.
 __device__ inline void wk_ldlt_factor(const WarpCtx& C, int n) {
     double* M = C.at(C.A.o_M);
     const int lane = C.lane;
-    const unsigned full = 0xffffffffu;
-    if (n > MOCOB200_LDLT_MAX) { // generic fallback for wide models: column-by-column in shared memory
-        for (int j = 0; j < n; ++j) {
-            if (lane == 0) {
-                double d = M[j * n + j];
-                for (int k = 0; k < j; ++k) d -= M[j * n + k] * M[j * n + k] * M[k * n + k];
-                M[j * n + j] = d;
-            }
-            __syncwarp();
-            const double dj = M[j * n + j];
-            for (int i = j + 1 + lane; i < n; i += 32) {
-                double v = M[i * n + j];
-                for (int k = 0; k < j; ++k) v -= M[i * n + k] * M[j * n + k] * M[k * n + k];
-                M[i * n + j] = v / dj;
-            }
-            __syncwarp();
+    for (int j = 0; j < n - 1; ++j) {
+        const double dj = M[j * n + j];
+        for (int i = j + 1 + lane; i < n; i += 32) {
+            const double a = M[i * n + j];
+            M[j * n + i] = a;
+            M[i * n + j] = a / dj;
         }
-        return;
-    }
-    double m[MOCOB200_LDLT_MAX];
-    const int row = lane < n ? lane : 0;
-#pragma unroll
-    for (int c = 0; c < MOCOB200_LDLT_MAX; ++c) m[c] = (c < n) ? M[row * n + c] : 0.0;
-#pragma unroll
-    for (int j = 0; j < MOCOB200_LDLT_MAX; ++j) {
-        if (j < n) { // uniform
-            const double dj = __shfl_sync(full, m[j], j);
-            const double l = m[j] / dj; // L_ij for lanes i > j
-#pragma unroll
-            for (int k = j + 1; k < MOCOB200_LDLT_MAX; ++k) {
-                if (k < n) {
-                    const double akj = __shfl_sync(full, m[j], k); // A_kj = A_jk (still un-normalised on lane k)
-                    if (lane > j) m[k] -= l * akj;
-                }
+        __syncwarp();
+        const int m = n - 1 - j;
+        for (int p = lane; p < m * m; p += 32) {
+            const int r = p / m, c = p - r * m;
+            if (c <= r) {
+                const int i = j + 1 + r, k = j + 1 + c;
+                M[i * n + k] -= M[i * n + j] * M[j * n + k];
             }
-            if (lane > j) m[j] = l;
         }
+        __syncwarp();
     }
-    __syncwarp();
-#pragma unroll
-    for (int c = 0; c < MOCOB200_LDLT_MAX; ++c)
-        if (c < n && lane < n && c <= lane) M[lane * n + c] = m[c];
-    __syncwarp();
 }
 // x = M^-1 rhs from the stored factor (whole warp): L y = rhs, z = y / D, L^T x = z.
 __device__ inline void wk_ldlt_solve(const WarpCtx& C, int n, const double* rhs, double* x) {
@@ -219,7 +203,8 @@ __device__ __forceinline__ double warp_sum(double v) { // fixed butterfly order 
 // already in place (same q as the evaluation that produced it); 2 = the velocity-dependent scratch as well (same q, u
 // and, in implicit mode, the same accelerations). The reused and the recomputed quantities come from the same device
 // functions, so a reusing evaluation is bit-identical to a full one.
-__device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, double* ws, unsigned mask, int reuse) {
+// time_moved: the evaluation's time differs from the one whose tracking-reference values sit in the scratch.
+__device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, double* ws, unsigned mask, int reuse, bool time_moved) {
     const WarpCtx C{T, A, ws, (int)(threadIdx.x & 31)};
     const int lane = C.lane;
     const int nq = T.nq, nz = T.nz, nc = T.nc, nb = T.nb;
@@ -243,6 +228,14 @@ __device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, dou
             ++gi;
         }
     }
+    PHASE_MARK(0);
+    // lane-parallel table look-ups first: tracking references at this time, splines of the moving path points at this q
+    if ((mask >> 1) && (reuse == 0 || time_moved))
+        for (int r = lane; r < T.nppoly; r += 32) ws[A.o_ref + r] = ppoly_eval(T, r, time);
+    if (dyn && reuse == 0)
+        for (int t = lane; t < 6 * A.nmpp; t += 32) wk_moving_point_spline(C, t, q);
+    __syncwarp();
+    PHASE_MARK(11);
     if (need_contacts) {
         if (reuse < 2) {
             const double* udot = T.implicit ? der : nullptr;
@@ -254,10 +247,13 @@ __device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, dou
                 __syncwarp();
             }
         }
+        PHASE_MARK(1);
         if (reuse == 0) {
             for (int b = lane; b < nb; b += 32) wk_body_inertia(C, b);
+            PHASE_MARK(2);
             if (dyn) for (int m = lane; m < T.nmus; m += 32) wk_muscle_geometry(C, m, q);
         }
+        PHASE_MARK(3);
         for (int k = lane; k < 3 * T.npp; k += 32) ws[A.o_pf + k] = 0.0;
         __syncwarp();
         const int nent = (dyn ? T.nmus : 0) + (reuse < 2 ? T.ncontact : 0);
@@ -277,15 +273,18 @@ __device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, dou
         }
         __syncwarp();
     }
+    PHASE_MARK(4);
     if (dyn) {
         for (int b = lane; b < nb; b += 32) wk_gather_body(C, b);
         for (int k = lane; k < nq; k += 32) wk_gather_coord(C, k, ctl);
         __syncwarp();
+        PHASE_MARK(5);
         const bool composite = !T.implicit && reuse == 0;
         for (int L = A.nlevels - 1; L >= 0; --L) {
             for (int b = A.level_start[L] + lane; b < A.level_start[L + 1]; b += 32) wk_inward(C, b, composite);
             __syncwarp();
         }
+        PHASE_MARK(6);
         if (T.implicit) {
             for (int k = lane; k < nq; k += 32) out[k] = ws[A.o_tau + k] - ws[A.o_taub + k];
         } else {
@@ -295,7 +294,9 @@ __device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, dou
                 __syncwarp();
                 for (int e = lane; e < A.npairs; e += 32) wk_mass_entry(C, A.pair_i[e], A.pair_j[e], nq);
                 __syncwarp();
+                PHASE_MARK(7);
                 wk_ldlt_factor(C, nq);
+                PHASE_MARK(8);
             }
             for (int i = lane; i < nq; i += 32) ws[A.o_tau + i] -= ws[A.o_taub + i]; // right-hand side
             __syncwarp();
@@ -303,6 +304,7 @@ __device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, dou
         }
         __syncwarp();
     }
+    PHASE_MARK(9);
     // goal integrands (MocoControlGoal.cpp:121-131, MocoStateTrackingGoal.cpp:103-117, MocoContactTrackingGoal.cpp:240-287)
     double* integ = out + nq + nz + T.n_auxres;
     int gi = 0;
@@ -312,7 +314,7 @@ __device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, dou
         const int slot = gi++;
         if (!((mask >> (1 + slot)) & 1u)) continue;
         const int* ip = T.idx + gr[4];
-        const double* dp = T.dbl + gr[5];
+        const double* dp = T.dblG + gr[5];
         double val = 0;
         switch (gr[0]) {
         case MOCOB200_GOAL_CONTROL: {
@@ -324,13 +326,13 @@ __device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, dou
         } break;
         case MOCOB200_GOAL_STATE_TRACKING:
             for (int k = lane; k < ip[0]; k += 32) {
-                const double e = q[ip[1 + 2 * k]] - ppoly_eval(T, ip[2 + 2 * k], time);
+                const double e = q[ip[1 + 2 * k]] - ws[A.o_ref + ip[2 + 2 * k]];
                 val += dp[3 + k] * (e * e);
             }
             break;
         case MOCOB200_GOAL_CONTROL_TRACKING:
             for (int k = lane; k < ip[0]; k += 32) {
-                const double e = ctl[ip[1 + 2 * k]] - ppoly_eval(T, ip[2 + 2 * k], time);
+                const double e = ctl[ip[1 + 2 * k]] - ws[A.o_ref + ip[2 + 2 * k]];
                 val += dp[3 + k] * (e * e);
             }
             break;
@@ -343,23 +345,20 @@ __device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, dou
         case MOCOB200_GOAL_CONTACT_TRACKING: {
             const int proj = ip[0], ng = ip[1];
             const V3 pv = ld3(dp + 3);
-            // lane t < 3 ng evaluates reference component t % 3 of group t / 3 (one parallel spline pass)
-            int myref = -1, mygrp = -1;
+            int mygrp = -1; // lane k sums group k
             {
                 const int* gp = ip + 2;
                 for (int k = 0; k < ng; ++k) {
-                    const int ncon = gp[0];
-                    if (lane / 3 == k) myref = gp[1 + 2 * ncon + lane % 3];
                     if (lane == k) mygrp = (int)(gp - ip);
-                    gp += 1 + 2 * ncon + 3;
+                    gp += 1 + 2 * gp[0] + 3;
                 }
             }
-            const double r = myref >= 0 ? ppoly_eval(T, myref, time) : 0.0;
-            const int src = 3 * min(lane, max(ng - 1, 0));
-            const V3 fr = mk(__shfl_sync(0xffffffffu, r, src), __shfl_sync(0xffffffffu, r, src + 1), __shfl_sync(0xffffffffu, r, src + 2));
             if (mygrp >= 0) {
                 const int* gp = ip + mygrp;
                 const int ncon = gp[0];
+                const double* ref = ws + A.o_ref;
+                const int r0 = gp[1 + 2 * ncon], r1 = gp[2 + 2 * ncon], r2 = gp[3 + 2 * ncon];
+                const V3 fr = mk(r0 >= 0 ? ref[r0] : 0.0, r1 >= 0 ? ref[r1] : 0.0, r2 >= 0 ? ref[r2] : 0.0);
                 V3 fm = mk(0, 0, 0);
                 for (int c = 0; c < ncon; ++c) {
                     const V3 f = ldv(ws + A.o_cF + 3 * gp[1 + 2 * c]);
@@ -378,6 +377,7 @@ __device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, dou
         if (lane == 0) integ[slot] = val;
     }
     __syncwarp();
+    PHASE_MARK(10);
 }
 
 } // namespace mocob200

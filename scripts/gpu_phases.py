@@ -1,0 +1,36 @@
+"""Development: phase stopwatch of one warp evaluation (library built with MOCOB200_PROFILE_PHASES=1) and the NaN hunt."""
+import ctypes as C, os, sys
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import __graft_entry__ as ge
+m = ge.package()
+gold = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+names = ["t0", "kin", "inertia", "musgeom", "forces", "gather", "inward", "mass", "ldlt", "solve", "integrands", "lookups"]
+def clocks():
+    buf = (C.c_longlong * 32)()
+    assert m.lib().mocob200_debug_phase_clocks(buf) == 0
+    a = np.array(buf[:12])
+    return a
+if hasattr(m.lib(), "mocob200_debug_phase_clocks"):
+    p = m.Problem.load(os.path.join(gold, "gait2d_tracking.mb20"))
+    ev = m.Evaluator(p)
+    x = p.make_iterate(seed=1, spread=0.1)
+    for what in ("nominal", "jac"):
+        for rep in range(3):
+            if what == "nominal": ev.eval_points(x)
+            else: ev.eval_jac_g(x)
+            a = clocks()
+            d = dict(zip(names[1:11], (a[1:11] - a[:10]).tolist()))
+            d["lookups"] = int(a[11] - a[0]); d["kin"] = int(a[1] - a[11])
+            print(what, rep, "total", a[10] - a[0], d)
+# NaN hunt: central h=1e-3 on gait2d_tracking
+sys.path.insert(0, os.path.join(os.path.dirname(gold), "..", "oracle"))
+import oracle_py as O
+p = m.Problem.load(os.path.join(gold, "gait2d_tracking.mb20"), "num_mesh_intervals=10")
+ev, o = m.Evaluator(p), O.Oracle(p)
+ev.set_fd(1, 1e-3, 0); o.set_fd(1, 1e-3, 0)
+x = p.make_iterate(seed=5, spread=0.3)
+J = ev.eval_points(x, jacobian=True)
+Yo, Jo = o.eval_point_jacobians(x)
+print("nan gpu", np.argwhere(np.isnan(J))[:20].tolist(), "nan oracle", np.argwhere(np.isnan(Jo))[:20].tolist())
+print("n nan", np.isnan(J).sum(), np.isnan(Jo).sum())

@@ -76,6 +76,8 @@ def test_fd_jacobian_pipeline_1e7(pkg, orc, name, scheme, h):
     x = p.make_iterate(seed=5, spread=0.3)
     J = ev.eval_points(x, jacobian=True)
     Yo, Jo = o.eval_point_jacobians(x)
+    assert np.isfinite(Jo).all(), "oracle FD block not finite at %s" % np.argwhere(~np.isfinite(Jo))[:8].tolist()
+    assert np.isfinite(J).all(), "device FD block not finite at %s" % np.argwhere(~np.isfinite(J))[:8].tolist()
     scale = np.abs(Yo)[:, :, None] + np.abs(Jo) + 1e-300
     assert np.max(np.abs(J - Jo) / scale) < 1e-7
     v, vo = ev.eval_jac_g(x), o.eval_jac_g(x)
@@ -107,6 +109,26 @@ def test_fd_jacobian_default_steps_noise_bound(pkg, orc, name, scheme):
     assert np.max(np.abs(J - Jo) / scale) < 2e-3
     # and the median entry is far better than the worst one
     assert np.median(np.abs(J - Jo) / scale) < 1e-6
+
+
+@pytest.mark.parametrize("name", ["gait2d_tracking", "gait2d_prediction", "hanging_muscle"])
+def test_no_read_of_uninitialised_scratch(pkg, orc, name, monkeypatch):
+    """MOCOB200_POISON_SCRATCH=1 starts every warp evaluation from NaN-filled shared memory: a quantity read before it
+    is written (e.g. the position of an inactive ConditionalPathPoint multiplied by its zero force) shows up as NaN."""
+    monkeypatch.setenv("MOCOB200_POISON_SCRATCH", "1")
+    monkeypatch.setenv("MOCOB200_KERNEL", "warp")
+    p = load(pkg, name)
+    ev, o = pkg.Evaluator(p), orc.Oracle(p)
+    for seed, spread in ((1, 0.2), (2, 1.0)):
+        x = p.make_iterate(seed=seed, spread=spread)
+        Yo = o.eval_points(x)
+        assert relerr(ev.eval_points(x), Yo) < 1e-10
+        for scheme in (FD_FORWARD, FD_CENTRAL):
+            ev.set_fd(scheme)
+            o.set_fd(scheme)
+            J = ev.eval_points(x, jacobian=True)
+            _, Jo = o.eval_point_jacobians(x)
+            assert np.array_equal(np.isfinite(J), np.isfinite(Jo))
 
 
 def test_fd_structural_zeros_are_exact(pkg):
