@@ -168,12 +168,51 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
             b = bodyI(b)[0];
         }
     }
+    // finite-difference work lists
+    std::vector<int> p0Dirs, p1Dirs, locDir, locKind, locOwner, locRole, dirClass(L.n_in, 4);
+    {
+        const char* e = getenv("MOCOB200_FD_LOCAL");
+        bool local = !(e && e[0] == '0');
+        for (int g = 0; g < T.ngoal; ++g) {
+            const int* gr = T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
+            const int k = gr[0];
+            if (gr[3] && k != MOCOB200_GOAL_CONTROL && k != MOCOB200_GOAL_STATE_TRACKING && k != MOCOB200_GOAL_CONTACT_TRACKING &&
+                k != MOCOB200_GOAL_SUM_SQUARED_STATE && k != MOCOB200_GOAL_CONTROL_TRACKING)
+                local = false; // an integrand this analysis does not know
+        }
+        const int ns = 2 * nq + T.nz, iz = 1 + 2 * nq, ic = 1 + ns, ider = 1 + ns + T.nc, iaux = ider + (L.implicit ? nq : 0);
+        for (int d = 0; d < L.n_in; ++d) {
+            if (d >= 1 && d <= nq) { dirClass[d] = 0; continue; }
+            if ((d > nq && d <= 2 * nq) || (L.implicit && d >= ider && d < ider + nq)) { dirClass[d] = 1; continue; }
+            if (d == 0) { dirClass[d] = 2; continue; }
+            if (!local) continue;
+            int owners = 0, kind = -1, owner = -1, role = -1;
+            for (int m = 0; m < T.nmus; ++m) {
+                const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
+                if (d == ic + mi[2]) { ++owners; kind = 0; owner = m; role = 0; }
+                if (mi[3] >= 0 && d == iz + mi[3]) { ++owners; kind = 0; owner = m; role = 1; }
+                if (mi[4] >= 0 && d == iz + mi[4]) { ++owners; kind = 0; owner = m; role = 2; }
+                if (mi[6] >= 0 && d == iaux + mi[6]) { ++owners; kind = 0; owner = m; role = 3; }
+            }
+            for (int a = 0; a < T.ncact; ++a)
+                if (d == ic + T.idx[T.o_cact_i + a * MOCOB200_CACT_ISTRIDE + 1]) { ++owners; kind = 1; owner = a; role = 0; }
+            if (owners != 1) continue; // shared or unread input: difference the whole function
+            dirClass[d] = 3;
+            locDir.push_back(d); locKind.push_back(kind); locOwner.push_back(owner); locRole.push_back(role);
+        }
+        for (int d = 0; d < L.n_in; ++d) {
+            if (dirClass[d] == 0) p0Dirs.push_back(d);
+            else if (dirClass[d] != 3) p1Dirs.push_back(d);
+        }
+        h->WA.time_integrands_only = local ? 1 : 0;
+    }
     // all topology arrays live in one int pool so that a block can stage them with one copy loop
     std::vector<int> pool;
     std::vector<size_t> at;
     auto put = [&](const std::vector<int>& v) { at.push_back(pool.size()); pool.insert(pool.end(), v.begin(), v.end()); pool.push_back(0); };
     put(levelStart); put(childStart); put(childList); put(bodyPpStart); put(bodyPpList); put(dofBody); put(bodyFlags);
     put(ppMpp); put(mppPp); put(mppCoord); put(pairI); put(pairJ);
+    put(p0Dirs); put(p1Dirs); put(locDir); put(locKind); put(locOwner); put(locRole); put(dirClass);
     const int* base = devUpload(pool);
     h->owned.push_back((void*)base);
     WarpAux& A = h->WA;
@@ -194,6 +233,10 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     A.npairs = (int)pairI.size();
     A.pair_i = base + at[10];
     A.pair_j = base + at[11];
+    A.n_p0 = (int)p0Dirs.size(); A.n_p1 = (int)p1Dirs.size(); A.n_local = (int)locDir.size();
+    A.p0_dirs = base + at[12]; A.p1_dirs = base + at[13];
+    A.loc_dir = base + at[14]; A.loc_kind = base + at[15]; A.loc_owner = base + at[16]; A.loc_role = base + at[17];
+    A.dir_class = base + at[18];
     // staged part of the pools: everything below the bounds block (host-only), plus the goal payload
     {
         int goal0 = T.n_dbl;
@@ -224,11 +267,14 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     // velocity-dependent block
     A.o_w = take(3 * nb); A.o_v = take(3 * nb); A.o_al = take(3 * nb); A.o_ac = take(3 * nb);
     A.o_cF = take(3 * T.ncontact); A.o_cP = take(3 * T.ncontact);
+    A.o_mlen = take(T.nmus); A.o_mspd = take(T.nmus); A.o_mout = take(4 * T.nmus); // nominal muscle lengths, speeds, outputs
     A.blob_end = o;
     // per-evaluation scratch
     A.o_F = take(3 * nb); A.o_N = take(3 * nb); A.o_cm = take(nb); A.o_ch = take(3 * nb); A.o_cJ = take(6 * nb);
     A.o_tau = take(nq); A.o_taub = take(nq); A.o_lin = take(3 * nq); A.o_ang = take(3 * nq);
     A.o_pf = take(3 * npp); A.o_dp = take(3 * A.nmpp);
+    // right-hand sides / solutions of the local columns: reuse the wrench + composite-inertia scratch, dead by then
+    A.o_Rm = ((T.nmus + T.ncact) * nq <= A.o_tau - A.o_F) ? A.o_F : take((T.nmus + T.ncact) * nq);
     A.ws_doubles = o;
     { const char* e = getenv("MOCOB200_POISON_SCRATCH"); A.poison = (e && e[0] == '1') ? 1 : 0; }
     return warp_kernels_configure(A, err);

@@ -1,7 +1,11 @@
 // Warp-per-evaluation kernels: point functions over the grid and their CasADi-style finite differences.
 // Work item = (grid point, FD direction[, callback group]); each warp owns ws_doubles of shared memory.
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+
 #include "kernels.cuh"
-#include "point_warp_dyn.cuh"
+#include "point_warp_local.cuh"
 
 namespace mocob200 {
 
@@ -17,6 +21,20 @@ __device__ __forceinline__ void warp_gather_inputs(const DevLayout& L, const dou
     __syncwarp();
 }
 
+// Copies with several independent loads in flight per thread (a plain copy loop serialises on the load latency).
+template <class V>
+__device__ __forceinline__ void copy_batched(V* __restrict__ dst, const V* __restrict__ src, int n, int tid, int nt) {
+    int i = tid;
+    for (; i + 7 * nt < n; i += 8 * nt) {
+        V v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = src[i + k * nt];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) dst[i + k * nt] = v[k];
+    }
+    for (; i < n; i += nt) dst[i] = src[i];
+}
+
 // Block prologue: copy the model tables and the topology arrays into shared memory (coalesced, all threads), and
 // return table descriptors whose pointers address the staged copies. Every thread of the block must call this.
 __device__ __forceinline__ double* stage_tables(const DevTables& T, const WarpAux& A, double* smem, DevTables& Ts, WarpAux& As) {
@@ -25,15 +43,11 @@ __device__ __forceinline__ double* stage_tables(const DevTables& T, const WarpAu
     int* si = (int*)(smem + ((nd + ng + 1) & ~1));
     int* sa = si + A.st_nint;
     const int tid = threadIdx.x, nt = blockDim.x;
-    {
-        const double2* src = (const double2*)T.dbl;
-        double2* dst = (double2*)sd;
-        for (int i = tid; i < nd / 2; i += nt) dst[i] = src[i];
-        if ((nd & 1) && tid == 0) sd[nd - 1] = T.dbl[nd - 1];
-    }
-    for (int i = tid; i < ng; i += nt) sd[nd + i] = T.dbl[A.st_goal0 + i];
-    for (int i = tid; i < A.st_nint; i += nt) si[i] = T.idx[i];
-    for (int i = tid; i < A.st_naux; i += nt) sa[i] = A.aux_base[i];
+    copy_batched((double2*)sd, (const double2*)T.dbl, nd / 2, tid, nt);
+    if ((nd & 1) && tid == 0) sd[nd - 1] = T.dbl[nd - 1];
+    copy_batched(sd + nd, T.dbl + A.st_goal0, ng, tid, nt);
+    copy_batched(si, T.idx, A.st_nint, tid, nt);
+    copy_batched(sa, A.aux_base, A.st_naux, tid, nt);
     __syncthreads();
     Ts = T;
     Ts.dblP = T.dbl;
@@ -63,7 +77,10 @@ __device__ __forceinline__ void blob_load(const WarpAux& A, double* ws, const do
     const int n = A.blob_end - A.blob_begin;
     const int m = (reuse == 2 ? A.blob_end : A.blob_pos_end) - A.blob_begin;
     const double* src = cfg + (size_t)j * n;
-    for (int i = lane; i < m; i += 32) ws[A.blob_begin + i] = src[i];
+    if ((((size_t)j * n) & 1) == 0) { // 16-byte aligned blob: two doubles per load
+        copy_batched((double2*)(ws + A.blob_begin), (const double2*)src, m / 2, lane, 32);
+        if ((m & 1) && lane == 0) ws[A.blob_begin + m - 1] = src[m - 1];
+    } else copy_batched(ws + A.blob_begin, src, m, lane, 32);
     __syncwarp();
 }
 // which part of the nominal evaluation survives a perturbation of input `dir`:
@@ -96,9 +113,10 @@ __global__ void k_wpoints_nominal(DevTables Tg, WarpAux Ag, DevLayout L, const d
 }
 
 // one-sided differences, two launches:
-//   phase 0: item = point * (1 + nq) + k; k = 0 is the nominal evaluation (writes Y and the blob), k >= 1 perturbs
-//            coordinate k (a full evaluation);
-//   phase 1: item = point * (n_in - nq) + t; t = 0 perturbs time, t >= 1 perturbs input nq + t; these reload the blob.
+//   phase 0: item = point * (1 + n_p0) + k; k = 0 is the nominal evaluation (writes Y and the blob), k >= 1 perturbs
+//            coordinate p0_dirs[k-1] (a full evaluation);
+//   phase 1: item = point * (n_p1 + 1) + t; t < n_p1 perturbs input p1_dirs[t] (time, speeds, ...), t = n_p1 writes
+//            the columns of all "local" inputs (point_warp_local.cuh); all of these reload the blob.
 // Perturbed evaluations write their RAW outputs into J[j][o][dir]; k_fd1_finalize turns them into differences.
 __global__ void k_wpoints_fd1(DevTables Tg, WarpAux Ag, DevLayout L, FdSettings fd, const double* __restrict__ x, double* __restrict__ Y,
                               double* __restrict__ J, double* __restrict__ cfg, int p0, int np, int phase) {
@@ -108,32 +126,52 @@ __global__ void k_wpoints_fd1(DevTables Tg, WarpAux Ag, DevLayout L, FdSettings 
     double* scratch = stage_tables(Tg, Ag, smem, T, A);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long item = (long)blockIdx.x * (blockDim.x >> 5) + warp;
-    const int per = phase == 0 ? 1 + L.nq : L.n_in - L.nq;
+    const int per = phase == 0 ? 1 + A.n_p0 : A.n_p1 + (A.n_local > 0 ? 1 : 0);
     if (item >= (long)np * per) return;
     double* ws = scratch + (size_t)warp * A.ws_doubles;
     const int j = p0 + (int)(item / per), t = (int)(item % per);
-    const int dir = phase == 0 ? (t == 0 ? -1 : t) : (t == 0 ? 0 : L.nq + t);
+    double* Jp = J + (size_t)j * L.n_out * L.n_in;
+#ifdef MOCOB200_PROFILE_PHASES
+    const long long clk0 = clock64();
+    struct ItemClock { int phase; long item; long long c0; int lane;
+        __device__ ~ItemClock() { if (lane == 0 && item < 16384) g_item_clk[phase][item] = clock64() - c0; } } itemClock{phase, item, clk0, lane};
+#endif
+    if (phase == 1 && t == A.n_p1) {
+        poison_scratch(A, ws, lane);
+        warp_gather_inputs(L, x, j, ws + A.o_in, lane);
+        blob_load(A, ws, cfg, j, lane, 2);
+        wk_local_columns(T, A, ws, ws + A.o_Rm, fd.h, fd.scheme == MOCOB200_FD_FORWARD, Jp, Y + (size_t)j * L.n_out, L.n_in, L.n_out);
+        return;
+    }
+    const int dir = phase == 0 ? (t == 0 ? -1 : A.p0_dirs[t - 1]) : A.p1_dirs[t];
     const int reuse = dir < 0 ? 0 : reuse_level(L, dir);
     poison_scratch(A, ws, lane);
     warp_gather_inputs(L, x, j, ws + A.o_in, lane);
     if (dir >= 0 && lane == 0) ws[A.o_in + dir] += (fd.scheme == MOCOB200_FD_FORWARD) ? fd.h : -fd.h;
     if (reuse) blob_load(A, ws, cfg, j, lane, reuse);
     __syncwarp();
-    warp_eval_point(T, A, ws, 0xffffffffu, reuse, dir == 0);
+    unsigned mask = 0xffffffffu;
+    if (dir == 0 && A.time_integrands_only) {
+        // nothing but the tracking references depends on time: the dynamics rows keep their nominal values
+        mask = 0xfffffffeu;
+        for (int o = lane; o < L.n_dyn_out; o += 32) ws[A.o_out + o] = Y[(size_t)j * L.n_out + o];
+    }
+    warp_eval_point(T, A, ws, mask, reuse, dir == 0, phase == 0 && A.lockstep);
     if (dir < 0) {
         for (int o = lane; o < L.n_out; o += 32) Y[(size_t)j * L.n_out + o] = ws[A.o_out + o];
         blob_save(A, ws, cfg, j, lane);
     } else {
-        double* Jp = J + (size_t)j * L.n_out * L.n_in;
         for (int o = lane; o < L.n_out; o += 32) Jp[(size_t)o * L.n_in + dir] = ws[A.o_out + o];
     }
 }
-__global__ void k_fd1_finalize(DevLayout L, FdSettings fd, const double* __restrict__ Y, double* __restrict__ J, int p0, int np) {
+__global__ void k_fd1_finalize(DevLayout L, FdSettings fd, const int* __restrict__ dir_class, const double* __restrict__ Y,
+                               double* __restrict__ J, int p0, int np) {
     const long n = (long)np * L.n_out * L.n_in;
     const long t = (long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
     const long base = (long)p0 * L.n_out * L.n_in;
     const long row = t / L.n_in; // (point - p0) * n_out + o
+    if (dir_class[t - row * L.n_in] == 3) return; // a finished column (point_warp_local.cuh)
     const double y0 = Y[(size_t)p0 * L.n_out + row];
     const double yp = J[base + t];
     J[base + t] = (fd.scheme == MOCOB200_FD_FORWARD) ? (yp - y0) / fd.h : (y0 - yp) / fd.h;
@@ -203,14 +241,23 @@ __global__ void k_wpoints_central(DevTables Tg, WarpAux Ag, DevLayout L, FdSetti
 }
 
 // ---------------------------------------------------------------------------------------------
-static size_t warpSmemBytes(const WarpAux& A) { return ((size_t)A.st_doubles + (size_t)A.wpb * A.ws_doubles) * sizeof(double); }
+static size_t smemBytesFor(const WarpAux& A, int warps) { return ((size_t)A.st_doubles + (size_t)warps * A.ws_doubles) * sizeof(double); }
+static size_t warpSmemBytes(const WarpAux& A) { return smemBytesFor(A, A.wpb); }
+// phase 1 of the one-sided scheme: all partial evaluations of one grid point in one block when they fit, so that the
+// point's blob is read from L2 once and served to the other warps by L1
+static int phase1Warps(const WarpAux& A) {
+    const int per = A.n_p1 + (A.n_local > 0 ? 1 : 0);
+    return (per >= 1 && per <= 32 && smemBytesFor(A, per) <= 220 * 1024) ? per : A.wpb;
+}
 
 bool warp_kernels_configure(WarpAux& A, std::string& err) {
     // choose the number of warps per block so that a block's scratch fits and several blocks share an SM
     A.wpb = 4;
-    while (A.wpb > 1 && warpSmemBytes(A) > 96 * 1024) A.wpb >>= 1;
-    const size_t bytes = warpSmemBytes(A);
-    if (bytes > 227 * 1024) { err = "per-warp scratch exceeds shared memory"; return false; }
+    if (const char* e = getenv("MOCOB200_WPB")) A.wpb = atoi(e) > 0 ? atoi(e) : 4;
+    { const char* e = getenv("MOCOB200_LOCKSTEP"); A.lockstep = (e && e[0] == '1') ? 1 : 0; }
+    while (A.wpb > 1 && warpSmemBytes(A) > (getenv("MOCOB200_WPB") ? 220 : 96) * 1024) A.wpb >>= 1;
+    const size_t bytes = std::max(warpSmemBytes(A), smemBytesFor(A, phase1Warps(A)));
+    if (warpSmemBytes(A) > 227 * 1024) { err = "per-warp scratch exceeds shared memory"; return false; }
     // the attribute is per function, not per handle: only ever raise it
     static size_t g_maxBytes[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     int dev = 0;
@@ -237,12 +284,30 @@ int launch_wpoints_fd(const DevTables& T, const WarpAux& A, const DevLayout& L, 
                       double* d_J, double* d_cfg, int p0, int np, cudaStream_t s, cudaEvent_t after_nominal) {
     if (np <= 0) { if (after_nominal) cudaEventRecord(after_nominal, s); return 0; }
     if (fd.scheme != MOCOB200_FD_CENTRAL) {
-        const long items0 = (long)np * (1 + L.nq), items1 = (long)np * (L.n_in - L.nq);
+        const long items0 = (long)np * (1 + A.n_p0), items1 = (long)np * (A.n_p1 + (A.n_local > 0 ? 1 : 0));
+        // development stopwatch (MOCOB200_TIMING=1): per-kernel CUDA-event times of the previous call on stderr
+        static const bool timing = getenv("MOCOB200_TIMING") != nullptr;
+        static cudaEvent_t te[4] = {nullptr, nullptr, nullptr, nullptr};
+        if (timing) {
+            if (!te[0]) for (auto& e : te) cudaEventCreate(&e);
+            else if (cudaEventQuery(te[3]) == cudaSuccess) {
+                float a = 0, b = 0, c = 0;
+                cudaEventElapsedTime(&a, te[0], te[1]); cudaEventElapsedTime(&b, te[1], te[2]); cudaEventElapsedTime(&c, te[2], te[3]);
+                fprintf(stderr, "[mocob200 timing] phase0 %.1f us  phase1 %.1f us  finalize %.1f us\n", 1e3 * a, 1e3 * b, 1e3 * c);
+            }
+            cudaEventRecord(te[0], s);
+        }
         k_wpoints_fd1<<<(unsigned)((items0 + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np, 0);
         if (after_nominal) cudaEventRecord(after_nominal, s);
-        k_wpoints_fd1<<<(unsigned)((items1 + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np, 1);
+        if (timing) cudaEventRecord(te[1], s);
+        if (items1 > 0) {
+            const int w1 = phase1Warps(A);
+            k_wpoints_fd1<<<(unsigned)((items1 + w1 - 1) / w1), w1 * 32, smemBytesFor(A, w1), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np, 1);
+        }
+        if (timing) cudaEventRecord(te[2], s);
         const long n = (long)np * L.n_out * L.n_in;
-        k_fd1_finalize<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(L, fd, d_Y, d_J, p0, np);
+        k_fd1_finalize<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(L, fd, A.dir_class, d_Y, d_J, p0, np);
+        if (timing) cudaEventRecord(te[3], s);
         return 3;
     }
     launch_wpoints_nominal(T, A, L, d_x, d_Y, d_cfg, p0, np, s);
@@ -255,6 +320,9 @@ int launch_wpoints_fd(const DevTables& T, const WarpAux& A, const DevLayout& L, 
 } // namespace mocob200
 
 #ifdef MOCOB200_PROFILE_PHASES
+extern "C" int mocob200_debug_item_clocks(long long* out, int phase, int n) {
+    return cudaMemcpyFromSymbol(out, mocob200::g_item_clk, sizeof(long long) * n, sizeof(long long) * 16384 * phase) == cudaSuccess ? 0 : 3;
+}
 extern "C" int mocob200_debug_phase_clocks(long long* out32) {
     return cudaMemcpyFromSymbol(out32, mocob200::g_phase_clk, sizeof(long long) * 32) == cudaSuccess ? 0 : 3;
 }

@@ -39,6 +39,17 @@ struct WarpAux {
     // (one int pool starting at aux_base). st_doubles = size of the staged region in doubles.
     int st_ndbl, st_goal0, st_ngoal, st_nint, st_naux, st_doubles;
     const int* aux_base;
+    // Finite-difference work lists (one-sided schemes). Directions are point-function input indices.
+    //   p0_dirs: full evaluations (coordinates), run beside the nominal one;
+    //   p1_dirs: partial evaluations that reload the nominal scratch (speeds, time, anything unclassified);
+    //   loc_*:   inputs acting through one muscle / coordinate actuator, whose columns the nominal warp writes itself
+    //            (point_warp_local.cuh); dir_class[dir] == 3 marks them for k_fd1_finalize.
+    int n_p0, n_p1, n_local, time_integrands_only;
+    const int* p0_dirs; const int* p1_dirs;
+    const int* loc_dir; const int* loc_kind; const int* loc_owner; const int* loc_role;
+    const int* dir_class;
+    int o_mlen, o_mspd, o_mout, o_Rm;
+    int lockstep;
     int poison; // development switch (MOCOB200_POISON_SCRATCH=1): every evaluation starts from NaN-filled scratch
     int ws_doubles;
     int wpb; // warps (= evaluations in flight) per block, chosen at create from the scratch size
@@ -317,6 +328,8 @@ __device__ inline MuscleOut wk_muscle_dynamics(const WarpCtx& C, int m, const do
         prevV = vG;
         ++na;
     }
+    C.at(A.o_mlen)[m] = length;
+    C.at(A.o_mspd)[m] = speed;
     const double activation = (flags & MOCOB200_MUS_FLAG_IGNORE_ACTIVATION_DYNAMICS) ? ctl[mi[2]] : z[mi[3]];
     const double ntf = (mi[4] >= 0) ? z[mi[4]] : NAN;
     const double ntfd = (mi[6] >= 0) ? auxder[mi[6]] : NAN;

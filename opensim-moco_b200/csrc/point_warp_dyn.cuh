@@ -10,9 +10,10 @@ __device__ __forceinline__ V3 sym6mul(const double* s, V3 v) { return symmul(s, 
 // phase boundaries of its evaluation. Compiled out of the product.
 #ifdef MOCOB200_PROFILE_PHASES
 __device__ long long g_phase_clk[32];
-#define PHASE_MARK(k) do { __syncwarp(); if (blockIdx.x == 0 && threadIdx.x == 0) g_phase_clk[k] = clock64(); } while (0)
+__device__ long long g_item_clk[2][16384]; // [phase][item]: cycles of each fd1 work item
+#define PHASE_MARK(k) do { if (lockstep) __syncthreads(); __syncwarp(); if (blockIdx.x == 0 && threadIdx.x == 0) g_phase_clk[k] = clock64(); } while (0)
 #else
-#define PHASE_MARK(k) do { } while (0)
+#define PHASE_MARK(k) do { if (lockstep) __syncthreads(); } while (0)
 #endif
 
 // ---- phase 3: applied wrench on body b about its origin (one lane per body), fixed summation order -------------
@@ -204,7 +205,10 @@ __device__ __forceinline__ double warp_sum(double v) { // fixed butterfly order 
 // and, in implicit mode, the same accelerations). The reused and the recomputed quantities come from the same device
 // functions, so a reusing evaluation is bit-identical to a full one.
 // time_moved: the evaluation's time differs from the one whose tracking-reference values sit in the scratch.
-__device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, double* ws, unsigned mask, int reuse, bool time_moved) {
+// lockstep: every warp of the block runs the same kind of evaluation (same mask and reuse), so they meet at a block
+// barrier between phases and share their instruction fetches (the code is long and mostly straight-line).
+__device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, double* ws, unsigned mask, int reuse, bool time_moved,
+                                       bool lockstep = false) {
     const WarpCtx C{T, A, ws, (int)(threadIdx.x & 31)};
     const int lane = C.lane;
     const int nq = T.nq, nz = T.nz, nc = T.nc, nb = T.nb;
@@ -266,9 +270,12 @@ __device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, dou
                 const MuscleOut mo = wk_muscle_dynamics(C, m, u, z, ctl, auxder, true, false);
                 double* zdot = out + nq;
                 double* auxres = zdot + nz;
-                if (mi[3] >= 0) zdot[mi[3]] = activation_dot(ctl[mi[2]], z[mi[3]], md[5], md[6]);
+                const double adot = mi[3] >= 0 ? activation_dot(ctl[mi[2]], z[mi[3]], md[5], md[6]) : 0.0;
+                if (mi[3] >= 0) zdot[mi[3]] = adot;
                 if (mi[4] >= 0) zdot[mi[4]] = mo.nfDeriv;
                 if (mi[7] >= 0) auxres[mi[7]] = mo.residual;
+                double* keep = ws + A.o_mout + 4 * m; // for the local Jacobian columns (point_warp_local.cuh)
+                keep[0] = mo.tendonForce; keep[1] = mo.nfDeriv; keep[2] = mo.residual; keep[3] = adot;
             }
         }
         __syncwarp();

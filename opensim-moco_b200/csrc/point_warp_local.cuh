@@ -1,0 +1,199 @@
+// Warp-cooperative point function, part 3: Jacobian columns of the inputs that act through ONE muscle or ONE
+// coordinate actuator (auxiliary states, controls, auxiliary derivative variables).
+//
+// The multibody outputs are exactly linear in every actuator force: udot = M^-1 (tau_applied - bias) in explicit mode,
+// residual = tau_applied - M udot - bias in implicit mode, and tau_applied = sum_m R_m(q) F_m + ... with R_m the
+// generalized force of a unit tension in muscle m (minus its moment arms). For such an input x the finite difference
+// of the point function therefore factors exactly:
+//       (f(x + h) - f(x)) / h  =  M^-1 R_m (F_m(x + h) - F_m(x)) / h            (rows udot; R_m alone for residuals)
+// and the rows of the muscle's own auxiliary dynamics are scalar finite differences of the muscle model. So the warp
+// that evaluates the nominal point also produces these columns: R_m for all muscles (one lane each), one multi-right-
+// hand-side solve with the LDL^T factor it already holds (one lane per right-hand side), then one lane per input for
+// the scalar differences — instead of one full point evaluation per input. The step h and the one-sided formula are
+// the caller's (CasADi's forward/backward scheme, CasOCFunction.h:38-44); only the order of the floating-point
+// operations differs from differencing the whole function, and the result carries less cancellation error.
+// Goal integrands are plain sums over inputs, so their rows are the differences of the one changed term.
+#pragma once
+#include "point_warp_dyn.cuh"
+
+namespace mocob200 {
+
+enum { MOCOB200_LOCAL_MUSCLE = 0, MOCOB200_LOCAL_ACTUATOR = 1 };
+enum { MOCOB200_ROLE_CONTROL = 0, MOCOB200_ROLE_ACTIVATION = 1, MOCOB200_ROLE_TENDON_FORCE = 2, MOCOB200_ROLE_TENDON_FORCE_DERIV = 3 };
+
+// R_m: generalized force of a unit tension in muscle m, from the stored path geometry (one lane). The tension pulls
+// the two end points of every inter-body segment towards each other (GeometryPath.cpp:306-432); a force f at point P
+// of body b loads every dof k between b and ground with a_k . ((P - oM_k) x f) + l_k . f, and a moving point adds
+// (dP/dq) . f on its coordinate (MovingPathPoint.cpp:374-392).
+__device__ inline void wk_unit_tension_force(const WarpCtx& C, int m, double* Rm) {
+    const DevTables& T = C.T;
+    const WarpAux& A = C.A;
+    const int nq = T.nq;
+    const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
+    const int first = mi[0], count = mi[1];
+    const unsigned active = (unsigned)C.at(A.o_mact)[m];
+    const double* ppos = C.at(A.o_ppos);
+    for (int k = 0; k < nq; ++k) Rm[k] = 0.0;
+    int prev = -1;
+    for (int k = 0; k < count; ++k) {
+        if (!((active >> k) & 1u)) continue;
+        if (prev >= 0) {
+            const int pa = first + prev, pb = first + k;
+            const int* ia = T.idx + T.o_pp_i + pa * MOCOB200_PP_ISTRIDE;
+            const int* ib = T.idx + T.o_pp_i + pb * MOCOB200_PP_ISTRIDE;
+            if (ia[0] != ib[0]) {
+                V3 dir = ldv(ppos + 3 * pb) - ldv(ppos + 3 * pa);
+                const double nn = sqrt(dot(dir, dir));
+                dir = (nn < 1.9984014443252818e-14) ? (NAN * dir) : ((1.0 / nn) * dir);
+                // the pair of opposite forces loads only the dofs between the two bodies and their common ancestor
+                // (on the common part of the tree the two moments cancel exactly: dir is parallel to Pb - Pa); bodies are
+                // stored parent-before-child, so the larger index is never an ancestor of the smaller
+                const V3 Pa = ldv(ppos + 3 * pa), Pb = ldv(ppos + 3 * pb);
+#pragma unroll 1
+                for (int side = 0; side < 2; ++side) {
+                    const int pp = side ? pb : pa;
+                    const int* pi = side ? ib : ia;
+                    if (pi[1] == MOCOB200_PP_MOVING) {
+                        const V3 dpl = ldv(C.at(A.o_dpl) + 3 * A.pp_mpp[pp]);
+                        const V3 dpg = pi[0] >= 0 ? rmul(C.at(A.o_R) + 9 * pi[0], dpl) : dpl;
+                        Rm[pi[6]] += side ? -dot(dpg, dir) : dot(dpg, dir);
+                    }
+                }
+                int ba = ia[0], bb = ib[0];
+                while (ba != bb) {
+                    const bool sideB = bb > ba;
+                    const int b = sideB ? bb : ba;
+                    const V3 f = sideB ? -1.0 * dir : dir;
+                    const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
+                    const V3 mom = cross((sideB ? Pb : Pa) - ldv(C.at(A.o_oM) + 3 * b), f);
+                    for (int d = 0; d < bi[3]; ++d) {
+                        const int dof = bi[2] + d;
+                        Rm[dof] += dot(ldv(C.at(A.o_a) + 3 * dof), mom) + dot(ldv(C.at(A.o_l) + 3 * dof), f);
+                    }
+                    if (sideB) bb = bi[0]; else ba = bi[0];
+                }
+            }
+        }
+        prev = k;
+    }
+}
+
+// x <- M^-1 x with the stored LDL^T factor, one lane, in place
+__device__ inline void wk_ldlt_solve_lane(const double* M, int n, double* x) {
+    for (int i = 1; i < n; ++i) { double v = x[i]; for (int k = 0; k < i; ++k) v -= M[i * n + k] * x[k]; x[i] = v; }
+    for (int i = 0; i < n; ++i) x[i] /= M[i * n + i];
+    for (int i = n - 2; i >= 0; --i) { double v = x[i]; for (int k = i + 1; k < n; ++k) v -= M[k * n + i] * x[k]; x[i] = v; }
+}
+
+// change of integrand `slot`'s value when input `dir` moves from v0 to v1 (all other inputs fixed): the one term of
+// the goal's sum that reads it (MocoControlGoal.cpp:121-131, MocoStateTrackingGoal.cpp:103-117, ...).
+__device__ inline double wk_integrand_term_delta(const DevTables& T, const WarpAux& A, const double* ws, const int* gr, int dir, double v0,
+                                                 double v1) {
+    const int* ip = T.idx + gr[4];
+    const double* dp = T.dblG + gr[5];
+    const int ns = 2 * T.nq + T.nz;
+    const int state = (dir >= 1 && dir <= ns) ? dir - 1 : -1;               // index relative to q
+    const int control = (dir > ns && dir <= ns + T.nc) ? dir - 1 - ns : -1;
+    double d = 0.0;
+    switch (gr[0]) {
+    case MOCOB200_GOAL_CONTROL: {
+        const int expo = ip[0], n = ip[2];
+        for (int k = 0; k < n; ++k)
+            if (ip[3 + k] == control) {
+                const double g1 = expo == 2 ? v1 * v1 : pow(fabs(v1), (double)expo), g0 = expo == 2 ? v0 * v0 : pow(fabs(v0), (double)expo);
+                d += dp[3 + k] * g1 - dp[3 + k] * g0;
+            }
+    } break;
+    case MOCOB200_GOAL_STATE_TRACKING:
+        for (int k = 0; k < ip[0]; ++k)
+            if (ip[1 + 2 * k] == state) {
+                const double r = ws[A.o_ref + ip[2 + 2 * k]], e1 = v1 - r, e0 = v0 - r;
+                d += dp[3 + k] * (e1 * e1) - dp[3 + k] * (e0 * e0);
+            }
+        break;
+    case MOCOB200_GOAL_CONTROL_TRACKING:
+        for (int k = 0; k < ip[0]; ++k)
+            if (ip[1 + 2 * k] == control) {
+                const double r = ws[A.o_ref + ip[2 + 2 * k]], e1 = v1 - r, e0 = v0 - r;
+                d += dp[3 + k] * (e1 * e1) - dp[3 + k] * (e0 * e0);
+            }
+        break;
+    case MOCOB200_GOAL_SUM_SQUARED_STATE:
+        for (int k = 0; k < ip[0]; ++k)
+            if (ip[1 + 2 * k] == state) d += dp[3 + k] * (v1 * v1) - dp[3 + k] * (v0 * v0);
+        break;
+    default: break; // contact tracking reads coordinates, speeds and time only
+    }
+    return d;
+}
+
+// The columns J[:, dir] of every "local" input of one grid point (whole warp; the scratch holds the nominal
+// evaluation or its reloaded blob, y0 its outputs, Rm is (nmus + ncact) * nq doubles of scratch that the evaluation no longer needs).
+__device__ inline void wk_local_columns(const DevTables& T, const WarpAux& A, double* ws, double* Rm, double h, bool forward,
+                                        double* __restrict__ Jp, const double* __restrict__ y0, int n_in, int n_out) {
+    const WarpCtx C{T, A, ws, (int)(threadIdx.x & 31)};
+    const int lane = C.lane, nq = T.nq, nz = T.nz, nc = T.nc;
+    const double* in = ws + A.o_in;
+    const double* z = in + 1 + 2 * nq;
+    const double* ctl = z + nz;
+    const double* auxder = ctl + nc + (T.implicit ? nq : 0);
+    // right-hand sides: unit tension of every muscle, unit control of every coordinate actuator
+    for (int r = lane; r < T.nmus + T.ncact; r += 32) {
+        double* x = Rm + r * nq;
+        if (r < T.nmus) wk_unit_tension_force(C, r, x);
+        else {
+            const int a = r - T.nmus;
+            const int* ai = T.idx + T.o_cact_i + a * MOCOB200_CACT_ISTRIDE;
+            for (int k = 0; k < nq; ++k) x[k] = 0.0;
+            x[ai[0]] = T.dbl[T.o_cact_d + a * MOCOB200_CACT_DSTRIDE];
+        }
+        if (!T.implicit) wk_ldlt_solve_lane(ws + A.o_M, nq, x);
+    }
+    __syncwarp();
+    const double step = forward ? h : -h;
+    for (int t = lane; t < A.n_local; t += 32) {
+        const int dir = A.loc_dir[t], kind = A.loc_kind[t], owner = A.loc_owner[t], role = A.loc_role[t];
+        const double v0 = in[dir], v1 = v0 + step;
+        const double inv = forward ? 1.0 / h : -1.0 / h; // (f(x+h) - f(x)) / h or (f(x) - f(x-h)) / h
+        double* col = Jp + dir;
+        for (int o = 0; o < n_out; ++o) col[(size_t)o * n_in] = 0.0;
+        const double* c = Rm + (kind == MOCOB200_LOCAL_MUSCLE ? owner : T.nmus + owner) * nq;
+        if (kind == MOCOB200_LOCAL_ACTUATOR) {
+            // force = optimal_force * control (CoordinateActuator.cpp:185-204): c already carries optimal_force
+            const double dctl = (v1 - v0) * inv;
+            for (int k = 0; k < nq; ++k) col[(size_t)k * n_in] = c[k] * dctl;
+        } else {
+            const int m = owner;
+            const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
+            const double* md = T.dbl + T.o_mus_d + m * MOCOB200_MUS_DSTRIDE;
+            const int flags = mi[5];
+            double e = ctl[mi[2]], a = mi[3] >= 0 ? z[mi[3]] : NAN, ntf = mi[4] >= 0 ? z[mi[4]] : NAN, ntfd = mi[6] >= 0 ? auxder[mi[6]] : NAN;
+            const double length = ws[A.o_mlen + m], speed = ws[A.o_mspd + m];
+            const bool noActDyn = flags & MOCOB200_MUS_FLAG_IGNORE_ACTIVATION_DYNAMICS;
+            const double* mo0 = ws + A.o_mout + 4 * m; // nominal tension, d(tendon force)/dt, residual, activation rate
+            if (role == MOCOB200_ROLE_CONTROL) e = v1;
+            else if (role == MOCOB200_ROLE_ACTIVATION) a = v1;
+            else if (role == MOCOB200_ROLE_TENDON_FORCE) ntf = v1;
+            else ntfd = v1;
+            const MuscleOut o1 = dgf_muscle(md, flags, length, speed, noActDyn ? e : a, ntf, ntfd, false);
+            const double dF = (o1.tendonForce - mo0[0]) * inv;
+            for (int k = 0; k < nq; ++k) col[(size_t)k * n_in] = c[k] * dF;
+            if (mi[3] >= 0) col[(size_t)(nq + mi[3]) * n_in] = (activation_dot(e, a, md[5], md[6]) - mo0[3]) * inv;
+            if (mi[4] >= 0) col[(size_t)(nq + mi[4]) * n_in] = (o1.nfDeriv - mo0[1]) * inv;
+            if (mi[7] >= 0) col[(size_t)(nq + nz + mi[7]) * n_in] = (o1.residual - mo0[2]) * inv;
+        }
+        int slot = 0;
+        for (int g = 0; g < T.ngoal; ++g) {
+            const int* gr = T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
+            if (!gr[3]) continue;
+            col[(size_t)(nq + nz + T.n_auxres + slot) * n_in] = wk_integrand_term_delta(T, A, ws, gr, dir, v0, v1) * inv;
+            ++slot;
+        }
+        // a non-finite nominal output poisons its whole row, as it does when the full function is differenced
+        for (int o = 0; o < n_out; ++o)
+            if (!isfinite(y0[o])) col[(size_t)o * n_in] = NAN;
+    }
+    __syncwarp();
+}
+
+} // namespace mocob200

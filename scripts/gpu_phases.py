@@ -23,6 +23,15 @@ if hasattr(m.lib(), "mocob200_debug_phase_clocks"):
             d = dict(zip(names[1:11], (a[1:11] - a[:10]).tolist()))
             d["lookups"] = int(a[11] - a[0]); d["kin"] = int(a[1] - a[11])
             print(what, rep, "total", a[10] - a[0], d)
+if hasattr(m.lib(), "mocob200_debug_item_clocks"):
+    ev.eval_jac_g(x); ev.eval_jac_g(x)
+    for phase, per in ((0, 11), (1, 12)):
+        n = 101 * per
+        buf = (C.c_longlong * n)()
+        assert m.lib().mocob200_debug_item_clocks(buf, phase, n) == 0
+        a = np.array(buf[:n]).reshape(101, per)
+        print("phase", phase, "item cycles by type: median", np.median(a, axis=0).astype(int).tolist(), "max", a.max(axis=0).tolist())
+sys.exit(0)
 # NaN hunt: central h=1e-3 on gait2d_tracking
 sys.path.insert(0, os.path.join(os.path.dirname(gold), "..", "oracle"))
 import oracle_py as O

@@ -131,6 +131,27 @@ def test_no_read_of_uninitialised_scratch(pkg, orc, name, monkeypatch):
             assert np.array_equal(np.isfinite(J), np.isfinite(Jo))
 
 
+@pytest.mark.parametrize("name", FIXTURES)
+@pytest.mark.parametrize("scheme", [FD_FORWARD, FD_BACKWARD])
+def test_local_columns_equal_whole_function_differences(pkg, name, scheme, monkeypatch):
+    """Inputs that act through one muscle / one coordinate actuator: the factored difference written by the nominal
+    warp (point_warp_local.cuh) against differencing the whole point function (MOCOB200_FD_LOCAL=0), same step."""
+    monkeypatch.setenv("MOCOB200_KERNEL", "warp")
+    p = load(pkg, name)
+    x = p.make_iterate(seed=9, spread=0.4)
+    ev = pkg.Evaluator(p)
+    ev.set_fd(scheme, 1e-4, 0)
+    J = ev.eval_points(x, jacobian=True)
+    Y = ev.eval_points(x)
+    monkeypatch.setenv("MOCOB200_FD_LOCAL", "0")
+    ev0 = pkg.Evaluator(p)
+    ev0.set_fd(scheme, 1e-4, 0)
+    J0 = ev0.eval_points(x, jacobian=True)
+    scale = np.abs(Y)[:, :, None] + np.abs(J0) + 1e-300
+    # the whole-function difference carries eps*|Y|/h of cancellation noise (2e-12 |Y| here); the factored one does not
+    assert np.max(np.abs(J - J0) / scale) < 1e-8
+
+
 def test_fd_structural_zeros_are_exact(pkg):
     """Perturbing an input that an output does not depend on must give an exactly zero difference (the evaluations that
     reuse the nominal poses / velocities are bit-identical to full ones): muscle excitations do not enter udot, and an
