@@ -89,6 +89,7 @@ struct mocob200_handle {
     // side stream: the endpoint functions (which need only x and the integrals of the nominal point outputs) run
     // beside the FD evaluations of the point functions
     cudaStream_t stream2 = nullptr;
+    SideStreams side{};
     cudaEvent_t evY = nullptr, evE = nullptr;
     double* d_I2 = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -169,7 +170,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
         }
     }
     // finite-difference work lists
-    std::vector<int> p0Dirs, p1Dirs, locDir, locKind, locOwner, locRole, dirClass(L.n_in, 4);
+    std::vector<int> p0Dirs, p1Dirs, p2Dirs, locDir, locKind, locOwner, locRole, dirClass(L.n_in, 4);
     {
         const char* e = getenv("MOCOB200_FD_LOCAL");
         bool local = !(e && e[0] == '0');
@@ -202,7 +203,8 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
         }
         for (int d = 0; d < L.n_in; ++d) {
             if (dirClass[d] == 0) p0Dirs.push_back(d);
-            else if (dirClass[d] != 3) p1Dirs.push_back(d);
+            else if (dirClass[d] == 1) p1Dirs.push_back(d);
+            else if (dirClass[d] != 3) p2Dirs.push_back(d);
         }
         h->WA.time_integrands_only = local ? 1 : 0;
     }
@@ -212,7 +214,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     auto put = [&](const std::vector<int>& v) { at.push_back(pool.size()); pool.insert(pool.end(), v.begin(), v.end()); pool.push_back(0); };
     put(levelStart); put(childStart); put(childList); put(bodyPpStart); put(bodyPpList); put(dofBody); put(bodyFlags);
     put(ppMpp); put(mppPp); put(mppCoord); put(pairI); put(pairJ);
-    put(p0Dirs); put(p1Dirs); put(locDir); put(locKind); put(locOwner); put(locRole); put(dirClass);
+    put(p0Dirs); put(p1Dirs); put(p2Dirs); put(locDir); put(locKind); put(locOwner); put(locRole); put(dirClass);
     const int* base = devUpload(pool);
     h->owned.push_back((void*)base);
     WarpAux& A = h->WA;
@@ -233,10 +235,10 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     A.npairs = (int)pairI.size();
     A.pair_i = base + at[10];
     A.pair_j = base + at[11];
-    A.n_p0 = (int)p0Dirs.size(); A.n_p1 = (int)p1Dirs.size(); A.n_local = (int)locDir.size();
-    A.p0_dirs = base + at[12]; A.p1_dirs = base + at[13];
-    A.loc_dir = base + at[14]; A.loc_kind = base + at[15]; A.loc_owner = base + at[16]; A.loc_role = base + at[17];
-    A.dir_class = base + at[18];
+    A.n_p0 = (int)p0Dirs.size(); A.n_p1 = (int)p1Dirs.size(); A.n_p2 = (int)p2Dirs.size(); A.n_local = (int)locDir.size();
+    A.p0_dirs = base + at[12]; A.p1_dirs = base + at[13]; A.p2_dirs = base + at[14];
+    A.loc_dir = base + at[15]; A.loc_kind = base + at[16]; A.loc_owner = base + at[17]; A.loc_role = base + at[18];
+    A.dir_class = base + at[19];
     // staged part of the pools: everything below the bounds block (host-only), plus the goal payload
     {
         int goal0 = T.n_dbl;
@@ -340,7 +342,7 @@ bool runFd(mocob200_handle* h) {
     const bool overlap = h->world == 1; // single rank: Y is complete as soon as the nominal evaluations are
     if (h->warpFor(mocob200_point_evals_per_jacobian(h) / h->world))
         h->launches += launch_wpoints_fd(h->DT, h->WA, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_cfg, h->p0, h->p1 - h->p0, h->stream,
-                                         overlap ? h->evY : nullptr);
+                                         overlap ? h->evY : nullptr, &h->side);
     else {
         launch_points_fd(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream);
         h->launches++;
@@ -399,6 +401,9 @@ void mocob200_destroy(mocob200_handle* h) {
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     for (void* p : h->owned) cudaFree(p);
     for (auto& e : h->ev) if (e) cudaEventDestroy(e);
+    for (auto& st : h->side.s) if (st) cudaStreamDestroy(st);
+    if (h->side.fork) cudaEventDestroy(h->side.fork);
+    for (auto& e : h->side.join) if (e) cudaEventDestroy(e);
     if (h->evY) cudaEventDestroy(h->evY);
     if (h->evE) cudaEventDestroy(h->evE);
     if (h->stream2) cudaStreamDestroy(h->stream2);
@@ -510,6 +515,9 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     if (!h->ck(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking), "stream")) return fail(MOCOB200_ERR_CUDA, "");
     if (!h->ck(cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking), "stream")) return fail(MOCOB200_ERR_CUDA, "");
     for (auto& e : h->ev) cudaEventCreate(&e);
+    for (auto& st : h->side.s) cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&h->side.fork, cudaEventDisableTiming);
+    for (auto& e : h->side.join) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&h->evY, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&h->evE, cudaEventDisableTiming);
     defaultFd(h->fd, R->fd_scheme);

@@ -62,8 +62,13 @@ double measure_fp64_peak_tflops(int device);
 bool warp_kernels_configure(WarpAux& A, std::string& err);
 void launch_wpoints_nominal(const DevTables& T, const WarpAux& A, const DevLayout& L, const double* d_x, double* d_Y, double* d_cfg,
                             int p0, int np, cudaStream_t s);
+// side streams + events for kernels that run next to each other inside one evaluation (owned by the handle)
+struct SideStreams {
+    cudaStream_t s[2];
+    cudaEvent_t fork, join[2];
+};
 // after_nominal (may be null) is recorded on s once Y (the nominal point outputs) is complete
 int launch_wpoints_fd(const DevTables& T, const WarpAux& A, const DevLayout& L, const FdSettings& fd, const double* d_x, double* d_Y,
-                      double* d_J, double* d_cfg, int p0, int np, cudaStream_t s, cudaEvent_t after_nominal);
+                      double* d_J, double* d_cfg, int p0, int np, cudaStream_t s, cudaEvent_t after_nominal, const SideStreams* side);
 
 } // namespace mocob200

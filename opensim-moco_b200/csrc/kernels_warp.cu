@@ -105,65 +105,85 @@ __global__ void k_wpoints_nominal(DevTables Tg, WarpAux Ag, DevLayout L, const d
     if (item >= np) return;
     double* ws = scratch + (size_t)warp * A.ws_doubles;
     const int j = p0 + item;
+#ifdef MOCOB200_PROFILE_PHASES
+    const long long clk0 = clock64();
+    struct ItemClock { long item; long long c0; int lane;
+        __device__ ~ItemClock() { if (lane == 0 && item < 16384) g_item_clk[0][item] = clock64() - c0; } } itemClock{item, clk0, lane};
+#endif
     poison_scratch(A, ws, lane);
     warp_gather_inputs(L, x, j, ws + A.o_in, lane);
-    warp_eval_point(T, A, ws, 0xffffffffu, 0, false);
+    warp_eval_point_t<0>(T, A, ws, 0xffffffffu, false, false);
     for (int o = lane; o < L.n_out; o += 32) Y[(size_t)j * L.n_out + o] = ws[A.o_out + o];
     if (cfg) blob_save(A, ws, cfg, j, lane);
 }
 
-// one-sided differences, two launches:
-//   phase 0: item = point * (1 + n_p0) + k; k = 0 is the nominal evaluation (writes Y and the blob), k >= 1 perturbs
-//            coordinate p0_dirs[k-1] (a full evaluation);
-//   phase 1: item = point * (n_p1 + 1) + t; t < n_p1 perturbs input p1_dirs[t] (time, speeds, ...), t = n_p1 writes
-//            the columns of all "local" inputs (point_warp_local.cuh); all of these reload the blob.
-// Perturbed evaluations write their RAW outputs into J[j][o][dir]; k_fd1_finalize turns them into differences.
+// One-sided differences. Four kernels, each holding only the code of its own kind of work item (the point function is
+// long, mostly straight-line code: a kernel that carries all variants runs every one of them at half speed on
+// instruction fetch):
+//   KIND 0  item = point * (1 + n_p0) + k; k = 0 is the nominal evaluation (writes Y and the blob), k >= 1 perturbs
+//           coordinate p0_dirs[k-1] (a full evaluation);
+//   KIND 1  item = point * n_p1 + t perturbs p1_dirs[t] (speeds, implicit-mode accelerations): reloads the poses;
+//   KIND 2  item = point * n_p2 + t perturbs p2_dirs[t] (time, unclassified inputs): reloads poses and velocities;
+//   KIND 3  item = point: the columns of all "local" inputs (point_warp_local.cuh) from the reloaded blob.
+// KIND 1-3 run side by side once KIND 0 is done and write finished difference quotients. The coordinate evaluations of
+// KIND 0 run beside the nominal one, so they leave their RAW outputs in J[j][o][dir]; the first KIND 2 item of each grid
+// point (or k_fd1_finalize when there is none) turns those columns into quotients.
+template <int KIND>
 __global__ void k_wpoints_fd1(DevTables Tg, WarpAux Ag, DevLayout L, FdSettings fd, const double* __restrict__ x, double* __restrict__ Y,
-                              double* __restrict__ J, double* __restrict__ cfg, int p0, int np, int phase) {
+                              double* __restrict__ J, double* __restrict__ cfg, int p0, int np) {
     extern __shared__ double smem[];
     DevTables T;
     WarpAux A;
     double* scratch = stage_tables(Tg, Ag, smem, T, A);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long item = (long)blockIdx.x * (blockDim.x >> 5) + warp;
-    const int per = phase == 0 ? 1 + A.n_p0 : A.n_p1 + (A.n_local > 0 ? 1 : 0);
+    const int per = KIND == 0 ? 1 + A.n_p0 : KIND == 1 ? A.n_p1 : KIND == 2 ? A.n_p2 : 1;
     if (item >= (long)np * per) return;
     double* ws = scratch + (size_t)warp * A.ws_doubles;
     const int j = p0 + (int)(item / per), t = (int)(item % per);
     double* Jp = J + (size_t)j * L.n_out * L.n_in;
 #ifdef MOCOB200_PROFILE_PHASES
     const long long clk0 = clock64();
-    struct ItemClock { int phase; long item; long long c0; int lane;
-        __device__ ~ItemClock() { if (lane == 0 && item < 16384) g_item_clk[phase][item] = clock64() - c0; } } itemClock{phase, item, clk0, lane};
+    struct ItemClock { long item; long long c0; int lane;
+        __device__ ~ItemClock() { if (lane == 0 && item < 16384) g_item_clk[KIND][item] = clock64() - c0; } } itemClock{item, clk0, lane};
 #endif
-    if (phase == 1 && t == A.n_p1) {
-        poison_scratch(A, ws, lane);
-        warp_gather_inputs(L, x, j, ws + A.o_in, lane);
+    poison_scratch(A, ws, lane);
+    warp_gather_inputs(L, x, j, ws + A.o_in, lane);
+    if (KIND == 3) {
         blob_load(A, ws, cfg, j, lane, 2);
         wk_local_columns(T, A, ws, ws + A.o_Rm, fd.h, fd.scheme == MOCOB200_FD_FORWARD, Jp, Y + (size_t)j * L.n_out, L.n_in, L.n_out);
         return;
     }
-    const int dir = phase == 0 ? (t == 0 ? -1 : A.p0_dirs[t - 1]) : A.p1_dirs[t];
-    const int reuse = dir < 0 ? 0 : reuse_level(L, dir);
-    poison_scratch(A, ws, lane);
-    warp_gather_inputs(L, x, j, ws + A.o_in, lane);
+    const int dir = KIND == 0 ? (t == 0 ? -1 : A.p0_dirs[t - 1]) : KIND == 1 ? A.p1_dirs[t] : A.p2_dirs[t];
     if (dir >= 0 && lane == 0) ws[A.o_in + dir] += (fd.scheme == MOCOB200_FD_FORWARD) ? fd.h : -fd.h;
-    if (reuse) blob_load(A, ws, cfg, j, lane, reuse);
+    if (KIND > 0) blob_load(A, ws, cfg, j, lane, KIND);
     __syncwarp();
     unsigned mask = 0xffffffffu;
-    if (dir == 0 && A.time_integrands_only) {
+    if (KIND == 2 && dir == 0 && A.time_integrands_only) {
         // nothing but the tracking references depends on time: the dynamics rows keep their nominal values
         mask = 0xfffffffeu;
         for (int o = lane; o < L.n_dyn_out; o += 32) ws[A.o_out + o] = Y[(size_t)j * L.n_out + o];
     }
-    warp_eval_point(T, A, ws, mask, reuse, dir == 0, phase == 0 && A.lockstep);
+    warp_eval_point_t<KIND>(T, A, ws, mask, KIND == 2 && dir == 0, false);
+    const double inv = (fd.scheme == MOCOB200_FD_FORWARD) ? 1.0 / fd.h : -1.0 / fd.h;
     if (dir < 0) {
         for (int o = lane; o < L.n_out; o += 32) Y[(size_t)j * L.n_out + o] = ws[A.o_out + o];
         blob_save(A, ws, cfg, j, lane);
-    } else {
+    } else if (KIND == 0) {
         for (int o = lane; o < L.n_out; o += 32) Jp[(size_t)o * L.n_in + dir] = ws[A.o_out + o];
+    } else {
+        const double* y0 = Y + (size_t)j * L.n_out;
+        for (int o = lane; o < L.n_out; o += 32) Jp[(size_t)o * L.n_in + dir] = (ws[A.o_out + o] - y0[o]) * inv;
+        if (KIND == 2 && t == 0) { // finish the coordinate columns of this grid point
+            for (int e = lane; e < L.n_out * A.n_p0; e += 32) {
+                const int o = e / A.n_p0, c = A.p0_dirs[e - o * A.n_p0];
+                double* v = Jp + (size_t)o * L.n_in + c;
+                *v = (*v - y0[o]) * inv;
+            }
+        }
     }
 }
+// fallback when no KIND 2 work exists: quotients of the coordinate columns (dir_class 0) only
 __global__ void k_fd1_finalize(DevLayout L, FdSettings fd, const int* __restrict__ dir_class, const double* __restrict__ Y,
                                double* __restrict__ J, int p0, int np) {
     const long n = (long)np * L.n_out * L.n_in;
@@ -171,7 +191,7 @@ __global__ void k_fd1_finalize(DevLayout L, FdSettings fd, const int* __restrict
     if (t >= n) return;
     const long base = (long)p0 * L.n_out * L.n_in;
     const long row = t / L.n_in; // (point - p0) * n_out + o
-    if (dir_class[t - row * L.n_in] == 3) return; // a finished column (point_warp_local.cuh)
+    if (dir_class[t - row * L.n_in] != 0) return; // every other column is written finished
     const double y0 = Y[(size_t)p0 * L.n_out + row];
     const double yp = J[base + t];
     J[base + t] = (fd.scheme == MOCOB200_FD_FORWARD) ? (yp - y0) / fd.h : (y0 - yp) / fd.h;
@@ -246,7 +266,7 @@ static size_t warpSmemBytes(const WarpAux& A) { return smemBytesFor(A, A.wpb); }
 // phase 1 of the one-sided scheme: all partial evaluations of one grid point in one block when they fit, so that the
 // point's blob is read from L2 once and served to the other warps by L1
 static int phase1Warps(const WarpAux& A) {
-    const int per = A.n_p1 + (A.n_local > 0 ? 1 : 0);
+    const int per = A.n_p1;
     return (per >= 1 && per <= 32 && smemBytesFor(A, per) <= 220 * 1024) ? per : A.wpb;
 }
 
@@ -265,7 +285,10 @@ bool warp_kernels_configure(WarpAux& A, std::string& err) {
     if (dev >= 0 && dev < 8 && bytes <= g_maxBytes[dev]) return true;
     cudaError_t e;
     if ((e = cudaFuncSetAttribute(k_wpoints_nominal, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
-        (e = cudaFuncSetAttribute(k_wpoints_fd1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_wpoints_fd1<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_wpoints_fd1<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_wpoints_fd1<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_wpoints_fd1<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
         (e = cudaFuncSetAttribute(k_wpoints_central, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess) {
         err = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e);
         return false;
@@ -281,11 +304,11 @@ void launch_wpoints_nominal(const DevTables& T, const WarpAux& A, const DevLayou
 }
 // returns the number of kernels launched
 int launch_wpoints_fd(const DevTables& T, const WarpAux& A, const DevLayout& L, const FdSettings& fd, const double* d_x, double* d_Y,
-                      double* d_J, double* d_cfg, int p0, int np, cudaStream_t s, cudaEvent_t after_nominal) {
+                      double* d_J, double* d_cfg, int p0, int np, cudaStream_t s, cudaEvent_t after_nominal, const SideStreams* side) {
     if (np <= 0) { if (after_nominal) cudaEventRecord(after_nominal, s); return 0; }
     if (fd.scheme != MOCOB200_FD_CENTRAL) {
-        const long items0 = (long)np * (1 + A.n_p0), items1 = (long)np * (A.n_p1 + (A.n_local > 0 ? 1 : 0));
-        // development stopwatch (MOCOB200_TIMING=1): per-kernel CUDA-event times of the previous call on stderr
+        const long items0 = (long)np * (1 + A.n_p0), items1 = (long)np * A.n_p1, items2 = (long)np * A.n_p2;
+        // development stopwatch (MOCOB200_TIMING=1): per-stage CUDA-event times of the previous call on stderr
         static const bool timing = getenv("MOCOB200_TIMING") != nullptr;
         static cudaEvent_t te[4] = {nullptr, nullptr, nullptr, nullptr};
         if (timing) {
@@ -293,22 +316,49 @@ int launch_wpoints_fd(const DevTables& T, const WarpAux& A, const DevLayout& L, 
             else if (cudaEventQuery(te[3]) == cudaSuccess) {
                 float a = 0, b = 0, c = 0;
                 cudaEventElapsedTime(&a, te[0], te[1]); cudaEventElapsedTime(&b, te[1], te[2]); cudaEventElapsedTime(&c, te[2], te[3]);
-                fprintf(stderr, "[mocob200 timing] phase0 %.1f us  phase1 %.1f us  finalize %.1f us\n", 1e3 * a, 1e3 * b, 1e3 * c);
+                fprintf(stderr, "[mocob200 timing] full %.1f us  partial+local %.1f us  finalize %.1f us\n", 1e3 * a, 1e3 * b, 1e3 * c);
             }
             cudaEventRecord(te[0], s);
         }
-        k_wpoints_fd1<<<(unsigned)((items0 + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np, 0);
+        k_wpoints_fd1<0><<<(unsigned)((items0 + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
         if (after_nominal) cudaEventRecord(after_nominal, s);
         if (timing) cudaEventRecord(te[1], s);
+        int launched = 1;
+        // the three kinds of blob-reloading work run side by side
+        const bool fork = side && side->s[0] && side->s[1];
+        cudaStream_t s2 = fork ? side->s[0] : s, s3 = fork ? side->s[1] : s;
+        if (fork) {
+            cudaEventRecord(side->fork, s);
+            cudaStreamWaitEvent(s2, side->fork, 0);
+            cudaStreamWaitEvent(s3, side->fork, 0);
+        }
         if (items1 > 0) {
             const int w1 = phase1Warps(A);
-            k_wpoints_fd1<<<(unsigned)((items1 + w1 - 1) / w1), w1 * 32, smemBytesFor(A, w1), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np, 1);
+            k_wpoints_fd1<1><<<(unsigned)((items1 + w1 - 1) / w1), w1 * 32, smemBytesFor(A, w1), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
+            ++launched;
+        }
+        if (items2 > 0) {
+            k_wpoints_fd1<2><<<(unsigned)((items2 + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s2>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
+            ++launched;
+        }
+        if (A.n_local > 0) {
+            k_wpoints_fd1<3><<<(unsigned)((np + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s3>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
+            ++launched;
+        }
+        if (fork) {
+            cudaEventRecord(side->join[0], s2);
+            cudaEventRecord(side->join[1], s3);
+            cudaStreamWaitEvent(s, side->join[0], 0);
+            cudaStreamWaitEvent(s, side->join[1], 0);
         }
         if (timing) cudaEventRecord(te[2], s);
-        const long n = (long)np * L.n_out * L.n_in;
-        k_fd1_finalize<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(L, fd, A.dir_class, d_Y, d_J, p0, np);
+        if (items2 == 0) {
+            const long n = (long)np * L.n_out * L.n_in;
+            k_fd1_finalize<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(L, fd, A.dir_class, d_Y, d_J, p0, np);
+            ++launched;
+        }
         if (timing) cudaEventRecord(te[3], s);
-        return 3;
+        return launched;
     }
     launch_wpoints_nominal(T, A, L, d_x, d_Y, d_cfg, p0, np, s);
     if (after_nominal) cudaEventRecord(after_nominal, s);

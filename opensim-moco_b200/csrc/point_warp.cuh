@@ -41,11 +41,12 @@ struct WarpAux {
     const int* aux_base;
     // Finite-difference work lists (one-sided schemes). Directions are point-function input indices.
     //   p0_dirs: full evaluations (coordinates), run beside the nominal one;
-    //   p1_dirs: partial evaluations that reload the nominal scratch (speeds, time, anything unclassified);
+    //   p1_dirs: partial evaluations that reload the nominal poses (speeds, implicit-mode accelerations);
+    //   p2_dirs: partial evaluations that reload poses and velocities (time, anything unclassified);
     //   loc_*:   inputs acting through one muscle / coordinate actuator, whose columns the nominal warp writes itself
     //            (point_warp_local.cuh); dir_class[dir] == 3 marks them for k_fd1_finalize.
-    int n_p0, n_p1, n_local, time_integrands_only;
-    const int* p0_dirs; const int* p1_dirs;
+    int n_p0, n_p1, n_p2, n_local, time_integrands_only;
+    const int* p0_dirs; const int* p1_dirs; const int* p2_dirs;
     const int* loc_dir; const int* loc_kind; const int* loc_owner; const int* loc_role;
     const int* dir_class;
     int o_mlen, o_mspd, o_mout, o_Rm;

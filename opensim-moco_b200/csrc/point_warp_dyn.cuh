@@ -10,7 +10,7 @@ __device__ __forceinline__ V3 sym6mul(const double* s, V3 v) { return symmul(s, 
 // phase boundaries of its evaluation. Compiled out of the product.
 #ifdef MOCOB200_PROFILE_PHASES
 __device__ long long g_phase_clk[32];
-__device__ long long g_item_clk[2][16384]; // [phase][item]: cycles of each fd1 work item
+__device__ long long g_item_clk[4][16384]; // [phase][item]: cycles of each fd1 work item
 #define PHASE_MARK(k) do { if (lockstep) __syncthreads(); __syncwarp(); if (blockIdx.x == 0 && threadIdx.x == 0) g_phase_clk[k] = clock64(); } while (0)
 #else
 #define PHASE_MARK(k) do { if (lockstep) __syncthreads(); } while (0)
@@ -207,8 +207,9 @@ __device__ __forceinline__ double warp_sum(double v) { // fixed butterfly order 
 // time_moved: the evaluation's time differs from the one whose tracking-reference values sit in the scratch.
 // lockstep: every warp of the block runs the same kind of evaluation (same mask and reuse), so they meet at a block
 // barrier between phases and share their instruction fetches (the code is long and mostly straight-line).
-__device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, double* ws, unsigned mask, int reuse, bool time_moved,
-                                       bool lockstep = false) {
+template <int reuse>
+__device__ __forceinline__ void warp_eval_point_t(const DevTables& T, const WarpAux& A, double* ws, unsigned mask, bool time_moved,
+                                                  bool lockstep) {
     const WarpCtx C{T, A, ws, (int)(threadIdx.x & 31)};
     const int lane = C.lane;
     const int nq = T.nq, nz = T.nz, nc = T.nc, nb = T.nb;
@@ -385,6 +386,13 @@ __device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, dou
     }
     __syncwarp();
     PHASE_MARK(10);
+}
+// run-time reuse level: one specialised copy of the evaluation per level
+__device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, double* ws, unsigned mask, int reuse, bool time_moved,
+                                       bool lockstep = false) {
+    if (reuse == 0) warp_eval_point_t<0>(T, A, ws, mask, time_moved, lockstep);
+    else if (reuse == 1) warp_eval_point_t<1>(T, A, ws, mask, time_moved, lockstep);
+    else warp_eval_point_t<2>(T, A, ws, mask, time_moved, lockstep);
 }
 
 } // namespace mocob200

@@ -12,7 +12,7 @@ def clocks():
     a = np.array(buf[:12])
     return a
 if hasattr(m.lib(), "mocob200_debug_phase_clocks"):
-    p = m.Problem.load(os.path.join(gold, "gait2d_tracking.mb20"))
+    p = m.Problem.load(os.path.join(gold, "gait2d_tracking.mb20"), os.environ.get("PH_OPTS"))
     ev = m.Evaluator(p)
     x = p.make_iterate(seed=1, spread=0.1)
     for what in ("nominal", "jac"):
@@ -23,9 +23,15 @@ if hasattr(m.lib(), "mocob200_debug_phase_clocks"):
             d = dict(zip(names[1:11], (a[1:11] - a[:10]).tolist()))
             d["lookups"] = int(a[11] - a[0]); d["kin"] = int(a[1] - a[11])
             print(what, rep, "total", a[10] - a[0], d)
-if hasattr(m.lib(), "mocob200_debug_item_clocks"):
+            if what == "nominal" and hasattr(m.lib(), "mocob200_debug_item_clocks"):
+                n = min(ev.dims.n_grid, 16384)
+                buf = (C.c_longlong * n)()
+                m.lib().mocob200_debug_item_clocks(buf, 0, n)
+                b = np.array(buf[:n])
+                print("   nominal kernel item cycles: min %d median %d max %d (n=%d)" % (b.min(), np.median(b), b.max(), n))
+if hasattr(m.lib(), "mocob200_debug_item_clocks") and not os.environ.get("PH_OPTS"):
     ev.eval_jac_g(x); ev.eval_jac_g(x)
-    for phase, per in ((0, 11), (1, 12)):
+    for phase, per in ((0, 11), (1, 10), (2, 1), (3, 1)):
         n = 101 * per
         buf = (C.c_longlong * n)()
         assert m.lib().mocob200_debug_item_clocks(buf, phase, n) == 0
