@@ -79,7 +79,7 @@ struct mocob200_handle {
     // (throughput: enough evaluations to fill the machine with threads). MOCOB200_KERNEL=warp|thread forces one.
     bool useWarp = true;
     int kernelMode = 0; // 0 auto, 1 warp, 2 thread
-    long warpMaxEvals = 48000;
+    long warpMaxEvals = 30000;
     bool warpFor(long evals) const { return kernelMode == 1 || (kernelMode == 0 && evals <= warpMaxEvals); }
     std::vector<void*> owned;
     double* d_cfg = nullptr; // per-point blobs of the nominal evaluation (warp kernels)
@@ -170,7 +170,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
         }
     }
     // finite-difference work lists
-    std::vector<int> p0Dirs, p1Dirs, p2Dirs, locDir, locKind, locOwner, locRole, dirClass(L.n_in, 4);
+    std::vector<int> p0Dirs, p1Dirs, p2Dirs, cdDirs, locDir, locKind, locOwner, locRole, dirClass(L.n_in, 4);
     {
         const char* e = getenv("MOCOB200_FD_LOCAL");
         bool local = !(e && e[0] == '0');
@@ -202,6 +202,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
             locDir.push_back(d); locKind.push_back(kind); locOwner.push_back(owner); locRole.push_back(role);
         }
         for (int d = 0; d < L.n_in; ++d) {
+            if (dirClass[d] != 3) cdDirs.push_back(d);
             if (dirClass[d] == 0) p0Dirs.push_back(d);
             else if (dirClass[d] == 1) p1Dirs.push_back(d);
             else if (dirClass[d] != 3) p2Dirs.push_back(d);
@@ -214,7 +215,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     auto put = [&](const std::vector<int>& v) { at.push_back(pool.size()); pool.insert(pool.end(), v.begin(), v.end()); pool.push_back(0); };
     put(levelStart); put(childStart); put(childList); put(bodyPpStart); put(bodyPpList); put(dofBody); put(bodyFlags);
     put(ppMpp); put(mppPp); put(mppCoord); put(pairI); put(pairJ);
-    put(p0Dirs); put(p1Dirs); put(p2Dirs); put(locDir); put(locKind); put(locOwner); put(locRole); put(dirClass);
+    put(p0Dirs); put(p1Dirs); put(p2Dirs); put(cdDirs); put(locDir); put(locKind); put(locOwner); put(locRole); put(dirClass);
     const int* base = devUpload(pool);
     h->owned.push_back((void*)base);
     WarpAux& A = h->WA;
@@ -236,9 +237,10 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     A.pair_i = base + at[10];
     A.pair_j = base + at[11];
     A.n_p0 = (int)p0Dirs.size(); A.n_p1 = (int)p1Dirs.size(); A.n_p2 = (int)p2Dirs.size(); A.n_local = (int)locDir.size();
-    A.p0_dirs = base + at[12]; A.p1_dirs = base + at[13]; A.p2_dirs = base + at[14];
-    A.loc_dir = base + at[15]; A.loc_kind = base + at[16]; A.loc_owner = base + at[17]; A.loc_role = base + at[18];
-    A.dir_class = base + at[19];
+    A.p0_dirs = base + at[12]; A.p1_dirs = base + at[13]; A.p2_dirs = base + at[14]; A.cd_dirs = base + at[15];
+    A.n_cd = (int)cdDirs.size();
+    A.loc_dir = base + at[16]; A.loc_kind = base + at[17]; A.loc_owner = base + at[18]; A.loc_role = base + at[19];
+    A.dir_class = base + at[20];
     // staged part of the pools: everything below the bounds block (host-only), plus the goal payload
     {
         int goal0 = T.n_dbl;
@@ -344,9 +346,24 @@ bool runFd(mocob200_handle* h) {
         h->launches += launch_wpoints_fd(h->DT, h->WA, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_cfg, h->p0, h->p1 - h->p0, h->stream,
                                          overlap ? h->evY : nullptr, &h->side);
     else {
-        launch_points_fd(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream);
-        h->launches++;
-        if (overlap) cudaEventRecord(h->evY, h->stream);
+        // thread-per-evaluation kernel for the inputs that need whole evaluations; the local columns beside it
+        const bool local = h->WA.n_local > 0 && h->side.s[0];
+        if (local) {
+            // warp nominal evaluation first (Y and the blobs), then the local-column kernel next to the flat FD kernel
+            launch_wpoints_nominal(h->DT, h->WA, h->DL, h->d_x, h->d_Y, h->d_cfg, h->p0, h->p1 - h->p0, h->stream);
+            if (overlap) cudaEventRecord(h->evY, h->stream);
+            cudaEventRecord(h->side.fork, h->stream);
+            cudaStreamWaitEvent(h->side.s[0], h->side.fork, 0);
+            h->launches += 1 + launch_wlocal(h->DT, h->WA, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_cfg, h->p0, h->p1 - h->p0, h->side.s[0]);
+            cudaEventRecord(h->side.join[0], h->side.s[0]);
+            launch_points_fd_flat(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream, h->WA.cd_dirs, h->WA.n_cd);
+            h->launches++;
+            cudaStreamWaitEvent(h->stream, h->side.join[0], 0);
+        } else {
+            launch_points_fd(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream);
+            h->launches++;
+            if (overlap) cudaEventRecord(h->evY, h->stream);
+        }
     }
     cudaEventRecord(h->ev[1], h->stream);
     if (overlap) {
@@ -523,7 +540,8 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     defaultFd(h->fd, R->fd_scheme);
     // shard grid points evenly over ranks
     h->shard.resize(world + 1);
-    for (int r = 0; r <= world; ++r) h->shard[r] = (int)((long long)L.n_grid * r / world);
+    h->shard[0] = 0;
+    for (int r = 0; r < world; ++r) { int a = 0, b = 0; mocob200_shard_range(L.n_grid, r, world, &a, &b); h->shard[r + 1] = b; }
     h->p0 = h->shard[rank];
     h->p1 = h->shard[rank + 1];
     if (world > 1) {

@@ -196,4 +196,11 @@ int mocob200_make_iterate(const mocob200_tables* T, const mocob200_transcription
     } catch (const std::exception&) { return MOCOB200_ERR_UNSUPPORTED; }
 }
 
+int mocob200_shard_range(int n_grid, int rank, int world, int* p0, int* p1) {
+    if (n_grid < 0 || world < 1 || rank < 0 || rank >= world || !p0 || !p1) return MOCOB200_ERR_ARG;
+    *p0 = (int)((long long)n_grid * rank / world);
+    *p1 = (int)((long long)n_grid * (rank + 1) / world);
+    return MOCOB200_OK;
+}
+
 } // extern "C"

@@ -72,12 +72,15 @@ __device__ inline void fd_group(F&& f, const FdSettings& fd, double* in, int a, 
     }
 }
 
-// block = one grid point; thread a < n_in = FD direction a; thread n_in = nominal evaluation.
+// block = one grid point; thread t < ndirs = FD direction dirs[t] (all n_in inputs when dirs == nullptr); thread ndirs =
+// nominal evaluation. Columns outside the list are produced elsewhere (point_warp_local.cuh).
 __global__ void __launch_bounds__(256)
-k_points_fd(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ x, double* __restrict__ Y, double* __restrict__ J, int p0) {
+k_points_fd(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ x, double* __restrict__ Y, double* __restrict__ J, int p0,
+            const int* __restrict__ dirs, int ndirs) {
     extern __shared__ double sh_y0[]; // [n_out]
     const int j = p0 + blockIdx.x;
-    const int a = threadIdx.x;
+    const int tix = threadIdx.x;
+    const int a = tix < ndirs ? (dirs ? dirs[tix] : tix) : (tix == ndirs ? L.n_in : L.n_in + 1);
     double in[MOCOB200_MAX_IN];
     double ya[MOCOB200_MAX_OUT], yb[MOCOB200_MAX_OUT], Jc[MOCOB200_MAX_OUT];
     const bool active = a <= L.n_in;
@@ -415,11 +418,46 @@ void launch_points_nominal(const DevTables& T, const DevLayout& L, const double*
     const int bs = 32;
     k_points_nominal<<<(np + bs - 1) / bs, bs, 0, s>>>(T, L, d_x, d_Y, p0, np);
 }
+// Flat variant: one thread per (grid point, listed direction), nominal outputs read from Y (already evaluated). Every
+// lane of every warp carries an evaluation chain, so a short direction list still fills the machine in one wave.
+__global__ void __launch_bounds__(64)
+k_points_fd_flat(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ x, const double* __restrict__ Y, double* __restrict__ J,
+                 int p0, int np, const int* __restrict__ dirs, int ndirs) {
+    const long gid = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= (long)np * ndirs) return;
+    const int j = p0 + (int)(gid / ndirs);
+    const int a = dirs[gid % ndirs];
+    double in[MOCOB200_MAX_IN];
+    double ya[MOCOB200_MAX_OUT], yb[MOCOB200_MAX_OUT], Jc[MOCOB200_MAX_OUT];
+    gather_inputs(L, x, j, in);
+    const double* y0 = Y + (size_t)j * L.n_out;
+    if (fd.scheme != MOCOB200_FD_CENTRAL) {
+        fd_group([&](const double* xin, double* yout) { eval_point(T, xin, yout, 0xffffffffu); }, fd, in, a, y0, 0, L.n_out, yb, ya, Jc);
+    } else {
+        const int ngroups = 1 + L.n_integrand;
+        for (int gidx = 0; gidx < ngroups; ++gidx) {
+            const unsigned mask = 1u << gidx;
+            const int lo = gidx == 0 ? 0 : L.n_dyn_out + gidx - 1;
+            const int hi = gidx == 0 ? L.n_dyn_out : lo + 1;
+            fd_group([&](const double* xin, double* yout) { eval_point(T, xin, yout, mask); }, fd, in, a, y0, lo, hi, yb, ya, Jc);
+        }
+    }
+    double* Jp = J + (size_t)j * L.n_out * L.n_in;
+    for (int o = 0; o < L.n_out; ++o) Jp[(size_t)o * L.n_in + a] = Jc[o];
+}
+void launch_points_fd_flat(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, const double* d_Y, double* d_J,
+                           int p0, int np, cudaStream_t s, const int* d_dirs, int ndirs) {
+    const long n = (long)np * ndirs;
+    if (n <= 0) return;
+    k_points_fd_flat<<<(unsigned)((n + 63) / 64), 64, 0, s>>>(T, L, fd, d_x, d_Y, d_J, p0, np, d_dirs, ndirs);
+}
+
 void launch_points_fd(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, double* d_Y, double* d_J, int p0,
-                      int np, cudaStream_t s) {
+                      int np, cudaStream_t s, const int* d_dirs, int ndirs) {
     if (np <= 0) return;
-    const int bs = ((L.n_in + 1 + 31) / 32) * 32;
-    k_points_fd<<<np, bs, L.n_out * sizeof(double), s>>>(T, L, fd, d_x, d_Y, d_J, p0);
+    if (!d_dirs) ndirs = L.n_in;
+    const int bs = ((ndirs + 1 + 31) / 32) * 32;
+    k_points_fd<<<np, bs, L.n_out * sizeof(double), s>>>(T, L, fd, d_x, d_Y, d_J, p0, d_dirs, ndirs);
 }
 void launch_integrals(const DevLayout& L, const double* d_x, const double* d_Y, const double* d_J, double* d_I, bool withJ, cudaStream_t s) {
     if (L.n_integrand <= 0) return;

@@ -43,8 +43,16 @@ struct DevLayout {
 };
 
 void launch_points_nominal(const DevTables& T, const DevLayout& L, const double* d_x, double* d_Y, int p0, int np, cudaStream_t s);
+// d_dirs (device, may be null = all inputs): the FD directions this launch differences
 void launch_points_fd(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, double* d_Y, double* d_J,
-                      int p0, int np, cudaStream_t s);
+                      int p0, int np, cudaStream_t s, const int* d_dirs = nullptr, int ndirs = 0);
+// one thread per (grid point, listed direction); Y must already hold the nominal outputs
+void launch_points_fd_flat(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, const double* d_Y, double* d_J,
+                           int p0, int np, cudaStream_t s, const int* d_dirs, int ndirs);
+// the columns of the "local" inputs (point_warp_local.cuh) for callers that difference the other inputs with
+// launch_points_fd_flat: the local-column kernel on stream s; d_Y and the blobs in d_cfg come from launch_wpoints_nominal
+int launch_wlocal(const DevTables& T, const WarpAux& A, const DevLayout& L, const FdSettings& fd, const double* d_x, double* d_Y,
+                  double* d_J, double* d_cfg, int p0, int np, cudaStream_t s);
 // integrals[n_integrand], dIdt0[n_integrand], dIdtf[n_integrand] (derivative parts need J)
 void launch_integrals(const DevLayout& L, const double* d_x, const double* d_Y, const double* d_J, double* d_I, bool withJ, cudaStream_t s);
 // G[n_eout_total] values and E[n_eout_total][n_ein] FD blocks of every goal's endpoint function

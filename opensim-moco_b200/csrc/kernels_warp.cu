@@ -208,12 +208,12 @@ __global__ void k_wpoints_central(DevTables Tg, WarpAux Ag, DevLayout L, FdSetti
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long item = (long)blockIdx.x * (blockDim.x >> 5) + warp;
     const int ngroups = 1 + L.n_integrand;
-    const long per = (long)L.n_in * ngroups;
+    const long per = (long)A.n_cd * ngroups;
     if (item >= (long)np * per) return;
     double* ws = scratch + (size_t)warp * A.ws_doubles;
     const int j = p0 + (int)(item / per);
     const int rem = (int)(item % per);
-    const int dir = rem / ngroups, gidx = rem % ngroups;
+    const int dir = A.cd_dirs[rem / ngroups], gidx = rem % ngroups;
     const int lo = gidx == 0 ? 0 : L.n_dyn_out + gidx - 1;
     const int hi = gidx == 0 ? L.n_dyn_out : lo + 1;
     if (hi == lo) return;
@@ -260,6 +260,25 @@ __global__ void k_wpoints_central(DevTables Tg, WarpAux Ag, DevLayout L, FdSetti
     }
 }
 
+// columns of the local inputs under the central scheme: one warp per grid point, from the reloaded blob
+__global__ void k_wlocal_central(DevTables Tg, WarpAux Ag, DevLayout L, FdSettings fd, const double* __restrict__ x,
+                                 const double* __restrict__ Y, double* __restrict__ J, const double* __restrict__ cfg, int p0, int np) {
+    extern __shared__ double smem[];
+    DevTables T;
+    WarpAux A;
+    double* scratch = stage_tables(Tg, Ag, smem, T, A);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int item = blockIdx.x * (blockDim.x >> 5) + warp;
+    if (item >= np) return;
+    double* ws = scratch + (size_t)warp * A.ws_doubles;
+    const int j = p0 + item;
+    poison_scratch(A, ws, lane);
+    warp_gather_inputs(L, x, j, ws + A.o_in, lane);
+    blob_load(A, ws, cfg, j, lane, 2);
+    wk_local_columns_central(T, A, ws, ws + A.o_Rm, fd.h, fd.h_iter, fd.u_aim, fd.reltol, fd.abstol, J + (size_t)j * L.n_out * L.n_in,
+                             Y + (size_t)j * L.n_out, L.n_in, L.n_out);
+}
+
 // ---------------------------------------------------------------------------------------------
 static size_t smemBytesFor(const WarpAux& A, int warps) { return ((size_t)A.st_doubles + (size_t)warps * A.ws_doubles) * sizeof(double); }
 static size_t warpSmemBytes(const WarpAux& A) { return smemBytesFor(A, A.wpb); }
@@ -289,6 +308,7 @@ bool warp_kernels_configure(WarpAux& A, std::string& err) {
         (e = cudaFuncSetAttribute(k_wpoints_fd1<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
         (e = cudaFuncSetAttribute(k_wpoints_fd1<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
         (e = cudaFuncSetAttribute(k_wpoints_fd1<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_wlocal_central, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
         (e = cudaFuncSetAttribute(k_wpoints_central, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess) {
         err = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e);
         return false;
@@ -362,9 +382,34 @@ int launch_wpoints_fd(const DevTables& T, const WarpAux& A, const DevLayout& L, 
     }
     launch_wpoints_nominal(T, A, L, d_x, d_Y, d_cfg, p0, np, s);
     if (after_nominal) cudaEventRecord(after_nominal, s);
-    const long items = (long)np * L.n_in * (1 + L.n_integrand);
-    k_wpoints_central<<<(unsigned)((items + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
-    return 2;
+    int launched = 2;
+    const bool fork = A.n_local > 0 && side && side->s[0];
+    if (fork) {
+        cudaEventRecord(side->fork, s);
+        cudaStreamWaitEvent(side->s[0], side->fork, 0);
+        k_wlocal_central<<<(np + A.wpb - 1) / A.wpb, A.wpb * 32, warpSmemBytes(A), side->s[0]>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
+        cudaEventRecord(side->join[0], side->s[0]);
+        ++launched;
+    } else if (A.n_local > 0) {
+        k_wlocal_central<<<(np + A.wpb - 1) / A.wpb, A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
+        ++launched;
+    }
+    const long items = (long)np * A.n_cd * (1 + L.n_integrand);
+    if (items > 0)
+        k_wpoints_central<<<(unsigned)((items + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
+    if (fork) cudaStreamWaitEvent(s, side->join[0], 0);
+    return launched;
+}
+
+int launch_wlocal(const DevTables& T, const WarpAux& A, const DevLayout& L, const FdSettings& fd, const double* d_x, double* d_Y,
+                  double* d_J, double* d_cfg, int p0, int np, cudaStream_t s) {
+    if (np <= 0 || A.n_local <= 0) return 0;
+    // d_Y and the blobs in d_cfg come from launch_wpoints_nominal
+    if (fd.scheme == MOCOB200_FD_CENTRAL)
+        k_wlocal_central<<<(np + A.wpb - 1) / A.wpb, A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
+    else
+        k_wpoints_fd1<3><<<(np + A.wpb - 1) / A.wpb, A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
+    return 1;
 }
 
 } // namespace mocob200

@@ -45,8 +45,9 @@ struct WarpAux {
     //   p2_dirs: partial evaluations that reload poses and velocities (time, anything unclassified);
     //   loc_*:   inputs acting through one muscle / coordinate actuator, whose columns the nominal warp writes itself
     //            (point_warp_local.cuh); dir_class[dir] == 3 marks them for k_fd1_finalize.
-    int n_p0, n_p1, n_p2, n_local, time_integrands_only;
+    int n_p0, n_p1, n_p2, n_cd, n_local, time_integrands_only;
     const int* p0_dirs; const int* p1_dirs; const int* p2_dirs;
+    const int* cd_dirs; // every non-local direction (central scheme, thread-per-evaluation kernel)
     const int* loc_dir; const int* loc_kind; const int* loc_owner; const int* loc_role;
     const int* dir_class;
     int o_mlen, o_mspd, o_mout, o_Rm;

@@ -127,18 +127,37 @@ __device__ inline double wk_integrand_term_delta(const DevTables& T, const WarpA
     return d;
 }
 
-// The columns J[:, dir] of every "local" input of one grid point (whole warp; the scratch holds the nominal
-// evaluation or its reloaded blob, y0 its outputs, Rm is (nmus + ncact) * nq doubles of scratch that the evaluation no longer needs).
-__device__ inline void wk_local_columns(const DevTables& T, const WarpAux& A, double* ws, double* Rm, double h, bool forward,
-                                        double* __restrict__ Jp, const double* __restrict__ y0, int n_in, int n_out) {
-    const WarpCtx C{T, A, ws, (int)(threadIdx.x & 31)};
-    const int lane = C.lane, nq = T.nq, nz = T.nz, nc = T.nc;
+// Outputs of muscle m's own model with input `role` set to v (everything else nominal): tension, d(normalized tendon
+// force)/dt, equilibrium residual, activation rate.
+struct LocalMuscleEval { double F, nfDeriv, residual, actDot; };
+__device__ inline LocalMuscleEval wk_local_muscle(const DevTables& T, const WarpAux& A, const double* ws, int m, int role, double v) {
+    const int nq = T.nq;
     const double* in = ws + A.o_in;
     const double* z = in + 1 + 2 * nq;
-    const double* ctl = z + nz;
-    const double* auxder = ctl + nc + (T.implicit ? nq : 0);
-    // right-hand sides: unit tension of every muscle, unit control of every coordinate actuator
-    for (int r = lane; r < T.nmus + T.ncact; r += 32) {
+    const double* ctl = z + T.nz;
+    const double* auxder = ctl + T.nc + (T.implicit ? nq : 0);
+    const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
+    const double* md = T.dbl + T.o_mus_d + m * MOCOB200_MUS_DSTRIDE;
+    const int flags = mi[5];
+    double e = ctl[mi[2]], a = mi[3] >= 0 ? z[mi[3]] : NAN, ntf = mi[4] >= 0 ? z[mi[4]] : NAN, ntfd = mi[6] >= 0 ? auxder[mi[6]] : NAN;
+    if (role == MOCOB200_ROLE_CONTROL) e = v;
+    else if (role == MOCOB200_ROLE_ACTIVATION) a = v;
+    else if (role == MOCOB200_ROLE_TENDON_FORCE) ntf = v;
+    else ntfd = v;
+    const bool noActDyn = flags & MOCOB200_MUS_FLAG_IGNORE_ACTIVATION_DYNAMICS;
+    const MuscleOut o = dgf_muscle(md, flags, ws[A.o_mlen + m], ws[A.o_mspd + m], noActDyn ? e : a, ntf, ntfd, false);
+    LocalMuscleEval r;
+    r.F = o.tendonForce; r.nfDeriv = o.nfDeriv; r.residual = o.residual;
+    r.actDot = mi[3] >= 0 ? activation_dot(e, a, md[5], md[6]) : 0.0;
+    return r;
+}
+
+// right-hand sides of the local columns: M^-1 R_m (explicit) or R_m (implicit) per muscle, then per coordinate actuator
+__device__ inline void wk_local_rhs(const WarpCtx& C, double* Rm) {
+    const DevTables& T = C.T;
+    const WarpAux& A = C.A;
+    const int nq = T.nq;
+    for (int r = C.lane; r < T.nmus + T.ncact; r += 32) {
         double* x = Rm + r * nq;
         if (r < T.nmus) wk_unit_tension_force(C, r, x);
         else {
@@ -147,9 +166,105 @@ __device__ inline void wk_local_columns(const DevTables& T, const WarpAux& A, do
             for (int k = 0; k < nq; ++k) x[k] = 0.0;
             x[ai[0]] = T.dbl[T.o_cact_d + a * MOCOB200_CACT_DSTRIDE];
         }
-        if (!T.implicit) wk_ldlt_solve_lane(ws + A.o_M, nq, x);
+        if (!T.implicit) wk_ldlt_solve_lane(C.ws + A.o_M, nq, x);
     }
     __syncwarp();
+}
+
+// CasADi's central-difference step control for one output: accumulates u = max |et / er| (finite_differences of the
+// pinned fork, restated in kernels.cu fd_group); returns false when a value is not finite
+__device__ __forceinline__ bool fd_central_u(double vf, double vc, double vb, double h, double reltol, double abstol, double& u) {
+    if (!isfinite(vf) || !isfinite(vc) || !isfinite(vb)) return false;
+    const double et = vf - 2 * vc + vb;
+    const double er = reltol / h * fmax(fabs(vf - vc), fabs(vc - vb)) + abstol;
+    u = fmax(u, fabs(et / er));
+    return true;
+}
+
+// Central-difference version (CasADi's scheme with step refinement, one refinement loop per callback group as in the
+// reference: the dynamics group, then every integrand on its own). One lane per local input.
+__device__ inline void wk_local_columns_central(const DevTables& T, const WarpAux& A, double* ws, double* Rm, double h0, int h_iter,
+                                                double u_aim, double reltol, double abstol, double* __restrict__ Jp,
+                                                const double* __restrict__ y0, int n_in, int n_out) {
+    const WarpCtx C{T, A, ws, (int)(threadIdx.x & 31)};
+    const int lane = C.lane, nq = T.nq, nz = T.nz;
+    const double* in = ws + A.o_in;
+    wk_local_rhs(C, Rm);
+    for (int t = lane; t < A.n_local; t += 32) {
+        const int dir = A.loc_dir[t], kind = A.loc_kind[t], owner = A.loc_owner[t], role = A.loc_role[t];
+        const double x0 = in[dir];
+        double* col = Jp + dir;
+        for (int o = 0; o < n_out; ++o) col[(size_t)o * n_in] = 0.0;
+        const double* c = Rm + (kind == MOCOB200_LOCAL_MUSCLE ? owner : T.nmus + owner) * nq;
+        // ---- dynamics group
+        double h = h0;
+        for (int iter = 0;; ++iter) {
+            double u = 0;
+            bool ok = true;
+            if (kind == MOCOB200_LOCAL_ACTUATOR) {
+                const double vf = x0 + h, vb = x0 - h; // force = optimal_force * control; c carries optimal_force
+                for (int k = 0; k < nq; ++k) {
+                    ok = fd_central_u(c[k] * vf, c[k] * x0, c[k] * vb, h, reltol, abstol, u) && ok;
+                    col[(size_t)k * n_in] = (c[k] * vf - c[k] * vb) / (2 * h);
+                }
+            } else {
+                const int* mi = T.idx + T.o_mus_i + owner * MOCOB200_MUS_ISTRIDE;
+                const double* mo0 = ws + A.o_mout + 4 * owner;
+                const LocalMuscleEval f = wk_local_muscle(T, A, ws, owner, role, x0 + h), b = wk_local_muscle(T, A, ws, owner, role, x0 - h);
+                for (int k = 0; k < nq; ++k) {
+                    // udot_k(x) = udot_k(x0) + c_k (F(x) - F(x0)): difference the tension, then map
+                    ok = fd_central_u(c[k] * (f.F - mo0[0]), 0.0, c[k] * (b.F - mo0[0]), h, reltol, abstol, u) && ok;
+                    col[(size_t)k * n_in] = c[k] * ((f.F - b.F) / (2 * h));
+                }
+                if (mi[3] >= 0) {
+                    ok = fd_central_u(f.actDot, mo0[3], b.actDot, h, reltol, abstol, u) && ok;
+                    col[(size_t)(nq + mi[3]) * n_in] = (f.actDot - b.actDot) / (2 * h);
+                }
+                if (mi[4] >= 0) {
+                    ok = fd_central_u(f.nfDeriv, mo0[1], b.nfDeriv, h, reltol, abstol, u) && ok;
+                    col[(size_t)(nq + mi[4]) * n_in] = (f.nfDeriv - b.nfDeriv) / (2 * h);
+                }
+                if (mi[7] >= 0) {
+                    ok = fd_central_u(f.residual, mo0[2], b.residual, h, reltol, abstol, u) && ok;
+                    col[(size_t)(nq + nz + mi[7]) * n_in] = (f.residual - b.residual) / (2 * h);
+                }
+            }
+            if (iter == h_iter) break;
+            if (!ok) h /= u_aim;
+            else h *= sqrt(u_aim / fmax(1.0, u));
+        }
+        // ---- one group per integrand
+        int slot = 0;
+        for (int g = 0; g < T.ngoal; ++g) {
+            const int* gr = T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
+            if (!gr[3]) continue;
+            double hg = h0, jv = 0.0;
+            for (int iter = 0;; ++iter) {
+                const double df = wk_integrand_term_delta(T, A, ws, gr, dir, x0, x0 + hg), db = wk_integrand_term_delta(T, A, ws, gr, dir, x0, x0 - hg);
+                double u = 0;
+                const bool ok = fd_central_u(df, 0.0, db, hg, reltol, abstol, u);
+                jv = ok ? (df - db) / (2 * hg) : NAN;
+                if (iter == h_iter) break;
+                if (!ok) hg /= u_aim;
+                else hg *= sqrt(u_aim / fmax(1.0, u));
+            }
+            col[(size_t)(nq + nz + T.n_auxres + slot) * n_in] = jv;
+            ++slot;
+        }
+        for (int o = 0; o < n_out; ++o)
+            if (!isfinite(y0[o])) col[(size_t)o * n_in] = NAN;
+    }
+    __syncwarp();
+}
+
+// The columns J[:, dir] of every "local" input of one grid point (whole warp; the scratch holds the nominal
+// evaluation or its reloaded blob, y0 its outputs, Rm is (nmus + ncact) * nq doubles of scratch that the evaluation no longer needs).
+__device__ inline void wk_local_columns(const DevTables& T, const WarpAux& A, double* ws, double* Rm, double h, bool forward,
+                                        double* __restrict__ Jp, const double* __restrict__ y0, int n_in, int n_out) {
+    const WarpCtx C{T, A, ws, (int)(threadIdx.x & 31)};
+    const int lane = C.lane, nq = T.nq, nz = T.nz;
+    const double* in = ws + A.o_in;
+    wk_local_rhs(C, Rm);
     const double step = forward ? h : -h;
     for (int t = lane; t < A.n_local; t += 32) {
         const int dir = A.loc_dir[t], kind = A.loc_kind[t], owner = A.loc_owner[t], role = A.loc_role[t];
@@ -165,20 +280,11 @@ __device__ inline void wk_local_columns(const DevTables& T, const WarpAux& A, do
         } else {
             const int m = owner;
             const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
-            const double* md = T.dbl + T.o_mus_d + m * MOCOB200_MUS_DSTRIDE;
-            const int flags = mi[5];
-            double e = ctl[mi[2]], a = mi[3] >= 0 ? z[mi[3]] : NAN, ntf = mi[4] >= 0 ? z[mi[4]] : NAN, ntfd = mi[6] >= 0 ? auxder[mi[6]] : NAN;
-            const double length = ws[A.o_mlen + m], speed = ws[A.o_mspd + m];
-            const bool noActDyn = flags & MOCOB200_MUS_FLAG_IGNORE_ACTIVATION_DYNAMICS;
             const double* mo0 = ws + A.o_mout + 4 * m; // nominal tension, d(tendon force)/dt, residual, activation rate
-            if (role == MOCOB200_ROLE_CONTROL) e = v1;
-            else if (role == MOCOB200_ROLE_ACTIVATION) a = v1;
-            else if (role == MOCOB200_ROLE_TENDON_FORCE) ntf = v1;
-            else ntfd = v1;
-            const MuscleOut o1 = dgf_muscle(md, flags, length, speed, noActDyn ? e : a, ntf, ntfd, false);
-            const double dF = (o1.tendonForce - mo0[0]) * inv;
+            const LocalMuscleEval o1 = wk_local_muscle(T, A, ws, m, role, v1);
+            const double dF = (o1.F - mo0[0]) * inv;
             for (int k = 0; k < nq; ++k) col[(size_t)k * n_in] = c[k] * dF;
-            if (mi[3] >= 0) col[(size_t)(nq + mi[3]) * n_in] = (activation_dot(e, a, md[5], md[6]) - mo0[3]) * inv;
+            if (mi[3] >= 0) col[(size_t)(nq + mi[3]) * n_in] = (o1.actDot - mo0[3]) * inv;
             if (mi[4] >= 0) col[(size_t)(nq + mi[4]) * n_in] = (o1.nfDeriv - mo0[1]) * inv;
             if (mi[7] >= 0) col[(size_t)(nq + nz + mi[7]) * n_in] = (o1.residual - mo0[2]) * inv;
         }

@@ -152,6 +152,31 @@ def test_local_columns_equal_whole_function_differences(pkg, name, scheme, monke
     assert np.max(np.abs(J - J0) / scale) < 1e-8
 
 
+@pytest.mark.parametrize("name", FIXTURES)
+@pytest.mark.parametrize("kernel", ["warp", "thread"])
+def test_local_columns_central_scheme(pkg, name, kernel, monkeypatch):
+    """Central differences: factored local columns (with CasADi's step refinement applied to the factored values) against
+    whole-function central differences, fixed step (no refinement) so that both use the same h."""
+    monkeypatch.setenv("MOCOB200_KERNEL", kernel)
+    p = load(pkg, name)
+    x = p.make_iterate(seed=10, spread=0.4)
+    ev = pkg.Evaluator(p)
+    ev.set_fd(FD_CENTRAL, 1e-3, 0)
+    J = ev.eval_points(x, jacobian=True)
+    Y = ev.eval_points(x)
+    monkeypatch.setenv("MOCOB200_FD_LOCAL", "0")
+    ev0 = pkg.Evaluator(p)
+    ev0.set_fd(FD_CENTRAL, 1e-3, 0)
+    J0 = ev0.eval_points(x, jacobian=True)
+    scale = np.abs(Y)[:, :, None] + np.abs(J0) + 1e-300
+    assert np.max(np.abs(J - J0) / scale) < 1e-8
+    # default refinement: the refined steps differ (they are driven by round-off in the linear rows), the values agree
+    ev.set_fd(FD_CENTRAL)
+    ev0.set_fd(FD_CENTRAL)
+    Jr, Jr0 = ev.eval_points(x, jacobian=True), ev0.eval_points(x, jacobian=True)
+    assert np.max(np.abs(Jr - Jr0) / scale) < 1e-5
+
+
 def test_fd_structural_zeros_are_exact(pkg):
     """Perturbing an input that an output does not depend on must give an exactly zero difference (the evaluations that
     reuse the nominal poses / velocities are bit-identical to full ones): muscle excitations do not enter udot, and an
