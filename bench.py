@@ -250,16 +250,27 @@ def main():
         # roofline of the dominant kernel: this rank's share of the point-function FD work
         key = fixture[:-5]
         flops, fc = flop_per_jacobian(key, d, tr_fd, h_iter)
-        flops_rank = flops / world
+        eff = m.lib().mocob200_effective_world(d["n_grid"], world)  # ranks that own grid points
+        flops_rank = flops / eff
         peak = m.measure_fp64_peak(local_rank)
         achieved = flops_rank / (kern_ms * 1e-3) / 1e12
-        algo_bytes = 8.0 * (d["n_grid"] * (d["n_in"] + d["n_out"] + d["n_out"] * d["n_in"])) / world
+        algo_bytes = 8.0 * (d["n_grid"] * (d["n_in"] + d["n_out"] + d["n_out"] * d["n_in"])) / eff
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except Exception:
             pass
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        # DRAM bytes of the stage per launch from the committed `ncu --set full` capture of this workload (not measured live)
+        traffic, traffic_src = None, None
+        try:
+            nc = json.load(open(os.path.join(ROOT, "profiles", "ncu_r01_summary.json")))
+            pick = [v for k, v in nc.items() if ("k_wpoints_fd1" in k if args.workload == "config3" else ("k_points_fd_flat" in k or "k_wlocal_central" in k or "k_wpoints_nominal" in k))]
+            if pick and world == 1:
+                traffic = float(sum(v["dram__bytes_read.sum"] + v["dram__bytes_write.sum"] for v in pick))
+                traffic_src = "profiles/ncu_r01_summary.json: sum over the stage's kernels, one launch each"
+        except Exception:
+            pass
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
@@ -271,18 +282,22 @@ def main():
                               "buffer k %% %d of %.0f MB (L2 = 126 MB); no flush, code and model tables stay warm as in an IPOPT loop"
                               % (n_x, n_x * 8e-6 * d["n_var"], n_v, n_v * 8e-6 * d["nnz_jac"])) if args.l2 == "rotate" else
                              "256 MiB device fill between steps (outside the per-step CUDA events): cold code and tables",
-                       "point_evals_per_step": int(ev.point_evals_per_jacobian()), "sharding": "grid points / rank"},
+                       "point_evals_per_step": int(ev.point_evals_per_jacobian()),
+                       "sharding": "grid points over %d of %d rank(s) (a rank needs >= 384 grid points to be worth its launch + "
+                                   "gather latency, mocob200_effective_world); NCCL send/recv of x and of the per-point blocks" % (eff, world)},
             "clocks": clocks,
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": 8 * d["n_var"], "d2h_bytes_per_step": 8 * d["nnz_jac"],
                     "ms_per_step": e2e_ms / args.steps, "api": "mocob200_eval_jac_g(handle, x_host_pinned, values_host_pinned)"},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "fp64", "kernel": "k_points_fd", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+            "roofline": {"bound": "fp64", "kernel": "point-function FD stage: " + (
+                             "k_wpoints_fd1<0> then <1>,<2>,<3> side by side (warp per evaluation)" if ev.point_evals_per_jacobian() / eff <= 30000
+                             else "k_wpoints_nominal then k_points_fd_flat + k_wlocal_central side by side"), "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                          "frac": achieved / peak, "peak_source": "FP64 FMA saturation kernel measured in this process "
                          "(MEASURED_PEAKS.json has no FP64 entry)", "kernel_ms": kern_ms, "assemble_kernel_ms": asm_ms,
                          "flop_per_launch": flops_rank, "flop_per_point_eval": fc["all"]["flop"],
                          "hbm": {"achieved_gbs": algo_bytes / (kern_ms * 1e-3) / 1e9, "peak_gbs": hbm_peak,
                                  "frac": algo_bytes / (kern_ms * 1e-3) / 1e9 / hbm_peak, "algorithmic_bytes": algo_bytes},
-                         "traffic": None},
+                         "traffic": traffic, "traffic_source": traffic_src},
         }
         # CPU baseline leg (rank 0, N=1 only): the oracle on all host threads, bounded by --cpu-seconds
         if world == 1:

@@ -157,8 +157,13 @@ int mocob200_layout_structure(const mocob200_tables*, const mocob200_transcripti
  * about the midpoint (createRandomIterateWithinBounds, :1151-1177). */
 int mocob200_make_iterate(const mocob200_tables*, const mocob200_transcription*, long seed, double spread, double* x);
 
-/* Grid points [*p0, *p1) evaluated by `rank` of `world` (contiguous, every point owned by exactly one rank; the
- * reference's analogue is the split of the time indices over CasADi Map threads, CasOCTranscription.cpp:1179-1212).
+/* Number of ranks that actually get grid points: min(world, n_grid / 384) but at least 1 (MOCOB200_MIN_POINTS_PER_RANK
+ * overrides the 384) — a rank is only worth its launch + gather latency with about one wave of work; the remaining
+ * ranks idle (the reference caps its worker threads the same way, MocoCasADiSolver.cpp:127-143). */
+int mocob200_effective_world(int n_grid, int world);
+/* Grid points [*p0, *p1) evaluated by `rank` of `world` (contiguous, every point owned by exactly one rank, ranks >=
+ * mocob200_effective_world get the empty range; the reference's analogue is the split of the time indices over CasADi
+ * Map threads, CasOCTranscription.cpp:1179-1212).
  * Host only; mocob200_create uses the same rule, and rank r's rows of the per-point blocks Y[n_grid][n_out] /
  * J[n_grid][n_out][n_in] are gathered to rank 0 at offset *p0 * stride. */
 int mocob200_shard_range(int n_grid, int rank, int world, int* p0, int* p1);

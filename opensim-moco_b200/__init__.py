@@ -25,7 +25,7 @@ ABI_SYMBOLS = [
     "mocob200_set_fd", "mocob200_jac_g_structure", "mocob200_eval_points", "mocob200_eval_f", "mocob200_eval_g",
     "mocob200_eval_grad_f", "mocob200_eval_jac_g", "mocob200_eval_jac_g_device", "mocob200_eval_g_device",
     "mocob200_sync", "mocob200_mark", "mocob200_elapsed_ms", "mocob200_launch_count", "mocob200_last_kernel_ms",
-    "mocob200_point_evals_per_jacobian", "mocob200_measure_fp64_peak", "mocob200_shard_range",
+    "mocob200_point_evals_per_jacobian", "mocob200_measure_fp64_peak", "mocob200_shard_range", "mocob200_effective_world",
 ]
 
 
@@ -64,6 +64,7 @@ def lib():
         L.mocob200_layout_bounds.argtypes = [vp, vp, dp, dp, dp, dp]
         L.mocob200_layout_structure.argtypes = [vp, vp, ip, ip]
         L.mocob200_make_iterate.argtypes = [vp, vp, C.c_long, C.c_double, dp]
+        L.mocob200_effective_world.argtypes = [C.c_int, C.c_int]
         L.mocob200_shard_range.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.mocob200_create.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, C.POINTER(vp)]
         L.mocob200_nccl_unique_id.argtypes = [vp]

@@ -70,6 +70,7 @@ T* devUpload(const std::vector<T>& v) {
 struct mocob200_handle {
     std::string err;
     int device = 0, rank = 0, world = 1;
+    int eff = 1; // ranks that own grid points (mocob200_effective_world)
     Layout L;
     DevTables DT{};
     DevLayout DL{};
@@ -303,19 +304,23 @@ bool stageX(mocob200_handle* h, const double* x_host) {
     return true;
 }
 bool bcastX(mocob200_handle* h, const double* d_src) {
-    if (h->world > 1) {
-        if (!ncclOk(h, g_nccl.Broadcast(d_src, h->d_x, (size_t)h->L.n_var, kNcclDouble, 0, h->comm, h->stream), "ncclBroadcast")) return false;
-    } else if (d_src != h->d_x) {
+    if (h->rank == 0 && d_src != h->d_x) {
         if (!h->ck(cudaMemcpyAsync(h->d_x, d_src, sizeof(double) * h->L.n_var, cudaMemcpyDeviceToDevice, h->stream), "D2D x")) return false;
+    }
+    if (h->eff > 1 && h->rank < h->eff) { // only the ranks that own grid points need x
+        if (!ncclOk(h, g_nccl.GroupStart(), "ncclGroupStart")) return false;
+        if (h->rank == 0) for (int r = 1; r < h->eff; ++r) g_nccl.Send(h->d_x, (size_t)h->L.n_var, kNcclDouble, r, h->comm, h->stream);
+        else g_nccl.Recv(h->d_x, (size_t)h->L.n_var, kNcclDouble, 0, h->comm, h->stream);
+        if (!ncclOk(h, g_nccl.GroupEnd(), "ncclGroupEnd")) return false;
     }
     return true;
 }
 // gather per-point blocks (stride doubles per grid point) to rank 0
 bool gatherBlocks(mocob200_handle* h, double* d_buf, size_t stride) {
-    if (h->world == 1) return true;
+    if (h->eff == 1 || h->rank >= h->eff) return true;
     if (!ncclOk(h, g_nccl.GroupStart(), "ncclGroupStart")) return false;
     if (h->rank == 0) {
-        for (int r = 1; r < h->world; ++r) {
+        for (int r = 1; r < h->eff; ++r) {
             const size_t n = (size_t)(h->shard[r + 1] - h->shard[r]) * stride;
             if (n) g_nccl.Recv(d_buf + (size_t)h->shard[r] * stride, n, kNcclDouble, r, h->comm, h->stream);
         }
@@ -328,6 +333,7 @@ bool gatherBlocks(mocob200_handle* h, double* d_buf, size_t stride) {
 
 // stages shared by the pipelines; x must already be in d_x
 bool runNominal(mocob200_handle* h) {
+    if (h->rank >= h->eff) return true; // idle rank
     if (h->warpFor(h->p1 - h->p0)) launch_wpoints_nominal(h->DT, h->WA, h->DL, h->d_x, h->d_Y, nullptr, h->p0, h->p1 - h->p0, h->stream);
     else launch_points_nominal(h->DT, h->DL, h->d_x, h->d_Y, h->p0, h->p1 - h->p0, h->stream);
     h->launches++;
@@ -341,8 +347,9 @@ bool runNominal(mocob200_handle* h) {
 }
 bool runFd(mocob200_handle* h) {
     cudaEventRecord(h->ev[0], h->stream);
-    const bool overlap = h->world == 1; // single rank: Y is complete as soon as the nominal evaluations are
-    if (h->warpFor(mocob200_point_evals_per_jacobian(h) / h->world))
+    if (h->rank >= h->eff) { cudaEventRecord(h->ev[1], h->stream); return true; } // idle rank
+    const bool overlap = h->eff == 1; // single rank: Y is complete as soon as the nominal evaluations are
+    if (h->warpFor(mocob200_point_evals_per_jacobian(h) / h->eff))
         h->launches += launch_wpoints_fd(h->DT, h->WA, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_cfg, h->p0, h->p1 - h->p0, h->stream,
                                          overlap ? h->evY : nullptr, &h->side);
     else {
@@ -544,7 +551,8 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     for (int r = 0; r < world; ++r) { int a = 0, b = 0; mocob200_shard_range(L.n_grid, r, world, &a, &b); h->shard[r + 1] = b; }
     h->p0 = h->shard[rank];
     h->p1 = h->shard[rank + 1];
-    if (world > 1) {
+    h->eff = mocob200_effective_world(L.n_grid, world);
+    if (h->eff > 1) { // a communicator only when more than one rank owns grid points
         if (!nccl_unique_id) return fail(MOCOB200_ERR_ARG, "world > 1 needs a NCCL unique id");
         std::string e;
         if (!g_nccl.load(e)) return fail(MOCOB200_ERR_NCCL, e);
@@ -637,7 +645,7 @@ int mocob200_eval_f(mocob200_handle* h, const double* x, double* f, double* f_te
 int mocob200_eval_grad_f(mocob200_handle* h, const double* x, double* grad) {
     if (!h) return MOCOB200_ERR_ARG;
     cudaSetDevice(h->device);
-    const bool reuse = h->world == 1 && h->haveJ && sameX(h, x);
+    const bool reuse = h->eff == 1 && h->haveJ && sameX(h, x);
     if (!reuse) {
         if (!stageX(h, x) || !bcastX(h, h->d_x) || !runFd(h)) return MOCOB200_ERR_CUDA;
     }
@@ -665,7 +673,7 @@ static bool jacPipeline(mocob200_handle* h, double* d_vals) {
 int mocob200_eval_jac_g(mocob200_handle* h, const double* x, double* values) {
     if (!h) return MOCOB200_ERR_ARG;
     cudaSetDevice(h->device);
-    const bool reuse = h->world == 1 && h->haveJ && sameX(h, x);
+    const bool reuse = h->eff == 1 && h->haveJ && sameX(h, x);
     if (!reuse) {
         if (!stageX(h, x) || !bcastX(h, h->d_x)) return MOCOB200_ERR_CUDA;
         if (!jacPipeline(h, h->d_vals)) return MOCOB200_ERR_CUDA;

@@ -1,4 +1,5 @@
 // Host-only half of the C ABI: example problems, save/load of flattened problems, NLP layout.
+#include <cstdlib>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -196,10 +197,21 @@ int mocob200_make_iterate(const mocob200_tables* T, const mocob200_transcription
     } catch (const std::exception&) { return MOCOB200_ERR_UNSUPPORTED; }
 }
 
+int mocob200_effective_world(int n_grid, int world) {
+    // a rank is only worth its launch + gather latency when it gets a few hundred grid points (one wave of work)
+    int min_points = 384;
+    if (const char* e = getenv("MOCOB200_MIN_POINTS_PER_RANK")) { const int v = atoi(e); if (v > 0) min_points = v; }
+    int eff = n_grid / min_points;
+    if (eff < 1) eff = 1;
+    return eff < world ? eff : world;
+}
+
 int mocob200_shard_range(int n_grid, int rank, int world, int* p0, int* p1) {
     if (n_grid < 0 || world < 1 || rank < 0 || rank >= world || !p0 || !p1) return MOCOB200_ERR_ARG;
-    *p0 = (int)((long long)n_grid * rank / world);
-    *p1 = (int)((long long)n_grid * (rank + 1) / world);
+    const int eff = mocob200_effective_world(n_grid, world);
+    if (rank >= eff) { *p0 = *p1 = n_grid; return MOCOB200_OK; } // idle rank: small problems are not worth splitting
+    *p0 = (int)((long long)n_grid * rank / eff);
+    *p1 = (int)((long long)n_grid * (rank + 1) / eff);
     return MOCOB200_OK;
 }
 

@@ -21,6 +21,7 @@ def _free_port():
 
 
 def _worker(rank, world, port, fixture, opts, out_path):
+    os.environ["MOCOB200_MIN_POINTS_PER_RANK"] = "1"  # split even these small grids
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import ctypes as C
@@ -75,8 +76,11 @@ def test_sharded_point_blocks_gather_to_the_single_rank_result(pkg, orc, tmp_pat
     assert same == 1.0, "gathered blocks differ from the single-rank evaluation"
 
 
-def test_shard_ranges_tile_any_grid(pkg):
+def test_shard_ranges_tile_any_grid(pkg, monkeypatch):
     import ctypes as C
+
+    assert pkg.lib().mocob200_effective_world(101, 8) == 1 and pkg.lib().mocob200_effective_world(1601, 8) == 4
+    monkeypatch.setenv("MOCOB200_MIN_POINTS_PER_RANK", "1")
 
     for n_grid in (0, 1, 3, 20, 101, 1601):
         for world in (1, 2, 3, 4, 8):
@@ -85,9 +89,11 @@ def test_shard_ranges_tile_any_grid(pkg):
                 a, b = C.c_int(), C.c_int()
                 assert pkg.lib().mocob200_shard_range(n_grid, r, world, C.byref(a), C.byref(b)) == 0
                 edges.append((a.value, b.value))
+            eff = pkg.lib().mocob200_effective_world(n_grid, world)
+            assert 1 <= eff <= world
             assert edges[0][0] == 0 and edges[-1][1] == n_grid
             assert all(edges[i][1] == edges[i + 1][0] for i in range(world - 1))
             sizes = [b - a for a, b in edges]
-            assert max(sizes) - min(sizes) <= 1
+            assert max(sizes[:eff]) - min(sizes[:eff]) <= 1 and all(sz == 0 for sz in sizes[eff:])
     a, b = C.c_int(), C.c_int()
     assert pkg.lib().mocob200_shard_range(10, 2, 2, C.byref(a), C.byref(b)) != 0
