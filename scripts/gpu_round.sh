@@ -16,5 +16,5 @@ cat gpurun_out/${TAG}_bench.json gpurun_out/${TAG}_bench_config5.json
 # launch list (per-launch durations are cold-cache and serialised under ncu: shares, not absolutes)
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 3 --warmup 3 --cpu-seconds 0.3 > gpurun_out/${TAG}_ncu_launch.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_wpoints_fd1 -s 16 -c 4 -o gpurun_out/${TAG}_wfd1_full -f python bench.py --steps 3 --warmup 3 --cpu-seconds 0.3 > gpurun_out/${TAG}_ncu_full.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_points_fd -s 2 -c 1 -o gpurun_out/${TAG}_tfd_full -f python bench.py --steps 2 --warmup 3 --cpu-seconds 0.3 --workload config5 > gpurun_out/${TAG}_ncu_full5.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_points_fd_flat|k_wlocal_central|k_wpoints_nominal" -s 9 -c 3 -o gpurun_out/${TAG}_tfd_full -f python bench.py --steps 2 --warmup 3 --cpu-seconds 0.3 --workload config5 > gpurun_out/${TAG}_ncu_full5.log 2>&1
 ls -la gpurun_out | tail -30
