@@ -92,6 +92,9 @@ struct mocob200_handle {
     // beside the FD evaluations of the point functions
     cudaStream_t stream2 = nullptr;
     SideStreams side{};
+    cudaGraphExec_t jacGraph = nullptr; // captured Jacobian pipeline (d_x -> d_vals), rebuilt after mocob200_set_fd
+    long graphLaunches = 0;
+    bool graphFailed = false;
     cudaEvent_t evY = nullptr, evE = nullptr;
     double* d_I2 = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -332,6 +335,14 @@ bool gatherBlocks(mocob200_handle* h, double* d_buf, size_t stride) {
     return ncclOk(h, g_nccl.GroupEnd(), "ncclGroupEnd");
 }
 
+// stopwatch events also work inside a captured graph (as external event-record nodes)
+void recTiming(cudaEvent_t e, cudaStream_t s) {
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(s, &st);
+    if (st == cudaStreamCaptureStatusActive) cudaEventRecordWithFlags(e, s, cudaEventRecordExternal);
+    else cudaEventRecord(e, s);
+}
+
 // stages shared by the pipelines; x must already be in d_x
 bool runNominal(mocob200_handle* h) {
     if (h->rank >= h->eff) return true; // idle rank
@@ -347,8 +358,8 @@ bool runNominal(mocob200_handle* h) {
     return true;
 }
 bool runFd(mocob200_handle* h) {
-    cudaEventRecord(h->ev[0], h->stream);
-    if (h->rank >= h->eff) { cudaEventRecord(h->ev[1], h->stream); return true; } // idle rank
+    recTiming(h->ev[0], h->stream);
+    if (h->rank >= h->eff) { recTiming(h->ev[1], h->stream); return true; } // idle rank
     const bool overlap = h->eff == 1; // single rank: Y is complete as soon as the nominal evaluations are
     if (h->warpFor(mocob200_point_evals_per_jacobian(h) / h->eff))
         h->launches += launch_wpoints_fd(h->DT, h->WA, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_cfg, h->p0, h->p1 - h->p0, h->stream,
@@ -373,7 +384,7 @@ bool runFd(mocob200_handle* h) {
             if (overlap) cudaEventRecord(h->evY, h->stream);
         }
     }
-    cudaEventRecord(h->ev[1], h->stream);
+    recTiming(h->ev[1], h->stream);
     if (overlap) {
         cudaStreamWaitEvent(h->stream2, h->evY, 0);
         launch_integrals(h->DL, h->d_x, h->d_Y, h->d_J, h->d_I2, false, h->stream2);
@@ -426,6 +437,7 @@ void mocob200_destroy(mocob200_handle* h) {
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     for (void* p : h->owned) cudaFree(p);
     for (auto& e : h->ev) if (e) cudaEventDestroy(e);
+    if (h->jacGraph) cudaGraphExecDestroy(h->jacGraph);
     for (auto& st : h->side.s) if (st) cudaStreamDestroy(st);
     if (h->side.fork) cudaEventDestroy(h->side.fork);
     for (auto& e : h->side.join) if (e) cudaEventDestroy(e);
@@ -582,6 +594,7 @@ int mocob200_set_fd(mocob200_handle* h, int scheme, double step, int h_iter, dou
     if (step > 0) h->fd.h = step;
     if (h_iter >= 0) h->fd.h_iter = h_iter;
     if (u_aim > 0) h->fd.u_aim = u_aim;
+    if (h->jacGraph) { cudaSetDevice(h->device); cudaStreamSynchronize(h->stream); cudaGraphExecDestroy(h->jacGraph); h->jacGraph = nullptr; }
     h->x_cached.clear();
     return MOCOB200_OK;
 }
@@ -660,14 +673,44 @@ int mocob200_eval_grad_f(mocob200_handle* h, const double* x, double* grad) {
     return MOCOB200_OK;
 }
 
-static bool jacPipeline(mocob200_handle* h, double* d_vals) {
+static bool jacPipelineLaunches(mocob200_handle* h, double* d_vals) {
     if (!runFd(h)) return false;
     if (h->rank == 0) {
-        cudaEventRecord(h->ev[2], h->stream);
+        recTiming(h->ev[2], h->stream);
         launch_assemble_jac(h->DL, h->d_x, h->d_Y, h->d_J, h->d_I, h->d_E, d_vals, h->stream);
-        cudaEventRecord(h->ev[3], h->stream);
+        recTiming(h->ev[3], h->stream);
         h->launches++;
     }
+    return true;
+}
+// The Jacobian pipeline (FD kernels on three streams, integrals, endpoint functions, assembly: 8-9 launches and a dozen
+// event dependencies) is captured once per handle and FD setting into a CUDA graph that reads h->d_x and writes h->d_vals;
+// every later evaluation is one graph launch. Single-rank handles only (the NCCL gather stays outside graphs);
+// MOCOB200_GRAPH=0 or MOCOB200_TIMING=1 launches the kernels one by one.
+static bool jacPipeline(mocob200_handle* h, double* d_vals) {
+    static const bool allowGraph = !(getenv("MOCOB200_GRAPH") && getenv("MOCOB200_GRAPH")[0] == '0') && !getenv("MOCOB200_TIMING");
+    if (!allowGraph || h->eff != 1 || h->rank != 0 || h->graphFailed) return jacPipelineLaunches(h, d_vals);
+    if (!h->jacGraph) {
+        const long before = h->launches;
+        cudaGraph_t g = nullptr;
+        if (cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaGetLastError(); h->graphFailed = true; return jacPipelineLaunches(h, d_vals); }
+        const bool ok = jacPipelineLaunches(h, h->d_vals);
+        const cudaError_t e = cudaStreamEndCapture(h->stream, &g);
+        h->graphLaunches = h->launches - before;
+        h->launches = before;
+        if (!ok || e != cudaSuccess || !g || cudaGraphInstantiate(&h->jacGraph, g, 0) != cudaSuccess) {
+            cudaGetLastError();
+            if (g) cudaGraphDestroy(g);
+            h->jacGraph = nullptr;
+            h->graphFailed = true;
+            return jacPipelineLaunches(h, d_vals);
+        }
+        cudaGraphDestroy(g);
+    }
+    if (!h->ck(cudaGraphLaunch(h->jacGraph, h->stream), "cudaGraphLaunch")) return false;
+    h->launches += h->graphLaunches;
+    if (d_vals != h->d_vals &&
+        !h->ck(cudaMemcpyAsync(d_vals, h->d_vals, sizeof(double) * h->L.nnz, cudaMemcpyDeviceToDevice, h->stream), "D2D values")) return false;
     return true;
 }
 
