@@ -95,6 +95,7 @@ struct mocob200_handle {
     cudaGraphExec_t jacGraph = nullptr; // captured Jacobian pipeline (d_x -> d_vals), rebuilt after mocob200_set_fd
     long graphLaunches = 0;
     bool graphFailed = false;
+    bool allowGraph = true; // read at create: MOCOB200_GRAPH=0 or MOCOB200_TIMING=1 turn the graph off
     cudaEvent_t evY = nullptr, evE = nullptr;
     double* d_I2 = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -565,6 +566,7 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     h->p0 = h->shard[rank];
     h->p1 = h->shard[rank + 1];
     h->eff = mocob200_effective_world(L.n_grid, world);
+    h->allowGraph = !(getenv("MOCOB200_GRAPH") && getenv("MOCOB200_GRAPH")[0] == '0') && !getenv("MOCOB200_TIMING");
     if (h->eff > 1) { // a communicator only when more than one rank owns grid points
         if (!nccl_unique_id) return fail(MOCOB200_ERR_ARG, "world > 1 needs a NCCL unique id");
         std::string e;
@@ -688,8 +690,7 @@ static bool jacPipelineLaunches(mocob200_handle* h, double* d_vals) {
 // every later evaluation is one graph launch. Single-rank handles only (the NCCL gather stays outside graphs);
 // MOCOB200_GRAPH=0 or MOCOB200_TIMING=1 launches the kernels one by one.
 static bool jacPipeline(mocob200_handle* h, double* d_vals) {
-    static const bool allowGraph = !(getenv("MOCOB200_GRAPH") && getenv("MOCOB200_GRAPH")[0] == '0') && !getenv("MOCOB200_TIMING");
-    if (!allowGraph || h->eff != 1 || h->rank != 0 || h->graphFailed) return jacPipelineLaunches(h, d_vals);
+    if (!h->allowGraph || h->eff != 1 || h->rank != 0 || h->graphFailed) return jacPipelineLaunches(h, d_vals);
     if (!h->jacGraph) {
         const long before = h->launches;
         cudaGraph_t g = nullptr;

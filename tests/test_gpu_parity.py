@@ -177,6 +177,24 @@ def test_local_columns_central_scheme(pkg, name, kernel, monkeypatch):
     assert np.max(np.abs(Jr - Jr0) / scale) < 1e-5
 
 
+@pytest.mark.parametrize("name", ["gait2d_tracking", "hanging_muscle", "pendulum3_implicit"])
+def test_graph_replay_equals_kernel_by_kernel_launches(pkg, name, monkeypatch):
+    """The captured CUDA graph of the Jacobian pipeline, replayed on changing iterates and after a change of the FD
+    scheme, gives bit-identical values to launching the kernels one by one (MOCOB200_GRAPH=0)."""
+    p = load(pkg, name)
+    ev = pkg.Evaluator(p)
+    monkeypatch.setenv("MOCOB200_GRAPH", "0")
+    ev0 = pkg.Evaluator(p)
+    for scheme in (FD_FORWARD, FD_CENTRAL, FD_FORWARD):
+        ev.set_fd(scheme)
+        ev0.set_fd(scheme)
+        for seed in (21, 22, 23):
+            x = p.make_iterate(seed=seed, spread=0.3)
+            v, v0 = ev.eval_jac_g(x), ev0.eval_jac_g(x)
+            assert np.array_equal(v, v0, equal_nan=True)
+            assert np.array_equal(ev.eval_grad_f(x), ev0.eval_grad_f(x), equal_nan=True)
+
+
 def test_fd_structural_zeros_are_exact(pkg):
     """Perturbing an input that an output does not depend on must give an exactly zero difference (the evaluations that
     reuse the nominal poses / velocities are bit-identical to full ones): muscle excitations do not enter udot, and an
