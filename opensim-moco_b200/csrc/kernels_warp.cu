@@ -229,13 +229,13 @@ __global__ void k_wpoints_central(DevTables Tg, WarpAux Ag, DevLayout L, FdSetti
     double* Jp = J + (size_t)j * L.n_out * L.n_in;
     double h = fd.h;
     for (int iter = 0;; ++iter) {
-        if (lane == 0) ws[A.o_in + dir] = x0 - h;
-        __syncwarp();
-        warp_eval_point(T, A, ws, mask, reuse, dir == 0);
-        for (int o = lo + lane; o < hi; o += 32) yb[o] = yf[o];
-        if (lane == 0) ws[A.o_in + dir] = x0 + h;
-        __syncwarp();
-        warp_eval_point(T, A, ws, mask, reuse, dir == 0);
+#pragma unroll 1
+        for (int side = 0; side < 2; ++side) { // one copy of the evaluation code serves both sides
+            if (lane == 0) ws[A.o_in + dir] = side ? x0 + h : x0 - h;
+            __syncwarp();
+            warp_eval_point(T, A, ws, mask, reuse, dir == 0);
+            if (side == 0) for (int o = lo + lane; o < hi; o += 32) yb[o] = yf[o];
+        }
         double u = 0;
         bool bad = false;
         for (int o = lo + lane; o < hi; o += 32) {
