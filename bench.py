@@ -128,6 +128,9 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--workload", default="config3", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="CPU work budget of the cpu_baseline leg")
+    ap.add_argument("--sparsity", default="none", choices=["none", "random"],
+                    help="optim_sparsity_detection: none = dense callback blocks (the reference solver's default, the headline "
+                         "configuration); random = detected block sparsity (fewer CSC entries to assemble and copy back)")
     ap.add_argument("--l2", default="rotate", choices=["rotate", "flush"],
                     help="rotate: every step reads a different iterate out of a set larger than L2 and writes a different "
                          "output buffer (also > L2 in total); flush: 10 iterates, 256 MiB fill between steps (cold code too)")
@@ -166,6 +169,8 @@ def main():
     fixture, opts, desc = WORKLOADS[args.workload]
     prob = m.Problem.load(os.path.join(GOLD, fixture), opts)
     ev = m.Evaluator(prob, device=local_rank, rank=rank, world=world, nccl_id=nccl_id)
+    if args.sparsity != "none":
+        ev.set_sparsity_detection(args.sparsity)
     d = ev.dims.asdict()
     tr_fd = {"config3": 0, "config5": 1}[args.workload]
     ev.set_fd(tr_fd)
@@ -276,7 +281,7 @@ def main():
             "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": args.workload + ": " + desc, "n_grid": d["n_grid"], "n_var": d["n_var"], "n_con": d["n_con"],
-                       "nnz_jac": d["nnz_jac"], "fd": ["forward", "central", "backward"][tr_fd],
+                       "nnz_jac": d["nnz_jac"], "sparsity_detection": args.sparsity, "fd": ["forward", "central", "backward"][tr_fd],
                        "iterates": "%d seeded iterates, bounds midpoint + 0.1*U(-1,1)*half-range (mt19937_64 seeds 0-%d)" % (n_x, n_x - 1),
                        "l2": ("inputs larger than L2: step k reads iterate k %% %d out of %.0f MB of distinct iterates and writes CSC "
                               "buffer k %% %d of %.0f MB (L2 = 126 MB); no flush, code and model tables stay warm as in an IPOPT loop"

@@ -21,6 +21,7 @@
  *                                 CasOCTranscription.cpp:661-677)
  *   mocob200_eval_jac_g        <- nlp_jac_g (CasOCFunction.h:38-44 enable_fd/fd_method)
  *   mocob200_set_fd            <- optim_finite_difference_scheme (MocoCasADiSolver.cpp:255-257)
+ *   mocob200_set_sparsity_detection <- optim_sparsity_detection (CasOCFunction.cpp:25-105, CasOCSolver.cpp:71-87)
  *
  * Conventions: plain C, POD only, caller owns every buffer, every call returns an
  * int status (0 = ok), nothing throws across the boundary, NaN/Inf pass through.
@@ -179,6 +180,10 @@ const char* mocob200_last_error(const mocob200_handle*);
 int mocob200_get_dims(const mocob200_handle*, mocob200_dims*);
 int mocob200_set_fd(mocob200_handle*, int scheme, double h /*<=0: CasADi default*/, int h_iter /*<0 default*/,
                     double u_aim /*<=0 default 100*/);
+/* optim_sparsity_detection (MocoCasADiSolver.h:139-147; CasOCFunction.cpp:25-105): mode 0 = "none" (dense callback
+ * blocks, the default), 1 = "random" (block sparsity detected by perturbation at n_iterates random iterates within the
+ * bounds, <= 0: 3). Changes nnz_jac and the CSC structure: call before mocob200_jac_g_structure / mocob200_get_dims. */
+int mocob200_set_sparsity_detection(mocob200_handle*, int mode, int n_iterates);
 int mocob200_jac_g_structure(const mocob200_handle*, int* colptr, int* rowidx);
 /* x, outputs: HOST pointers (pinned or pageable). Full-size arrays on every rank;
  * after the call rank 0 holds the gathered result (all ranks for eval_f). */

@@ -25,7 +25,7 @@ ABI_SYMBOLS = [
     "mocob200_set_fd", "mocob200_jac_g_structure", "mocob200_eval_points", "mocob200_eval_f", "mocob200_eval_g",
     "mocob200_eval_grad_f", "mocob200_eval_jac_g", "mocob200_eval_jac_g_device", "mocob200_eval_g_device",
     "mocob200_sync", "mocob200_mark", "mocob200_elapsed_ms", "mocob200_launch_count", "mocob200_last_kernel_ms",
-    "mocob200_point_evals_per_jacobian", "mocob200_measure_fp64_peak", "mocob200_shard_range", "mocob200_effective_world",
+    "mocob200_point_evals_per_jacobian", "mocob200_measure_fp64_peak", "mocob200_shard_range", "mocob200_effective_world", "mocob200_set_sparsity_detection",
 ]
 
 
@@ -65,6 +65,7 @@ def lib():
         L.mocob200_layout_structure.argtypes = [vp, vp, ip, ip]
         L.mocob200_make_iterate.argtypes = [vp, vp, C.c_long, C.c_double, dp]
         L.mocob200_effective_world.argtypes = [C.c_int, C.c_int]
+        L.mocob200_set_sparsity_detection.argtypes = [vp, C.c_int, C.c_int]
         L.mocob200_shard_range.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.mocob200_create.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, C.POINTER(vp)]
         L.mocob200_nccl_unique_id.argtypes = [vp]
@@ -203,6 +204,14 @@ class Evaluator:
 
     def set_fd(self, scheme, h=-1.0, h_iter=-1, u_aim=-1.0):
         self._ck(lib().mocob200_set_fd(self._h, scheme, h, h_iter, u_aim), "set_fd")
+
+    def set_sparsity_detection(self, mode, n_iterates=0):
+        """mode "none" (dense callback blocks) or "random" (optim_sparsity_detection); changes nnz_jac and the structure."""
+        code = {"none": 0, "random": 1}[mode] if isinstance(mode, str) else int(mode)
+        self._ck(lib().mocob200_set_sparsity_detection(self._h, code, n_iterates), "set_sparsity_detection")
+        d = Dims()
+        lib().mocob200_get_dims(self._h, C.byref(d))
+        self.dims = d
 
     def structure(self):
         colptr, rowidx = np.empty(self.dims.n_var + 1, np.int32), np.empty(self.dims.nnz_jac, np.int32)

@@ -92,6 +92,11 @@ struct mocob200_handle {
     // beside the FD evaluations of the point functions
     cudaStream_t stream2 = nullptr;
     SideStreams side{};
+    // host copies of the problem (the layout is rebuilt when the sparsity detection mode changes)
+    std::vector<double> hostDbl, hostMesh;
+    std::vector<int> hostIdx;
+    mocob200_tables hostT{};
+    mocob200_transcription hostR{};
     cudaGraphExec_t jacGraph = nullptr; // captured Jacobian pipeline (d_x -> d_vals), rebuilt after mocob200_set_fd
     long graphLaunches = 0;
     bool graphFailed = false;
@@ -479,6 +484,11 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     if (L.n_integrand > 30) return fail(MOCOB200_ERR_UNSUPPORTED, "too many integrand goals");
 
     auto own = [&](void* p) { h->owned.push_back(p); return p; };
+    h->hostDbl.assign(T->dbl, T->dbl + T->n_dbl);
+    h->hostIdx.assign(T->idx, T->idx + T->n_int);
+    h->hostT = *T; h->hostT.dbl = h->hostDbl.data(); h->hostT.idx = h->hostIdx.data();
+    h->hostR = *R;
+    if (R->mesh) { h->hostMesh.assign(R->mesh, R->mesh + R->n_mesh); h->hostR.mesh = h->hostMesh.data(); }
     // tables
     DevTables& D = h->DT;
     std::vector<double> dbl(T->dbl, T->dbl + T->n_dbl);
@@ -597,6 +607,58 @@ int mocob200_set_fd(mocob200_handle* h, int scheme, double step, int h_iter, dou
     if (h_iter >= 0) h->fd.h_iter = h_iter;
     if (u_aim > 0) h->fd.u_aim = u_aim;
     if (h->jacGraph) { cudaSetDevice(h->device); cudaStreamSynchronize(h->stream); cudaGraphExecDestroy(h->jacGraph); h->jacGraph = nullptr; }
+    h->x_cached.clear();
+    return MOCOB200_OK;
+}
+
+// optim_sparsity_detection (MocoCasADiSolver.h:139-147): "none" = dense callback blocks; "random" = the per-callback block
+// sparsity found by perturbing every input (eps = 1e-5, entry kept when the output changes or is NaN) at random iterates
+// within the bounds, united over the iterates (CasOCFunction.cpp:25-105, CasOCSolver.cpp:71-87,
+// CasOCTranscription.cpp:1151-1177). The reference perturbs at the first time point of each iterate; here every grid
+// point of each iterate votes (a superset, so never fewer entries than the reference would keep).
+int mocob200_set_sparsity_detection(mocob200_handle* h, int mode, int n_iterates) {
+    if (!h || mode < 0 || mode > 1) return MOCOB200_ERR_ARG;
+    if (h->world != 1) { h->err = "sparsity detection is single-rank"; return MOCOB200_ERR_UNSUPPORTED; }
+    cudaSetDevice(h->device);
+    if (!finish(h, "set_sparsity_detection")) return MOCOB200_ERR_CUDA;
+    const Layout& L0 = h->L;
+    std::vector<unsigned char> mask;
+    if (mode == 1) {
+        if (n_iterates <= 0) n_iterates = 3;
+        mask.assign((size_t)L0.n_out * L0.n_in, 0);
+        const FdSettings keep = h->fd;
+        defaultFd(h->fd, MOCOB200_FD_FORWARD);
+        h->fd.h = 1e-5;
+        std::vector<double> x(L0.n_var), J((size_t)L0.n_grid * L0.n_out * L0.n_in);
+        bool ok = true;
+        for (int k = 0; k < n_iterates && ok; ++k) {
+            mocob200_make_iterate(&h->hostT, &h->hostR, k, 1.0, x.data());
+            ok = stageX(h, x.data()) && bcastX(h, h->d_x) && runFd(h) &&
+                 h->ck(cudaMemcpyAsync(J.data(), h->d_J, sizeof(double) * J.size(), cudaMemcpyDeviceToHost, h->stream), "D2H J") &&
+                 finish(h, "sparsity detection");
+            if (!ok) break;
+            const size_t blk = (size_t)L0.n_out * L0.n_in;
+            for (int j = 0; j < L0.n_grid; ++j)
+                for (size_t e = 0; e < blk; ++e) {
+                    const double v = J[(size_t)j * blk + e];
+                    if (v != 0.0 || v != v) mask[e] = 1;
+                }
+        }
+        h->fd = keep;
+        if (!ok) return MOCOB200_ERR_CUDA;
+    }
+    Layout L;
+    try {
+        L = buildLayout(h->hostT, h->hostR, true, mode == 1 ? mask.data() : nullptr);
+    } catch (const std::exception& e) { h->err = e.what(); return MOCOB200_ERR_UNSUPPORTED; }
+    h->L.colptr = L.colptr; h->L.rowidx = L.rowidx; h->L.nnzcol = L.nnzcol; h->L.nnz = L.nnz;
+    int* c = devUpload(L.colptr); int* r = devUpload(L.rowidx); int* n = devUpload(L.nnzcol);
+    double* v = devAlloc<double>(L.nnz);
+    if (!c || !r || !n || !v) { h->err = "device allocation failed"; return MOCOB200_ERR_CUDA; }
+    h->owned.push_back(c); h->owned.push_back(r); h->owned.push_back(n); h->owned.push_back(v);
+    h->DL.colptr = c; h->DL.rowidx = r; h->DL.nnzcol = n; h->DL.nnz = L.nnz;
+    h->d_vals = v;
+    if (h->jacGraph) { cudaGraphExecDestroy(h->jacGraph); h->jacGraph = nullptr; }
     h->x_cached.clear();
     return MOCOB200_OK;
 }

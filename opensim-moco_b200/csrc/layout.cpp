@@ -10,7 +10,7 @@ namespace {
 inline const int* goalRec(const mocob200_tables& T, int g) { return T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE; }
 }
 
-Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bool withStructure) {
+Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bool withStructure, const unsigned char* blockMask) {
     Layout L{};
     L.scheme = R.scheme;
     L.implicit = R.dynamics_mode == MOCOB200_DYNAMICS_IMPLICIT;
@@ -114,11 +114,15 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
     for (int g = 0; g < T.ngoal; ++g)
         if (L.goal_row[g] >= 0 && goalRec(T, g)[3]) { ecHasInt[g] = 1; anyGoalIntegrandEC = true; }
     (void)anyGoalIntegrandEC;
+    // does output row `o` of the point function depend on its input `in`?
+    auto maskAt = [&](int o, int in) -> bool { return !blockMask || blockMask[(size_t)o * L.n_in + in] != 0; };
+    // output row of residual row o of a grid point (same mapping as RowMeta above)
+    auto residOutRow = [&](int o) { return (L.implicit && o < L.nq) ? o : L.nq + L.nz + (o - (L.implicit ? L.nq : 0)); };
     // does xdot_s (state s) at a point depend on input `in` of the same point?
     auto xdotDepends = [&](int s, const ColMeta& c) -> bool {
         if (s < L.nq) return c.kind == COL_STATE && c.k == L.nq + s; // qdot = u
         if (s < 2 * L.nq && L.implicit) return c.kind == COL_DERIV && c.k == s - L.nq; // udot = w
-        return true; // dense callback block
+        return maskAt(s - L.nq, c.in); // the callback block: dense unless a detected mask is given
     };
     L.colptr.assign(L.n_var + 1, 0);
     L.rowidx.clear();
@@ -131,16 +135,19 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
             for (int r = 0; r < L.n_endpoint_rows; ++r) emit(col, r);
             for (int m = 0; m < L.n_intervals; ++m) {
                 for (int k = 0; k < ppi; ++k)
-                    for (int o = 0; o < L.n_resid_rows_per_point; ++o) emit(col, L.row_resid[ppi * m + k] + o);
-                for (int o = 0; o < L.n_defect_rows; ++o) emit(col, L.row_defect[m] + o);
+                    for (int o = 0; o < L.n_resid_rows_per_point; ++o)
+                        if (maskAt(residOutRow(o), 0)) emit(col, L.row_resid[ppi * m + k] + o); // through the time input
+                for (int o = 0; o < L.n_defect_rows; ++o) emit(col, L.row_defect[m] + o);      // through h, always
             }
-            for (int o = 0; o < L.n_resid_rows_per_point; ++o) emit(col, L.row_resid[L.n_grid - 1] + o);
+            for (int o = 0; o < L.n_resid_rows_per_point; ++o)
+                if (maskAt(residOutRow(o), 0)) emit(col, L.row_resid[L.n_grid - 1] + o);
             continue;
         }
         const int j = c.point;
         for (int g = 0; g < T.ngoal; ++g) {
             if (L.goal_row[g] < 0) continue;
-            if (j == 0 || j == L.n_grid - 1 || ecHasInt[g])
+            const bool viaIntegral = ecHasInt[g] && maskAt(L.n_dyn_out + L.goal_integrand[g], c.in);
+            if (j == 0 || j == L.n_grid - 1 || viaIntegral)
                 for (int o = 0; o < goalRec(T, g)[2]; ++o) emit(col, L.goal_row[g] + o);
         }
         // intervals that contain grid point j, ascending
@@ -158,7 +165,8 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
         for (int t = 0; t < nm; ++t) {
             const int m = ms[t], role = roles[t];
             if (role != 2) // residual rows of j sit in the block of the interval that starts at / contains j
-                for (int o = 0; o < L.n_resid_rows_per_point; ++o) emit(col, L.row_resid[j] + o);
+                for (int o = 0; o < L.n_resid_rows_per_point; ++o)
+                    if (maskAt(residOutRow(o), c.in)) emit(col, L.row_resid[j] + o);
             for (int s = 0; s < L.ns; ++s) {
                 const bool dep = xdotDepends(s, c);
                 const bool direct = c.kind == COL_STATE && c.k == s;
@@ -179,7 +187,8 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
             if (L.n_interp_rows && c.kind == COL_CONTROL) emit(col, L.row_interp[m] + c.k);
         }
         if (j == L.n_grid - 1)
-            for (int o = 0; o < L.n_resid_rows_per_point; ++o) emit(col, L.row_resid[j] + o);
+            for (int o = 0; o < L.n_resid_rows_per_point; ++o)
+                if (maskAt(residOutRow(o), c.in)) emit(col, L.row_resid[j] + o);
     }
     L.colptr[L.n_var] = (int)L.rowidx.size();
     L.nnz = (int)L.rowidx.size();

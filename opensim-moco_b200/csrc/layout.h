@@ -37,7 +37,11 @@ struct Layout {
     int n_ein;
 };
 
-Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bool withStructure);
+// blockMask (may be null = dense callback blocks): [n_out][n_in] flags, non-zero where the point function's output row
+// depends on its input (the per-callback Jacobian sparsity of optim_sparsity_detection = "random",
+// CasOCFunction.cpp:25-105); the structure then holds only the entries CasADi's sparsity propagation would keep.
+Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bool withStructure,
+                   const unsigned char* blockMask = nullptr);
 void layoutBounds(const mocob200_tables& T, const mocob200_transcription& R, const Layout& L, double* xlo, double* xhi,
                   double* glo, double* ghi);
 

@@ -195,6 +195,41 @@ def test_graph_replay_equals_kernel_by_kernel_launches(pkg, name, monkeypatch):
             assert np.array_equal(ev.eval_grad_f(x), ev0.eval_grad_f(x), equal_nan=True)
 
 
+@pytest.mark.parametrize("name", ["gait2d_tracking", "gait2d_prediction", "hanging_muscle", "pendulum3_implicit", "sliding_mass"])
+def test_random_sparsity_detection_keeps_every_nonzero(pkg, name):
+    """optim_sparsity_detection = "random" (CasOCFunction.cpp:25-105): the detected structure is a subset of the dense-
+    block structure, the surviving entries carry bit-identical values, and every dropped entry is exactly zero."""
+    p = load(pkg, name)
+    ev = pkg.Evaluator(p)
+    colptr, rowidx = ev.structure()
+    n_var, n_con = ev.dims.n_var, ev.dims.n_con
+    cols = np.repeat(np.arange(n_var), np.diff(colptr))
+    key = cols.astype(np.int64) * n_con + rowidx
+    xs = [p.make_iterate(seed=s, spread=sp) for s, sp in ((31, 0.2), (32, 0.6), (33, 1.0))]
+    dense = [ev.eval_jac_g(x) for x in xs]
+    g = [ev.eval_g(x) for x in xs]
+    ev.set_sparsity_detection("random")
+    c2, r2 = ev.structure()
+    assert ev.dims.nnz_jac == r2.size <= rowidx.size
+    cols2 = np.repeat(np.arange(n_var), np.diff(c2))
+    key2 = cols2.astype(np.int64) * n_con + r2
+    assert np.all(np.diff(key2) > 0), "CSC order: columns ascending, rows ascending inside a column"
+    pos = np.searchsorted(key, key2)
+    assert np.array_equal(key[pos], key2), "detected structure is not a subset of the dense-block structure"
+    dropped = np.ones(key.size, bool)
+    dropped[pos] = False
+    for x, vd, gd in zip(xs, dense, g):
+        vs = ev.eval_jac_g(x)
+        assert np.array_equal(vs, vd[pos], equal_nan=True)
+        assert np.all(vd[dropped] == 0.0)
+        assert np.array_equal(ev.eval_g(x), gd)
+    if name.startswith("gait2d"):
+        assert r2.size < 0.8 * rowidx.size  # the muscle blocks are far from dense
+    ev.set_sparsity_detection("none")
+    c3, r3 = ev.structure()
+    assert np.array_equal(c3, colptr) and np.array_equal(r3, rowidx)
+
+
 def test_fd_structural_zeros_are_exact(pkg):
     """Perturbing an input that an output does not depend on must give an exactly zero difference (the evaluations that
     reuse the nominal poses / velocities are bit-identical to full ones): muscle excitations do not enter udot, and an
