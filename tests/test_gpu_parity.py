@@ -305,6 +305,31 @@ def test_nonuniform_mesh(pkg, orc):
     assert abs(ev.eval_f(x) - o.eval_f(x)) < 1e-10 * max(1, abs(o.eval_f(x)))
 
 
+# ---- BASELINE config 3 at its full size (50 intervals, 101 grid points): everything against the oracle ------------------
+def test_config3_full_size_against_oracle(pkg, orc):
+    p = pkg.Problem.load(golden("gait2d_tracking.mb20"))
+    ev, o = pkg.Evaluator(p), orc.Oracle(p)
+    assert (ev.dims.n_grid, ev.dims.n_var, ev.dims.n_con, ev.dims.nnz_jac) == (101, 5759, 4788, 420258)
+    c, r = ev.structure()
+    co, ro = o.structure()
+    assert np.array_equal(c, co) and np.array_equal(r, ro)
+    for seed, spread in ((41, 0.1), (42, 0.4)):
+        x = p.make_iterate(seed=seed, spread=spread)
+        assert relerr(ev.eval_points(x), o.eval_points(x)) < 1e-10
+        assert relerr(ev.eval_g(x), o.eval_g(x)) < 1e-10
+        assert abs(ev.eval_f(x) - o.eval_f(x)) <= 1e-10 * max(1.0, abs(o.eval_f(x)))
+        ev.set_fd(FD_FORWARD, 1e-4, 0)
+        o.set_fd(FD_FORWARD, 1e-4, 0)
+        assert rowscaled_err(ev.eval_jac_g(x), o.eval_jac_g(x), ro, o.n_con) < 5e-7
+        ev.set_fd(FD_FORWARD)  # CasADi's default step, as the example uses: noise-model bound
+        o.set_fd(FD_FORWARD)
+        v, vo = ev.eval_jac_g(x), o.eval_jac_g(x)
+        assert rowscaled_err(v, vo, ro, o.n_con) < 2e-3
+        rowmax = np.zeros(o.n_con)
+        np.maximum.at(rowmax, ro, np.abs(vo))
+        assert np.median(np.abs(v - vo) / (np.abs(vo) + rowmax[ro] + 1e-300)) < 1e-8
+
+
 # ---- full-size (BASELINE.json) properties that need no oracle run ---------------------------------------------
 @pytest.fixture(scope="module")
 def config5(pkg):
