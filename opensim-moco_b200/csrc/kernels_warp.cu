@@ -320,7 +320,15 @@ bool warp_kernels_configure(WarpAux& A, std::string& err) {
 void launch_wpoints_nominal(const DevTables& T, const WarpAux& A, const DevLayout& L, const double* d_x, double* d_Y, double* d_cfg,
                             int p0, int np, cudaStream_t s) {
     if (np <= 0) return;
+    static const bool timing = getenv("MOCOB200_TIMING") != nullptr; // development stopwatch
+    static cudaEvent_t ne[2] = {nullptr, nullptr};
+    if (timing) {
+        if (!ne[0]) { cudaEventCreate(&ne[0]); cudaEventCreate(&ne[1]); }
+        else { float a = 0; if (cudaEventElapsedTime(&a, ne[0], ne[1]) == cudaSuccess) fprintf(stderr, "[mocob200 timing] nominal %.1f us (%d points)\n", 1e3 * a, np); }
+        cudaEventRecord(ne[0], s);
+    }
     k_wpoints_nominal<<<(np + A.wpb - 1) / A.wpb, A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, d_x, d_Y, d_cfg, p0, np);
+    if (timing) cudaEventRecord(ne[1], s);
 }
 // returns the number of kernels launched
 int launch_wpoints_fd(const DevTables& T, const WarpAux& A, const DevLayout& L, const FdSettings& fd, const double* d_x, double* d_Y,
