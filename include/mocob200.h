@@ -53,8 +53,12 @@ enum { MOCOB200_GOAL_CONTROL = 0, MOCOB200_GOAL_STATE_TRACKING = 1,
        MOCOB200_GOAL_CONTACT_TRACKING = 2, MOCOB200_GOAL_FINAL_TIME = 3,
        MOCOB200_GOAL_AVERAGE_SPEED = 4, MOCOB200_GOAL_PERIODICITY = 5,
        MOCOB200_GOAL_INITIAL_ACTIVATION = 6, MOCOB200_GOAL_INITIAL_VELOCITY_EQUILIBRIUM_DGF = 7,
-       MOCOB200_GOAL_SUM_SQUARED_STATE = 8, MOCOB200_GOAL_CONTROL_TRACKING = 9 };
-enum { MOCOB200_MODE_COST = 0, MOCOB200_MODE_ENDPOINT_CONSTRAINT = 1 };
+       MOCOB200_GOAL_SUM_SQUARED_STATE = 8, MOCOB200_GOAL_CONTROL_TRACKING = 9,
+       /* path constraints (Moco/Moco/MocoConstraint.h) share the goal record; their mode is MOCOB200_MODE_PATH_CONSTRAINT */
+       MOCOB200_PATHCON_CONTROL_BOUND = 10 /* MocoControlBoundConstraint.cpp:121-148 */ };
+/* MODE_PATH_CONSTRAINT: n_outputs equations evaluated at every mesh point (CasOCTranscription.cpp:414-432); rows sit in
+ * front of the mesh point's residual rows (CasOCTranscription.h:279-283). */
+enum { MOCOB200_MODE_COST = 0, MOCOB200_MODE_ENDPOINT_CONSTRAINT = 1, MOCOB200_MODE_PATH_CONSTRAINT = 2 };
 enum { MOCOB200_SCHEME_TRAPEZOIDAL = 0, MOCOB200_SCHEME_HERMITE_SIMPSON = 1 };
 enum { MOCOB200_DYNAMICS_EXPLICIT = 0, MOCOB200_DYNAMICS_IMPLICIT = 1 };
 enum { MOCOB200_FD_FORWARD = 0, MOCOB200_FD_CENTRAL = 1, MOCOB200_FD_BACKWARD = 2 };
@@ -78,6 +82,8 @@ enum { MOCOB200_POINTS_OUTPUTS = 0 /* [n_grid][n_out] */, MOCOB200_POINTS_JACOBI
 #define MOCOB200_CACT_ISTRIDE 2     /* speed index u | control */
 #define MOCOB200_SPLINE_ISTRIDE 3   /* first knot offset (into dbl, relative to o_spline_data) | n knots | 0 */
 #define MOCOB200_GOAL_ISTRIDE 8     /* kind | mode | n_outputs | has_integrand | ioff (into idx) | doff (into dbl) | ni | nd */
+/* payload of MOCOB200_PATHCON_CONTROL_BOUND: idx = n_eq x { control | ppoly id of the bound function } ;
+ * dbl = weight(1) 0 0 | n_eq x { lower, upper } (bounds of the equation control - bound(t)) */
 #define MOCOB200_PPOLY_ISTRIDE 3    /* first break offset (rel. o_ppoly_data) | n pieces | order (coeffs per piece) */
 
 /* A fixed-topology model + optimal control problem flattened into two pools.

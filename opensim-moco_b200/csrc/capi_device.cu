@@ -616,6 +616,20 @@ int mocob200_set_fd(mocob200_handle* h, int scheme, double step, int h_iter, dou
 // within the bounds, united over the iterates (CasOCFunction.cpp:25-105, CasOCSolver.cpp:71-87,
 // CasOCTranscription.cpp:1151-1177). The reference perturbs at the first time point of each iterate; here every grid
 // point of each iterate votes (a superset, so never fewer entries than the reference would keep).
+// host copy of ppoly_eval (point_eval.cuh) for the set-up time sparsity probe of the path constraints
+static double hostPPoly(const mocob200_tables& T, int id, double t) {
+    const int* rec = T.idx + T.o_ppoly_i + id * MOCOB200_PPOLY_ISTRIDE;
+    const int np = rec[1], order = rec[2];
+    const double* br = T.dbl + T.o_ppoly_data + rec[0];
+    const double* co = br + np + 1;
+    int k = 0;
+    while (k + 1 < np && t >= br[k + 1]) ++k;
+    const double s = t - br[k];
+    double v = co[(size_t)k * order + order - 1];
+    for (int j = order - 2; j >= 0; --j) v = v * s + co[(size_t)k * order + j];
+    return v;
+}
+
 int mocob200_set_sparsity_detection(mocob200_handle* h, int mode, int n_iterates) {
     if (!h || mode < 0 || mode > 1) return MOCOB200_ERR_ARG;
     if (h->world != 1) { h->err = "sparsity detection is single-rank"; return MOCOB200_ERR_UNSUPPORTED; }
@@ -625,7 +639,7 @@ int mocob200_set_sparsity_detection(mocob200_handle* h, int mode, int n_iterates
     std::vector<unsigned char> mask;
     if (mode == 1) {
         if (n_iterates <= 0) n_iterates = 3;
-        mask.assign((size_t)L0.n_out * L0.n_in, 0);
+        mask.assign((size_t)(L0.n_out + L0.n_path_rows) * L0.n_in, 0);
         const FdSettings keep = h->fd;
         defaultFd(h->fd, MOCOB200_FD_FORWARD);
         h->fd.h = 1e-5;
@@ -643,6 +657,21 @@ int mocob200_set_sparsity_detection(mocob200_handle* h, int mode, int n_iterates
                     const double v = J[(size_t)j * blk + e];
                     if (v != 0.0 || v != v) mask[e] = 1;
                 }
+            // path-constraint callbacks: same perturbation test at the iterate's first time point (CasOCFunction.cpp:25-74)
+            const mocob200_tables& T = h->hostT;
+            for (int g = 0; g < T.ngoal; ++g) {
+                if (L0.goal_path_off[g] < 0) continue;
+                const int* gr = T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
+                const int* ip = T.idx + gr[4];
+                for (int e = 0; e < gr[2]; ++e) {
+                    unsigned char* row = mask.data() + (size_t)(L0.n_out + L0.goal_path_off[g] + e) * L0.n_in;
+                    const double u = x[L0.off_controls + ip[2 * e]], b0 = hostPPoly(T, ip[2 * e + 1], x[0]);
+                    const double dt = (u - hostPPoly(T, ip[2 * e + 1], x[0] + 1e-5)) - (u - b0);
+                    const double du = ((u + 1e-5) - b0) - (u - b0);
+                    if (dt != 0.0 || dt != dt) row[0] = 1;
+                    if (du != 0.0 || du != du) row[1 + L0.ns + ip[2 * e]] = 1;
+                }
+            }
         }
         h->fd = keep;
         if (!ok) return MOCOB200_ERR_CUDA;
@@ -693,7 +722,7 @@ int mocob200_eval_g(mocob200_handle* h, const double* x, double* g) {
     cudaSetDevice(h->device);
     if (!stageX(h, x) || !bcastX(h, h->d_x) || !runNominal(h)) return MOCOB200_ERR_CUDA;
     if (h->rank == 0) {
-        launch_assemble_g(h->DL, h->d_x, h->d_Y, h->d_G, h->d_g, h->stream);
+        launch_assemble_g(h->DT, h->DL, h->d_x, h->d_Y, h->d_G, h->d_g, h->stream);
         h->launches++;
         if (g) cudaMemcpyAsync(g, h->d_g, sizeof(double) * h->L.n_con, cudaMemcpyDeviceToHost, h->stream);
     }
@@ -741,7 +770,7 @@ static bool jacPipelineLaunches(mocob200_handle* h, double* d_vals) {
     if (!runFd(h)) return false;
     if (h->rank == 0) {
         recTiming(h->ev[2], h->stream);
-        launch_assemble_jac(h->DL, h->d_x, h->d_Y, h->d_J, h->d_I, h->d_E, d_vals, h->stream);
+        launch_assemble_jac(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_I, h->d_E, d_vals, h->stream);
         recTiming(h->ev[3], h->stream);
         h->launches++;
     }
@@ -785,7 +814,7 @@ int mocob200_eval_jac_g(mocob200_handle* h, const double* x, double* values) {
         if (!stageX(h, x) || !bcastX(h, h->d_x)) return MOCOB200_ERR_CUDA;
         if (!jacPipeline(h, h->d_vals)) return MOCOB200_ERR_CUDA;
     } else {
-        launch_assemble_jac(h->DL, h->d_x, h->d_Y, h->d_J, h->d_I, h->d_E, h->d_vals, h->stream);
+        launch_assemble_jac(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_I, h->d_E, h->d_vals, h->stream);
         h->launches++;
     }
     if (h->rank == 0 && values)
@@ -811,7 +840,7 @@ int mocob200_eval_g_device(mocob200_handle* h, const double* d_x, double* d_g, v
     (void)cuda_stream;
     h->x_cached.clear();
     if (!bcastX(h, d_x) || !runNominal(h)) return MOCOB200_ERR_CUDA;
-    if (h->rank == 0) { launch_assemble_g(h->DL, h->d_x, h->d_Y, h->d_G, d_g ? d_g : h->d_g, h->stream); h->launches++; }
+    if (h->rank == 0) { launch_assemble_g(h->DT, h->DL, h->d_x, h->d_Y, h->d_G, d_g ? d_g : h->d_g, h->stream); h->launches++; }
     return h->ck(cudaGetLastError(), "eval_g_device") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
 }
 

@@ -169,6 +169,57 @@ std::unique_ptr<FlatProblem> pendulum(int n, const std::string& options) {
     return flatten(P, S);
 }
 
+// The three solvable sections of TEMPLATE_TEST_CASE("MocoControlBoundConstraint") (Moco/Tests/testConstraints.cpp:1458-1541)
+// on ModelFactory::createPendulum(): which = "lower" | "upper" | "equality" | "both" (lower and upper, this repo's own case).
+std::unique_ptr<FlatProblem> pendulumControlBound(const std::string& which, const std::string& options) {
+    Problem P;
+    ModelSpec& M = P.model;
+    M.name = "pendulum";
+    BodySpec b;
+    b.name = "b0";
+    b.mass = 1;
+    b.inertiaCom[0] = b.inertiaCom[1] = b.inertiaCom[2] = 1;
+    M.bodies.push_back(b);
+    JointSpec j;
+    j.name = "j0";
+    j.kind = MOCOB200_JOINT_PIN;
+    j.parent.body = -1;
+    j.child.body = 0;
+    j.child.X.p.v[0] = -1;
+    j.coords.push_back({"q0", -10, 10});
+    M.joints.push_back(j);
+    CoordActSpec a;
+    a.path = "/tau0";
+    a.coord = "q0";
+    M.coordActs.push_back(a);
+    M.actuatorOrder.emplace_back(0, 0);
+    if (which == "upper") {
+        P.setTimeBounds(Bounds(0), Bounds(0.1, 10));
+        P.setStateInfo("/jointset/j0/q0/value", Bounds(0, 1), Bounds(0), Bounds(0.53));
+        P.setStateInfo("/jointset/j0/q0/speed", Bounds(-10, 10), Bounds(0), Bounds(0));
+        P.setControlInfo("/tau0", Bounds(-20, 20));
+        P.addGoal(MOCOB200_GOAL_FINAL_TIME, "time");
+    } else {
+        P.setTimeBounds(Bounds(0), Bounds(1));
+        P.setStateInfo("/jointset/j0/q0/value", Bounds(-10, 10), Bounds(0));
+        P.setStateInfo("/jointset/j0/q0/speed", Bounds(-10, 10), Bounds(0));
+        P.setControlInfo("/tau0", Bounds(-5, 5));
+        P.addGoal(MOCOB200_GOAL_CONTROL, "effort");
+    }
+    GoalSpec& constr = P.addPathConstraint(MOCOB200_PATHCON_CONTROL_BOUND, "control_bound");
+    constr.addControlPath("/tau0");
+    const PiecewisePoly violateLower = piecewiseLinearFunction({0, 0.2, 0.7, 1}, {0, 0.5316, -0.3137, .0319});
+    if (which == "lower") constr.lowerBound = constantFunction(0.1318);
+    else if (which == "upper") constr.upperBound = constantFunction(11.236);
+    else if (which == "equality") { constr.lowerBound = violateLower; constr.equalityWithLower = true; }
+    else if (which == "both") { constr.lowerBound = violateLower; constr.upperBound = constantFunction(0.75); }
+    else if (which != "none") throw std::runtime_error("pendulum_control_bound:<lower|upper|equality|both|none>");
+    SolverSettings S;
+    S.num_mesh_intervals = 25;
+    S.applyOptions(options);
+    return flatten(P, S);
+}
+
 // symmetry goal shared by gaitTracking / gaitPrediction (example2DWalking.cpp:80-126, 225-271)
 void addSymmetryGoal(Problem& P) {
     GoalSpec& g = P.addGoal(MOCOB200_GOAL_PERIODICITY, "symmetryGoal");
@@ -300,6 +351,7 @@ std::unique_ptr<FlatProblem> buildExample(const std::string& name, const std::st
     if (name == "hanging_muscle") return hangingMuscle(options, false, false);
     if (name == "hanging_muscle_rigidtendon") return hangingMuscle(options, false, true);
     if (name == "hanging_muscle_noactdyn") return hangingMuscle(options, true, false);
+    if (name.rfind("pendulum_control_bound:", 0) == 0) return pendulumControlBound(name.substr(23), options);
     if (name.rfind("pendulum:", 0) == 0) return pendulum(std::stoi(name.substr(9)), options);
     if (name == "gait2d_tracking") return gaitTracking(dataDir, options);
     if (name == "gait2d_prediction") return gaitPrediction(dataDir, options);

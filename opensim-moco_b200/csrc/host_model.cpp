@@ -197,6 +197,28 @@ PiecewisePoly fitNaturalSpline(const std::vector<double>& t, const std::vector<d
         const double hk = t[k + 1] - t[k];
         for (int j = 0; j < nc; ++j) pp.coef[(size_t)k * nc + j] = b[k * nc + j] / std::pow(hk, j);
     }
+    pp.isSpline = true;
+    return pp;
+}
+
+PiecewisePoly constantFunction(double v) {
+    PiecewisePoly pp;
+    pp.breaks = {0.0, 1.0};
+    pp.coef = {v};
+    pp.order = 1;
+    return pp;
+}
+// y[k] + (t - x[k]) * b[k], end slopes extended beyond the first/last point (PiecewiseLinearFunction.cpp:429-463)
+PiecewisePoly piecewiseLinearFunction(const std::vector<double>& x, const std::vector<double>& y) {
+    if (x.size() < 2 || x.size() != y.size()) throw std::runtime_error("piecewiseLinearFunction: need >= 2 points");
+    PiecewisePoly pp;
+    pp.breaks = x;
+    pp.order = 2;
+    for (size_t k = 0; k + 1 < x.size(); ++k) {
+        if (!(x[k + 1] > x[k])) throw std::runtime_error("piecewiseLinearFunction: x must increase");
+        pp.coef.push_back(y[k]);
+        pp.coef.push_back((y[k + 1] - y[k]) / (x[k + 1] - x[k]));
+    }
     return pp;
 }
 
@@ -597,6 +619,8 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
         int mode = g.mode;
         const bool defaultEC = g.kind == MOCOB200_GOAL_AVERAGE_SPEED || g.kind == MOCOB200_GOAL_PERIODICITY ||
                                g.kind == MOCOB200_GOAL_INITIAL_ACTIVATION;
+        if (mode == MOCOB200_MODE_PATH_CONSTRAINT && g.kind != MOCOB200_PATHCON_CONTROL_BOUND)
+            throw std::runtime_error("unsupported path constraint (only MocoControlBoundConstraint, SURVEY §8 a10)");
         if (mode < 0) mode = defaultEC ? MOCOB200_MODE_ENDPOINT_CONSTRAINT : MOCOB200_MODE_COST;
         const int ioff = (int)goalI.size(), doff = (int)goalD.size();
         int nout = 1, hasInt = 0;
@@ -694,6 +718,43 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
             nout = (int)ms.size();
             goalI.push_back(nout);
             goalI.insert(goalI.end(), ms.begin(), ms.end());
+        } break;
+        case MOCOB200_PATHCON_CONTROL_BOUND: { // MocoControlBoundConstraint::initializeOnModelImpl (.cpp:37-119)
+            if (mode != MOCOB200_MODE_PATH_CONSTRAINT) throw std::runtime_error("MocoControlBoundConstraint is a path constraint");
+            const bool hasLower = !g.lowerBound.breaks.empty(), hasUpper = !g.upperBound.breaks.empty();
+            if (g.equalityWithLower && hasUpper)
+                throw std::runtime_error("If equality_with_lower==true, upper bound function must not be set.");
+            if (g.equalityWithLower && !hasLower)
+                throw std::runtime_error("If equality_with_lower==true, lower bound function must be set.");
+            auto checkTimeRange = [&](const PiecewisePoly& f) {
+                if (!f.isSpline) return;
+                if (f.breaks.front() > P.timeInitial.lo)
+                    throw std::runtime_error("The function's minimum domain value (" + std::to_string(f.breaks.front()) +
+                                             ") must be less than or equal to the minimum possible initial time (" +
+                                             std::to_string(P.timeInitial.lo) + ").");
+                if (f.breaks.back() < P.timeFinal.hi)
+                    throw std::runtime_error("The function's maximum domain value (" + std::to_string(f.breaks.back()) +
+                                             ") must be greater than or equal to the maximum possible final time (" +
+                                             std::to_string(P.timeFinal.hi) + ").");
+            };
+            if (hasLower) checkTimeRange(g.lowerBound);
+            if (hasUpper) checkTimeRange(g.upperBound);
+            const int lowerId = hasLower ? addPPoly(g.lowerBound) : -1, upperId = hasUpper ? addPPoly(g.upperBound) : -1;
+            nout = 0;
+            if (hasLower || hasUpper)
+                for (const std::string& path : g.controlPaths) {
+                    const int c = controlIndex(path);
+                    if (hasLower) { // 0 <= control - lower(t) <= inf   (or == 0 with equality_with_lower)
+                        goalI.push_back(c); goalI.push_back(lowerId);
+                        goalD.push_back(0.0); goalD.push_back(g.equalityWithLower ? 0.0 : inf);
+                        ++nout;
+                    }
+                    if (hasUpper) { // -inf <= control - upper(t) <= 0
+                        goalI.push_back(c); goalI.push_back(upperId);
+                        goalD.push_back(-inf); goalD.push_back(0.0);
+                        ++nout;
+                    }
+                }
         } break;
         default: throw std::runtime_error("unsupported goal kind");
         }

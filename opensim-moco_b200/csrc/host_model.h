@@ -127,6 +127,7 @@ struct VariableInfo {
 struct PiecewisePoly { // value(t) on [breaks[k], breaks[k+1]) = sum_j coef[k*order+j] (t-breaks[k])^j
     std::vector<double> breaks, coef;
     int order = 0;
+    bool isSpline = false; // came from a GCVSpline (domain-checked where the reference checks, e.g. MocoControlBoundConstraint.cpp:74-92)
 };
 // natural interpolating spline of odd degree (what GCVSPL returns for zero smoothing), as a piecewise polynomial
 PiecewisePoly fitNaturalSpline(const std::vector<double>& t, const std::vector<double>& y, int degree);
@@ -167,7 +168,15 @@ struct GoalSpec {
     double desiredAverageSpeed = 0;
     // endpoint-constraint bounds (default 0,0)
     Bounds ecBounds{0, 0};
+    // MocoControlBoundConstraint (kind MOCOB200_PATHCON_CONTROL_BOUND): control_paths, lower_bound / upper_bound
+    // functions of time (empty breaks = not set), equality_with_lower (MocoControlBoundConstraint.h)
+    std::vector<std::string> controlPaths;
+    PiecewisePoly lowerBound, upperBound;
+    bool equalityWithLower = false;
+    void addControlPath(const std::string& p) { controlPaths.push_back(p); }
 };
+PiecewisePoly constantFunction(double v);                                                    // OpenSim::Constant
+PiecewisePoly piecewiseLinearFunction(const std::vector<double>& x, const std::vector<double>& y); // PiecewiseLinearFunction.cpp:429-463
 
 struct Problem {
     ModelSpec model;
@@ -186,6 +195,12 @@ struct Problem {
         goals.back().name = name;
         goals.back().weight = weight;
         return goals.back();
+    }
+    // MocoProblem::addPathConstraint<T>() ; evaluated after the goals' records (their own index space in the reference)
+    GoalSpec& addPathConstraint(int kind, const std::string& name) {
+        GoalSpec& g = addGoal(kind, name);
+        g.mode = MOCOB200_MODE_PATH_CONSTRAINT;
+        return g;
     }
 };
 

@@ -182,6 +182,7 @@ __global__ void k_endpoint(DevTables T, DevLayout L, FdSettings fd, const double
     const int g = blockIdx.x;
     const int a = threadIdx.x;
     const int nout = T.idx[T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE + 2];
+    if (T.idx[T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE + 1] == MOCOB200_MODE_PATH_CONSTRAINT) return; // not an endpoint function (whole block)
     double* sh_in = sh;
     double* sh_g0 = sh + L.n_ein;
     {   // cooperative gather of [t0, x0, c0, d0, tf, xf, cf, df, integral]
@@ -254,7 +255,56 @@ __device__ __forceinline__ void defect_coeffs(int kind, int role, double& lin, d
     }
 }
 
-__global__ void k_assemble_g(DevLayout L, const double* __restrict__ x, const double* __restrict__ Y, const double* __restrict__ G,
+// ---------------------------------------------------------------------------------------------
+// Path constraints (CasOC::PathConstraint::eval CasOCFunction.cpp:137-143). The one supported kind,
+// MocoControlBoundConstraint (MocoControlBoundConstraint.cpp:121-148), is error_e = control_e - bound_e(time): a function
+// of the mesh point's time and controls only, so it is evaluated here in the assembly kernels, not in the point kernels.
+__device__ inline double pathcon_error(const DevTables& T, const int* ip, int e, double time, const double* ctl, int ck, double cv) {
+    const int c = ip[2 * e];
+    return (c == ck ? cv : ctl[c]) - ppoly_eval(T, ip[2 * e + 1], time);
+}
+// One entry of the FD block of path constraint `g` at grid point j: d error_e / d input_a, CasADi FiniteDiff on that callback
+// (fd_group above: every equation of the constraint shares the refined central step). Inputs the constraint does not read
+// still own a (zero-valued) structural entry of the dense block.
+__device__ double pathcon_fd_entry(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* __restrict__ x, int j, int g,
+                                   int e, int a) {
+    const int* gr = T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
+    const int* ip = T.idx + gr[4];
+    const int neq = gr[2];
+    const double t = x[0] + (x[1] - x[0]) * L.grid[j];
+    const double* ctl = x + L.off_controls + (size_t)j * L.nc;
+    const int ck = (a > L.ns && a <= L.ns + L.nc) ? a - 1 - L.ns : -1; // perturbed control (or none)
+    const double x0 = a == 0 ? t : (ck >= 0 ? ctl[ck] : 0.0);
+    auto at = [&](int ee, double xa) { return pathcon_error(T, ip, ee, a == 0 ? xa : t, ctl, ck, xa); };
+    const double vc_e = pathcon_error(T, ip, e, t, ctl, -1, 0.0);
+    if (fd.scheme != MOCOB200_FD_CENTRAL) {
+        const bool fwd = fd.scheme == MOCOB200_FD_FORWARD;
+        const double yf = at(e, fwd ? x0 + fd.h : x0 - fd.h);
+        return fwd ? (yf - vc_e) / fd.h : (vc_e - yf) / fd.h;
+    }
+    double h = fd.h, jv = 0;
+    for (int iter = 0;; ++iter) {
+        double u = 0;
+        for (int ee = 0; ee < neq; ++ee) {
+            const double vb = at(ee, x0 - h), vf = at(ee, x0 + h), vc = pathcon_error(T, ip, ee, t, ctl, -1, 0.0);
+            double je;
+            if (!isfinite(vf) || !isfinite(vc) || !isfinite(vb)) { je = NAN; u = -1; }
+            else {
+                je = (vf - vb) / (2 * h);
+                const double et = vf - 2 * vc + vb;
+                const double er = fd.reltol / h * fmax(fabs(vf - vc), fabs(vc - vb)) + fd.abstol;
+                if (u >= 0) u = fmax(u, fabs(et / er));
+            }
+            if (ee == e) jv = je;
+        }
+        if (iter == fd.h_iter) break;
+        if (u < 0) h /= fd.u_aim;
+        else h *= sqrt(fd.u_aim / fmax(1.0, u));
+    }
+    return jv;
+}
+
+__global__ void k_assemble_g(DevTables T, DevLayout L, const double* __restrict__ x, const double* __restrict__ Y, const double* __restrict__ G,
                              double* __restrict__ g) {
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= L.n_con) return;
@@ -263,7 +313,10 @@ __global__ void k_assemble_g(DevLayout L, const double* __restrict__ x, const do
     double v = 0;
     if (rm.kind == ROW_ENDPOINT_D) v = G[L.goal_eoff[rm.a] + rm.b];
     else if (rm.kind == ROW_RESIDUAL_D) v = Y[(size_t)rm.a * L.n_out + rm.b];
-    else if (rm.kind == ROW_INTERP_D) {
+    else if (rm.kind == ROW_PATH_D) {
+        const int* gr = T.idx + T.o_goal_i + rm.pad * MOCOB200_GOAL_ISTRIDE;
+        v = pathcon_error(T, T.idx + gr[4], rm.b, x[0] + (x[1] - x[0]) * L.grid[rm.a], x + L.off_controls + (size_t)rm.a * L.nc, -1, 0.0);
+    } else if (rm.kind == ROW_INTERP_D) {
         const int m = rm.a, c = rm.b;
         const double* xc = x + L.off_controls;
         v = xc[(size_t)(2 * m + 1) * L.nc + c] - 0.5 * (xc[(size_t)(2 * m + 2) * L.nc + c] + xc[(size_t)(2 * m) * L.nc + c]);
@@ -335,7 +388,7 @@ __device__ __forceinline__ double endpoint_entry(const DevLayout& L, const doubl
     return v;
 }
 
-__global__ void k_assemble_jac(DevLayout L, const double* __restrict__ x, const double* __restrict__ Y, const double* __restrict__ J,
+__global__ void k_assemble_jac(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ x, const double* __restrict__ Y, const double* __restrict__ J,
                                const double* __restrict__ I, const double* __restrict__ E, double* __restrict__ vals) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= L.nnz) return;
@@ -351,6 +404,10 @@ __global__ void k_assemble_jac(DevLayout L, const double* __restrict__ x, const 
         const double* Jr = J + ((size_t)j * L.n_out + rm.b) * L.n_in;
         if (isTime) v = Jr[0] * (c.kind == COL_TF_D ? L.grid[j] : 1.0 - L.grid[j]);
         else v = Jr[c.in];
+    } else if (rm.kind == ROW_PATH_D) {
+        const int j = rm.a;
+        if (isTime) v = pathcon_fd_entry(T, L, fd, x, j, rm.pad, rm.b, 0) * (c.kind == COL_TF_D ? L.grid[j] : 1.0 - L.grid[j]);
+        else v = pathcon_fd_entry(T, L, fd, x, j, rm.pad, rm.b, c.in);
     } else if (rm.kind == ROW_INTERP_D) {
         v = (c.point == 2 * rm.a + 1) ? 1.0 : -0.5;
     } else {
@@ -469,17 +526,18 @@ void launch_endpoint(const DevTables& T, const DevLayout& L, const FdSettings& f
     const int bs = ((L.n_ein + 1 + 31) / 32) * 32;
     k_endpoint<<<T.ngoal, bs, (L.n_ein + MOCOB200_MAX_EOUT) * sizeof(double), s>>>(T, L, fd, d_x, d_I, d_G, d_E, withFd ? 1 : 0);
 }
-void launch_assemble_g(const DevLayout& L, const double* d_x, const double* d_Y, const double* d_G, double* d_g, cudaStream_t s) {
+void launch_assemble_g(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_Y, const double* d_G, double* d_g,
+                       cudaStream_t s) {
     if (L.n_con <= 0) return;
-    k_assemble_g<<<(L.n_con + 127) / 128, 128, 0, s>>>(L, d_x, d_Y, d_G, d_g);
+    k_assemble_g<<<(L.n_con + 127) / 128, 128, 0, s>>>(T, L, d_x, d_Y, d_G, d_g);
 }
 void launch_assemble_f(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_G, double* d_f, cudaStream_t s) {
     k_assemble_f<<<1, 32, 0, s>>>(T, L, d_x, d_G, d_f);
 }
-void launch_assemble_jac(const DevLayout& L, const double* d_x, const double* d_Y, const double* d_J, const double* d_I, const double* d_E,
-                         double* d_vals, cudaStream_t s) {
+void launch_assemble_jac(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, const double* d_Y, const double* d_J,
+                         const double* d_I, const double* d_E, double* d_vals, cudaStream_t s) {
     if (L.nnz <= 0) return;
-    k_assemble_jac<<<(L.nnz + 255) / 256, 256, 0, s>>>(L, d_x, d_Y, d_J, d_I, d_E, d_vals);
+    k_assemble_jac<<<(L.nnz + 255) / 256, 256, 0, s>>>(T, L, fd, d_x, d_Y, d_J, d_I, d_E, d_vals);
 }
 void launch_assemble_grad(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_Y, const double* d_J, const double* d_I,
                           const double* d_E, double* d_grad, cudaStream_t s) {

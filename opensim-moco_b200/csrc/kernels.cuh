@@ -20,7 +20,7 @@ struct FdSettings {
     double reltol, abstol;
 };
 
-enum { ROW_ENDPOINT_D = 0, ROW_RESIDUAL_D = 1, ROW_DEFECT_TRAP_D = 2, ROW_DEFECT_HERMITE_D = 3, ROW_DEFECT_SIMPSON_D = 4, ROW_INTERP_D = 5 };
+enum { ROW_ENDPOINT_D = 0, ROW_RESIDUAL_D = 1, ROW_DEFECT_TRAP_D = 2, ROW_DEFECT_HERMITE_D = 3, ROW_DEFECT_SIMPSON_D = 4, ROW_INTERP_D = 5, ROW_PATH_D = 6 };
 enum { COL_T0_D = 0, COL_TF_D = 1, COL_STATE_D = 2, COL_CONTROL_D = 3, COL_DERIV_D = 4 };
 struct RowMetaD { int kind, a, b, pad; };
 struct ColMetaD { int kind, point, k, in; };
@@ -58,10 +58,11 @@ void launch_integrals(const DevLayout& L, const double* d_x, const double* d_Y, 
 // G[n_eout_total] values and E[n_eout_total][n_ein] FD blocks of every goal's endpoint function
 void launch_endpoint(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, const double* d_I, double* d_G,
                      double* d_E, bool withFd, cudaStream_t s);
-void launch_assemble_g(const DevLayout& L, const double* d_x, const double* d_Y, const double* d_G, double* d_g, cudaStream_t s);
+void launch_assemble_g(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_Y, const double* d_G, double* d_g,
+                       cudaStream_t s);
 void launch_assemble_f(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_G, double* d_f /*[1+n_cost_terms]*/, cudaStream_t s);
-void launch_assemble_jac(const DevLayout& L, const double* d_x, const double* d_Y, const double* d_J, const double* d_I,
-                         const double* d_E, double* d_vals, cudaStream_t s);
+void launch_assemble_jac(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, const double* d_Y,
+                         const double* d_J, const double* d_I, const double* d_E, double* d_vals, cudaStream_t s);
 void launch_assemble_grad(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_Y, const double* d_J, const double* d_I,
                           const double* d_E, double* d_grad, cudaStream_t s);
 double measure_fp64_peak_tflops(int device);

@@ -20,9 +20,11 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
     L.n_auxres = T.nderiv_aux;
     L.goal_integrand.assign(T.ngoal, -1);
     L.goal_row.assign(T.ngoal, -1);
-    L.n_integrand = 0; L.n_endpoint_rows = 0; L.n_cost_terms = 0;
+    L.goal_path_off.assign(T.ngoal, -1);
+    L.n_integrand = 0; L.n_endpoint_rows = 0; L.n_cost_terms = 0; L.n_path_rows = 0;
     for (int g = 0; g < T.ngoal; ++g) {
         const int* gr = goalRec(T, g);
+        if (gr[1] == MOCOB200_MODE_PATH_CONSTRAINT) { L.goal_path_off[g] = L.n_path_rows; L.n_path_rows += gr[2]; continue; }
         if (gr[3]) L.goal_integrand[g] = L.n_integrand++;
         if (gr[1] == MOCOB200_MODE_ENDPOINT_CONSTRAINT) { L.goal_row[g] = L.n_endpoint_rows; L.n_endpoint_rows += gr[2]; }
         else L.n_cost_terms++;
@@ -69,19 +71,27 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
     L.row_resid.assign(L.n_grid, -1);
     L.row_defect.assign(L.n_intervals, -1);
     L.row_interp.assign(L.n_intervals, -1);
+    L.row_path.assign(L.n_mesh, -1);
     int row = L.n_endpoint_rows;
     const int ppi = hs ? 2 : 1; // grid points whose residuals are grouped with interval m
     for (int m = 0; m < L.n_intervals; ++m) {
+        L.row_path[m] = row; row += L.n_path_rows; // [kinematic: none,] path constraints of mesh point m first
         for (int k = 0; k < ppi; ++k) { L.row_resid[ppi * m + k] = row; row += L.n_resid_rows_per_point; }
         L.row_defect[m] = row; row += L.n_defect_rows;
         L.row_interp[m] = row; row += L.n_interp_rows;
     }
+    L.row_path[L.n_mesh - 1] = row; row += L.n_path_rows;
     L.row_resid[L.n_grid - 1] = row; row += L.n_resid_rows_per_point;
     L.n_con = row;
     L.rows.assign(L.n_con, RowMeta{0, 0, 0, 0});
     for (int g = 0; g < T.ngoal; ++g)
         if (L.goal_row[g] >= 0)
             for (int o = 0; o < goalRec(T, g)[2]; ++o) L.rows[L.goal_row[g] + o] = RowMeta{ROW_ENDPOINT, g, o, 0};
+    for (int g = 0; g < T.ngoal; ++g)
+        if (L.goal_path_off[g] >= 0)
+            for (int im = 0; im < L.n_mesh; ++im)
+                for (int e = 0; e < goalRec(T, g)[2]; ++e)
+                    L.rows[L.row_path[im] + L.goal_path_off[g] + e] = RowMeta{ROW_PATH, hs ? 2 * im : im, e, g};
     for (int j = 0; j < L.n_grid; ++j)
         for (int o = 0; o < L.n_resid_rows_per_point; ++o) {
             // out rows: implicit multibody residual [0,nq) then aux residuals at [nq+nz, ...)
@@ -134,11 +144,15 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
         if (c.kind == COL_T0 || c.kind == COL_TF) {
             for (int r = 0; r < L.n_endpoint_rows; ++r) emit(col, r);
             for (int m = 0; m < L.n_intervals; ++m) {
+                for (int e = 0; e < L.n_path_rows; ++e)
+                    if (maskAt(L.n_out + e, 0)) emit(col, L.row_path[m] + e);
                 for (int k = 0; k < ppi; ++k)
                     for (int o = 0; o < L.n_resid_rows_per_point; ++o)
                         if (maskAt(residOutRow(o), 0)) emit(col, L.row_resid[ppi * m + k] + o); // through the time input
                 for (int o = 0; o < L.n_defect_rows; ++o) emit(col, L.row_defect[m] + o);      // through h, always
             }
+            for (int e = 0; e < L.n_path_rows; ++e)
+                if (maskAt(L.n_out + e, 0)) emit(col, L.row_path[L.n_mesh - 1] + e);
             for (int o = 0; o < L.n_resid_rows_per_point; ++o)
                 if (maskAt(residOutRow(o), 0)) emit(col, L.row_resid[L.n_grid - 1] + o);
             continue;
@@ -162,8 +176,17 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
             if (j - 1 >= 0) { ms[nm] = j - 1; roles[nm++] = 2; }
             if (j < L.n_intervals) { ms[nm] = j; roles[nm++] = 0; }
         }
+        // the path-constraint callbacks of mesh point j: after the interval that ends at j, before the one that starts there
+        bool pathDone = !(hs ? j % 2 == 0 : true) || L.n_path_rows == 0;
+        auto emitPath = [&]() {
+            if (pathDone) return;
+            pathDone = true;
+            for (int e = 0; e < L.n_path_rows; ++e)
+                if (maskAt(L.n_out + e, c.in)) emit(col, L.row_path[hs ? j / 2 : j] + e);
+        };
         for (int t = 0; t < nm; ++t) {
             const int m = ms[t], role = roles[t];
+            if (role != 2) emitPath();
             if (role != 2) // residual rows of j sit in the block of the interval that starts at / contains j
                 for (int o = 0; o < L.n_resid_rows_per_point; ++o)
                     if (maskAt(residOutRow(o), c.in)) emit(col, L.row_resid[j] + o);
@@ -186,6 +209,7 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
                 }
             if (L.n_interp_rows && c.kind == COL_CONTROL) emit(col, L.row_interp[m] + c.k);
         }
+        emitPath();
         if (j == L.n_grid - 1)
             for (int o = 0; o < L.n_resid_rows_per_point; ++o)
                 if (maskAt(residOutRow(o), c.in)) emit(col, L.row_resid[j] + o);
@@ -222,9 +246,15 @@ void layoutBounds(const mocob200_tables& T, const mocob200_transcription& R, con
     if (glo && ghi) {
         for (int r = 0; r < L.n_con; ++r) { glo[r] = 0; ghi[r] = 0; }
         for (int g = 0; g < T.ngoal; ++g) {
-            if (L.goal_row[g] < 0) continue;
             const int* gr = T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
             const double* dp = T.dbl + gr[5];
+            if (L.goal_path_off[g] >= 0) // MocoConstraintInfo bounds repeated over the mesh points (CasOCTranscription.cpp:429-432)
+                for (int im = 0; im < L.n_mesh; ++im)
+                    for (int e = 0; e < gr[2]; ++e) {
+                        glo[L.row_path[im] + L.goal_path_off[g] + e] = dp[3 + 2 * e];
+                        ghi[L.row_path[im] + L.goal_path_off[g] + e] = dp[4 + 2 * e];
+                    }
+            if (L.goal_row[g] < 0) continue;
             for (int o = 0; o < gr[2]; ++o) { glo[L.goal_row[g] + o] = dp[1]; ghi[L.goal_row[g] + o] = dp[2]; }
         }
     }

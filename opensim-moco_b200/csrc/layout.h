@@ -10,11 +10,11 @@
 namespace mocob200 {
 
 // row kinds
-enum { ROW_ENDPOINT = 0, ROW_RESIDUAL = 1, ROW_DEFECT_TRAP = 2, ROW_DEFECT_HERMITE = 3, ROW_DEFECT_SIMPSON = 4, ROW_INTERP = 5 };
+enum { ROW_ENDPOINT = 0, ROW_RESIDUAL = 1, ROW_DEFECT_TRAP = 2, ROW_DEFECT_HERMITE = 3, ROW_DEFECT_SIMPSON = 4, ROW_INTERP = 5, ROW_PATH = 6 };
 // column kinds
 enum { COL_T0 = 0, COL_TF = 1, COL_STATE = 2, COL_CONTROL = 3, COL_DERIV = 4 };
 
-struct RowMeta { int kind, a, b, pad; };  // ENDPOINT: a = goal, b = output ; RESIDUAL: a = grid point, b = out row ; DEFECT_*: a = interval, b = state ; INTERP: a = interval, b = control
+struct RowMeta { int kind, a, b, pad; };  // ENDPOINT: a = goal, b = output ; RESIDUAL: a = grid point, b = out row ; DEFECT_*: a = interval, b = state ; INTERP: a = interval, b = control ; PATH: a = grid point, b = equation of the path constraint, pad = its goal record
 struct ColMeta { int kind, point, k, in; }; // in = index into the point-function input vector (0 = time)
 
 struct Layout {
@@ -26,6 +26,9 @@ struct Layout {
     int off_states, off_controls, off_derivs;
     int n_endpoint_rows, n_resid_rows_per_point, n_defect_rows, n_interp_rows;
     int n_cost_terms;
+    int n_path_rows;                           // path-constraint equations per mesh point (all path constraints)
+    std::vector<int> row_path;                 // first path-constraint row of each mesh point
+    std::vector<int> goal_path_off;            // offset of path constraint g inside a mesh point's path rows (or -1)
     std::vector<double> mesh, grid, quad;      // normalised times and quadrature coefficients
     std::vector<int> row_resid, row_defect, row_interp; // first row of each block (per grid point / interval)
     std::vector<int> goal_row;                 // first endpoint-constraint row of goal g (or -1)
@@ -37,7 +40,8 @@ struct Layout {
     int n_ein;
 };
 
-// blockMask (may be null = dense callback blocks): [n_out][n_in] flags, non-zero where the point function's output row
+// blockMask (may be null = dense callback blocks): [n_out + n_path_rows][n_in] flags (point-function outputs, then the
+// path-constraint equations), non-zero where the point function's output row
 // depends on its input (the per-callback Jacobian sparsity of optim_sparsity_detection = "random",
 // CasOCFunction.cpp:25-105); the structure then holds only the entries CasADi's sparsity propagation would keep.
 Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bool withStructure,

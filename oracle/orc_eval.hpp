@@ -267,6 +267,19 @@ void evalPoint(const Model& M, const S* in, S* out, unsigned mask = 0xffffffffu)
 }
 
 // Endpoint function of goal g (MocoGoal::calcGoal, MocoGoal.h:215-248, and each goal's calcGoalImpl):
+// Path constraint g at one mesh point: in = [time, states, controls, derivatives] -> errors[n_outputs]
+// (CasOC::PathConstraint::eval CasOCFunction.cpp:137-143 -> MocoCasOCProblem.h:463-484).
+// Only MocoControlBoundConstraint: error = control - bound_function(time), one equation per (control, bound)
+// (MocoControlBoundConstraint.cpp:121-148).
+template <class S>
+void evalPathConstraint(const Model& M, int g, const S* in, S* errors) {
+    const int* gr = M.goalRec(g);
+    const int* ip = M.T->idx + gr[4];
+    const S time = in[0];
+    const S* controls = in + 1 + 2 * M.nq + M.nz;
+    for (int e = 0; e < gr[2]; ++e) errors[e] = controls[ip[2 * e]] - piecewisePoly(M, ip[2 * e + 1], time);
+}
+
 // ein = [t0, x0, c0, d0, tf, xf, cf, df, integral] -> vals[n_outputs].
 template <class S>
 void evalEndpoint(const Model& M, int g, const S* ein, S* vals) {

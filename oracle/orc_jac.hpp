@@ -96,6 +96,24 @@ struct JacBuilder {
                 addEndpointRow(r, x, J, structural ? nullptr : (*Eblocks)[g].data(), g, row - N.goalRow[g], 1.0, structural);
                 return;
             }
+        // path-constraint rows: each path constraint is its own callback with a dense block over the mesh point's inputs
+        if (N.nPathPerMesh)
+            for (int im = 0; im < N.nMesh; ++im)
+                if (row >= N.pathRow[im] && row < N.pathRow[im] + N.nPathPerMesh) {
+                    int k = row - N.pathRow[im];
+                    const int j = N.meshGridIndex(im);
+                    for (int pg : N.pathGoals) {
+                        if (k >= N.goalNout[pg]) { k -= N.goalNout[pg]; continue; }
+                        if (structural) { r.mark(0); r.mark(1); for (int a = 1; a < N.nIn; ++a) r.mark(colOfInput(j, a)); return; }
+                        std::vector<double> Jp((size_t)N.goalNout[pg] * N.nIn);
+                        N.pathJacobian(x, im, pg, Jp.data());
+                        const double* Jr = Jp.data() + (size_t)k * N.nIn;
+                        r.add(0, Jr[0] * (1.0 - N.grid[j]));
+                        r.add(1, Jr[0] * N.grid[j]);
+                        for (int a = 1; a < N.nIn; ++a) r.add(colOfInput(j, a), Jr[a]);
+                        return;
+                    }
+                }
         // residual rows
         for (int j = 0; j < N.nGrid; ++j)
             if (row >= N.residRow[j] && row < N.residRow[j] + N.nResidPerPoint) {

@@ -79,6 +79,8 @@ struct Nlp {
     std::vector<double> mesh, grid, quad;
     std::vector<int> goalRow, goalSlot, goalNout; // first endpoint row (or -1), integrand slot (or -1), outputs
     std::vector<int> residRow, defectRow, interpRow; // first row per grid point / interval
+    std::vector<int> pathGoals, pathRow;              // path constraints (goal records) ; first path row per mesh point
+    int nPathPerMesh = 0;
     bool interp = false;
 
     void init(const mocob200_tables* T, const mocob200_transcription* tr) {
@@ -109,19 +111,23 @@ struct Nlp {
         nEin = 2 * (1 + ns + nc + nd) + 1;
         // rows
         goalRow.assign(T->ngoal, -1); goalSlot.assign(T->ngoal, -1); goalNout.assign(T->ngoal, 0);
+        pathGoals.clear(); nPathPerMesh = 0;
         int row = 0, slot = 0;
         for (int g = 0; g < T->ngoal; ++g) {
             const int* gr = M.goalRec(g);
             goalNout[g] = gr[2];
+            if (gr[1] == MOCOB200_MODE_PATH_CONSTRAINT) { pathGoals.push_back(g); nPathPerMesh += gr[2]; continue; }
             if (gr[3]) goalSlot[g] = slot++;
             if (gr[1] == MOCOB200_MODE_ENDPOINT_CONSTRAINT) { goalRow[g] = row; row += gr[2]; }
         }
         nEndpointRows = row;
+        pathRow.assign(nMesh, -1);
         nResidPerPoint = (M.implicit ? nq : 0) + M.n_auxres;
         interp = hs && tr->interpolate_control_midpoints && nc > 0;
         residRow.assign(nGrid, -1); defectRow.assign(nIntervals, -1); interpRow.assign(nIntervals, -1);
         int igrid = 0;
         for (int im = 0; im < nMesh; ++im) {
+            pathRow[im] = row; row += nPathPerMesh; // copyColumn(path, imesh) for every path constraint
             if (im < nIntervals) {
                 while (grid[igrid] < mesh[im + 1]) { residRow[igrid] = row; row += nResidPerPoint; ++igrid; }
                 defectRow[im] = row; row += (hs ? 2 : 1) * ns;
@@ -130,6 +136,20 @@ struct Nlp {
         }
         residRow[nGrid - 1] = row; row += nResidPerPoint;
         nCon = row;
+    }
+
+    int meshGridIndex(int im) const { return hs ? 2 * im : im; }
+    // FD block of path constraint pg at mesh point im: Jp[nout][nIn] (its own FiniteDiff function)
+    void pathJacobian(const double* x, int im, int pg, double* Jp) const {
+        const int nout = goalNout[pg];
+        std::vector<double> in(nIn), y0(std::max(nout, 1)), col(std::max(nout, 1));
+        gatherInputs(x, meshGridIndex(im), in.data());
+        evalPathConstraint<double>(M, pg, in.data(), y0.data());
+        auto f = [&](const double* xin, double* yout) { evalPathConstraint<double>(M, pg, xin, yout); };
+        for (int a = 0; a < nIn; ++a) {
+            fdColumn(f, fd, in, a, y0.data(), nout, col.data());
+            for (int o = 0; o < nout; ++o) Jp[(size_t)o * nIn + a] = col[o];
+        }
     }
 
     // ---- point functions over the trajectory
@@ -207,6 +227,12 @@ struct Nlp {
             endpointInputs(x, Y, gi, ein.data());
             evalEndpoint<double>(M, gi, ein.data(), vals.data());
             for (int o = 0; o < goalNout[gi]; ++o) g[goalRow[gi] + o] = vals[o];
+        }
+        for (int im = 0; im < nMesh; ++im) { // path constraints at the mesh points (m_meshIndices)
+            std::vector<double> in(nIn);
+            gatherInputs(x, meshGridIndex(im), in.data());
+            int r = pathRow[im];
+            for (int pg : pathGoals) { evalPathConstraint<double>(M, pg, in.data(), g + r); r += goalNout[pg]; }
         }
         for (int j = 0; j < nGrid; ++j) {
             int r = residRow[j];

@@ -20,6 +20,11 @@ CASES = {
     "hanging_muscle_rigidtendon": ("hanging_muscle_rigidtendon", None),
     "pendulum2": ("pendulum:2", None),
     "pendulum3_implicit": ("pendulum:3", "multibody_dynamics_mode=implicit"),
+    # MocoControlBoundConstraint sections of testConstraints.cpp:1458-1541 (+ one with both bounds)
+    "pendulum_cb_lower": ("pendulum_control_bound:lower", None),
+    "pendulum_cb_upper_trap": ("pendulum_control_bound:upper", "transcription_scheme=trapezoidal"),
+    "pendulum_cb_equality": ("pendulum_control_bound:equality", None),
+    "pendulum_cb_both": ("pendulum_control_bound:both", "num_mesh_intervals=10;optim_finite_difference_scheme=forward"),
     "gait2d_tracking": ("gait2d_tracking", None),
     "gait2d_prediction": ("gait2d_prediction", None),
 }

@@ -37,4 +37,5 @@ def golden(name):
 
 
 FIXTURES = ["sliding_mass", "sliding_mass_trap", "hanging_muscle", "hanging_muscle_rigidtendon", "pendulum2",
-            "pendulum3_implicit", "gait2d_tracking", "gait2d_prediction"]
+            "pendulum3_implicit", "gait2d_tracking", "gait2d_prediction", "pendulum_cb_lower", "pendulum_cb_upper_trap",
+            "pendulum_cb_equality", "pendulum_cb_both"]

@@ -195,7 +195,43 @@ def test_graph_replay_equals_kernel_by_kernel_launches(pkg, name, monkeypatch):
             assert np.array_equal(ev.eval_grad_f(x), ev0.eval_grad_f(x), equal_nan=True)
 
 
-@pytest.mark.parametrize("name", ["gait2d_tracking", "gait2d_prediction", "hanging_muscle", "pendulum3_implicit", "sliding_mass"])
+@pytest.mark.parametrize("scheme", [FD_FORWARD, FD_BACKWARD, FD_CENTRAL])
+def test_control_bound_path_constraint_rows(pkg, orc, scheme):
+    """SURVEY §8 a10 — MocoControlBoundConstraint (MocoControlBoundConstraint.cpp:121-148) through the C ABI: g rows are
+    control - bound(t) at the mesh points; their Jacobian rows are the callback's dense FD block (1 in the control's
+    column up to FD round-off, exact zeros elsewhere) and agree with the oracle bit for bit (same IEEE operations)."""
+    p = load(pkg, "pendulum_cb_lower")
+    ev, o = pkg.Evaluator(p), orc.Oracle(p)
+    ev.set_fd(scheme)
+    o.set_fd(scheme)
+    d = ev.dims
+    x = p.make_iterate(seed=8, spread=0.7)
+    rows = np.arange(d.n_mesh) * 6
+    ctl = x[2 + 2 * d.n_grid:][: d.n_grid][::2]
+    g = ev.eval_g(x)
+    assert np.array_equal(g[rows], ctl - 0.1318)
+    colptr, rowidx = ev.structure()
+    v, vo = ev.eval_jac_g(x), o.eval_jac_g(x)
+    cols = np.repeat(np.arange(d.n_var), np.diff(colptr))
+    on_path = np.isin(rowidx, rows)
+    assert on_path.sum() == d.n_mesh * (2 + d.n_in - 1)  # t0, tf and the mesh point's states + control
+    assert np.array_equal(v[on_path], vo[on_path])
+    is_ctl = on_path & (cols >= 2 + 2 * d.n_grid)
+    assert is_ctl.sum() == d.n_mesh and np.max(np.abs(v[is_ctl] - 1.0)) < 1e-7
+    assert np.all(v[on_path & ~is_ctl] == 0.0)  # constant bound: no dependence on time or the states
+    # a time-varying bound: the time column chains into t0 and tf
+    p = load(pkg, "pendulum_cb_both")
+    ev, o = pkg.Evaluator(p), orc.Oracle(p)
+    ev.set_fd(scheme)
+    o.set_fd(scheme)
+    x = p.make_iterate(seed=9, spread=0.4)
+    assert relerr(ev.eval_g(x), o.eval_g(x)) < 1e-12
+    v, vo = ev.eval_jac_g(x), o.eval_jac_g(x)
+    assert np.isfinite(vo).all() and np.max(np.abs(v - vo)) < 1e-7 * max(1.0, np.abs(vo).max())
+
+
+@pytest.mark.parametrize("name", ["gait2d_tracking", "gait2d_prediction", "hanging_muscle", "pendulum3_implicit", "sliding_mass",
+                                  "pendulum_cb_lower", "pendulum_cb_equality", "pendulum_cb_both"])
 def test_random_sparsity_detection_keeps_every_nonzero(pkg, name):
     """optim_sparsity_detection = "random" (CasOCFunction.cpp:25-105): the detected structure is a subset of the dense-
     block structure, the surviving entries carry bit-identical values, and every dropped entry is exactly zero."""

@@ -88,3 +88,72 @@ def test_make_iterate_is_deterministic_and_within_bounds(pkg):
     assert np.array_equal(a, b)
     assert np.all(a >= xl) and np.all(a <= xu)
     assert not np.array_equal(a, p.make_iterate(seed=8, spread=0.5))
+
+
+# ---- path constraints: MocoControlBoundConstraint on the pendulum of testConstraints.cpp:1458-1541
+CB_CASES = ["pendulum_cb_lower", "pendulum_cb_upper_trap", "pendulum_cb_equality", "pendulum_cb_both"]
+
+
+def test_control_bound_rows_and_bounds(pkg, orc):
+    """Section 'Lower bound only': one row per mesh point, bounds [0, inf), value = control - 0.1318
+    (MocoControlBoundConstraint.cpp:93-119,121-148); rows sit at the head of each mesh point's block."""
+    p = pkg.Problem.load(golden("pendulum_cb_lower.mb20"))
+    d = p.dims()
+    xl, xu, gl, gu = p.bounds()
+    rows = np.flatnonzero(np.isinf(gu))
+    assert len(rows) == d.n_mesh and np.all(gl[rows] == 0)
+    # HS, ns = 2, nc = 1: per interval [path(1) | defects(4) | interp(1)] and the last mesh point's path row at the end
+    assert np.array_equal(rows, np.arange(d.n_mesh) * 6)
+    o = orc.Oracle(p)
+    x = p.make_iterate(seed=2, spread=0.5)
+    g = o.eval_g(x)
+    ctl = x[2 + 2 * d.n_grid:][: d.n_grid]
+    assert np.array_equal(g[rows], ctl[::2] - 0.1318)
+
+
+def test_control_bound_equality_and_both(pkg, orc):
+    """'Upper and lower bounds are the same' -> one equality row per mesh point following the piecewise-linear function;
+    both bounds -> (lower, upper) row pairs with bounds [0, inf), (-inf, 0]."""
+    p = pkg.Problem.load(golden("pendulum_cb_equality.mb20"))
+    d = p.dims()
+    xl, xu, gl, gu = p.bounds()
+    assert np.all(gl == 0) and np.all(gu == 0) and d.n_con == 4 * 25 + 25 + 26
+    o = orc.Oracle(p)
+    x = p.make_iterate(seed=1, spread=0.3)
+    g = o.eval_g(x)
+    t = x[0] + (x[1] - x[0]) * np.linspace(0, 1, d.n_mesh)
+    want = x[2 + 2 * d.n_grid:][: d.n_grid][::2] - np.interp(t, [0, 0.2, 0.7, 1], [0, 0.5316, -0.3137, .0319])
+    assert np.allclose(g[np.arange(d.n_mesh) * 6], want, rtol=0, atol=1e-15)
+    p = pkg.Problem.load(golden("pendulum_cb_both.mb20"))
+    xl, xu, gl, gu = p.bounds()
+    lo_rows, up_rows = np.flatnonzero(np.isinf(gu)), np.flatnonzero(np.isinf(gl))
+    assert np.array_equal(up_rows, lo_rows + 1) and len(lo_rows) == p.dims().n_mesh
+    x = p.make_iterate(seed=1, spread=0.3)
+    g = orc.Oracle(p).eval_g(x)
+    ctl = x[2 + 2 * p.dims().n_grid:][: p.dims().n_grid][::2]
+    assert np.array_equal(g[up_rows], ctl - 0.75)
+
+
+def test_control_bound_refusals(pkg):
+    """Error behaviour of MocoControlBoundConstraint::initializeOnModelImpl (.cpp:37-92)."""
+    assert pkg.Problem.example("pendulum_control_bound:none").dims().n_con == 125  # 'Can omit both bounds.'
+    with pytest.raises(Exception):
+        pkg.Problem.example("pendulum_control_bound:bogus")
+
+
+@pytest.mark.parametrize("name", CB_CASES)
+def test_control_bound_oracle_jacobian_is_derivative_of_g(pkg, orc, name):
+    p = pkg.Problem.load(golden(name + ".mb20"), "num_mesh_intervals=7")  # no mesh point on a knot of the bound function
+    o = orc.Oracle(p)
+    d = p.dims()
+    x = p.make_iterate(seed=4, spread=0.2)
+    colptr, rowidx = o.structure()
+    vals = o.eval_jac_g(x)
+    v = np.random.default_rng(0).uniform(-1, 1, d.n_var)
+    Jv = np.zeros(d.n_con)
+    for c in range(d.n_var):
+        sl = slice(colptr[c], colptr[c + 1])
+        Jv[rowidx[sl]] += vals[sl] * v[c]
+    e = 1e-6
+    fd = (o.eval_g(x + e * v) - o.eval_g(x - e * v)) / (2 * e)
+    assert np.allclose(Jv, fd, rtol=2e-5, atol=2e-5 * max(1.0, np.abs(fd).max()))
