@@ -517,6 +517,7 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     std::vector<int> eoff(T->ngoal + 1, 0);
     for (int g = 0; g < T->ngoal; ++g) eoff[g + 1] = eoff[g] + T->idx[T->o_goal_i + g * MOCOB200_GOAL_ISTRIDE + 2];
     G.n_eout_total = eoff[T->ngoal];
+    G.n_path_rows = L.n_path_rows;
     G.mesh = (const double*)own(devUpload(L.mesh));
     G.grid = (const double*)own(devUpload(L.grid));
     G.quad = (const double*)own(devUpload(L.quad));
@@ -723,7 +724,7 @@ int mocob200_eval_g(mocob200_handle* h, const double* x, double* g) {
     if (!stageX(h, x) || !bcastX(h, h->d_x) || !runNominal(h)) return MOCOB200_ERR_CUDA;
     if (h->rank == 0) {
         launch_assemble_g(h->DT, h->DL, h->d_x, h->d_Y, h->d_G, h->d_g, h->stream);
-        h->launches++;
+        h->launches += 1 + (h->DL.n_path_rows > 0);
         if (g) cudaMemcpyAsync(g, h->d_g, sizeof(double) * h->L.n_con, cudaMemcpyDeviceToHost, h->stream);
     }
     h->x_cached.clear();
@@ -772,7 +773,7 @@ static bool jacPipelineLaunches(mocob200_handle* h, double* d_vals) {
         recTiming(h->ev[2], h->stream);
         launch_assemble_jac(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_I, h->d_E, d_vals, h->stream);
         recTiming(h->ev[3], h->stream);
-        h->launches++;
+        h->launches += 1 + (h->DL.n_path_rows > 0);
     }
     return true;
 }
@@ -815,7 +816,7 @@ int mocob200_eval_jac_g(mocob200_handle* h, const double* x, double* values) {
         if (!jacPipeline(h, h->d_vals)) return MOCOB200_ERR_CUDA;
     } else {
         launch_assemble_jac(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_I, h->d_E, h->d_vals, h->stream);
-        h->launches++;
+        h->launches += 1 + (h->DL.n_path_rows > 0);
     }
     if (h->rank == 0 && values)
         cudaMemcpyAsync(values, h->d_vals, sizeof(double) * h->L.nnz, cudaMemcpyDeviceToHost, h->stream);
@@ -840,7 +841,7 @@ int mocob200_eval_g_device(mocob200_handle* h, const double* d_x, double* d_g, v
     (void)cuda_stream;
     h->x_cached.clear();
     if (!bcastX(h, d_x) || !runNominal(h)) return MOCOB200_ERR_CUDA;
-    if (h->rank == 0) { launch_assemble_g(h->DT, h->DL, h->d_x, h->d_Y, h->d_G, d_g ? d_g : h->d_g, h->stream); h->launches++; }
+    if (h->rank == 0) { launch_assemble_g(h->DT, h->DL, h->d_x, h->d_Y, h->d_G, d_g ? d_g : h->d_g, h->stream); h->launches += 1 + (h->DL.n_path_rows > 0); }
     return h->ck(cudaGetLastError(), "eval_g_device") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
 }
 

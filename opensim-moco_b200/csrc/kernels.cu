@@ -4,6 +4,8 @@
 
 #include "kernels.cuh"
 
+#include <cstdlib>
+
 namespace mocob200 {
 
 // ---------------------------------------------------------------------------------------------
@@ -304,7 +306,28 @@ __device__ double pathcon_fd_entry(const DevTables& T, const DevLayout& L, const
     return jv;
 }
 
-__global__ void k_assemble_g(DevTables T, DevLayout L, const double* __restrict__ x, const double* __restrict__ Y, const double* __restrict__ G,
+// path-constraint rows of g and of jac_g: separate small kernels, launched only for problems that have path constraints
+__global__ void k_assemble_g_path(DevTables T, DevLayout L, const double* __restrict__ x, double* __restrict__ g) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= L.n_con) return;
+    const RowMetaD rm = L.rows[r];
+    if (rm.kind != ROW_PATH_D) return;
+    const int* gr = T.idx + T.o_goal_i + rm.pad * MOCOB200_GOAL_ISTRIDE;
+    g[r] = pathcon_error(T, T.idx + gr[4], rm.b, x[0] + (x[1] - x[0]) * L.grid[rm.a], x + L.off_controls + (size_t)rm.a * L.nc, -1, 0.0);
+}
+__global__ void k_assemble_jac_path(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ x, double* __restrict__ vals) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= L.nnz) return;
+    const RowMetaD rm = L.rows[L.rowidx[k]];
+    if (rm.kind != ROW_PATH_D) return;
+    const ColMetaD c = L.cols[L.nnzcol[k]];
+    const int j = rm.a;
+    if (c.kind == COL_T0_D || c.kind == COL_TF_D)
+        vals[k] = pathcon_fd_entry(T, L, fd, x, j, rm.pad, rm.b, 0) * (c.kind == COL_TF_D ? L.grid[j] : 1.0 - L.grid[j]);
+    else vals[k] = pathcon_fd_entry(T, L, fd, x, j, rm.pad, rm.b, c.in);
+}
+
+__global__ void k_assemble_g(DevLayout L, const double* __restrict__ x, const double* __restrict__ Y, const double* __restrict__ G,
                              double* __restrict__ g) {
     const int r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= L.n_con) return;
@@ -313,10 +336,8 @@ __global__ void k_assemble_g(DevTables T, DevLayout L, const double* __restrict_
     double v = 0;
     if (rm.kind == ROW_ENDPOINT_D) v = G[L.goal_eoff[rm.a] + rm.b];
     else if (rm.kind == ROW_RESIDUAL_D) v = Y[(size_t)rm.a * L.n_out + rm.b];
-    else if (rm.kind == ROW_PATH_D) {
-        const int* gr = T.idx + T.o_goal_i + rm.pad * MOCOB200_GOAL_ISTRIDE;
-        v = pathcon_error(T, T.idx + gr[4], rm.b, x[0] + (x[1] - x[0]) * L.grid[rm.a], x + L.off_controls + (size_t)rm.a * L.nc, -1, 0.0);
-    } else if (rm.kind == ROW_INTERP_D) {
+    else if (rm.kind == ROW_PATH_D) return; // k_assemble_g_path
+    else if (rm.kind == ROW_INTERP_D) {
         const int m = rm.a, c = rm.b;
         const double* xc = x + L.off_controls;
         v = xc[(size_t)(2 * m + 1) * L.nc + c] - 0.5 * (xc[(size_t)(2 * m + 2) * L.nc + c] + xc[(size_t)(2 * m) * L.nc + c]);
@@ -388,7 +409,7 @@ __device__ __forceinline__ double endpoint_entry(const DevLayout& L, const doubl
     return v;
 }
 
-__global__ void k_assemble_jac(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ x, const double* __restrict__ Y, const double* __restrict__ J,
+__global__ void k_assemble_jac(DevLayout L, const double* __restrict__ x, const double* __restrict__ Y, const double* __restrict__ J,
                                const double* __restrict__ I, const double* __restrict__ E, double* __restrict__ vals) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= L.nnz) return;
@@ -405,9 +426,7 @@ __global__ void k_assemble_jac(DevTables T, DevLayout L, FdSettings fd, const do
         if (isTime) v = Jr[0] * (c.kind == COL_TF_D ? L.grid[j] : 1.0 - L.grid[j]);
         else v = Jr[c.in];
     } else if (rm.kind == ROW_PATH_D) {
-        const int j = rm.a;
-        if (isTime) v = pathcon_fd_entry(T, L, fd, x, j, rm.pad, rm.b, 0) * (c.kind == COL_TF_D ? L.grid[j] : 1.0 - L.grid[j]);
-        else v = pathcon_fd_entry(T, L, fd, x, j, rm.pad, rm.b, c.in);
+        return; // k_assemble_jac_path
     } else if (rm.kind == ROW_INTERP_D) {
         v = (c.point == 2 * rm.a + 1) ? 1.0 : -0.5;
     } else {
@@ -477,7 +496,8 @@ void launch_points_nominal(const DevTables& T, const DevLayout& L, const double*
 }
 // Flat variant: one thread per (grid point, listed direction), nominal outputs read from Y (already evaluated). Every
 // lane of every warp carries an evaluation chain, so a short direction list still fills the machine in one wave.
-__global__ void __launch_bounds__(64)
+template <int MINB>
+__global__ void __launch_bounds__(64, MINB)
 k_points_fd_flat(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ x, const double* __restrict__ Y, double* __restrict__ J,
                  int p0, int np, const int* __restrict__ dirs, int ndirs) {
     const long gid = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -502,11 +522,82 @@ k_points_fd_flat(DevTables T, DevLayout L, FdSettings fd, const double* __restri
     double* Jp = J + (size_t)j * L.n_out * L.n_in;
     for (int o = 0; o < L.n_out; ++o) Jp[(size_t)o * L.n_in + a] = Jc[o];
 }
+// Central differences with the two sides of a direction on adjacent lanes (lane ^ 1): each lane evaluates one side per
+// refinement pass, the pair exchanges the group's outputs by shuffle and both derive the same refined step — the
+// arithmetic and its order are those of fd_group, the dependent chain per thread is half as long.
+template <class F>
+__device__ inline void fd_group_central_pair(F&& f, const FdSettings& fd, double* in, int a, const double* y0, int lo, int hi, double* yo,
+                                             double* Jcol, int side) {
+    const double x0 = in[a];
+    double h = fd.h;
+    for (int iter = 0;; ++iter) {
+        in[a] = side ? x0 + h : x0 - h;
+        f(in, yo);
+        in[a] = x0;
+        double u = 0;
+        for (int o = lo; o < hi; ++o) {
+            const double mine = yo[o];
+            const double other = __shfl_xor_sync(0xffffffffu, mine, 1);
+            const double vf = side ? mine : other, vb = side ? other : mine, vc = y0[o];
+            if (!isfinite(vf) || !isfinite(vc) || !isfinite(vb)) { Jcol[o] = NAN; u = -1; continue; }
+            Jcol[o] = (vf - vb) / (2 * h);
+            const double et = vf - 2 * vc + vb;
+            const double er = fd.reltol / h * fmax(fabs(vf - vc), fabs(vc - vb)) + fd.abstol;
+            if (u >= 0) u = fmax(u, fabs(et / er));
+        }
+        if (iter == fd.h_iter) break;
+        if (u < 0) h /= fd.u_aim;
+        else h *= sqrt(fd.u_aim / fmax(1.0, u));
+    }
+}
+template <int MINB>
+__global__ void __launch_bounds__(64, MINB)
+k_points_fd_flat_pair(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ x, const double* __restrict__ Y,
+                      double* __restrict__ J, int p0, int np, const int* __restrict__ dirs, int ndirs) {
+    const long total = (long)np * ndirs * 2;
+    long gid = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = gid < total;
+    if (!valid) gid = total - 1 - ((threadIdx.x ^ 1) & 1); // tail lanes shadow the last pair (every lane joins the shuffles)
+    const int side = (int)(gid & 1);
+    const long item = gid >> 1;
+    const int j = p0 + (int)(item / ndirs);
+    const int a = dirs[item % ndirs];
+    double in[MOCOB200_MAX_IN];
+    double yo[MOCOB200_MAX_OUT], Jc[MOCOB200_MAX_OUT];
+    gather_inputs(L, x, j, in);
+    const double* y0 = Y + (size_t)j * L.n_out;
+    const int ngroups = 1 + L.n_integrand;
+    for (int gidx = 0; gidx < ngroups; ++gidx) {
+        const unsigned mask = 1u << gidx;
+        const int lo = gidx == 0 ? 0 : L.n_dyn_out + gidx - 1;
+        const int hi = gidx == 0 ? L.n_dyn_out : lo + 1;
+        fd_group_central_pair([&](const double* xin, double* yout) { eval_point(T, xin, yout, mask); }, fd, in, a, y0, lo, hi, yo, Jc, side);
+    }
+    if (!valid || side) return;
+    double* Jp = J + (size_t)j * L.n_out * L.n_in;
+    for (int o = 0; o < L.n_out; ++o) Jp[(size_t)o * L.n_in + a] = Jc[o];
+}
 void launch_points_fd_flat(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, const double* d_Y, double* d_J,
                            int p0, int np, cudaStream_t s, const int* d_dirs, int ndirs) {
     const long n = (long)np * ndirs;
     if (n <= 0) return;
-    k_points_fd_flat<<<(unsigned)((n + 63) / 64), 64, 0, s>>>(T, L, fd, d_x, d_Y, d_J, p0, np, d_dirs, ndirs);
+    // MOCOB200_FLAT_MINBLOCKS: resident 64-thread blocks per SM the register allocation must allow (4: 255 registers,
+    // 8: 128 registers); MOCOB200_FLAT_PAIR=0: central differences with both sides on one thread.
+    // Measured on config 5 (profiles/flat_variants_r01.txt): unpaired 4 -> 427 Jac/s, 8 -> 381; paired 4 -> 493, 8 -> 632:
+    // the paired kernel has twice the threads, and only the 128-register build keeps them all resident in one wave.
+    static const bool pair = [] { const char* e = getenv("MOCOB200_FLAT_PAIR"); return !e || atoi(e) != 0; }();
+    const bool paired = fd.scheme == MOCOB200_FD_CENTRAL && pair;
+    static const int minbEnv = [] { const char* e = getenv("MOCOB200_FLAT_MINBLOCKS"); return e ? atoi(e) : 0; }();
+    const int minb = minbEnv ? minbEnv : (paired ? 8 : 4);
+    if (paired) {
+        const unsigned nb = (unsigned)((2 * n + 63) / 64);
+        if (minb == 8) k_points_fd_flat_pair<8><<<nb, 64, 0, s>>>(T, L, fd, d_x, d_Y, d_J, p0, np, d_dirs, ndirs);
+        else k_points_fd_flat_pair<4><<<nb, 64, 0, s>>>(T, L, fd, d_x, d_Y, d_J, p0, np, d_dirs, ndirs);
+        return;
+    }
+    const unsigned nb = (unsigned)((n + 63) / 64);
+    if (minb == 8) k_points_fd_flat<8><<<nb, 64, 0, s>>>(T, L, fd, d_x, d_Y, d_J, p0, np, d_dirs, ndirs);
+    else k_points_fd_flat<4><<<nb, 64, 0, s>>>(T, L, fd, d_x, d_Y, d_J, p0, np, d_dirs, ndirs);
 }
 
 void launch_points_fd(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, double* d_Y, double* d_J, int p0,
@@ -529,7 +620,8 @@ void launch_endpoint(const DevTables& T, const DevLayout& L, const FdSettings& f
 void launch_assemble_g(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_Y, const double* d_G, double* d_g,
                        cudaStream_t s) {
     if (L.n_con <= 0) return;
-    k_assemble_g<<<(L.n_con + 127) / 128, 128, 0, s>>>(T, L, d_x, d_Y, d_G, d_g);
+    k_assemble_g<<<(L.n_con + 127) / 128, 128, 0, s>>>(L, d_x, d_Y, d_G, d_g);
+    if (L.n_path_rows > 0) k_assemble_g_path<<<(L.n_con + 127) / 128, 128, 0, s>>>(T, L, d_x, d_g);
 }
 void launch_assemble_f(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_G, double* d_f, cudaStream_t s) {
     k_assemble_f<<<1, 32, 0, s>>>(T, L, d_x, d_G, d_f);
@@ -537,7 +629,8 @@ void launch_assemble_f(const DevTables& T, const DevLayout& L, const double* d_x
 void launch_assemble_jac(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, const double* d_Y, const double* d_J,
                          const double* d_I, const double* d_E, double* d_vals, cudaStream_t s) {
     if (L.nnz <= 0) return;
-    k_assemble_jac<<<(L.nnz + 255) / 256, 256, 0, s>>>(T, L, fd, d_x, d_Y, d_J, d_I, d_E, d_vals);
+    k_assemble_jac<<<(L.nnz + 255) / 256, 256, 0, s>>>(L, d_x, d_Y, d_J, d_I, d_E, d_vals);
+    if (L.n_path_rows > 0) k_assemble_jac_path<<<(L.nnz + 255) / 256, 256, 0, s>>>(T, L, fd, d_x, d_vals);
 }
 void launch_assemble_grad(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_Y, const double* d_J, const double* d_I,
                           const double* d_E, double* d_grad, cudaStream_t s) {

@@ -40,6 +40,7 @@ struct DevLayout {
     const RowMetaD* rows; const ColMetaD* cols;
     const int* colptr; const int* rowidx; const int* nnzcol;
     int n_eout_total; // total outputs over all goals
+    int n_path_rows;  // path-constraint equations per mesh point (0: no path-constraint kernels are launched)
 };
 
 void launch_points_nominal(const DevTables& T, const DevLayout& L, const double* d_x, double* d_Y, int p0, int np, cudaStream_t s);
