@@ -296,7 +296,7 @@ def main():
             "gpu_launches": int(launches),
             "roofline": {"bound": "fp64", "kernel": "point-function FD stage: " + (
                              "k_wpoints_fd1<0> then <1>,<2>,<3> side by side (warp per evaluation)" if ev.point_evals_per_jacobian() / eff <= 30000
-                             else "k_wpoints_nominal then k_points_fd_flat + k_wlocal_central side by side"), "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                             else "k_wpoints_nominal then k_points_fd_flat_pair<8> (thread per (point, direction, side)) + k_wlocal_central side by side"), "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                          "frac": achieved / peak, "peak_source": "FP64 FMA saturation kernel measured in this process "
                          "(MEASURED_PEAKS.json has no FP64 entry)", "kernel_ms": kern_ms, "assemble_kernel_ms": asm_ms,
                          "flop_per_launch": flops_rank, "flop_per_point_eval": fc["all"]["flop"],
