@@ -585,10 +585,11 @@ void launch_points_fd_flat(const DevTables& T, const DevLayout& L, const FdSetti
     // 8: 128 registers); MOCOB200_FLAT_PAIR=0: central differences with both sides on one thread.
     // Measured on config 5 (profiles/flat_variants_r01.txt): unpaired 4 -> 427 Jac/s, 8 -> 381; paired 4 -> 493, 8 -> 632:
     // the paired kernel has twice the threads, and only the 128-register build keeps them all resident in one wave.
-    static const bool pair = [] { const char* e = getenv("MOCOB200_FLAT_PAIR"); return !e || atoi(e) != 0; }();
-    const bool paired = fd.scheme == MOCOB200_FD_CENTRAL && pair;
-    static const int minbEnv = [] { const char* e = getenv("MOCOB200_FLAT_MINBLOCKS"); return e ? atoi(e) : 0; }();
-    const int minb = minbEnv ? minbEnv : (paired ? 8 : 4);
+    // (read per launch so that tests can switch them; steady-state launches are CUDA-graph replays)
+    const char* ePair = getenv("MOCOB200_FLAT_PAIR");
+    const bool paired = fd.scheme == MOCOB200_FD_CENTRAL && (!ePair || atoi(ePair) != 0);
+    const char* eMinb = getenv("MOCOB200_FLAT_MINBLOCKS");
+    const int minb = eMinb && atoi(eMinb) > 0 ? atoi(eMinb) : (paired ? 8 : 4);
     if (paired) {
         const unsigned nb = (unsigned)((2 * n + 63) / 64);
         if (minb == 8) k_points_fd_flat_pair<8><<<nb, 64, 0, s>>>(T, L, fd, d_x, d_Y, d_J, p0, np, d_dirs, ndirs);

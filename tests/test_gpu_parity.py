@@ -177,6 +177,27 @@ def test_local_columns_central_scheme(pkg, name, kernel, monkeypatch):
     assert np.max(np.abs(Jr - Jr0) / scale) < 1e-5
 
 
+@pytest.mark.parametrize("name", ["gait2d_prediction", "hanging_muscle", "pendulum3_implicit", "pendulum_cb_both"])
+def test_paired_central_differences_are_bit_identical(pkg, name, monkeypatch):
+    """The thread kernel puts the two sides of a central difference on adjacent lanes (k_points_fd_flat_pair): same
+    arithmetic in the same order as one thread doing both sides, with CasADi's step refinement and without; an odd
+    number of (point, direction) items exercises the shadow lanes of the last warp."""
+    monkeypatch.setenv("MOCOB200_KERNEL", "thread")
+    monkeypatch.setenv("MOCOB200_GRAPH", "0")
+    p = load(pkg, name, 3)
+    x = p.make_iterate(seed=12, spread=0.5)
+    out = {}
+    for pair in ("1", "0"):
+        monkeypatch.setenv("MOCOB200_FLAT_PAIR", pair)
+        ev = pkg.Evaluator(p)
+        ev.set_fd(FD_CENTRAL)
+        a = ev.eval_points(x, jacobian=True)
+        ev.set_fd(FD_CENTRAL, 1e-3, 0)
+        out[pair] = (a, ev.eval_points(x, jacobian=True), ev.eval_jac_g(x))
+    for a, b in zip(out["1"], out["0"]):
+        assert np.array_equal(a, b, equal_nan=True)
+
+
 @pytest.mark.parametrize("name", ["gait2d_tracking", "hanging_muscle", "pendulum3_implicit"])
 def test_graph_replay_equals_kernel_by_kernel_launches(pkg, name, monkeypatch):
     """The captured CUDA graph of the Jacobian pipeline, replayed on changing iterates and after a change of the FD
