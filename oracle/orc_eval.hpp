@@ -5,7 +5,10 @@
 
 namespace orc {
 
-// SimTK::SmoothSphereHalfSpaceForce (Simbody 3.7; source NOT in the reference tree — PARITY UNPINNED).
+// SimTK::SmoothSphereHalfSpaceForce (Simbody 3.7; source NOT in the reference tree). Pinned against data the reference
+// produced with it — example2DWalking's referenceGRF.sto along referenceCoordinates.sto: normal force 0.25 % rms of peak,
+// friction loosely (the files hold no speeds; tests/test_oracle_known_answers.py) — but not to round-off: bit-level parity
+// with Simbody stays UNPINNED.
 // Restated from the model description cited by
 // opensim-core/OpenSim/Simulation/Model/SmoothSphereHalfSpaceForce.h:28-66 (Serrancoli et al. 2019) and the
 // parameter plumbing in SmoothSphereHalfSpaceForce.cpp:50-94. The half space fills +X of its frame, so the

@@ -256,3 +256,35 @@ def test_contact_force_behaviour(orc):
     u[1] = 0.5  # sliding forward well above the transition speed (0.2): friction = (mu_d + mu_v v) fn, backwards
     f, _ = o.contact(0, q, u)
     assert f[0] < 0 and abs(f[0]) == pytest.approx((0.8 + 0.5 * math.sqrt(0.25 + 1e-5)) * f[1] * 0.5 / math.sqrt(0.25 + 1e-5), rel=1e-9)
+
+
+def test_contact_forces_reproduce_the_reference_grf_file(orc):
+    """Golden data produced by the reference itself: example2DWalking's referenceGRF.sto holds the ground-reaction forces
+    that Simbody's SmoothSphereHalfSpaceForce gave along referenceCoordinates.sto in a Moco simulation of 2D_gait.osim
+    (both files in Moco/Examples/C++/example2DWalking; fixture made by scripts/make_grf_fixture.py). The files carry no
+    speeds, so they are taken from a cubic spline through the 50 coordinate rows: the normal (vertical) force, which is set
+    by the penetration depth, is reproduced to 0.25 % rms of its 1138 N peak; the friction force depends on the tangential
+    velocity through tanh(v / v_t) and is only loosely determined at the rows around heel strike."""
+    import json
+
+    from scipy.interpolate import CubicSpline
+
+    d = json.load(open(golden("gait2d_reference_grf.json")))
+    t, q, G = np.array(d["time"]), np.array(d["q"]), np.array(d["grf_r_xy_l_xy"])
+    u = CubicSpline(t, q)(t, 1)
+    o = orc.Oracle(golden("gait2d_tracking.mb20"))
+    # 2D_gait.osim order: contactHeel_r, contactHeel_l, contactFront_r, contactFront_l ; force on the sphere (= on the foot)
+    F = np.array([[o.contact(c, q[i], u[i])[0][:2] for c in range(4)] for i in range(len(t))])
+    right, left = F[:, 0] + F[:, 2], F[:, 1] + F[:, 3]
+    for mine, ref in ((right, G[:, 0:2]), (left, G[:, 2:4])):
+        peak = np.abs(ref[:, 1]).max()
+        dv = mine[:, 1] - ref[:, 1]
+        assert np.sqrt(np.mean(dv ** 2)) < 0.005 * peak
+        assert np.abs(dv).max() < 0.02 * peak
+        # friction: same sign and size away from the impact transients
+        dh = mine[:, 0] - ref[:, 0]
+        assert np.median(np.abs(dh)) < 0.01 * np.abs(ref[:, 0]).max()
+    # mid-stance rows, where the speeds from the spline are good: both components to better than 1 N
+    for i in (10, 30, 40, 49):
+        assert np.allclose(right[i], G[i, 0:2], atol=1.5, rtol=5e-3)
+        assert np.allclose(left[i], G[i, 2:4], atol=1.5, rtol=5e-3)
