@@ -101,7 +101,8 @@ struct mocob200_handle {
     long graphLaunches = 0;
     bool graphFailed = false;
     bool allowGraph = true; // read at create: MOCOB200_GRAPH=0 or MOCOB200_TIMING=1 turn the graph off
-    cudaEvent_t evY = nullptr, evE = nullptr;
+    cudaEvent_t evY = nullptr, evE = nullptr, evJ = nullptr, evI = nullptr;
+    bool ecHasIntegrand = false; // some endpoint-constraint goal has an integrand: jac_g needs dI/dt0, dI/dtf
     double* d_I2 = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     long launches = 0;
@@ -363,7 +364,10 @@ bool runNominal(mocob200_handle* h) {
     }
     return true;
 }
-bool runFd(mocob200_handle* h) {
+// deferIntegralDerivs: the caller (the jac_g pipeline) does not read dI/dt0, dI/dtf — they are computed on the side stream
+// beside its assembly kernel and the caller joins on h->evI afterwards. Returns through *deferred whether that happened.
+bool runFd(mocob200_handle* h, bool deferIntegralDerivs = false, bool* deferred = nullptr) {
+    if (deferred) *deferred = false;
     recTiming(h->ev[0], h->stream);
     if (h->rank >= h->eff) { recTiming(h->ev[1], h->stream); return true; } // idle rank
     const bool overlap = h->eff == 1; // single rank: Y is complete as soon as the nominal evaluations are
@@ -396,7 +400,13 @@ bool runFd(mocob200_handle* h) {
         launch_integrals(h->DL, h->d_x, h->d_Y, h->d_J, h->d_I2, false, h->stream2);
         launch_endpoint(h->DT, h->DL, h->fd, h->d_x, h->d_I2, h->d_G, h->d_E, true, h->stream2);
         cudaEventRecord(h->evE, h->stream2);
-        launch_integrals(h->DL, h->d_x, h->d_Y, h->d_J, h->d_I, true, h->stream);
+        if (deferIntegralDerivs && deferred && h->L.n_integrand > 0) {
+            cudaEventRecord(h->evJ, h->stream);
+            cudaStreamWaitEvent(h->stream2, h->evJ, 0);
+            launch_integrals(h->DL, h->d_x, h->d_Y, h->d_J, h->d_I, true, h->stream2);
+            cudaEventRecord(h->evI, h->stream2);
+            *deferred = true;
+        } else launch_integrals(h->DL, h->d_x, h->d_Y, h->d_J, h->d_I, true, h->stream);
         cudaStreamWaitEvent(h->stream, h->evE, 0);
         h->launches += 2 * (h->L.n_integrand > 0) + (h->DL.n_eout_total > 0);
         return true;
@@ -449,6 +459,8 @@ void mocob200_destroy(mocob200_handle* h) {
     for (auto& e : h->side.join) if (e) cudaEventDestroy(e);
     if (h->evY) cudaEventDestroy(h->evY);
     if (h->evE) cudaEventDestroy(h->evE);
+    if (h->evJ) cudaEventDestroy(h->evJ);
+    if (h->evI) cudaEventDestroy(h->evI);
     if (h->stream2) cudaStreamDestroy(h->stream2);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -569,6 +581,12 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     for (auto& e : h->side.join) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&h->evY, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&h->evE, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&h->evJ, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&h->evI, cudaEventDisableTiming);
+    for (int g = 0; g < T->ngoal; ++g) {
+        const int* gr = T->idx + T->o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
+        if (gr[1] == MOCOB200_MODE_ENDPOINT_CONSTRAINT && gr[3]) h->ecHasIntegrand = true;
+    }
     defaultFd(h->fd, R->fd_scheme);
     // shard grid points evenly over ranks
     h->shard.resize(world + 1);
@@ -768,13 +786,15 @@ int mocob200_eval_grad_f(mocob200_handle* h, const double* x, double* grad) {
 }
 
 static bool jacPipelineLaunches(mocob200_handle* h, double* d_vals) {
-    if (!runFd(h)) return false;
+    bool deferred = false;
+    if (!runFd(h, !h->ecHasIntegrand, &deferred)) return false;
     if (h->rank == 0) {
         recTiming(h->ev[2], h->stream);
         launch_assemble_jac(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_I, h->d_E, d_vals, h->stream);
         recTiming(h->ev[3], h->stream);
         h->launches += 1 + (h->DL.n_path_rows > 0);
     }
+    if (deferred) cudaStreamWaitEvent(h->stream, h->evI, 0); // d_I (for a grad_f at the same x) complete; side stream rejoined
     return true;
 }
 // The Jacobian pipeline (FD kernels on three streams, integrals, endpoint functions, assembly: 8-9 launches and a dozen
