@@ -101,7 +101,7 @@ struct mocob200_handle {
     long graphLaunches = 0;
     bool graphFailed = false;
     bool allowGraph = true; // read at create: MOCOB200_GRAPH=0 or MOCOB200_TIMING=1 turn the graph off
-    cudaEvent_t evY = nullptr, evE = nullptr, evJ = nullptr, evI = nullptr;
+    cudaEvent_t evY = nullptr, evE = nullptr, evJ = nullptr, evI = nullptr, evX = nullptr;
     bool ecHasIntegrand = false; // some endpoint-constraint goal has an integrand: jac_g needs dI/dt0, dI/dtf
     double* d_I2 = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -371,6 +371,17 @@ bool runFd(mocob200_handle* h, bool deferIntegralDerivs = false, bool* deferred 
     recTiming(h->ev[0], h->stream);
     if (h->rank >= h->eff) { recTiming(h->ev[1], h->stream); return true; } // idle rank
     const bool overlap = h->eff == 1; // single rank: Y is complete as soon as the nominal evaluations are
+    // jac_g pipeline without integrand-carrying endpoint constraints: the endpoint functions that read only x (periodicity,
+    // initial activation ...) start now, beside the point kernels; the integrand goals' blocks feed grad_f only and run
+    // beside the assembly (measured: waiting for one k_endpoint launch after the FD stage cost 14 us of a 131 us step)
+    const bool split = overlap && deferIntegralDerivs && deferred && h->DL.n_eout_total > 0;
+    if (split) {
+        cudaEventRecord(h->evX, h->stream);
+        cudaStreamWaitEvent(h->stream2, h->evX, 0);
+        launch_endpoint(h->DT, h->DL, h->fd, h->d_x, h->d_I2, h->d_G, h->d_E, true, h->stream2, 1);
+        cudaEventRecord(h->evE, h->stream2);
+        h->launches++;
+    }
     if (h->warpFor(mocob200_point_evals_per_jacobian(h) / h->eff))
         h->launches += launch_wpoints_fd(h->DT, h->WA, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_cfg, h->p0, h->p1 - h->p0, h->stream,
                                          overlap ? h->evY : nullptr, &h->side);
@@ -398,13 +409,13 @@ bool runFd(mocob200_handle* h, bool deferIntegralDerivs = false, bool* deferred 
     if (overlap) {
         cudaStreamWaitEvent(h->stream2, h->evY, 0);
         launch_integrals(h->DL, h->d_x, h->d_Y, h->d_J, h->d_I2, false, h->stream2);
-        launch_endpoint(h->DT, h->DL, h->fd, h->d_x, h->d_I2, h->d_G, h->d_E, true, h->stream2);
-        cudaEventRecord(h->evE, h->stream2);
-        if (deferIntegralDerivs && deferred && h->L.n_integrand > 0) {
+        launch_endpoint(h->DT, h->DL, h->fd, h->d_x, h->d_I2, h->d_G, h->d_E, true, h->stream2, split ? 2 : 0);
+        if (!split) cudaEventRecord(h->evE, h->stream2);
+        if (deferIntegralDerivs && deferred) {
             cudaEventRecord(h->evJ, h->stream);
             cudaStreamWaitEvent(h->stream2, h->evJ, 0);
             launch_integrals(h->DL, h->d_x, h->d_Y, h->d_J, h->d_I, true, h->stream2);
-            cudaEventRecord(h->evI, h->stream2);
+            cudaEventRecord(h->evI, h->stream2); // everything queued on stream2 is done: the caller joins on it
             *deferred = true;
         } else launch_integrals(h->DL, h->d_x, h->d_Y, h->d_J, h->d_I, true, h->stream);
         cudaStreamWaitEvent(h->stream, h->evE, 0);
@@ -460,6 +471,7 @@ void mocob200_destroy(mocob200_handle* h) {
     if (h->evY) cudaEventDestroy(h->evY);
     if (h->evE) cudaEventDestroy(h->evE);
     if (h->evJ) cudaEventDestroy(h->evJ);
+    if (h->evX) cudaEventDestroy(h->evX);
     if (h->evI) cudaEventDestroy(h->evI);
     if (h->stream2) cudaStreamDestroy(h->stream2);
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -582,6 +594,7 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     cudaEventCreateWithFlags(&h->evY, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&h->evE, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&h->evJ, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&h->evX, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&h->evI, cudaEventDisableTiming);
     for (int g = 0; g < T->ngoal; ++g) {
         const int* gr = T->idx + T->o_goal_i + g * MOCOB200_GOAL_ISTRIDE;

@@ -178,13 +178,15 @@ __device__ inline bool endpoint_reads(const DevTables& T, const DevLayout& L, in
 }
 
 // one block per goal; thread a < n_ein = FD direction, thread n_ein = nominal evaluation.
+// which: 0 = every goal, 1 = only goals without an integrand (functions of x alone), 2 = only goals with one.
 __global__ void k_endpoint(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ x, const double* __restrict__ I,
-                           double* __restrict__ G, double* __restrict__ E, int withFd) {
+                           double* __restrict__ G, double* __restrict__ E, int withFd, int which) {
     extern __shared__ double sh[]; // [n_ein] nominal inputs, then [nout] nominal outputs
     const int g = blockIdx.x;
     const int a = threadIdx.x;
     const int nout = T.idx[T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE + 2];
     if (T.idx[T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE + 1] == MOCOB200_MODE_PATH_CONSTRAINT) return; // not an endpoint function (whole block)
+    if (which && (which == 1) == (L.goal_integrand[g] >= 0)) return;                                  // not this launch's share
     double* sh_in = sh;
     double* sh_g0 = sh + L.n_ein;
     {   // cooperative gather of [t0, x0, c0, d0, tf, xf, cf, df, integral]
@@ -613,10 +615,10 @@ void launch_integrals(const DevLayout& L, const double* d_x, const double* d_Y, 
     k_integrals<<<L.n_integrand, 256, 0, s>>>(L, d_x, d_Y, d_J, d_I, withJ ? 1 : 0);
 }
 void launch_endpoint(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, const double* d_I, double* d_G,
-                     double* d_E, bool withFd, cudaStream_t s) {
+                     double* d_E, bool withFd, cudaStream_t s, int which) {
     if (L.n_eout_total <= 0) return;
     const int bs = ((L.n_ein + 1 + 31) / 32) * 32;
-    k_endpoint<<<T.ngoal, bs, (L.n_ein + MOCOB200_MAX_EOUT) * sizeof(double), s>>>(T, L, fd, d_x, d_I, d_G, d_E, withFd ? 1 : 0);
+    k_endpoint<<<T.ngoal, bs, (L.n_ein + MOCOB200_MAX_EOUT) * sizeof(double), s>>>(T, L, fd, d_x, d_I, d_G, d_E, withFd ? 1 : 0, which);
 }
 void launch_assemble_g(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_Y, const double* d_G, double* d_g,
                        cudaStream_t s) {

@@ -57,8 +57,9 @@ int launch_wlocal(const DevTables& T, const WarpAux& A, const DevLayout& L, cons
 // integrals[n_integrand], dIdt0[n_integrand], dIdtf[n_integrand] (derivative parts need J)
 void launch_integrals(const DevLayout& L, const double* d_x, const double* d_Y, const double* d_J, double* d_I, bool withJ, cudaStream_t s);
 // G[n_eout_total] values and E[n_eout_total][n_ein] FD blocks of every goal's endpoint function
+// which: 0 = every goal, 1 = only the goals without an integrand (they read x alone), 2 = only the goals with one
 void launch_endpoint(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, const double* d_I, double* d_G,
-                     double* d_E, bool withFd, cudaStream_t s);
+                     double* d_E, bool withFd, cudaStream_t s, int which = 0);
 void launch_assemble_g(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_Y, const double* d_G, double* d_g,
                        cudaStream_t s);
 void launch_assemble_f(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_G, double* d_f /*[1+n_cost_terms]*/, cudaStream_t s);
