@@ -164,6 +164,14 @@ int mocob200_layout_structure(const mocob200_tables*, const mocob200_transcripti
  * about the midpoint (createRandomIterateWithinBounds, :1151-1177). */
 int mocob200_make_iterate(const mocob200_tables*, const mocob200_transcription*, long seed, double spread, double* x);
 
+/* Guesses and solutions as MocoTrajectory tables (.sto; Moco/Moco/MocoTrajectory.cpp:610-860, setGuessFile of
+ * MocoCasADiSolver.h:162-202): write = one row per grid point, columns time | states | controls | derivatives with the num_*
+ * metadata; read = columns matched by name and resampled onto this problem's grid with the interpolating spline
+ * MocoTrajectory::resample uses (degree min(rows-1, 5)); t0/tf from the first/last row. Host only; the problem must carry
+ * variable names (created from a model, not loaded from a .mb20 file). */
+int mocob200_iterate_write_sto(const mocob200_problem*, const double* x, const char* path);
+int mocob200_iterate_read_sto(const mocob200_problem*, const char* path, double* x, char* err, int errlen);
+
 /* Number of ranks that actually get grid points: min(world, n_grid / 384) but at least 1 (MOCOB200_MIN_POINTS_PER_RANK
  * overrides the 384) — a rank is only worth its launch + gather latency with about one wave of work; the remaining
  * ranks idle (the reference caps its worker threads the same way, MocoCasADiSolver.cpp:127-143). */

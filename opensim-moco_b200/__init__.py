@@ -26,6 +26,7 @@ ABI_SYMBOLS = [
     "mocob200_eval_grad_f", "mocob200_eval_jac_g", "mocob200_eval_jac_g_device", "mocob200_eval_g_device",
     "mocob200_sync", "mocob200_mark", "mocob200_elapsed_ms", "mocob200_launch_count", "mocob200_last_kernel_ms",
     "mocob200_point_evals_per_jacobian", "mocob200_measure_fp64_peak", "mocob200_shard_range", "mocob200_effective_world", "mocob200_set_sparsity_detection",
+    "mocob200_iterate_write_sto", "mocob200_iterate_read_sto",
 ]
 
 
@@ -92,6 +93,8 @@ def lib():
         L.mocob200_point_evals_per_jacobian.argtypes = [vp]
         L.mocob200_point_evals_per_jacobian.restype = C.c_long
         L.mocob200_measure_fp64_peak.argtypes = [C.c_int, dp]
+        L.mocob200_iterate_write_sto.argtypes = [vp, dp, C.c_char_p]
+        L.mocob200_iterate_read_sto.argtypes = [vp, C.c_char_p, dp, C.c_char_p, C.c_int]
         _lib = L
     return _lib
 
@@ -169,6 +172,22 @@ class Problem:
         rc = lib().mocob200_make_iterate(self.tables, self.transcription, seed, spread, _dptr(x))
         if rc:
             raise RuntimeError("mocob200_make_iterate failed (%d)" % rc)
+        return x
+
+    def write_sto(self, x, path):
+        """MocoTrajectory::write of the iterate x (one row per grid point)."""
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        rc = lib().mocob200_iterate_write_sto(self._h, _dptr(x), str(path).encode())
+        if rc:
+            raise RuntimeError("mocob200_iterate_write_sto failed (%d)" % rc)
+
+    def read_sto(self, path):
+        """setGuessFile: a MocoTrajectory table resampled onto this problem's grid, as the NLP vector x."""
+        x = np.zeros(self.dims().n_var)
+        err = C.create_string_buffer(512)
+        rc = lib().mocob200_iterate_read_sto(self._h, str(path).encode(), _dptr(x), err, 512)
+        if rc:
+            raise RuntimeError("mocob200_iterate_read_sto: %s" % err.value.decode())
         return x
 
     def close(self):

@@ -125,6 +125,107 @@ const mocob200_transcription* mocob200_problem_transcription(const mocob200_prob
 void mocob200_problem_destroy(mocob200_problem* p) { delete p; }
 
 // names as '\n'-joined strings: which = 0 states, 1 controls, 2 derivatives(aux)
+// ---- guesses / solutions as MocoTrajectory tables ------------------------------------------------
+namespace {
+// derivative variable names in NLP order: implicit-mode accelerations ("/speed" -> "/accel", MocoCasOCProblem.cpp) then the
+// implicit auxiliary derivatives
+std::vector<std::string> derivativeNamesOf(const FlatProblem& fp) {
+    std::vector<std::string> v;
+    if (fp.tr.dynamics_mode == MOCOB200_DYNAMICS_IMPLICIT)
+        for (int k = 0; k < fp.tables.nq; ++k) {
+            std::string n = fp.stateNames[fp.tables.nq + k];
+            const size_t at = n.rfind("/speed");
+            if (at != std::string::npos) n.replace(at, 6, "/accel");
+            v.push_back(n);
+        }
+    v.insert(v.end(), fp.derivativeNames.begin(), fp.derivativeNames.end());
+    return v;
+}
+} // namespace
+
+// MocoTrajectory::write (MocoTrajectory.cpp:780-860): one row per grid point, columns time | states | controls |
+// [multipliers: none] | derivatives | [slacks, parameters: none], metadata num_* in the header.
+int mocob200_iterate_write_sto(const mocob200_problem* p, const double* x, const char* path) {
+    if (!p || !x || !path) return MOCOB200_ERR_ARG;
+    const FlatProblem& fp = *p->fp;
+    try {
+        const Layout L = buildLayout(fp.tables, fp.tr, false);
+        if ((int)fp.stateNames.size() != L.ns || (int)fp.controlNames.size() != L.nc) return MOCOB200_ERR_UNSUPPORTED; // no names (loaded .mb20)
+        const std::vector<std::string> dn = derivativeNamesOf(fp);
+        if ((int)dn.size() != L.nd) return MOCOB200_ERR_UNSUPPORTED;
+        FILE* f = std::fopen(path, "w");
+        if (!f) return MOCOB200_ERR_IO;
+        std::fprintf(f, "inDegrees=no\nnum_controls=%d\nnum_derivatives=%d\nnum_multipliers=0\nnum_parameters=0\nnum_slacks=0\n"
+                        "num_states=%d\nDataType=double\nversion=3\nOpenSimVersion=mocob200\nendheader\ntime", L.nc, L.nd, L.ns);
+        for (auto& n : fp.stateNames) std::fprintf(f, "\t%s", n.c_str());
+        for (auto& n : fp.controlNames) std::fprintf(f, "\t%s", n.c_str());
+        for (auto& n : dn) std::fprintf(f, "\t%s", n.c_str());
+        std::fprintf(f, "\n");
+        for (int j = 0; j < L.n_grid; ++j) {
+            std::fprintf(f, "%.17g", x[0] + (x[1] - x[0]) * L.grid[j]);
+            for (int k = 0; k < L.ns; ++k) std::fprintf(f, "\t%.17g", x[L.off_states + (size_t)j * L.ns + k]);
+            for (int k = 0; k < L.nc; ++k) std::fprintf(f, "\t%.17g", x[L.off_controls + (size_t)j * L.nc + k]);
+            for (int k = 0; k < L.nd; ++k) std::fprintf(f, "\t%.17g", x[L.off_derivs + (size_t)j * L.nd + k]);
+            std::fprintf(f, "\n");
+        }
+        std::fclose(f);
+        return MOCOB200_OK;
+    } catch (const std::exception&) { return MOCOB200_ERR_UNSUPPORTED; }
+}
+
+// setGuessFile + the resampling of the guess onto the solver's grid (MocoTrajectory(file) .cpp:662-760, isCompatible,
+// resample :610-662 with GCVSplineSet(table, {}, min(rows - 1, 5)); CasOCTranscription.cpp:595-597). Initial and final
+// time come from the first and last row; every variable of the problem must have a column of its name.
+int mocob200_iterate_read_sto(const mocob200_problem* p, const char* path, double* x, char* err, int errlen) {
+    if (!p || !path || !x) return MOCOB200_ERR_ARG;
+    const FlatProblem& fp = *p->fp;
+    try {
+        const Layout L = buildLayout(fp.tables, fp.tr, false);
+        if ((int)fp.stateNames.size() != L.ns || (int)fp.controlNames.size() != L.nc)
+            throw std::runtime_error("the problem carries no variable names (loaded from a .mb20 file)");
+        const StoTable t = readSto(path);
+        const int rows = (int)t.time.size();
+        if (rows < 1) throw std::runtime_error("no rows in '" + std::string(path) + "'");
+        std::vector<std::string> names = fp.stateNames;
+        names.insert(names.end(), fp.controlNames.begin(), fp.controlNames.end());
+        const std::vector<std::string> dn = derivativeNamesOf(fp);
+        names.insert(names.end(), dn.begin(), dn.end());
+        std::vector<int> col(names.size());
+        for (size_t k = 0; k < names.size(); ++k) {
+            col[k] = t.col(names[k]);
+            if (col[k] < 0) throw std::runtime_error("guess is not compatible with the problem: no column '" + names[k] + "'");
+        }
+        const double t0 = t.time.front(), tf = t.time.back();
+        x[0] = t0; x[1] = tf;
+        // same time grid (a solution of this very transcription): copy; otherwise interpolate with the natural spline
+        bool sameGrid = rows == L.n_grid;
+        for (int j = 0; sameGrid && j < rows; ++j)
+            sameGrid = std::fabs(t.time[j] - (t0 + (tf - t0) * L.grid[j])) <= 1e-12 * std::fmax(1.0, std::fabs(tf));
+        for (int j = 1; j < rows; ++j)
+            if (!(t.time[j] > t.time[j - 1]) && !(tf == t0)) throw std::runtime_error("guess times must increase");
+        if (!sameGrid && rows > 400) throw std::runtime_error("resampling a guess of more than 400 rows onto another grid is not supported");
+        for (size_t k = 0; k < names.size(); ++k) {
+            const std::vector<double>& y = t.cols[col[k]];
+            PiecewisePoly pp;
+            if (!sameGrid && rows > 1 && tf > t0) pp = fitNaturalSpline(t.time, y, std::min(rows - 1, 5));
+            for (int j = 0; j < L.n_grid; ++j) {
+                double v;
+                if (sameGrid) v = y[j];
+                else if (rows == 1 || !(tf > t0)) v = y[0]; // all times equal: constant (MocoTrajectory.cpp:623-641)
+                else v = evalPiecewisePoly(pp, t0 + (tf - t0) * L.grid[j]);
+                const int kk = (int)k;
+                if (kk < L.ns) x[L.off_states + (size_t)j * L.ns + kk] = v;
+                else if (kk < L.ns + L.nc) x[L.off_controls + (size_t)j * L.nc + (kk - L.ns)] = v;
+                else x[L.off_derivs + (size_t)j * L.nd + (kk - L.ns - L.nc)] = v;
+            }
+        }
+        return MOCOB200_OK;
+    } catch (const std::exception& e) {
+        setErr(err, errlen, e.what());
+        return MOCOB200_ERR_IO;
+    }
+}
+
 int mocob200_problem_names(const mocob200_problem* p, int which, char* buf, int buflen) {
     if (!p || !buf) return MOCOB200_ERR_ARG;
     const auto& v = which == 0 ? p->fp->stateNames : which == 1 ? p->fp->controlNames : p->fp->derivativeNames;

@@ -1,0 +1,70 @@
+"""Guess / solution files: MocoTrajectory tables written and read by the host library
+(Moco/Moco/MocoTrajectory.cpp:610-860; setGuessFile, MocoCasADiSolver.h:162-202). CPU only."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import golden
+
+
+def _example(pkg, intervals):
+    return pkg.Problem.example("pendulum:3", ".", "multibody_dynamics_mode=implicit;num_mesh_intervals=%d" % intervals)
+
+
+def test_write_then_read_is_the_identity(pkg, tmp_path):
+    p = _example(pkg, 12)
+    x = p.make_iterate(seed=3, spread=0.5)
+    path = tmp_path / "iterate.sto"
+    p.write_sto(x, path)
+    head = open(path).read().split("endheader")[0]
+    # the metadata MocoTrajectory's file constructor reads (MocoTrajectory.cpp:664-692)
+    for key in ("num_states=6", "num_controls=3", "num_derivatives=3", "num_multipliers=0", "num_slacks=0", "num_parameters=0",
+                "inDegrees=no", "DataType=double", "version=3"):
+        assert key in head
+    labels = open(path).read().split("endheader\n")[1].split("\n")[0].split("\t")
+    assert labels[0] == "time" and labels[1] == "/jointset/j0/q0/value" and labels[7] == "/tau0"
+    assert labels[10] == "/jointset/j0/q0/accel"  # implicit mode: acceleration variables named after the speeds
+    assert np.array_equal(p.read_sto(path), x)
+
+
+def test_guess_is_resampled_onto_the_grid(pkg, tmp_path):
+    """MocoTrajectory::resample: interpolating spline of degree min(rows - 1, 5) through the table, evaluated at the grid
+    times between the first and the last row (CasOCTranscription.cpp:595-597)."""
+    p = _example(pkg, 12)
+    d = p.dims()
+    x = p.make_iterate(seed=3, spread=0.5)
+    t = x[0] + (x[1] - x[0]) * np.linspace(0, 1, d.n_grid)
+    for k in range(d.ns):
+        x[2 + np.arange(d.n_grid) * d.ns + k] = np.sin(1.3 * t + k)
+    off_c = 2 + d.ns * d.n_grid
+    for k in range(d.nc):
+        x[off_c + np.arange(d.n_grid) * d.nc + k] = np.cos(0.7 * t + k)
+    path = tmp_path / "guess.sto"
+    p.write_sto(x, path)
+    q = _example(pkg, 17)
+    dq = q.dims()
+    xr = q.read_sto(path)
+    assert (xr[0], xr[1]) == (x[0], x[1])
+    tq = x[0] + (x[1] - x[0]) * np.linspace(0, 1, dq.n_grid)
+    for k in range(d.ns):
+        assert np.abs(xr[2 + np.arange(dq.n_grid) * d.ns + k] - np.sin(1.3 * tq + k)).max() < 1e-4
+    off_cq = 2 + d.ns * dq.n_grid
+    for k in range(d.nc):
+        assert np.abs(xr[off_cq + np.arange(dq.n_grid) * d.nc + k] - np.cos(0.7 * tq + k)).max() < 1e-4
+    # the table's own rows are interpolated exactly
+    assert xr[2] == pytest.approx(x[2], abs=1e-12)
+
+
+def test_incompatible_or_nameless_guesses_are_refused(pkg, tmp_path):
+    """MocoTrajectory::isCompatible: every variable of the problem needs a column of its name. The file here is the head of
+    a solution written by the reference itself (Moco/Tests/std_testMocoInverse_subject_18musc_solution.sto), so the header
+    parser also sees the reference's metadata lines (objective=, status=, num_iterations= ...)."""
+    p = _example(pkg, 5)
+    with pytest.raises(RuntimeError, match="no column '/jointset/j0/q0/value'"):
+        p.read_sto(golden("moco_trajectory_head.sto"))
+    loaded = pkg.Problem.load(golden("pendulum3_implicit.mb20"))  # .mb20 files hold numbers only
+    with pytest.raises(RuntimeError, match="no variable names"):
+        loaded.read_sto(golden("moco_trajectory_head.sto"))
+    with pytest.raises(RuntimeError):
+        p.read_sto(os.path.join(str(tmp_path), "does_not_exist.sto"))
