@@ -204,15 +204,19 @@ int mocob200_iterate_read_sto(const mocob200_problem* p, const char* path, doubl
         for (int j = 1; j < rows; ++j)
             if (!(t.time[j] > t.time[j - 1]) && !(tf == t0)) throw std::runtime_error("guess times must increase");
         if (!sameGrid && rows > 400) throw std::runtime_error("resampling a guess of more than 400 rows onto another grid is not supported");
+        std::vector<PiecewisePoly> pps;
+        if (!sameGrid && rows > 1 && tf > t0) { // one factorisation for all columns
+            std::vector<const std::vector<double>*> ys;
+            for (size_t k = 0; k < names.size(); ++k) ys.push_back(&t.cols[col[k]]);
+            pps = fitNaturalSplines(t.time, ys, std::min(rows - 1, 5));
+        }
         for (size_t k = 0; k < names.size(); ++k) {
             const std::vector<double>& y = t.cols[col[k]];
-            PiecewisePoly pp;
-            if (!sameGrid && rows > 1 && tf > t0) pp = fitNaturalSpline(t.time, y, std::min(rows - 1, 5));
             for (int j = 0; j < L.n_grid; ++j) {
                 double v;
                 if (sameGrid) v = y[j];
                 else if (rows == 1 || !(tf > t0)) v = y[0]; // all times equal: constant (MocoTrajectory.cpp:623-641)
-                else v = evalPiecewisePoly(pp, t0 + (tf - t0) * L.grid[j]);
+                else v = evalPiecewisePoly(pps[k], t0 + (tf - t0) * L.grid[j]);
                 const int kk = (int)k;
                 if (kk < L.ns) x[L.off_states + (size_t)j * L.ns + kk] = v;
                 else if (kk < L.ns + L.nc) x[L.off_controls + (size_t)j * L.nc + (kk - L.ns)] = v;

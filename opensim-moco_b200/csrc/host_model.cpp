@@ -128,7 +128,34 @@ StoTable readSto(const std::string& path) {
 // ---------------------------------------------------------------- natural spline fit
 // Interpolating natural spline of odd degree d = 2m-1 (GCVSPL with zero smoothing,
 // opensim-core/OpenSim/Common/GCVSpline.cpp + gcvspl.c), as a piecewise polynomial.
-static void solveDense(std::vector<double>& A, std::vector<double>& b, int n) {
+static void solveDense(std::vector<double>& A, std::vector<double>& b, int n, int nrhs = 1) {
+    if (nrhs != 1) { // same elimination, right-hand sides stored row-major b[n][nrhs]
+        for (int c = 0; c < n; ++c) {
+            int piv = c;
+            double best = std::fabs(A[(size_t)c * n + c]);
+            for (int r = c + 1; r < n; ++r)
+                if (std::fabs(A[(size_t)r * n + c]) > best) { best = std::fabs(A[(size_t)r * n + c]); piv = r; }
+            if (best == 0) throw std::runtime_error("fitNaturalSpline: singular system");
+            if (piv != c) {
+                for (int k = 0; k < n; ++k) std::swap(A[(size_t)piv * n + k], A[(size_t)c * n + k]);
+                for (int k = 0; k < nrhs; ++k) std::swap(b[(size_t)piv * nrhs + k], b[(size_t)c * nrhs + k]);
+            }
+            const double inv = 1.0 / A[(size_t)c * n + c];
+            for (int r = c + 1; r < n; ++r) {
+                const double f = A[(size_t)r * n + c] * inv;
+                if (f == 0) continue;
+                for (int k = c; k < n; ++k) A[(size_t)r * n + k] -= f * A[(size_t)c * n + k];
+                for (int k = 0; k < nrhs; ++k) b[(size_t)r * nrhs + k] -= f * b[(size_t)c * nrhs + k];
+            }
+        }
+        for (int r = n - 1; r >= 0; --r)
+            for (int q = 0; q < nrhs; ++q) {
+                double s = b[(size_t)r * nrhs + q];
+                for (int k = r + 1; k < n; ++k) s -= A[(size_t)r * n + k] * b[(size_t)k * nrhs + q];
+                b[(size_t)r * nrhs + q] = s / A[(size_t)r * n + r];
+            }
+        return;
+    }
     for (int c = 0; c < n; ++c) {
         int piv = c;
         double best = std::fabs(A[(size_t)c * n + c]);
@@ -155,14 +182,20 @@ static void solveDense(std::vector<double>& A, std::vector<double>& b, int n) {
 }
 
 PiecewisePoly fitNaturalSpline(const std::vector<double>& t, const std::vector<double>& y, int degree) {
-    const int n = (int)t.size();
-    if (n < 2 || (int)y.size() != n) throw std::runtime_error("fitNaturalSpline: need >= 2 samples");
+    return fitNaturalSplines(t, {&y}, degree)[0];
+}
+// several data columns over the same abscissae: one factorisation of the (data-independent) system
+std::vector<PiecewisePoly> fitNaturalSplines(const std::vector<double>& t, const std::vector<const std::vector<double>*>& ys, int degree) {
+    const int n = (int)t.size(), nrhs = (int)ys.size();
+    if (nrhs < 1) return {};
+    for (auto* y : ys)
+        if (n < 2 || (int)y->size() != n) throw std::runtime_error("fitNaturalSpline: need >= 2 samples");
     int d = degree;
     if (d % 2 == 0) d -= 1;
     while (d > 1 && n < d + 1) d -= 2; // GCVSPL needs n >= 2m
     const int m = (d + 1) / 2, np = n - 1, nc = d + 1, N = np * nc;
     // unknowns: coefficient j of piece k in the local coordinate s = (t - t_k)/h_k in [0,1]
-    std::vector<double> A((size_t)N * N, 0.0), b(N, 0.0);
+    std::vector<double> A((size_t)N * N, 0.0), b((size_t)N * nrhs, 0.0);
     auto dcoef = [](int j, int r) { // d^r/ds^r s^j at s = 1 -> j!/(j-r)!
         double c = 1;
         for (int q = 0; q < r; ++q) c *= (j - q);
@@ -170,35 +203,42 @@ PiecewisePoly fitNaturalSpline(const std::vector<double>& t, const std::vector<d
     };
     int row = 0;
     for (int k = 0; k < np; ++k) { // interpolation at both ends of each piece
-        A[(size_t)row * N + k * nc + 0] = 1; b[row++] = y[k];
+        A[(size_t)row * N + k * nc + 0] = 1;
+        for (int q = 0; q < nrhs; ++q) b[(size_t)row * nrhs + q] = (*ys[q])[k];
+        ++row;
         for (int j = 0; j < nc; ++j) A[(size_t)row * N + k * nc + j] = 1;
-        b[row++] = y[k + 1];
+        for (int q = 0; q < nrhs; ++q) b[(size_t)row * nrhs + q] = (*ys[q])[k + 1];
+        ++row;
     }
     for (int k = 0; k + 1 < np; ++k) { // continuity of derivatives 1..d-1 at interior knots
         const double hk = t[k + 1] - t[k], hn = t[k + 2] - t[k + 1];
         for (int r = 1; r <= d - 1; ++r) {
             for (int j = r; j < nc; ++j) A[(size_t)row * N + k * nc + j] = dcoef(j, r) / std::pow(hk, r);
             A[(size_t)row * N + (k + 1) * nc + r] = -dcoef(r, r) / std::pow(hn, r);
-            b[row++] = 0;
+            ++row;
         }
     }
     for (int r = m; r <= d - 1; ++r) { // natural end conditions
-        A[(size_t)row * N + 0 * nc + r] = dcoef(r, r); b[row++] = 0;
+        A[(size_t)row * N + 0 * nc + r] = dcoef(r, r);
+        ++row;
         for (int j = r; j < nc; ++j) A[(size_t)row * N + (np - 1) * nc + j] = dcoef(j, r);
-        b[row++] = 0;
+        ++row;
     }
     if (row != N) throw std::runtime_error("fitNaturalSpline: internal row count");
-    solveDense(A, b, N);
-    PiecewisePoly pp;
-    pp.order = nc;
-    pp.breaks = t;
-    pp.coef.resize((size_t)N);
-    for (int k = 0; k < np; ++k) {
-        const double hk = t[k + 1] - t[k];
-        for (int j = 0; j < nc; ++j) pp.coef[(size_t)k * nc + j] = b[k * nc + j] / std::pow(hk, j);
+    solveDense(A, b, N, nrhs);
+    std::vector<PiecewisePoly> out(nrhs);
+    for (int q = 0; q < nrhs; ++q) {
+        PiecewisePoly& pp = out[q];
+        pp.order = nc;
+        pp.breaks = t;
+        pp.coef.resize((size_t)N);
+        for (int k = 0; k < np; ++k) {
+            const double hk = t[k + 1] - t[k];
+            for (int j = 0; j < nc; ++j) pp.coef[(size_t)k * nc + j] = b[(size_t)(k * nc + j) * nrhs + q] / std::pow(hk, j);
+        }
+        pp.isSpline = true;
     }
-    pp.isSpline = true;
-    return pp;
+    return out;
 }
 
 PiecewisePoly constantFunction(double v) {

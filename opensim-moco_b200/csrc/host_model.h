@@ -131,6 +131,7 @@ struct PiecewisePoly { // value(t) on [breaks[k], breaks[k+1]) = sum_j coef[k*or
 };
 // natural interpolating spline of odd degree (what GCVSPL returns for zero smoothing), as a piecewise polynomial
 PiecewisePoly fitNaturalSpline(const std::vector<double>& t, const std::vector<double>& y, int degree);
+std::vector<PiecewisePoly> fitNaturalSplines(const std::vector<double>& t, const std::vector<const std::vector<double>*>& ys, int degree);
 double evalPiecewisePoly(const PiecewisePoly& pp, double t, int deriv = 0);
 
 struct GoalSpec {
