@@ -752,28 +752,35 @@ int mocob200_eval_points(mocob200_handle* h, int what, const double* x, double* 
 int mocob200_eval_g(mocob200_handle* h, const double* x, double* g) {
     if (!h) return MOCOB200_ERR_ARG;
     cudaSetDevice(h->device);
-    if (!stageX(h, x) || !bcastX(h, h->d_x) || !runNominal(h)) return MOCOB200_ERR_CUDA;
+    // IPOPT asks for f, g, grad_f and jac_g at the same x one after the other: the point outputs and endpoint values of
+    // the last evaluation are reused when x has not changed (x_cached non-empty <=> d_Y, d_G hold the values at x_cached)
+    const bool reuse = h->eff == 1 && sameX(h, x);
+    if (!reuse && (!stageX(h, x) || !bcastX(h, h->d_x) || !runNominal(h))) return MOCOB200_ERR_CUDA;
     if (h->rank == 0) {
         launch_assemble_g(h->DT, h->DL, h->d_x, h->d_Y, h->d_G, h->d_g, h->stream);
         h->launches += 1 + (h->DL.n_path_rows > 0);
         if (g) cudaMemcpyAsync(g, h->d_g, sizeof(double) * h->L.n_con, cudaMemcpyDeviceToHost, h->stream);
     }
-    h->x_cached.clear();
-    return finish(h, "eval_g") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
+    if (!reuse) h->x_cached.clear();
+    if (!finish(h, "eval_g")) return MOCOB200_ERR_CUDA;
+    if (!reuse && h->eff == 1) rememberX(h, x, false);
+    return MOCOB200_OK;
 }
 
 int mocob200_eval_f(mocob200_handle* h, const double* x, double* f, double* f_terms) {
     if (!h) return MOCOB200_ERR_ARG;
     cudaSetDevice(h->device);
-    if (!stageX(h, x) || !bcastX(h, h->d_x) || !runNominal(h)) return MOCOB200_ERR_CUDA;
+    const bool reuse = h->eff == 1 && sameX(h, x);
+    if (!reuse && (!stageX(h, x) || !bcastX(h, h->d_x) || !runNominal(h))) return MOCOB200_ERR_CUDA;
     std::vector<double> host(1 + h->L.n_cost_terms, 0.0);
     if (h->rank == 0) {
         launch_assemble_f(h->DT, h->DL, h->d_x, h->d_G, h->d_f, h->stream);
         h->launches++;
         cudaMemcpyAsync(host.data(), h->d_f, sizeof(double) * host.size(), cudaMemcpyDeviceToHost, h->stream);
     }
-    h->x_cached.clear();
+    if (!reuse) h->x_cached.clear();
     if (!finish(h, "eval_f")) return MOCOB200_ERR_CUDA;
+    if (!reuse && h->eff == 1) rememberX(h, x, false);
     if (h->rank == 0) {
         if (f) *f = host[0];
         if (f_terms) for (int k = 0; k < h->L.n_cost_terms; ++k) f_terms[k] = host[1 + k];

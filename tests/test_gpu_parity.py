@@ -198,6 +198,35 @@ def test_paired_central_differences_are_bit_identical(pkg, name, monkeypatch):
         assert np.array_equal(a, b, equal_nan=True)
 
 
+@pytest.mark.parametrize("name", ["gait2d_tracking", "hanging_muscle", "pendulum_cb_both"])
+def test_same_x_reuses_the_last_evaluation(pkg, name):
+    """IPOPT's call pattern: f, g, grad_f, jac_g at one x. The point outputs and endpoint values of the last evaluation are
+    reused while x is unchanged (fewer launches, identical results); a different x recomputes."""
+    p = load(pkg, name)
+    x, x2 = p.make_iterate(seed=21, spread=0.4), p.make_iterate(seed=22, spread=0.4)
+    fresh = pkg.Evaluator(p)
+    want = dict(f=fresh.eval_f(x), g=pkg.Evaluator(p).eval_g(x), grad=pkg.Evaluator(p).eval_grad_f(x), jac=pkg.Evaluator(p).eval_jac_g(x))
+    ev = pkg.Evaluator(p)
+    n0 = ev.launch_count()
+    g = ev.eval_g(x)
+    n1 = ev.launch_count()
+    f = ev.eval_f(x)
+    g_again = ev.eval_g(x)
+    n2 = ev.launch_count()
+    assert n2 - n1 < n1 - n0, "same x: only the assembly kernels run"
+    assert f == want["f"] and np.array_equal(g, want["g"]) and np.array_equal(g_again, want["g"])
+    jac = ev.eval_jac_g(x)
+    n3 = ev.launch_count()
+    grad, f3, g3 = ev.eval_grad_f(x), ev.eval_f(x), ev.eval_g(x)
+    assert ev.launch_count() - n3 <= 5
+    assert np.array_equal(jac, want["jac"], equal_nan=True) and np.array_equal(grad, want["grad"], equal_nan=True)
+    assert f3 == want["f"] and np.array_equal(g3, want["g"])
+    # a new x invalidates everything
+    assert np.array_equal(ev.eval_g(x2), pkg.Evaluator(p).eval_g(x2))
+    assert np.array_equal(ev.eval_jac_g(x2), pkg.Evaluator(p).eval_jac_g(x2), equal_nan=True)
+    assert ev.eval_f(x) == want["f"]
+
+
 @pytest.mark.parametrize("name", ["gait2d_tracking", "hanging_muscle", "pendulum3_implicit"])
 def test_graph_replay_equals_kernel_by_kernel_launches(pkg, name, monkeypatch):
     """The captured CUDA graph of the Jacobian pipeline, replayed on changing iterates and after a change of the FD
