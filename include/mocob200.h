@@ -210,7 +210,12 @@ int mocob200_eval_jac_g(mocob200_handle*, const double* x, double* values);
  * (device pointers; used by bench.py's device-resident timing and by callers that chain kernels). */
 int mocob200_eval_jac_g_device(mocob200_handle*, const double* d_x, double* d_values, void* cuda_stream);
 int mocob200_eval_g_device(mocob200_handle*, const double* d_x, double* d_g, void* cuda_stream);
-/* the *_device calls only enqueue work on the handle's stream: */
+/* n independent single-rank problems on one device evaluated side by side (one handle each; each on its own stream,
+ * forked from and joined to handles[0]'s stream, so mocob200_mark / mocob200_sync on handles[0] cover the batch).
+ * d_values may be NULL (or hold NULL entries): results stay in the handles' own buffers. Replaces running one
+ * reference process per study (one NLP per MocoCasADiSolver::solveImpl, MocoCasADiSolver.cpp:312-415). */
+int mocob200_eval_jac_g_batch(mocob200_handle* const* handles, int n, const double* const* d_x, double* const* d_values);
+/* the *_device and *_batch calls only enqueue work on the handle's stream: */
 int mocob200_sync(mocob200_handle*);
 int mocob200_mark(mocob200_handle*, int which /*0 start, 1 stop*/); /* CUDA-event stopwatch on that stream */
 int mocob200_elapsed_ms(mocob200_handle*, float* ms);

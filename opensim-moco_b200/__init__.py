@@ -24,6 +24,7 @@ ABI_SYMBOLS = [
     "mocob200_create", "mocob200_nccl_unique_id", "mocob200_destroy", "mocob200_last_error", "mocob200_get_dims",
     "mocob200_set_fd", "mocob200_jac_g_structure", "mocob200_eval_points", "mocob200_eval_f", "mocob200_eval_g",
     "mocob200_eval_grad_f", "mocob200_eval_jac_g", "mocob200_eval_jac_g_device", "mocob200_eval_g_device",
+    "mocob200_eval_jac_g_batch",
     "mocob200_sync", "mocob200_mark", "mocob200_elapsed_ms", "mocob200_launch_count", "mocob200_last_kernel_ms",
     "mocob200_point_evals_per_jacobian", "mocob200_measure_fp64_peak", "mocob200_shard_range", "mocob200_effective_world", "mocob200_set_sparsity_detection",
     "mocob200_iterate_write_sto", "mocob200_iterate_read_sto",
@@ -84,6 +85,7 @@ def lib():
         L.mocob200_eval_jac_g.argtypes = [vp, vp, vp]
         L.mocob200_eval_jac_g_device.argtypes = [vp, vp, vp, vp]
         L.mocob200_eval_g_device.argtypes = [vp, vp, vp, vp]
+        L.mocob200_eval_jac_g_batch.argtypes = [C.POINTER(vp), C.c_int, C.POINTER(vp), C.POINTER(vp)]
         L.mocob200_sync.argtypes = [vp]
         L.mocob200_mark.argtypes = [vp, C.c_int]
         L.mocob200_elapsed_ms.argtypes = [vp, C.POINTER(C.c_float)]
@@ -326,3 +328,15 @@ def measure_fp64_peak(device=0):
     if rc:
         raise RuntimeError("mocob200_measure_fp64_peak failed (%d)" % rc)
     return t.value
+
+
+def eval_jac_g_batch(evaluators, d_x_ptrs, d_vals_ptrs=None):
+    """mocob200_eval_jac_g_batch: independent problems side by side; only enqueues (sync / mark on evaluators[0])."""
+    n = len(evaluators)
+    hs = (C.c_void_p * n)(*[e._h for e in evaluators])
+    xs = (C.c_void_p * n)(*[C.c_void_p(p) for p in d_x_ptrs])
+    vs = (C.c_void_p * n)(*[C.c_void_p(p) if p else None for p in d_vals_ptrs]) if d_vals_ptrs is not None else None
+    rc = lib().mocob200_eval_jac_g_batch(hs, n, xs, vs)
+    if rc != 0:
+        raise RuntimeError("eval_jac_g_batch failed (%d): %s" % (rc, "; ".join(
+            (lib().mocob200_last_error(e._h) or b"").decode() for e in evaluators)))

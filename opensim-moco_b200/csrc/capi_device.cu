@@ -102,6 +102,7 @@ struct mocob200_handle {
     bool graphFailed = false;
     bool allowGraph = true; // read at create: MOCOB200_GRAPH=0 or MOCOB200_TIMING=1 turn the graph off
     cudaEvent_t evY = nullptr, evE = nullptr, evJ = nullptr, evI = nullptr, evX = nullptr;
+    cudaEvent_t evBatch = nullptr; // fork / join event of mocob200_eval_jac_g_batch
     bool ecHasIntegrand = false; // some endpoint-constraint goal has an integrand: jac_g needs dI/dt0, dI/dtf
     double* d_I2 = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -472,6 +473,7 @@ void mocob200_destroy(mocob200_handle* h) {
     if (h->evE) cudaEventDestroy(h->evE);
     if (h->evJ) cudaEventDestroy(h->evJ);
     if (h->evX) cudaEventDestroy(h->evX);
+    if (h->evBatch) cudaEventDestroy(h->evBatch);
     if (h->evI) cudaEventDestroy(h->evI);
     if (h->stream2) cudaStreamDestroy(h->stream2);
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -595,6 +597,7 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     cudaEventCreateWithFlags(&h->evE, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&h->evJ, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&h->evX, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&h->evBatch, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&h->evI, cudaEventDisableTiming);
     for (int g = 0; g < T->ngoal; ++g) {
         const int* gr = T->idx + T->o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
@@ -873,6 +876,39 @@ int mocob200_eval_jac_g_device(mocob200_handle* h, const double* d_x, double* d_
     if (!bcastX(h, d_x)) return MOCOB200_ERR_CUDA;
     if (!jacPipeline(h, d_values ? d_values : h->d_vals)) return MOCOB200_ERR_CUDA;
     return h->ck(cudaGetLastError(), "eval_jac_g_device") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
+}
+
+// n independent problems (one handle each, single-rank, same device) evaluated side by side: every handle's pipeline
+// is queued on its own stream behind a fork point on hs[0]'s stream, and hs[0]'s stream waits for all of them, so a
+// mocob200_mark pair / mocob200_sync on hs[0] brackets the whole batch. The reference runs one NLP per process and
+// fans its point functions over threads (CasOCTranscription.cpp:1179-1212); one config-3 Jacobian leaves most of a
+// B200 idle (SURVEY 8(d) sizing caveat), independent studies (multi-start, parameter sweeps) fill it.
+int mocob200_eval_jac_g_batch(mocob200_handle* const* hs, int n, const double* const* d_x, double* const* d_values) {
+    if (!hs || n <= 0 || !d_x) return MOCOB200_ERR_ARG;
+    for (int k = 0; k < n; ++k) {
+        if (!hs[k] || !d_x[k]) return MOCOB200_ERR_ARG;
+        if (hs[k]->world != 1 || hs[k]->device != hs[0]->device) {
+            hs[k]->err = "eval_jac_g_batch: handles must be single-rank and on one device";
+            return MOCOB200_ERR_ARG;
+        }
+        for (int j = 0; j < k; ++j) if (hs[j] == hs[k]) { hs[k]->err = "eval_jac_g_batch: a handle appears twice"; return MOCOB200_ERR_ARG; }
+    }
+    mocob200_handle* h0 = hs[0];
+    cudaSetDevice(h0->device);
+    if (!h0->ck(cudaEventRecord(h0->evBatch, h0->stream), "batch fork")) return MOCOB200_ERR_CUDA;
+    for (int k = 0; k < n; ++k) {
+        mocob200_handle* h = hs[k];
+        if (k && !h->ck(cudaStreamWaitEvent(h->stream, h0->evBatch, 0), "batch fork wait")) return MOCOB200_ERR_CUDA;
+        h->x_cached.clear();
+        if (!bcastX(h, d_x[k])) return MOCOB200_ERR_CUDA;
+        if (!jacPipeline(h, d_values && d_values[k] ? d_values[k] : h->d_vals)) return MOCOB200_ERR_CUDA;
+    }
+    for (int k = 1; k < n; ++k) {
+        mocob200_handle* h = hs[k];
+        if (!h->ck(cudaEventRecord(h->evBatch, h->stream), "batch join")) return MOCOB200_ERR_CUDA;
+        if (!h0->ck(cudaStreamWaitEvent(h0->stream, h->evBatch, 0), "batch join wait")) return MOCOB200_ERR_CUDA;
+    }
+    return h0->ck(cudaGetLastError(), "eval_jac_g_batch") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
 }
 
 int mocob200_eval_g_device(mocob200_handle* h, const double* d_x, double* d_g, void* cuda_stream) {

@@ -509,3 +509,28 @@ def test_config5_left_right_mirror(config5):
     operm = np.concatenate([qperm, 10 + np.concatenate([np.arange(9, 18), np.arange(0, 9)])])
     a, b = Ym[:, :28], Y[:, operm]
     assert np.max(np.abs(a - b) / (np.abs(b) + 1e-6 * np.abs(b).max())) < 1e-8
+
+
+def test_batch_of_independent_problems_is_bit_identical(pkg):
+    """mocob200_eval_jac_g_batch: different problems side by side on their own streams give exactly the values each
+    handle gives alone, whatever the order of the handles; results land in the caller's buffers or stay in the handle."""
+    import torch
+
+    names = ["gait2d_hs", "double_pendulum_trap", "gait2d_hs", "sliding_mass"]
+    names = [n for n in names if n in FIXTURES] or list(FIXTURES)[:3]
+    probs = [load(pkg, n, intervals=6 + 2 * k) for k, n in enumerate(names)]
+    evs = [pkg.Evaluator(p) for p in probs]
+    xs = [p.make_iterate(seed=10 + k, spread=0.3) for k, p in enumerate(probs)]
+    alone = [ev.eval_jac_g(x).copy() for ev, x in zip(evs, xs)]
+    dx = [torch.from_numpy(x).cuda() for x in xs]
+    dv = [torch.full((ev.dims.nnz_jac,), float("nan"), dtype=torch.float64, device="cuda") for ev in evs]
+    for order in (list(range(len(evs))), list(reversed(range(len(evs))))):
+        for v in dv:
+            v.fill_(float("nan"))
+        for rep in range(3):  # the second and third pass replay the handles' CUDA graphs
+            pkg.eval_jac_g_batch([evs[k] for k in order], [dx[k].data_ptr() for k in order], [dv[k].data_ptr() for k in order])
+        evs[order[0]].sync()  # the join makes the first handle's stream wait for every other handle
+        for k in range(len(evs)):
+            assert np.array_equal(dv[k].cpu().numpy(), alone[k]), (order, k)
+    with pytest.raises(RuntimeError):
+        pkg.eval_jac_g_batch([evs[0], evs[0]], [dx[0].data_ptr()] * 2, None)
