@@ -203,7 +203,6 @@ int mocob200_iterate_read_sto(const mocob200_problem* p, const char* path, doubl
             sameGrid = std::fabs(t.time[j] - (t0 + (tf - t0) * L.grid[j])) <= 1e-12 * std::fmax(1.0, std::fabs(tf));
         for (int j = 1; j < rows; ++j)
             if (!(t.time[j] > t.time[j - 1]) && !(tf == t0)) throw std::runtime_error("guess times must increase");
-        if (!sameGrid && rows > 400) throw std::runtime_error("resampling a guess of more than 400 rows onto another grid is not supported");
         std::vector<PiecewisePoly> pps;
         if (!sameGrid && rows > 1 && tf > t0) { // one factorisation for all columns
             std::vector<const std::vector<double>*> ys;

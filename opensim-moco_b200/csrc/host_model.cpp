@@ -1,6 +1,7 @@
 #include "host_model.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <fstream>
 #include <sstream>
@@ -181,8 +182,104 @@ static void solveDense(std::vector<double>& A, std::vector<double>& b, int n, in
     }
 }
 
+// Banded LU with partial pivoting (the layout of LAPACK's dgbsv: kl sub-diagonals, ku super-diagonals, kl more for the
+// fill-in of the row exchanges). AB[i][j - i + kl] holds A(i, j) for i - kl <= j <= i + ku + kl. b is [n][nrhs].
+static void solveBanded(std::vector<double>& AB, std::vector<double>& b, int n, int kl, int ku, int nrhs) {
+    const int w = 2 * kl + ku + 1;
+    auto at = [&](int i, int j) -> double& { return AB[(size_t)i * w + (j - i + kl)]; };
+    for (int c = 0; c < n; ++c) {
+        const int rmax = std::min(n - 1, c + kl), jmax = std::min(n - 1, c + ku + kl);
+        int piv = c;
+        double best = std::fabs(at(c, c));
+        for (int r = c + 1; r <= rmax; ++r)
+            if (std::fabs(at(r, c)) > best) { best = std::fabs(at(r, c)); piv = r; }
+        if (best == 0) throw std::runtime_error("fitNaturalSpline: singular system");
+        if (piv != c) {
+            for (int j = c; j <= jmax; ++j) std::swap(at(piv, j), at(c, j));
+            for (int q = 0; q < nrhs; ++q) std::swap(b[(size_t)piv * nrhs + q], b[(size_t)c * nrhs + q]);
+        }
+        const double inv = 1.0 / at(c, c);
+        for (int r = c + 1; r <= rmax; ++r) {
+            const double f = at(r, c) * inv;
+            if (f == 0) continue;
+            for (int j = c; j <= jmax; ++j) at(r, j) -= f * at(c, j);
+            for (int q = 0; q < nrhs; ++q) b[(size_t)r * nrhs + q] -= f * b[(size_t)c * nrhs + q];
+        }
+    }
+    for (int r = n - 1; r >= 0; --r) {
+        const int jmax = std::min(n - 1, r + ku + kl);
+        for (int q = 0; q < nrhs; ++q) {
+            double v = b[(size_t)r * nrhs + q];
+            for (int j = r + 1; j <= jmax; ++j) v -= at(r, j) * b[(size_t)j * nrhs + q];
+            b[(size_t)r * nrhs + q] = v / at(r, r);
+        }
+    }
+}
+
 PiecewisePoly fitNaturalSpline(const std::vector<double>& t, const std::vector<double>& y, int degree) {
     return fitNaturalSplines(t, {&y}, degree)[0];
+}
+// The same equations as below, ordered piece by piece so that the system is banded (an equation couples one piece with
+// the next one at most): O(n) memory and time instead of the dense O(n^2) / O(n^3). Used for long tables only, so that the
+// short ones (reference data of the examples, fixtures) keep the arithmetic their golden files were written with.
+static int splineDenseMaxUnknowns() { // MOCOB200_SPLINE_DENSE_MAX=0 sends every fit through the banded solver (A-B tests)
+    const char* e = std::getenv("MOCOB200_SPLINE_DENSE_MAX");
+    return e ? std::atoi(e) : 2400; // 400 rows of degree 5
+}
+static std::vector<PiecewisePoly> fitNaturalSplinesBanded(const std::vector<double>& t, const std::vector<const std::vector<double>*>& ys, int d) {
+    const int n = (int)t.size(), nrhs = (int)ys.size();
+    const int m = (d + 1) / 2, np = n - 1, nc = d + 1, N = np * nc;
+    struct Term { int row, col; double v; };
+    std::vector<Term> terms;
+    std::vector<double> b((size_t)N * nrhs, 0.0);
+    auto dcoef = [](int j, int r) {
+        double c = 1;
+        for (int q = 0; q < r; ++q) c *= (j - q);
+        return c;
+    };
+    int row = 0;
+    for (int r = m; r <= d - 1; ++r) terms.push_back({row++, r, dcoef(r, r)}); // natural end conditions at t[0]
+    for (int k = 0; k < np; ++k) {
+        terms.push_back({row, k * nc, 1.0}); // interpolation at both ends of the piece
+        for (int q = 0; q < nrhs; ++q) b[(size_t)row * nrhs + q] = (*ys[q])[k];
+        ++row;
+        for (int j = 0; j < nc; ++j) terms.push_back({row, k * nc + j, 1.0});
+        for (int q = 0; q < nrhs; ++q) b[(size_t)row * nrhs + q] = (*ys[q])[k + 1];
+        ++row;
+        if (k + 1 < np) { // continuity of derivatives 1..d-1 with the next piece
+            const double hk = t[k + 1] - t[k], hn = t[k + 2] - t[k + 1];
+            for (int r = 1; r <= d - 1; ++r) {
+                for (int j = r; j < nc; ++j) terms.push_back({row, k * nc + j, dcoef(j, r) / std::pow(hk, r)});
+                terms.push_back({row, (k + 1) * nc + r, -dcoef(r, r) / std::pow(hn, r)});
+                ++row;
+            }
+        } else { // natural end conditions at t[n-1]
+            for (int r = m; r <= d - 1; ++r) {
+                for (int j = r; j < nc; ++j) terms.push_back({row, k * nc + j, dcoef(j, r)});
+                ++row;
+            }
+        }
+    }
+    if (row != N) throw std::runtime_error("fitNaturalSpline: internal row count");
+    int kl = 0, ku = 0;
+    for (const Term& e : terms) { kl = std::max(kl, e.row - e.col); ku = std::max(ku, e.col - e.row); }
+    const int w = 2 * kl + ku + 1;
+    std::vector<double> AB((size_t)N * w, 0.0);
+    for (const Term& e : terms) AB[(size_t)e.row * w + (e.col - e.row + kl)] = e.v;
+    solveBanded(AB, b, N, kl, ku, nrhs);
+    std::vector<PiecewisePoly> out(nrhs);
+    for (int q = 0; q < nrhs; ++q) {
+        PiecewisePoly& pp = out[q];
+        pp.order = nc;
+        pp.breaks = t;
+        pp.coef.resize((size_t)N);
+        for (int k = 0; k < np; ++k) {
+            const double hk = t[k + 1] - t[k];
+            for (int j = 0; j < nc; ++j) pp.coef[(size_t)k * nc + j] = b[(size_t)(k * nc + j) * nrhs + q] / std::pow(hk, j);
+        }
+        pp.isSpline = true;
+    }
+    return out;
 }
 // several data columns over the same abscissae: one factorisation of the (data-independent) system
 std::vector<PiecewisePoly> fitNaturalSplines(const std::vector<double>& t, const std::vector<const std::vector<double>*>& ys, int degree) {
@@ -195,6 +292,7 @@ std::vector<PiecewisePoly> fitNaturalSplines(const std::vector<double>& t, const
     while (d > 1 && n < d + 1) d -= 2; // GCVSPL needs n >= 2m
     const int m = (d + 1) / 2, np = n - 1, nc = d + 1, N = np * nc;
     // unknowns: coefficient j of piece k in the local coordinate s = (t - t_k)/h_k in [0,1]
+    if (N > splineDenseMaxUnknowns()) return fitNaturalSplinesBanded(t, ys, d);
     std::vector<double> A((size_t)N * N, 0.0), b((size_t)N * nrhs, 0.0);
     auto dcoef = [](int j, int r) { // d^r/ds^r s^j at s = 1 -> j!/(j-r)!
         double c = 1;

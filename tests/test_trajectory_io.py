@@ -56,6 +56,52 @@ def test_guess_is_resampled_onto_the_grid(pkg, tmp_path):
     assert xr[2] == pytest.approx(x[2], abs=1e-12)
 
 
+def _sine_guess(p, tmp_path, name):
+    d = p.dims()
+    x = p.make_iterate(seed=3, spread=0.5)
+    t = x[0] + (x[1] - x[0]) * np.linspace(0, 1, d.n_grid)
+    for k in range(d.ns):
+        x[2 + np.arange(d.n_grid) * d.ns + k] = np.sin(1.3 * t + k)
+    off_c = 2 + d.ns * d.n_grid
+    for k in range(d.nc):
+        x[off_c + np.arange(d.n_grid) * d.nc + k] = np.cos(0.7 * t + k)
+    path = tmp_path / name
+    p.write_sto(x, path)
+    return x, path
+
+
+def test_banded_spline_fit_equals_the_dense_one(pkg, tmp_path, monkeypatch):
+    """Long tables go through a banded factorisation of the same spline equations (piece-by-piece ordering); forced onto a
+    short table it reproduces the dense solve to round-off."""
+    x, path = _sine_guess(_example(pkg, 30), tmp_path, "guess.sto")
+    q = _example(pkg, 17)
+    dense = q.read_sto(path)
+    monkeypatch.setenv("MOCOB200_SPLINE_DENSE_MAX", "0")
+    banded = q.read_sto(path)
+    assert not np.array_equal(dense, banded)  # another elimination order
+    assert np.abs(dense - banded).max() < 1e-11
+
+
+def test_long_guess_is_resampled(pkg, tmp_path):
+    """A solution on a fine mesh as the guess of another mesh (mesh refinement): 1001 rows -> 401 and -> 1201 grid
+    points; linear cost in the number of rows."""
+    import time
+
+    x, path = _sine_guess(_example(pkg, 500), tmp_path, "fine.sto")
+    for intervals in (200, 600):
+        q = _example(pkg, intervals)
+        dq = q.dims()
+        t0 = time.perf_counter()
+        xr = q.read_sto(path)
+        assert time.perf_counter() - t0 < 5.0
+        tq = x[0] + (x[1] - x[0]) * np.linspace(0, 1, dq.n_grid)
+        for k in range(dq.ns):
+            assert np.abs(xr[2 + np.arange(dq.n_grid) * dq.ns + k] - np.sin(1.3 * tq + k)).max() < 1e-9
+        off_cq = 2 + dq.ns * dq.n_grid
+        for k in range(dq.nc):
+            assert np.abs(xr[off_cq + np.arange(dq.n_grid) * dq.nc + k] - np.cos(0.7 * tq + k)).max() < 1e-9
+
+
 def test_incompatible_or_nameless_guesses_are_refused(pkg, tmp_path):
     """MocoTrajectory::isCompatible: every variable of the problem needs a column of its name. The file here is the head of
     a solution written by the reference itself (Moco/Tests/std_testMocoInverse_subject_18musc_solution.sto), so the header
