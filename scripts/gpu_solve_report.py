@@ -1,0 +1,26 @@
+"""Sliding-mass NLP solved twice with the same host SQP loop (tests/nlp_solve.py): callbacks from the GPU evaluator and from the
+CPU oracle. Prints iterations, objective and time spent inside the callbacks -> profiles/solve_r01.json. A 65-variable problem
+is launch-latency territory: the point of the report is identical convergence, not speed."""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "tests"), os.path.join(ROOT, "oracle")]
+import __graft_entry__ as ge  # noqa: E402
+import oracle_py as O  # noqa: E402
+from nlp_solve import solve  # noqa: E402
+
+m = ge.package()
+out = []
+for scheme, n in (("trapezoidal", 20), ("hermite-simpson", 20), ("hermite-simpson", 50)):
+    p = m.Problem.example("sliding_mass", ".", "num_mesh_intervals=%d;transcription_scheme=%s" % (n, scheme))
+    row = {"problem": "sliding_mass", "scheme": scheme, "intervals": n, "n_var": p.dims().n_var, "exact_final_time": 0.4}
+    for name, ev in (("gpu", m.Evaluator(p)), ("cpu_oracle", O.Oracle(p))):
+        res, st = solve(p, ev)
+        row[name] = {"success": bool(res.success), "objective": float(res.fun), "iterations": st["iterations"],
+                     "callbacks": {k: st[k] for k in ("f", "grad", "g", "jac")}, "callback_seconds": st["t_eval"],
+                     "total_seconds": st["t_total"]}
+    row["objective_difference"] = abs(row["gpu"]["objective"] - row["cpu_oracle"]["objective"])
+    out.append(row)
+    print(json.dumps(row), flush=True)

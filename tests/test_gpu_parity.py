@@ -534,3 +534,23 @@ def test_batch_of_independent_problems_is_bit_identical(pkg):
             assert np.array_equal(dv[k].cpu().numpy(), alone[k]), (order, k)
     with pytest.raises(RuntimeError):
         pkg.eval_jac_g_batch([evs[0], evs[0]], [dx[0].data_ptr()] * 2, None)
+
+
+@pytest.mark.parametrize("name", ["gait2d_tracking", "pendulum_cb_both", "pendulum3_implicit"])
+def test_pinned_host_buffer_receives_the_same_values(pkg, name):
+    """Pinned and pageable caller buffers receive the same bits: on the first call (graph capture), on replays, when the
+    same x comes again (re-assembly only) and when the buffer changes."""
+    import torch
+
+    p = load(pkg, name)
+    ev = pkg.Evaluator(p)
+    n = ev.dims.nnz_jac
+    xs = [p.make_iterate(seed=s, spread=0.3) for s in (1, 2, 3)]
+    pageable = [ev.eval_jac_g(x).copy() for x in xs]
+    xp = [torch.from_numpy(x).pin_memory() for x in xs]
+    bufs = [torch.full((n,), float("nan"), dtype=torch.float64).pin_memory() for _ in range(2)]
+    for k in (0, 1, 2, 2, 0):  # 2, 2: same x twice
+        for b in bufs:
+            b.fill_(float("nan"))
+            ev.eval_jac_g_ptr(xp[k].data_ptr(), b.data_ptr())
+            assert np.array_equal(b.numpy(), pageable[k]), (k,)
