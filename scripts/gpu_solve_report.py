@@ -12,10 +12,15 @@ import oracle_py as O  # noqa: E402
 from nlp_solve import solve  # noqa: E402
 
 m = ge.package()
+O.set_threads(1)  # a few hundred evaluations of a 20-point problem: OpenMP fork/join would dominate the oracle's time
 out = []
-for scheme, n in (("trapezoidal", 20), ("hermite-simpson", 20), ("hermite-simpson", 50)):
-    p = m.Problem.example("sliding_mass", ".", "num_mesh_intervals=%d;transcription_scheme=%s" % (n, scheme))
-    row = {"problem": "sliding_mass", "scheme": scheme, "intervals": n, "n_var": p.dims().n_var, "exact_final_time": 0.4}
+for prob, scheme, n in (("sliding_mass", "trapezoidal", 20), ("sliding_mass", "hermite-simpson", 20),
+                        ("hanging_muscle_rigidtendon", "hermite-simpson", 10), ("hanging_muscle", "hermite-simpson", 10),
+                        ("pendulum:2", "hermite-simpson", 10)):
+    p = m.Problem.example(prob, ".", "num_mesh_intervals=%d;transcription_scheme=%s" % (n, scheme))
+    row = {"problem": prob, "scheme": scheme, "intervals": n, "n_var": p.dims().n_var}
+    if prob == "sliding_mass":
+        row["exact_final_time"] = 0.4
     for name, ev in (("gpu", m.Evaluator(p)), ("cpu_oracle", O.Oracle(p))):
         res, st = solve(p, ev)
         row[name] = {"success": bool(res.success), "objective": float(res.fun), "iterations": st["iterations"],

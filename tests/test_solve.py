@@ -51,3 +51,21 @@ def test_gpu_solve_converges_like_the_cpu_solve(pkg, orc, scheme):
     assert abs(res_g.fun - res_o.fun) < 1e-6
     assert abs(st_g["iterations"] - st_o["iterations"]) <= max(1, round(0.05 * st_o["iterations"]))
     assert np.abs(res_g.x - res_o.x).max() < 1e-4 * 50.0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["hanging_muscle_rigidtendon", "hanging_muscle", "pendulum:2"])
+def test_gpu_solve_of_muscle_and_pendulum_problems_converges_like_the_cpu_solve(pkg, orc, name):
+    """Minimum-time lift with a DeGrooteFregly2016 muscle (testMocoActuators.cpp:1088-1160; rigid tendon, and compliant tendon
+    in implicit mode) and the double pendulum: the finite-difference Jacobians of the two paths differ by round-off / h, the
+    optimisation paths must not."""
+    p = pkg.Problem.example(name, ".", "num_mesh_intervals=10")
+    orc.set_threads(1)
+    try:
+        res_o, st_o = solve(p, orc.Oracle(p), maxiter=150)
+    finally:
+        orc.set_threads(orc.max_threads())
+    res_g, st_g = solve(p, pkg.Evaluator(p), maxiter=150)
+    assert res_o.success and res_g.success, (res_o.message, res_g.message)
+    assert abs(res_g.fun - res_o.fun) < 1e-6 * max(1.0, abs(res_o.fun))
+    assert abs(st_g["iterations"] - st_o["iterations"]) <= max(1, round(0.05 * st_o["iterations"]))
