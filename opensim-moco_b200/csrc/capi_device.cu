@@ -103,6 +103,7 @@ struct mocob200_handle {
     bool allowGraph = true; // read at create: MOCOB200_GRAPH=0 or MOCOB200_TIMING=1 turn the graph off
     cudaEvent_t evY = nullptr, evE = nullptr, evJ = nullptr, evI = nullptr, evX = nullptr;
     cudaEvent_t evBatch = nullptr; // fork / join event of mocob200_eval_jac_g_batch
+    cudaEvent_t marks[2] = {nullptr, nullptr}; // mocob200_mark stopwatch (per handle: handles may sit on different devices)
     bool ecHasIntegrand = false; // some endpoint-constraint goal has an integrand: jac_g needs dI/dt0, dI/dtf
     double* d_I2 = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -474,6 +475,7 @@ void mocob200_destroy(mocob200_handle* h) {
     if (h->evJ) cudaEventDestroy(h->evJ);
     if (h->evX) cudaEventDestroy(h->evX);
     if (h->evBatch) cudaEventDestroy(h->evBatch);
+    for (auto& e : h->marks) if (e) cudaEventDestroy(e);
     if (h->evI) cudaEventDestroy(h->evI);
     if (h->stream2) cudaStreamDestroy(h->stream2);
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -928,17 +930,17 @@ int mocob200_sync(mocob200_handle* h) {
     return finish(h, "sync") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
 }
 // CUDA-event stopwatch on the handle's stream: mark(0) ... mark(1), then elapsed
-static cudaEvent_t g_marks[2] = {nullptr, nullptr};
 int mocob200_mark(mocob200_handle* h, int which) {
     if (!h || which < 0 || which > 1) return MOCOB200_ERR_ARG;
     cudaSetDevice(h->device);
-    if (!g_marks[which]) cudaEventCreate(&g_marks[which]);
-    return h->ck(cudaEventRecord(g_marks[which], h->stream), "mark") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
+    if (!h->marks[which] && !h->ck(cudaEventCreate(&h->marks[which]), "mark")) return MOCOB200_ERR_CUDA;
+    return h->ck(cudaEventRecord(h->marks[which], h->stream), "mark") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
 }
 int mocob200_elapsed_ms(mocob200_handle* h, float* ms) {
-    if (!h || !ms || !g_marks[0] || !g_marks[1]) return MOCOB200_ERR_ARG;
-    if (!h->ck(cudaEventSynchronize(g_marks[1]), "elapsed")) return MOCOB200_ERR_CUDA;
-    return h->ck(cudaEventElapsedTime(ms, g_marks[0], g_marks[1]), "elapsed") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
+    if (!h || !ms || !h->marks[0] || !h->marks[1]) return MOCOB200_ERR_ARG;
+    cudaSetDevice(h->device);
+    if (!h->ck(cudaEventSynchronize(h->marks[1]), "elapsed")) return MOCOB200_ERR_CUDA;
+    return h->ck(cudaEventElapsedTime(ms, h->marks[0], h->marks[1]), "elapsed") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
 }
 
 long mocob200_launch_count(const mocob200_handle* h) { return h ? h->launches : 0; }
