@@ -286,6 +286,8 @@ static size_t warpSmemBytes(const WarpAux& A) { return smemBytesFor(A, A.wpb); }
 // point's blob is read from L2 once and served to the other warps by L1
 static int phase1Warps(const WarpAux& A) {
     const int per = A.n_p1;
+    static const int forced = getenv("MOCOB200_P1W") ? atoi(getenv("MOCOB200_P1W")) : 0; // A-B tests: warps per phase-1 block
+    if (forced >= 1 && forced <= 32 && smemBytesFor(A, forced) <= 220 * 1024) return forced;
     return (per >= 1 && per <= 32 && smemBytesFor(A, per) <= 220 * 1024) ? per : A.wpb;
 }
 
