@@ -34,7 +34,12 @@ def _check_bang_bang(p, x, tol):
 @pytest.mark.parametrize("scheme", ["trapezoidal", "hermite-simpson"])
 def test_oracle_solves_the_sliding_mass(pkg, orc, scheme):
     p = _problem(pkg, scheme)
-    res, stats = solve(p, orc.Oracle(p))
+    nthreads = orc.max_threads()
+    orc.set_threads(1)  # a 21-point problem: OpenMP fork/join would dominate
+    try:
+        res, stats = solve(p, orc.Oracle(p))
+    finally:
+        orc.set_threads(nthreads)
     assert res.success, res.message
     _check_bang_bang(p, res.x, 1e-2)
     assert abs(res.fun - res.x[1]) < 1e-12  # MocoFinalTimeGoal
@@ -44,7 +49,12 @@ def test_oracle_solves_the_sliding_mass(pkg, orc, scheme):
 @pytest.mark.parametrize("scheme", ["trapezoidal", "hermite-simpson"])
 def test_gpu_solve_converges_like_the_cpu_solve(pkg, orc, scheme):
     p = _problem(pkg, scheme)
-    res_o, st_o = solve(p, orc.Oracle(p))
+    nthreads = orc.max_threads()
+    orc.set_threads(1)
+    try:
+        res_o, st_o = solve(p, orc.Oracle(p))
+    finally:
+        orc.set_threads(nthreads)
     res_g, st_g = solve(p, pkg.Evaluator(p))
     assert res_g.success, res_g.message
     _check_bang_bang(p, res_g.x, 1e-2)
@@ -60,11 +70,12 @@ def test_gpu_solve_of_muscle_and_pendulum_problems_converges_like_the_cpu_solve(
     in implicit mode) and the double pendulum: the finite-difference Jacobians of the two paths differ by round-off / h, the
     optimisation paths must not."""
     p = pkg.Problem.example(name, ".", "num_mesh_intervals=10")
+    nthreads = orc.max_threads()
     orc.set_threads(1)
     try:
         res_o, st_o = solve(p, orc.Oracle(p), maxiter=150)
     finally:
-        orc.set_threads(orc.max_threads())
+        orc.set_threads(nthreads)
     res_g, st_g = solve(p, pkg.Evaluator(p), maxiter=150)
     assert res_o.success and res_g.success, (res_o.message, res_g.message)
     assert abs(res_g.fun - res_o.fun) < 1e-6 * max(1.0, abs(res_o.fun))
