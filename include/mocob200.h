@@ -45,7 +45,13 @@ extern "C" {
 /* joint (mobilizer) kinds; conventions of Simbody mobilizers used by
  * opensim-core/OpenSim/Simulation/SimbodyEngine/{Pin,Slider,Planar,Weld}Joint.cpp */
 enum { MOCOB200_JOINT_WELD = 0, MOCOB200_JOINT_PIN = 1, MOCOB200_JOINT_SLIDER = 2,
-       MOCOB200_JOINT_PLANAR = 3 };
+       MOCOB200_JOINT_PLANAR = 3,
+       /* CustomJoint (SimbodyEngine/CustomJoint.cpp:205-273 -> SimTK::MobilizedBody::FunctionBased): X_FM(q) =
+        * [ R(axis0, f0) R(axis1, f1) R(axis2, f2) , axis3 f3 + axis4 f4 + axis5 f5 ], every f a scalar function of ONE of the
+        * joint's coordinates (or a constant); 1..6 coordinates; u = qdot. Record: MOCOB200_CJ_* below. */
+       MOCOB200_JOINT_CUSTOM = 4 };
+/* scalar functions of one variable used by custom joints (Common/{Constant,LinearFunction,SimmSpline,MultiplierFunction}.cpp) */
+enum { MOCOB200_FN_CONSTANT = 0 /* c1 */, MOCOB200_FN_LINEAR = 1 /* c0 x + c1 */, MOCOB200_FN_SIMMSPLINE = 2 /* spline id, scale inside */ };
 /* path point kinds (PathPoint / ConditionalPathPoint / MovingPathPoint) */
 enum { MOCOB200_PP_FIXED = 0, MOCOB200_PP_CONDITIONAL = 1, MOCOB200_PP_MOVING = 2 };
 /* goal kinds (Moco/Moco/MocoGoal) */
@@ -63,7 +69,10 @@ enum { MOCOB200_SCHEME_TRAPEZOIDAL = 0, MOCOB200_SCHEME_HERMITE_SIMPSON = 1 };
 enum { MOCOB200_DYNAMICS_EXPLICIT = 0, MOCOB200_DYNAMICS_IMPLICIT = 1 };
 enum { MOCOB200_FD_FORWARD = 0, MOCOB200_FD_CENTRAL = 1, MOCOB200_FD_BACKWARD = 2 };
 /* what mocob200_eval_points returns */
-enum { MOCOB200_POINTS_OUTPUTS = 0 /* [n_grid][n_out] */, MOCOB200_POINTS_JACOBIAN = 1 /* [n_grid][n_out][n_in] */ };
+enum { MOCOB200_POINTS_OUTPUTS = 0 /* [n_grid][n_out] */, MOCOB200_POINTS_JACOBIAN = 1 /* [n_grid][n_out][n_in] */,
+       /* [n_grid][nmus][2]: muscle-tendon path length and lengthening speed (GeometryPath.cpp:848-864, 1117-1145), what the
+        * reference's Actuation / MuscleAnalysis analyses report; single rank */
+       MOCOB200_POINTS_PATHS = 2 };
 
 /* Layout of per-entity records inside the pools.  All strides are in elements. */
 #define MOCOB200_BODY_DSTRIDE 34   /* X_PF R(9) p(3) | X_BM R(9) p(3) | mass | com(3) | inertia about origin xx yy zz xy xz yz (6) */
@@ -76,6 +85,8 @@ enum { MOCOB200_POINTS_OUTPUTS = 0 /* [n_grid][n_out] */, MOCOB200_POINTS_JACOBI
 #define MOCOB200_MUS_FLAG_IGNORE_ACTIVATION_DYNAMICS 2
 #define MOCOB200_MUS_FLAG_IGNORE_PASSIVE 4
 #define MOCOB200_MUS_FLAG_TENDON_IMPLICIT 8
+/* PathActuator (Actuators/PathActuator.cpp:156-197): tension = optimal_force (the Fmax slot) x control; no states */
+#define MOCOB200_MUS_FLAG_PATH_ACTUATOR 16
 #define MOCOB200_CONTACT_DSTRIDE 28 /* sphere centre(3) radius | halfspace R(9) p(3) | stiffness dissipation mu_s mu_d mu_v v_t c_f b_d b_v | pad(3) */
 #define MOCOB200_CONTACT_ISTRIDE 2  /* sphere body | half-space body (-1 ground) */
 #define MOCOB200_CACT_DSTRIDE 1     /* optimal force */
@@ -85,6 +96,9 @@ enum { MOCOB200_POINTS_OUTPUTS = 0 /* [n_grid][n_out] */, MOCOB200_POINTS_JACOBI
 /* payload of MOCOB200_PATHCON_CONTROL_BOUND: idx = n_eq x { control | ppoly id of the bound function } ;
  * dbl = weight(1) 0 0 | n_eq x { lower, upper } (bounds of the equation control - bound(t)) */
 #define MOCOB200_PPOLY_ISTRIDE 3    /* first break offset (rel. o_ppoly_data) | n pieces | order (coeffs per piece) */
+#define MOCOB200_CJ_DSTRIDE 30      /* 6 x { axis(3) | c0 | c1 } : rotation1..3 then translation1..3 (SpatialTransform.cpp:168-176) */
+#define MOCOB200_CJ_ISTRIDE 18      /* 6 x { function kind | q index driving it (-1: constant) | spline id (MOCOB200_FN_SIMMSPLINE) } */
+#define MOCOB200_XFORCE_ISTRIDE 12  /* applied body | force-expressed-in body (-1 ground) | point-expressed-in body | 9 ppoly ids: force xyz, point xyz, torque xyz (-1 = none) */
 
 /* A fixed-topology model + optimal control problem flattened into two pools.
  * Filled by the host flattener (the reference analogue is MocoProblemRep,
@@ -106,6 +120,13 @@ typedef struct mocob200_tables {
     int o_time_bounds; /* t0 lo,hi ; tf lo,hi */
     /* offsets into idx */
     int o_body_i, o_pp_i, o_mus_i, o_contact_i, o_cact_i, o_spline_i, o_goal_i, o_ppoly_i;
+    /* ---- format version 2 additions (all zero in version-1 problem files) ---- */
+    int ncustom;     /* custom joints */
+    int o_cj_d, o_cj_i;
+    int o_body_cj;   /* idx[nb]: custom-joint record of body b, or -1 (valid when ncustom > 0) */
+    int nxforce;     /* ExternalForce components (Model/ExternalForce.cpp:330-355): functions of time applied to a body */
+    int o_xforce_i;
+    int reserved[10];
 } mocob200_tables;
 
 /* Solver-side settings: mirrors the properties of MocoDirectCollocationSolver /
@@ -122,6 +143,14 @@ typedef struct mocob200_transcription {
     double auxderiv_bounds[2];         /* implicit_auxiliary_derivative_bounds */
     int minimize_accelerations;  double accelerations_weight;
     int minimize_auxiliary_derivatives; double auxiliary_derivatives_weight;
+    /* ---- format version 2 additions (zero in version-1 files = the solver defaults below are applied by the loader) ---- */
+    /* kinematic constraints (MocoCasADiSolver.h:115-159): enforce_constraint_derivatives, minimize_lagrange_multipliers,
+     * lagrange_multiplier_weight, velocity_correction_bounds; multiplier bounds of MocoProblem (default [-1000, 1000]) */
+    int enforce_constraint_derivatives; int minimize_lagrange_multipliers;
+    double lagrange_multiplier_weight;
+    double velocity_correction_bounds[2];
+    double multiplier_bounds[2];
+    int reserved[8];
 } mocob200_transcription;
 
 typedef struct mocob200_dims {

@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libmocob200.so")
 
 FD_FORWARD, FD_CENTRAL, FD_BACKWARD = 0, 1, 2
-POINTS_OUTPUTS, POINTS_JACOBIAN = 0, 1
+POINTS_OUTPUTS, POINTS_JACOBIAN, POINTS_PATHS = 0, 1, 2
 
 # every symbol include/mocob200.h declares (checked by tests/test_abi.py)
 ABI_SYMBOLS = [
@@ -105,6 +105,15 @@ def _dptr(a):
     return a.ctypes.data_as(C.POINTER(C.c_double))
 
 
+class Tables(C.Structure):
+    """mocob200_tables (include/mocob200.h), for reading sizes from Python."""
+    _fields_ = ([("n_dbl", C.c_int), ("n_int", C.c_int), ("dbl", C.c_void_p), ("idx", C.c_void_p)] +
+                [(n, C.c_int) for n in ("nb nq nz nc nderiv_aux nmus npp nspline ncontact ncact ngoal nppoly o_body_d o_gravity o_pp_d "
+                                        "o_mus_d o_contact_d o_cact_d o_spline_data o_ppoly_data o_bounds o_time_bounds o_body_i o_pp_i "
+                                        "o_mus_i o_contact_i o_cact_i o_spline_i o_goal_i o_ppoly_i ncustom o_cj_d o_cj_i o_body_cj nxforce "
+                                        "o_xforce_i").split()] + [("reserved", C.c_int * 10)])
+
+
 def _vptr(a):
     return C.c_void_p(a.ctypes.data) if a is not None else None
 
@@ -138,6 +147,9 @@ class Problem:
         rc = lib().mocob200_problem_save(self._h, path.encode())
         if rc:
             raise RuntimeError("mocob200_problem_save failed (%d)" % rc)
+
+    def table_sizes(self):
+        return C.cast(self.tables, C.POINTER(Tables)).contents
 
     def names(self, which):
         buf = C.create_string_buffer(1 << 16)
@@ -246,6 +258,14 @@ class Evaluator:
         out = np.empty((d.n_grid, d.n_out, d.n_in) if jacobian else (d.n_grid, d.n_out))
         self._ck(lib().mocob200_eval_points(self._h, POINTS_JACOBIAN if jacobian else POINTS_OUTPUTS, _vptr(x), _vptr(out)),
                  "eval_points")
+        return out
+
+    def eval_paths(self, x):
+        """[n_grid][nmus][2]: muscle-tendon path length and lengthening speed at every grid point."""
+        x = np.ascontiguousarray(x, np.float64)
+        nmus = self.problem.table_sizes().nmus
+        out = np.empty((self.dims.n_grid, nmus, 2))
+        self._ck(lib().mocob200_eval_points(self._h, POINTS_PATHS, _vptr(x), _vptr(out)), "eval_points(paths)")
         return out
 
     def eval_f(self, x, terms=False):

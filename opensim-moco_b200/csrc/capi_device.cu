@@ -221,7 +221,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
             else if (dirClass[d] == 1) p1Dirs.push_back(d);
             else if (dirClass[d] != 3) p2Dirs.push_back(d);
         }
-        h->WA.time_integrands_only = local ? 1 : 0;
+        h->WA.time_integrands_only = (local && T.nxforce == 0) ? 1 : 0; // external forces are functions of time
     }
     // all topology arrays live in one int pool so that a block can stage them with one copy loop
     std::vector<int> pool;
@@ -281,6 +281,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     A.o_R = take(9 * nb); A.o_p = take(3 * nb); A.o_oM = take(3 * nb); A.o_a = take(3 * nq); A.o_l = take(3 * nq);
     A.o_cg = take(3 * nb); A.o_Io = take(6 * nb); A.o_ppos = take(3 * npp); A.o_prel = take(3 * npp);
     A.o_dpl = take(3 * A.nmpp); A.o_mloc = take(3 * A.nmpp); A.o_ref = take(T.nppoly); A.o_mact = take(T.nmus); A.o_M = take(nq * nq);
+    A.o_cjs = take(30 * T.ncustom);
     A.blob_pos_end = o;
     // velocity-dependent block
     A.o_w = take(3 * nb); A.o_v = take(3 * nb); A.o_al = take(3 * nb); A.o_ac = take(3 * nb);
@@ -531,6 +532,8 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     D.o_contact_d = T->o_contact_d; D.o_cact_d = T->o_cact_d; D.o_spline_data = T->o_spline_data; D.o_ppoly_data = T->o_ppoly_data;
     D.o_body_i = T->o_body_i; D.o_pp_i = T->o_pp_i; D.o_mus_i = T->o_mus_i; D.o_contact_i = T->o_contact_i; D.o_cact_i = T->o_cact_i;
     D.o_spline_i = T->o_spline_i; D.o_goal_i = T->o_goal_i; D.o_ppoly_i = T->o_ppoly_i;
+    D.ncustom = T->ncustom; D.o_cj_d = T->o_cj_d; D.o_cj_i = T->o_cj_i; D.o_body_cj = T->o_body_cj;
+    D.nxforce = T->nxforce; D.o_xforce_i = T->o_xforce_i;
     D.implicit = L.implicit; D.n_auxres = L.n_auxres; D.n_integrand = L.n_integrand;
     // layout
     DevLayout& G = h->DL;
@@ -570,6 +573,11 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     {
         const char* k = getenv("MOCOB200_KERNEL");
         h->kernelMode = (k && std::string(k) == "thread") ? 2 : (k && std::string(k) == "warp") ? 1 : 0;
+        // the thread-per-evaluation dynamics handle the constant-axis joints only: function-based joints run on the warp kernels
+        if (T->ncustom > 0) {
+            if (h->kernelMode == 2) return fail(MOCOB200_ERR_UNSUPPORTED, "the thread-per-evaluation kernels do not support custom joints");
+            h->kernelMode = 1;
+        }
         std::string e;
         if (!buildWarpAux(h, *T, e)) return fail(MOCOB200_ERR_UNSUPPORTED, "warp kernels: " + e);
     }
@@ -746,6 +754,18 @@ int mocob200_eval_points(mocob200_handle* h, int what, const double* x, double* 
         if (h->rank == 0 && out) cudaMemcpyAsync(out, h->d_Y, sizeof(double) * L.n_grid * L.n_out, cudaMemcpyDeviceToHost, h->stream);
         rememberX(h, nullptr, false);
         h->x_cached.clear();
+    } else if (what == MOCOB200_POINTS_PATHS) {
+        if (h->world != 1) { h->err = "MOCOB200_POINTS_PATHS is single-rank"; return MOCOB200_ERR_UNSUPPORTED; }
+        const size_t n = (size_t)L.n_grid * h->DT.nmus * 2;
+        double* d_out = nullptr; // a diagnostic output: allocated per call
+        if (n == 0) return MOCOB200_OK;
+        if (!h->ck(cudaMalloc(&d_out, n * sizeof(double)), "cudaMalloc paths")) return MOCOB200_ERR_CUDA;
+        launch_paths(h->DT, h->DL, h->d_x, d_out, 0, L.n_grid, h->stream);
+        h->launches++;
+        if (out) cudaMemcpyAsync(out, d_out, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream);
+        const bool ok = finish(h, "eval_points(paths)");
+        cudaFree(d_out);
+        return ok ? MOCOB200_OK : MOCOB200_ERR_CUDA;
     } else {
         if (!runFd(h)) return MOCOB200_ERR_CUDA;
         if (h->rank == 0 && out) cudaMemcpyAsync(out, h->d_J, sizeof(double) * L.n_grid * L.n_out * L.n_in, cudaMemcpyDeviceToHost, h->stream);

@@ -47,9 +47,11 @@ int mocob200_problem_save(const mocob200_problem* p, const char* path) {
     std::ofstream f(path, std::ios::binary);
     if (!f) return MOCOB200_ERR_IO;
     const FlatProblem& fp = *p->fp;
-    unsigned magic = kMagic, ver = 1;
+    unsigned magic = kMagic, ver = 2, szT = (unsigned)sizeof(mocob200_tables), szR = (unsigned)sizeof(mocob200_transcription);
     f.write((const char*)&magic, 4);
     f.write((const char*)&ver, 4);
+    f.write((const char*)&szT, 4); // version 2: the struct sizes travel with the file, so later (appended) fields stay readable
+    f.write((const char*)&szR, 4);
     mocob200_tables t = fp.tables;
     t.dbl = nullptr; t.idx = nullptr;
     mocob200_transcription r = fp.tr;
@@ -71,11 +73,27 @@ int mocob200_problem_load_opts(const char* path, const char* options, mocob200_p
         unsigned magic = 0, ver = 0;
         f.read((char*)&magic, 4);
         f.read((char*)&ver, 4);
-        if (magic != kMagic || ver != 1) throw std::runtime_error("not a mocob200 problem file");
+        if (magic != kMagic || (ver != 1 && ver != 2)) throw std::runtime_error("not a mocob200 problem file");
+        // version 1 files hold the structs as they were then (144 / 96 bytes); later fields are appended and zero = absent
+        unsigned szT = 144, szR = 96;
+        if (ver >= 2) { f.read((char*)&szT, 4); f.read((char*)&szR, 4); }
+        if (szT > sizeof(mocob200_tables) || szR > sizeof(mocob200_transcription) || szT < 144 || szR < 96)
+            throw std::runtime_error("problem file written by a newer library");
         auto fp = std::make_unique<FlatProblem>();
-        f.read((char*)&fp->tables, sizeof fp->tables);
-        f.read((char*)&fp->tr, sizeof fp->tr);
-        if (fp->tables.n_dbl < 0 || fp->tables.n_int < 0 || fp->tr.n_mesh < 2) throw std::runtime_error("corrupt problem file");
+        std::memset(&fp->tables, 0, sizeof fp->tables);
+        std::memset(&fp->tr, 0, sizeof fp->tr);
+        f.read((char*)&fp->tables, szT);
+        f.read((char*)&fp->tr, szR);
+        if (szR < sizeof(mocob200_transcription)) { // solver defaults of the fields the file predates
+            fp->tr.enforce_constraint_derivatives = 0;
+            fp->tr.minimize_lagrange_multipliers = 0;
+            fp->tr.lagrange_multiplier_weight = 1.0;
+            fp->tr.velocity_correction_bounds[0] = -0.1; fp->tr.velocity_correction_bounds[1] = 0.1;
+            fp->tr.multiplier_bounds[0] = -1000; fp->tr.multiplier_bounds[1] = 1000;
+        }
+        if (fp->tables.n_dbl < 0 || fp->tables.n_int < 0 || fp->tr.n_mesh < 2 || fp->tables.n_dbl > (1 << 28) || fp->tables.n_int > (1 << 28) ||
+            fp->tr.n_mesh > (1 << 24))
+            throw std::runtime_error("corrupt problem file");
         fp->dbl.resize(fp->tables.n_dbl);
         fp->idx.resize(fp->tables.n_int);
         fp->mesh.resize(fp->tr.n_mesh);
@@ -83,28 +101,12 @@ int mocob200_problem_load_opts(const char* path, const char* options, mocob200_p
         f.read((char*)fp->idx.data(), (std::streamsize)(fp->idx.size() * sizeof(int)));
         f.read((char*)fp->mesh.data(), (std::streamsize)(fp->mesh.size() * sizeof(double)));
         if (!f) throw std::runtime_error("truncated problem file");
+        fp->rebind();
+        validateTables(fp->tables); // every offset/count inside the pools (a corrupt file must not become an out-of-bounds read)
         if (options && *options) {
-            SolverSettings S; // only the keys present in `options` are applied
-            S.num_mesh_intervals = -1;
-            S.transcription_scheme = "";
-            S.multibody_dynamics_mode = "";
-            S.optim_finite_difference_scheme = "";
-            S.applyOptions(options);
-            if (!S.mesh.empty()) fp->mesh = S.mesh;
-            else if (S.num_mesh_intervals > 0) {
-                fp->mesh.clear();
-                for (int i = 0; i <= S.num_mesh_intervals; ++i) fp->mesh.push_back(i / (double)S.num_mesh_intervals);
-            }
-            if (S.transcription_scheme == "trapezoidal") fp->tr.scheme = MOCOB200_SCHEME_TRAPEZOIDAL;
-            else if (S.transcription_scheme == "hermite-simpson") fp->tr.scheme = MOCOB200_SCHEME_HERMITE_SIMPSON;
-            else if (!S.transcription_scheme.empty()) throw std::runtime_error("unknown transcription_scheme");
-            if (S.multibody_dynamics_mode == "explicit") fp->tr.dynamics_mode = MOCOB200_DYNAMICS_EXPLICIT;
-            else if (S.multibody_dynamics_mode == "implicit") fp->tr.dynamics_mode = MOCOB200_DYNAMICS_IMPLICIT;
-            else if (!S.multibody_dynamics_mode.empty()) throw std::runtime_error("unknown multibody_dynamics_mode");
-            if (S.optim_finite_difference_scheme == "central") fp->tr.fd_scheme = MOCOB200_FD_CENTRAL;
-            else if (S.optim_finite_difference_scheme == "forward") fp->tr.fd_scheme = MOCOB200_FD_FORWARD;
-            else if (S.optim_finite_difference_scheme == "backward") fp->tr.fd_scheme = MOCOB200_FD_BACKWARD;
-            else if (!S.optim_finite_difference_scheme.empty()) throw std::runtime_error("unknown fd scheme");
+            SolverSettings S;
+            S.applyOptions(options); // records which keys were given; every accepted key maps onto the stored transcription
+            applySettingsToTranscription(S, *fp, /*onlyKeysGiven=*/true);
         }
         fp->rebind();
         auto p = new mocob200_problem;

@@ -344,6 +344,39 @@ std::unique_ptr<FlatProblem> gaitPrediction(const std::string& dir, const std::s
     return flatten(P, S);
 }
 
+// Replay model for the reference-held CMC / ID results of opensim-models/Pipelines/Gait10dof18musc/OutputReference
+// (CMC/walk_Setup_CMC.xml): CMC/subject01_metabolics.osim - the variant of subject01.osim (document Version 30000, CustomJoint
+// pelvis and knees; its gluteus maximus path differs) whose path speeds reproduce ResultsCMC/walk_subject_Actuation_speed.sto
+// to the file's 8 decimals, i.e. the model those results were written with - with every muscle read as a
+// PathActuator of optimal force 1 (control = recorded tension), the reserve CoordinateActuators of
+// gait10dof_Reserve_Actuators.xml, the measured ground reactions of ExperimentalData/subject01_walk_grf.xml as
+// ExternalForces, and three CoordinateActuators on the pelvis coordinates standing for the FX / FY / MZ residual
+// Point/TorqueActuators (the caller maps their recorded forces onto pelvis generalized forces). dir = .../OutputReference
+std::unique_ptr<FlatProblem> gait10dofReplay(const std::string& dir, const std::string& options) {
+    Problem P;
+    P.model = loadOsim(dir + "/CMC/subject01_metabolics.osim", /*musclesAsPathActuators=*/true);
+    appendForceSetFile(P.model, dir + "/gait10dof_Reserve_Actuators.xml");
+    const char* pelvis[3] = {"pelvis_tilt", "pelvis_tx", "pelvis_ty"};
+    for (const char* c : pelvis) {
+        CoordActSpec a;
+        a.path = std::string("/forceset/residual_") + c;
+        a.coord = c;
+        P.model.actuatorOrder.emplace_back(0, (int)P.model.coordActs.size());
+        P.model.coordActs.push_back(a);
+    }
+    appendExternalLoads(P.model, dir + "/ExperimentalData/subject01_walk_grf.xml");
+    P.setTimeBounds(Bounds(0.03), Bounds(2.494));
+    P.defaultSpeedBounds = Bounds(-50, 50);
+    for (auto& a : P.model.coordActs) P.setControlInfo(a.path, Bounds(-1e4, 1e4));
+    for (auto& m : P.model.muscles) P.setControlInfo(m.path, Bounds(0, 1e4));
+    P.addGoal(MOCOB200_GOAL_CONTROL, "effort");
+    SolverSettings S;
+    S.num_mesh_intervals = 10;
+    S.transcription_scheme = "trapezoidal";
+    S.applyOptions(options);
+    return flatten(P, S);
+}
+
 } // namespace
 
 std::unique_ptr<FlatProblem> buildExample(const std::string& name, const std::string& dataDir, const std::string& options) {
@@ -355,6 +388,7 @@ std::unique_ptr<FlatProblem> buildExample(const std::string& name, const std::st
     if (name.rfind("pendulum:", 0) == 0) return pendulum(std::stoi(name.substr(9)), options);
     if (name == "gait2d_tracking") return gaitTracking(dataDir, options);
     if (name == "gait2d_prediction") return gaitPrediction(dataDir, options);
+    if (name == "gait10dof_replay") return gait10dofReplay(dataDir, options);
     throw std::runtime_error("unknown example '" + name + "'");
 }
 

@@ -63,6 +63,12 @@ int ModelSpec::bodyIndex(const std::string& n) const {
 }
 
 // ---------------------------------------------------------------- options
+static bool boolOpt(const std::string& v) { return v == "1" || v == "true" || v == "True"; }
+static Bounds boundsOpt(const std::string& v) {
+    auto d = parseDoubles(v);
+    if (d.size() != 2) throw std::runtime_error("expected two numbers 'lo hi', got '" + v + "'");
+    return Bounds(d[0], d[1]);
+}
 void SolverSettings::applyOptions(const std::string& opts) {
     std::stringstream ss(opts);
     std::string kv;
@@ -72,17 +78,184 @@ void SolverSettings::applyOptions(const std::string& opts) {
         size_t eq = kv.find('=');
         if (eq == std::string::npos) throw std::runtime_error("option without '=': " + kv);
         std::string k = trim(kv.substr(0, eq)), v = trim(kv.substr(eq + 1));
+        if (k == "scheme") k = "transcription_scheme";
+        if (k == "dynamics_mode") k = "multibody_dynamics_mode";
+        if (k == "fd_scheme") k = "optim_finite_difference_scheme";
         if (k == "num_mesh_intervals") num_mesh_intervals = std::stoi(v);
-        else if (k == "transcription_scheme" || k == "scheme") transcription_scheme = v;
-        else if (k == "interpolate_control_midpoints") interpolate_control_midpoints = (v == "1" || v == "true");
-        else if (k == "multibody_dynamics_mode" || k == "dynamics_mode") multibody_dynamics_mode = v;
-        else if (k == "optim_finite_difference_scheme" || k == "fd_scheme") optim_finite_difference_scheme = v;
-        else if (k == "minimize_implicit_multibody_accelerations") minimize_implicit_multibody_accelerations = (v == "1" || v == "true");
-        else if (k == "minimize_implicit_auxiliary_derivatives") minimize_implicit_auxiliary_derivatives = (v == "1" || v == "true");
+        else if (k == "transcription_scheme") transcription_scheme = v;
+        else if (k == "interpolate_control_midpoints") interpolate_control_midpoints = boolOpt(v);
+        else if (k == "multibody_dynamics_mode") multibody_dynamics_mode = v;
+        else if (k == "optim_finite_difference_scheme") optim_finite_difference_scheme = v;
+        else if (k == "minimize_implicit_multibody_accelerations") minimize_implicit_multibody_accelerations = boolOpt(v);
+        else if (k == "minimize_implicit_auxiliary_derivatives") minimize_implicit_auxiliary_derivatives = boolOpt(v);
         else if (k == "implicit_multibody_accelerations_weight") implicit_multibody_accelerations_weight = std::stod(v);
         else if (k == "implicit_auxiliary_derivatives_weight") implicit_auxiliary_derivatives_weight = std::stod(v);
+        else if (k == "implicit_multibody_acceleration_bounds") implicit_multibody_acceleration_bounds = boundsOpt(v);
+        else if (k == "implicit_auxiliary_derivative_bounds") implicit_auxiliary_derivative_bounds = boundsOpt(v);
+        else if (k == "enforce_constraint_derivatives") enforce_constraint_derivatives = boolOpt(v);
+        else if (k == "minimize_lagrange_multipliers") minimize_lagrange_multipliers = boolOpt(v);
+        else if (k == "lagrange_multiplier_weight") lagrange_multiplier_weight = std::stod(v);
+        else if (k == "velocity_correction_bounds") velocity_correction_bounds = boundsOpt(v);
         else if (k == "mesh") { mesh = parseDoubles(v); }
         else throw std::runtime_error("unknown solver option '" + k + "'");
+        keysGiven.push_back(k);
+    }
+}
+bool SolverSettings::given(const std::string& k) const { return std::find(keysGiven.begin(), keysGiven.end(), k) != keysGiven.end(); }
+
+void applySettingsToTranscription(const SolverSettings& S, FlatProblem& fp, bool only) {
+    mocob200_transcription& R = fp.tr;
+    auto want = [&](const char* k) { return !only || S.given(k); };
+    if (want("transcription_scheme")) {
+        if (S.transcription_scheme == "trapezoidal") R.scheme = MOCOB200_SCHEME_TRAPEZOIDAL;
+        else if (S.transcription_scheme == "hermite-simpson") R.scheme = MOCOB200_SCHEME_HERMITE_SIMPSON;
+        else throw std::runtime_error("unknown transcription_scheme '" + S.transcription_scheme + "'");
+    }
+    if (want("multibody_dynamics_mode")) {
+        if (S.multibody_dynamics_mode == "explicit") R.dynamics_mode = MOCOB200_DYNAMICS_EXPLICIT;
+        else if (S.multibody_dynamics_mode == "implicit") R.dynamics_mode = MOCOB200_DYNAMICS_IMPLICIT;
+        else throw std::runtime_error("unknown multibody_dynamics_mode '" + S.multibody_dynamics_mode + "'");
+    }
+    if (want("optim_finite_difference_scheme")) {
+        if (S.optim_finite_difference_scheme == "central") R.fd_scheme = MOCOB200_FD_CENTRAL;
+        else if (S.optim_finite_difference_scheme == "forward") R.fd_scheme = MOCOB200_FD_FORWARD;
+        else if (S.optim_finite_difference_scheme == "backward") R.fd_scheme = MOCOB200_FD_BACKWARD;
+        else throw std::runtime_error("unknown optim_finite_difference_scheme");
+    }
+    if (!only && S.optim_sparsity_detection != "none")
+        throw std::runtime_error("optim_sparsity_detection is a property of the evaluator handle (mocob200_set_sparsity_detection)");
+    if (!S.mesh.empty() && want("mesh")) {
+        // validity checks of MocoCasADiSolver.cpp:192-209
+        if (S.mesh.front() != 0.0 || S.mesh.back() != 1.0) throw std::runtime_error("mesh must start at 0 and end at 1");
+        for (size_t i = 1; i < S.mesh.size(); ++i)
+            if (!(S.mesh[i] > S.mesh[i - 1])) throw std::runtime_error("mesh must be strictly increasing");
+        fp.mesh = S.mesh;
+    } else if (want("num_mesh_intervals")) {
+        if (S.num_mesh_intervals < 1) throw std::runtime_error("num_mesh_intervals must be >= 1");
+        fp.mesh.clear();
+        for (int i = 0; i <= S.num_mesh_intervals; ++i) fp.mesh.push_back(i / (double)S.num_mesh_intervals);
+    }
+    if (want("interpolate_control_midpoints")) R.interpolate_control_midpoints = S.interpolate_control_midpoints ? 1 : 0;
+    if (want("implicit_multibody_acceleration_bounds")) {
+        R.accel_bounds[0] = S.implicit_multibody_acceleration_bounds.lo;
+        R.accel_bounds[1] = S.implicit_multibody_acceleration_bounds.hi;
+    }
+    if (want("implicit_auxiliary_derivative_bounds")) {
+        R.auxderiv_bounds[0] = S.implicit_auxiliary_derivative_bounds.lo;
+        R.auxderiv_bounds[1] = S.implicit_auxiliary_derivative_bounds.hi;
+    }
+    if (want("minimize_implicit_multibody_accelerations")) R.minimize_accelerations = S.minimize_implicit_multibody_accelerations;
+    if (want("implicit_multibody_accelerations_weight")) R.accelerations_weight = S.implicit_multibody_accelerations_weight;
+    if (want("minimize_implicit_auxiliary_derivatives")) R.minimize_auxiliary_derivatives = S.minimize_implicit_auxiliary_derivatives;
+    if (want("implicit_auxiliary_derivatives_weight")) R.auxiliary_derivatives_weight = S.implicit_auxiliary_derivatives_weight;
+    if (want("enforce_constraint_derivatives")) R.enforce_constraint_derivatives = S.enforce_constraint_derivatives;
+    if (want("minimize_lagrange_multipliers")) R.minimize_lagrange_multipliers = S.minimize_lagrange_multipliers;
+    if (want("lagrange_multiplier_weight")) R.lagrange_multiplier_weight = S.lagrange_multiplier_weight;
+    if (want("velocity_correction_bounds")) {
+        R.velocity_correction_bounds[0] = S.velocity_correction_bounds.lo;
+        R.velocity_correction_bounds[1] = S.velocity_correction_bounds.hi;
+    }
+    if (!only) { R.multiplier_bounds[0] = -1000; R.multiplier_bounds[1] = 1000; } // MocoProblem default multiplier bounds
+    fp.rebind();
+}
+
+void validateTables(const mocob200_tables& T) {
+    auto bad = [](const char* what) { throw std::runtime_error(std::string("corrupt problem tables: ") + what); };
+    auto dblRange = [&](int off, long n, const char* what) { if (off < 0 || n < 0 || (long)off + n > T.n_dbl) bad(what); };
+    auto intRange = [&](int off, long n, const char* what) { if (off < 0 || n < 0 || (long)off + n > T.n_int) bad(what); };
+    if (T.nb < 0 || T.nq < 0 || T.nz < 0 || T.nc < 0 || T.nderiv_aux < 0 || T.nmus < 0 || T.npp < 0 || T.nspline < 0 || T.ncontact < 0 ||
+        T.ncact < 0 || T.ngoal < 0 || T.nppoly < 0 || T.ncustom < 0 || T.nxforce < 0) bad("negative count");
+    dblRange(T.o_body_d, (long)T.nb * MOCOB200_BODY_DSTRIDE, "bodies");
+    intRange(T.o_body_i, (long)T.nb * MOCOB200_BODY_ISTRIDE, "bodies");
+    dblRange(T.o_gravity, 3, "gravity");
+    dblRange(T.o_pp_d, (long)T.npp * MOCOB200_PP_DSTRIDE, "path points");
+    intRange(T.o_pp_i, (long)T.npp * MOCOB200_PP_ISTRIDE, "path points");
+    dblRange(T.o_mus_d, (long)T.nmus * MOCOB200_MUS_DSTRIDE, "muscles");
+    intRange(T.o_mus_i, (long)T.nmus * MOCOB200_MUS_ISTRIDE, "muscles");
+    dblRange(T.o_contact_d, (long)T.ncontact * MOCOB200_CONTACT_DSTRIDE, "contacts");
+    intRange(T.o_contact_i, (long)T.ncontact * MOCOB200_CONTACT_ISTRIDE, "contacts");
+    dblRange(T.o_cact_d, (long)T.ncact * MOCOB200_CACT_DSTRIDE, "coordinate actuators");
+    intRange(T.o_cact_i, (long)T.ncact * MOCOB200_CACT_ISTRIDE, "coordinate actuators");
+    intRange(T.o_spline_i, (long)T.nspline * MOCOB200_SPLINE_ISTRIDE, "splines");
+    intRange(T.o_ppoly_i, (long)T.nppoly * MOCOB200_PPOLY_ISTRIDE, "piecewise polynomials");
+    intRange(T.o_goal_i, (long)T.ngoal * MOCOB200_GOAL_ISTRIDE, "goals");
+    dblRange(T.o_bounds, 6L * (2 * T.nq + T.nz + T.nc), "bounds");
+    dblRange(T.o_time_bounds, 4, "time bounds");
+    dblRange(T.o_spline_data, 0, "spline data");
+    dblRange(T.o_ppoly_data, 0, "piecewise-polynomial data");
+    int nq = 0;
+    for (int b = 0; b < T.nb; ++b) {
+        const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
+        if (bi[0] < -1 || bi[0] >= b) bad("body parent");
+        if (bi[1] < 0 || bi[1] > MOCOB200_JOINT_CUSTOM || bi[3] < 0 || bi[3] > 6 || bi[2] != nq) bad("joint record");
+        nq += bi[3];
+    }
+    if (nq != T.nq) bad("coordinate count");
+    for (int s = 0; s < T.nspline; ++s) {
+        const int* r = T.idx + T.o_spline_i + s * MOCOB200_SPLINE_ISTRIDE;
+        if (r[1] < 2) bad("spline knots");
+        dblRange(T.o_spline_data + r[0], 5L * r[1] + 1, "spline data");
+        if (r[0] < 0) bad("spline data");
+    }
+    for (int s = 0; s < T.nppoly; ++s) {
+        const int* r = T.idx + T.o_ppoly_i + s * MOCOB200_PPOLY_ISTRIDE;
+        if (r[0] < 0 || r[1] < 1 || r[2] < 1) bad("piecewise polynomial record");
+        dblRange(T.o_ppoly_data + r[0], (long)r[1] + 1 + (long)r[1] * r[2], "piecewise-polynomial data");
+    }
+    for (int p = 0; p < T.npp; ++p) {
+        const int* pi = T.idx + T.o_pp_i + p * MOCOB200_PP_ISTRIDE;
+        if (pi[0] < -1 || pi[0] >= T.nb || pi[1] < 0 || pi[1] > MOCOB200_PP_MOVING) bad("path point record");
+        if (pi[1] == MOCOB200_PP_CONDITIONAL && (pi[2] < 0 || pi[2] >= T.nq)) bad("conditional path point coordinate");
+        if (pi[1] == MOCOB200_PP_MOVING)
+            for (int a = 0; a < 3; ++a)
+                if (pi[3 + a] < 0 || pi[3 + a] >= T.nspline || pi[6] < 0 || pi[6] >= T.nq) bad("moving path point record");
+    }
+    for (int m = 0; m < T.nmus; ++m) {
+        const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
+        if (mi[0] < 0 || mi[1] < 2 || mi[0] + mi[1] > T.npp || mi[2] < 0 || mi[2] >= T.nc || mi[3] >= T.nz || mi[4] >= T.nz ||
+            mi[6] >= T.nderiv_aux || mi[7] >= T.nderiv_aux) bad("muscle record");
+    }
+    for (int c = 0; c < T.ncontact; ++c) {
+        const int* ci = T.idx + T.o_contact_i + c * MOCOB200_CONTACT_ISTRIDE;
+        if (ci[0] < -1 || ci[0] >= T.nb || ci[1] < -1 || ci[1] >= T.nb) bad("contact record");
+    }
+    for (int a = 0; a < T.ncact; ++a) {
+        const int* ai = T.idx + T.o_cact_i + a * MOCOB200_CACT_ISTRIDE;
+        if (ai[0] < 0 || ai[0] >= T.nq || ai[1] < 0 || ai[1] >= T.nc) bad("coordinate actuator record");
+    }
+    for (int g = 0; g < T.ngoal; ++g) {
+        const int* gr = T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
+        if (gr[2] < 0 || gr[6] < 0 || gr[7] < 0) bad("goal record");
+        intRange(gr[4], gr[6], "goal payload");
+        dblRange(gr[5], gr[7], "goal payload");
+    }
+    if (T.ncustom > 0) {
+        dblRange(T.o_cj_d, (long)T.ncustom * MOCOB200_CJ_DSTRIDE, "custom joints");
+        intRange(T.o_cj_i, (long)T.ncustom * MOCOB200_CJ_ISTRIDE, "custom joints");
+        intRange(T.o_body_cj, T.nb, "custom joint map");
+        for (int b = 0; b < T.nb; ++b) {
+            const int cj = T.idx[T.o_body_cj + b];
+            const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
+            if ((bi[1] == MOCOB200_JOINT_CUSTOM) != (cj >= 0) || cj >= T.ncustom) bad("custom joint map");
+            if (cj < 0) continue;
+            const int* ci = T.idx + T.o_cj_i + cj * MOCOB200_CJ_ISTRIDE;
+            for (int a = 0; a < 6; ++a) {
+                if (ci[3 * a] < 0 || ci[3 * a] > MOCOB200_FN_SIMMSPLINE) bad("custom joint function kind");
+                if (ci[3 * a] != MOCOB200_FN_CONSTANT && (ci[3 * a + 1] < bi[2] || ci[3 * a + 1] >= bi[2] + bi[3])) bad("custom joint coordinate");
+                if (ci[3 * a] == MOCOB200_FN_SIMMSPLINE && (ci[3 * a + 2] < 0 || ci[3 * a + 2] >= T.nspline)) bad("custom joint spline");
+            }
+        }
+    } else {
+        for (int b = 0; b < T.nb; ++b)
+            if (T.idx[T.o_body_i + b * MOCOB200_BODY_ISTRIDE + 1] == MOCOB200_JOINT_CUSTOM) bad("custom joint without a record");
+    }
+    if (T.nxforce > 0) {
+        intRange(T.o_xforce_i, (long)T.nxforce * MOCOB200_XFORCE_ISTRIDE, "external forces");
+        for (int f = 0; f < T.nxforce; ++f) {
+            const int* xi = T.idx + T.o_xforce_i + f * MOCOB200_XFORCE_ISTRIDE;
+            if (xi[0] < 0 || xi[0] >= T.nb || xi[1] < -1 || xi[1] >= T.nb || xi[2] < -1 || xi[2] >= T.nb) bad("external force bodies");
+            for (int k = 0; k < 9; ++k) if (xi[3 + k] < -1 || xi[3 + k] >= T.nppoly) bad("external force function");
+        }
     }
 }
 
@@ -490,18 +663,59 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
     for (int k = 0; k < nBodies; ++k) newIndex[order[k]] = k;
     auto mapBody = [&](int b) { return b < 0 ? -1 : newIndex[b]; };
 
+    // ---- splines (SimmSpline knots + cubic coefficients, pre-scaled by the MultiplierFunction scale)
+    std::vector<int> splineRec; // istride records
+    std::vector<double> splineData;
+    auto addSpline = [&](const SplineSpec& s) {
+        const int n = (int)s.x.size();
+        std::vector<double> b, c, d;
+        fmmSpline(s.x, s.y, b, c, d);
+        const int id = (int)splineRec.size() / MOCOB200_SPLINE_ISTRIDE;
+        splineRec.push_back((int)splineData.size());
+        splineRec.push_back(n);
+        splineRec.push_back(0);
+        // layout: x[n] y[n] b[n] c[n] d[n] scale
+        splineData.insert(splineData.end(), s.x.begin(), s.x.end());
+        splineData.insert(splineData.end(), s.y.begin(), s.y.end());
+        splineData.insert(splineData.end(), b.begin(), b.end());
+        splineData.insert(splineData.end(), c.begin(), c.end());
+        splineData.insert(splineData.end(), d.begin(), d.end());
+        splineData.push_back(s.scale);
+        return id;
+    };
+
     T.nb = nBodies;
     T.o_body_d = (int)D.size();
     T.o_body_i = (int)I.size();
     std::map<std::string, int> coordIndex;      // coordinate name -> q index
     std::vector<std::string> coordPath;         // "/jointset/<joint>/<coord>"
     std::vector<std::array<double, 2>> coordRange;
+    std::vector<double> cjD;                    // custom-joint records
+    std::vector<int> cjI, bodyCj(nBodies, -1);
     int nq = 0;
     for (int k = 0; k < nBodies; ++k) {
         const BodySpec& B = M.bodies[order[k]];
         const JointSpec& J = M.joints[jointOfBody[order[k]]];
-        const int expect = J.kind == MOCOB200_JOINT_WELD ? 0 : J.kind == MOCOB200_JOINT_PLANAR ? 3 : 1;
+        const int expect = J.kind == MOCOB200_JOINT_WELD ? 0 : J.kind == MOCOB200_JOINT_PLANAR ? 3 : J.kind == MOCOB200_JOINT_CUSTOM ? (int)J.coords.size() : 1;
         if ((int)J.coords.size() != expect) throw std::runtime_error("joint '" + J.name + "': wrong number of coordinates");
+        if (J.kind == MOCOB200_JOINT_CUSTOM) {
+            // SimTK::MobilizedBody::FunctionBased as CustomJoint builds it (CustomJoint.cpp:205-273): 1..6 mobilities
+            if (expect < 1 || expect > 6) throw std::runtime_error("CustomJoint '" + J.name + "' must have 1 to 6 coordinates");
+            bodyCj[k] = (int)cjI.size() / MOCOB200_CJ_ISTRIDE;
+            for (int a = 0; a < 6; ++a) {
+                const TransformAxisSpec& A = J.axes[a];
+                int local = -1;
+                for (size_t c = 0; c < J.coords.size(); ++c) if (J.coords[c].name == A.coord) local = (int)c;
+                if (A.fnKind != MOCOB200_FN_CONSTANT && local < 0)
+                    throw std::runtime_error("CustomJoint '" + J.name + "': TransformAxis coordinate '" + A.coord + "' is not one of the joint's");
+                for (int c = 0; c < 3; ++c) cjD.push_back(A.axis.v[c]);
+                cjD.push_back(A.fnKind == MOCOB200_FN_LINEAR ? A.c0 : 0.0);
+                cjD.push_back(A.fnKind == MOCOB200_FN_SIMMSPLINE ? 0.0 : A.c1);
+                cjI.push_back(A.fnKind);
+                cjI.push_back(A.fnKind == MOCOB200_FN_CONSTANT ? -1 : nq + local);
+                cjI.push_back(A.fnKind == MOCOB200_FN_SIMMSPLINE ? addSpline(A.spline) : -1);
+            }
+        }
         pushX(D, J.parent.X); // X_PF
         pushX(D, J.child.X);  // X_BM
         // massless body with inertia -> inertia ignored (SimbodyEngine/Body.cpp:133-140)
@@ -540,6 +754,7 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
     int nz = 0, nda = 0;
     for (size_t m = 0; m < M.muscles.size(); ++m) {
         const MuscleSpec& mu = M.muscles[m];
+        if (mu.pathActuator) continue; // no states
         if (!mu.ignoreActivationDynamics) { musAct[m] = nz++; sn.push_back(mu.path + "/activation"); }
         if (!mu.ignoreTendonCompliance) {
             musTen[m] = nz++;
@@ -576,27 +791,6 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
         return it->second;
     };
 
-    // ---- splines (SimmSpline knots + cubic coefficients, pre-scaled by the MultiplierFunction scale)
-    std::vector<int> splineRec; // istride records
-    std::vector<double> splineData;
-    auto addSpline = [&](const SplineSpec& s) {
-        const int n = (int)s.x.size();
-        std::vector<double> b, c, d;
-        fmmSpline(s.x, s.y, b, c, d);
-        const int id = (int)splineRec.size() / MOCOB200_SPLINE_ISTRIDE;
-        splineRec.push_back((int)splineData.size());
-        splineRec.push_back(n);
-        splineRec.push_back(0);
-        // layout: x[n] y[n] b[n] c[n] d[n] scale
-        splineData.insert(splineData.end(), s.x.begin(), s.x.end());
-        splineData.insert(splineData.end(), s.y.begin(), s.y.end());
-        splineData.insert(splineData.end(), b.begin(), b.end());
-        splineData.insert(splineData.end(), c.begin(), c.end());
-        splineData.insert(splineData.end(), d.begin(), d.end());
-        splineData.push_back(s.scale);
-        return id;
-    };
-
     // ---- muscles and their path points
     T.nmus = (int)M.muscles.size();
     std::vector<double> ppD, musD;
@@ -605,8 +799,11 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
     for (size_t m = 0; m < M.muscles.size(); ++m) {
         const MuscleSpec& mu = M.muscles[m];
         if (mu.points.size() < 2) throw std::runtime_error("muscle '" + mu.path + "' needs >= 2 path points");
-        if (std::fabs(mu.activationTimeConstant - M.muscles[0].activationTimeConstant) > 0 ||
-            std::fabs(mu.deactivationTimeConstant - M.muscles[0].deactivationTimeConstant) > 0)
+        const MuscleSpec* firstMuscle = nullptr;
+        for (auto& other : M.muscles) if (!other.pathActuator) { firstMuscle = &other; break; }
+        if (!mu.pathActuator && firstMuscle &&
+            (std::fabs(mu.activationTimeConstant - firstMuscle->activationTimeConstant) > 0 ||
+             std::fabs(mu.deactivationTimeConstant - firstMuscle->deactivationTimeConstant) > 0))
             throw std::runtime_error("muscles must share activation/deactivation time constants "
                                      "(the reference's static-local constants, DeGrooteFregly2016Muscle.cpp:194-195)");
         const int first = npp;
@@ -650,6 +847,7 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
         if (mu.ignoreActivationDynamics) flags |= MOCOB200_MUS_FLAG_IGNORE_ACTIVATION_DYNAMICS;
         if (mu.ignorePassiveFiberForce) flags |= MOCOB200_MUS_FLAG_IGNORE_PASSIVE;
         if (mu.tendonImplicit) flags |= MOCOB200_MUS_FLAG_TENDON_IMPLICIT;
+        if (mu.pathActuator) flags |= MOCOB200_MUS_FLAG_PATH_ACTUATOR | MOCOB200_MUS_FLAG_IGNORE_TENDON_COMPLIANCE | MOCOB200_MUS_FLAG_IGNORE_ACTIVATION_DYNAMICS;
         int mi[MOCOB200_MUS_ISTRIDE] = {first, (int)mu.points.size(), musCtl[m], musAct[m], musTen[m], flags,
                                         musDeriv[m], musDeriv[m], 0, 0};
         musI.insert(musI.end(), mi, mi + MOCOB200_MUS_ISTRIDE);
@@ -684,6 +882,14 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
         D.push_back(M.coordActs[a].optimalForce);
         I.push_back(coordOf(M.coordActs[a].coord));
         I.push_back(cactCtl[a]);
+    }
+
+    // ---- custom joints (before the bounds block: the warp kernels stage everything below o_bounds in shared memory)
+    T.ncustom = (int)cjI.size() / MOCOB200_CJ_ISTRIDE;
+    if (T.ncustom > 0) {
+        T.o_cj_d = (int)D.size(); D.insert(D.end(), cjD.begin(), cjD.end());
+        T.o_cj_i = (int)I.size(); I.insert(I.end(), cjI.begin(), cjI.end());
+        T.o_body_cj = (int)I.size(); I.insert(I.end(), bodyCj.begin(), bodyCj.end());
     }
 
     // ---- variable bounds (MocoProblemRep.cpp:300-430 ; CasOCProblem.h:603-606)
@@ -747,6 +953,21 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
         ppolyData.insert(ppolyData.end(), pp.coef.begin(), pp.coef.end());
         return id;
     };
+    // ---- external forces (ExternalForce.cpp:330-355): functions of time in the piecewise-polynomial table
+    {
+        std::vector<int> xfI;
+        for (const ExternalForceSpec& X : M.externalForces) {
+            xfI.push_back(mapBody(X.appliedTo));
+            xfI.push_back(mapBody(X.forceExpressedIn));
+            xfI.push_back(mapBody(X.pointExpressedIn));
+            for (int a = 0; a < 3; ++a) xfI.push_back(X.hasForce ? addPPoly(X.force[a]) : -1);
+            for (int a = 0; a < 3; ++a) xfI.push_back(X.hasPoint ? addPPoly(X.point[a]) : -1);
+            for (int a = 0; a < 3; ++a) xfI.push_back(X.hasTorque ? addPPoly(X.torque[a]) : -1);
+        }
+        T.nxforce = (int)M.externalForces.size();
+        T.o_xforce_i = (int)I.size();
+        I.insert(I.end(), xfI.begin(), xfI.end());
+    }
     auto contactId = [&](const std::string& n) {
         for (size_t i = 0; i < M.contacts.size(); ++i) if (M.contacts[i].name == n) return (int)i;
         throw std::runtime_error("no contact force named '" + n + "'");
@@ -916,38 +1137,8 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
     D.insert(D.end(), goalD.begin(), goalD.end());
 
     // ---- transcription
-    mocob200_transcription& R = fp->tr;
-    if (S.transcription_scheme == "trapezoidal") R.scheme = MOCOB200_SCHEME_TRAPEZOIDAL;
-    else if (S.transcription_scheme == "hermite-simpson") R.scheme = MOCOB200_SCHEME_HERMITE_SIMPSON;
-    else throw std::runtime_error("unknown transcription_scheme '" + S.transcription_scheme + "'");
-    if (S.multibody_dynamics_mode == "explicit") R.dynamics_mode = MOCOB200_DYNAMICS_EXPLICIT;
-    else if (S.multibody_dynamics_mode == "implicit") R.dynamics_mode = MOCOB200_DYNAMICS_IMPLICIT;
-    else throw std::runtime_error("unknown multibody_dynamics_mode '" + S.multibody_dynamics_mode + "'");
-    if (S.optim_finite_difference_scheme == "central") R.fd_scheme = MOCOB200_FD_CENTRAL;
-    else if (S.optim_finite_difference_scheme == "forward") R.fd_scheme = MOCOB200_FD_FORWARD;
-    else if (S.optim_finite_difference_scheme == "backward") R.fd_scheme = MOCOB200_FD_BACKWARD;
-    else throw std::runtime_error("unknown optim_finite_difference_scheme");
-    if (S.optim_sparsity_detection != "none")
-        throw std::runtime_error("optim_sparsity_detection other than 'none' is unsupported");
-    if (!S.mesh.empty()) {
-        // validity checks of MocoCasADiSolver.cpp:192-209
-        if (S.mesh.front() != 0.0 || S.mesh.back() != 1.0) throw std::runtime_error("mesh must start at 0 and end at 1");
-        for (size_t i = 1; i < S.mesh.size(); ++i)
-            if (!(S.mesh[i] > S.mesh[i - 1])) throw std::runtime_error("mesh must be strictly increasing");
-        fp->mesh = S.mesh;
-    } else {
-        if (S.num_mesh_intervals < 1) throw std::runtime_error("num_mesh_intervals must be >= 1");
-        for (int i = 0; i <= S.num_mesh_intervals; ++i) fp->mesh.push_back(i / (double)S.num_mesh_intervals);
-    }
-    R.interpolate_control_midpoints = S.interpolate_control_midpoints ? 1 : 0;
-    R.accel_bounds[0] = S.implicit_multibody_acceleration_bounds.lo;
-    R.accel_bounds[1] = S.implicit_multibody_acceleration_bounds.hi;
-    R.auxderiv_bounds[0] = S.implicit_auxiliary_derivative_bounds.lo;
-    R.auxderiv_bounds[1] = S.implicit_auxiliary_derivative_bounds.hi;
-    R.minimize_accelerations = S.minimize_implicit_multibody_accelerations;
-    R.accelerations_weight = S.implicit_multibody_accelerations_weight;
-    R.minimize_auxiliary_derivatives = S.minimize_implicit_auxiliary_derivatives;
-    R.auxiliary_derivatives_weight = S.implicit_auxiliary_derivatives_weight;
+    std::memset(&fp->tr, 0, sizeof fp->tr);
+    applySettingsToTranscription(S, *fp, false);
     fp->rebind();
     return fp;
 }

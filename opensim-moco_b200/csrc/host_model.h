@@ -51,16 +51,26 @@ struct CoordSpec {
     std::string name;
     double lo = -10, hi = 10;
 };
+struct SplineSpec { // SimmSpline wrapped in a MultiplierFunction
+    std::vector<double> x, y;
+    double scale = 1;
+};
+// One TransformAxis of a CustomJoint's SpatialTransform (SimbodyEngine/TransformAxis.cpp, SpatialTransform.cpp:100-176):
+// an axis and a scalar function of (at most) one of the joint's coordinates.
+struct TransformAxisSpec {
+    Vec3 axis;
+    int fnKind = MOCOB200_FN_CONSTANT;
+    double c0 = 0, c1 = 0;   // linear: c0 x + c1 (LinearFunction coefficients) ; constant: c1
+    SplineSpec spline;       // MOCOB200_FN_SIMMSPLINE (scale = product of the enclosing MultiplierFunctions)
+    std::string coord;       // empty: constant
+};
 struct JointSpec {
     std::string name;
     std::string container = "/jointset/"; // "/" when added with Model::addComponent
     int kind = MOCOB200_JOINT_WELD;
     FrameRef parent, child;
     std::vector<CoordSpec> coords;
-};
-struct SplineSpec { // SimmSpline wrapped in a MultiplierFunction
-    std::vector<double> x, y;
-    double scale = 1;
+    TransformAxisSpec axes[6]; // MOCOB200_JOINT_CUSTOM: rotation1..3, translation1..3
 };
 struct PathPointSpec {
     int kind = MOCOB200_PP_FIXED;
@@ -82,6 +92,8 @@ struct MuscleSpec { // DeGrooteFregly2016Muscle properties (Components/DeGrooteF
     double minControl = 0, maxControl = 1;
     bool ignoreTendonCompliance = false, ignoreActivationDynamics = false, ignorePassiveFiberForce = false;
     bool tendonImplicit = false; // tendon_compliance_dynamics_mode == "implicit"
+    // PathActuator (Actuators/PathActuator.cpp:156-197): tension = optimal_force (maxIsometricForce here) x control, no states
+    bool pathActuator = false;
     std::vector<PathPointSpec> points;
 };
 struct ContactSpec { // SmoothSphereHalfSpaceForce + its ContactSphere / ContactHalfSpace
@@ -98,6 +110,19 @@ struct CoordActSpec {
            maxControl = std::numeric_limits<double>::infinity();
 };
 
+struct PiecewisePoly { // value(t) on [breaks[k], breaks[k+1]) = sum_j coef[k*order+j] (t-breaks[k])^j
+    std::vector<double> breaks, coef;
+    int order = 0;
+    bool isSpline = false; // came from a GCVSpline (domain-checked where the reference checks, e.g. MocoControlBoundConstraint.cpp:74-92)
+};
+// ExternalForce (Model/ExternalForce.cpp:276-355): force / point / torque as functions of time (GCVSpline degree 3 for
+// tables of >= 4 rows, piecewise linear for 2-3 rows, constant for 1), applied to a body.
+struct ExternalForceSpec {
+    std::string name;
+    int appliedTo = -1, forceExpressedIn = -1, pointExpressedIn = -1; // body indices (-1 = ground)
+    bool hasForce = false, hasPoint = false, hasTorque = false;
+    PiecewisePoly force[3], point[3], torque[3];
+};
 struct ModelSpec {
     std::string name;
     Vec3 gravity;
@@ -106,12 +131,20 @@ struct ModelSpec {
     std::vector<MuscleSpec> muscles;
     std::vector<ContactSpec> contacts;
     std::vector<CoordActSpec> coordActs;
+    std::vector<ExternalForceSpec> externalForces;
     std::vector<std::pair<int, int>> actuatorOrder; // (0 = coordinate actuator, 1 = muscle ; index) in component order
     ModelSpec() { gravity.v[1] = -9.80665; }
     int bodyIndex(const std::string& n) const;
 };
 
-ModelSpec loadOsim(const std::string& path); // .osim document Version 40000 subset
+// .osim: document Version 40000 subset and the Version 30000 layout (joints nested in bodies) of the
+// opensim-models pipelines. musclesAsPathActuators: every muscle of any class is read as a PathActuator with
+// optimal_force 1 on its GeometryPath (its tension becomes the control) - used to replay recorded actuator forces.
+ModelSpec loadOsim(const std::string& path, bool musclesAsPathActuators = false);
+// ForceSet file (e.g. reserve actuators) appended to a model: CoordinateActuators only; other classes are returned by name
+std::vector<std::string> appendForceSetFile(ModelSpec& M, const std::string& path);
+// ExternalLoads .xml (+ its data file, resolved relative to the .xml) -> M.externalForces (ExternalLoads.cpp, ExternalForce.cpp:200-317)
+void appendExternalLoads(ModelSpec& M, const std::string& xmlPath);
 
 // ---- the optimal control problem (MocoProblem / MocoPhase surface) ----
 struct Bounds {
@@ -123,11 +156,6 @@ struct Bounds {
 };
 struct VariableInfo {
     Bounds bounds, initial, final;
-};
-struct PiecewisePoly { // value(t) on [breaks[k], breaks[k+1]) = sum_j coef[k*order+j] (t-breaks[k])^j
-    std::vector<double> breaks, coef;
-    int order = 0;
-    bool isSpline = false; // came from a GCVSpline (domain-checked where the reference checks, e.g. MocoControlBoundConstraint.cpp:74-92)
 };
 // natural interpolating spline of odd degree (what GCVSPL returns for zero smoothing), as a piecewise polynomial
 PiecewisePoly fitNaturalSpline(const std::vector<double>& t, const std::vector<double>& y, int degree);
@@ -223,7 +251,14 @@ struct SolverSettings {
     // IPOPT-side properties are carried but unused by the evaluator
     double optim_convergence_tolerance = -1, optim_constraint_tolerance = -1;
     int optim_max_iterations = -1;
+    // kinematic constraints (MocoCasADiSolver.h:115-159, MocoDirectCollocationSolver.h:90-168)
+    bool enforce_constraint_derivatives = false;
+    bool minimize_lagrange_multipliers = false;
+    double lagrange_multiplier_weight = 1.0;
+    Bounds velocity_correction_bounds{-0.1, 0.1};
     void applyOptions(const std::string& opts); // "key=value;key=value"
+    std::vector<std::string> keysGiven;         // canonical names of the keys applyOptions has seen
+    bool given(const std::string& k) const;
 };
 
 // Owner of one flattened problem (pools + transcription).
@@ -238,6 +273,10 @@ struct FlatProblem {
 };
 
 std::unique_ptr<FlatProblem> flatten(const Problem& p, const SolverSettings& s);
+// solver settings -> fp.tr / fp.mesh (all of them, or only the keys applyOptions was given); throws on invalid values
+void applySettingsToTranscription(const SolverSettings& s, FlatProblem& fp, bool onlyKeysGiven);
+// throws unless every offset / count of the tables lies inside its pool
+void validateTables(const mocob200_tables& T);
 std::unique_ptr<FlatProblem> buildExample(const std::string& name, const std::string& dataDir, const std::string& options);
 
 // simple .sto/.mot table

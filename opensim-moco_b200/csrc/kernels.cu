@@ -31,6 +31,33 @@ __global__ void k_points_nominal(DevTables T, DevLayout L, const double* __restr
     for (int o = 0; o < L.n_out; ++o) Y[(size_t)j * L.n_out + o] = out[o];
 }
 
+// Muscle-tendon path length and lengthening speed of every path at every grid point: out[j][m] = (length, speed).
+// What GeometryPath::getLength / getLengtheningSpeed report (GeometryPath.cpp:848-864, 1117-1145) - the quantities the
+// reference's MuscleAnalysis / Actuation analyses print; one thread per (grid point, muscle).
+__global__ void k_paths(DevTables T, DevLayout L, const double* __restrict__ x, double* __restrict__ out, int p0, int np) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= np * T.nmus) return;
+    const int j = p0 + t / T.nmus, m = t % T.nmus;
+    double in[MOCOB200_MAX_IN];
+    gather_inputs(L, x, j, in);
+    const double* q = in + 1;
+    const double* u = q + T.nq;
+    const double* z = u + T.nq;
+    const double* ctl = z + T.nz;
+    const double* auxder = ctl + T.nc + (T.implicit ? T.nq : 0);
+    Scratch S;
+    kinematics(T, q, u, S);
+    double ls[2];
+    muscle_force(T, m, q, u, z, ctl, auxder, S, false, false, ls);
+    out[2 * ((size_t)j * T.nmus + m)] = ls[0];
+    out[2 * ((size_t)j * T.nmus + m) + 1] = ls[1];
+}
+void launch_paths(const DevTables& T, const DevLayout& L, const double* d_x, double* d_out, int p0, int np, cudaStream_t s) {
+    const int n = np * T.nmus;
+    if (n <= 0) return;
+    k_paths<<<(n + 63) / 64, 64, 0, s>>>(T, L, d_x, d_out, p0, np);
+}
+
 // One finite-difference column of one callback group, following CasADi's FiniteDiff
 // (casadi/core/finite_differences.cpp of the pinned fork; restated from its documented algorithm):
 //   forward : (f(x+h v) - f(x)) / h                       h = sqrt(abstol)

@@ -44,6 +44,8 @@ struct DevLayout {
 };
 
 void launch_points_nominal(const DevTables& T, const DevLayout& L, const double* d_x, double* d_Y, int p0, int np, cudaStream_t s);
+// out[j][m] = (path length, lengthening speed) of muscle m at grid point j
+void launch_paths(const DevTables& T, const DevLayout& L, const double* d_x, double* d_out, int p0, int np, cudaStream_t s);
 // d_dirs (device, may be null = all inputs): the FD directions this launch differences
 void launch_points_fd(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, double* d_Y, double* d_J,
                       int p0, int np, cudaStream_t s, const int* d_dirs = nullptr, int ndirs = 0);

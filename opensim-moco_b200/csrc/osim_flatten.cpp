@@ -1,9 +1,13 @@
-// .osim (OpenSimDocument Version 40000) -> ModelSpec, for the component subset of SURVEY.md Appendix E:
-// Body, Pin/Slider/Planar/Weld joints with PhysicalOffsetFrames, DeGrooteFregly2016Muscle with
-// PathPoint / ConditionalPathPoint / MovingPathPoint(SimmSpline in MultiplierFunction),
-// ContactSphere / ContactHalfSpace / SmoothSphereHalfSpaceForce, CoordinateActuator.
+// .osim -> ModelSpec, for the component subset of SURVEY.md Appendix E:
+// Body; Pin/Slider/Planar/Weld/Custom joints (PhysicalOffsetFrames in document Version 40000, joint-in-body with
+// location/orientation pairs in Version 30000); DeGrooteFregly2016Muscle (or any path-carrying force read as a
+// PathActuator) with PathPoint / ConditionalPathPoint / MovingPathPoint(SimmSpline in MultiplierFunction);
+// ContactSphere / ContactHalfSpace / SmoothSphereHalfSpaceForce; CoordinateActuator; ExternalLoads files.
 // Anything else that would change the dynamics is refused loudly (no silent approximation).
+#include <algorithm>
+#include <cmath>
 #include <cstdlib>
+#include <limits>
 #include <stdexcept>
 
 #include "host_model.h"
@@ -23,9 +27,14 @@ bool boolOf(const std::string& s, bool def) {
     if (s.empty()) return def;
     return s == "true" || s == "1" || s == "True";
 }
+double numOf(const std::string& s) {
+    if (s == "Inf" || s == "inf" || s == "+Inf" || s == "infinity") return std::numeric_limits<double>::infinity();
+    if (s == "-Inf" || s == "-inf" || s == "-infinity") return -std::numeric_limits<double>::infinity();
+    return std::strtod(s.c_str(), nullptr);
+}
 double dblOf(const XmlNode& n, const char* tag, double def) {
     std::string s = n.childText(tag);
-    return s.empty() ? def : std::strtod(s.c_str(), nullptr);
+    return s.empty() ? def : numOf(s);
 }
 std::string leaf(const std::string& path) {
     size_t sl = path.rfind('/');
@@ -34,12 +43,18 @@ std::string leaf(const std::string& path) {
 
 struct Ctx {
     ModelSpec& M;
-    // resolve "/bodyset/x", "/ground", "ground"
+    bool v3 = false; // document Version < 40000: frames are bodies referenced by bare name
+    bool asPathActuators = false;
+    // resolve "/bodyset/x", "/ground", "ground", and (Version 30000) a bare body name
     bool baseFrame(const std::string& path, int& body) const {
         if (path == "/ground" || path == "ground") { body = -1; return true; }
         const std::string pre = "/bodyset/";
         if (path.compare(0, pre.size(), pre) == 0 && path.find('/', pre.size()) == std::string::npos) {
             body = M.bodyIndex(path.substr(pre.size()));
+            return true;
+        }
+        if (v3 && !path.empty() && path.find('/') == std::string::npos) {
+            body = M.bodyIndex(path);
             return true;
         }
         return false;
@@ -67,21 +82,169 @@ struct Ctx {
     }
 };
 
-SplineSpec splineOf(const XmlNode& holder, const std::string& what) {
-    // <x_location><MultiplierFunction><function><SimmSpline><x/><y/></SimmSpline></function><scale/></MultiplierFunction>
+// <holder> [<MultiplierFunction> <function>] <SimmSpline | LinearFunction | Constant> ... ; the scales of nested
+// MultiplierFunctions multiply (Common/MultiplierFunction.cpp)
+const XmlNode* unwrapFunction(const XmlNode& holder, double& scale) {
+    const XmlNode* cur = &holder;
+    scale = 1.0;
+    for (;;) {
+        if (const XmlNode* mf = cur->child("MultiplierFunction")) {
+            scale *= dblOf(*mf, "scale", 1.0);
+            const XmlNode* inner = mf->child("function");
+            if (!inner) throw std::runtime_error("MultiplierFunction without a function");
+            cur = inner;
+            continue;
+        }
+        for (auto& c : cur->children)
+            if (c->tag == "SimmSpline" || c->tag == "LinearFunction" || c->tag == "Constant") return c.get();
+        return nullptr;
+    }
+}
+
+SplineSpec simmSplineOf(const XmlNode& fn, double scale, const std::string& what) {
     SplineSpec s;
-    const XmlNode* fn = nullptr;
-    if (const XmlNode* mf = holder.child("MultiplierFunction")) {
-        s.scale = dblOf(*mf, "scale", 1.0);
-        const XmlNode* inner = mf->child("function");
-        if (inner) fn = inner->child("SimmSpline");
-    } else
-        fn = holder.child("SimmSpline");
-    if (!fn) throw std::runtime_error(what + ": only SimmSpline (optionally inside a MultiplierFunction) is supported");
-    s.x = parseDoubles(fn->childText("x"));
-    s.y = parseDoubles(fn->childText("y"));
+    s.scale = scale;
+    s.x = parseDoubles(fn.childText("x"));
+    s.y = parseDoubles(fn.childText("y"));
     if (s.x.size() != s.y.size() || s.x.size() < 2) throw std::runtime_error(what + ": bad SimmSpline knots");
     return s;
+}
+
+SplineSpec splineOf(const XmlNode& holder, const std::string& what) {
+    double scale = 1;
+    const XmlNode* fn = unwrapFunction(holder, scale);
+    if (!fn || fn->tag != "SimmSpline")
+        throw std::runtime_error(what + ": only SimmSpline (optionally inside a MultiplierFunction) is supported");
+    return simmSplineOf(*fn, scale, what);
+}
+
+// SpatialTransform of a CustomJoint: six TransformAxis children in order rotation1..3, translation1..3
+// (SpatialTransform.cpp:100-176). An axis without a function but with one coordinate gets LinearFunction(1, 0), without
+// coordinates Constant(0) (SpatialTransform::connectToJoint).
+void readSpatialTransform(const XmlNode& joint, JointSpec& J) {
+    const XmlNode* st = joint.child("SpatialTransform");
+    if (!st) throw std::runtime_error("CustomJoint '" + J.name + "' has no SpatialTransform");
+    int k = 0;
+    for (auto& ta : st->children) {
+        if (ta->tag != "TransformAxis") continue;
+        if (k >= 6) throw std::runtime_error("CustomJoint '" + J.name + "': more than 6 TransformAxis entries");
+        TransformAxisSpec& A = J.axes[k++];
+        A.axis = vec3Of(ta->childText("axis"), "TransformAxis axis");
+        std::vector<std::string> coords;
+        {
+            std::string cs = ta->childText("coordinates");
+            size_t i = 0;
+            while (i < cs.size()) {
+                while (i < cs.size() && isspace((unsigned char)cs[i])) ++i;
+                size_t j = i;
+                while (j < cs.size() && !isspace((unsigned char)cs[j])) ++j;
+                if (j > i) coords.push_back(cs.substr(i, j - i));
+                i = j;
+            }
+        }
+        if (coords.size() > 1) throw std::runtime_error("CustomJoint '" + J.name + "': multi-coordinate TransformAxis functions are unsupported");
+        if (!coords.empty()) A.coord = coords[0];
+        double scale = 1;
+        const XmlNode* holder = ta->child("function");
+        const XmlNode* fn = holder ? unwrapFunction(*holder, scale) : nullptr;
+        if (!holder || holder->children.empty()) {
+            if (A.coord.empty()) { A.fnKind = MOCOB200_FN_CONSTANT; A.c1 = 0; }
+            else { A.fnKind = MOCOB200_FN_LINEAR; A.c0 = 1; A.c1 = 0; }
+        } else if (!fn) {
+            throw std::runtime_error("CustomJoint '" + J.name + "': unsupported TransformAxis function (SimmSpline, LinearFunction, Constant)");
+        } else if (fn->tag == "Constant") {
+            A.fnKind = MOCOB200_FN_CONSTANT;
+            A.c1 = scale * dblOf(*fn, "value", 0.0);
+            A.coord.clear();
+        } else if (fn->tag == "LinearFunction") {
+            auto c = parseDoubles(fn->childText("coefficients", "1 0"));
+            if (c.size() != 2) throw std::runtime_error("LinearFunction needs 2 coefficients");
+            if (A.coord.empty()) { A.fnKind = MOCOB200_FN_CONSTANT; A.c1 = scale * c[1]; } // SimTK::Function::Linear of no argument
+            else { A.fnKind = MOCOB200_FN_LINEAR; A.c0 = scale * c[0]; A.c1 = scale * c[1]; }
+        } else {
+            if (A.coord.empty()) throw std::runtime_error("CustomJoint '" + J.name + "': SimmSpline axis without a coordinate");
+            A.fnKind = MOCOB200_FN_SIMMSPLINE;
+            A.spline = simmSplineOf(*fn, scale, "CustomJoint '" + J.name + "'");
+        }
+        const double n2 = A.axis.v[0] * A.axis.v[0] + A.axis.v[1] * A.axis.v[1] + A.axis.v[2] * A.axis.v[2];
+        if (!(n2 > 0)) throw std::runtime_error("CustomJoint '" + J.name + "': zero TransformAxis axis");
+        const double inv = 1.0 / std::sqrt(n2); // SimTK::UnitVec3 normalises
+        for (int a = 0; a < 3; ++a) A.axis.v[a] *= inv;
+    }
+    if (k != 6) throw std::runtime_error("CustomJoint '" + J.name + "': SpatialTransform needs 6 TransformAxis entries");
+    // the mobilizer's coordinate i is the i-th distinct coordinate name met in the axes (SpatialTransform::getCoordinateNames,
+    // CustomJoint.cpp:150-160); the joint's own Coordinate list must be in that order for the names to mean what they say
+    std::vector<std::string> order;
+    for (auto& A : J.axes)
+        if (!A.coord.empty() && std::find(order.begin(), order.end(), A.coord) == order.end()) order.push_back(A.coord);
+    if (order.size() != J.coords.size()) throw std::runtime_error("CustomJoint '" + J.name + "': coordinates and SpatialTransform disagree");
+    for (size_t i = 0; i < order.size(); ++i)
+        if (order[i] != J.coords[i].name)
+            throw std::runtime_error("CustomJoint '" + J.name + "': coordinate order differs from the SpatialTransform's (unsupported)");
+}
+
+int jointKindOf(const std::string& tag, const std::string& name) {
+    if (tag == "PinJoint") return MOCOB200_JOINT_PIN;
+    if (tag == "SliderJoint") return MOCOB200_JOINT_SLIDER;
+    if (tag == "PlanarJoint") return MOCOB200_JOINT_PLANAR;
+    if (tag == "WeldJoint") return MOCOB200_JOINT_WELD;
+    if (tag == "CustomJoint") return MOCOB200_JOINT_CUSTOM;
+    throw std::runtime_error("unsupported joint type '" + tag + "' (" + name + ")");
+}
+void readCoordinates(const XmlNode* holder, JointSpec& J) {
+    if (!holder) return;
+    for (auto& c : holder->children) {
+        if (c->tag != "Coordinate") continue;
+        CoordSpec C;
+        C.name = c->name();
+        auto r = parseDoubles(c->childText("range", "-10 10"));
+        if (r.size() == 2) { C.lo = r[0]; C.hi = r[1]; }
+        if (boolOf(c->childText("locked"), false) || boolOf(c->childText("prescribed"), false))
+            throw std::runtime_error("coordinate '" + C.name + "': locked/prescribed coordinates are unsupported");
+        J.coords.push_back(C);
+    }
+}
+
+void readPath(const Ctx& cx, const XmlNode& n, MuscleSpec& mu) {
+    const XmlNode* gp = n.child("GeometryPath");
+    if (!gp) throw std::runtime_error("'" + mu.path + "' has no GeometryPath");
+    if (const XmlNode* ws = gp->child("PathWrapSet"))
+        if (const XmlNode* wo = ws->child("objects"))
+            if (!wo->children.empty())
+                throw std::runtime_error("muscle '" + mu.path + "': PathWrap objects are unsupported (SURVEY §8 a18)");
+    const XmlNode* pps = gp->child("PathPointSet");
+    const XmlNode* objs = pps ? pps->child("objects") : nullptr;
+    if (!objs) throw std::runtime_error("muscle '" + mu.path + "' has no path points");
+    for (auto& pn : objs->children) {
+        PathPointSpec pt;
+        std::string frame = cx.v3 ? pn->childText("body") : pn->childText("socket_parent_frame");
+        if (!cx.baseFrame(frame, pt.body))
+            throw std::runtime_error("path point '" + pn->name() + "': parent frame '" + frame + "' must be a body");
+        if (pn->tag == "PathPoint") {
+            pt.kind = MOCOB200_PP_FIXED;
+            pt.location = vec3Of(pn->childText("location"), "location");
+        } else if (pn->tag == "ConditionalPathPoint") {
+            pt.kind = MOCOB200_PP_CONDITIONAL;
+            pt.location = vec3Of(pn->childText("location"), "location");
+            auto r = parseDoubles(pn->childText("range"));
+            if (r.size() != 2) throw std::runtime_error("ConditionalPathPoint '" + pn->name() + "': bad range");
+            pt.range[0] = r[0];
+            pt.range[1] = r[1];
+            pt.condCoord = leaf(cx.v3 ? pn->childText("coordinate") : pn->childText("socket_coordinate"));
+        } else if (pn->tag == "MovingPathPoint") {
+            pt.kind = MOCOB200_PP_MOVING;
+            const char* ax[3] = {"x", "y", "z"};
+            for (int a = 0; a < 3; ++a) {
+                const XmlNode* loc = pn->child(std::string(ax[a]) + "_location");
+                if (!loc) throw std::runtime_error("MovingPathPoint '" + pn->name() + "': missing location function");
+                pt.fn[a] = splineOf(*loc, "MovingPathPoint '" + pn->name() + "'");
+                pt.coord[a] = leaf(cx.v3 ? pn->childText(std::string(ax[a]) + "_coordinate")
+                                         : pn->childText(std::string("socket_") + ax[a] + "_coordinate"));
+            }
+        } else
+            throw std::runtime_error("unsupported path point type '" + pn->tag + "'");
+        mu.points.push_back(pt);
+    }
 }
 
 void readMuscle(const Ctx& cx, const XmlNode& n, const std::string& prefix) {
@@ -106,60 +269,47 @@ void readMuscle(const Ctx& cx, const XmlNode& n, const std::string& prefix) {
     mu.tendonStrainAtOneNormForce = dblOf(n, "tendon_strain_at_one_norm_force", 0.049);
     mu.ignorePassiveFiberForce = boolOf(n.childText("ignore_passive_fiber_force"), false);
     mu.tendonImplicit = n.childText("tendon_compliance_dynamics_mode", "explicit") == "implicit";
-    const XmlNode* gp = n.child("GeometryPath");
-    if (!gp) throw std::runtime_error("muscle '" + mu.path + "' has no GeometryPath");
-    if (const XmlNode* ws = gp->child("PathWrapSet"))
-        if (const XmlNode* wo = ws->child("objects"))
-            if (!wo->children.empty())
-                throw std::runtime_error("muscle '" + mu.path + "': PathWrap objects are unsupported (SURVEY §8 a18)");
-    const XmlNode* pps = gp->child("PathPointSet");
-    const XmlNode* objs = pps ? pps->child("objects") : nullptr;
-    if (!objs) throw std::runtime_error("muscle '" + mu.path + "' has no path points");
-    for (auto& pn : objs->children) {
-        PathPointSpec pt;
-        std::string frame = pn->childText("socket_parent_frame");
-        if (!cx.baseFrame(frame, pt.body))
-            throw std::runtime_error("path point '" + pn->name() + "': parent frame '" + frame + "' must be a body");
-        if (pn->tag == "PathPoint") {
-            pt.kind = MOCOB200_PP_FIXED;
-            pt.location = vec3Of(pn->childText("location"), "location");
-        } else if (pn->tag == "ConditionalPathPoint") {
-            pt.kind = MOCOB200_PP_CONDITIONAL;
-            pt.location = vec3Of(pn->childText("location"), "location");
-            auto r = parseDoubles(pn->childText("range"));
-            if (r.size() != 2) throw std::runtime_error("ConditionalPathPoint '" + pn->name() + "': bad range");
-            pt.range[0] = r[0];
-            pt.range[1] = r[1];
-            pt.condCoord = leaf(pn->childText("socket_coordinate"));
-        } else if (pn->tag == "MovingPathPoint") {
-            pt.kind = MOCOB200_PP_MOVING;
-            const char* ax[3] = {"x", "y", "z"};
-            for (int a = 0; a < 3; ++a) {
-                const XmlNode* loc = pn->child(std::string(ax[a]) + "_location");
-                if (!loc) throw std::runtime_error("MovingPathPoint '" + pn->name() + "': missing location function");
-                pt.fn[a] = splineOf(*loc, "MovingPathPoint '" + pn->name() + "'");
-                pt.coord[a] = leaf(pn->childText(std::string("socket_") + ax[a] + "_coordinate"));
-            }
-        } else
-            throw std::runtime_error("unsupported path point type '" + pn->tag + "'");
-        mu.points.push_back(pt);
-    }
+    readPath(cx, n, mu);
     cx.M.actuatorOrder.emplace_back(1, (int)cx.M.muscles.size());
     cx.M.muscles.push_back(std::move(mu));
 }
 
+// PathActuator (Actuators/PathActuator.cpp:156-197), or — with musclesAsPathActuators — any force that carries a GeometryPath
+void readPathActuator(const Ctx& cx, const XmlNode& n, const std::string& prefix, bool isPathActuator) {
+    MuscleSpec mu;
+    mu.path = prefix + n.name();
+    mu.pathActuator = true;
+    mu.ignoreActivationDynamics = true;
+    mu.ignoreTendonCompliance = true;
+    mu.maxIsometricForce = isPathActuator ? dblOf(n, "optimal_force", 1.0) : 1.0;
+    mu.minControl = isPathActuator ? dblOf(n, "min_control", -std::numeric_limits<double>::infinity()) : -std::numeric_limits<double>::infinity();
+    mu.maxControl = isPathActuator ? dblOf(n, "max_control", std::numeric_limits<double>::infinity()) : std::numeric_limits<double>::infinity();
+    readPath(cx, n, mu);
+    cx.M.actuatorOrder.emplace_back(1, (int)cx.M.muscles.size());
+    cx.M.muscles.push_back(std::move(mu));
+}
+
+void readCoordinateActuator(const Ctx& cx, const XmlNode& n, const std::string& prefix) {
+    CoordActSpec a;
+    a.path = prefix + n.name();
+    a.coord = n.childText("coordinate");
+    a.optimalForce = dblOf(n, "optimal_force", 1.0);
+    a.minControl = dblOf(n, "min_control", a.minControl);
+    a.maxControl = dblOf(n, "max_control", a.maxControl);
+    cx.M.actuatorOrder.emplace_back(0, (int)cx.M.coordActs.size());
+    cx.M.coordActs.push_back(a);
+}
+
 void readForceLike(const Ctx& cx, const XmlNode& n, const std::string& prefix, const XmlNode* contactGeom) {
-    if (n.tag == "DeGrooteFregly2016Muscle") {
+    if (boolOf(n.childText("isDisabled"), false) || !boolOf(n.childText("appliesForce"), true)) return;
+    if (cx.asPathActuators && n.child("GeometryPath")) {
+        readPathActuator(cx, n, prefix, n.tag == "PathActuator");
+    } else if (n.tag == "DeGrooteFregly2016Muscle") {
         readMuscle(cx, n, prefix);
+    } else if (n.tag == "PathActuator") {
+        readPathActuator(cx, n, prefix, true);
     } else if (n.tag == "CoordinateActuator") {
-        CoordActSpec a;
-        a.path = prefix + n.name();
-        a.coord = n.childText("coordinate");
-        a.optimalForce = dblOf(n, "optimal_force", 1.0);
-        a.minControl = dblOf(n, "min_control", a.minControl);
-        a.maxControl = dblOf(n, "max_control", a.maxControl);
-        cx.M.actuatorOrder.emplace_back(0, (int)cx.M.coordActs.size());
-        cx.M.coordActs.push_back(a);
+        readCoordinateActuator(cx, n, prefix);
     } else if (n.tag == "SmoothSphereHalfSpaceForce") {
         if (!contactGeom) throw std::runtime_error("SmoothSphereHalfSpaceForce without a ContactGeometrySet");
         ContactSpec c;
@@ -196,59 +346,85 @@ void readForceLike(const Ctx& cx, const XmlNode& n, const std::string& prefix, c
 
 } // namespace
 
-ModelSpec loadOsim(const std::string& path) {
+ModelSpec loadOsim(const std::string& path, bool musclesAsPathActuators) {
     auto doc = parseXmlFile(path);
     if (doc->tag != "OpenSimDocument") throw std::runtime_error(path + ": not an OpenSimDocument");
     const std::string* ver = doc->attr("Version");
-    if (!ver || std::atoi(ver->c_str()) < 40000)
-        throw std::runtime_error(path + ": only document Version >= 40000 is supported");
+    const int version = ver ? std::atoi(ver->c_str()) : 0;
+    if (version < 30000) throw std::runtime_error(path + ": only document Version >= 30000 is supported");
     const XmlNode* model = doc->child("Model");
     if (!model) throw std::runtime_error(path + ": no <Model>");
     ModelSpec M;
     M.name = model->name();
     if (model->has("gravity")) M.gravity = vec3Of(model->childText("gravity"), "gravity");
     Ctx cx{M};
+    cx.v3 = version < 40000;
+    cx.asPathActuators = musclesAsPathActuators;
 
     const XmlNode* bs = model->child("BodySet");
     const XmlNode* bobjs = bs ? bs->child("objects") : nullptr;
     if (!bobjs) throw std::runtime_error(path + ": no BodySet");
+    std::vector<const XmlNode*> bodyNodes;
     for (auto& b : bobjs->children) {
         if (b->tag != "Body") throw std::runtime_error("unsupported BodySet entry '" + b->tag + "'");
+        if (cx.v3 && b->name() == "ground") continue; // Version 30000 lists ground as a body
         BodySpec B;
         B.name = b->name();
         B.mass = dblOf(*b, "mass", 0.0);
         B.com = vec3Of(b->childText("mass_center", "0 0 0"), "mass_center");
-        auto in = parseDoubles(b->childText("inertia", "0 0 0 0 0 0"));
-        if (in.size() != 6) throw std::runtime_error("body '" + B.name + "': inertia needs 6 numbers");
-        for (int i = 0; i < 6; ++i) B.inertiaCom[i] = in[i];
+        if (cx.v3) {
+            const char* tags[6] = {"inertia_xx", "inertia_yy", "inertia_zz", "inertia_xy", "inertia_xz", "inertia_yz"};
+            for (int i = 0; i < 6; ++i) B.inertiaCom[i] = dblOf(*b, tags[i], 0.0);
+            if (const XmlNode* ws = b->child("WrapObjectSet"))
+                if (const XmlNode* wo = ws->child("objects"))
+                    if (!wo->children.empty()) { /* wrap objects matter only when a path refers to them (refused there) */ }
+        } else {
+            auto in = parseDoubles(b->childText("inertia", "0 0 0 0 0 0"));
+            if (in.size() != 6) throw std::runtime_error("body '" + B.name + "': inertia needs 6 numbers");
+            for (int i = 0; i < 6; ++i) B.inertiaCom[i] = in[i];
+        }
         M.bodies.push_back(B);
+        bodyNodes.push_back(b.get());
     }
 
-    const XmlNode* js = model->child("JointSet");
-    const XmlNode* jobjs = js ? js->child("objects") : nullptr;
-    if (!jobjs) throw std::runtime_error(path + ": no JointSet");
-    for (auto& j : jobjs->children) {
-        JointSpec J;
-        J.name = j->name();
-        if (j->tag == "PinJoint") J.kind = MOCOB200_JOINT_PIN;
-        else if (j->tag == "SliderJoint") J.kind = MOCOB200_JOINT_SLIDER;
-        else if (j->tag == "PlanarJoint") J.kind = MOCOB200_JOINT_PLANAR;
-        else if (j->tag == "WeldJoint") J.kind = MOCOB200_JOINT_WELD;
-        else throw std::runtime_error("unsupported joint type '" + j->tag + "' (" + J.name + ")");
-        J.parent = cx.jointFrame(*j, j->childText("socket_parent_frame"));
-        J.child = cx.jointFrame(*j, j->childText("socket_child_frame"));
-        if (const XmlNode* cs = j->child("coordinates"))
-            for (auto& c : cs->children) {
-                if (c->tag != "Coordinate") continue;
-                CoordSpec C;
-                C.name = c->name();
-                auto r = parseDoubles(c->childText("range", "-10 10"));
-                if (r.size() == 2) { C.lo = r[0]; C.hi = r[1]; }
-                if (boolOf(c->childText("locked"), false) || boolOf(c->childText("prescribed"), false))
-                    throw std::runtime_error("coordinate '" + C.name + "': locked/prescribed coordinates are unsupported");
-                J.coords.push_back(C);
-            }
-        M.joints.push_back(J);
+    if (cx.v3) {
+        // Version 30000: every body owns the joint that connects it to its parent (Joint.cpp updateFromXMLNode, 30500 conversion):
+        // parent frame = (location_in_parent, orientation_in_parent) on parent_body, child frame = (location, orientation)
+        for (size_t bi = 0; bi < bodyNodes.size(); ++bi) {
+            const XmlNode* jh = bodyNodes[bi]->child("Joint");
+            if (!jh || jh->children.empty()) throw std::runtime_error("body '" + M.bodies[bi].name + "' has no joint");
+            const XmlNode* j = jh->children[0].get();
+            JointSpec J;
+            J.name = j->name();
+            J.kind = jointKindOf(j->tag, J.name);
+            if (boolOf(j->childText("reverse"), false)) throw std::runtime_error("joint '" + J.name + "': reversed joints are unsupported");
+            if (!cx.baseFrame(j->childText("parent_body"), J.parent.body))
+                throw std::runtime_error("joint '" + J.name + "': unknown parent_body");
+            J.child.body = (int)bi;
+            Vec3 o = vec3Of(j->childText("orientation_in_parent", "0 0 0"), "orientation_in_parent");
+            J.parent.X.R = rotXYZ(o.v[0], o.v[1], o.v[2]);
+            J.parent.X.p = vec3Of(j->childText("location_in_parent", "0 0 0"), "location_in_parent");
+            o = vec3Of(j->childText("orientation", "0 0 0"), "orientation");
+            J.child.X.R = rotXYZ(o.v[0], o.v[1], o.v[2]);
+            J.child.X.p = vec3Of(j->childText("location", "0 0 0"), "location");
+            if (const XmlNode* cs = j->child("CoordinateSet")) readCoordinates(cs->child("objects"), J);
+            if (J.kind == MOCOB200_JOINT_CUSTOM) readSpatialTransform(*j, J);
+            M.joints.push_back(J);
+        }
+    } else {
+        const XmlNode* js = model->child("JointSet");
+        const XmlNode* jobjs = js ? js->child("objects") : nullptr;
+        if (!jobjs) throw std::runtime_error(path + ": no JointSet");
+        for (auto& j : jobjs->children) {
+            JointSpec J;
+            J.name = j->name();
+            J.kind = jointKindOf(j->tag, J.name);
+            J.parent = cx.jointFrame(*j, j->childText("socket_parent_frame"));
+            J.child = cx.jointFrame(*j, j->childText("socket_child_frame"));
+            readCoordinates(j->child("coordinates"), J);
+            if (J.kind == MOCOB200_JOINT_CUSTOM) readSpatialTransform(*j, J);
+            M.joints.push_back(J);
+        }
     }
     if (const XmlNode* cs = model->child("ConstraintSet"))
         if (const XmlNode* o = cs->child("objects"))
@@ -262,6 +438,75 @@ ModelSpec loadOsim(const std::string& path) {
         if (const XmlNode* o = fs->child("objects"))
             for (auto& c : o->children) readForceLike(cx, *c, "/forceset/", cgobjs);
     return M;
+}
+
+// A ForceSet file appended to the model (AbstractTool force_set_files, e.g. reserve actuators). CoordinateActuators are
+// added; the names of entries of other classes (PointActuator, TorqueActuator residuals ...) are returned to the caller.
+std::vector<std::string> appendForceSetFile(ModelSpec& M, const std::string& path) {
+    auto doc = parseXmlFile(path);
+    const XmlNode* fs = doc->child("ForceSet");
+    const XmlNode* objs = fs ? fs->child("objects") : nullptr;
+    if (!objs) throw std::runtime_error(path + ": no ForceSet");
+    Ctx cx{M};
+    cx.v3 = true;
+    std::vector<std::string> skipped;
+    for (auto& c : objs->children) {
+        if (boolOf(c->childText("isDisabled"), false)) continue;
+        if (c->tag == "CoordinateActuator") readCoordinateActuator(cx, *c, "/forceset/");
+        else skipped.push_back(c->tag + ":" + c->name());
+    }
+    return skipped;
+}
+
+// ExternalLoads (Simulation/Model/ExternalLoads.cpp) + ExternalForce::setDataSource (ExternalForce.cpp:200-317): the three
+// columns whose labels start with the force / point / torque identifier become functions of time.
+void appendExternalLoads(ModelSpec& M, const std::string& xmlPath) {
+    auto doc = parseXmlFile(xmlPath);
+    const XmlNode* el = doc->child("ExternalLoads");
+    const XmlNode* objs = el ? el->child("objects") : nullptr;
+    if (!objs) throw std::runtime_error(xmlPath + ": no ExternalLoads");
+    std::string datafile = el->childText("datafile");
+    if (datafile.empty()) throw std::runtime_error(xmlPath + ": no datafile");
+    if (datafile[0] != '/') {
+        size_t sl = xmlPath.rfind('/');
+        datafile = (sl == std::string::npos ? std::string() : xmlPath.substr(0, sl + 1)) + datafile;
+    }
+    const StoTable tab = readSto(datafile);
+    Ctx cx{M};
+    cx.v3 = true;
+    auto functionsOf = [&](const std::string& id, PiecewisePoly* out) {
+        // getDataForIdentifier: the columns whose label starts with the identifier, in file order
+        std::vector<int> cols;
+        for (size_t c = 0; c < tab.labels.size(); ++c)
+            if (tab.labels[c].compare(0, id.size(), id) == 0) cols.push_back((int)c);
+        if (cols.size() != 3) throw std::runtime_error("ExternalForce: 3 unique components could not be identified for identifier: " + id);
+        const size_t nt = tab.time.size();
+        for (int a = 0; a < 3; ++a) {
+            const std::vector<double>& y = tab.cols[cols[a]];
+            if (nt == 1) out[a] = constantFunction(y[0]);
+            else if (nt <= 3) out[a] = piecewiseLinearFunction(tab.time, y);
+            else out[a] = fitNaturalSpline(tab.time, y, 3);
+        }
+    };
+    for (auto& f : objs->children) {
+        if (f->tag != "ExternalForce") continue;
+        if (boolOf(f->childText("isDisabled"), false) || !boolOf(f->childText("appliesForce"), true)) continue;
+        ExternalForceSpec X;
+        X.name = f->name();
+        if (!cx.baseFrame(f->childText("applied_to_body"), X.appliedTo) || X.appliedTo < 0)
+            throw std::runtime_error("ExternalForce '" + X.name + "': applied_to_body must be a body");
+        if (!cx.baseFrame(f->childText("force_expressed_in_body", "ground"), X.forceExpressedIn) ||
+            !cx.baseFrame(f->childText("point_expressed_in_body", "ground"), X.pointExpressedIn))
+            throw std::runtime_error("ExternalForce '" + X.name + "': unknown expressed-in body");
+        const std::string fid = f->childText("force_identifier"), pid = f->childText("point_identifier"), tid = f->childText("torque_identifier");
+        X.hasForce = !fid.empty();
+        X.hasPoint = X.hasForce && !pid.empty();
+        X.hasTorque = !tid.empty();
+        if (X.hasForce) functionsOf(fid, X.force);
+        if (X.hasPoint) functionsOf(pid, X.point);
+        if (X.hasTorque) functionsOf(tid, X.torque);
+        M.externalForces.push_back(std::move(X));
+    }
 }
 
 } // namespace mocob200

@@ -37,6 +37,8 @@ struct DevTables { // mocob200_tables with device (or shared-memory) pool pointe
     int nb, nq, nz, nc, nderiv_aux, nmus, npp, nspline, ncontact, ncact, ngoal, nppoly;
     int o_body_d, o_gravity, o_pp_d, o_mus_d, o_contact_d, o_cact_d, o_spline_data, o_ppoly_data;
     int o_body_i, o_pp_i, o_mus_i, o_contact_i, o_cact_i, o_spline_i, o_goal_i, o_ppoly_i;
+    int ncustom, o_cj_d, o_cj_i, o_body_cj; // custom (function-based) joints
+    int nxforce, o_xforce_i;                // external forces (functions of time)
     int implicit; // multibody dynamics mode
     int n_auxres;
     int n_integrand; // goals with an integrand, in goal order
@@ -84,10 +86,16 @@ __device__ inline double simm_spline(const DevTables& T, int id, double ax, int 
     const double* c = b + n;
     const double* d = c + n;
     const double scale = d[n];
+    if (deriv == 2) { // second derivative (SimmSpline.cpp:578-685): zero outside the knots, 2 c at the end knots
+        if (ax < x[0] || ax > x[n - 1]) return 0.0;
+        if (fabs(ax - x[0]) <= 2e-13) return scale * 2.0 * c[0];
+        if (fabs(ax - x[n - 1]) <= 2e-13) return scale * 2.0 * c[n - 1];
+    } else {
     if (ax < x[0]) return scale * (deriv ? b[0] : y[0] + (ax - x[0]) * b[0]);
     if (ax > x[n - 1]) return scale * (deriv ? b[n - 1] : y[n - 1] + (ax - x[n - 1]) * b[n - 1]);
     if (fabs(ax - x[0]) <= 2e-13) return scale * (deriv ? b[0] : y[0]);
     if (fabs(ax - x[n - 1]) <= 2e-13) return scale * (deriv ? b[n - 1] : y[n - 1]);
+    }
     int k = 0;
     if (n >= 3) { // x[k] <= ax <= x[k+1]: interpolation guess, then walk (the knots are sorted)
         k = (int)((ax - x[0]) / (x[n - 1] - x[0]) * (double)(n - 1));
@@ -96,8 +104,81 @@ __device__ inline double simm_spline(const DevTables& T, int id, double ax, int 
         while (k < n - 2 && ax > x[k + 1]) ++k;
     }
     const double dx = ax - x[k];
+    if (deriv == 2) return scale * (2.0 * c[k] + 6.0 * dx * d[k]);
     if (deriv) return scale * (b[k] + dx * (2.0 * c[k] + 3.0 * dx * d[k]));
     return scale * (y[k] + dx * (b[k] + dx * (c[k] + dx * d[k])));
+}
+
+// ---- custom (function-based) joint: SimbodyEngine/CustomJoint.cpp:205-273 -> SimTK::MobilizedBody::FunctionBased.
+// X_FM(q) = [ R(A0, f0) R(A1, f1) R(A2, f2) , A3 f3 + A4 f4 + A5 f5 ], u = qdot.
+// Everything below is written from that definition: the joint's spatial velocity in F is
+//   omega = th0' A0 + th1' R0 A1 + th2' R0 R1 A2 ,  v = sum_i Ai fi'          (thi' = dfi/dq u)
+// so the motion axis of coordinate k collects the terms whose function reads q_k, and the velocity-product acceleration
+// (what remains of d/dt(omega, v) at zero udot) is
+//   b_omega = w0 x w1 + (w0 + w1) x w2 + sum_i Wi fi'' u^2 ,  b_v = sum_i Ai fi'' u^2     (wi = thi' Wi).
+struct CustomJointEval {
+    double R[9];     // R_FM
+    V3 p;            // p_FM (in F)
+    V3 g[6];         // W0, W1, W2 (rotation axes carried by the preceding rotations), A3, A4, A5 — all in F
+    double df[6], d2f[6];
+    int qi[6];       // coordinate driving axis i, or -1
+};
+__device__ inline void rot_axis(double angle, V3 a, double* R) { // cos 1 + (1 - cos) a a^T + sin [a]x, row-major
+    double s, c;
+    sincos(angle, &s, &c);
+    const double t = 1.0 - c;
+    R[0] = t * a.x * a.x + c;       R[1] = t * a.x * a.y - s * a.z; R[2] = t * a.x * a.z + s * a.y;
+    R[3] = t * a.y * a.x + s * a.z; R[4] = t * a.y * a.y + c;       R[5] = t * a.y * a.z - s * a.x;
+    R[6] = t * a.z * a.x - s * a.y; R[7] = t * a.z * a.y + s * a.x; R[8] = t * a.z * a.z + c;
+}
+__device__ inline void custom_joint_eval(const DevTables& T, int cj, const double* q, CustomJointEval& E) {
+    const double* d = T.dbl + T.o_cj_d + cj * MOCOB200_CJ_DSTRIDE;
+    const int* rec = T.idx + T.o_cj_i + cj * MOCOB200_CJ_ISTRIDE;
+    double f[6];
+    for (int a = 0; a < 6; ++a) {
+        const int kind = rec[3 * a], qi = rec[3 * a + 1];
+        E.qi[a] = kind == MOCOB200_FN_CONSTANT ? -1 : qi;
+        if (kind == MOCOB200_FN_LINEAR) { f[a] = d[5 * a + 3] * q[qi] + d[5 * a + 4]; E.df[a] = d[5 * a + 3]; E.d2f[a] = 0.0; }
+        else if (kind == MOCOB200_FN_SIMMSPLINE) {
+            f[a] = simm_spline(T, rec[3 * a + 2], q[qi], 0);
+            E.df[a] = simm_spline(T, rec[3 * a + 2], q[qi], 1);
+            E.d2f[a] = simm_spline(T, rec[3 * a + 2], q[qi], 2);
+        } else { f[a] = d[5 * a + 4]; E.df[a] = 0.0; E.d2f[a] = 0.0; }
+    }
+    double R0[9], R1[9], R2[9], R01[9];
+    rot_axis(f[0], ld3(d), R0);
+    rot_axis(f[1], ld3(d + 5), R1);
+    rot_axis(f[2], ld3(d + 10), R2);
+    mm3(R0, R1, R01);
+    mm3(R01, R2, E.R);
+    E.g[0] = ld3(d);
+    E.g[1] = rmul(R0, ld3(d + 5));
+    E.g[2] = rmul(R01, ld3(d + 10));
+    E.p = mk(0, 0, 0);
+    for (int a = 3; a < 6; ++a) { E.g[a] = ld3(d + 5 * a); E.p = E.p + f[a] * E.g[a]; }
+}
+// velocity-product acceleration of the joint (in F) for the speeds u
+__device__ inline void custom_joint_bias(const CustomJointEval& E, const double* u, V3& bw, V3& bv) {
+    V3 w[3];
+    bw = mk(0, 0, 0);
+    bv = mk(0, 0, 0);
+    for (int i = 0; i < 3; ++i) {
+        const double ui = E.qi[i] >= 0 ? u[E.qi[i]] : 0.0;
+        w[i] = (E.df[i] * ui) * E.g[i];
+        bw = bw + (E.d2f[i] * ui * ui) * E.g[i];
+    }
+    bw = bw + cross(w[0], w[1]) + cross(w[0] + w[1], w[2]);
+    for (int i = 3; i < 6; ++i) {
+        const double ui = E.qi[i] >= 0 ? u[E.qi[i]] : 0.0;
+        bv = bv + (E.d2f[i] * ui * ui) * E.g[i];
+    }
+}
+// motion axis of the joint's coordinate qk (absolute index) in F: angular a, linear l (acting at the M origin)
+__device__ inline void custom_joint_axis(const CustomJointEval& E, int qk, V3& a, V3& l) {
+    a = mk(0, 0, 0);
+    l = mk(0, 0, 0);
+    for (int i = 0; i < 3; ++i) if (E.qi[i] == qk) a = a + E.df[i] * E.g[i];
+    for (int i = 3; i < 6; ++i) if (E.qi[i] == qk) l = l + E.df[i] * E.g[i];
 }
 
 // ---- piecewise polynomial (tracking references; natural spline fitted on the host)
@@ -180,9 +261,14 @@ __device__ inline MuscleOut dgf_muscle(const double* p, int flags, double mtLeng
     const double c1 = 0.200, c2 = 1.0, c3 = 0.200;
     const bool rigid = flags & MOCOB200_MUS_FLAG_IGNORE_TENDON_COMPLIANCE;
     const bool implicitT = flags & MOCOB200_MUS_FLAG_TENDON_IMPLICIT;
+    MuscleOut o;
+    if (flags & MOCOB200_MUS_FLAG_PATH_ACTUATOR) { // PathActuator::computeActuation: optimal_force x control (PathActuator.cpp:156-165)
+        o.tendonForce = Fmax * activation;
+        o.residual = 0.0; o.nfDeriv = 0.0; o.linResidDeriv = 0.0;
+        return o;
+    }
     const double fiberWidth = lopt * sin(alpha0);
     const double vmax = vmaxN * lopt;
-    MuscleOut o;
     // length info
     const double normTendonLength = rigid ? 1.0 : log((1.0 / c1) * (normTendonForce + c3)) / kT + c2;
     const double tendonLength = lslack * normTendonLength;
@@ -272,7 +358,18 @@ __device__ inline void kinematics(const DevTables& T, const double* q, const dou
         V3 oM = oF;
         const V3 xF = mk(RGF[0], RGF[3], RGF[6]), yF = mk(RGF[1], RGF[4], RGF[7]), zF = mk(RGF[2], RGF[5], RGF[8]);
         V3 wrel = mk(0, 0, 0), vtr = mk(0, 0, 0);
-        if (kind == MOCOB200_JOINT_PIN || kind == MOCOB200_JOINT_PLANAR) {
+        if (kind == MOCOB200_JOINT_CUSTOM) {
+            CustomJointEval E;
+            custom_joint_eval(T, T.idx[T.o_body_cj + b], q, E);
+            mm3(RGF, E.R, RGM);
+            oM = oF + rmul(RGF, E.p);
+            for (int k = 0; k < bi[3]; ++k) {
+                V3 a, l;
+                custom_joint_axis(E, q0 + k, a, l);
+                wrel = wrel + u[q0 + k] * rmul(RGF, a);
+                vtr = vtr + u[q0 + k] * rmul(RGF, l);
+            }
+        } else if (kind == MOCOB200_JOINT_PIN || kind == MOCOB200_JOINT_PLANAR) {
             double s, c;
             sincos(q[q0], &s, &c);
             // R_GM = R_GF * Rz(theta)
@@ -364,7 +461,8 @@ __device__ inline V3 contact_force(const DevTables& T, int ci, Scratch& S, bool 
 // (GeometryPath.cpp:306-432, 817-864, 1117-1145; Point.cpp:130-140; ConditionalPathPoint.cpp:160-169;
 //  MovingPathPoint.cpp:216-315, 374-392; PathActuator.cpp:170-197).
 __device__ inline MuscleOut muscle_force(const DevTables& T, int m, const double* q, const double* u, const double* z,
-                                        const double* ctl, const double* deriv, Scratch& S, bool apply, bool wantStiffness) {
+                                        const double* ctl, const double* deriv, Scratch& S, bool apply, bool wantStiffness,
+                                        double* lengthSpeed = nullptr) {
     const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
     const double* md = T.dbl + T.o_mus_d + m * MOCOB200_MUS_DSTRIDE;
     const int first = mi[0], count = mi[1], flags = mi[5];
@@ -411,6 +509,7 @@ __device__ inline MuscleOut muscle_force(const DevTables& T, int m, const double
         if (na < MOCOB200_MAXPPM) { pos[na] = pG; body[na] = b; mcoord[na] = mc; dPdq[na] = dp; }
         ++na;
     }
+    if (lengthSpeed) { lengthSpeed[0] = length; lengthSpeed[1] = speed; }
     double activation = (flags & MOCOB200_MUS_FLAG_IGNORE_ACTIVATION_DYNAMICS) ? ctl[mi[2]] : z[mi[3]];
     const double ntf = (mi[4] >= 0) ? z[mi[4]] : NAN;
     const double ntfd = (mi[6] >= 0) ? deriv[mi[6]] : NAN;
@@ -742,6 +841,26 @@ __device__ inline void eval_point(const DevTables& T, const double* in, double* 
             const V3 c = rmul(S.R[b], ld3(bd + 25));
             S.Ff[b] = S.Ff[b] + m * g;
             S.Fm[b] = S.Fm[b] + cross(c, m * g);
+        }
+        // external forces (ExternalForce::computeForce, Model/ExternalForce.cpp:330-355)
+        for (int f = 0; f < T.nxforce; ++f) {
+            const int* xi = T.idx + T.o_xforce_i + f * MOCOB200_XFORCE_ISTRIDE;
+            const int body = xi[0];
+            if (xi[3] >= 0) {
+                V3 force = mk(ppoly_eval(T, xi[3], time), ppoly_eval(T, xi[4], time), ppoly_eval(T, xi[5], time));
+                if (xi[1] >= 0) force = rmul(S.R[xi[1]], force);
+                V3 point = S.p[body];
+                if (xi[6] >= 0) {
+                    point = mk(ppoly_eval(T, xi[6], time), ppoly_eval(T, xi[7], time), ppoly_eval(T, xi[8], time));
+                    if (xi[2] >= 0) point = S.p[xi[2]] + rmul(S.R[xi[2]], point);
+                }
+                apply_point_force(S, body, point, force);
+            }
+            if (xi[9] >= 0) {
+                V3 torque = mk(ppoly_eval(T, xi[9], time), ppoly_eval(T, xi[10], time), ppoly_eval(T, xi[11], time));
+                if (xi[1] >= 0) torque = rmul(S.R[xi[1]], torque);
+                S.Fm[body] = S.Fm[body] + torque;
+            }
         }
         for (int m = 0; m < T.nmus; ++m) {
             const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;

@@ -51,6 +51,7 @@ struct WarpAux {
     const int* loc_dir; const int* loc_kind; const int* loc_owner; const int* loc_role;
     const int* dir_class;
     int o_mlen, o_mspd, o_mout, o_Rm;
+    int o_cjs; // per custom joint (position-dependent): 6 axis vectors in ground (18), df[6], d2f[6]
     int lockstep;
     int poison; // development switch (MOCOB200_POISON_SCRATCH=1): every evaluation starts from NaN-filled scratch
     int ws_doubles;
@@ -99,7 +100,23 @@ __device__ inline void wk_body_pose(const WarpCtx& C, int b, const double* q) {
     V3 oM = oF;
     double* ax = C.at(A.o_a);
     double* lx = C.at(A.o_l);
-    if (kind == MOCOB200_JOINT_PIN || kind == MOCOB200_JOINT_PLANAR) {
+    if (kind == MOCOB200_JOINT_CUSTOM) {
+        // function-based joint (point_eval.cuh: custom_joint_eval): transform, motion axes, and what the velocity pass
+        // needs for the velocity-product acceleration (axis vectors in ground, first and second function derivatives)
+        const int cj = T.idx[T.o_body_cj + b];
+        CustomJointEval E;
+        custom_joint_eval(T, cj, q, E);
+        mm3(RGF, E.R, RGM);
+        oM = oF + rmul(RGF, E.p);
+        double* cs = C.at(A.o_cjs) + 30 * cj;
+        for (int i = 0; i < 6; ++i) { stv(cs + 3 * i, rmul(RGF, E.g[i])); cs[18 + i] = E.df[i]; cs[24 + i] = E.d2f[i]; }
+        for (int k = 0; k < bi[3]; ++k) {
+            V3 a, l;
+            custom_joint_axis(E, q0 + k, a, l);
+            stv(ax + 3 * (q0 + k), rmul(RGF, a));
+            stv(lx + 3 * (q0 + k), rmul(RGF, l));
+        }
+    } else if (kind == MOCOB200_JOINT_PIN || kind == MOCOB200_JOINT_PLANAR) {
         double s, c;
         sincos(q[q0], &s, &c);
 #pragma unroll
@@ -151,9 +168,32 @@ __device__ inline void wk_body_velocity(const WarpCtx& C, int b, const double* u
         aP = ldv(C.at(A.o_ac) + 3 * par);
     }
     V3 wrel = mk(0, 0, 0), vrel = mk(0, 0, 0), wrd = mk(0, 0, 0), vrd = mk(0, 0, 0);
+    V3 bw = mk(0, 0, 0), bv = mk(0, 0, 0); // velocity-product acceleration of a function-based joint's own motion
     const double* ax = C.at(A.o_a) + 3 * q0;
     const double* lx = C.at(A.o_l) + 3 * q0;
-    if (kind == MOCOB200_JOINT_PIN || kind == MOCOB200_JOINT_PLANAR) {
+    if (kind == MOCOB200_JOINT_CUSTOM) {
+        for (int k = 0; k < bi[3]; ++k) {
+            const V3 a = ldv(ax + 3 * k), l = ldv(lx + 3 * k);
+            wrel = wrel + u[q0 + k] * a;
+            vrel = vrel + u[q0 + k] * l;
+            if (udot) { wrd = wrd + udot[q0 + k] * a; vrd = vrd + udot[q0 + k] * l; }
+        }
+        const int cj = T.idx[T.o_body_cj + b];
+        const int* rec = T.idx + T.o_cj_i + cj * MOCOB200_CJ_ISTRIDE;
+        const double* cs = C.at(A.o_cjs) + 30 * cj;
+        V3 w[3];
+        for (int i = 0; i < 3; ++i) {
+            const double ui = rec[3 * i] != MOCOB200_FN_CONSTANT ? u[rec[3 * i + 1]] : 0.0;
+            const V3 g = ldv(cs + 3 * i);
+            w[i] = (cs[18 + i] * ui) * g;
+            bw = bw + (cs[24 + i] * ui * ui) * g;
+        }
+        bw = bw + cross(w[0], w[1]) + cross(w[0] + w[1], w[2]);
+        for (int i = 3; i < 6; ++i) {
+            const double ui = rec[3 * i] != MOCOB200_FN_CONSTANT ? u[rec[3 * i + 1]] : 0.0;
+            bv = bv + (cs[24 + i] * ui * ui) * ldv(cs + 3 * i);
+        }
+    } else if (kind == MOCOB200_JOINT_PIN || kind == MOCOB200_JOINT_PLANAR) {
         const V3 zF = ldv(ax);
         wrel = u[q0] * zF;
         if (udot) wrd = udot[q0] * zF;
@@ -174,8 +214,9 @@ __device__ inline void wk_body_velocity(const WarpCtx& C, int b, const double* u
     stv(C.at(A.o_w) + 3 * b, wB);
     stv(C.at(A.o_v) + 3 * b, vM + cross(wB, sv));
     // the joint axes are fixed in the parent: d(axis)/dt = wP x axis
-    const V3 al = alP + cross(wP, wrel) + wrd;
-    const V3 aM = aP + cross(alP, r) + cross(wP, cross(wP, r)) + 2.0 * cross(wP, vrel) + vrd;
+    V3 al = alP + cross(wP, wrel) + wrd;
+    V3 aM = aP + cross(alP, r) + cross(wP, cross(wP, r)) + 2.0 * cross(wP, vrel) + vrd;
+    if (kind == MOCOB200_JOINT_CUSTOM) { al = al + bw; aM = aM + bv; }
     stv(C.at(A.o_al) + 3 * b, al);
     stv(C.at(A.o_ac) + 3 * b, aM + cross(al, sv) + cross(wB, cross(wB, sv)));
 }

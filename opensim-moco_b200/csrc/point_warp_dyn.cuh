@@ -34,6 +34,28 @@ __device__ inline void wk_gather_body(const WarpCtx& C, int b) {
         F = F + f;
         N = N + cross(ldv(ppos + 3 * pp) - pB, f);
     }
+    for (int f = 0; f < T.nxforce; ++f) { // ExternalForce::computeForce (Model/ExternalForce.cpp:330-355); functions of time in o_ref
+        const int* xi = T.idx + T.o_xforce_i + f * MOCOB200_XFORCE_ISTRIDE;
+        if (xi[0] != b) continue;
+        const double* ref = C.at(A.o_ref);
+        if (xi[3] >= 0) {
+            V3 force = mk(ref[xi[3]], ref[xi[4]], ref[xi[5]]);
+            if (xi[1] >= 0) force = rmul(C.at(A.o_R) + 9 * xi[1], force);
+            V3 arm = mk(0, 0, 0);
+            if (xi[6] >= 0) {
+                V3 point = mk(ref[xi[6]], ref[xi[7]], ref[xi[8]]);
+                if (xi[2] >= 0) point = ldv(C.at(A.o_p) + 3 * xi[2]) + rmul(C.at(A.o_R) + 9 * xi[2], point);
+                arm = point - pB;
+            }
+            F = F + force;
+            N = N + cross(arm, force);
+        }
+        if (xi[9] >= 0) {
+            V3 torque = mk(ref[xi[9]], ref[xi[10]], ref[xi[11]]);
+            if (xi[1] >= 0) torque = rmul(C.at(A.o_R) + 9 * xi[1], torque);
+            N = N + torque;
+        }
+    }
     for (int c = 0; c < T.ncontact; ++c) {
         const int* cidx = T.idx + T.o_contact_i + c * MOCOB200_CONTACT_ISTRIDE;
         if (cidx[0] != b && cidx[1] != b) continue;
@@ -235,7 +257,7 @@ __device__ __forceinline__ void warp_eval_point_t(const DevTables& T, const Warp
     }
     PHASE_MARK(0);
     // lane-parallel table look-ups first: tracking references at this time, splines of the moving path points at this q
-    if ((mask >> 1) && (reuse == 0 || time_moved))
+    if (((mask >> 1) || (dyn && T.nxforce > 0)) && (reuse == 0 || time_moved))
         for (int r = lane; r < T.nppoly; r += 32) ws[A.o_ref + r] = ppoly_eval(T, r, time);
     if (dyn && reuse == 0)
         for (int t = lane; t < 6 * A.nmpp; t += 32) wk_moving_point_spline(C, t, q);

@@ -20,6 +20,9 @@ struct Frames { // everything expressed in ground
     // per dof: unit twist of the joint (angular axis, linear axis acting at jointPoint), in ground
     Vec3<S> axA[kMaxDof], axL[kMaxDof];
     int dofBody[kMaxDof];
+    // velocity-product acceleration of the joint's own motion (d/dt of the axes relative to F, times the speeds), in ground:
+    // zero for the constant-axis joints, non-zero for function-based (custom) joints
+    Vec3<S> biasA[kMaxBodies], biasL[kMaxBodies];
 };
 
 // A wrench accumulated about the GROUND ORIGIN.
@@ -33,12 +36,58 @@ struct Wrench {
 // opensim-core's joints create (SimbodyEngine/PinJoint.cpp:40-44, SliderJoint.cpp, PlanarJoint.cpp:40-44,
 // WeldJoint.cpp): Pin = rotation about Z; Slider = translation along X; Planar = (rotation about Z,
 // translation along X, translation along Y of F); Weld = none.
-inline int jointDofs(int kind) { return kind == MOCOB200_JOINT_PLANAR ? 3 : (kind == MOCOB200_JOINT_WELD ? 0 : 1); }
+inline int jointDofs(const int* bodyRec) { return bodyRec[3]; }
 inline void jointAxis(int kind, int k, double a[3], double l[3]) {
     a[0] = a[1] = a[2] = l[0] = l[1] = l[2] = 0;
     if (kind == MOCOB200_JOINT_PIN) a[2] = 1;
     else if (kind == MOCOB200_JOINT_SLIDER) l[0] = 1;
     else if (kind == MOCOB200_JOINT_PLANAR) { if (k == 0) a[2] = 1; else l[k - 1] = 1; }
+}
+
+// Scalar function of a custom joint's TransformAxis and its first derivative (Common/Constant.cpp, LinearFunction.cpp:
+// SimTK::Function::Linear c0 x + c1, SimmSpline.cpp:511-685 inside MultiplierFunction.cpp), any scalar type X.
+template <class X>
+void axisFunction(const Model& M, const int* rec /*kind | q | spline*/, const double* d /*axis(3) c0 c1*/, const X& q, X& value, X& slope) {
+    if (rec[0] == MOCOB200_FN_LINEAR) { value = X(d[3]) * q + X(d[4]); slope = X(d[3]); }
+    else if (rec[0] == MOCOB200_FN_SIMMSPLINE) { value = simmSpline<X>(M, rec[2], q, false); slope = simmSpline<X>(M, rec[2], q, true); }
+    else { value = X(d[4]); slope = X(0.0); }
+}
+
+// Function-based mobilizer (CustomJoint.cpp:205-273 -> SimTK::MobilizedBody::FunctionBased): X_FM(q) =
+// [ R(A0, f0) R(A1, f1) R(A2, f2) , A3 f3 + A4 f4 + A5 f5 ], u = qdot. Written from that definition alone: the motion axes
+// are the partial derivatives of the joint's spatial velocity (angular: successive rotation axes carried by the preceding
+// rotations; linear: the translation axes), and their time derivatives come from evaluating the same expressions on dual
+// numbers seeded with the joint speeds. Outputs in the F frame.
+template <class S>
+void customJoint(const Model& M, int cj, int q0, int nd, const S* q, const S* u, Mat3<S>& R_FM, Vec3<S>& p_FM, Vec3<S>* axA, Vec3<S>* axL,
+                 Vec3<S>& biasA, Vec3<S>& biasL) {
+    typedef Dual<S> X;
+    const double* d = M.cjD(cj);
+    const int* rec = M.cjI(cj);
+    X f[6], df[6];
+    for (int a = 0; a < 6; ++a) {
+        const int qi = rec[3 * a + 1];
+        const X arg = qi >= 0 ? X(q[qi], u[qi]) : X(0.0);
+        axisFunction<X>(M, rec + 3 * a, d + 5 * a, arg, f[a], df[a]);
+    }
+    // rotation axes in F: W0 = A0, W1 = R0 A1, W2 = R0 R1 A2
+    const Mat3<X> R0 = rotAxis<X>(f[0], d[0], d[1], d[2]), R1 = rotAxis<X>(f[1], d[5], d[6], d[7]), R2 = rotAxis<X>(f[2], d[10], d[11], d[12]);
+    const Mat3<X> R01 = R0 * R1, R = R01 * R2;
+    const Vec3<X> W[3] = {Vec3<X>(X(d[0]), X(d[1]), X(d[2])), R0 * Vec3<X>(X(d[5]), X(d[6]), X(d[7])), R01 * Vec3<X>(X(d[10]), X(d[11]), X(d[12]))};
+    for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) R_FM.m[r][c] = R.m[r][c].v;
+    Vec3<X> p;
+    for (int a = 3; a < 6; ++a) p = p + f[a] * Vec3<X>(X(d[5 * a]), X(d[5 * a + 1]), X(d[5 * a + 2]));
+    p_FM = Vec3<S>(p.x.v, p.y.v, p.z.v);
+    biasA = Vec3<S>(); biasL = Vec3<S>();
+    for (int k = 0; k < nd; ++k) {
+        Vec3<X> a, l;
+        for (int i = 0; i < 3; ++i) if (rec[3 * i + 1] == q0 + k) a = a + df[i] * W[i];
+        for (int i = 3; i < 6; ++i) if (rec[3 * i + 1] == q0 + k) l = l + df[i] * Vec3<X>(X(d[5 * i]), X(d[5 * i + 1]), X(d[5 * i + 2]));
+        axA[k] = Vec3<S>(a.x.v, a.y.v, a.z.v);
+        axL[k] = Vec3<S>(l.x.v, l.y.v, l.z.v);
+        biasA = biasA + u[q0 + k] * Vec3<S>(a.x.d, a.y.d, a.z.d);
+        biasL = biasL + u[q0 + k] * Vec3<S>(l.x.d, l.y.d, l.z.d);
+    }
 }
 
 // Position and velocity kinematics, base to tip.
@@ -56,7 +105,9 @@ void kinematics(const Model& M, const S* q, const S* u, Frames<S>& K) {
         const Vec3<S> oF = oP + R_GP * p_PF;
         // joint transform X_FM(q)
         Mat3<S> R_FM; Vec3<S> p_FM;
-        if (kind == MOCOB200_JOINT_PIN) R_FM = rotZ(q[q0]);
+        Vec3<S> cAxA[6], cAxL[6], cBiasA, cBiasL;
+        if (kind == MOCOB200_JOINT_CUSTOM) customJoint<S>(M, M.customOf(b), q0, bi[3], q, u, R_FM, p_FM, cAxA, cAxL, cBiasA, cBiasL);
+        else if (kind == MOCOB200_JOINT_PIN) R_FM = rotZ(q[q0]);
         else if (kind == MOCOB200_JOINT_SLIDER) p_FM = Vec3<S>(q[q0], S(0.0), S(0.0));
         else if (kind == MOCOB200_JOINT_PLANAR) { R_FM = rotZ(q[q0]); p_FM = Vec3<S>(q[q0 + 1], q[q0 + 2], S(0.0)); }
         const Mat3<S> R_GM = R_GF * R_FM;
@@ -67,12 +118,19 @@ void kinematics(const Model& M, const S* q, const S* u, Frames<S>& K) {
         K.origin[b] = oM - K.R[b] * p_BM;
         // velocity: relative angular velocity and relative velocity of the M origin, both fixed in F
         Vec3<S> wRel, vRel;
-        const int nd = jointDofs(kind);
+        const int nd = jointDofs(bi);
+        K.biasA[b] = kind == MOCOB200_JOINT_CUSTOM ? R_GF * cBiasA : Vec3<S>();
+        K.biasL[b] = kind == MOCOB200_JOINT_CUSTOM ? R_GF * cBiasL : Vec3<S>();
         for (int k = 0; k < nd; ++k) {
-            double a[3], l[3];
-            jointAxis(kind, k, a, l);
-            K.axA[q0 + k] = R_GF * Vec3<S>(S(a[0]), S(a[1]), S(a[2]));
-            K.axL[q0 + k] = R_GF * Vec3<S>(S(l[0]), S(l[1]), S(l[2]));
+            if (kind == MOCOB200_JOINT_CUSTOM) {
+                K.axA[q0 + k] = R_GF * cAxA[k];
+                K.axL[q0 + k] = R_GF * cAxL[k];
+            } else {
+                double a[3], l[3];
+                jointAxis(kind, k, a, l);
+                K.axA[q0 + k] = R_GF * Vec3<S>(S(a[0]), S(a[1]), S(a[2]));
+                K.axL[q0 + k] = R_GF * Vec3<S>(S(l[0]), S(l[1]), S(l[2]));
+            }
             K.dofBody[q0 + k] = b;
             wRel = wRel + u[q0 + k] * K.axA[q0 + k];
             vRel = vRel + u[q0 + k] * K.axL[q0 + k];
@@ -105,7 +163,7 @@ void inverseDynamics(const Model& M, const Frames<S>& K, const S* u, const S* ud
     for (int b = 0; b < M.nb; ++b) {
         const double* d = M.bodyD(b);
         const int* bi = M.bodyI(b);
-        const int parent = bi[0], q0 = bi[2], nd = jointDofs(bi[1]);
+        const int parent = bi[0], q0 = bi[2], nd = jointDofs(bi);
         Vec3<S> alP, aP, wP, oP;
         if (parent >= 0) { alP = alpha[parent]; aP = aOrigin[parent]; wP = K.omega[parent]; oP = K.origin[parent]; }
         Vec3<S> wRel, vRel, wRelDot, vRelDot;
@@ -119,8 +177,8 @@ void inverseDynamics(const Model& M, const Frames<S>& K, const S* u, const S* ud
         Vec3<S> al = alP + wRelDot;
         Vec3<S> aM = aP + cross(alP, r) + vRelDot;
         if (withVelocity) {
-            al = al + cross(wP, wRel);
-            aM = aM + cross(wP, cross(wP, r)) + S(2.0) * cross(wP, vRel);
+            al = al + cross(wP, wRel) + K.biasA[b];
+            aM = aM + cross(wP, cross(wP, r)) + S(2.0) * cross(wP, vRel) + K.biasL[b];
         }
         Vec3<S> aB = aM + cross(al, s);
         const Vec3<S> w = K.omega[b];
@@ -151,7 +209,7 @@ void inverseDynamics(const Model& M, const Frames<S>& K, const S* u, const S* ud
     }
     for (int b = M.nb - 1; b >= 0; --b) {
         const int* bi = M.bodyI(b);
-        const int parent = bi[0], q0 = bi[2], nd = jointDofs(bi[1]);
+        const int parent = bi[0], q0 = bi[2], nd = jointDofs(bi);
         const Vec3<S> mAtJoint = need[b].m - cross(K.jointPoint[b], need[b].f);
         for (int k = 0; k < nd; ++k) tau[q0 + k] = dot(K.axA[q0 + k], mAtJoint) + dot(K.axL[q0 + k], need[b].f);
         if (parent >= 0) { need[parent].f = need[parent].f + need[b].f; need[parent].m = need[parent].m + need[b].m; }
@@ -198,7 +256,7 @@ void massMatrix(const Model& M, const Frames<S>& K, S* Mass /* nq x nq row-major
         int bb = b;
         while (bb >= 0) {
             const int* bi = M.bodyI(bb);
-            const int q0 = bi[2], nd = jointDofs(bi[1]);
+            const int q0 = bi[2], nd = jointDofs(bi);
             for (int k = 0; k < nd; ++k) {
                 const int j = q0 + k;
                 if (j > i) continue;

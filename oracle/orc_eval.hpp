@@ -122,6 +122,12 @@ MuscleResult<S> evalMuscle(const Model& M, int m, const S* q, const S* u, const 
     const int* mi = M.musI(m);
     pathGeometry(M, m, q, u, K, P);
     const int flags = mi[5];
+    if (flags & MOCOB200_MUS_FLAG_PATH_ACTUATOR) { // PathActuator::computeActuation: optimal_force x control (PathActuator.cpp:156-165)
+        MuscleResult<S> r{};
+        r.tendonForce = S(M.musD(m)[0]) * ctl[mi[2]];
+        r.equilibriumResidual = S(0.0); r.normTendonForceRate = S(0.0); r.linearizedResidualRate = S(0.0);
+        return r;
+    }
     const S activation = (flags & MOCOB200_MUS_FLAG_IGNORE_ACTIVATION_DYNAMICS) ? ctl[mi[2]] : z[mi[3]];
     const S ntf = mi[4] >= 0 ? z[mi[4]] : S(NAN);
     const S ntfRate = mi[6] >= 0 ? auxDeriv[mi[6]] : S(NAN);
@@ -178,6 +184,25 @@ void evalPoint(const Model& M, const S* in, S* out, unsigned mask = 0xffffffffu)
         for (int b = 0; b < M.nb; ++b) {
             const S m(M.bodyD(b)[24]);
             applied[b].addForceAt(K.origin[b] + K.comOffset[b], m * Vec3<S>(S(g[0]), S(g[1]), S(g[2])));
+        }
+        // ExternalForce::computeForce (Model/ExternalForce.cpp:330-355): force / torque re-expressed in ground, the point
+        // taken from its expressed-in frame to ground; applied to the body at that point
+        for (int f = 0; f < M.T->nxforce; ++f) {
+            const int* xi = M.xforceI(f);
+            const int body = xi[0];
+            auto vecAt = [&](int o) { return Vec3<S>(piecewisePoly(M, xi[o], time), piecewisePoly(M, xi[o + 1], time), piecewisePoly(M, xi[o + 2], time)); };
+            if (xi[3] >= 0) {
+                Vec3<S> force = vecAt(3);
+                if (xi[1] >= 0) force = K.R[xi[1]] * force;
+                Vec3<S> point = K.origin[body];
+                if (xi[6] >= 0) point = stationPosition(K, xi[2], vecAt(6));
+                applied[body].addForceAt(point, force);
+            }
+            if (xi[9] >= 0) {
+                Vec3<S> torque = vecAt(9);
+                if (xi[1] >= 0) torque = K.R[xi[1]] * torque;
+                applied[body].m = applied[body].m + torque;
+            }
         }
         S* zdot = out + nq; S* auxres = zdot + nz;
         static thread_local PathState<S> P;

@@ -51,6 +51,24 @@ inline double val(double a) { return a; }
 using std::sqrt; using std::fabs; using std::exp; using std::log; using std::tanh; using std::sinh;
 using std::sin; using std::cos; using std::asin; using std::pow; using std::fmin; using std::fmax; using std::isfinite;
 
+// First-order dual number over S: value + derivative along one direction. The custom-joint kinematics run once with
+// Dual<S> (direction = the joint's speeds) so that the time derivatives of the joint's motion axes - the velocity-product
+// ("H-dot u") terms of a function-based mobilizer - come from the same few lines that define its transform.
+template <class S>
+struct Dual {
+    S v, d;
+    Dual() : v(0.0), d(0.0) {}
+    Dual(double x) : v(x), d(0.0) {}
+    Dual(S value, S deriv) : v(value), d(deriv) {}
+};
+template <class S> inline Dual<S> operator+(const Dual<S>& a, const Dual<S>& b) { return {a.v + b.v, a.d + b.d}; }
+template <class S> inline Dual<S> operator-(const Dual<S>& a, const Dual<S>& b) { return {a.v - b.v, a.d - b.d}; }
+template <class S> inline Dual<S> operator-(const Dual<S>& a) { return {-a.v, -a.d}; }
+template <class S> inline Dual<S> operator*(const Dual<S>& a, const Dual<S>& b) { return {a.v * b.v, a.v * b.d + a.d * b.v}; }
+template <class S> inline Dual<S> sin(const Dual<S>& a) { return {sin(a.v), cos(a.v) * a.d}; }
+template <class S> inline Dual<S> cos(const Dual<S>& a) { return {cos(a.v), -(sin(a.v) * a.d)}; }
+template <class S> inline double val(const Dual<S>& a) { return val(a.v); }
+
 template <class S>
 struct Vec3 {
     S x, y, z;
@@ -94,6 +112,18 @@ template <class S> inline Mat3<S> operator+(const Mat3<S>& A, const Mat3<S>& B) 
     Mat3<S> C;
     for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) C.m[r][c] = A.m[r][c] + B.m[r][c];
     return C;
+}
+// rotation by `angle` about the unit vector (ax, ay, az): cos 1 + (1 - cos) a a^T + sin [a]x
+template <class S> inline Mat3<S> rotAxis(S angle, double ax, double ay, double az) {
+    const S c = cos(angle), s = sin(angle), t = S(1.0) - c;
+    const double a[3] = {ax, ay, az};
+    Mat3<S> R;
+    for (int r = 0; r < 3; ++r)
+        for (int k = 0; k < 3; ++k) R.m[r][k] = t * S(a[r] * a[k]) + (r == k ? c : S(0.0));
+    R.m[0][1] = R.m[0][1] - s * S(az); R.m[0][2] = R.m[0][2] + s * S(ay);
+    R.m[1][0] = R.m[1][0] + s * S(az); R.m[1][2] = R.m[1][2] - s * S(ax);
+    R.m[2][0] = R.m[2][0] - s * S(ay); R.m[2][1] = R.m[2][1] + s * S(ax);
+    return R;
 }
 template <class S> inline Mat3<S> rotZ(S angle) {
     Mat3<S> R;

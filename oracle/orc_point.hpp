@@ -42,6 +42,11 @@ struct Model {
     const double* contactD(int c) const { return T->dbl + T->o_contact_d + c * MOCOB200_CONTACT_DSTRIDE; }
     const int* contactI(int c) const { return T->idx + T->o_contact_i + c * MOCOB200_CONTACT_ISTRIDE; }
     const int* goalRec(int g) const { return T->idx + T->o_goal_i + g * MOCOB200_GOAL_ISTRIDE; }
+    // custom-joint record of body b (null for the built-in joint kinds)
+    int customOf(int b) const { return T->ncustom > 0 ? T->idx[T->o_body_cj + b] : -1; }
+    const double* cjD(int cj) const { return T->dbl + T->o_cj_d + cj * MOCOB200_CJ_DSTRIDE; }
+    const int* cjI(int cj) const { return T->idx + T->o_cj_i + cj * MOCOB200_CJ_ISTRIDE; }
+    const int* xforceI(int f) const { return T->idx + T->o_xforce_i + f * MOCOB200_XFORCE_ISTRIDE; }
 };
 
 // ---- scalar functions of the path ------------------------------------------------------------
