@@ -201,10 +201,13 @@ int mocob200_make_iterate(const mocob200_tables*, const mocob200_transcription*,
 int mocob200_iterate_write_sto(const mocob200_problem*, const double* x, const char* path);
 int mocob200_iterate_read_sto(const mocob200_problem*, const char* path, double* x, char* err, int errlen);
 
-/* Number of ranks that actually get grid points: min(world, n_grid / 384) but at least 1 (MOCOB200_MIN_POINTS_PER_RANK
- * overrides the 384) — a rank is only worth its launch + gather latency with about one wave of work; the remaining
- * ranks idle (the reference caps its worker threads the same way, MocoCasADiSolver.cpp:127-143). */
+/* Number of ranks that actually get grid points: min(world, n_grid / 96) but at least 1 — a rank is only worth its launch +
+ * exchange latency with a hundred or so grid points; the remaining ranks idle (the reference caps its worker threads the same
+ * way, MocoCasADiSolver.cpp:127-143). A fixed rule evaluated identically on every rank. */
 int mocob200_effective_world(int n_grid, int world);
+/* Process-wide override of the 96 (<= 0 restores it); every rank of a job must make the same call before mocob200_create.
+ * For tests and for measuring the sharded path on small grids. */
+void mocob200_set_min_points_per_rank(int n);
 /* Grid points [*p0, *p1) evaluated by `rank` of `world` (contiguous, every point owned by exactly one rank, ranks >=
  * mocob200_effective_world get the empty range; the reference's analogue is the split of the time indices over CasADi
  * Map threads, CasOCTranscription.cpp:1179-1212).
@@ -235,8 +238,11 @@ int mocob200_eval_f(mocob200_handle*, const double* x, double* f, double* f_term
 int mocob200_eval_g(mocob200_handle*, const double* x, double* g);
 int mocob200_eval_grad_f(mocob200_handle*, const double* x, double* grad);
 int mocob200_eval_jac_g(mocob200_handle*, const double* x, double* values);
-/* Same evaluations with x already resident on the device and results left there
- * (device pointers; used by bench.py's device-resident timing and by callers that chain kernels). */
+/* Same evaluations with x already resident on the device and results left there (device pointers; used by bench.py's
+ * device-resident timing and by callers that chain kernels). The work runs on the handle's own stream. cuda_stream != NULL: that
+ * stream is ordered around the call - the handle's stream first waits for everything already queued on cuda_stream (the
+ * producer of d_x) and cuda_stream then waits for the pipeline, so consumers of the outputs can be queued on it directly.
+ * cuda_stream == NULL: no ordering is added (NULL cannot be told from the legacy default stream); call mocob200_sync. */
 int mocob200_eval_jac_g_device(mocob200_handle*, const double* d_x, double* d_values, void* cuda_stream);
 int mocob200_eval_g_device(mocob200_handle*, const double* d_x, double* d_g, void* cuda_stream);
 /* n independent single-rank problems on one device evaluated side by side (one handle each; each on its own stream,
@@ -251,7 +257,11 @@ int mocob200_elapsed_ms(mocob200_handle*, float* ms);
 /* bookkeeping for bench.py */
 long mocob200_launch_count(const mocob200_handle*);           /* kernels launched so far */
 int mocob200_last_kernel_ms(const mocob200_handle*, float* point_kernel_ms, float* assemble_kernel_ms);
-long mocob200_point_evals_per_jacobian(const mocob200_handle*);
+long mocob200_point_evals_per_jacobian(const mocob200_handle*); /* credited: what differencing the whole function costs */
+/* executed: evaluations one eval_jac_g launches over all ranks: whole | pose-reusing | pose+velocity-reusing | local-column warps */
+int mocob200_executed_evals(const mocob200_handle*, long out[4]);
+int mocob200_working_ranks(const mocob200_handle*);      /* ranks that own grid points */
+int mocob200_uses_warp_kernels(const mocob200_handle*);  /* 1: warp-per-evaluation FD kernels, 0: thread-per-evaluation */
 /* FP64 FMA saturation microbenchmark: returns measured TFLOP/s (the FP64 roofline peak). */
 int mocob200_measure_fp64_peak(int device, double* tflops);
 

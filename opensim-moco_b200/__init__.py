@@ -26,7 +26,8 @@ ABI_SYMBOLS = [
     "mocob200_eval_grad_f", "mocob200_eval_jac_g", "mocob200_eval_jac_g_device", "mocob200_eval_g_device",
     "mocob200_eval_jac_g_batch",
     "mocob200_sync", "mocob200_mark", "mocob200_elapsed_ms", "mocob200_launch_count", "mocob200_last_kernel_ms",
-    "mocob200_point_evals_per_jacobian", "mocob200_measure_fp64_peak", "mocob200_shard_range", "mocob200_effective_world", "mocob200_set_sparsity_detection",
+    "mocob200_point_evals_per_jacobian", "mocob200_executed_evals", "mocob200_working_ranks", "mocob200_uses_warp_kernels",
+    "mocob200_measure_fp64_peak", "mocob200_shard_range", "mocob200_effective_world", "mocob200_set_min_points_per_rank", "mocob200_set_sparsity_detection",
     "mocob200_iterate_write_sto", "mocob200_iterate_read_sto",
 ]
 
@@ -67,6 +68,8 @@ def lib():
         L.mocob200_layout_structure.argtypes = [vp, vp, ip, ip]
         L.mocob200_make_iterate.argtypes = [vp, vp, C.c_long, C.c_double, dp]
         L.mocob200_effective_world.argtypes = [C.c_int, C.c_int]
+        L.mocob200_set_min_points_per_rank.argtypes = [C.c_int]
+        L.mocob200_set_min_points_per_rank.restype = None
         L.mocob200_set_sparsity_detection.argtypes = [vp, C.c_int, C.c_int]
         L.mocob200_shard_range.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.mocob200_create.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, C.POINTER(vp)]
@@ -95,6 +98,9 @@ def lib():
         L.mocob200_point_evals_per_jacobian.argtypes = [vp]
         L.mocob200_point_evals_per_jacobian.restype = C.c_long
         L.mocob200_measure_fp64_peak.argtypes = [C.c_int, dp]
+        L.mocob200_executed_evals.argtypes = [vp, C.POINTER(C.c_long)]
+        L.mocob200_working_ranks.argtypes = [vp]
+        L.mocob200_uses_warp_kernels.argtypes = [vp]
         L.mocob200_iterate_write_sto.argtypes = [vp, dp, C.c_char_p]
         L.mocob200_iterate_read_sto.argtypes = [vp, C.c_char_p, dp, C.c_char_p, C.c_int]
         _lib = L
@@ -329,6 +335,17 @@ class Evaluator:
 
     def point_evals_per_jacobian(self):
         return lib().mocob200_point_evals_per_jacobian(self._h)
+
+    def executed_evals(self):
+        out = (C.c_long * 4)()
+        self._ck(lib().mocob200_executed_evals(self._h, out), "executed_evals")
+        return list(out)
+
+    def working_ranks(self):
+        return lib().mocob200_working_ranks(self._h)
+
+    def uses_warp_kernels(self):
+        return bool(lib().mocob200_uses_warp_kernels(self._h))
 
     def close(self):
         if self._h:

@@ -3,6 +3,7 @@
 #include <dlfcn.h>
 
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -72,6 +73,11 @@ struct mocob200_handle {
     std::string err;
     int device = 0, rank = 0, world = 1;
     int eff = 1; // ranks that own grid points (mocob200_effective_world)
+    int mergedBodies = 0; // welded bodies folded into their parents in the device tables
+    double* d_Jt = nullptr; // sharded evaluation: time column of every grid point's FD block, gathered to rank 0
+    DevLayout DLt{};        // DL with Jt set (rank 0's assembly of the t0 / tf columns)
+    // CSC value runs of the columns each rank assembles itself: [rank][block: states, controls, derivatives] = [k0, k1)
+    std::vector<int> runs;
     Layout L;
     DevTables DT{};
     DevLayout DL{};
@@ -103,6 +109,7 @@ struct mocob200_handle {
     bool allowGraph = true; // read at create: MOCOB200_GRAPH=0 or MOCOB200_TIMING=1 turn the graph off
     cudaEvent_t evY = nullptr, evE = nullptr, evJ = nullptr, evI = nullptr, evX = nullptr;
     cudaEvent_t evBatch = nullptr; // fork / join event of mocob200_eval_jac_g_batch
+    cudaEvent_t evCaller = nullptr; // ordering against a caller-supplied stream (*_device entry points)
     cudaEvent_t marks[2] = {nullptr, nullptr}; // mocob200_mark stopwatch (per handle: handles may sit on different devices)
     bool ecHasIntegrand = false; // some endpoint-constraint goal has an integrand: jac_g needs dI/dt0, dI/dtf
     double* d_I2 = nullptr;
@@ -323,9 +330,11 @@ bool bcastX(mocob200_handle* h, const double* d_src) {
     }
     if (h->eff > 1 && h->rank < h->eff) { // only the ranks that own grid points need x
         if (!ncclOk(h, g_nccl.GroupStart(), "ncclGroupStart")) return false;
-        if (h->rank == 0) for (int r = 1; r < h->eff; ++r) g_nccl.Send(h->d_x, (size_t)h->L.n_var, kNcclDouble, r, h->comm, h->stream);
-        else g_nccl.Recv(h->d_x, (size_t)h->L.n_var, kNcclDouble, 0, h->comm, h->stream);
-        if (!ncclOk(h, g_nccl.GroupEnd(), "ncclGroupEnd")) return false;
+        int rc = 0;
+        if (h->rank == 0) { for (int r = 1; r < h->eff && rc == 0; ++r) rc = g_nccl.Send(h->d_x, (size_t)h->L.n_var, kNcclDouble, r, h->comm, h->stream); }
+        else rc = g_nccl.Recv(h->d_x, (size_t)h->L.n_var, kNcclDouble, 0, h->comm, h->stream);
+        const int rcEnd = g_nccl.GroupEnd(); // always close the group, then report the first failure
+        if (!ncclOk(h, rc, "ncclSend/ncclRecv(x)") || !ncclOk(h, rcEnd, "ncclGroupEnd")) return false;
     }
     return true;
 }
@@ -333,16 +342,18 @@ bool bcastX(mocob200_handle* h, const double* d_src) {
 bool gatherBlocks(mocob200_handle* h, double* d_buf, size_t stride) {
     if (h->eff == 1 || h->rank >= h->eff) return true;
     if (!ncclOk(h, g_nccl.GroupStart(), "ncclGroupStart")) return false;
+    int rc = 0;
     if (h->rank == 0) {
-        for (int r = 1; r < h->eff; ++r) {
+        for (int r = 1; r < h->eff && rc == 0; ++r) {
             const size_t n = (size_t)(h->shard[r + 1] - h->shard[r]) * stride;
-            if (n) g_nccl.Recv(d_buf + (size_t)h->shard[r] * stride, n, kNcclDouble, r, h->comm, h->stream);
+            if (n) rc = g_nccl.Recv(d_buf + (size_t)h->shard[r] * stride, n, kNcclDouble, r, h->comm, h->stream);
         }
     } else {
         const size_t n = (size_t)(h->p1 - h->p0) * stride;
-        if (n) g_nccl.Send(d_buf + (size_t)h->p0 * stride, n, kNcclDouble, 0, h->comm, h->stream);
+        if (n) rc = g_nccl.Send(d_buf + (size_t)h->p0 * stride, n, kNcclDouble, 0, h->comm, h->stream);
     }
-    return ncclOk(h, g_nccl.GroupEnd(), "ncclGroupEnd");
+    const int rcEnd = g_nccl.GroupEnd();
+    return ncclOk(h, rc, "ncclSend/ncclRecv(blocks)") && ncclOk(h, rcEnd, "ncclGroupEnd");
 }
 
 // stopwatch events also work inside a captured graph (as external event-record nodes)
@@ -367,6 +378,33 @@ bool runNominal(mocob200_handle* h) {
     }
     return true;
 }
+// point-function FD kernels of this rank's grid points (Y and J rows [p0, p1)); after_nominal as in launch_wpoints_fd
+void launchFdKernels(mocob200_handle* h, cudaEvent_t after_nominal) {
+    if (h->warpFor(mocob200_point_evals_per_jacobian(h) / h->eff)) {
+        h->launches += launch_wpoints_fd(h->DT, h->WA, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_cfg, h->p0, h->p1 - h->p0, h->stream,
+                                         after_nominal, &h->side);
+        return;
+    }
+    // thread-per-evaluation kernel for the inputs that need whole evaluations; the local columns beside it
+    const bool local = h->WA.n_local > 0 && h->side.s[0];
+    if (local) {
+        // warp nominal evaluation first (Y and the blobs), then the local-column kernel next to the flat FD kernel
+        launch_wpoints_nominal(h->DT, h->WA, h->DL, h->d_x, h->d_Y, h->d_cfg, h->p0, h->p1 - h->p0, h->stream);
+        if (after_nominal) cudaEventRecord(after_nominal, h->stream);
+        cudaEventRecord(h->side.fork, h->stream);
+        cudaStreamWaitEvent(h->side.s[0], h->side.fork, 0);
+        h->launches += 1 + launch_wlocal(h->DT, h->WA, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_cfg, h->p0, h->p1 - h->p0, h->side.s[0]);
+        cudaEventRecord(h->side.join[0], h->side.s[0]);
+        launch_points_fd_flat(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream, h->WA.cd_dirs, h->WA.n_cd);
+        h->launches++;
+        cudaStreamWaitEvent(h->stream, h->side.join[0], 0);
+    } else {
+        launch_points_fd(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream);
+        h->launches++;
+        if (after_nominal) cudaEventRecord(after_nominal, h->stream);
+    }
+}
+
 // deferIntegralDerivs: the caller (the jac_g pipeline) does not read dI/dt0, dI/dtf — they are computed on the side stream
 // beside its assembly kernel and the caller joins on h->evI afterwards. Returns through *deferred whether that happened.
 bool runFd(mocob200_handle* h, bool deferIntegralDerivs = false, bool* deferred = nullptr) {
@@ -385,29 +423,7 @@ bool runFd(mocob200_handle* h, bool deferIntegralDerivs = false, bool* deferred 
         cudaEventRecord(h->evE, h->stream2);
         h->launches++;
     }
-    if (h->warpFor(mocob200_point_evals_per_jacobian(h) / h->eff))
-        h->launches += launch_wpoints_fd(h->DT, h->WA, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_cfg, h->p0, h->p1 - h->p0, h->stream,
-                                         overlap ? h->evY : nullptr, &h->side);
-    else {
-        // thread-per-evaluation kernel for the inputs that need whole evaluations; the local columns beside it
-        const bool local = h->WA.n_local > 0 && h->side.s[0];
-        if (local) {
-            // warp nominal evaluation first (Y and the blobs), then the local-column kernel next to the flat FD kernel
-            launch_wpoints_nominal(h->DT, h->WA, h->DL, h->d_x, h->d_Y, h->d_cfg, h->p0, h->p1 - h->p0, h->stream);
-            if (overlap) cudaEventRecord(h->evY, h->stream);
-            cudaEventRecord(h->side.fork, h->stream);
-            cudaStreamWaitEvent(h->side.s[0], h->side.fork, 0);
-            h->launches += 1 + launch_wlocal(h->DT, h->WA, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_cfg, h->p0, h->p1 - h->p0, h->side.s[0]);
-            cudaEventRecord(h->side.join[0], h->side.s[0]);
-            launch_points_fd_flat(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream, h->WA.cd_dirs, h->WA.n_cd);
-            h->launches++;
-            cudaStreamWaitEvent(h->stream, h->side.join[0], 0);
-        } else {
-            launch_points_fd(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream);
-            h->launches++;
-            if (overlap) cudaEventRecord(h->evY, h->stream);
-        }
-    }
+    launchFdKernels(h, overlap ? h->evY : nullptr);
     recTiming(h->ev[1], h->stream);
     if (overlap) {
         cudaStreamWaitEvent(h->stream2, h->evY, 0);
@@ -476,6 +492,7 @@ void mocob200_destroy(mocob200_handle* h) {
     if (h->evJ) cudaEventDestroy(h->evJ);
     if (h->evX) cudaEventDestroy(h->evX);
     if (h->evBatch) cudaEventDestroy(h->evBatch);
+    if (h->evCaller) cudaEventDestroy(h->evCaller);
     for (auto& e : h->marks) if (e) cudaEventDestroy(e);
     if (h->evI) cudaEventDestroy(h->evI);
     if (h->stream2) cudaStreamDestroy(h->stream2);
@@ -500,8 +517,6 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
         h->L = buildLayout(*T, *R, true);
     } catch (const std::exception& e) { return fail(MOCOB200_ERR_UNSUPPORTED, e.what()); }
     Layout& L = h->L;
-    if (T->nb > MOCOB200_MAXB || T->nq > MOCOB200_MAXQ || T->ncontact > MOCOB200_MAXCONTACT)
-        return fail(MOCOB200_ERR_UNSUPPORTED, "model exceeds the compiled limits (bodies/coordinates/contacts)");
     if (L.n_in > MOCOB200_MAX_IN || L.n_out > MOCOB200_MAX_OUT || L.n_in + 1 > 256 || L.n_ein + 1 > 1024)
         return fail(MOCOB200_ERR_UNSUPPORTED, "point function exceeds the compiled input/output limits");
     for (int m = 0; m < T->nmus; ++m)
@@ -518,10 +533,35 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     h->hostT = *T; h->hostT.dbl = h->hostDbl.data(); h->hostT.idx = h->hostIdx.data();
     h->hostR = *R;
     if (R->mesh) { h->hostMesh.assign(R->mesh, R->mesh + R->n_mesh); h->hostR.mesh = h->hostMesh.data(); }
-    // tables
+    // tables: the device works on the model with welded bodies merged into their parents (table_opt.cpp); the NLP layout,
+    // the host copies and the ABI keep the caller's tables
+    const mocob200_tables* const callerT = T;
+    std::vector<double> dbl;
+    std::vector<int> idx;
+    mocob200_tables reduced;
+    {
+        const char* e = getenv("MOCOB200_MERGE_WELDS"); // development A-B switch, read once at create
+        if (e && e[0] == '0') { dbl.assign(callerT->dbl, callerT->dbl + callerT->n_dbl); idx.assign(callerT->idx, callerT->idx + callerT->n_int); reduced = *callerT; reduced.dbl = dbl.data(); reduced.idx = idx.data(); }
+        else h->mergedBodies = mergeWeldedBodies(*callerT, dbl, idx, reduced);
+    }
+    T = &reduced;
+    // constants of the muscle and contact models that depend on the parameters only, into the device copy (point_eval.cuh DEV_* slots)
+    for (int m = 0; m < T->nmus; ++m) {
+        double* md = dbl.data() + T->o_mus_d + m * MOCOB200_MUS_DSTRIDE;
+        const double kPE = 4.0, offset = std::exp(kPE * (0.2 - 1.0) / md[9]);
+        const double fiberWidth = md[1] * std::sin(md[3]);
+        md[DEV_MUS_PE_DENOM] = std::exp(kPE) - offset;
+        md[DEV_MUS_FIBER_WIDTH] = fiberWidth;
+        md[DEV_MUS_PE_OFFSET] = offset;
+    }
+    for (int c = 0; c < T->ncontact; ++c) {
+        double* cd = dbl.data() + T->o_contact_d + c * MOCOB200_CONTACT_DSTRIDE;
+        const double k = 0.5 * std::pow(cd[16], 2.0 / 3.0);
+        cd[DEV_CONTACT_HERTZ] = (4.0 / 3.0) * k * std::sqrt(cd[3] * k);
+    }
+    if (T->nb > MOCOB200_MAXB || T->nq > MOCOB200_MAXQ || T->ncontact > MOCOB200_MAXCONTACT)
+        return fail(MOCOB200_ERR_UNSUPPORTED, "model exceeds the compiled limits (bodies/coordinates/contacts)");
     DevTables& D = h->DT;
-    std::vector<double> dbl(T->dbl, T->dbl + T->n_dbl);
-    std::vector<int> idx(T->idx, T->idx + T->n_int);
     D.dbl = (const double*)own(devUpload(dbl));
     D.idx = (const int*)own(devUpload(idx));
     D.dblP = D.dbl;
@@ -549,6 +589,12 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     for (int g = 0; g < T->ngoal; ++g) eoff[g + 1] = eoff[g] + T->idx[T->o_goal_i + g * MOCOB200_GOAL_ISTRIDE + 2];
     G.n_eout_total = eoff[T->ngoal];
     G.n_path_rows = L.n_path_rows;
+    {
+        int maxPpm = 0;
+        for (int m = 0; m < T->nmus; ++m) maxPpm = std::max(maxPpm, T->idx[T->o_mus_i + m * MOCOB200_MUS_ISTRIDE + 1]);
+        G.small_size = (T->nb <= SizeSmall::NB && T->nq <= SizeSmall::NQ && maxPpm <= SizeSmall::NPPM && L.n_in <= SizeSmall::NIN &&
+                        L.n_out <= SizeSmall::NOUT) ? 1 : 0;
+    }
     G.mesh = (const double*)own(devUpload(L.mesh));
     G.grid = (const double*)own(devUpload(L.grid));
     G.quad = (const double*)own(devUpload(L.quad));
@@ -621,6 +667,19 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     h->p0 = h->shard[rank];
     h->p1 = h->shard[rank + 1];
     h->eff = mocob200_effective_world(L.n_grid, world);
+    if (h->eff > 1) {
+        h->d_Jt = (double*)own(devAlloc<double>((size_t)L.n_grid * L.n_out));
+        if (!h->d_Jt) return fail(MOCOB200_ERR_CUDA, "device allocation failed");
+        h->DLt = h->DL;
+        h->DLt.Jt = h->d_Jt;
+        h->runs.assign((size_t)world * 6, 0);
+        for (int r = 0; r < h->eff; ++r) {
+            const int a = h->shard[r], b = h->shard[r + 1];
+            const int c0[3] = {L.off_states + a * L.ns, L.off_controls + a * L.nc, L.off_derivs + a * L.nd};
+            const int c1[3] = {L.off_states + b * L.ns, L.off_controls + b * L.nc, L.off_derivs + b * L.nd};
+            for (int k = 0; k < 3; ++k) { h->runs[6 * r + 2 * k] = L.colptr[c0[k]]; h->runs[6 * r + 2 * k + 1] = L.colptr[c1[k]]; }
+        }
+    }
     h->allowGraph = !(getenv("MOCOB200_GRAPH") && getenv("MOCOB200_GRAPH")[0] == '0') && !getenv("MOCOB200_TIMING");
     if (h->eff > 1) { // a communicator only when more than one rank owns grid points
         if (!nccl_unique_id) return fail(MOCOB200_ERR_ARG, "world > 1 needs a NCCL unique id");
@@ -830,7 +889,75 @@ int mocob200_eval_grad_f(mocob200_handle* h, const double* x, double* grad) {
     return MOCOB200_OK;
 }
 
+// Sharded Jacobian (eff > 1). Every working rank differences its own grid points and assembles the CSC entries of
+// the columns that belong to them — a column's entries need the FD block of the column's own grid point only, and CasADi's
+// column order (CasOCTranscription.h:192-199: states of all points, controls, derivatives) makes them three contiguous runs of
+// the value array per rank. Rank 0 receives the runs straight into the destination buffer, plus the point outputs and the time
+// column of every block, from which it finishes the two columns every grid point contributes to (t0, tf). Endpoint-constraint
+// goals here read x alone, so every rank evaluates them itself (the caller routes problems whose endpoint constraints carry an
+// integral through the gather-everything pipeline instead).
+static bool jacPipelineSharded(mocob200_handle* h, double* d_vals) {
+    recTiming(h->ev[0], h->stream);
+    if (h->rank >= h->eff) { recTiming(h->ev[1], h->stream); return true; } // idle rank
+    const Layout& L = h->L;
+    if (h->DL.n_eout_total > 0) {
+        cudaEventRecord(h->evX, h->stream);
+        cudaStreamWaitEvent(h->stream2, h->evX, 0);
+        launch_endpoint(h->DT, h->DL, h->fd, h->d_x, h->d_I2, h->d_G, h->d_E, true, h->stream2, 1);
+        cudaEventRecord(h->evE, h->stream2);
+        h->launches++;
+    }
+    launchFdKernels(h, nullptr);
+    recTiming(h->ev[1], h->stream);
+    const int np = h->p1 - h->p0;
+    launch_pack_time_column(h->DL, h->d_J, h->d_Jt, h->p0, np, h->stream);
+    h->launches++;
+    if (h->DL.n_eout_total > 0) cudaStreamWaitEvent(h->stream, h->evE, 0);
+    recTiming(h->ev[2], h->stream);
+    double* mine = h->rank == 0 ? d_vals : h->d_vals;
+    for (int k = 0; k < 3; ++k) {
+        const int k0 = h->runs[6 * h->rank + 2 * k], k1 = h->runs[6 * h->rank + 2 * k + 1];
+        if (k1 > k0) { launch_assemble_jac(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_I, h->d_E, mine, h->stream, k0, k1); h->launches += 1 + (h->DL.n_path_rows > 0); }
+    }
+    // one NCCL group: point outputs + time columns + value runs to rank 0
+    if (!ncclOk(h, g_nccl.GroupStart(), "ncclGroupStart")) return false;
+    int rc = 0;
+    const size_t no = (size_t)L.n_out;
+    if (h->rank == 0) {
+        for (int r = 1; r < h->eff && rc == 0; ++r) {
+            const size_t a = h->shard[r], n = (size_t)(h->shard[r + 1] - h->shard[r]) * no;
+            if (n) {
+                rc = g_nccl.Recv(h->d_Y + a * no, n, kNcclDouble, r, h->comm, h->stream);
+                if (rc == 0) rc = g_nccl.Recv(h->d_Jt + a * no, n, kNcclDouble, r, h->comm, h->stream);
+            }
+            for (int k = 0; k < 3 && rc == 0; ++k) {
+                const int k0 = h->runs[6 * r + 2 * k], k1 = h->runs[6 * r + 2 * k + 1];
+                if (k1 > k0) rc = g_nccl.Recv(d_vals + k0, (size_t)(k1 - k0), kNcclDouble, r, h->comm, h->stream);
+            }
+        }
+    } else {
+        const size_t a = h->p0, n = (size_t)np * no;
+        if (n) {
+            rc = g_nccl.Send(h->d_Y + a * no, n, kNcclDouble, 0, h->comm, h->stream);
+            if (rc == 0) rc = g_nccl.Send(h->d_Jt + a * no, n, kNcclDouble, 0, h->comm, h->stream);
+        }
+        for (int k = 0; k < 3 && rc == 0; ++k) {
+            const int k0 = h->runs[6 * h->rank + 2 * k], k1 = h->runs[6 * h->rank + 2 * k + 1];
+            if (k1 > k0) rc = g_nccl.Send(h->d_vals + k0, (size_t)(k1 - k0), kNcclDouble, 0, h->comm, h->stream);
+        }
+    }
+    const int rcEnd = g_nccl.GroupEnd();
+    if (!ncclOk(h, rc, "ncclSend/ncclRecv(values)") || !ncclOk(h, rcEnd, "ncclGroupEnd")) return false;
+    if (h->rank == 0) { // the t0 and tf columns: the first two columns of the value array
+        launch_assemble_jac(h->DT, h->DLt, h->fd, h->d_x, h->d_Y, h->d_J, h->d_I, h->d_E, d_vals, h->stream, 0, L.colptr[2]);
+        h->launches += 1 + (h->DL.n_path_rows > 0);
+    }
+    recTiming(h->ev[3], h->stream);
+    return true;
+}
+
 static bool jacPipelineLaunches(mocob200_handle* h, double* d_vals) {
+    if (h->eff > 1 && !h->ecHasIntegrand) return jacPipelineSharded(h, d_vals);
     bool deferred = false;
     if (!runFd(h, !h->ecHasIntegrand, &deferred)) return false;
     if (h->rank == 0) {
@@ -890,13 +1017,29 @@ int mocob200_eval_jac_g(mocob200_handle* h, const double* x, double* values) {
     return MOCOB200_OK;
 }
 
+// Ordering against the caller's stream (non-NULL cuda_stream): the handle's stream first waits for everything queued on the
+// caller's stream so far (the producer of d_x), and the caller's stream afterwards waits for the pipeline (so a consumer of
+// d_values may simply be queued on it). NULL: no ordering is added; the caller synchronises through mocob200_sync.
+static bool orderAfterCaller(mocob200_handle* h, void* cuda_stream) {
+    if (!cuda_stream) return true;
+    if (!h->evCaller && !h->ck(cudaEventCreateWithFlags(&h->evCaller, cudaEventDisableTiming), "event")) return false;
+    return h->ck(cudaEventRecord(h->evCaller, (cudaStream_t)cuda_stream), "record on the caller's stream") &&
+           h->ck(cudaStreamWaitEvent(h->stream, h->evCaller, 0), "wait for the caller's stream");
+}
+static bool orderCallerAfter(mocob200_handle* h, void* cuda_stream) {
+    if (!cuda_stream) return true;
+    return h->ck(cudaEventRecord(h->evCaller, h->stream), "record on the handle's stream") &&
+           h->ck(cudaStreamWaitEvent((cudaStream_t)cuda_stream, h->evCaller, 0), "caller's stream waits for the pipeline");
+}
+
 int mocob200_eval_jac_g_device(mocob200_handle* h, const double* d_x, double* d_values, void* cuda_stream) {
     if (!h || !d_x) return MOCOB200_ERR_ARG;
     cudaSetDevice(h->device);
-    (void)cuda_stream; // the handle's own stream orders the work; the caller synchronises through mocob200_sync
     h->x_cached.clear();
+    if (!orderAfterCaller(h, cuda_stream)) return MOCOB200_ERR_CUDA;
     if (!bcastX(h, d_x)) return MOCOB200_ERR_CUDA;
     if (!jacPipeline(h, d_values ? d_values : h->d_vals)) return MOCOB200_ERR_CUDA;
+    if (!orderCallerAfter(h, cuda_stream)) return MOCOB200_ERR_CUDA;
     return h->ck(cudaGetLastError(), "eval_jac_g_device") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
 }
 
@@ -936,10 +1079,11 @@ int mocob200_eval_jac_g_batch(mocob200_handle* const* hs, int n, const double* c
 int mocob200_eval_g_device(mocob200_handle* h, const double* d_x, double* d_g, void* cuda_stream) {
     if (!h || !d_x) return MOCOB200_ERR_ARG;
     cudaSetDevice(h->device);
-    (void)cuda_stream;
     h->x_cached.clear();
+    if (!orderAfterCaller(h, cuda_stream)) return MOCOB200_ERR_CUDA;
     if (!bcastX(h, d_x) || !runNominal(h)) return MOCOB200_ERR_CUDA;
     if (h->rank == 0) { launch_assemble_g(h->DT, h->DL, h->d_x, h->d_Y, h->d_G, d_g ? d_g : h->d_g, h->stream); h->launches += 1 + (h->DL.n_path_rows > 0); }
+    if (!orderCallerAfter(h, cuda_stream)) return MOCOB200_ERR_CUDA;
     return h->ck(cudaGetLastError(), "eval_g_device") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
 }
 
@@ -979,6 +1123,36 @@ long mocob200_point_evals_per_jacobian(const mocob200_handle* h) {
     long per_dir = 1;
     if (h->fd.scheme == MOCOB200_FD_CENTRAL) per_dir = 2L * (1 + h->fd.h_iter);
     return (long)L.n_grid * (1 + per_dir * L.n_in);
+}
+
+// Evaluations of the point function that one eval_jac_g launches on all ranks together, by kind:
+// out[0] whole evaluations, out[1] evaluations that reload the nominal poses (speeds, implicit-mode accelerations),
+// out[2] evaluations that reload poses and velocities (time, unclassified inputs), out[3] local-column warps (one per grid point).
+int mocob200_executed_evals(const mocob200_handle* h, long out[4]) {
+    if (!h || !out) return MOCOB200_ERR_ARG;
+    const Layout& L = h->L;
+    const WarpAux& A = h->WA;
+    const long N = L.n_grid;
+    const bool central = h->fd.scheme == MOCOB200_FD_CENTRAL;
+    const long per = central ? 2L * (1 + h->fd.h_iter) : 1;
+    const bool warp = h->warpFor(mocob200_point_evals_per_jacobian(h) / h->eff);
+    out[0] = out[1] = out[2] = out[3] = 0;
+    if (warp) {
+        out[0] = N * (1 + per * A.n_p0);
+        out[1] = N * per * A.n_p1;
+        out[2] = N * per * A.n_p2;
+        out[3] = A.n_local > 0 ? N : 0;
+    } else if (A.n_local > 0 && h->side.s[0]) {
+        out[0] = N * (1 + per * A.n_cd); // the thread kernels evaluate every non-local direction whole
+        out[3] = N;
+    } else {
+        out[0] = N * (1 + per * L.n_in);
+    }
+    return MOCOB200_OK;
+}
+int mocob200_working_ranks(const mocob200_handle* h) { return h ? h->eff : 0; }
+int mocob200_uses_warp_kernels(const mocob200_handle* h) {
+    return h && h->warpFor(mocob200_point_evals_per_jacobian(h) / h->eff) ? 1 : 0;
 }
 
 int mocob200_measure_fp64_peak(int device, double* tflops) {

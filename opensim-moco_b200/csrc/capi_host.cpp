@@ -303,10 +303,13 @@ int mocob200_make_iterate(const mocob200_tables* T, const mocob200_transcription
     } catch (const std::exception&) { return MOCOB200_ERR_UNSUPPORTED; }
 }
 
+static int g_min_points_per_rank = 96;
+void mocob200_set_min_points_per_rank(int n) { g_min_points_per_rank = n > 0 ? n : 96; }
+
 int mocob200_effective_world(int n_grid, int world) {
-    // a rank is only worth its launch + gather latency when it gets a few hundred grid points (one wave of work)
-    int min_points = 384;
-    if (const char* e = getenv("MOCOB200_MIN_POINTS_PER_RANK")) { const int v = atoi(e); if (v > 0) min_points = v; }
+    // a rank is only worth its launch + exchange latency when it gets a hundred or so grid points: BASELINE config 5 (1601 points)
+    // spreads over 8 GPUs, config 3 (101 points, a 0.1 ms latency-bound step) stays on one. A fixed rule, the same on every rank.
+    const int min_points = g_min_points_per_rank;
     int eff = n_grid / min_points;
     if (eff < 1) eff = 1;
     return eff < world ? eff : world;

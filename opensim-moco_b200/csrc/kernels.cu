@@ -21,13 +21,14 @@ __device__ __forceinline__ void gather_inputs(const DevLayout& L, const double* 
     for (int k = 0; k < L.nd; ++k) in[1 + L.ns + L.nc + k] = xd[k];
 }
 
+template <class SZ>
 __global__ void k_points_nominal(DevTables T, DevLayout L, const double* __restrict__ x, double* __restrict__ Y, int p0, int np) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= np) return;
     const int j = p0 + t;
-    double in[MOCOB200_MAX_IN], out[MOCOB200_MAX_OUT];
+    double in[SZ::NIN], out[SZ::NOUT];
     gather_inputs(L, x, j, in);
-    eval_point(T, in, out, 0xffffffffu);
+    eval_point<SZ>(T, in, out, 0xffffffffu);
     for (int o = 0; o < L.n_out; ++o) Y[(size_t)j * L.n_out + o] = out[o];
 }
 
@@ -147,6 +148,11 @@ k_points_fd(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ 
 }
 
 // ---------------------------------------------------------------------------------------------
+// d(point output row)/d(time) at grid point j: column 0 of the point's FD block, or — when the blocks of other ranks' grid points
+// are not resident (sharded evaluation) — the gathered compact copy Jt[n_grid][n_out]
+__device__ __forceinline__ double time_col(const DevLayout& L, const double* J, int j, int row) {
+    return L.Jt ? L.Jt[(size_t)j * L.n_out + row] : J[((size_t)j * L.n_out + row) * L.n_in];
+}
 // integrals of the goal integrands: I_k = T * sum_j quad_j * integrand_k(j)  (CasOCTranscription.cpp:489-493)
 // d_I = [I (n_integrand) | dI/dt0 | dI/dtf]
 __global__ void k_integrals(DevLayout L, const double* __restrict__ x, const double* __restrict__ Y, const double* __restrict__ J, double* I, int withJ) {
@@ -159,7 +165,7 @@ __global__ void k_integrals(DevLayout L, const double* __restrict__ x, const dou
         const double qj = L.quad[j];
         s0 += qj * Y[(size_t)j * L.n_out + row];
         if (withJ) {
-            const double dydt = J[((size_t)j * L.n_out + row) * L.n_in];
+            const double dydt = time_col(L, J, j, row);
             s1 += qj * dydt * (1.0 - L.grid[j]);
             s2 += qj * dydt * L.grid[j];
         }
@@ -270,7 +276,17 @@ __device__ __forceinline__ double dxdot(const DevLayout& L, const double* J, int
 __device__ __forceinline__ double dxdot_dt(const DevLayout& L, const double* J, int j, int s) {
     if (s < L.nq) return 0.0;
     if (s < 2 * L.nq && L.implicit) return 0.0;
-    return J[((size_t)j * L.n_out + (s - L.nq)) * L.n_in];
+    return time_col(L, J, j, s - L.nq);
+}
+__global__ void k_pack_time_column(DevLayout L, const double* __restrict__ J, double* __restrict__ Jt, int p0, int np) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= np * L.n_out) return;
+    const size_t e = (size_t)p0 * L.n_out + t;
+    Jt[e] = J[e * L.n_in];
+}
+void launch_pack_time_column(const DevLayout& L, const double* d_J, double* d_Jt, int p0, int np, cudaStream_t s) {
+    const int n = np * L.n_out;
+    if (n > 0) k_pack_time_column<<<(n + 255) / 256, 256, 0, s>>>(L, d_J, d_Jt, p0, np);
 }
 // defect coefficients: defect = sum_role lin_role * x_role,s + sum_role (wc_role * h) * xdot_role,s
 __device__ __forceinline__ void defect_coeffs(int kind, int role, double& lin, double& wc) {
@@ -344,9 +360,9 @@ __global__ void k_assemble_g_path(DevTables T, DevLayout L, const double* __rest
     const int* gr = T.idx + T.o_goal_i + rm.pad * MOCOB200_GOAL_ISTRIDE;
     g[r] = pathcon_error(T, T.idx + gr[4], rm.b, x[0] + (x[1] - x[0]) * L.grid[rm.a], x + L.off_controls + (size_t)rm.a * L.nc, -1, 0.0);
 }
-__global__ void k_assemble_jac_path(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ x, double* __restrict__ vals) {
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= L.nnz) return;
+__global__ void k_assemble_jac_path(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ x, double* __restrict__ vals, int k0, int k1) {
+    const int k = k0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= k1) return;
     const RowMetaD rm = L.rows[L.rowidx[k]];
     if (rm.kind != ROW_PATH_D) return;
     const ColMetaD c = L.cols[L.nnzcol[k]];
@@ -438,10 +454,12 @@ __device__ __forceinline__ double endpoint_entry(const DevLayout& L, const doubl
     return v;
 }
 
+// entries [k0, k1) of the CSC value array (the whole array, or the run of one block of columns when the columns are shared out
+// over ranks: a column's entries need the FD blocks of that column's own grid point only, except the t0 / tf columns)
 __global__ void k_assemble_jac(DevLayout L, const double* __restrict__ x, const double* __restrict__ Y, const double* __restrict__ J,
-                               const double* __restrict__ I, const double* __restrict__ E, double* __restrict__ vals) {
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= L.nnz) return;
+                               const double* __restrict__ I, const double* __restrict__ E, double* __restrict__ vals, int k0, int k1) {
+    const int k = k0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= k1) return;
     const RowMetaD rm = L.rows[L.rowidx[k]];
     const ColMetaD c = L.cols[L.nnzcol[k]];
     const bool hs = L.scheme == MOCOB200_SCHEME_HERMITE_SIMPSON;
@@ -451,9 +469,8 @@ __global__ void k_assemble_jac(DevLayout L, const double* __restrict__ x, const 
         v = endpoint_entry(L, x, J, I, E, rm.a, rm.b, c);
     } else if (rm.kind == ROW_RESIDUAL_D) {
         const int j = rm.a;
-        const double* Jr = J + ((size_t)j * L.n_out + rm.b) * L.n_in;
-        if (isTime) v = Jr[0] * (c.kind == COL_TF_D ? L.grid[j] : 1.0 - L.grid[j]);
-        else v = Jr[c.in];
+        if (isTime) v = time_col(L, J, j, rm.b) * (c.kind == COL_TF_D ? L.grid[j] : 1.0 - L.grid[j]);
+        else v = J[((size_t)j * L.n_out + rm.b) * L.n_in + c.in];
     } else if (rm.kind == ROW_PATH_D) {
         return; // k_assemble_jac_path
     } else if (rm.kind == ROW_INTERP_D) {
@@ -521,11 +538,12 @@ __global__ void k_assemble_grad(DevTables T, DevLayout L, const double* __restri
 void launch_points_nominal(const DevTables& T, const DevLayout& L, const double* d_x, double* d_Y, int p0, int np, cudaStream_t s) {
     if (np <= 0) return;
     const int bs = 32;
-    k_points_nominal<<<(np + bs - 1) / bs, bs, 0, s>>>(T, L, d_x, d_Y, p0, np);
+    if (L.small_size) k_points_nominal<SizeSmall><<<(np + bs - 1) / bs, bs, 0, s>>>(T, L, d_x, d_Y, p0, np);
+    else k_points_nominal<SizeLarge><<<(np + bs - 1) / bs, bs, 0, s>>>(T, L, d_x, d_Y, p0, np);
 }
 // Flat variant: one thread per (grid point, listed direction), nominal outputs read from Y (already evaluated). Every
 // lane of every warp carries an evaluation chain, so a short direction list still fills the machine in one wave.
-template <int MINB>
+template <int MINB, class SZ>
 __global__ void __launch_bounds__(64, MINB)
 k_points_fd_flat(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ x, const double* __restrict__ Y, double* __restrict__ J,
                  int p0, int np, const int* __restrict__ dirs, int ndirs) {
@@ -533,19 +551,19 @@ k_points_fd_flat(DevTables T, DevLayout L, FdSettings fd, const double* __restri
     if (gid >= (long)np * ndirs) return;
     const int j = p0 + (int)(gid / ndirs);
     const int a = dirs[gid % ndirs];
-    double in[MOCOB200_MAX_IN];
-    double ya[MOCOB200_MAX_OUT], yb[MOCOB200_MAX_OUT], Jc[MOCOB200_MAX_OUT];
+    double in[SZ::NIN];
+    double ya[SZ::NOUT], yb[SZ::NOUT], Jc[SZ::NOUT];
     gather_inputs(L, x, j, in);
     const double* y0 = Y + (size_t)j * L.n_out;
     if (fd.scheme != MOCOB200_FD_CENTRAL) {
-        fd_group([&](const double* xin, double* yout) { eval_point(T, xin, yout, 0xffffffffu); }, fd, in, a, y0, 0, L.n_out, yb, ya, Jc);
+        fd_group([&](const double* xin, double* yout) { eval_point<SZ>(T, xin, yout, 0xffffffffu); }, fd, in, a, y0, 0, L.n_out, yb, ya, Jc);
     } else {
         const int ngroups = 1 + L.n_integrand;
         for (int gidx = 0; gidx < ngroups; ++gidx) {
             const unsigned mask = 1u << gidx;
             const int lo = gidx == 0 ? 0 : L.n_dyn_out + gidx - 1;
             const int hi = gidx == 0 ? L.n_dyn_out : lo + 1;
-            fd_group([&](const double* xin, double* yout) { eval_point(T, xin, yout, mask); }, fd, in, a, y0, lo, hi, yb, ya, Jc);
+            fd_group([&](const double* xin, double* yout) { eval_point<SZ>(T, xin, yout, mask); }, fd, in, a, y0, lo, hi, yb, ya, Jc);
         }
     }
     double* Jp = J + (size_t)j * L.n_out * L.n_in;
@@ -579,7 +597,7 @@ __device__ inline void fd_group_central_pair(F&& f, const FdSettings& fd, double
         else h *= sqrt(fd.u_aim / fmax(1.0, u));
     }
 }
-template <int MINB>
+template <int MINB, class SZ>
 __global__ void __launch_bounds__(64, MINB)
 k_points_fd_flat_pair(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ x, const double* __restrict__ Y,
                       double* __restrict__ J, int p0, int np, const int* __restrict__ dirs, int ndirs) {
@@ -591,8 +609,8 @@ k_points_fd_flat_pair(DevTables T, DevLayout L, FdSettings fd, const double* __r
     const long item = gid >> 1;
     const int j = p0 + (int)(item / ndirs);
     const int a = dirs[item % ndirs];
-    double in[MOCOB200_MAX_IN];
-    double yo[MOCOB200_MAX_OUT], Jc[MOCOB200_MAX_OUT];
+    double in[SZ::NIN];
+    double yo[SZ::NOUT], Jc[SZ::NOUT];
     gather_inputs(L, x, j, in);
     const double* y0 = Y + (size_t)j * L.n_out;
     const int ngroups = 1 + L.n_integrand;
@@ -600,7 +618,7 @@ k_points_fd_flat_pair(DevTables T, DevLayout L, FdSettings fd, const double* __r
         const unsigned mask = 1u << gidx;
         const int lo = gidx == 0 ? 0 : L.n_dyn_out + gidx - 1;
         const int hi = gidx == 0 ? L.n_dyn_out : lo + 1;
-        fd_group_central_pair([&](const double* xin, double* yout) { eval_point(T, xin, yout, mask); }, fd, in, a, y0, lo, hi, yo, Jc, side);
+        fd_group_central_pair([&](const double* xin, double* yout) { eval_point<SZ>(T, xin, yout, mask); }, fd, in, a, y0, lo, hi, yo, Jc, side);
     }
     if (!valid || side) return;
     double* Jp = J + (size_t)j * L.n_out * L.n_in;
@@ -619,15 +637,26 @@ void launch_points_fd_flat(const DevTables& T, const DevLayout& L, const FdSetti
     const bool paired = fd.scheme == MOCOB200_FD_CENTRAL && (!ePair || atoi(ePair) != 0);
     const char* eMinb = getenv("MOCOB200_FLAT_MINBLOCKS");
     const int minb = eMinb && atoi(eMinb) > 0 ? atoi(eMinb) : (paired ? 8 : 4);
+    const bool small = L.small_size != 0;
     if (paired) {
         const unsigned nb = (unsigned)((2 * n + 63) / 64);
-        if (minb == 8) k_points_fd_flat_pair<8><<<nb, 64, 0, s>>>(T, L, fd, d_x, d_Y, d_J, p0, np, d_dirs, ndirs);
-        else k_points_fd_flat_pair<4><<<nb, 64, 0, s>>>(T, L, fd, d_x, d_Y, d_J, p0, np, d_dirs, ndirs);
+        if (small) {
+            if (minb == 8) k_points_fd_flat_pair<8, SizeSmall><<<nb, 64, 0, s>>>(T, L, fd, d_x, d_Y, d_J, p0, np, d_dirs, ndirs);
+            else k_points_fd_flat_pair<4, SizeSmall><<<nb, 64, 0, s>>>(T, L, fd, d_x, d_Y, d_J, p0, np, d_dirs, ndirs);
+        } else {
+            if (minb == 8) k_points_fd_flat_pair<8, SizeLarge><<<nb, 64, 0, s>>>(T, L, fd, d_x, d_Y, d_J, p0, np, d_dirs, ndirs);
+            else k_points_fd_flat_pair<4, SizeLarge><<<nb, 64, 0, s>>>(T, L, fd, d_x, d_Y, d_J, p0, np, d_dirs, ndirs);
+        }
         return;
     }
     const unsigned nb = (unsigned)((n + 63) / 64);
-    if (minb == 8) k_points_fd_flat<8><<<nb, 64, 0, s>>>(T, L, fd, d_x, d_Y, d_J, p0, np, d_dirs, ndirs);
-    else k_points_fd_flat<4><<<nb, 64, 0, s>>>(T, L, fd, d_x, d_Y, d_J, p0, np, d_dirs, ndirs);
+    if (small) {
+        if (minb == 8) k_points_fd_flat<8, SizeSmall><<<nb, 64, 0, s>>>(T, L, fd, d_x, d_Y, d_J, p0, np, d_dirs, ndirs);
+        else k_points_fd_flat<4, SizeSmall><<<nb, 64, 0, s>>>(T, L, fd, d_x, d_Y, d_J, p0, np, d_dirs, ndirs);
+    } else {
+        if (minb == 8) k_points_fd_flat<8, SizeLarge><<<nb, 64, 0, s>>>(T, L, fd, d_x, d_Y, d_J, p0, np, d_dirs, ndirs);
+        else k_points_fd_flat<4, SizeLarge><<<nb, 64, 0, s>>>(T, L, fd, d_x, d_Y, d_J, p0, np, d_dirs, ndirs);
+    }
 }
 
 void launch_points_fd(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, double* d_Y, double* d_J, int p0,
@@ -657,10 +686,12 @@ void launch_assemble_f(const DevTables& T, const DevLayout& L, const double* d_x
     k_assemble_f<<<1, 32, 0, s>>>(T, L, d_x, d_G, d_f);
 }
 void launch_assemble_jac(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, const double* d_Y, const double* d_J,
-                         const double* d_I, const double* d_E, double* d_vals, cudaStream_t s) {
-    if (L.nnz <= 0) return;
-    k_assemble_jac<<<(L.nnz + 255) / 256, 256, 0, s>>>(L, d_x, d_Y, d_J, d_I, d_E, d_vals);
-    if (L.n_path_rows > 0) k_assemble_jac_path<<<(L.nnz + 255) / 256, 256, 0, s>>>(T, L, fd, d_x, d_vals);
+                         const double* d_I, const double* d_E, double* d_vals, cudaStream_t s, int k0, int k1) {
+    if (k1 < 0) { k0 = 0; k1 = L.nnz; }
+    const int n = k1 - k0;
+    if (n <= 0) return;
+    k_assemble_jac<<<(n + 255) / 256, 256, 0, s>>>(L, d_x, d_Y, d_J, d_I, d_E, d_vals, k0, k1);
+    if (L.n_path_rows > 0) k_assemble_jac_path<<<(n + 255) / 256, 256, 0, s>>>(T, L, fd, d_x, d_vals, k0, k1);
 }
 void launch_assemble_grad(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_Y, const double* d_J, const double* d_I,
                           const double* d_E, double* d_grad, cudaStream_t s) {

@@ -41,6 +41,8 @@ struct DevLayout {
     const int* colptr; const int* rowidx; const int* nnzcol;
     int n_eout_total; // total outputs over all goals
     int n_path_rows;  // path-constraint equations per mesh point (0: no path-constraint kernels are launched)
+    const double* Jt; // sharded evaluation: the time column of every grid point's FD block, gathered ([n_grid][n_out]); else null
+    int small_size;   // the model fits the SizeSmall class of the thread-per-evaluation kernels (point_eval.cuh)
 };
 
 void launch_points_nominal(const DevTables& T, const DevLayout& L, const double* d_x, double* d_Y, int p0, int np, cudaStream_t s);
@@ -65,8 +67,10 @@ void launch_endpoint(const DevTables& T, const DevLayout& L, const FdSettings& f
 void launch_assemble_g(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_Y, const double* d_G, double* d_g,
                        cudaStream_t s);
 void launch_assemble_f(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_G, double* d_f /*[1+n_cost_terms]*/, cudaStream_t s);
+// CSC entries [k0, k1) (k1 < 0: all of them)
 void launch_assemble_jac(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, const double* d_Y,
-                         const double* d_J, const double* d_I, const double* d_E, double* d_vals, cudaStream_t s);
+                         const double* d_J, const double* d_I, const double* d_E, double* d_vals, cudaStream_t s, int k0 = 0, int k1 = -1);
+void launch_pack_time_column(const DevLayout& L, const double* d_J, double* d_Jt, int p0, int np, cudaStream_t s);
 void launch_assemble_grad(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_Y, const double* d_J, const double* d_I,
                           const double* d_E, double* d_grad, cudaStream_t s);
 double measure_fp64_peak_tflops(int device);

@@ -46,6 +46,10 @@ struct Layout {
 // CasOCFunction.cpp:25-105); the structure then holds only the entries CasADi's sparsity propagation would keep.
 Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bool withStructure,
                    const unsigned char* blockMask = nullptr);
+// Copies T into (dbl, idx) with every body that hangs on a WeldJoint merged into its parent (table_opt.cpp); `out` addresses the
+// copies. Returns the number of bodies removed. Coordinates, states, controls and goals are untouched, so the NLP layout of T
+// stays valid for the reduced tables.
+int mergeWeldedBodies(const mocob200_tables& T, std::vector<double>& dbl, std::vector<int>& idx, mocob200_tables& out);
 void layoutBounds(const mocob200_tables& T, const mocob200_transcription& R, const Layout& L, double* xlo, double* xhi,
                   double* glo, double* ghi);
 

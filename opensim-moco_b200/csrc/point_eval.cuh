@@ -26,6 +26,10 @@ namespace mocob200 {
 #endif
 #define MOCOB200_MAXCONTACT 8
 #define MOCOB200_MAXPPM 12 /* path points per muscle */
+// The thread-per-evaluation code keeps its scratch in thread-local memory, whose traffic bounds it: every array
+// is sized by a size class chosen at launch, so that a 8-body / 58-input model does not carry 16-body / 160-input frames.
+struct SizeLarge { static constexpr int NB = MOCOB200_MAXB, NQ = MOCOB200_MAXQ, NPPM = MOCOB200_MAXPPM, NIN = 160, NOUT = 72; };
+struct SizeSmall { static constexpr int NB = 8, NQ = 12, NPPM = 8, NIN = 64, NOUT = 32; };
 
 struct DevTables { // mocob200_tables with device (or shared-memory) pool pointers
     const double* dbl;
@@ -223,16 +227,15 @@ __device__ __forceinline__ double dgf_active_fl_d(double nfl, double scale) {
                             dgf_gauss_d(x, 0.433004984392647, 0.716775413397760, -0.029947116970696, 0.200356847296188) +
                             dgf_gauss_d(x, 0.1, 1.0, 0.353553390593274, 0.0));
 }
-__device__ __forceinline__ double dgf_passive_fl(double nfl, double e0) {
+// offset = exp(kPE (minNormFiberLength - 1) / e0) and denom = exp(kPE) - offset depend on the muscle's parameters only: the device
+// copy of the muscle record carries them (mocob200_create, DEV_MUS_* slots below)
+__device__ __forceinline__ double dgf_passive_fl(double nfl, double e0, double offset, double denom) {
     const double kPE = 4.0;
-    const double offset = exp(kPE * (0.2 - 1.0) / e0);
-    const double denom = exp(kPE) - offset;
     return (exp(kPE * (nfl - 1.0) / e0) - offset) / denom;
 }
-__device__ __forceinline__ double dgf_passive_fl_d(double nfl, double e0) {
+__device__ __forceinline__ double dgf_passive_fl_d(double nfl, double e0, double denom) {
     const double kPE = 4.0;
-    const double offset = exp(kPE * (0.2 - 1.0) / e0);
-    return (kPE * exp((kPE * (nfl - 1.0)) / e0)) / (e0 * (exp(kPE) - offset));
+    return (kPE * exp((kPE * (nfl - 1.0)) / e0)) / (e0 * denom);
 }
 __device__ __forceinline__ double dgf_fv(double nv) {
     const double d1 = -0.3211346127989808, d2 = -8.149, d3 = -0.374, d4 = 0.8825327733249912;
@@ -242,6 +245,20 @@ __device__ __forceinline__ double dgf_fv(double nv) {
 __device__ __forceinline__ double dgf_fv_inv(double fv) {
     const double d1 = -0.3211346127989808, d2 = -8.149, d3 = -0.374, d4 = 0.8825327733249912;
     return (sinh(1.0 / d1 * (fv - d4)) - d3) / d2;
+}
+
+// Slots of the DEVICE copy of a muscle record that hold constants derived at mocob200_create from the record's own parameters
+// (they replace fields only the host reads: tendon strain -> kT is already in slot 13, the control bounds live in the bounds table).
+#define DEV_MUS_PE_DENOM 8     /* exp(kPE) - offset                        (was tendon_strain_at_one_norm_force) */
+#define DEV_MUS_FIBER_WIDTH 11 /* optimal_fiber_length sin(pennation)      (was min_control) */
+#define DEV_MUS_PE_OFFSET 12   /* exp(kPE (0.2 - 1) / passive_fiber_strain) (was max_control) */
+#define DEV_CONTACT_HERTZ 25   /* (4/3) k sqrt(radius k), k = stiffness^(2/3) / 2 (a pad slot of the contact record) */
+// |c|^n for the integer exponents of MocoControlGoal (n >= 2)
+__device__ __forceinline__ double abs_ipow(double c, int n) {
+    const double a = fabs(c);
+    double r = a * a;
+    for (int k = 2; k < n; ++k) r *= a;
+    return r;
 }
 
 struct MuscleOut {
@@ -256,8 +273,7 @@ struct MuscleOut {
 // reaches the outputs; wantStiffness adds the stiffness terms needed by the linearized residual.
 __device__ inline MuscleOut dgf_muscle(const double* p, int flags, double mtLength, double mtVelocity, double activation,
                                       double normTendonForce, double normTendonForceDeriv, bool wantStiffness) {
-    const double Fmax = p[0], lopt = p[1], lslack = p[2], alpha0 = p[3], vmaxN = p[4], damping = p[7], e0 = p[9],
-                 wscale = p[10], kT = p[13];
+    const double Fmax = p[0], lopt = p[1], lslack = p[2], vmaxN = p[4], damping = p[7], e0 = p[9], wscale = p[10], kT = p[13];
     const double c1 = 0.200, c2 = 1.0, c3 = 0.200;
     const bool rigid = flags & MOCOB200_MUS_FLAG_IGNORE_TENDON_COMPLIANCE;
     const bool implicitT = flags & MOCOB200_MUS_FLAG_TENDON_IMPLICIT;
@@ -267,7 +283,8 @@ __device__ inline MuscleOut dgf_muscle(const double* p, int flags, double mtLeng
         o.residual = 0.0; o.nfDeriv = 0.0; o.linResidDeriv = 0.0;
         return o;
     }
-    const double fiberWidth = lopt * sin(alpha0);
+    const double fiberWidth = p[DEV_MUS_FIBER_WIDTH]; // lopt * sin(alpha0)
+    const double peOffset = p[DEV_MUS_PE_OFFSET], peDenom = p[DEV_MUS_PE_DENOM];
     const double vmax = vmaxN * lopt;
     // length info
     const double normTendonLength = rigid ? 1.0 : log((1.0 / c1) * (normTendonForce + c3)) / kT + c2;
@@ -277,7 +294,7 @@ __device__ inline MuscleOut dgf_muscle(const double* p, int flags, double mtLeng
     const double nfl = fiberLength / lopt;
     const double cosA = fibAlong / fiberLength;
     const double sinA = fiberWidth / fiberLength;
-    const double fpe = (flags & MOCOB200_MUS_FLAG_IGNORE_PASSIVE) ? 0.0 : dgf_passive_fl(nfl, e0);
+    const double fpe = (flags & MOCOB200_MUS_FLAG_IGNORE_PASSIVE) ? 0.0 : dgf_passive_fl(nfl, e0, peOffset, peDenom);
     const double fal = dgf_active_fl(nfl, wscale);
     // velocity info
     double normFiberVelocity, fv, fiberVelAlong, tendonVelocity;
@@ -314,7 +331,7 @@ __device__ inline MuscleOut dgf_muscle(const double* p, int flags, double mtLeng
         // calcPartialFiberForceAlongTendonPartialFiberLength, calcFiberStiffnessAlongTendon,
         // calcTendonStiffness (DeGrooteFregly2016Muscle.h:506-618)
         const double fiberStiffness = Fmax * (activation * (1.0 / lopt) * dgf_active_fl_d(nfl, wscale) * fv +
-                                              ((flags & MOCOB200_MUS_FLAG_IGNORE_PASSIVE) ? 0.0 : (1.0 / lopt) * dgf_passive_fl_d(nfl, e0)));
+                                              ((flags & MOCOB200_MUS_FLAG_IGNORE_PASSIVE) ? 0.0 : (1.0 / lopt) * dgf_passive_fl_d(nfl, e0, peDenom)));
         const double dAlpha_dL = -fiberWidth / (fiberLength * fiberLength) / sqrt(1.0 - (fiberWidth / fiberLength) * (fiberWidth / fiberLength));
         const double dFalong_dL = fiberStiffness * cosA - fiberForce * sinA * dAlpha_dL;
         const double dLalong_dL = cosA - fiberLength * sinA * dAlpha_dL;
@@ -326,17 +343,20 @@ __device__ inline MuscleOut dgf_muscle(const double* p, int flags, double mtLeng
 }
 
 // Scratch for one evaluation. Lives in thread-local memory.
-struct Scratch {
-    double R[MOCOB200_MAXB][9]; // R_GB
-    V3 p[MOCOB200_MAXB];        // body origin in ground
-    V3 w[MOCOB200_MAXB], v[MOCOB200_MAXB]; // spatial velocity of the body origin
-    V3 Fm[MOCOB200_MAXB], Ff[MOCOB200_MAXB]; // applied spatial force (moment about origin ; force)
-    double tau[MOCOB200_MAXQ];  // applied mobility forces
+template <class SZ>
+struct ScratchT {
+    double R[SZ::NB][9]; // R_GB
+    V3 p[SZ::NB];        // body origin in ground
+    V3 w[SZ::NB], v[SZ::NB]; // spatial velocity of the body origin
+    V3 Fm[SZ::NB], Ff[SZ::NB]; // applied spatial force (moment about origin ; force)
+    double tau[SZ::NQ];  // applied mobility forces
     V3 contactF[MOCOB200_MAXCONTACT]; // force on the sphere body of each contact (ground frame)
 };
+typedef ScratchT<SizeLarge> Scratch;
 
 // position + velocity kinematics, base to tip.
-__device__ inline void kinematics(const DevTables& T, const double* q, const double* u, Scratch& S) {
+template <class SZ>
+__device__ inline void kinematics(const DevTables& T, const double* q, const double* u, ScratchT<SZ>& S) {
     for (int b = 0; b < T.nb; ++b) {
         const double* bd = T.dbl + T.o_body_d + b * MOCOB200_BODY_DSTRIDE;
         const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
@@ -403,12 +423,14 @@ __device__ inline void kinematics(const DevTables& T, const double* q, const dou
     }
 }
 
-__device__ __forceinline__ void apply_point_force(Scratch& S, int b, V3 pointG, V3 f) {
+template <class SZ>
+__device__ __forceinline__ void apply_point_force(ScratchT<SZ>& S, int b, V3 pointG, V3 f) {
     if (b < 0) return; // ground
     S.Ff[b] = S.Ff[b] + f;
     S.Fm[b] = S.Fm[b] + cross(pointG - S.p[b], f);
 }
-__device__ __forceinline__ V3 point_velocity(const Scratch& S, int b, V3 pointG) {
+template <class SZ>
+__device__ __forceinline__ V3 point_velocity(const ScratchT<SZ>& S, int b, V3 pointG) {
     if (b < 0) return mk(0, 0, 0);
     return S.v[b] + cross(S.w[b], pointG - S.p[b]);
 }
@@ -417,13 +439,14 @@ __device__ __forceinline__ V3 point_velocity(const Scratch& S, int b, V3 pointG)
 // model description in opensim-core/OpenSim/Simulation/Model/SmoothSphereHalfSpaceForce.h:28-66 and
 // Serrancoli et al. 2019: smoothed Hertz force, Hunt–Crossley dissipation,
 // smooth stick–slip friction. Returns the force on the sphere body; applies both sides.
-__device__ inline V3 contact_force(const DevTables& T, int ci, Scratch& S, bool apply) {
+template <class SZ>
+__device__ inline V3 contact_force(const DevTables& T, int ci, ScratchT<SZ>& S, bool apply) {
     const double* cd = T.dbl + T.o_contact_d + ci * MOCOB200_CONTACT_DSTRIDE;
     const int* cidx = T.idx + T.o_contact_i + ci * MOCOB200_CONTACT_ISTRIDE;
     const int bs = cidx[0], bh = cidx[1];
     const double radius = cd[3];
     const double* pr = cd + 16;
-    const double stiffness = pr[0], diss = pr[1], us = pr[2], ud = pr[3], uv = pr[4], vt = pr[5], cf = pr[6], bd = pr[7], bv = pr[8];
+    const double diss = pr[1], us = pr[2], ud = pr[3], uv = pr[4], vt = pr[5], cf = pr[6], bd = pr[7], bv = pr[8];
     // half-space frame in ground; the half space fills +x of its frame, so the outward normal is -x
     V3 nrm, oH;
     {
@@ -440,8 +463,8 @@ __device__ inline V3 contact_force(const DevTables& T, int ci, Scratch& S, bool 
     const double vnormal = dot(vrel, nrm);
     const V3 vtan = vrel - vnormal * nrm;
     const double indVel = -vnormal;
-    const double k = 0.5 * pow(stiffness, 2.0 / 3.0);
-    const double fH = (4.0 / 3.0) * k * sqrt(radius * k) * pow(sqrt(indentation * indentation + cf), 1.5);
+    const double ind = sqrt(indentation * indentation + cf);
+    const double fH = cd[DEV_CONTACT_HERTZ] * (ind * sqrt(ind)); // (4/3) k sqrt(radius k) ind^(3/2)
     const double fHs = fH * (0.5 + 0.5 * tanh(bd * indentation)) + cf;
     const double fHC = fHs * (1.0 + 1.5 * diss * indVel);
     const double fn = fHC * (0.5 + 0.5 * tanh(bv * (indVel + 2.0 / (3.0 * diss))));
@@ -460,14 +483,15 @@ __device__ inline V3 contact_force(const DevTables& T, int ci, Scratch& S, bool 
 // Muscle path geometry + muscle model + equivalent forces for muscle m
 // (GeometryPath.cpp:306-432, 817-864, 1117-1145; Point.cpp:130-140; ConditionalPathPoint.cpp:160-169;
 //  MovingPathPoint.cpp:216-315, 374-392; PathActuator.cpp:170-197).
+template <class SZ>
 __device__ inline MuscleOut muscle_force(const DevTables& T, int m, const double* q, const double* u, const double* z,
-                                        const double* ctl, const double* deriv, Scratch& S, bool apply, bool wantStiffness,
+                                        const double* ctl, const double* deriv, ScratchT<SZ>& S, bool apply, bool wantStiffness,
                                         double* lengthSpeed = nullptr) {
     const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
     const double* md = T.dbl + T.o_mus_d + m * MOCOB200_MUS_DSTRIDE;
     const int first = mi[0], count = mi[1], flags = mi[5];
-    V3 pos[MOCOB200_MAXPPM], dPdq[MOCOB200_MAXPPM];
-    int body[MOCOB200_MAXPPM], mcoord[MOCOB200_MAXPPM];
+    V3 pos[SZ::NPPM], dPdq[SZ::NPPM];
+    int body[SZ::NPPM], mcoord[SZ::NPPM];
     int na = 0;
     double length = 0, speed = 0;
     V3 prevP = mk(0, 0, 0), prevV = mk(0, 0, 0);
@@ -506,7 +530,7 @@ __device__ inline MuscleOut muscle_force(const DevTables& T, int m, const double
         }
         prevP = pG;
         prevV = vG;
-        if (na < MOCOB200_MAXPPM) { pos[na] = pG; body[na] = b; mcoord[na] = mc; dPdq[na] = dp; }
+        if (na < SZ::NPPM) { pos[na] = pG; body[na] = b; mcoord[na] = mc; dPdq[na] = dp; }
         ++na;
     }
     if (lengthSpeed) { lengthSpeed[0] = length; lengthSpeed[1] = speed; }
@@ -553,7 +577,8 @@ __device__ __forceinline__ V3 bmul(const double* B, V3 v) { return rmul(B, v); }
 __device__ __forceinline__ V3 btmul(const double* B, V3 v) { return rtmul(B, v); }
 
 // spatial inertia of body b about its origin, in ground: I_o = R I R^T, c = R com
-__device__ inline void body_inertia_ground(const DevTables& T, int b, const Scratch& S, double* Io /*sym6*/, V3& mc, double& mass) {
+template <class SZ>
+__device__ inline void body_inertia_ground(const DevTables& T, int b, const ScratchT<SZ>& S, double* Io /*sym6*/, V3& mc, double& mass) {
     const double* bd = T.dbl + T.o_body_d + b * MOCOB200_BODY_DSTRIDE;
     mass = bd[24];
     const V3 c = rmul(S.R[b], ld3(bd + 25));
@@ -568,7 +593,8 @@ __device__ inline void body_inertia_ground(const DevTables& T, int b, const Scra
 }
 
 // hinge data of body b in ground: returns dof; axes as (angular, linear-at-B-origin) pairs
-__device__ inline int hinge(const DevTables& T, int b, const Scratch& S, V3* Ha, V3* Hl, V3& oMrel /* pB - oM */) {
+template <class SZ>
+__device__ inline int hinge(const DevTables& T, int b, const ScratchT<SZ>& S, V3* Ha, V3* Hl, V3& oMrel /* pB - oM */) {
     const double* bd = T.dbl + T.o_body_d + b * MOCOB200_BODY_DSTRIDE;
     const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
     const int par = bi[0], kind = bi[1];
@@ -599,7 +625,8 @@ __device__ inline int hinge(const DevTables& T, int b, const Scratch& S, V3* Ha,
 }
 
 // velocity-dependent (Coriolis) acceleration of body b relative to its parent, ground frame
-__device__ inline void coriolis(const DevTables& T, int b, const Scratch& S, const double* u, V3& ca, V3& cl) {
+template <class SZ>
+__device__ inline void coriolis(const DevTables& T, int b, const ScratchT<SZ>& S, const double* u, V3& ca, V3& cl) {
     const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
     const int par = bi[0], q0 = bi[2];
     V3 Ha[3], Hl[3], sv;
@@ -614,11 +641,12 @@ __device__ inline void coriolis(const DevTables& T, int b, const Scratch& S, con
 }
 
 // Explicit mode: articulated-body algorithm. udot out.
-__device__ inline void forward_dynamics(const DevTables& T, const double* u, Scratch& S, double* udot) {
-    ArtI P[MOCOB200_MAXB];
-    V3 zm[MOCOB200_MAXB], zf[MOCOB200_MAXB]; // z (moment; force)
-    V3 Ga[MOCOB200_MAXQ], Gl[MOCOB200_MAXQ]; // G = P H D^-1 columns
-    double nu[MOCOB200_MAXQ];                 // D^-1 eps
+template <class SZ>
+__device__ inline void forward_dynamics(const DevTables& T, const double* u, ScratchT<SZ>& S, double* udot) {
+    ArtI P[SZ::NB];
+    V3 zm[SZ::NB], zf[SZ::NB]; // z (moment; force)
+    V3 Ga[SZ::NQ], Gl[SZ::NQ]; // G = P H D^-1 columns
+    double nu[SZ::NQ];          // D^-1 eps
     const int nb = T.nb;
     // initialise with rigid-body inertias and bias forces
     for (int b = 0; b < nb; ++b) {
@@ -745,8 +773,9 @@ __device__ inline void forward_dynamics(const DevTables& T, const double* u, Scr
 // Implicit mode: residual = f_app - M udot - f_inertial by recursive Newton–Euler
 // (what SimbodyMatterSubsystem::findMotionForces reports under AccelerationMotion,
 //  MocoCasOCProblem.h:245-297; sign per Moco/doc/MocoDeveloperGuide.dox:175-208).
-__device__ inline void inverse_dynamics_residual(const DevTables& T, const double* u, const double* udot, Scratch& S, double* resid) {
-    V3 fm[MOCOB200_MAXB], ff[MOCOB200_MAXB], aa[MOCOB200_MAXB], al[MOCOB200_MAXB];
+template <class SZ>
+__device__ inline void inverse_dynamics_residual(const DevTables& T, const double* u, const double* udot, ScratchT<SZ>& S, double* resid) {
+    V3 fm[SZ::NB], ff[SZ::NB], aa[SZ::NB], al[SZ::NB];
     const int nb = T.nb;
     for (int b = 0; b < nb; ++b) {
         const int* bi = T.idx + T.o_body_i + b * MOCOB200_BODY_ISTRIDE;
@@ -784,7 +813,8 @@ __device__ inline void inverse_dynamics_residual(const DevTables& T, const doubl
 }
 
 // whole-model mass centre in ground (Model::calcMassCenterPosition), needs kinematics()
-__device__ inline V3 mass_center(const DevTables& T, const Scratch& S) {
+template <class SZ>
+__device__ inline V3 mass_center(const DevTables& T, const ScratchT<SZ>& S) {
     V3 acc = mk(0, 0, 0);
     double mt = 0;
     for (int b = 0; b < T.nb; ++b) {
@@ -799,6 +829,7 @@ __device__ inline V3 mass_center(const DevTables& T, const Scratch& S) {
 // The fused point function. in = [time, states(2nq+nz), controls(nc), derivatives(nd)], out[n_out].
 // mask selects output groups (one group per reference callback): bit 0 = dynamics
 // (udot|residual, zdot, aux residuals), bit 1+k = integrand k. Unselected outputs are left untouched.
+template <class SZ = SizeLarge>
 __device__ inline void eval_point(const DevTables& T, const double* in, double* out, unsigned mask) {
     const int nq = T.nq, nz = T.nz, nc = T.nc;
     const double time = in[0];
@@ -820,7 +851,7 @@ __device__ inline void eval_point(const DevTables& T, const double* in, double* 
             ++gi;
         }
     }
-    Scratch S;
+    ScratchT<SZ> S;
     if (need_contacts) {
         kinematics(T, q, u, S);
         for (int c = 0; c < T.ncontact; ++c) {
@@ -895,7 +926,7 @@ __device__ inline void eval_point(const DevTables& T, const double* in, double* 
             const int expo = ip[0], n = ip[2];
             for (int k = 0; k < n; ++k) {
                 const double c = ctl[ip[3 + k]];
-                val += dp[3 + k] * (expo == 2 ? c * c : pow(fabs(c), (double)expo));
+                val += dp[3 + k] * (expo == 2 ? c * c : abs_ipow(c, expo));
             }
         } break;
         case MOCOB200_GOAL_STATE_TRACKING: {

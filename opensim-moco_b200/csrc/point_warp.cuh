@@ -251,7 +251,7 @@ __device__ inline void wk_contact(const WarpCtx& C, int ci) {
     const int bs = cidx[0], bh = cidx[1];
     const double radius = cd[3];
     const double* pr = cd + 16;
-    const double stiffness = pr[0], diss = pr[1], us = pr[2], ud = pr[3], uv = pr[4], vt = pr[5], cf = pr[6], bd = pr[7], bv = pr[8];
+    const double diss = pr[1], us = pr[2], ud = pr[3], uv = pr[4], vt = pr[5], cf = pr[6], bd = pr[7], bv = pr[8];
     V3 nrm, oH;
     {
         const V3 xh = mk(cd[4], cd[7], cd[10]);
@@ -269,8 +269,8 @@ __device__ inline void wk_contact(const WarpCtx& C, int ci) {
     const double vnormal = dot(vrel, nrm);
     const V3 vtan = vrel - vnormal * nrm;
     const double indVel = -vnormal;
-    const double k = 0.5 * pow(stiffness, 2.0 / 3.0);
-    const double fH = (4.0 / 3.0) * k * sqrt(radius * k) * pow(sqrt(indentation * indentation + cf), 1.5);
+    const double ind = sqrt(indentation * indentation + cf);
+    const double fH = cd[DEV_CONTACT_HERTZ] * (ind * sqrt(ind)); // (4/3) k sqrt(radius k) ind^(3/2)
     const double fHs = fH * (0.5 + 0.5 * tanh(bd * indentation)) + cf;
     const double fHC = fHs * (1.0 + 1.5 * diss * indVel);
     const double fn = fHC * (0.5 + 0.5 * tanh(bv * (indVel + 2.0 / (3.0 * diss))));

@@ -351,7 +351,7 @@ __device__ __forceinline__ void warp_eval_point_t(const DevTables& T, const Warp
             const int expo = ip[0], n = ip[2];
             for (int k = lane; k < n; k += 32) {
                 const double c = ctl[ip[3 + k]];
-                val += dp[3 + k] * (expo == 2 ? c * c : pow(fabs(c), (double)expo));
+                val += dp[3 + k] * (expo == 2 ? c * c : abs_ipow(c, expo));
             }
         } break;
         case MOCOB200_GOAL_STATE_TRACKING:

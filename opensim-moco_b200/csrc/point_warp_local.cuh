@@ -100,7 +100,7 @@ __device__ inline double wk_integrand_term_delta(const DevTables& T, const WarpA
         const int expo = ip[0], n = ip[2];
         for (int k = 0; k < n; ++k)
             if (ip[3 + k] == control) {
-                const double g1 = expo == 2 ? v1 * v1 : pow(fabs(v1), (double)expo), g0 = expo == 2 ? v0 * v0 : pow(fabs(v0), (double)expo);
+                const double g1 = expo == 2 ? v1 * v1 : abs_ipow(v1, expo), g0 = expo == 2 ? v0 * v0 : abs_ipow(v0, expo);
                 d += dp[3 + k] * g1 - dp[3 + k] * g0;
             }
     } break;

@@ -21,7 +21,6 @@ def _free_port():
 
 
 def _worker(rank, world, port, fixture, opts, out_path):
-    os.environ["MOCOB200_MIN_POINTS_PER_RANK"] = "1"  # split even these small grids
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import ctypes as C
@@ -30,6 +29,7 @@ def _worker(rank, world, port, fixture, opts, out_path):
     import oracle_py as O
 
     m = ge.package()
+    m.lib().mocob200_set_min_points_per_rank(1)  # split even these small grids (every rank makes the same call)
     dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
     try:
         p = m.Problem.load(golden(fixture), opts)
@@ -57,9 +57,45 @@ def _worker(rank, world, port, fixture, opts, out_path):
                 Y[ra.value:rb.value] = buf.numpy()
                 covered[ra.value:rb.value] += 1
             full = o.eval_points(x.numpy())
-            np.save(out_path, np.array([float(np.array_equal(Y, full)), float((covered == 1).all())]))
+            ok_blocks = float(np.array_equal(Y, full))
         elif p1 > p0:
             dist.send(torch.from_numpy(np.ascontiguousarray(mine)), dst=0)
+        dist.barrier()
+        # the Jacobian exchange (jacPipelineSharded): every rank owns the CSC value runs of the state / control / derivative
+        # columns of its grid points (three contiguous runs, CasOCTranscription.h:192-199 column order), rank 0 the t0 / tf columns
+        d = p.dims()
+        colptr, rowidx = p.structure()
+        vals = o.eval_jac_g(x.numpy())  # stands in for the rank's own assembly of its runs
+        n_var, ns, nc, nd = d.n_var, d.ns, d.nc, d.nd
+        off_s, off_c = 2, 2 + n_grid * ns
+        off_d = off_c + n_grid * nc
+
+        def runs_of(r):
+            ra, rb = C.c_int(), C.c_int()
+            m.lib().mocob200_shard_range(n_grid, r, world, C.byref(ra), C.byref(rb))
+            return [(int(colptr[o0 + ra.value * w]), int(colptr[o0 + rb.value * w])) for o0, w in ((off_s, ns), (off_c, nc), (off_d, nd))]
+
+        if rank == 0:
+            out = np.full(vals.size, np.nan)
+            count = np.zeros(vals.size, dtype=int)
+            out[:colptr[2]] = vals[:colptr[2]]
+            count[:colptr[2]] += 1
+            for k0, k1 in runs_of(0):
+                out[k0:k1] = vals[k0:k1]
+                count[k0:k1] += 1
+            for r in range(1, world):
+                for k0, k1 in runs_of(r):
+                    if k1 > k0:
+                        buf = torch.empty(k1 - k0, dtype=torch.float64)
+                        dist.recv(buf, src=r)
+                        out[k0:k1] = buf.numpy()
+                        count[k0:k1] += 1
+            np.save(out_path, np.array([ok_blocks, float((covered == 1).all()), float(np.array_equal(out, vals, equal_nan=True)),
+                                        float((count == 1).all())]))
+        else:
+            for k0, k1 in runs_of(rank):
+                if k1 > k0:
+                    dist.send(torch.from_numpy(np.ascontiguousarray(vals[k0:k1])), dst=0)
         dist.barrier()
     finally:
         dist.destroy_process_group()
@@ -71,16 +107,27 @@ def _worker(rank, world, port, fixture, opts, out_path):
 def test_sharded_point_blocks_gather_to_the_single_rank_result(pkg, orc, tmp_path, fixture, opts, world):
     out = str(tmp_path / "ok.npy")
     mp.spawn(_worker, args=(world, _free_port(), fixture, opts, out), nprocs=world, join=True)
-    same, tiled = np.load(out)
+    same, tiled, same_vals, tiled_vals = np.load(out)
     assert tiled == 1.0, "shards do not tile the grid exactly once"
     assert same == 1.0, "gathered blocks differ from the single-rank evaluation"
+    assert tiled_vals == 1.0, "the ranks' value runs and the time columns do not tile the CSC value array exactly once"
+    assert same_vals == 1.0, "the exchanged value runs differ from the single-rank Jacobian"
 
 
 def test_shard_ranges_tile_any_grid(pkg, monkeypatch):
     import ctypes as C
 
-    assert pkg.lib().mocob200_effective_world(101, 8) == 1 and pkg.lib().mocob200_effective_world(1601, 8) == 4
-    monkeypatch.setenv("MOCOB200_MIN_POINTS_PER_RANK", "1")
+    assert pkg.lib().mocob200_effective_world(101, 8) == 1 and pkg.lib().mocob200_effective_world(1601, 8) == 8
+    assert pkg.lib().mocob200_effective_world(1601, 32) == 16
+    pkg.lib().mocob200_set_min_points_per_rank(1)
+    try:
+        _check_tiling(pkg)
+    finally:
+        pkg.lib().mocob200_set_min_points_per_rank(0)
+
+
+def _check_tiling(pkg):
+    import ctypes as C
 
     for n_grid in (0, 1, 3, 20, 101, 1601):
         for world in (1, 2, 3, 4, 8):
