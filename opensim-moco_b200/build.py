@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libmocob200.so")
 HOST_SRCS = ["xml_reader.cpp", "host_model.cpp", "osim_flatten.cpp", "examples.cpp", "layout.cpp", "table_opt.cpp", "capi_host.cpp"]
-CUDA_SRCS = ["kernels.cu", "kernels_warp.cu", "capi_device.cu"]
+CUDA_SRCS = ["kernels.cu", "kernels_vel.cu", "kernels_warp.cu", "capi_device.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 

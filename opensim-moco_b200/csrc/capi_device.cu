@@ -73,6 +73,7 @@ struct mocob200_handle {
     std::string err;
     int device = 0, rank = 0, world = 1;
     int eff = 1; // ranks that own grid points (mocob200_effective_world)
+    bool velKernel = true; // thread path: pose-reusing directions through eval_point_vel (MOCOB200_VEL_KERNEL=0: whole evaluations, A-B)
     int mergedBodies = 0; // welded bodies folded into their parents in the device tables
     double* d_Jt = nullptr; // sharded evaluation: time column of every grid point's FD block, gathered to rank 0
     DevLayout DLt{};        // DL with Jt set (rank 0's assembly of the t0 / tf columns)
@@ -191,6 +192,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
         }
     }
     // finite-difference work lists
+    std::vector<int> cwDirs;
     std::vector<int> p0Dirs, p1Dirs, p2Dirs, cdDirs, locDir, locKind, locOwner, locRole, dirClass(L.n_in, 4);
     {
         const char* e = getenv("MOCOB200_FD_LOCAL");
@@ -224,6 +226,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
         }
         for (int d = 0; d < L.n_in; ++d) {
             if (dirClass[d] != 3) cdDirs.push_back(d);
+            if (dirClass[d] != 3 && dirClass[d] != 1) cwDirs.push_back(d);
             if (dirClass[d] == 0) p0Dirs.push_back(d);
             else if (dirClass[d] == 1) p1Dirs.push_back(d);
             else if (dirClass[d] != 3) p2Dirs.push_back(d);
@@ -237,6 +240,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     put(levelStart); put(childStart); put(childList); put(bodyPpStart); put(bodyPpList); put(dofBody); put(bodyFlags);
     put(ppMpp); put(mppPp); put(mppCoord); put(pairI); put(pairJ);
     put(p0Dirs); put(p1Dirs); put(p2Dirs); put(cdDirs); put(locDir); put(locKind); put(locOwner); put(locRole); put(dirClass);
+    put(cwDirs);
     const int* base = devUpload(pool);
     h->owned.push_back((void*)base);
     WarpAux& A = h->WA;
@@ -262,6 +266,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     A.n_cd = (int)cdDirs.size();
     A.loc_dir = base + at[16]; A.loc_kind = base + at[17]; A.loc_owner = base + at[18]; A.loc_role = base + at[19];
     A.dir_class = base + at[20];
+    A.cw_dirs = base + at[21]; A.n_cw = (int)cwDirs.size();
     // staged part of the pools: everything below the bounds block (host-only), plus the goal payload
     {
         int goal0 = T.n_dbl;
@@ -395,8 +400,18 @@ void launchFdKernels(mocob200_handle* h, cudaEvent_t after_nominal) {
         cudaStreamWaitEvent(h->side.s[0], h->side.fork, 0);
         h->launches += 1 + launch_wlocal(h->DT, h->WA, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_cfg, h->p0, h->p1 - h->p0, h->side.s[0]);
         cudaEventRecord(h->side.join[0], h->side.s[0]);
-        launch_points_fd_flat(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream, h->WA.cd_dirs, h->WA.n_cd);
-        h->launches++;
+        if (h->velKernel && h->WA.n_p1 > 0 && h->side.s[1]) {
+            // pose-reusing directions on their own (lighter) kernel beside the whole-evaluation ones
+            cudaStreamWaitEvent(h->side.s[1], h->side.fork, 0);
+            launch_points_fd_vel(h->DT, h->WA, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_cfg, h->p0, h->p1 - h->p0, h->side.s[1]);
+            cudaEventRecord(h->side.join[1], h->side.s[1]);
+            launch_points_fd_flat(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream, h->WA.cw_dirs, h->WA.n_cw);
+            h->launches += 2;
+            cudaStreamWaitEvent(h->stream, h->side.join[1], 0);
+        } else {
+            launch_points_fd_flat(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream, h->WA.cd_dirs, h->WA.n_cd);
+            h->launches++;
+        }
         cudaStreamWaitEvent(h->stream, h->side.join[0], 0);
     } else {
         launch_points_fd(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->p0, h->p1 - h->p0, h->stream);
@@ -680,6 +695,7 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
             for (int k = 0; k < 3; ++k) { h->runs[6 * r + 2 * k] = L.colptr[c0[k]]; h->runs[6 * r + 2 * k + 1] = L.colptr[c1[k]]; }
         }
     }
+    { const char* e = getenv("MOCOB200_VEL_KERNEL"); h->velKernel = !(e && e[0] == '0'); }
     h->allowGraph = !(getenv("MOCOB200_GRAPH") && getenv("MOCOB200_GRAPH")[0] == '0') && !getenv("MOCOB200_TIMING");
     if (h->eff > 1) { // a communicator only when more than one rank owns grid points
         if (!nccl_unique_id) return fail(MOCOB200_ERR_ARG, "world > 1 needs a NCCL unique id");
@@ -1143,7 +1159,8 @@ int mocob200_executed_evals(const mocob200_handle* h, long out[4]) {
         out[2] = N * per * A.n_p2;
         out[3] = A.n_local > 0 ? N : 0;
     } else if (A.n_local > 0 && h->side.s[0]) {
-        out[0] = N * (1 + per * A.n_cd); // the thread kernels evaluate every non-local direction whole
+        if (h->velKernel && A.n_p1 > 0 && h->side.s[1]) { out[0] = N * (1 + per * A.n_cw); out[1] = N * per * A.n_p1; }
+        else out[0] = N * (1 + per * A.n_cd); // the thread kernels evaluate every non-local direction whole
         out[3] = N;
     } else {
         out[0] = N * (1 + per * L.n_in);

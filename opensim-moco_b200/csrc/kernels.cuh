@@ -54,6 +54,10 @@ void launch_points_fd(const DevTables& T, const DevLayout& L, const FdSettings& 
 // one thread per (grid point, listed direction); Y must already hold the nominal outputs
 void launch_points_fd_flat(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* d_x, const double* d_Y, double* d_J,
                            int p0, int np, cudaStream_t s, const int* d_dirs, int ndirs);
+// the pose-reusing directions (WarpAux::p1_dirs: speeds, implicit-mode accelerations), one thread per (point, direction[, side]);
+// d_Y and the blobs in d_cfg come from launch_wpoints_nominal (kernels_vel.cu)
+void launch_points_fd_vel(const DevTables& T, const WarpAux& A, const DevLayout& L, const FdSettings& fd, const double* d_x, const double* d_Y,
+                          double* d_J, const double* d_cfg, int p0, int np, cudaStream_t s);
 // the columns of the "local" inputs (point_warp_local.cuh) for callers that difference the other inputs with
 // launch_points_fd_flat: the local-column kernel on stream s; d_Y and the blobs in d_cfg come from launch_wpoints_nominal
 int launch_wlocal(const DevTables& T, const WarpAux& A, const DevLayout& L, const FdSettings& fd, const double* d_x, double* d_Y,

@@ -48,6 +48,7 @@ struct WarpAux {
     int n_p0, n_p1, n_p2, n_cd, n_local, time_integrands_only;
     const int* p0_dirs; const int* p1_dirs; const int* p2_dirs;
     const int* cd_dirs; // every non-local direction (central scheme, thread-per-evaluation kernel)
+    const int* cw_dirs; int n_cw; // the non-local directions that need whole evaluations (cd_dirs without p1_dirs)
     const int* loc_dir; const int* loc_kind; const int* loc_owner; const int* loc_role;
     const int* dir_class;
     int o_mlen, o_mspd, o_mout, o_Rm;

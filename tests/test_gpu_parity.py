@@ -560,3 +560,30 @@ def test_pinned_host_buffer_receives_the_same_values(pkg, name):
             b.fill_(float("nan"))
             ev.eval_jac_g_ptr(xp[k].data_ptr(), b.data_ptr())
             assert np.array_equal(b.numpy(), pageable[k]), (k,)
+
+
+@pytest.mark.parametrize("name", ["gait2d_prediction", "gait2d_tracking", "hanging_muscle", "pendulum3_implicit", "pendulum2"])
+@pytest.mark.parametrize("fd", [FD_FORWARD, FD_CENTRAL])
+def test_pose_reusing_thread_evaluation_matches_the_whole_evaluation(pkg, orc, name, fd, monkeypatch):
+    """Thread path: the speed (and implicit-mode acceleration) directions go through eval_point_vel, which reads the nominal
+    poses, path geometry and mass-matrix factor of the grid point from the blob of the nominal warp evaluation instead of
+    recomputing them. Same function, so with a round-off-negligible fixed step the columns agree with whole evaluations
+    (MOCOB200_VEL_KERNEL=0) and with the oracle to 1e-7 of the row scale."""
+    monkeypatch.setenv("MOCOB200_KERNEL", "thread")
+    monkeypatch.setenv("MOCOB200_GRAPH", "0")
+    p = load(pkg, name, 3)
+    x = p.make_iterate(seed=21, spread=0.4)
+    h = 1e-4 if fd == FD_FORWARD else 1e-3
+    out = {}
+    for vel in ("1", "0"):
+        monkeypatch.setenv("MOCOB200_VEL_KERNEL", vel)
+        ev = pkg.Evaluator(p)
+        ev.set_fd(fd, h, 0)
+        out[vel] = ev.eval_points(x, jacobian=True)
+    o = orc.Oracle(p)
+    o.set_fd(fd, h, 0)
+    _, Jo = o.eval_point_jacobians(x)
+    scale = np.abs(Jo).max(axis=2, keepdims=True) + 1e-300
+    assert np.array_equal(np.isnan(out["1"]), np.isnan(out["0"]))
+    assert np.nanmax(np.abs(out["1"] - out["0"]) / scale) < 1e-8
+    assert np.nanmax(np.abs(out["1"] - Jo) / scale) < 1e-7
