@@ -98,6 +98,8 @@ enum { MOCOB200_POINTS_OUTPUTS = 0 /* [n_grid][n_out] */, MOCOB200_POINTS_JACOBI
 #define MOCOB200_PPOLY_ISTRIDE 3    /* first break offset (rel. o_ppoly_data) | n pieces | order (coeffs per piece) */
 #define MOCOB200_CJ_DSTRIDE 30      /* 6 x { axis(3) | c0 | c1 } : rotation1..3 then translation1..3 (SpatialTransform.cpp:168-176) */
 #define MOCOB200_CJ_ISTRIDE 18      /* 6 x { function kind | q index driving it (-1: constant) | spline id (MOCOB200_FN_SIMMSPLINE) } */
+#define MOCOB200_CC_ISTRIDE 4       /* function kind (MOCOB200_FN_*) | independent q | dependent q | spline id */
+#define MOCOB200_CC_DSTRIDE 2       /* c0 c1 of the linear / constant function, scale_factor folded in (splines carry it in their record) */
 #define MOCOB200_XFORCE_ISTRIDE 12  /* applied body | force-expressed-in body (-1 ground) | point-expressed-in body | 9 ppoly ids: force xyz, point xyz, torque xyz (-1 = none) */
 
 /* A fixed-topology model + optimal control problem flattened into two pools.
@@ -126,7 +128,12 @@ typedef struct mocob200_tables {
     int o_body_cj;   /* idx[nb]: custom-joint record of body b, or -1 (valid when ncustom > 0) */
     int nxforce;     /* ExternalForce components (Model/ExternalForce.cpp:330-355): functions of time applied to a body */
     int o_xforce_i;
-    int reserved[10];
+    /* kinematic constraints: CoordinateCouplerConstraints (SimbodyEngine/CoordinateCouplerConstraint.cpp:40-237 ->
+     * SimTK::Constraint::CoordinateCoupler): one holonomic equation each, error = scale f(q_independent) - q_dependent, one
+     * Lagrange multiplier each (and one velocity-correction slack each with enforce_constraint_derivatives + Hermite-Simpson) */
+    int ncoupler;
+    int o_cc_i, o_cc_d;
+    int reserved[7];
 } mocob200_tables;
 
 /* Solver-side settings: mirrors the properties of MocoDirectCollocationSolver /
@@ -155,11 +162,12 @@ typedef struct mocob200_transcription {
 
 typedef struct mocob200_dims {
     int n_grid, n_mesh, n_var, n_con, nnz_jac;
-    int ns, nc, nd, n_in, n_out;       /* point function: n_in = 1+ns+nc+nd ; n_out = nu + nz + n_auxres + n_integrands */
+    int ns, nc, nd, n_in, n_out;       /* point function: n_in = 1+ns+nc+nm+nd ; n_out = nu + nz + n_auxres + n_kc + n_integrands */
     int n_dyn_out, n_integrand;
     int n_cost_terms;
     int first_interval, n_intervals_local; /* this rank's shard of mesh intervals */
     int rank, world;
+    int nm, nsl, n_kc;                 /* multipliers per grid point, slacks per interior point, kinematic-constraint equations per mesh point */
 } mocob200_dims;
 
 typedef struct mocob200_handle mocob200_handle;
@@ -177,7 +185,7 @@ int mocob200_problem_load(const char* path, mocob200_problem** out, char* err, i
 /* options (may be NULL) override the stored transcription: "num_mesh_intervals=800;fd_scheme=central;..." */
 int mocob200_problem_load_opts(const char* path, const char* options, mocob200_problem** out, char* err, int errlen);
 int mocob200_problem_save(const mocob200_problem*, const char* path);
-/* '\n'-joined names in NLP order; which = 0 states, 1 controls, 2 auxiliary derivative variables */
+/* '\n'-joined names in NLP order; which = 0 states, 1 controls, 2 auxiliary derivative variables, 3 multipliers, 4 slacks */
 int mocob200_problem_names(const mocob200_problem*, int which, char* buf, int buflen);
 const mocob200_tables* mocob200_problem_tables(const mocob200_problem*);
 const mocob200_transcription* mocob200_problem_transcription(const mocob200_problem*);

@@ -35,7 +35,7 @@ ABI_SYMBOLS = [
 class Dims(C.Structure):
     _fields_ = [(n, C.c_int) for n in (
         "n_grid n_mesh n_var n_con nnz_jac ns nc nd n_in n_out n_dyn_out n_integrand n_cost_terms "
-        "first_interval n_intervals_local rank world").split()]
+        "first_interval n_intervals_local rank world nm nsl n_kc").split()]
 
     def asdict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

@@ -204,7 +204,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
                 k != MOCOB200_GOAL_SUM_SQUARED_STATE && k != MOCOB200_GOAL_CONTROL_TRACKING)
                 local = false; // an integrand this analysis does not know
         }
-        const int ns = 2 * nq + T.nz, iz = 1 + 2 * nq, ic = 1 + ns, ider = 1 + ns + T.nc, iaux = ider + (L.implicit ? nq : 0);
+        const int ns = 2 * nq + T.nz, iz = 1 + 2 * nq, ic = 1 + ns, ider = 1 + ns + T.nc + L.nm, iaux = ider + (L.implicit ? nq : 0);
         for (int d = 0; d < L.n_in; ++d) {
             if (d >= 1 && d <= nq) { dirClass[d] = 0; continue; }
             if ((d > nq && d <= 2 * nq) || (L.implicit && d >= ider && d < ider + nq)) { dirClass[d] = 1; continue; }
@@ -589,6 +589,8 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     D.o_spline_i = T->o_spline_i; D.o_goal_i = T->o_goal_i; D.o_ppoly_i = T->o_ppoly_i;
     D.ncustom = T->ncustom; D.o_cj_d = T->o_cj_d; D.o_cj_i = T->o_cj_i; D.o_body_cj = T->o_body_cj;
     D.nxforce = T->nxforce; D.o_xforce_i = T->o_xforce_i;
+    D.ncoupler = T->ncoupler; D.o_cc_i = T->o_cc_i; D.o_cc_d = T->o_cc_d;
+    D.nm = L.nm; D.n_kc = L.n_kc; D.enforce_derivs = L.enforce_derivs;
     D.implicit = L.implicit; D.n_auxres = L.n_auxres; D.n_integrand = L.n_integrand;
     // layout
     DevLayout& G = h->DL;
@@ -596,6 +598,8 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     G.n_auxres = L.n_auxres; G.n_integrand = L.n_integrand; G.n_dyn_out = L.n_dyn_out; G.n_out = L.n_out;
     G.n_mesh = L.n_mesh; G.n_grid = L.n_grid; G.n_intervals = L.n_intervals; G.n_var = L.n_var; G.n_con = L.n_con; G.nnz = L.nnz;
     G.off_states = L.off_states; G.off_controls = L.off_controls; G.off_derivs = L.off_derivs;
+    G.nm = L.nm; G.nsl = L.nsl; G.n_kc = L.n_kc; G.off_mult = L.off_mult; G.off_slacks = L.off_slacks;
+    G.minimize_mult = (L.nm > 0 && R->minimize_lagrange_multipliers) ? 1 : 0; G.mult_weight = R->lagrange_multiplier_weight;
     G.n_endpoint_rows = L.n_endpoint_rows; G.n_resid_rows_per_point = L.n_resid_rows_per_point; G.n_defect_rows = L.n_defect_rows;
     G.n_interp_rows = L.n_interp_rows; G.n_ein = L.n_ein; G.n_cost_terms = L.n_cost_terms;
     G.minimize_accel = R->minimize_accelerations; G.minimize_auxderiv = R->minimize_auxiliary_derivatives;
@@ -973,7 +977,7 @@ static bool jacPipelineSharded(mocob200_handle* h, double* d_vals) {
 }
 
 static bool jacPipelineLaunches(mocob200_handle* h, double* d_vals) {
-    if (h->eff > 1 && !h->ecHasIntegrand) return jacPipelineSharded(h, d_vals);
+    if (h->eff > 1 && !h->ecHasIntegrand && h->L.nm == 0) return jacPipelineSharded(h, d_vals);
     bool deferred = false;
     if (!runFd(h, !h->ecHasIntegrand, &deferred)) return false;
     if (h->rank == 0) {

@@ -233,7 +233,8 @@ int mocob200_iterate_read_sto(const mocob200_problem* p, const char* path, doubl
 
 int mocob200_problem_names(const mocob200_problem* p, int which, char* buf, int buflen) {
     if (!p || !buf) return MOCOB200_ERR_ARG;
-    const auto& v = which == 0 ? p->fp->stateNames : which == 1 ? p->fp->controlNames : p->fp->derivativeNames;
+    const auto& v = which == 0 ? p->fp->stateNames : which == 1 ? p->fp->controlNames : which == 2 ? p->fp->derivativeNames
+                    : which == 3 ? p->fp->multiplierNames : p->fp->slackNames;
     std::string s;
     for (auto& n : v) { s += n; s += '\n'; }
     std::snprintf(buf, (size_t)buflen, "%s", s.c_str());
@@ -244,6 +245,7 @@ static void fillDims(const Layout& L, mocob200_dims* d) {
     std::memset(d, 0, sizeof *d);
     d->n_grid = L.n_grid; d->n_mesh = L.n_mesh; d->n_var = L.n_var; d->n_con = L.n_con; d->nnz_jac = L.nnz;
     d->ns = L.ns; d->nc = L.nc; d->nd = L.nd; d->n_in = L.n_in; d->n_out = L.n_out;
+    d->nm = L.nm; d->nsl = L.nsl; d->n_kc = L.n_kc;
     d->n_dyn_out = L.n_dyn_out; d->n_integrand = L.n_integrand; d->n_cost_terms = L.n_cost_terms;
     d->first_interval = 0; d->n_intervals_local = L.n_intervals; d->rank = 0; d->world = 1;
 }

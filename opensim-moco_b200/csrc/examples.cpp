@@ -344,6 +344,114 @@ std::unique_ptr<FlatProblem> gaitPrediction(const std::string& dir, const std::s
     return flatten(P, S);
 }
 
+// "Planar point mass with CoordinateCouplerConstraint" (Moco/Tests/testConstraints.cpp:1371-1416; model
+// ModelFactory::createPlanarPointMass, ModelFactory.cpp:91-132): the coupler ty = tx makes the multiplier 0.5 (Fx - Fy).
+std::unique_ptr<FlatProblem> planarPointMassCoupler(const std::string& options) {
+    Problem P;
+    ModelSpec& M = P.model;
+    M.name = "planar_point_mass";
+    M.gravity = Vec3();
+    BodySpec intermed, body;
+    intermed.name = "intermed";
+    intermed.mass = 0;
+    body.name = "body";
+    body.mass = 1;
+    M.bodies = {intermed, body};
+    JointSpec jx, jy;
+    jx.name = "tx";
+    jx.kind = MOCOB200_JOINT_SLIDER;
+    jx.parent.body = -1;
+    jx.child.body = 0;
+    jx.coords.push_back({"tx", -10, 10});
+    jy.name = "ty"; // the joint's x axis points in the global +y direction
+    jy.kind = MOCOB200_JOINT_SLIDER;
+    jy.parent.body = 0;
+    jy.child.body = 1;
+    jy.parent.X.R = rotXYZ(0, 0, 0.5 * kPi);
+    jy.child.X.R = rotXYZ(0, 0, 0.5 * kPi);
+    jy.coords.push_back({"ty", -10, 10});
+    M.joints = {jx, jy};
+    const char* names[2] = {"force_x", "force_y"};
+    const char* coords[2] = {"tx", "ty"};
+    for (int k = 0; k < 2; ++k) {
+        CoordActSpec a;
+        a.path = std::string("/forceset/") + names[k];
+        a.coord = coords[k];
+        M.coordActs.push_back(a);
+        M.actuatorOrder.emplace_back(0, k);
+    }
+    CouplerSpec c;
+    c.name = "coupler";
+    c.independent = "tx";
+    c.dependent = "ty";
+    c.fn.fnKind = MOCOB200_FN_LINEAR;
+    c.fn.c0 = 1.0;
+    c.fn.c1 = 0.0;
+    M.couplers.push_back(c);
+    P.setTimeBounds(Bounds(0), Bounds(1));
+    P.setStateInfo("/jointset/tx/tx/value", Bounds(-5, 5), Bounds(0), Bounds(3));
+    P.setStateInfo("/jointset/tx/tx/speed", Bounds(-5, 5), Bounds(0), Bounds(0));
+    P.setControlInfo("/forceset/force_x", Bounds(0.5));
+    P.addGoal(MOCOB200_GOAL_CONTROL, "effort");
+    SolverSettings S;
+    S.num_mesh_intervals = 10;
+    S.enforce_constraint_derivatives = true;
+    S.applyOptions(options);
+    return flatten(P, S);
+}
+
+// testDoublePendulumCoordinateCoupler (Moco/Tests/testConstraints.cpp:620-693; model createDoublePendulumModel :391-440):
+// q1 = -2 q0 + pi, boundary conditions on q0 only, multipliers minimised with weight 10.
+std::unique_ptr<FlatProblem> doublePendulumCoupler(const std::string& options) {
+    Problem P;
+    ModelSpec& M = P.model;
+    M.name = "double_pendulum";
+    for (int i = 0; i < 2; ++i) {
+        const std::string is = std::to_string(i);
+        BodySpec b;
+        b.name = "b" + is;
+        b.mass = 1;
+        b.inertiaCom[0] = b.inertiaCom[1] = b.inertiaCom[2] = 1;
+        M.bodies.push_back(b);
+        JointSpec j;
+        j.name = "j" + is;
+        j.kind = MOCOB200_JOINT_PIN;
+        j.parent.body = i - 1;
+        j.child.body = i;
+        j.child.X.p.v[0] = -1;
+        j.coords.push_back({"q" + is, -10, 10});
+        M.joints.push_back(j);
+        CoordActSpec a;
+        a.path = "/tau" + is;
+        a.coord = "q" + is;
+        M.coordActs.push_back(a);
+        M.actuatorOrder.emplace_back(0, i);
+    }
+    CouplerSpec c;
+    c.name = "coupler";
+    c.independent = "q0";
+    c.dependent = "q1";
+    c.fn.fnKind = MOCOB200_FN_LINEAR;
+    c.fn.c0 = -2.0;
+    c.fn.c1 = kPi;
+    M.couplers.push_back(c);
+    P.setTimeBounds(Bounds(0), Bounds(1));
+    P.setStateInfo("/jointset/j0/q0/value", Bounds(-5, 5), Bounds(0), Bounds(kPi / 2));
+    P.setStateInfo("/jointset/j0/q0/speed", Bounds(-10, 10), Bounds(0), Bounds(0));
+    P.setStateInfo("/jointset/j1/q1/value", Bounds(-10, 10));
+    P.setStateInfo("/jointset/j1/q1/speed", Bounds(-5, 5), Bounds(0), Bounds(0));
+    P.setControlInfo("/tau0", Bounds(-50, 50));
+    P.setControlInfo("/tau1", Bounds(-50, 50));
+    P.addGoal(MOCOB200_GOAL_CONTROL, "effort");
+    SolverSettings S;
+    S.num_mesh_intervals = 20;
+    S.enforce_constraint_derivatives = true;
+    S.minimize_lagrange_multipliers = true;
+    S.lagrange_multiplier_weight = 10;
+    S.applyOptions(options);
+    return flatten(P, S);
+}
+
 // Replay model for the reference-held CMC / ID results of opensim-models/Pipelines/Gait10dof18musc/OutputReference
 // (CMC/walk_Setup_CMC.xml): CMC/subject01_metabolics.osim - the variant of subject01.osim (document Version 30000, CustomJoint
 // pelvis and knees; its gluteus maximus path differs) whose path speeds reproduce ResultsCMC/walk_subject_Actuation_speed.sto
@@ -389,6 +497,8 @@ std::unique_ptr<FlatProblem> buildExample(const std::string& name, const std::st
     if (name == "gait2d_tracking") return gaitTracking(dataDir, options);
     if (name == "gait2d_prediction") return gaitPrediction(dataDir, options);
     if (name == "gait10dof_replay") return gait10dofReplay(dataDir, options);
+    if (name == "planar_point_mass_coupler") return planarPointMassCoupler(options);
+    if (name == "double_pendulum_coupler") return doublePendulumCoupler(options);
     throw std::runtime_error("unknown example '" + name + "'");
 }
 

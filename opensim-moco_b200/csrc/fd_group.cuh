@@ -13,8 +13,10 @@ __device__ __forceinline__ void gather_inputs(const DevLayout& L, const double* 
     for (int k = 0; k < L.ns; ++k) in[1 + k] = xs[k];
     const double* xc = x + L.off_controls + (size_t)j * L.nc;
     for (int k = 0; k < L.nc; ++k) in[1 + L.ns + k] = xc[k];
+    const double* xm = x + L.off_mult + (size_t)j * L.nm;
+    for (int k = 0; k < L.nm; ++k) in[1 + L.ns + L.nc + k] = xm[k];
     const double* xd = x + L.off_derivs + (size_t)j * L.nd;
-    for (int k = 0; k < L.nd; ++k) in[1 + L.ns + L.nc + k] = xd[k];
+    for (int k = 0; k < L.nd; ++k) in[1 + L.ns + L.nc + L.nm + k] = xd[k];
 }
 
 // One finite-difference column of one callback group, following CasADi's FiniteDiff

@@ -164,7 +164,16 @@ void validateTables(const mocob200_tables& T) {
     auto dblRange = [&](int off, long n, const char* what) { if (off < 0 || n < 0 || (long)off + n > T.n_dbl) bad(what); };
     auto intRange = [&](int off, long n, const char* what) { if (off < 0 || n < 0 || (long)off + n > T.n_int) bad(what); };
     if (T.nb < 0 || T.nq < 0 || T.nz < 0 || T.nc < 0 || T.nderiv_aux < 0 || T.nmus < 0 || T.npp < 0 || T.nspline < 0 || T.ncontact < 0 ||
-        T.ncact < 0 || T.ngoal < 0 || T.nppoly < 0 || T.ncustom < 0 || T.nxforce < 0) bad("negative count");
+        T.ncact < 0 || T.ngoal < 0 || T.nppoly < 0 || T.ncustom < 0 || T.nxforce < 0 || T.ncoupler < 0) bad("negative count");
+    if (T.ncoupler > 0) {
+        intRange(T.o_cc_i, (long)T.ncoupler * MOCOB200_CC_ISTRIDE, "couplers");
+        dblRange(T.o_cc_d, (long)T.ncoupler * MOCOB200_CC_DSTRIDE, "couplers");
+        for (int k = 0; k < T.ncoupler; ++k) {
+            const int* ci = T.idx + T.o_cc_i + k * MOCOB200_CC_ISTRIDE;
+            if (ci[0] < 0 || ci[0] > MOCOB200_FN_SIMMSPLINE || ci[1] < 0 || ci[1] >= T.nq || ci[2] < 0 || ci[2] >= T.nq || ci[1] == ci[2] ||
+                (ci[0] == MOCOB200_FN_SIMMSPLINE && (ci[3] < 0 || ci[3] >= T.nspline))) bad("coupler record");
+        }
+    }
     dblRange(T.o_body_d, (long)T.nb * MOCOB200_BODY_DSTRIDE, "bodies");
     intRange(T.o_body_i, (long)T.nb * MOCOB200_BODY_ISTRIDE, "bodies");
     dblRange(T.o_gravity, 3, "gravity");
@@ -791,6 +800,25 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
         return it->second;
     };
 
+    // ---- kinematic constraints: coordinate couplers (MocoCasOCProblem.cpp:140-216 names the multipliers lambda_cid<i>_p<k>)
+    std::vector<int> ccI;
+    std::vector<double> ccD;
+    for (size_t k = 0; k < M.couplers.size(); ++k) {
+        const CouplerSpec& C = M.couplers[k];
+        const int qi = coordOf(C.independent), qd = coordOf(C.dependent);
+        if (qi == qd) throw std::runtime_error("CoordinateCouplerConstraint '" + C.name + "': dependent == independent coordinate");
+        SplineSpec sp = C.fn.spline;
+        sp.scale *= C.scaleFactor;
+        ccI.push_back(C.fn.fnKind);
+        ccI.push_back(qi);
+        ccI.push_back(qd);
+        ccI.push_back(C.fn.fnKind == MOCOB200_FN_SIMMSPLINE ? addSpline(sp) : -1);
+        ccD.push_back(C.fn.fnKind == MOCOB200_FN_LINEAR ? C.scaleFactor * C.fn.c0 : 0.0);
+        ccD.push_back(C.fn.fnKind == MOCOB200_FN_SIMMSPLINE ? 0.0 : C.scaleFactor * C.fn.c1);
+        fp->multiplierNames.push_back("lambda_cid" + std::to_string(k) + "_p0");
+        fp->slackNames.push_back("gamma_cid" + std::to_string(k) + "_p0");
+    }
+
     // ---- muscles and their path points
     T.nmus = (int)M.muscles.size();
     std::vector<double> ppD, musD;
@@ -890,6 +918,13 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
         T.o_cj_d = (int)D.size(); D.insert(D.end(), cjD.begin(), cjD.end());
         T.o_cj_i = (int)I.size(); I.insert(I.end(), cjI.begin(), cjI.end());
         T.o_body_cj = (int)I.size(); I.insert(I.end(), bodyCj.begin(), bodyCj.end());
+    }
+
+    // ---- kinematic constraints: the coupler records (built before the spline table was written)
+    T.ncoupler = (int)M.couplers.size();
+    if (T.ncoupler > 0) {
+        T.o_cc_i = (int)I.size(); I.insert(I.end(), ccI.begin(), ccI.end());
+        T.o_cc_d = (int)D.size(); D.insert(D.end(), ccD.begin(), ccD.end());
     }
 
     // ---- variable bounds (MocoProblemRep.cpp:300-430 ; CasOCProblem.h:603-606)
@@ -1139,6 +1174,10 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
     // ---- transcription
     std::memset(&fp->tr, 0, sizeof fp->tr);
     applySettingsToTranscription(S, *fp, false);
+    fp->tr.multiplier_bounds[0] = P.multiplierBounds.lo;
+    fp->tr.multiplier_bounds[1] = P.multiplierBounds.hi;
+    if (P.kinematicConstraintBounds.lo != 0 || P.kinematicConstraintBounds.hi != 0)
+        throw std::runtime_error("non-zero kinematic constraint bounds are unsupported");
     fp->rebind();
     return fp;
 }

@@ -123,6 +123,13 @@ struct ExternalForceSpec {
     bool hasForce = false, hasPoint = false, hasTorque = false;
     PiecewisePoly force[3], point[3], torque[3];
 };
+// CoordinateCouplerConstraint (SimbodyEngine/CoordinateCouplerConstraint.cpp): q_dependent = scale_factor * f(q_independent)
+struct CouplerSpec {
+    std::string name;
+    std::string independent, dependent;
+    TransformAxisSpec fn; // kind / c0 / c1 / spline (axis unused)
+    double scaleFactor = 1;
+};
 struct ModelSpec {
     std::string name;
     Vec3 gravity;
@@ -132,6 +139,7 @@ struct ModelSpec {
     std::vector<ContactSpec> contacts;
     std::vector<CoordActSpec> coordActs;
     std::vector<ExternalForceSpec> externalForces;
+    std::vector<CouplerSpec> couplers;
     std::vector<std::pair<int, int>> actuatorOrder; // (0 = coordinate actuator, 1 = muscle ; index) in component order
     ModelSpec() { gravity.v[1] = -9.80665; }
     int bodyIndex(const std::string& n) const;
@@ -212,6 +220,8 @@ struct Problem {
     Bounds timeInitial{0}, timeFinal{1};
     std::map<std::string, VariableInfo> stateInfos, controlInfos;
     Bounds defaultSpeedBounds{-50, 50};
+    Bounds multiplierBounds{-1000, 1000}; // MocoProblem::setMultiplierBounds (MocoProblem.h:197; MocoPhase default)
+    Bounds kinematicConstraintBounds{0, 0}; // MocoProblem::setKinematicConstraintBounds
     bool boundActivationFromExcitation = true;
     std::vector<GoalSpec> goals;
 
@@ -268,7 +278,7 @@ struct FlatProblem {
     std::vector<double> mesh;
     mocob200_tables tables{};
     mocob200_transcription tr{};
-    std::vector<std::string> stateNames, controlNames, derivativeNames;
+    std::vector<std::string> stateNames, controlNames, derivativeNames, multiplierNames, slackNames;
     void rebind(); // re-point tables.dbl/idx and tr.mesh after a copy/load
 };
 

@@ -33,7 +33,7 @@ __global__ void k_paths(DevTables T, DevLayout L, const double* __restrict__ x, 
     const double* u = q + T.nq;
     const double* z = u + T.nq;
     const double* ctl = z + T.nz;
-    const double* auxder = ctl + T.nc + (T.implicit ? T.nq : 0);
+    const double* auxder = ctl + T.nc + T.nm + (T.implicit ? T.nq : 0);
     Scratch S;
     kinematics(T, q, u, S);
     double ls[2];
@@ -133,7 +133,7 @@ __global__ void k_integrals(DevLayout L, const double* __restrict__ x, const dou
 __device__ inline bool endpoint_reads(const DevTables& T, const DevLayout& L, int g, int a) {
     const int* gr = T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
     const int* ip = T.idx + gr[4];
-    const int half = 1 + L.ns + L.nc + L.nd;
+    const int half = 1 + L.ns + L.nc + L.nm + L.nd;
     const bool isIntegral = a == 2 * half;
     const int side = a >= half ? 1 : 0;          // 0 = initial, 1 = final
     const int k = isIntegral ? -1 : a - side * half; // 0 = time, 1.. = states, controls, derivatives
@@ -168,7 +168,7 @@ __global__ void k_endpoint(DevTables T, DevLayout L, FdSettings fd, const double
     double* sh_in = sh;
     double* sh_g0 = sh + L.n_ein;
     {   // cooperative gather of [t0, x0, c0, d0, tf, xf, cf, df, integral]
-        const int half = 1 + L.ns + L.nc + L.nd, last = L.n_grid - 1;
+        const int half = 1 + L.ns + L.nc + L.nm + L.nd, last = L.n_grid - 1;
         for (int i = threadIdx.x; i < L.n_ein; i += blockDim.x) {
             double v;
             if (i == 2 * half) v = (L.goal_integrand[g] >= 0) ? I[L.goal_integrand[g]] : NAN; // NaN without an integrand (:495)
@@ -177,7 +177,8 @@ __global__ void k_endpoint(DevTables T, DevLayout L, FdSettings fd, const double
                 if (k == 0) v = x[side];
                 else if (k <= L.ns) v = x[L.off_states + (size_t)j * L.ns + (k - 1)];
                 else if (k <= L.ns + L.nc) v = x[L.off_controls + (size_t)j * L.nc + (k - 1 - L.ns)];
-                else v = x[L.off_derivs + (size_t)j * L.nd + (k - 1 - L.ns - L.nc)];
+                else if (k <= L.ns + L.nc + L.nm) v = x[L.off_mult + (size_t)j * L.nm + (k - 1 - L.ns - L.nc)];
+                else v = x[L.off_derivs + (size_t)j * L.nd + (k - 1 - L.ns - L.nc - L.nm)];
             }
             sh_in[i] = v;
         }
@@ -208,12 +209,60 @@ __global__ void k_endpoint(DevTables T, DevLayout L, FdSettings fd, const double
 }
 
 // ---------------------------------------------------------------------------------------------
+// Hermite-Simpson midpoints with enforced constraint derivatives: qdot = u + G(q)^T gamma (CasOCTranscription.cpp:315-332 ->
+// VelocityCorrection::eval CasOCFunction.cpp:286-291 -> MocoCasOCProblem.h:298-332)
+__device__ __forceinline__ bool vel_corrected(const DevLayout& L, int j) { return L.nsl > 0 && L.scheme == MOCOB200_SCHEME_HERMITE_SIMPSON && (j & 1); }
+__device__ inline double velcorr_value(const DevTables& T, const DevLayout& L, const double* x, int j, int s) {
+    return coupler_velocity_correction(T, x + L.off_states + (size_t)j * L.ns, x + L.off_slacks + (size_t)(j / 2) * L.nsl, s);
+}
+// One entry of the FD block of the VelocityCorrection callback at midpoint j: d corr_s / d input a, a = 0 time, 1..2nq the
+// multibody states, then the slacks; CasADi FiniteDiff on that callback (all nq outputs share the refined central step)
+__device__ double velcorr_fd_entry(const DevTables& T, const DevLayout& L, const FdSettings& fd, const double* __restrict__ x, int j, int s, int a) {
+    const int nmb = 2 * L.nq;
+    if (a == 0) return 0.0; // the correction does not read the time: every finite difference of it is exactly zero
+    double in[2 * MOCOB200_MAXQ + 16];
+    const double* xs = x + L.off_states + (size_t)j * L.ns;
+    const double* sl = x + L.off_slacks + (size_t)(j / 2) * L.nsl;
+    for (int k = 0; k < L.nq; ++k) in[k] = xs[k];
+    double* g = in + L.nq;
+    for (int k = 0; k < L.nsl; ++k) g[k] = sl[k];
+    double* slot = a <= L.nq ? in + (a - 1) : (a <= nmb ? nullptr : g + (a - 1 - nmb));
+    if (!slot) return 0.0; // the speeds are inputs the correction does not read
+    const double x0 = *slot;
+    auto at = [&](int ss, double xa) { *slot = xa; const double v = coupler_velocity_correction(T, in, g, ss); *slot = x0; return v; };
+    if (fd.scheme != MOCOB200_FD_CENTRAL) {
+        const bool fwd = fd.scheme == MOCOB200_FD_FORWARD;
+        const double vc = at(s, x0), yf = at(s, fwd ? x0 + fd.h : x0 - fd.h);
+        return fwd ? (yf - vc) / fd.h : (vc - yf) / fd.h;
+    }
+    double h = fd.h, jv = 0;
+    for (int iter = 0;; ++iter) {
+        double u = 0;
+        for (int ss = 0; ss < L.nq; ++ss) {
+            const double vb = at(ss, x0 - h), vf = at(ss, x0 + h), vc = at(ss, x0);
+            double je;
+            if (!isfinite(vf) || !isfinite(vc) || !isfinite(vb)) { je = NAN; u = -1; }
+            else {
+                je = (vf - vb) / (2 * h);
+                const double et = vf - 2 * vc + vb;
+                const double er = fd.reltol / h * fmax(fabs(vf - vc), fabs(vc - vb)) + fd.abstol;
+                if (u >= 0) u = fmax(u, fabs(et / er));
+            }
+            if (ss == s) jv = je;
+        }
+        if (iter == fd.h_iter) break;
+        if (u < 0) h /= fd.u_aim;
+        else h *= sqrt(fd.u_aim / fmax(1.0, u));
+    }
+    return jv;
+}
 __device__ __forceinline__ double xdot_val(const DevLayout& L, const double* x, const double* Y, int j, int s) {
     if (s < L.nq) return x[L.off_states + (size_t)j * L.ns + L.nq + s];                     // qdot = u (:313-314)
     if (s < 2 * L.nq && L.implicit) return x[L.off_derivs + (size_t)j * L.nd + (s - L.nq)]; // udot = w
     return Y[(size_t)j * L.n_out + (s - L.nq)];
 }
 __device__ __forceinline__ double dxdot(const DevLayout& L, const double* J, int j, int s, const ColMetaD& c) {
+    if (c.kind == COL_SLACK_D) return 0.0; // enters through the velocity correction only (k_assemble_jac_velcorr)
     if (s < L.nq) return (c.kind == COL_STATE_D && c.k == L.nq + s) ? 1.0 : 0.0;
     if (s < 2 * L.nq && L.implicit) return (c.kind == COL_DERIV_D && c.k == s - L.nq) ? 1.0 : 0.0;
     return J[((size_t)j * L.n_out + (s - L.nq)) * L.n_in + c.in];
@@ -325,7 +374,7 @@ __global__ void k_assemble_g(DevLayout L, const double* __restrict__ x, const do
     const bool hs = L.scheme == MOCOB200_SCHEME_HERMITE_SIMPSON;
     double v = 0;
     if (rm.kind == ROW_ENDPOINT_D) v = G[L.goal_eoff[rm.a] + rm.b];
-    else if (rm.kind == ROW_RESIDUAL_D) v = Y[(size_t)rm.a * L.n_out + rm.b];
+    else if (rm.kind == ROW_RESIDUAL_D || rm.kind == ROW_KINEMATIC_D) v = Y[(size_t)rm.a * L.n_out + rm.b];
     else if (rm.kind == ROW_PATH_D) return; // k_assemble_g_path
     else if (rm.kind == ROW_INTERP_D) {
         const int m = rm.a, c = rm.b;
@@ -363,6 +412,17 @@ __global__ void k_assemble_f(DevTables T, DevLayout L, const double* __restrict_
         total += s;
     }
     const double dur = x[1] - x[0];
+    if (L.minimize_mult) { // lagrange_multiplier_weight * duration * sum_j quad_j |lambda_j|^2 (CasOCTranscription.cpp:513-521)
+        double acc = 0;
+        for (int j = 0; j < L.n_grid; ++j) {
+            double sq = 0;
+            for (int k = 0; k < L.nm; ++k) { const double d = x[L.off_mult + (size_t)j * L.nm + k]; sq += d * d; }
+            acc += L.quad[j] * sq;
+        }
+        const double s = L.mult_weight * dur * acc;
+        f[1 + term++] = s;
+        total += s;
+    }
     for (int which = 0; which < 2; ++which) {
         const bool on = which == 0 ? (L.minimize_accel && L.implicit) : (L.minimize_auxderiv && L.n_auxres > 0);
         if (!on) continue;
@@ -384,11 +444,12 @@ __global__ void k_assemble_f(DevTables T, DevLayout L, const double* __restrict_
 __device__ __forceinline__ double endpoint_entry(const DevLayout& L, const double* x, const double* J, const double* I, const double* E,
                                                  int g, int o, const ColMetaD& c) {
     const double* Er = E + (size_t)(L.goal_eoff[g] + o) * L.n_ein;
-    const int half = 1 + L.ns + L.nc + L.nd;
+    const int half = 1 + L.ns + L.nc + L.nm + L.nd;
     const int slot = L.goal_integrand[g];
     const double dGdI = slot >= 0 ? Er[L.n_ein - 1] : 0.0;
     if (c.kind == COL_T0_D) return Er[0] + (slot >= 0 ? dGdI * I[L.n_integrand + slot] : 0.0);
     if (c.kind == COL_TF_D) return Er[half] + (slot >= 0 ? dGdI * I[2 * L.n_integrand + slot] : 0.0);
+    if (c.kind == COL_SLACK_D) return 0.0; // slacks enter through the velocity correction only
     double v = 0;
     if (c.point == 0) v += Er[c.in];
     if (c.point == L.n_grid - 1) v += Er[half + c.in];
@@ -412,7 +473,7 @@ __global__ void k_assemble_jac(DevLayout L, const double* __restrict__ x, const 
     double v = 0;
     if (rm.kind == ROW_ENDPOINT_D) {
         v = endpoint_entry(L, x, J, I, E, rm.a, rm.b, c);
-    } else if (rm.kind == ROW_RESIDUAL_D) {
+    } else if (rm.kind == ROW_RESIDUAL_D || rm.kind == ROW_KINEMATIC_D) {
         const int j = rm.a;
         if (isTime) v = time_col(L, J, j, rm.b) * (c.kind == COL_TF_D ? L.grid[j] : 1.0 - L.grid[j]);
         else v = J[((size_t)j * L.n_out + rm.b) * L.n_in + c.in];
@@ -448,6 +509,36 @@ __global__ void k_assemble_jac(DevLayout L, const double* __restrict__ x, const 
     vals[k] = v;
 }
 
+// Velocity-correction terms of the Simpson defects of the coordinates (launched only for problems with slack variables):
+// defect = x_ip - x_i - h/6 (xdot_ip + 4 xdot_mid + xdot_i) with qdot_mid = u_mid + corr(q_mid, gamma) adds -4h/6 corr.
+__global__ void k_assemble_g_velcorr(DevTables T, DevLayout L, const double* __restrict__ x, double* __restrict__ g) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= L.n_intervals * L.nq) return;
+    const int m = t / L.nq, s = t % L.nq;
+    const double h = (x[1] - x[0]) * (L.mesh[m + 1] - L.mesh[m]);
+    g[L.row_defect[m] + L.ns + s] += -(4.0 / 6.0) * h * velcorr_value(T, L, x, 2 * m + 1, s);
+}
+__global__ void k_assemble_jac_velcorr(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ x, double* __restrict__ vals, int k0, int k1) {
+    const int k = k0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= k1) return;
+    const RowMetaD rm = L.rows[L.rowidx[k]];
+    if (rm.kind != ROW_DEFECT_SIMPSON_D || rm.b >= L.nq) return;
+    const ColMetaD c = L.cols[L.nnzcol[k]];
+    const int m = rm.a, s = rm.b, j = 2 * m + 1;
+    const double dm = L.mesh[m + 1] - L.mesh[m];
+    const double h = (x[1] - x[0]) * dm, wc = -4.0 / 6.0;
+    if (c.kind == COL_T0_D || c.kind == COL_TF_D) { // through h (the correction itself does not read the time)
+        vals[k] += wc * ((c.kind == COL_TF_D) ? dm : -dm) * velcorr_value(T, L, x, j, s);
+        return;
+    }
+    if (c.point != j) return;
+    int a = -1; // input of the VelocityCorrection callback: 0 time, 1..2nq multibody states, then slacks
+    if (c.kind == COL_STATE_D && c.k < 2 * L.nq) a = 1 + c.k;
+    else if (c.kind == COL_SLACK_D) a = 1 + 2 * L.nq + c.k;
+    if (a < 0) return;
+    vals[k] += wc * h * velcorr_fd_entry(T, L, fd, x, j, s, a);
+}
+
 __global__ void k_assemble_grad(DevTables T, DevLayout L, const double* __restrict__ x, const double* __restrict__ Y, const double* __restrict__ J,
                                 const double* __restrict__ I, const double* __restrict__ E, double* __restrict__ grad) {
     const int vi = blockIdx.x * blockDim.x + threadIdx.x;
@@ -460,6 +551,18 @@ __global__ void k_assemble_grad(DevTables T, DevLayout L, const double* __restri
         for (int o = 0; o < gr[2]; ++o) v += endpoint_entry(L, x, J, I, E, g, o, c);
     }
     const double dur = x[1] - x[0];
+    if (L.minimize_mult) {
+        if (c.kind == COL_MULT_D) v += 2.0 * L.mult_weight * dur * L.quad[c.point] * x[vi];
+        if (c.kind == COL_T0_D || c.kind == COL_TF_D) {
+            double acc = 0;
+            for (int j = 0; j < L.n_grid; ++j) {
+                double sq = 0;
+                for (int k = 0; k < L.nm; ++k) { const double d = x[L.off_mult + (size_t)j * L.nm + k]; sq += d * d; }
+                acc += L.quad[j] * sq;
+            }
+            v += (c.kind == COL_TF_D ? 1.0 : -1.0) * L.mult_weight * acc;
+        }
+    }
     for (int which = 0; which < 2; ++which) {
         const bool on = which == 0 ? (L.minimize_accel && L.implicit) : (L.minimize_auxderiv && L.n_auxres > 0);
         if (!on) continue;
@@ -598,6 +701,7 @@ void launch_assemble_g(const DevTables& T, const DevLayout& L, const double* d_x
     if (L.n_con <= 0) return;
     k_assemble_g<<<(L.n_con + 127) / 128, 128, 0, s>>>(L, d_x, d_Y, d_G, d_g);
     if (L.n_path_rows > 0) k_assemble_g_path<<<(L.n_con + 127) / 128, 128, 0, s>>>(T, L, d_x, d_g);
+    if (L.nsl > 0) k_assemble_g_velcorr<<<(L.n_intervals * L.nq + 127) / 128, 128, 0, s>>>(T, L, d_x, d_g);
 }
 void launch_assemble_f(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_G, double* d_f, cudaStream_t s) {
     k_assemble_f<<<1, 32, 0, s>>>(T, L, d_x, d_G, d_f);
@@ -609,6 +713,7 @@ void launch_assemble_jac(const DevTables& T, const DevLayout& L, const FdSetting
     if (n <= 0) return;
     k_assemble_jac<<<(n + 255) / 256, 256, 0, s>>>(L, d_x, d_Y, d_J, d_I, d_E, d_vals, k0, k1);
     if (L.n_path_rows > 0) k_assemble_jac_path<<<(n + 255) / 256, 256, 0, s>>>(T, L, fd, d_x, d_vals, k0, k1);
+    if (L.nsl > 0) k_assemble_jac_velcorr<<<(n + 255) / 256, 256, 0, s>>>(T, L, fd, d_x, d_vals, k0, k1);
 }
 void launch_assemble_grad(const DevTables& T, const DevLayout& L, const double* d_x, const double* d_Y, const double* d_J, const double* d_I,
                           const double* d_E, double* d_grad, cudaStream_t s) {

@@ -20,8 +20,9 @@ struct FdSettings {
     double reltol, abstol;
 };
 
-enum { ROW_ENDPOINT_D = 0, ROW_RESIDUAL_D = 1, ROW_DEFECT_TRAP_D = 2, ROW_DEFECT_HERMITE_D = 3, ROW_DEFECT_SIMPSON_D = 4, ROW_INTERP_D = 5, ROW_PATH_D = 6 };
-enum { COL_T0_D = 0, COL_TF_D = 1, COL_STATE_D = 2, COL_CONTROL_D = 3, COL_DERIV_D = 4 };
+enum { ROW_ENDPOINT_D = 0, ROW_RESIDUAL_D = 1, ROW_DEFECT_TRAP_D = 2, ROW_DEFECT_HERMITE_D = 3, ROW_DEFECT_SIMPSON_D = 4, ROW_INTERP_D = 5, ROW_PATH_D = 6,
+       ROW_KINEMATIC_D = 7 };
+enum { COL_T0_D = 0, COL_TF_D = 1, COL_STATE_D = 2, COL_CONTROL_D = 3, COL_DERIV_D = 4, COL_MULT_D = 5, COL_SLACK_D = 6 };
 struct RowMetaD { int kind, a, b, pad; };
 struct ColMetaD { int kind, point, k, in; };
 
@@ -29,6 +30,8 @@ struct DevLayout {
     int scheme, implicit, nq, nz, ns, nc, nd, n_in, n_auxres, n_integrand, n_dyn_out, n_out;
     int n_mesh, n_grid, n_intervals, n_var, n_con, nnz;
     int off_states, off_controls, off_derivs;
+    int nm, nsl, n_kc, off_mult, off_slacks;   // kinematic constraints: multipliers per point, slacks per midpoint, rows per mesh point
+    int minimize_mult; double mult_weight;
     int n_endpoint_rows, n_resid_rows_per_point, n_defect_rows, n_interp_rows, n_ein, n_cost_terms;
     int minimize_accel, minimize_auxderiv;
     double accel_weight, auxderiv_weight;

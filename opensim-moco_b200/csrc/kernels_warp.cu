@@ -16,8 +16,10 @@ __device__ __forceinline__ void warp_gather_inputs(const DevLayout& L, const dou
     for (int k = lane; k < L.ns; k += 32) in[1 + k] = xs[k];
     const double* xc = x + L.off_controls + (size_t)j * L.nc;
     for (int k = lane; k < L.nc; k += 32) in[1 + L.ns + k] = xc[k];
+    const double* xm = x + L.off_mult + (size_t)j * L.nm;
+    for (int k = lane; k < L.nm; k += 32) in[1 + L.ns + L.nc + k] = xm[k];
     const double* xd = x + L.off_derivs + (size_t)j * L.nd;
-    for (int k = lane; k < L.nd; k += 32) in[1 + L.ns + L.nc + k] = xd[k];
+    for (int k = lane; k < L.nd; k += 32) in[1 + L.ns + L.nc + L.nm + k] = xd[k];
     __syncwarp();
 }
 
@@ -89,7 +91,7 @@ __device__ __forceinline__ void blob_load(const WarpAux& A, double* ws, const do
 __device__ __forceinline__ int reuse_level(const DevLayout& L, int dir) {
     if (dir >= 1 && dir <= L.nq) return 0;
     if (dir > L.nq && dir <= 2 * L.nq) return 1;
-    if (L.implicit && dir >= 1 + L.ns + L.nc && dir < 1 + L.ns + L.nc + L.nq) return 1;
+    if (L.implicit && dir >= 1 + L.ns + L.nc + L.nm && dir < 1 + L.ns + L.nc + L.nm + L.nq) return 1;
     return 2;
 }
 

@@ -16,7 +16,14 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
     L.implicit = R.dynamics_mode == MOCOB200_DYNAMICS_IMPLICIT;
     L.nq = T.nq; L.nz = T.nz; L.ns = 2 * T.nq + T.nz; L.nc = T.nc;
     L.nd = (L.implicit ? T.nq : 0) + T.nderiv_aux;
-    L.n_in = 1 + L.ns + L.nc + L.nd;
+    const bool hsScheme = R.scheme == MOCOB200_SCHEME_HERMITE_SIMPSON;
+    // kinematic constraints (CasOCProblem.h:473-524): one multiplier per holonomic equation; with enforce_constraint_derivatives
+    // the velocity- and acceleration-level equations are rows too and every Hermite-Simpson midpoint gets one slack per equation
+    L.nm = T.ncoupler;
+    L.enforce_derivs = (L.nm > 0 && R.enforce_constraint_derivatives) ? 1 : 0;
+    L.n_kc = L.enforce_derivs ? 3 * L.nm : L.nm;
+    L.nsl = (L.enforce_derivs && hsScheme) ? L.nm : 0;
+    L.n_in = 1 + L.ns + L.nc + L.nm + L.nd;
     L.n_auxres = T.nderiv_aux;
     L.goal_integrand.assign(T.ngoal, -1);
     L.goal_row.assign(T.ngoal, -1);
@@ -30,9 +37,10 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
         else L.n_cost_terms++;
     }
     // endpoint constraints come first in goal order among themselves (createEndpointConstraintNames)
+    if (L.nm && R.minimize_lagrange_multipliers) L.n_cost_terms++;
     if (L.implicit && R.minimize_accelerations) L.n_cost_terms++;
     if (L.n_auxres && R.minimize_auxiliary_derivatives) L.n_cost_terms++;
-    L.n_dyn_out = L.nq + L.nz + L.n_auxres;
+    L.n_dyn_out = L.nq + L.nz + L.n_auxres + L.n_kc;
     L.n_out = L.n_dyn_out + L.n_integrand;
     L.n_mesh = R.n_mesh;
     if (L.n_mesh < 2) throw std::runtime_error("need at least one mesh interval");
@@ -58,12 +66,16 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
             L.quad[m + 1] += 0.5 * dm;
         }
     }
-    // variables: t0, tf, vec(states), vec(controls), [multipliers, slacks: none], vec(derivatives), [parameters: none]
+    // variables: t0, tf, vec(states), vec(controls), vec(multipliers), vec(slacks at the interior points), vec(derivatives),
+    // [parameters: none]  (CasOCIterate.h:28-45 enum order, CasOCTranscription.h:192-199)
+    const int nInterior = L.n_grid - L.n_mesh;
     L.off_states = 2;
     L.off_controls = L.off_states + L.ns * L.n_grid;
-    L.off_derivs = L.off_controls + L.nc * L.n_grid;
+    L.off_mult = L.off_controls + L.nc * L.n_grid;
+    L.off_slacks = L.off_mult + L.nm * L.n_grid;
+    L.off_derivs = L.off_slacks + L.nsl * nInterior;
     L.n_var = L.off_derivs + L.nd * L.n_grid;
-    L.n_ein = 2 + 2 * (L.ns + L.nc + L.nd) + 1;
+    L.n_ein = 2 + 2 * (L.ns + L.nc + L.nm + L.nd) + 1;
     // constraints
     L.n_resid_rows_per_point = (L.implicit ? L.nq : 0) + L.n_auxres;
     L.n_defect_rows = (hs ? 2 : 1) * L.ns;
@@ -72,14 +84,17 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
     L.row_defect.assign(L.n_intervals, -1);
     L.row_interp.assign(L.n_intervals, -1);
     L.row_path.assign(L.n_mesh, -1);
+    L.row_kin.assign(L.n_mesh, -1);
     int row = L.n_endpoint_rows;
     const int ppi = hs ? 2 : 1; // grid points whose residuals are grouped with interval m
     for (int m = 0; m < L.n_intervals; ++m) {
-        L.row_path[m] = row; row += L.n_path_rows; // [kinematic: none,] path constraints of mesh point m first
+        L.row_kin[m] = row; row += L.n_kc;         // kinematic constraints of mesh point m, then its path constraints (CasOCTranscription.h:279-283)
+        L.row_path[m] = row; row += L.n_path_rows;
         for (int k = 0; k < ppi; ++k) { L.row_resid[ppi * m + k] = row; row += L.n_resid_rows_per_point; }
         L.row_defect[m] = row; row += L.n_defect_rows;
         L.row_interp[m] = row; row += L.n_interp_rows;
     }
+    L.row_kin[L.n_mesh - 1] = row; row += L.n_kc;
     L.row_path[L.n_mesh - 1] = row; row += L.n_path_rows;
     L.row_resid[L.n_grid - 1] = row; row += L.n_resid_rows_per_point;
     L.n_con = row;
@@ -92,6 +107,8 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
             for (int im = 0; im < L.n_mesh; ++im)
                 for (int e = 0; e < goalRec(T, g)[2]; ++e)
                     L.rows[L.row_path[im] + L.goal_path_off[g] + e] = RowMeta{ROW_PATH, hs ? 2 * im : im, e, g};
+    for (int im = 0; im < L.n_mesh; ++im)
+        for (int e = 0; e < L.n_kc; ++e) L.rows[L.row_kin[im] + e] = RowMeta{ROW_KINEMATIC, hs ? 2 * im : im, L.nq + L.nz + L.n_auxres + e, 0};
     for (int j = 0; j < L.n_grid; ++j)
         for (int o = 0; o < L.n_resid_rows_per_point; ++o) {
             // out rows: implicit multibody residual [0,nq) then aux residuals at [nq+nz, ...)
@@ -114,8 +131,11 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
     for (int j = 0; j < L.n_grid; ++j) {
         for (int k = 0; k < L.ns; ++k) L.cols[L.off_states + j * L.ns + k] = ColMeta{COL_STATE, j, k, 1 + k};
         for (int k = 0; k < L.nc; ++k) L.cols[L.off_controls + j * L.nc + k] = ColMeta{COL_CONTROL, j, k, 1 + L.ns + k};
-        for (int k = 0; k < L.nd; ++k) L.cols[L.off_derivs + j * L.nd + k] = ColMeta{COL_DERIV, j, k, 1 + L.ns + L.nc + k};
+        for (int k = 0; k < L.nm; ++k) L.cols[L.off_mult + j * L.nm + k] = ColMeta{COL_MULT, j, k, 1 + L.ns + L.nc + k};
+        for (int k = 0; k < L.nd; ++k) L.cols[L.off_derivs + j * L.nd + k] = ColMeta{COL_DERIV, j, k, 1 + L.ns + L.nc + L.nm + k};
     }
+    for (int i = 0; i < nInterior; ++i)
+        for (int k = 0; k < L.nsl; ++k) L.cols[L.off_slacks + i * L.nsl + k] = ColMeta{COL_SLACK, 2 * i + 1, k, -1};
     if (!withStructure) { L.nnz = -1; return L; }
 
     // ---- CSC structure with CasADi's dense point-function blocks (optim_sparsity_detection "none")
@@ -130,6 +150,8 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
     auto residOutRow = [&](int o) { return (L.implicit && o < L.nq) ? o : L.nq + L.nz + (o - (L.implicit ? L.nq : 0)); };
     // does xdot_s (state s) at a point depend on input `in` of the same point?
     auto xdotDepends = [&](int s, const ColMeta& c) -> bool {
+        if (s < L.nq && L.nsl > 0 && hs && c.point % 2 == 1 && c.kind == COL_STATE && c.k < 2 * L.nq)
+            return true; // qdot_mid = u_mid + velocity correction(multibody states of the midpoint, slacks): dense callback block
         if (s < L.nq) return c.kind == COL_STATE && c.k == L.nq + s; // qdot = u
         if (s < 2 * L.nq && L.implicit) return c.kind == COL_DERIV && c.k == s - L.nq; // udot = w
         return maskAt(s - L.nq, c.in); // the callback block: dense unless a detected mask is given
@@ -144,6 +166,8 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
         if (c.kind == COL_T0 || c.kind == COL_TF) {
             for (int r = 0; r < L.n_endpoint_rows; ++r) emit(col, r);
             for (int m = 0; m < L.n_intervals; ++m) {
+                for (int e = 0; e < L.n_kc; ++e)
+                    if (maskAt(L.nq + L.nz + L.n_auxres + e, 0)) emit(col, L.row_kin[m] + e);
                 for (int e = 0; e < L.n_path_rows; ++e)
                     if (maskAt(L.n_out + e, 0)) emit(col, L.row_path[m] + e);
                 for (int k = 0; k < ppi; ++k)
@@ -151,10 +175,20 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
                         if (maskAt(residOutRow(o), 0)) emit(col, L.row_resid[ppi * m + k] + o); // through the time input
                 for (int o = 0; o < L.n_defect_rows; ++o) emit(col, L.row_defect[m] + o);      // through h, always
             }
+            for (int e = 0; e < L.n_kc; ++e)
+                if (maskAt(L.nq + L.nz + L.n_auxres + e, 0)) emit(col, L.row_kin[L.n_mesh - 1] + e);
             for (int e = 0; e < L.n_path_rows; ++e)
                 if (maskAt(L.n_out + e, 0)) emit(col, L.row_path[L.n_mesh - 1] + e);
             for (int o = 0; o < L.n_resid_rows_per_point; ++o)
                 if (maskAt(residOutRow(o), 0)) emit(col, L.row_resid[L.n_grid - 1] + o);
+            continue;
+        }
+        if (c.kind == COL_SLACK) {
+            // a slack enters through the velocity correction of its midpoint only: qdot_mid = u_mid + G^T gamma
+            // (CasOCTranscription.cpp:315-332), i.e. the Simpson defects of the coordinates of its interval (the Hermite defect
+            // has no xdot_mid); the VelocityCorrection callback block is dense (CasOCFunction.cpp:250-291)
+            const int m = c.point / 2;
+            for (int s = 0; s < L.nq; ++s) emit(col, L.row_defect[m] + L.ns + s);
             continue;
         }
         const int j = c.point;
@@ -177,10 +211,12 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
             if (j < L.n_intervals) { ms[nm] = j; roles[nm++] = 0; }
         }
         // the path-constraint callbacks of mesh point j: after the interval that ends at j, before the one that starts there
-        bool pathDone = !(hs ? j % 2 == 0 : true) || L.n_path_rows == 0;
+        bool pathDone = !(hs ? j % 2 == 0 : true) || (L.n_path_rows == 0 && L.n_kc == 0);
         auto emitPath = [&]() {
             if (pathDone) return;
             pathDone = true;
+            for (int e = 0; e < L.n_kc; ++e)
+                if (maskAt(L.nq + L.nz + L.n_auxres + e, c.in)) emit(col, L.row_kin[hs ? j / 2 : j] + e);
             for (int e = 0; e < L.n_path_rows; ++e)
                 if (maskAt(L.n_out + e, c.in)) emit(col, L.row_path[hs ? j / 2 : j] + e);
         };
@@ -236,6 +272,10 @@ void layoutBounds(const mocob200_tables& T, const mocob200_transcription& R, con
                 xlo[L.off_controls + j * L.nc + k] = vb[6 * (L.ns + k) + which];
                 xhi[L.off_controls + j * L.nc + k] = vb[6 * (L.ns + k) + which + 1];
             }
+            for (int k = 0; k < L.nm; ++k) { // MocoPhase multiplier_bounds, the same at every point (MocoProblemRep.cpp:160-200)
+                xlo[L.off_mult + j * L.nm + k] = R.multiplier_bounds[0];
+                xhi[L.off_mult + j * L.nm + k] = R.multiplier_bounds[1];
+            }
             for (int k = 0; k < L.nd; ++k) {
                 const bool accel = L.implicit && k < L.nq;
                 xlo[L.off_derivs + j * L.nd + k] = accel ? R.accel_bounds[0] : R.auxderiv_bounds[0];
@@ -243,6 +283,11 @@ void layoutBounds(const mocob200_tables& T, const mocob200_transcription& R, con
             }
         }
     }
+    if (xlo && xhi)
+        for (int i = 0; i < (L.n_grid - L.n_mesh) * L.nsl; ++i) { // velocity_correction_bounds (MocoCasOCProblem.cpp:183-202)
+            xlo[L.off_slacks + i] = R.velocity_correction_bounds[0];
+            xhi[L.off_slacks + i] = R.velocity_correction_bounds[1];
+        }
     if (glo && ghi) {
         for (int r = 0; r < L.n_con; ++r) { glo[r] = 0; ghi[r] = 0; }
         for (int g = 0; g < T.ngoal; ++g) {

@@ -10,9 +10,11 @@
 namespace mocob200 {
 
 // row kinds
-enum { ROW_ENDPOINT = 0, ROW_RESIDUAL = 1, ROW_DEFECT_TRAP = 2, ROW_DEFECT_HERMITE = 3, ROW_DEFECT_SIMPSON = 4, ROW_INTERP = 5, ROW_PATH = 6 };
+enum { ROW_ENDPOINT = 0, ROW_RESIDUAL = 1, ROW_DEFECT_TRAP = 2, ROW_DEFECT_HERMITE = 3, ROW_DEFECT_SIMPSON = 4, ROW_INTERP = 5, ROW_PATH = 6,
+       ROW_KINEMATIC = 7 /* a = grid point of the mesh point, b = out row of the kinematic-constraint error */ };
 // column kinds
-enum { COL_T0 = 0, COL_TF = 1, COL_STATE = 2, COL_CONTROL = 3, COL_DERIV = 4 };
+enum { COL_T0 = 0, COL_TF = 1, COL_STATE = 2, COL_CONTROL = 3, COL_DERIV = 4, COL_MULT = 5,
+       COL_SLACK = 6 /* point = the interior grid point the slack belongs to, k = slack index, in = -1 (not a point-function input) */ };
 
 struct RowMeta { int kind, a, b, pad; };  // ENDPOINT: a = goal, b = output ; RESIDUAL: a = grid point, b = out row ; DEFECT_*: a = interval, b = state ; INTERP: a = interval, b = control ; PATH: a = grid point, b = equation of the path constraint, pad = its goal record
 struct ColMeta { int kind, point, k, in; }; // in = index into the point-function input vector (0 = time)
@@ -20,6 +22,10 @@ struct ColMeta { int kind, point, k, in; }; // in = index into the point-functio
 struct Layout {
     int scheme, implicit;
     int nq, nz, ns, nc, nd, n_in;
+    int nm, nsl, n_kc;                         // multipliers per grid point, slacks per interior grid point, kinematic rows per mesh point
+    int enforce_derivs;                        // enforce_constraint_derivatives (and kinematic constraints exist)
+    int off_mult, off_slacks;
+    std::vector<int> row_kin;                  // first kinematic-constraint row of each mesh point
     int n_auxres, n_integrand, n_dyn_out, n_out;
     int n_mesh, n_grid, n_intervals;
     int n_var, n_con, nnz;

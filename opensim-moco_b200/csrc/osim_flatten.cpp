@@ -428,7 +428,40 @@ ModelSpec loadOsim(const std::string& path, bool musclesAsPathActuators) {
     }
     if (const XmlNode* cs = model->child("ConstraintSet"))
         if (const XmlNode* o = cs->child("objects"))
-            if (!o->children.empty()) throw std::runtime_error("kinematic constraints are unsupported (SURVEY §8 a9)");
+            for (auto& c : o->children) {
+                if (boolOf(c->childText("isDisabled"), false) || !boolOf(c->childText("isEnforced"), true)) continue;
+                if (c->tag != "CoordinateCouplerConstraint")
+                    throw std::runtime_error("unsupported kinematic constraint '" + c->tag + "' (only CoordinateCouplerConstraint, SURVEY §8 a9)");
+                CouplerSpec C;
+                C.name = c->name();
+                C.dependent = trim(c->childText("dependent_coordinate_name"));
+                {
+                    std::string names = c->childText("independent_coordinate_names");
+                    std::vector<std::string> v;
+                    size_t i = 0;
+                    while (i < names.size()) {
+                        while (i < names.size() && isspace((unsigned char)names[i])) ++i;
+                        size_t j = i;
+                        while (j < names.size() && !isspace((unsigned char)names[j])) ++j;
+                        if (j > i) v.push_back(names.substr(i, j - i));
+                        i = j;
+                    }
+                    if (v.size() != 1) throw std::runtime_error("CoordinateCouplerConstraint '" + C.name + "': exactly one independent coordinate is supported");
+                    C.independent = v[0];
+                }
+                C.scaleFactor = dblOf(*c, "scale_factor", 1.0);
+                const XmlNode* holder = c->child("coupled_coordinates_function");
+                double scale = 1;
+                const XmlNode* fn = holder ? unwrapFunction(*holder, scale) : nullptr;
+                if (!fn) throw std::runtime_error("CoordinateCouplerConstraint '" + C.name + "': unsupported coupled_coordinates_function");
+                if (fn->tag == "Constant") { C.fn.fnKind = MOCOB200_FN_CONSTANT; C.fn.c1 = scale * dblOf(*fn, "value", 0.0); }
+                else if (fn->tag == "LinearFunction") {
+                    auto co = parseDoubles(fn->childText("coefficients", "1 0"));
+                    if (co.size() != 2) throw std::runtime_error("LinearFunction needs 2 coefficients");
+                    C.fn.fnKind = MOCOB200_FN_LINEAR; C.fn.c0 = scale * co[0]; C.fn.c1 = scale * co[1];
+                } else { C.fn.fnKind = MOCOB200_FN_SIMMSPLINE; C.fn.spline = simmSplineOf(*fn, scale, "CoordinateCouplerConstraint '" + C.name + "'"); }
+                M.couplers.push_back(C);
+            }
 
     const XmlNode* cg = model->child("ContactGeometrySet");
     const XmlNode* cgobjs = cg ? cg->child("objects") : nullptr;

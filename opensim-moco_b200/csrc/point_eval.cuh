@@ -43,6 +43,8 @@ struct DevTables { // mocob200_tables with device (or shared-memory) pool pointe
     int o_body_i, o_pp_i, o_mus_i, o_contact_i, o_cact_i, o_spline_i, o_goal_i, o_ppoly_i;
     int ncustom, o_cj_d, o_cj_i, o_body_cj; // custom (function-based) joints
     int nxforce, o_xforce_i;                // external forces (functions of time)
+    int ncoupler, o_cc_i, o_cc_d;           // coordinate-coupler kinematic constraints
+    int nm, n_kc, enforce_derivs;           // multipliers per point, kinematic-constraint outputs, their derivatives enforced
     int implicit; // multibody dynamics mode
     int n_auxres;
     int n_integrand; // goals with an integrand, in goal order
@@ -259,6 +261,51 @@ __device__ __forceinline__ double abs_ipow(double c, int n) {
     double r = a * a;
     for (int k = 2; k < n; ++k) r *= a;
     return r;
+}
+
+// CoordinateCouplerConstraint k: position error scale f(q_i) - q_d and the first two derivatives of scale f at q_i
+// (SimbodyEngine/CoordinateCouplerConstraint.cpp:40-90 CompoundFunction -> SimTK::Constraint::CoordinateCoupler)
+__device__ inline void coupler_function(const DevTables& T, int k, const double* q, double& err, double& d1, double& d2) {
+    const int* ci = T.idx + T.o_cc_i + k * MOCOB200_CC_ISTRIDE;
+    const double* cd = T.dbl + T.o_cc_d + k * MOCOB200_CC_DSTRIDE;
+    const double qi = q[ci[1]];
+    double f;
+    if (ci[0] == MOCOB200_FN_LINEAR) { f = cd[0] * qi + cd[1]; d1 = cd[0]; d2 = 0.0; }
+    else if (ci[0] == MOCOB200_FN_SIMMSPLINE) { f = simm_spline(T, ci[3], qi, 0); d1 = simm_spline(T, ci[3], qi, 1); d2 = simm_spline(T, ci[3], qi, 2); }
+    else { f = cd[1]; d1 = 0.0; d2 = 0.0; }
+    err = f - q[ci[2]];
+}
+// constraint forces of the solver's multipliers as applied mobility forces: G^T (-lambda) (MocoCasOCProblem.h:643-662)
+__device__ inline void coupler_forces(const DevTables& T, const double* q, const double* mult, double* tau) {
+    for (int k = 0; k < T.ncoupler; ++k) {
+        double e, d1, d2;
+        coupler_function(T, k, q, e, d1, d2);
+        const int* ci = T.idx + T.o_cc_i + k * MOCOB200_CC_ISTRIDE;
+        tau[ci[1]] -= d1 * mult[k];
+        tau[ci[2]] += mult[k];
+    }
+}
+// kinematic-constraint errors (MocoCasOCProblem.h:664-732): position level; with enforced derivatives also G u and
+// G udot + Gdot u, udot being this model's (explicit: just solved; implicit: the acceleration variables)
+__device__ inline void coupler_errors(const DevTables& T, int k, const double* q, const double* u, const double* udot, double* kc) {
+    double e, d1, d2;
+    coupler_function(T, k, q, e, d1, d2);
+    const int* ci = T.idx + T.o_cc_i + k * MOCOB200_CC_ISTRIDE;
+    kc[k] = e;
+    if (T.enforce_derivs) {
+        kc[T.nm + k] = d1 * u[ci[1]] - u[ci[2]];
+        kc[2 * T.nm + k] = d1 * udot[ci[1]] + d2 * u[ci[1]] * u[ci[1]] - udot[ci[2]];
+    }
+}
+// velocity correction of a Hermite-Simpson midpoint (MocoCasOCProblem.h:298-332): corr = G(q)^T gamma
+__device__ inline double coupler_velocity_correction(const DevTables& T, const double* q, const double* gamma, int s) {
+    double c = 0.0;
+    for (int k = 0; k < T.ncoupler; ++k) {
+        const int* ci = T.idx + T.o_cc_i + k * MOCOB200_CC_ISTRIDE;
+        if (ci[1] == s) { double e, d1, d2; coupler_function(T, k, q, e, d1, d2); c += d1 * gamma[k]; }
+        if (ci[2] == s) c -= gamma[k];
+    }
+    return c;
 }
 
 struct MuscleOut {
@@ -837,7 +884,8 @@ __device__ inline void eval_point(const DevTables& T, const double* in, double* 
     const double* u = q + nq;
     const double* z = u + nq;
     const double* ctl = z + nz;
-    const double* der = ctl + nc; // implicit: udot[nq] then aux derivatives
+    const double* mult = ctl + nc; // Lagrange multipliers of the kinematic constraints
+    const double* der = mult + T.nm; // implicit: udot[nq] then aux derivatives
     const double* auxder = der + (T.implicit ? nq : 0);
     const bool dyn_on = mask & 1u;
     // which integrands are wanted, and do any of them need kinematics + contact forces?
@@ -906,12 +954,15 @@ __device__ inline void eval_point(const DevTables& T, const double* in, double* 
             const int* ai = T.idx + T.o_cact_i + a * MOCOB200_CACT_ISTRIDE;
             S.tau[ai[0]] += T.dbl[T.o_cact_d + a * MOCOB200_CACT_DSTRIDE] * ctl[ai[1]];
         }
+        coupler_forces(T, q, mult, S.tau);
         if (T.implicit) inverse_dynamics_residual(T, u, der, S, dyn);
         else forward_dynamics(T, u, S, dyn);
+        double* kc = auxres + T.n_auxres;
+        for (int k = 0; k < T.ncoupler; ++k) coupler_errors(T, k, q, u, T.implicit ? der : dyn, kc);
     }
     // goal integrands (MocoGoal::calcIntegrand; MocoControlGoal.cpp:121-131,
     // MocoStateTrackingGoal.cpp:103-117, MocoContactTrackingGoal.cpp:240-287)
-    double* integ = auxres + T.n_auxres;
+    double* integ = auxres + T.n_auxres + T.n_kc;
     int gi = 0;
     for (int g2 = 0; g2 < T.ngoal; ++g2) {
         const int* gr = T.idx + T.o_goal_i + g2 * MOCOB200_GOAL_ISTRIDE;
@@ -983,11 +1034,11 @@ __device__ inline void eval_endpoint(const DevTables& T, int g, const double* ei
     const int* gr = T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
     const int* ip = T.idx + gr[4];
     const double* dp = T.dblG + gr[5];
-    const int half = 1 + ns + nc + nd;
+    const int half = 1 + ns + nc + T.nm + nd;
     const double t0 = ein[0], tf = ein[half];
     const double* x0 = ein + 1;
     const double* c0 = x0 + ns;
-    const double* d0 = c0 + nc;
+    const double* d0 = c0 + nc + T.nm;
     const double* xf = ein + half + 1;
     const double* cf = xf + ns;
     const double integral = ein[2 * half];

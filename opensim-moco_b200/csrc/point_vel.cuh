@@ -19,7 +19,9 @@ __device__ inline void eval_point_vel(const DevTables& T, const WarpAux& A, cons
     const double* u = in + 1 + nq;
     const double* z = u + nq;
     const double* ctl = z + nz;
-    const double* der = ctl + nc;
+    const double* q = in + 1;
+    const double* mult = ctl + nc;
+    const double* der = mult + T.nm;
     const double* auxder = der + (T.implicit ? nq : 0);
     const double* udot = T.implicit ? der : nullptr;
     const double* R = blobz + A.o_R;
@@ -215,6 +217,7 @@ __device__ inline void eval_point_vel(const DevTables& T, const WarpAux& A, cons
         const int* ai = T.idx + T.o_cact_i + a * MOCOB200_CACT_ISTRIDE;
         tau[ai[0]] += T.dbl[T.o_cact_d + a * MOCOB200_CACT_DSTRIDE] * ctl[ai[1]];
     }
+    coupler_forces(T, q, mult, tau);
     // ---- joint wrenches: inertial - applied, tip to base (wk_gather_body + wk_inward)
     for (int b = nb - 1; b >= 0; --b) {
         const double* bd = T.dbl + T.o_body_d + b * MOCOB200_BODY_DSTRIDE;
@@ -243,6 +246,7 @@ __device__ inline void eval_point_vel(const DevTables& T, const WarpAux& A, cons
         wk_ldlt_solve_lane(blobz + A.o_M, nq, tau);
         for (int k = 0; k < nq; ++k) out[k] = tau[k];
     }
+    for (int k = 0; k < T.ncoupler; ++k) coupler_errors(T, k, q, u, T.implicit ? der : out, out + nq + nz + T.n_auxres);
 }
 
 } // namespace mocob200

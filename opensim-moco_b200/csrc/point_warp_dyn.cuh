@@ -242,7 +242,8 @@ __device__ __forceinline__ void warp_eval_point_t(const DevTables& T, const Warp
     const double* u = q + nq;
     const double* z = u + nq;
     const double* ctl = z + nz;
-    const double* der = ctl + nc;
+    const double* mult = ctl + nc;
+    const double* der = mult + T.nm;
     const double* auxder = der + (T.implicit ? nq : 0);
     const bool dyn = mask & 1u;
     bool need_contacts = dyn;
@@ -308,6 +309,10 @@ __device__ __forceinline__ void warp_eval_point_t(const DevTables& T, const Warp
         for (int b = lane; b < nb; b += 32) wk_gather_body(C, b);
         for (int k = lane; k < nq; k += 32) wk_gather_coord(C, k, ctl);
         __syncwarp();
+        if (T.ncoupler > 0) { // constraint forces of the multipliers (few constraints: one lane)
+            if (lane == 0) coupler_forces(T, q, mult, ws + A.o_tau);
+            __syncwarp();
+        }
         PHASE_MARK(5);
         const bool composite = !T.implicit && reuse == 0;
         for (int L = A.nlevels - 1; L >= 0; --L) {
@@ -333,10 +338,12 @@ __device__ __forceinline__ void warp_eval_point_t(const DevTables& T, const Warp
             wk_ldlt_solve(C, nq, ws + A.o_tau, out);
         }
         __syncwarp();
+        for (int k = lane; k < T.ncoupler; k += 32) coupler_errors(T, k, q, u, T.implicit ? der : out, out + nq + nz + T.n_auxres);
+        __syncwarp();
     }
     PHASE_MARK(9);
     // goal integrands (MocoControlGoal.cpp:121-131, MocoStateTrackingGoal.cpp:103-117, MocoContactTrackingGoal.cpp:240-287)
-    double* integ = out + nq + nz + T.n_auxres;
+    double* integ = out + nq + nz + T.n_auxres + T.n_kc;
     int gi = 0;
     for (int g2 = 0; g2 < T.ngoal; ++g2) {
         const int* gr = T.idx + T.o_goal_i + g2 * MOCOB200_GOAL_ISTRIDE;

@@ -135,7 +135,7 @@ __device__ inline LocalMuscleEval wk_local_muscle(const DevTables& T, const Warp
     const double* in = ws + A.o_in;
     const double* z = in + 1 + 2 * nq;
     const double* ctl = z + T.nz;
-    const double* auxder = ctl + T.nc + (T.implicit ? nq : 0);
+    const double* auxder = ctl + T.nc + T.nm + (T.implicit ? nq : 0);
     const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
     const double* md = T.dbl + T.o_mus_d + m * MOCOB200_MUS_DSTRIDE;
     const int flags = mi[5];
@@ -248,7 +248,7 @@ __device__ inline void wk_local_columns_central(const DevTables& T, const WarpAu
                 if (!ok) hg /= u_aim;
                 else hg *= sqrt(u_aim / fmax(1.0, u));
             }
-            col[(size_t)(nq + nz + T.n_auxres + slot) * n_in] = jv;
+            col[(size_t)(nq + nz + T.n_auxres + T.n_kc + slot) * n_in] = jv;
             ++slot;
         }
         for (int o = 0; o < n_out; ++o)
@@ -292,7 +292,7 @@ __device__ inline void wk_local_columns(const DevTables& T, const WarpAux& A, do
         for (int g = 0; g < T.ngoal; ++g) {
             const int* gr = T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
             if (!gr[3]) continue;
-            col[(size_t)(nq + nz + T.n_auxres + slot) * n_in] = wk_integrand_term_delta(T, A, ws, gr, dir, v0, v1) * inv;
+            col[(size_t)(nq + nz + T.n_auxres + T.n_kc + slot) * n_in] = wk_integrand_term_delta(T, A, ws, gr, dir, v0, v1) * inv;
             ++slot;
         }
         // a non-finite nominal output poisons its whole row, as it does when the full function is differenced

@@ -146,8 +146,39 @@ Vec3<S> massCenter(const Model& M, const Frames<S>& K) {
     return (S(1.0) / total) * acc;
 }
 
-// The fused point function: in = [time, q, u, z, controls, derivatives] -> out = [udot | residual, zdot,
-// aux residuals, integrand_0 ...]. mask bit 0 = the dynamics callback
+// CoordinateCouplerConstraint k (SimbodyEngine/CoordinateCouplerConstraint.cpp:40-90 CompoundFunction): position error
+// scale f(q_i) - q_d and the first two derivatives of scale f at q_i.
+template <class S>
+void couplerFunction(const Model& M, int k, const S* q, S& err, S& d1, S& d2) {
+    const int* ci = M.couplerI(k);
+    const double* cd = M.couplerD(k);
+    const S qi = q[ci[1]];
+    S f;
+    if (ci[0] == MOCOB200_FN_LINEAR) { f = S(cd[0]) * qi + S(cd[1]); d1 = S(cd[0]); d2 = S(0.0); }
+    else if (ci[0] == MOCOB200_FN_SIMMSPLINE) {
+        // value, slope and curvature through a dual number seeded on q_i (slope) and once more on the slope (curvature)
+        const Dual<S> v = simmSpline<Dual<S>>(M, ci[3], Dual<S>(qi, S(1.0)), false);
+        const Dual<S> s1 = simmSpline<Dual<S>>(M, ci[3], Dual<S>(qi, S(1.0)), true);
+        f = v.v; d1 = s1.v; d2 = s1.d;
+    } else { f = S(cd[1]); d1 = S(0.0); d2 = S(0.0); }
+    err = f - q[ci[2]];
+}
+// Velocity correction of the Hermite-Simpson midpoints (MocoCasOCProblem.h:298-332; Posa et al. 2016): qdot = u + G^T gamma
+// with G the constraint Jacobian: row k = d err_k / dq = (f' at the independent coordinate, -1 at the dependent one).
+template <class S>
+void velocityCorrection(const Model& M, const S* q, const S* gamma, S* corr) {
+    for (int i = 0; i < M.nq; ++i) corr[i] = S(0.0);
+    for (int k = 0; k < M.nm; ++k) {
+        S e, d1, d2;
+        couplerFunction(M, k, q, e, d1, d2);
+        const int* ci = M.couplerI(k);
+        corr[ci[1]] += d1 * gamma[k];
+        corr[ci[2]] -= gamma[k];
+    }
+}
+
+// The fused point function: in = [time, q, u, z, controls, multipliers, derivatives] -> out = [udot | residual, zdot,
+// aux residuals, kinematic-constraint errors, integrand_0 ...]. mask bit 0 = the dynamics callback
 // (MultibodySystemExplicit/Implicit::eval, CasOCFunction.cpp:232-245, 317-331 -> MocoCasOCProblem.h:203-297),
 // bit 1+k = CostIntegrand k (CasOCFunction.cpp:145-151 -> MocoCasOCProblem.h:333-356).
 template <class S>
@@ -155,7 +186,8 @@ void evalPoint(const Model& M, const S* in, S* out, unsigned mask = 0xffffffffu)
     const int nq = M.nq, nz = M.nz, nc = M.nc;
     const S time = in[0];
     const S* q = in + 1; const S* u = q + nq; const S* z = u + nq; const S* ctl = z + nz;
-    const S* der = ctl + nc;
+    const S* mult = ctl + nc;
+    const S* der = mult + M.nm;
     const S* auxDeriv = der + (M.implicit ? nq : 0);
     const bool dyn = mask & 1u;
     bool needContact = dyn;
@@ -218,6 +250,15 @@ void evalPoint(const Model& M, const S* in, S* out, unsigned mask = 0xffffffffu)
             const int* ai = M.T->idx + M.T->o_cact_i + a * MOCOB200_CACT_ISTRIDE;
             mobility[ai[0]] += S(M.T->dbl[M.T->o_cact_d + a * MOCOB200_CACT_DSTRIDE]) * ctl[ai[1]];
         }
+        // kinematic-constraint forces from the solver's multipliers, applied like any other force: G^T (-lambda)
+        // (MocoCasOCProblem.h:643-662: calcConstraintForcesFromMultipliers with the multipliers negated)
+        for (int k = 0; k < M.nm; ++k) {
+            S e, d1, d2;
+            couplerFunction(M, k, q, e, d1, d2);
+            const int* ci = M.couplerI(k);
+            mobility[ci[1]] -= d1 * mult[k];
+            mobility[ci[2]] += mult[k];
+        }
         S tau[kMaxDof];
         if (M.implicit) {
             // residual = f_app - M udot - f_inertial (MocoCasOCProblem.h:280-285; MocoDeveloperGuide.dox:175-208)
@@ -233,6 +274,21 @@ void evalPoint(const Model& M, const S* in, S* out, unsigned mask = 0xffffffffu)
             Mass.resize((size_t)nq * nq);
             massMatrix(M, K, Mass.data());
             choleskySolve(nq, Mass.data(), rhs, out);
+        }
+        // kinematic-constraint errors (MocoCasOCProblem.h:664-732): position level, then - with their derivatives enforced -
+        // velocity level (G u) and acceleration level (G udot + Gdot u) with the udot of THIS model (explicit: the one just
+        // solved for; implicit: the acceleration variables)
+        S* kc = out + nq + nz + M.n_auxres;
+        const S* udotUsed = M.implicit ? der : out;
+        for (int k = 0; k < M.nm; ++k) {
+            S e, d1, d2;
+            couplerFunction(M, k, q, e, d1, d2);
+            const int* ci = M.couplerI(k);
+            kc[k] = e;
+            if (M.enforceDerivs) {
+                kc[M.nm + k] = d1 * u[ci[1]] - u[ci[2]];
+                kc[2 * M.nm + k] = d1 * udotUsed[ci[1]] + d2 * u[ci[1]] * u[ci[1]] - udotUsed[ci[2]];
+            }
         }
     }
     // integrands (MocoControlGoal.cpp:121-131, MocoStateTrackingGoal.cpp:103-117,
@@ -315,9 +371,9 @@ void evalEndpoint(const Model& M, int g, const S* ein, S* vals) {
     const int* ip = M.T->idx + gr[4];
     const double* dp = M.T->dbl + gr[5];
     const int ns = 2 * M.nq + M.nz, nc = M.nc, nd = M.nd, nq = M.nq;
-    const int half = 1 + ns + nc + nd;
+    const int half = 1 + ns + nc + M.nm + nd;
     const S t0 = ein[0], tf = ein[half];
-    const S* x0 = ein + 1; const S* c0 = x0 + ns; const S* d0 = c0 + nc;
+    const S* x0 = ein + 1; const S* c0 = x0 + ns; const S* d0 = c0 + nc + M.nm;
     const S* xf = ein + half + 1; const S* cf = xf + ns;
     const S integral = ein[2 * half];
     const S w(dp[0]);

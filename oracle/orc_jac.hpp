@@ -24,7 +24,8 @@ struct JacBuilder {
         const int k = a - 1;
         if (k < P.ns) return P.offStates + j * P.ns + k;
         if (k < P.ns + P.nc) return P.offControls + j * P.nc + (k - P.ns);
-        return P.offDerivs + j * P.nd + (k - P.ns - P.nc);
+        if (k < P.ns + P.nc + P.nm) return P.offMult + j * P.nm + (k - P.ns - P.nc);
+        return P.offDerivs + j * P.nd + (k - P.ns - P.nc - P.nm);
     }
     // scatter  coef * d(callback output row o of point j)/d(everything)  into the row
     // (time input chains to t0 and tf: time_j = t0 + (tf - t0) grid_j)
@@ -37,7 +38,34 @@ struct JacBuilder {
         for (int a = 1; a < P.nIn; ++a) r.add(colOfInput(j, a), coef * Jr[a]);
     }
     // coef * d xdot_s(j) / d(everything)
+    // FD block of the VelocityCorrection callback at midpoint j (CasOCFunction.cpp:250-291: inputs time, multibody states,
+    // slacks; output the nq corrections), row s, chained into the NLP columns
+    void addVelocityCorrectionRow(SparseRow& r, const double* x, int j, int s, double coef, bool structural) const {
+        const int nmb = 2 * P.nq, n = 1 + nmb + P.nsl;
+        const int slackCol = P.offSlacks + (j / 2) * P.nsl;
+        if (structural) {
+            r.mark(0); r.mark(1);
+            for (int a = 0; a < nmb; ++a) r.mark(P.offStates + j * P.ns + a);
+            for (int k = 0; k < P.nsl; ++k) r.mark(slackCol + k);
+            return;
+        }
+        std::vector<double> in(n), y0(P.nq), col(P.nq);
+        in[0] = x[0] + (x[1] - x[0]) * P.grid[j];
+        for (int a = 0; a < nmb; ++a) in[1 + a] = x[P.offStates + (size_t)j * P.ns + a];
+        for (int k = 0; k < P.nsl; ++k) in[1 + nmb + k] = x[slackCol + k];
+        auto f = [&](const double* xin, double* yout) { velocityCorrection<double>(P.M, xin + 1, xin + 1 + nmb, yout); };
+        f(in.data(), y0.data());
+        for (int a = 0; a < n; ++a) {
+            fdColumn(f, P.fd, in, a, y0.data(), P.nq, col.data());
+            const double d = coef * col[s];
+            if (a == 0) { r.add(0, d * (1.0 - P.grid[j])); r.add(1, d * P.grid[j]); }
+            else if (a <= nmb) r.add(P.offStates + j * P.ns + (a - 1), d);
+            else r.add(slackCol + (a - 1 - nmb), d);
+        }
+    }
+    const double* xptr = nullptr;
     void addXdotRow(SparseRow& r, const double* J, int j, int s, double coef, bool structural) const {
+        if (s < P.nq && P.corrected(j)) addVelocityCorrectionRow(r, xptr, j, s, coef, structural);
         if (s < P.nq) { if (structural) r.mark(P.offStates + j * P.ns + P.nq + s); else r.add(P.offStates + j * P.ns + P.nq + s, coef); return; }
         if (s < 2 * P.nq && P.M.implicit) { const int c = P.offDerivs + j * P.nd + (s - P.nq); if (structural) r.mark(c); else r.add(c, coef); return; }
         addCallbackRow(r, J, j, s - P.nq, coef, structural);
@@ -45,7 +73,7 @@ struct JacBuilder {
     // d(goal output o)/d(everything): endpoint FD block E[nout][nEin] + chain through the integral
     void addEndpointRow(SparseRow& r, const double* x, const double* J, const double* E, int g, int o, double coef,
                         bool structural) const {
-        const int half = 1 + P.ns + P.nc + P.nd, last = P.nGrid - 1;
+        const int half = 1 + P.ns + P.nc + P.nm + P.nd, last = P.nGrid - 1;
         const double* Er = E ? E + (size_t)o * P.nEin : nullptr;
         const int slot = P.goalSlot[g];
         if (structural) {
@@ -96,6 +124,13 @@ struct JacBuilder {
                 addEndpointRow(r, x, J, structural ? nullptr : (*Eblocks)[g].data(), g, row - N.goalRow[g], 1.0, structural);
                 return;
             }
+        // kinematic-constraint rows: output 3 of the multibody callback at the mesh points (CasOCTranscription.cpp:360, 398)
+        if (N.nKc)
+            for (int im = 0; im < N.nMesh; ++im)
+                if (row >= N.kinRow[im] && row < N.kinRow[im] + N.nKc) {
+                    addCallbackRow(r, J, N.meshGridIndex(im), N.nq + N.M.nz + N.M.n_auxres + (row - N.kinRow[im]), 1.0, structural);
+                    return;
+                }
         // path-constraint rows: each path constraint is its own callback with a dense block over the mesh point's inputs
         if (N.nPathPerMesh)
             for (int im = 0; im < N.nMesh; ++im)
@@ -187,6 +222,7 @@ struct JacBuilder {
         std::vector<double> Y((size_t)P.nGrid * P.nOut), J((size_t)P.nGrid * P.nOut * P.nIn);
         P.evalPointJacobians(x, Y.data(), J.data());
         Yptr = Y.data();
+        xptr = x;
         std::vector<std::vector<double>> E(P.M.T->ngoal);
         for (int g = 0; g < P.M.T->ngoal; ++g) if (P.goalRow[g] >= 0) endpointBlock(x, Y.data(), g, E[g]);
         std::vector<int> next(colptr.begin(), colptr.end() - 1);
@@ -229,6 +265,21 @@ struct JacBuilder {
             r.add(0, -w * acc);
             r.add(1, w * acc);
         };
+        if (P.nm && P.R.minimize_lagrange_multipliers) {
+            const double T = x[1] - x[0], w = P.R.lagrange_multiplier_weight;
+            double acc = 0;
+            for (int j = 0; j < P.nGrid; ++j) {
+                double sq = 0;
+                for (int k = 0; k < P.nm; ++k) {
+                    const int c = P.offMult + j * P.nm + k;
+                    sq += x[c] * x[c];
+                    r.add(c, 2.0 * w * T * P.quad[j] * x[c]);
+                }
+                acc += P.quad[j] * sq;
+            }
+            r.add(0, -w * acc);
+            r.add(1, w * acc);
+        }
         if (P.M.implicit && P.R.minimize_accelerations) pen(0, P.nq, P.R.accelerations_weight);
         if (P.M.n_auxres && P.R.minimize_auxiliary_derivatives) pen(P.M.implicit ? P.nq : 0, P.nd, P.R.auxiliary_derivatives_weight);
         for (int c = 0; c < P.nVar; ++c) grad[c] = r.v[c];

@@ -74,7 +74,9 @@ struct Nlp {
     FdOptions fd;
     bool hs = true;
     int nMesh = 0, nIntervals = 0, nGrid = 0, ns = 0, nc = 0, nd = 0, nq = 0, nIn = 0, nOut = 0;
-    int offStates = 2, offControls = 0, offDerivs = 0, nVar = 0, nCon = 0, nEin = 0;
+    int offStates = 2, offControls = 0, offMult = 0, offSlacks = 0, offDerivs = 0, nVar = 0, nCon = 0, nEin = 0;
+    int nm = 0, nsl = 0, nKc = 0;       // multipliers per grid point, slacks per interior point, kinematic rows per mesh point
+    std::vector<int> kinRow;            // first kinematic-constraint row per mesh point
     int nResidPerPoint = 0, nEndpointRows = 0;
     std::vector<double> mesh, grid, quad;
     std::vector<int> goalRow, goalSlot, goalNout; // first endpoint row (or -1), integrand slot (or -1), outputs
@@ -85,7 +87,7 @@ struct Nlp {
 
     void init(const mocob200_tables* T, const mocob200_transcription* tr) {
         R = *tr;
-        M.init(T, tr->dynamics_mode == MOCOB200_DYNAMICS_IMPLICIT);
+        M.init(T, tr->dynamics_mode == MOCOB200_DYNAMICS_IMPLICIT, tr->enforce_constraint_derivatives != 0);
         fd.defaults(tr->fd_scheme);
         hs = tr->scheme == MOCOB200_SCHEME_HERMITE_SIMPSON;
         nMesh = tr->n_mesh; nIntervals = nMesh - 1;
@@ -105,10 +107,15 @@ struct Nlp {
             else { quad[i] += 0.5 * dm; quad[i + 1] += 0.5 * dm; }
         }
         nq = M.nq; ns = 2 * M.nq + M.nz; nc = M.nc; nd = M.nd; nIn = M.n_in; nOut = M.n_out;
+        // x = [t0, tf, states, controls, multipliers, slacks (Hermite-Simpson midpoints, with enforced derivatives), derivatives]
+        nm = M.nm; nKc = M.n_kc;
+        nsl = (M.enforceDerivs && hs) ? nm : 0;
         offControls = offStates + ns * nGrid;
-        offDerivs = offControls + nc * nGrid;
+        offMult = offControls + nc * nGrid;
+        offSlacks = offMult + nm * nGrid;
+        offDerivs = offSlacks + nsl * (nGrid - nMesh);
         nVar = offDerivs + nd * nGrid;
-        nEin = 2 * (1 + ns + nc + nd) + 1;
+        nEin = 2 * (1 + ns + nc + nm + nd) + 1;
         // rows
         goalRow.assign(T->ngoal, -1); goalSlot.assign(T->ngoal, -1); goalNout.assign(T->ngoal, 0);
         pathGoals.clear(); nPathPerMesh = 0;
@@ -122,11 +129,13 @@ struct Nlp {
         }
         nEndpointRows = row;
         pathRow.assign(nMesh, -1);
+        kinRow.assign(nMesh, -1);
         nResidPerPoint = (M.implicit ? nq : 0) + M.n_auxres;
         interp = hs && tr->interpolate_control_midpoints && nc > 0;
         residRow.assign(nGrid, -1); defectRow.assign(nIntervals, -1); interpRow.assign(nIntervals, -1);
         int igrid = 0;
         for (int im = 0; im < nMesh; ++im) {
+            kinRow[im] = row; row += nKc;           // copyColumn(constraints.kinematic, imesh) comes first
             pathRow[im] = row; row += nPathPerMesh; // copyColumn(path, imesh) for every path constraint
             if (im < nIntervals) {
                 while (grid[igrid] < mesh[im + 1]) { residRow[igrid] = row; row += nResidPerPoint; ++igrid; }
@@ -157,8 +166,12 @@ struct Nlp {
         in[0] = x[0] + (x[1] - x[0]) * grid[j];
         for (int k = 0; k < ns; ++k) in[1 + k] = x[offStates + (size_t)j * ns + k];
         for (int k = 0; k < nc; ++k) in[1 + ns + k] = x[offControls + (size_t)j * nc + k];
-        for (int k = 0; k < nd; ++k) in[1 + ns + nc + k] = x[offDerivs + (size_t)j * nd + k];
+        for (int k = 0; k < nm; ++k) in[1 + ns + nc + k] = x[offMult + (size_t)j * nm + k];
+        for (int k = 0; k < nd; ++k) in[1 + ns + nc + nm + k] = x[offDerivs + (size_t)j * nd + k];
     }
+    // velocity correction at the interior (midpoint) grid point j: qdot_j = u_j + G(q_j)^T gamma_j (CasOCTranscription.cpp:315-332)
+    const double* slacksAt(const double* x, int j) const { return x + offSlacks + (size_t)(j / 2) * nsl; }
+    bool corrected(int j) const { return nsl > 0 && hs && (j % 2 == 1); }
     void evalPoints(const double* x, double* Y) const {
 #pragma omp parallel for schedule(dynamic)
         for (int j = 0; j < nGrid; ++j) {
@@ -196,6 +209,11 @@ struct Nlp {
     // ---- state derivatives used by the defects: qdot = u, udot = callback (explicit) or the
     // acceleration variables (implicit), zdot = callback (CasOCTranscription.cpp:313-411)
     double xdot(const double* x, const double* Y, int j, int s) const {
+        if (s < nq && corrected(j)) {
+            std::vector<double> corr(nq);
+            velocityCorrection<double>(M, x + offStates + (size_t)j * ns, slacksAt(x, j), corr.data());
+            return x[offStates + (size_t)j * ns + nq + s] + corr[s];
+        }
         if (s < nq) return x[offStates + (size_t)j * ns + nq + s];
         if (s < 2 * nq && M.implicit) return x[offDerivs + (size_t)j * nd + (s - nq)];
         return Y[(size_t)j * nOut + (s - nq)];
@@ -206,11 +224,12 @@ struct Nlp {
         return (x[1] - x[0]) * acc;
     }
     void endpointInputs(const double* x, const double* Y, int g, double* ein) const {
-        const int half = 1 + ns + nc + nd, last = nGrid - 1;
+        const int half = 1 + ns + nc + nm + nd, last = nGrid - 1;
         ein[0] = x[0]; ein[half] = x[1];
         for (int k = 0; k < ns; ++k) { ein[1 + k] = x[offStates + k]; ein[half + 1 + k] = x[offStates + (size_t)last * ns + k]; }
         for (int k = 0; k < nc; ++k) { ein[1 + ns + k] = x[offControls + k]; ein[half + 1 + ns + k] = x[offControls + (size_t)last * nc + k]; }
-        for (int k = 0; k < nd; ++k) { ein[1 + ns + nc + k] = x[offDerivs + k]; ein[half + 1 + ns + nc + k] = x[offDerivs + (size_t)last * nd + k]; }
+        for (int k = 0; k < nm; ++k) { ein[1 + ns + nc + k] = x[offMult + k]; ein[half + 1 + ns + nc + k] = x[offMult + (size_t)last * nm + k]; }
+        for (int k = 0; k < nd; ++k) { ein[1 + ns + nc + nm + k] = x[offDerivs + k]; ein[half + 1 + ns + nc + nm + k] = x[offDerivs + (size_t)last * nd + k]; }
         ein[2 * half] = goalSlot[g] >= 0 ? integral(x, Y, goalSlot[g]) : NAN;
     }
 
@@ -228,6 +247,8 @@ struct Nlp {
             evalEndpoint<double>(M, gi, ein.data(), vals.data());
             for (int o = 0; o < goalNout[gi]; ++o) g[goalRow[gi] + o] = vals[o];
         }
+        for (int im = 0; im < nMesh; ++im) // kinematic-constraint errors at the mesh points (m_constraints.kinematic = out.at(3))
+            for (int e = 0; e < nKc; ++e) g[kinRow[im] + e] = Y[(size_t)meshGridIndex(im) * nOut + nq + M.nz + M.n_auxres + e];
         for (int im = 0; im < nMesh; ++im) { // path constraints at the mesh points (m_meshIndices)
             std::vector<double> in(nIn);
             gatherInputs(x, meshGridIndex(im), in.data());
@@ -267,9 +288,20 @@ struct Nlp {
     int numCostTerms() const {
         int n = 0;
         for (int g = 0; g < M.T->ngoal; ++g) if (M.goalRec(g)[1] == MOCOB200_MODE_COST) ++n;
+        if (nm && R.minimize_lagrange_multipliers) ++n;
         if (M.implicit && R.minimize_accelerations) ++n;
         if (M.n_auxres && R.minimize_auxiliary_derivatives) ++n;
         return n;
+    }
+    // lagrange_multiplier_weight * duration * sum_j quad_j sum_k lambda_jk^2 (CasOCTranscription.cpp:513-521)
+    double multiplierPenalty(const double* x) const {
+        double acc = 0;
+        for (int j = 0; j < nGrid; ++j) {
+            double sq = 0;
+            for (int k = 0; k < nm; ++k) { const double d = x[offMult + (size_t)j * nm + k]; sq += d * d; }
+            acc += quad[j] * sq;
+        }
+        return R.lagrange_multiplier_weight * (x[1] - x[0]) * acc;
     }
     double penalty(const double* x, int lo, int hi, double w) const {
         double acc = 0;
@@ -296,6 +328,11 @@ struct Nlp {
             evalEndpoint<double>(M, gi, ein.data(), vals.data());
             double s = 0;
             for (int o = 0; o < goalNout[gi]; ++o) s += vals[o];
+            if (terms) terms[t] = s;
+            ++t; total += s;
+        }
+        if (nm && R.minimize_lagrange_multipliers) {
+            const double s = multiplierPenalty(x);
             if (terms) terms[t] = s;
             ++t; total += s;
         }

@@ -21,16 +21,22 @@ struct Model {
     const mocob200_tables* T = nullptr;
     bool implicit = false;
     int nq = 0, nz = 0, nc = 0, nb = 0, n_auxres = 0, n_integrand = 0, nd = 0, n_in = 0, n_dyn_out = 0, n_out = 0;
+    int nm = 0, n_kc = 0;     // Lagrange multipliers per grid point ; kinematic-constraint equations (3 nm with their derivatives, else nm)
+    bool enforceDerivs = false;
     std::vector<int> integrandGoals; // goal index of each integrand slot
-    void init(const mocob200_tables* t, bool implicitMode) {
+    void init(const mocob200_tables* t, bool implicitMode, bool enforceConstraintDerivatives = false) {
         T = t; implicit = implicitMode;
         nq = t->nq; nz = t->nz; nc = t->nc; nb = t->nb; n_auxres = t->nderiv_aux;
         nd = (implicit ? nq : 0) + t->nderiv_aux;
-        n_in = 1 + 2 * nq + nz + nc + nd;
+        // CasOCProblem.h:473-524: one multiplier per holonomic equation; 3 rows per equation when the derivatives are enforced
+        nm = t->ncoupler;
+        enforceDerivs = nm > 0 && enforceConstraintDerivatives;
+        n_kc = enforceDerivs ? 3 * nm : nm;
+        n_in = 1 + 2 * nq + nz + nc + nm + nd;
         integrandGoals.clear();
         for (int g = 0; g < t->ngoal; ++g) if (goalRec(g)[3]) integrandGoals.push_back(g);
         n_integrand = (int)integrandGoals.size();
-        n_dyn_out = nq + nz + n_auxres;
+        n_dyn_out = nq + nz + n_auxres + n_kc;
         n_out = n_dyn_out + n_integrand;
     }
     const double* bodyD(int b) const { return T->dbl + T->o_body_d + b * MOCOB200_BODY_DSTRIDE; }
@@ -47,6 +53,8 @@ struct Model {
     const double* cjD(int cj) const { return T->dbl + T->o_cj_d + cj * MOCOB200_CJ_DSTRIDE; }
     const int* cjI(int cj) const { return T->idx + T->o_cj_i + cj * MOCOB200_CJ_ISTRIDE; }
     const int* xforceI(int f) const { return T->idx + T->o_xforce_i + f * MOCOB200_XFORCE_ISTRIDE; }
+    const int* couplerI(int k) const { return T->idx + T->o_cc_i + k * MOCOB200_CC_ISTRIDE; }
+    const double* couplerD(int k) const { return T->dbl + T->o_cc_d + k * MOCOB200_CC_DSTRIDE; }
 };
 
 // ---- scalar functions of the path ------------------------------------------------------------

@@ -25,6 +25,11 @@ CASES = {
     "pendulum_cb_upper_trap": ("pendulum_control_bound:upper", "transcription_scheme=trapezoidal"),
     "pendulum_cb_equality": ("pendulum_control_bound:equality", None),
     "pendulum_cb_both": ("pendulum_control_bound:both", "num_mesh_intervals=10;optim_finite_difference_scheme=forward"),
+    # kinematic constraints (testConstraints.cpp:1371-1416, 620-693): multipliers, slacks, velocity correction
+    "point_mass_coupler": ("planar_point_mass_coupler", None),
+    "point_mass_coupler_implicit": ("planar_point_mass_coupler", "multibody_dynamics_mode=implicit"),
+    "double_pendulum_coupler": ("double_pendulum_coupler", None),
+    "double_pendulum_coupler_noderiv_trap": ("double_pendulum_coupler", "enforce_constraint_derivatives=0;transcription_scheme=trapezoidal;num_mesh_intervals=8"),
     "gait2d_tracking": ("gait2d_tracking", None),
     "gait2d_prediction": ("gait2d_prediction", None),
 }

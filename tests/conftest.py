@@ -38,4 +38,6 @@ def golden(name):
 
 FIXTURES = ["sliding_mass", "sliding_mass_trap", "hanging_muscle", "hanging_muscle_rigidtendon", "pendulum2",
             "pendulum3_implicit", "gait2d_tracking", "gait2d_prediction", "pendulum_cb_lower", "pendulum_cb_upper_trap",
-            "pendulum_cb_equality", "pendulum_cb_both"]
+            "pendulum_cb_equality", "pendulum_cb_both",
+            # kinematic constraints: multipliers, slacks, velocity correction
+            "point_mass_coupler", "point_mass_coupler_implicit", "double_pendulum_coupler", "double_pendulum_coupler_noderiv_trap"]
