@@ -171,6 +171,20 @@ __device__ inline void wk_local_rhs(const WarpCtx& C, double* Rm) {
     __syncwarp();
 }
 
+// Kinematic-constraint rows of a local column (explicit mode, derivatives enforced): the acceleration-level error
+// G udot + Gdot u is linear in udot, so its column is G times the udot rows just written; the position- and velocity-level
+// errors do not depend on a local input.
+__device__ inline void wk_local_constraint_rows(const DevTables& T, const double* q, double* col, int n_in) {
+    if (T.ncoupler == 0 || !T.enforce_derivs || T.implicit) return;
+    const int kc0 = T.nq + T.nz + T.n_auxres;
+    for (int k = 0; k < T.ncoupler; ++k) {
+        double e, d1, d2;
+        coupler_function(T, k, q, e, d1, d2);
+        const int* ci = T.idx + T.o_cc_i + k * MOCOB200_CC_ISTRIDE;
+        col[(size_t)(kc0 + 2 * T.nm + k) * n_in] = d1 * col[(size_t)ci[1] * n_in] - col[(size_t)ci[2] * n_in];
+    }
+}
+
 // CasADi's central-difference step control for one output: accumulates u = max |et / er| (finite_differences of the
 // pinned fork, restated in kernels.cu fd_group); returns false when a value is not finite
 __device__ __forceinline__ bool fd_central_u(double vf, double vc, double vb, double h, double reltol, double abstol, double& u) {
@@ -251,6 +265,7 @@ __device__ inline void wk_local_columns_central(const DevTables& T, const WarpAu
             col[(size_t)(nq + nz + T.n_auxres + T.n_kc + slot) * n_in] = jv;
             ++slot;
         }
+        wk_local_constraint_rows(T, in + 1, col, n_in);
         for (int o = 0; o < n_out; ++o)
             if (!isfinite(y0[o])) col[(size_t)o * n_in] = NAN;
     }
@@ -295,6 +310,7 @@ __device__ inline void wk_local_columns(const DevTables& T, const WarpAux& A, do
             col[(size_t)(nq + nz + T.n_auxres + T.n_kc + slot) * n_in] = wk_integrand_term_delta(T, A, ws, gr, dir, v0, v1) * inv;
             ++slot;
         }
+        wk_local_constraint_rows(T, in + 1, col, n_in);
         // a non-finite nominal output poisons its whole row, as it does when the full function is differenced
         for (int o = 0; o < n_out; ++o)
             if (!isfinite(y0[o])) col[(size_t)o * n_in] = NAN;
