@@ -146,14 +146,14 @@ def make_iterates(m, prob, n, kind):
     return xs
 
 
-def config_dict(workload, desc, dims, fd, sparsity, iterates_kind, n_iterates):
-    """the keys both arms report (the driver compares them)"""
+def config_dict(workload, desc, dims, fd, sparsity, iterates_kind):
+    """the workload description: identical in both arms (the driver compares the two dicts); run details go under "run" """
     return {"workload": workload + ": " + desc, "n_grid": int(dims["n_grid"]), "n_var": int(dims["n_var"]), "n_con": int(dims["n_con"]),
             "nnz_jac": int(dims["nnz_jac"]), "sparsity_detection": sparsity, "fd": FD_NAMES[fd],
-            "iterates": ("%d seeded iterates: reference walking trajectory (referenceCoordinates.sto splines) + U(-0.02,0.02)*(upper-lower) "
+            "iterates": ("seeded iterates: reference walking trajectory (referenceCoordinates.sto splines) + U(-0.02,0.02)*(upper-lower) "
                          "on coordinates and speeds, activations/excitations U(0.01,1), lumbar U(-10,10), tf = 0.47008941"
                          if iterates_kind == "trajectory" else
-                         "%d seeded iterates: bounds midpoint + 0.1*U(-1,1)*half-range") % n_iterates}
+                         "seeded iterates: bounds midpoint + 0.1*U(-1,1)*half-range")}
 
 
 # ------------------------------------------------------------------------------------------------ clocks
@@ -255,7 +255,8 @@ def run_reference(args, rank, workload):
     line = {"metric": METRIC, "value": val, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * dt / n, "higher_is_better": True, "scaling": "strong" if workload == "config5" else "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": config_dict(workload, desc, d, fd, "none", args.iterates, 10),
+            "config": config_dict(workload, desc, d, fd, "none", args.iterates),
+            "run": {"n_iterates": 10},
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
                              "sample": "%d full eval_jac_g calls (all %d grid points) in %.1f s wall; CPU restatement (oracle/) pinned to "
                                        "reference-produced CMC results, not the reference binary: Simbody/CasADi/IPOPT are absent so the "
@@ -495,8 +496,8 @@ def main():
         peak = m.measure_fp64_peak(local_rank)
         roof, n_exec = roofline(m, r, args, local_rank, workload, peak)
         workers = ev.working_ranks()
-        cfg = config_dict(workload, r["desc"], d, r["fd"], args.sparsity, args.iterates, r["n_x"])
-        cfg.update({
+        cfg = config_dict(workload, r["desc"], d, r["fd"], args.sparsity, args.iterates)
+        run = ({"n_iterates": r["n_x"],
             "l2": ("inputs larger than L2: step k reads iterate k %% %d out of %.0f MB of iterates and writes CSC buffer k %% %d of %.0f MB "
                    "(L2 = 126 MB); no flush, code and model tables stay warm as in an IPOPT loop"
                    % (r["n_x"], r["n_x"] * 8e-6 * d["n_var"], r["n_v"], r["n_v"] * 8e-6 * d["nnz_jac"])) if args.l2 == "rotate" else
@@ -506,7 +507,7 @@ def main():
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": r["dev_ms"] / args.steps, "higher_is_better": True, "scaling": "strong" if workload == "config5" else "weak",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg, "clocks": clocks,
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg, "run": run, "clocks": clocks,
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": 8 * d["n_var"], "d2h_bytes_per_step": 8 * d["nnz_jac"],
                     "ms_per_step": r["e2e_ms"] / args.steps, "api": "mocob200_eval_jac_g(handle, x_host_pinned, values_host_pinned)"},
             "gpu_launches": int(r["launches"]), "roofline": roof}

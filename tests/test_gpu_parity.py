@@ -587,3 +587,66 @@ def test_pose_reusing_thread_evaluation_matches_the_whole_evaluation(pkg, orc, n
     assert np.array_equal(np.isnan(out["1"]), np.isnan(out["0"]))
     assert np.nanmax(np.abs(out["1"] - out["0"]) / scale) < 1e-8
     assert np.nanmax(np.abs(out["1"] - Jo) / scale) < 1e-7
+
+
+@pytest.mark.parametrize("name", ["gait2d_tracking", "gait2d_prediction"])
+def test_gait2d_implicit_mode_matches_oracle(pkg, orc, name):
+    """MultibodySystemImplicit on the gait model (CasOCFunction.cpp:317-331): residuals, zdot and the FD blocks with the
+    acceleration variables as inputs, values 1e-10, Jacobian entries 1e-7 of the row scale at round-off-negligible steps."""
+    p = pkg.Problem.load(golden(name + ".mb20"), "multibody_dynamics_mode=implicit;num_mesh_intervals=6")
+    ev, o = pkg.Evaluator(p), orc.Oracle(p)
+    assert ev.dims.nd == 10 and ev.dims.n_in == 1 + 38 + 19 + 10
+    x = p.make_iterate(seed=9, spread=0.3)
+    Y, Yo = ev.eval_points(x), o.eval_points(x)
+    assert relerr(Y, Yo) < 1e-10
+    assert relerr(ev.eval_g(x), o.eval_g(x)) < 1e-10
+    for fd, h in ((FD_FORWARD, 1e-4), (FD_CENTRAL, 1e-3)):
+        ev.set_fd(fd, h, 0)
+        o.set_fd(fd, h, 0)
+        v, vo = ev.eval_jac_g(x), o.eval_jac_g(x)
+        colptr, rowidx = ev.structure()
+        assert np.array_equal(rowidx, o.structure()[1])
+        assert rowscaled_err(v, vo, rowidx, ev.dims.n_con) < 1e-7
+
+
+def test_config5_full_size_jacobian_matches_oracle(pkg, orc):
+    """BASELINE config 5 (gaitPrediction, 800 intervals = 1601 grid points, central differences) at full size: every CSC value
+    against the oracle's — 1e-7 of the row scale with a fixed round-off-negligible step, the refinement noise bound at
+    CasADi's default steps. One oracle Jacobian of this size costs a fraction of a second on the host cores."""
+    p = pkg.Problem.load(golden("gait2d_prediction.mb20"), "num_mesh_intervals=800")
+    ev, o = pkg.Evaluator(p), orc.Oracle(p)
+    assert ev.dims.n_grid == 1601
+    x = p.make_iterate(seed=3, spread=0.1)
+    colptr, rowidx = ev.structure()
+    assert np.array_equal(rowidx, o.structure()[1])
+    ev.set_fd(FD_CENTRAL, 1e-3, 0)
+    o.set_fd(FD_CENTRAL, 1e-3, 0)
+    assert rowscaled_err(ev.eval_jac_g(x), o.eval_jac_g(x), rowidx, ev.dims.n_con) < 1e-7
+    ev.set_fd(FD_CENTRAL)
+    o.set_fd(FD_CENTRAL)
+    v, vo = ev.eval_jac_g(x), o.eval_jac_g(x)
+    rowmax = np.zeros(ev.dims.n_con)
+    np.maximum.at(rowmax, rowidx, np.abs(vo))
+    rel = np.abs(v - vo) / (np.abs(vo) + rowmax[rowidx] + 1e-300)
+    assert rel.max() < 2e-3 and np.median(rel) < 1e-6
+
+
+@pytest.mark.parametrize("workload", ["config3", "config5"])
+def test_bench_trajectory_iterates_match_oracle(pkg, orc, workload):
+    """The bench's default iterates (reference walking trajectory + bounded noise, feet in contact) at the bench's
+    full sizes: point outputs and g against the oracle to 1e-10."""
+    import bench
+
+    fixture, opts, fd, _ = bench.WORKLOADS[workload]
+    p = pkg.Problem.load(golden(fixture), opts)
+    x = bench.make_iterates(pkg, p, 2, "trajectory")[1]
+    ev, o = pkg.Evaluator(p), orc.Oracle(p)
+    Y, Yo = ev.eval_points(x), o.eval_points(x)
+    assert np.isfinite(Yo).all()
+    # with the feet on the ground the contact stiffness (3e6 N/m^1.5 smoothed Hertz) multiplies the 1e-16 pose differences of
+    # the two formulations: measured 1.0e-10 on the raw point outputs at 1601 points; the constraint values keep 1e-10
+    assert relerr(Y, Yo) < 5e-10
+    assert relerr(ev.eval_g(x), o.eval_g(x)) < 1e-10
+    # the feet are on the ground: the contact forces are not negligible in these iterates
+    nq = 10
+    assert np.abs(Yo[:, :nq]).max() > 10.0
