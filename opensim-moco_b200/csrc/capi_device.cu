@@ -195,7 +195,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     std::vector<int> cwDirs;
     std::vector<int> p0Dirs, p1Dirs, p2Dirs, cdDirs, locDir, locKind, locOwner, locRole, dirClass(L.n_in, 4);
     {
-        const char* e = getenv("MOCOB200_FD_LOCAL");
+        const char* e = devEnv("MOCOB200_FD_LOCAL");
         bool local = !(e && e[0] == '0');
         for (int g = 0; g < T.ngoal; ++g) {
             const int* gr = T.idx + T.o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
@@ -307,7 +307,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     // right-hand sides / solutions of the local columns: reuse the wrench + composite-inertia scratch, dead by then
     A.o_Rm = ((T.nmus + T.ncact) * nq <= A.o_tau - A.o_F) ? A.o_F : take((T.nmus + T.ncact) * nq);
     A.ws_doubles = o;
-    { const char* e = getenv("MOCOB200_POISON_SCRATCH"); A.poison = (e && e[0] == '1') ? 1 : 0; }
+    { const char* e = devEnv("MOCOB200_POISON_SCRATCH"); A.poison = (e && e[0] == '1') ? 1 : 0; }
     return warp_kernels_configure(A, err);
 }
 
@@ -555,7 +555,7 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     std::vector<int> idx;
     mocob200_tables reduced;
     {
-        const char* e = getenv("MOCOB200_MERGE_WELDS"); // development A-B switch, read once at create
+        const char* e = devEnv("MOCOB200_MERGE_WELDS"); // development A-B switch, read once at create
         if (e && e[0] == '0') { dbl.assign(callerT->dbl, callerT->dbl + callerT->n_dbl); idx.assign(callerT->idx, callerT->idx + callerT->n_int); reduced = *callerT; reduced.dbl = dbl.data(); reduced.idx = idx.data(); }
         else h->mergedBodies = mergeWeldedBodies(*callerT, dbl, idx, reduced);
     }
@@ -636,7 +636,7 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     G.rowidx = (const int*)own(devUpload(L.rowidx));
     G.nnzcol = (const int*)own(devUpload(L.nnzcol));
     {
-        const char* k = getenv("MOCOB200_KERNEL");
+        const char* k = devEnv("MOCOB200_KERNEL");
         h->kernelMode = (k && std::string(k) == "thread") ? 2 : (k && std::string(k) == "warp") ? 1 : 0;
         // the thread-per-evaluation dynamics handle the constant-axis joints only: function-based joints run on the warp kernels
         if (T->ncustom > 0) {
@@ -699,8 +699,8 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
             for (int k = 0; k < 3; ++k) { h->runs[6 * r + 2 * k] = L.colptr[c0[k]]; h->runs[6 * r + 2 * k + 1] = L.colptr[c1[k]]; }
         }
     }
-    { const char* e = getenv("MOCOB200_VEL_KERNEL"); h->velKernel = !(e && e[0] == '0'); }
-    h->allowGraph = !(getenv("MOCOB200_GRAPH") && getenv("MOCOB200_GRAPH")[0] == '0') && !getenv("MOCOB200_TIMING");
+    { const char* e = devEnv("MOCOB200_VEL_KERNEL"); h->velKernel = !(e && e[0] == '0'); }
+    h->allowGraph = !(devEnv("MOCOB200_GRAPH") && devEnv("MOCOB200_GRAPH")[0] == '0') && !devEnv("MOCOB200_TIMING");
     if (h->eff > 1) { // a communicator only when more than one rank owns grid points
         if (!nccl_unique_id) return fail(MOCOB200_ERR_ARG, "world > 1 needs a NCCL unique id");
         std::string e;

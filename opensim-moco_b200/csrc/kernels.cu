@@ -650,12 +650,12 @@ void launch_points_fd_flat(const DevTables& T, const DevLayout& L, const FdSetti
     if (n <= 0) return;
     // MOCOB200_FLAT_MINBLOCKS: resident 64-thread blocks per SM the register allocation must allow (4: 255 registers,
     // 8: 128 registers); MOCOB200_FLAT_PAIR=0: central differences with both sides on one thread.
-    // Measured on config 5 (profiles/flat_variants_r01.txt): unpaired 4 -> 427 Jac/s, 8 -> 381; paired 4 -> 493, 8 -> 632:
+    // Measured on config 5 (profiles/r01/flat_variants_r01.txt): unpaired 4 -> 427 Jac/s, 8 -> 381; paired 4 -> 493, 8 -> 632:
     // the paired kernel has twice the threads, and only the 128-register build keeps them all resident in one wave.
     // (read per launch so that tests can switch them; steady-state launches are CUDA-graph replays)
-    const char* ePair = getenv("MOCOB200_FLAT_PAIR");
+    const char* ePair = devEnv("MOCOB200_FLAT_PAIR");
     const bool paired = fd.scheme == MOCOB200_FD_CENTRAL && (!ePair || atoi(ePair) != 0);
-    const char* eMinb = getenv("MOCOB200_FLAT_MINBLOCKS");
+    const char* eMinb = devEnv("MOCOB200_FLAT_MINBLOCKS");
     const int minb = eMinb && atoi(eMinb) > 0 ? atoi(eMinb) : (paired ? 8 : 4);
     const bool small = L.small_size != 0;
     if (paired) {

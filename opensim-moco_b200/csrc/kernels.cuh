@@ -1,12 +1,21 @@
 // Kernels of the evaluator: point functions over the grid, their finite-difference blocks,
 // endpoint functions, and the assembly of g / jac_g (CSC) / grad_f.
 #pragma once
+#include <cstdlib>
 #include <string>
 
 #include "point_eval.cuh"
 #include "point_warp.cuh"
 
 namespace mocob200 {
+
+// Development A-B switches (MOCOB200_FD_LOCAL, _KERNEL, _FLAT_PAIR, ...: scripts/README.md) are honoured only when
+// MOCOB200_DEVELOPER_SWITCHES=1 is set as well (tests and measurement scripts do); a production process is not steered by
+// stray environment variables. Settings a solver needs have ABI setters (mocob200_set_fd, _set_min_points_per_rank, ...).
+inline const char* devEnv(const char* name) {
+    static const bool on = [] { const char* e = std::getenv("MOCOB200_DEVELOPER_SWITCHES"); return e && e[0] == '1'; }();
+    return on ? std::getenv(name) : nullptr;
+}
 
 #define MOCOB200_MAX_IN 160
 #define MOCOB200_MAX_OUT 72

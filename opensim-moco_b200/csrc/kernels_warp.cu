@@ -288,7 +288,7 @@ static size_t warpSmemBytes(const WarpAux& A) { return smemBytesFor(A, A.wpb); }
 // point's blob is read from L2 once and served to the other warps by L1
 static int phase1Warps(const WarpAux& A) {
     const int per = A.n_p1;
-    static const int forced = getenv("MOCOB200_P1W") ? atoi(getenv("MOCOB200_P1W")) : 0; // A-B tests: warps per phase-1 block
+    static const int forced = devEnv("MOCOB200_P1W") ? atoi(devEnv("MOCOB200_P1W")) : 0; // A-B tests: warps per phase-1 block
     if (forced >= 1 && forced <= 32 && smemBytesFor(A, forced) <= 220 * 1024) return forced;
     return (per >= 1 && per <= 32 && smemBytesFor(A, per) <= 220 * 1024) ? per : A.wpb;
 }
@@ -296,9 +296,9 @@ static int phase1Warps(const WarpAux& A) {
 bool warp_kernels_configure(WarpAux& A, std::string& err) {
     // choose the number of warps per block so that a block's scratch fits and several blocks share an SM
     A.wpb = 4;
-    if (const char* e = getenv("MOCOB200_WPB")) A.wpb = atoi(e) > 0 ? atoi(e) : 4;
-    { const char* e = getenv("MOCOB200_LOCKSTEP"); A.lockstep = (e && e[0] == '1') ? 1 : 0; }
-    while (A.wpb > 1 && warpSmemBytes(A) > (getenv("MOCOB200_WPB") ? 220 : 96) * 1024) A.wpb >>= 1;
+    if (const char* e = devEnv("MOCOB200_WPB")) A.wpb = atoi(e) > 0 ? atoi(e) : 4;
+    { const char* e = devEnv("MOCOB200_LOCKSTEP"); A.lockstep = (e && e[0] == '1') ? 1 : 0; }
+    while (A.wpb > 1 && warpSmemBytes(A) > (devEnv("MOCOB200_WPB") ? 220 : 96) * 1024) A.wpb >>= 1;
     const size_t bytes = std::max(warpSmemBytes(A), smemBytesFor(A, phase1Warps(A)));
     if (warpSmemBytes(A) > 227 * 1024) { err = "per-warp scratch exceeds shared memory"; return false; }
     // the attribute is per function, not per handle: only ever raise it
@@ -324,7 +324,7 @@ bool warp_kernels_configure(WarpAux& A, std::string& err) {
 void launch_wpoints_nominal(const DevTables& T, const WarpAux& A, const DevLayout& L, const double* d_x, double* d_Y, double* d_cfg,
                             int p0, int np, cudaStream_t s) {
     if (np <= 0) return;
-    static const bool timing = getenv("MOCOB200_TIMING") != nullptr; // development stopwatch
+    static const bool timing = devEnv("MOCOB200_TIMING") != nullptr; // development stopwatch
     static cudaEvent_t ne[2] = {nullptr, nullptr};
     if (timing) {
         if (!ne[0]) { cudaEventCreate(&ne[0]); cudaEventCreate(&ne[1]); }
@@ -341,7 +341,7 @@ int launch_wpoints_fd(const DevTables& T, const WarpAux& A, const DevLayout& L, 
     if (fd.scheme != MOCOB200_FD_CENTRAL) {
         const long items0 = (long)np * (1 + A.n_p0), items1 = (long)np * A.n_p1, items2 = (long)np * A.n_p2;
         // development stopwatch (MOCOB200_TIMING=1): per-stage CUDA-event times of the previous call on stderr
-        static const bool timing = getenv("MOCOB200_TIMING") != nullptr;
+        static const bool timing = devEnv("MOCOB200_TIMING") != nullptr;
         static cudaEvent_t te[4] = {nullptr, nullptr, nullptr, nullptr};
         if (timing) {
             if (!te[0]) for (auto& e : te) cudaEventCreate(&e);

@@ -1,6 +1,7 @@
 #!/bin/bash
 # A-B of the development switches of the thread-per-evaluation kernels on the config-5 bench workload (run under gpurun).
 # prints: switches, device Jac/s, e2e Jac/s, FD-stage ms, assembly ms
+export MOCOB200_DEVELOPER_SWITCHES=1  # the library ignores its A-B switches without it
 run() {
     env "$@" python bench.py --steps 40 --warmup 5 --workload config5 --cpu-seconds 1 2>/dev/null | tail -1 | python -c "
 import sys, json

@@ -1,6 +1,7 @@
 #!/bin/bash
 # config 5: flat thread kernel variants — central sides paired on adjacent lanes or not (MOCOB200_FLAT_PAIR), compiled for
 # 4 / 8 resident 64-thread blocks per SM (MOCOB200_FLAT_MINBLOCKS)
+export MOCOB200_DEVELOPER_SWITCHES=1  # the library ignores its A-B switches without it
 mkdir -p gpurun_out
 for pair in 0 1; do for mb in 4 8; do
   tag=p${pair}_mb$mb

@@ -1,4 +1,5 @@
 """Device-side latency of the stages of one Jacobian (config 3 / config 5), warp vs thread kernels."""
+import os as _os; _os.environ.setdefault("MOCOB200_DEVELOPER_SWITCHES", "1")
 import os, sys, time
 import numpy as np, torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))

@@ -1,6 +1,7 @@
 #!/bin/bash
 # ncu --set full captures of the point-function kernels of both bench workloads, exported on the box as CSV (the .ncu-rep
 # files are tens of MB; gpurun_out/ is limited to 64 MiB). Run under gpurun from the repo root, after a plain bench run.
+export MOCOB200_DEVELOPER_SWITCHES=1  # the library ignores its A-B switches without it
 mkdir -p gpurun_out
 python bench.py --steps 5 --warmup 3 > /dev/null 2>&1 || exit 1
 MOCOB200_GRAPH=0 ncu --set full --clock-control none --import-source on -k regex:"k_wpoints_fd1" -c 8 -o /tmp/c3 \

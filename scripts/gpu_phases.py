@@ -1,4 +1,5 @@
 """Development: phase stopwatch of one warp evaluation (library built with MOCOB200_PROFILE_PHASES=1) and the NaN hunt."""
+import os as _os; _os.environ.setdefault("MOCOB200_DEVELOPER_SWITCHES", "1")
 import ctypes as C, os, sys
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))

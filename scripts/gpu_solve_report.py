@@ -1,5 +1,5 @@
 """Sliding-mass NLP solved twice with the same host SQP loop (tests/nlp_solve.py): callbacks from the GPU evaluator and from the
-CPU oracle. Prints iterations, objective and time spent inside the callbacks -> profiles/solve_r01.json. A 65-variable problem
+CPU oracle. Prints iterations, objective and time spent inside the callbacks -> profiles/r01/solve_r01.json. A 65-variable problem
 is launch-latency territory: the point of the report is identical convergence, not speed."""
 import json
 import os

@@ -7,6 +7,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "oracle"))
 GOLDEN = os.path.join(ROOT, "tests", "golden")
+# the library honours its development A-B switches (MOCOB200_FD_LOCAL, _KERNEL, ...) only with this set (kernels.cuh: devEnv)
+os.environ.setdefault("MOCOB200_DEVELOPER_SWITCHES", "1")
 
 
 def pytest_configure(config):
