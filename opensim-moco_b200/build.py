@@ -24,7 +24,7 @@ def build(force=False, verbose=False):
     os.makedirs(objdir, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
     headers.append(os.path.join(HERE, "..", "include", "mocob200.h"))
-    objs = []
+    objs, cmds = [], []
     for src in HOST_SRCS + CUDA_SRCS:
         s = os.path.join(CSRC, src)
         o = os.path.join(objdir, src + ".o")
@@ -35,9 +35,17 @@ def build(force=False, verbose=False):
                 cmd += ["-DMOCOB200_PROFILE_PHASES"]
             if src.endswith(".cu"):
                 cmd += ARCH + ["-Xptxas", "-v"] if verbose else ARCH
+            cmds.append(cmd)
+    if cmds:  # translation units are independent: compile them side by side
+        from concurrent.futures import ThreadPoolExecutor
+
+        def run(cmd):
             if verbose:
                 print(" ".join(cmd), flush=True)
             subprocess.check_call(cmd)
+
+        with ThreadPoolExecutor(max_workers=min(len(cmds), os.cpu_count() or 1)) as pool:
+            list(pool.map(run, cmds))
     if force or _newer(OUT, objs):
         cmd = [NVCC, "-shared", "-o", OUT] + objs + ARCH + ["-lcudart", "-ldl"]
         if verbose:
