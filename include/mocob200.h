@@ -253,6 +253,17 @@ int mocob200_eval_jac_g(mocob200_handle*, const double* x, double* values);
  * cuda_stream == NULL: no ordering is added (NULL cannot be told from the legacy default stream); call mocob200_sync. */
 int mocob200_eval_jac_g_device(mocob200_handle*, const double* d_x, double* d_values, void* cuda_stream);
 int mocob200_eval_g_device(mocob200_handle*, const double* d_x, double* d_g, void* cuda_stream);
+/* eval_g for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc). NO COUNTERPART IN THE REFERENCE. Same result as
+ * mocob200_eval_g_device (d_x[n_var] -> d_g[n_con], device pointers), but the pipeline's scratch (per-point outputs, goal
+ * integrals, endpoint values) is a static __device__ array inside the library instead of buffers of the handle, and the call
+ * itself allocates nothing (no cudaMalloc / cudaFree / event or stream creation): it clears the part of the array it uses and
+ * queues its kernels on cuda_stream (NULL: the handle's own stream; then call mocob200_sync). Limits: single-rank handles;
+ * scratch need = 8 * (n_grid * n_out + goal terms) bytes <= MOCOB200_STATIC_SCRATCH_BYTES, else MOCOB200_ERR_ARG with the
+ * sizes in mocob200_last_error. Every GPU that loads the library holds that array until exit. ALL calls (of all handles)
+ * share it and it keeps the last call's contents: calls that overlap on the GPU (different streams, no ordering) race. */
+#define MOCOB200_STATIC_SCRATCH_BYTES (1 << 20)
+int mocob200_eval_g_static(mocob200_handle*, const double* d_x, double* d_g, void* cuda_stream);
 /* n independent single-rank problems on one device evaluated side by side (one handle each; each on its own stream,
  * forked from and joined to handles[0]'s stream, so mocob200_mark / mocob200_sync on handles[0] cover the batch).
  * d_values may be NULL (or hold NULL entries): results stay in the handles' own buffers. Replaces running one

@@ -24,6 +24,7 @@ ABI_SYMBOLS = [
     "mocob200_create", "mocob200_nccl_unique_id", "mocob200_destroy", "mocob200_last_error", "mocob200_get_dims",
     "mocob200_set_fd", "mocob200_jac_g_structure", "mocob200_eval_points", "mocob200_eval_f", "mocob200_eval_g",
     "mocob200_eval_grad_f", "mocob200_eval_jac_g", "mocob200_eval_jac_g_device", "mocob200_eval_g_device",
+    "mocob200_eval_g_static",
     "mocob200_eval_jac_g_batch",
     "mocob200_sync", "mocob200_mark", "mocob200_elapsed_ms", "mocob200_launch_count", "mocob200_last_kernel_ms",
     "mocob200_point_evals_per_jacobian", "mocob200_executed_evals", "mocob200_working_ranks", "mocob200_uses_warp_kernels",
@@ -88,6 +89,7 @@ def lib():
         L.mocob200_eval_jac_g.argtypes = [vp, vp, vp]
         L.mocob200_eval_jac_g_device.argtypes = [vp, vp, vp, vp]
         L.mocob200_eval_g_device.argtypes = [vp, vp, vp, vp]
+        L.mocob200_eval_g_static.argtypes = [vp, vp, vp, vp]
         L.mocob200_eval_jac_g_batch.argtypes = [C.POINTER(vp), C.c_int, C.POINTER(vp), C.POINTER(vp)]
         L.mocob200_sync.argtypes = [vp]
         L.mocob200_mark.argtypes = [vp, C.c_int]
@@ -313,6 +315,11 @@ class Evaluator:
     def eval_g_device(self, d_x_ptr, d_g_ptr=None):
         self._ck(lib().mocob200_eval_g_device(self._h, C.c_void_p(d_x_ptr), C.c_void_p(d_g_ptr) if d_g_ptr else None, None),
                  "eval_g_device")
+
+    def eval_g_static(self, d_x_ptr, d_g_ptr, stream_ptr=None):
+        """eval_g on device pointers with the library's static scratch array: allocates nothing (include/mocob200.h)."""
+        self._ck(lib().mocob200_eval_g_static(self._h, C.c_void_p(d_x_ptr), C.c_void_p(d_g_ptr),
+                                              C.c_void_p(stream_ptr) if stream_ptr else None), "eval_g_static")
 
     def sync(self):
         self._ck(lib().mocob200_sync(self._h), "sync")

@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1185,3 +1186,60 @@ int mocob200_measure_fp64_peak(int device, double* tflops) {
 }
 
 } // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// mocob200_eval_g_static: eval_g for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that
+// forbid cudaMalloc). No counterpart in the reference. The pipeline's scratch
+// (per-point outputs Y, goal integrals, endpoint values) lives in the file-scope array below instead of the handle's buffers:
+// every GPU that loads the library holds MOCOB200_STATIC_SCRATCH_BYTES until exit, all calls (all handles) share it, it
+// keeps the last call's contents, and calls that overlap on the GPU race. In host code the array's name is a host-side
+// stand-in: the kernels get the address cudaGetSymbolAddress returns, looked up once per device with that device current.
+static __device__ __align__(256) double g_static_scratch[MOCOB200_STATIC_SCRATCH_BYTES / sizeof(double)];
+
+namespace {
+std::mutex g_static_mu;
+double* g_static_ptr[64] = {nullptr}; // device address of g_static_scratch, per device ordinal
+double* staticScratch(mocob200_handle* h) {
+    int dev = -1;
+    if (!h->ck(cudaGetDevice(&dev), "cudaGetDevice")) return nullptr;
+    if (dev < 0 || dev >= 64) { h->err = "eval_g_static: device ordinal out of range"; return nullptr; }
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_ptr[dev]) {
+        double* ptr = nullptr;
+        if (!h->ck(cudaGetSymbolAddress((void**)&ptr, g_static_scratch), "cudaGetSymbolAddress(static scratch)")) return nullptr;
+        g_static_ptr[dev] = ptr;
+    }
+    return g_static_ptr[dev];
+}
+inline size_t roundUp32(size_t n) { return (n + 31) / 32 * 32; } // 256-byte sections
+} // namespace
+
+extern "C" int mocob200_eval_g_static(mocob200_handle* h, const double* d_x, double* d_g, void* cuda_stream) {
+    if (!h || !d_x || !d_g) return MOCOB200_ERR_ARG;
+    if (h->world != 1 || h->eff != 1) { h->err = "eval_g_static: single-rank handles only"; return MOCOB200_ERR_UNSUPPORTED; }
+    const Layout& L = h->L;
+    const size_t nY = roundUp32((size_t)L.n_grid * L.n_out), nI = roundUp32(3 * (size_t)L.n_integrand + 1),
+                 nG = roundUp32((size_t)h->DL.n_eout_total + 1), nE = roundUp32((size_t)(h->DL.n_eout_total + 1) * L.n_ein);
+    const size_t need = (nY + nI + nG + nE) * sizeof(double);
+    if (need > (size_t)MOCOB200_STATIC_SCRATCH_BYTES) {
+        h->err = "eval_g_static: the problem needs " + std::to_string(need) + " bytes of scratch (" + std::to_string(L.n_grid) +
+                 " grid points x " + std::to_string(L.n_out) + " point outputs), more than the static limit of " +
+                 std::to_string((size_t)MOCOB200_STATIC_SCRATCH_BYTES) + " bytes (MOCOB200_STATIC_SCRATCH_BYTES); use mocob200_eval_g_device";
+        return MOCOB200_ERR_ARG;
+    }
+    if (!h->ck(cudaSetDevice(h->device), "cudaSetDevice")) return MOCOB200_ERR_CUDA;
+    double* base = staticScratch(h);
+    if (!base) return MOCOB200_ERR_CUDA;
+    double *sY = base, *sI = sY + nY, *sG = sI + nI, *sE = sG + nG;
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : h->stream; // everything is queued on ONE stream, in order
+    // the array keeps the previous call's contents: clear the part this call uses
+    if (!h->ck(cudaMemsetAsync(base, 0, need, s), "clear static scratch")) return MOCOB200_ERR_CUDA;
+    const int np = h->p1 - h->p0;
+    if (h->warpFor(np)) launch_wpoints_nominal(h->DT, h->WA, h->DL, d_x, sY, nullptr, h->p0, np, s);
+    else launch_points_nominal(h->DT, h->DL, d_x, sY, h->p0, np, s);
+    launch_integrals(h->DL, d_x, sY, nullptr, sI, false, s);
+    launch_endpoint(h->DT, h->DL, h->fd, d_x, sI, sG, sE, false, s);
+    launch_assemble_g(h->DT, h->DL, d_x, sY, sG, d_g, s);
+    h->launches += 2 + (L.n_integrand > 0) + (h->DL.n_eout_total > 0) + (h->DL.n_path_rows > 0);
+    return h->ck(cudaGetLastError(), "eval_g_static") ? MOCOB200_OK : MOCOB200_ERR_CUDA;
+}
