@@ -512,6 +512,9 @@ def main():
                     "ms_per_step": r["e2e_ms"] / args.steps, "api": "mocob200_eval_jac_g(handle, x_host_pinned, values_host_pinned)"},
             "gpu_launches": int(r["launches"]), "roofline": roof}
         line.update(sub)
+        if world > 1:
+            line["scaling_note"] = ("this line is config 5 (the configuration that shards, BASELINE.json configs[4]); the plain N = 1 bench line is "
+                                    "config 3 (101 grid points, does not shard): strong-scaling efficiency = value / (n_gpus * n1.value)")
         # CPU baseline leg (rank 0): the oracle on all host threads, bounded by --cpu-seconds
         val, n, dt, threads, _ = cpu_oracle_rate(m, r["prob"], r["fd"], r["xs_host"], args.cpu_seconds)
         line["cpu_baseline"] = {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
