@@ -133,7 +133,13 @@ typedef struct mocob200_tables {
      * Lagrange multiplier each (and one velocity-correction slack each with enforce_constraint_derivatives + Hermite-Simpson) */
     int ncoupler;
     int o_cc_i, o_cc_d;
-    int reserved[7];
+    /* prescribed kinematics (Components/PositionMotion.cpp:30-77, MocoProblemRep.cpp:70-100,546-560,
+     * CasOCProblem.h:223-233,485-517): prescribed != 0 = every coordinate follows a function of time, idx[o_presc_i + k] = the
+     * piecewise polynomial of coordinate k (value; speed and acceleration are its derivatives). The NLP then has no coordinate
+     * value / speed states and no acceleration variables, no kinematic-constraint rows, and nq multibody residual rows per grid
+     * point (implicit mode is required, MocoCasADiSolver.cpp:147-151); multipliers stay variables and their forces are applied */
+    int prescribed, o_presc_i;
+    int reserved[5];
 } mocob200_tables;
 
 /* Solver-side settings: mirrors the properties of MocoDirectCollocationSolver /

@@ -205,11 +205,13 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
                 k != MOCOB200_GOAL_SUM_SQUARED_STATE && k != MOCOB200_GOAL_CONTROL_TRACKING)
                 local = false; // an integrand this analysis does not know
         }
-        const int ns = 2 * nq + T.nz, iz = 1 + 2 * nq, ic = 1 + ns, ider = 1 + ns + T.nc + L.nm, iaux = ider + (L.implicit ? nq : 0);
+        const int nqs = L.nqs; // coordinate states among the inputs (0 with prescribed kinematics)
+        const int nacc = (L.implicit && !L.prescribed) ? nq : 0;
+        const int ns = 2 * nqs + T.nz, iz = 1 + 2 * nqs, ic = 1 + ns, ider = 1 + ns + T.nc + L.nm, iaux = ider + nacc;
         for (int d = 0; d < L.n_in; ++d) {
-            if (d >= 1 && d <= nq) { dirClass[d] = 0; continue; }
-            if ((d > nq && d <= 2 * nq) || (L.implicit && d >= ider && d < ider + nq)) { dirClass[d] = 1; continue; }
-            if (d == 0) { dirClass[d] = 2; continue; }
+            if (d >= 1 && d <= nqs) { dirClass[d] = 0; continue; }
+            if ((d > nqs && d <= 2 * nqs) || (d >= ider && d < ider + nacc)) { dirClass[d] = 1; continue; }
+            if (d == 0) { dirClass[d] = L.prescribed ? 0 : 2; continue; } // prescribed kinematics: time moves every coordinate
             if (!local) continue;
             int owners = 0, kind = -1, owner = -1, role = -1;
             for (int m = 0; m < T.nmus; ++m) {
@@ -232,7 +234,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
             else if (dirClass[d] == 1) p1Dirs.push_back(d);
             else if (dirClass[d] != 3) p2Dirs.push_back(d);
         }
-        h->WA.time_integrands_only = (local && T.nxforce == 0) ? 1 : 0; // external forces are functions of time
+        h->WA.time_integrands_only = (local && T.nxforce == 0 && !L.prescribed) ? 1 : 0; // external forces are functions of time
     }
     // all topology arrays live in one int pool so that a block can stage them with one copy loop
     std::vector<int> pool;
@@ -295,6 +297,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     A.o_cg = take(3 * nb); A.o_Io = take(6 * nb); A.o_ppos = take(3 * npp); A.o_prel = take(3 * npp);
     A.o_dpl = take(3 * A.nmpp); A.o_mloc = take(3 * A.nmpp); A.o_ref = take(T.nppoly); A.o_mact = take(T.nmus); A.o_M = take(nq * nq);
     A.o_cjs = take(30 * T.ncustom);
+    A.o_pk = take(L.prescribed ? 3 * nq : 0); // q, u, udot of prescribed kinematics
     A.blob_pos_end = o;
     // velocity-dependent block
     A.o_w = take(3 * nb); A.o_v = take(3 * nb); A.o_al = take(3 * nb); A.o_ac = take(3 * nb);
@@ -592,9 +595,11 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     D.nxforce = T->nxforce; D.o_xforce_i = T->o_xforce_i;
     D.ncoupler = T->ncoupler; D.o_cc_i = T->o_cc_i; D.o_cc_d = T->o_cc_d;
     D.nm = L.nm; D.n_kc = L.n_kc; D.enforce_derivs = L.enforce_derivs;
+    D.prescribed = L.prescribed; D.o_presc_i = T->o_presc_i;
     D.implicit = L.implicit; D.n_auxres = L.n_auxres; D.n_integrand = L.n_integrand;
     // layout
     DevLayout& G = h->DL;
+    G.prescribed = L.prescribed; G.nqs = L.nqs;
     G.scheme = L.scheme; G.implicit = L.implicit; G.nq = L.nq; G.nz = L.nz; G.ns = L.ns; G.nc = L.nc; G.nd = L.nd; G.n_in = L.n_in;
     G.n_auxres = L.n_auxres; G.n_integrand = L.n_integrand; G.n_dyn_out = L.n_dyn_out; G.n_out = L.n_out;
     G.n_mesh = L.n_mesh; G.n_grid = L.n_grid; G.n_intervals = L.n_intervals; G.n_var = L.n_var; G.n_con = L.n_con; G.nnz = L.nnz;

@@ -109,6 +109,8 @@ int mocob200_problem_load_opts(const char* path, const char* options, mocob200_p
             applySettingsToTranscription(S, *fp, /*onlyKeysGiven=*/true);
         }
         fp->rebind();
+        if (fp->tables.prescribed && fp->tr.dynamics_mode != MOCOB200_DYNAMICS_IMPLICIT) // MocoCasADiSolver.cpp:147-151
+            throw std::runtime_error("Prescribed kinematics (PositionMotion) requires implicit dynamics mode.");
         auto p = new mocob200_problem;
         p->fp = std::move(fp);
         *out = p;
@@ -133,7 +135,7 @@ namespace {
 // implicit auxiliary derivatives
 std::vector<std::string> derivativeNamesOf(const FlatProblem& fp) {
     std::vector<std::string> v;
-    if (fp.tr.dynamics_mode == MOCOB200_DYNAMICS_IMPLICIT)
+    if (fp.tr.dynamics_mode == MOCOB200_DYNAMICS_IMPLICIT && !fp.tables.prescribed)
         for (int k = 0; k < fp.tables.nq; ++k) {
             std::string n = fp.stateNames[fp.tables.nq + k];
             const size_t at = n.rfind("/speed");

@@ -485,6 +485,59 @@ std::unique_ptr<FlatProblem> gait10dofReplay(const std::string& dir, const std::
     return flatten(P, S);
 }
 
+// MocoInverse (Moco/Moco/MocoInverse.cpp:44-140) on the example2DWalking model: the kinematics of referenceCoordinates.sto are
+// prescribed (PositionMotion::createFromTable, Components/PositionMotion.cpp:121-150: GCVSplines of the value columns), reserve
+// actuators of optimal force 1 on every coordinate without an actuator (ModelFactory.cpp:265-320, ModOpAddReserves(1.0)),
+// MocoControlGoal "excitation_effort" + MocoInitialActivationGoal, implicit dynamics, no control interpolation at the
+// midpoints, implicit auxiliary derivatives minimised with weight 0.01, forward differences. The calf and shin muscles get
+// compliant tendons in implicit mode (ModOpTendonComplianceDynamicsModeDGF("implicit"), as testMocoInverse.cpp:122-129 does)
+// so that the problem carries auxiliary states, derivatives and residuals; the feet's contact spheres supply the ground reactions.
+// prescribe = false: the same problem with the coordinates left as states (used by the tests to check the prescribed point
+// function against the implicit one evaluated at the prescribed values).
+std::unique_ptr<FlatProblem> gaitInverse(const std::string& dir, const std::string& options, bool prescribe = true) {
+    Problem P;
+    P.model = loadOsim(dir + "/2D_gait.osim");
+    for (MuscleSpec& mu : P.model.muscles)
+        if (mu.path.find("soleus") != std::string::npos || mu.path.find("gastroc") != std::string::npos ||
+            mu.path.find("tib_ant") != std::string::npos) {
+            mu.ignoreTendonCompliance = false;
+            mu.tendonImplicit = true;
+        }
+    const StoTable ref = readSto(dir + "/referenceCoordinates.sto");
+    for (const JointSpec& J : P.model.joints)
+        for (const CoordSpec& c : J.coords) {
+            const std::string path = J.container + J.name + "/" + c.name;
+            const int ci = ref.col(path + "/value");
+            if (ci < 0) throw std::runtime_error("referenceCoordinates.sto lacks " + path + "/value");
+            if (prescribe) P.model.positionMotion.emplace_back(path, fitNaturalSpline(ref.time, ref.cols[ci], 5));
+            bool has = false;
+            for (const CoordActSpec& a : P.model.coordActs) has = has || a.coord == c.name;
+            if (has) continue;
+            CoordActSpec a;
+            std::string n = path;
+            for (char& ch : n) if (ch == '/') ch = '_';
+            a.path = "/forceset/reserve" + n;
+            a.coord = c.name;
+            a.optimalForce = 1.0;
+            P.model.actuatorOrder.emplace_back(0, (int)P.model.coordActs.size());
+            P.model.coordActs.push_back(a);
+        }
+    P.setTimeBounds(Bounds(ref.time.front()), Bounds(ref.time.back()));
+    P.addGoal(MOCOB200_GOAL_CONTROL, "excitation_effort", 1.0);
+    P.addGoal(MOCOB200_GOAL_INITIAL_ACTIVATION, "initial_activation");
+    SolverSettings S;
+    S.num_mesh_intervals = 24; // mesh_interval 0.02 s over 0.47 s
+    S.multibody_dynamics_mode = "implicit";
+    S.interpolate_control_midpoints = false;
+    S.minimize_implicit_auxiliary_derivatives = true;
+    S.implicit_auxiliary_derivatives_weight = 0.01;
+    S.optim_finite_difference_scheme = "forward";
+    S.optim_convergence_tolerance = 1e-3;
+    S.optim_constraint_tolerance = 1e-3;
+    S.applyOptions(options);
+    return flatten(P, S);
+}
+
 } // namespace
 
 std::unique_ptr<FlatProblem> buildExample(const std::string& name, const std::string& dataDir, const std::string& options) {
@@ -497,6 +550,8 @@ std::unique_ptr<FlatProblem> buildExample(const std::string& name, const std::st
     if (name == "gait2d_tracking") return gaitTracking(dataDir, options);
     if (name == "gait2d_prediction") return gaitPrediction(dataDir, options);
     if (name == "gait10dof_replay") return gait10dofReplay(dataDir, options);
+    if (name == "gait2d_inverse") return gaitInverse(dataDir, options);
+    if (name == "gait2d_inverse_free") return gaitInverse(dataDir, options, false);
     if (name == "planar_point_mass_coupler") return planarPointMassCoupler(options);
     if (name == "double_pendulum_coupler") return doublePendulumCoupler(options);
     throw std::runtime_error("unknown example '" + name + "'");

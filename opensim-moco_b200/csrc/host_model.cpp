@@ -188,7 +188,12 @@ void validateTables(const mocob200_tables& T) {
     intRange(T.o_spline_i, (long)T.nspline * MOCOB200_SPLINE_ISTRIDE, "splines");
     intRange(T.o_ppoly_i, (long)T.nppoly * MOCOB200_PPOLY_ISTRIDE, "piecewise polynomials");
     intRange(T.o_goal_i, (long)T.ngoal * MOCOB200_GOAL_ISTRIDE, "goals");
-    dblRange(T.o_bounds, 6L * (2 * T.nq + T.nz + T.nc), "bounds");
+    dblRange(T.o_bounds, 6L * ((T.prescribed ? 0 : 2 * T.nq) + T.nz + T.nc), "bounds");
+    if (T.prescribed) {
+        intRange(T.o_presc_i, T.nq, "prescribed kinematics");
+        for (int k = 0; k < T.nq; ++k)
+            if (T.idx[T.o_presc_i + k] < 0 || T.idx[T.o_presc_i + k] >= T.nppoly) bad("prescribed kinematics function");
+    }
     dblRange(T.o_time_bounds, 4, "time bounds");
     dblRange(T.o_spline_data, 0, "spline data");
     dblRange(T.o_ppoly_data, 0, "piecewise-polynomial data");
@@ -757,8 +762,18 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
 
     // ---- state / control naming (MocoUtilities.cpp:495-528, 557-587)
     std::vector<std::string>& sn = fp->stateNames;
-    for (int q = 0; q < nq; ++q) sn.push_back(coordPath[q] + "/value");
-    for (int q = 0; q < nq; ++q) sn.push_back(coordPath[q] + "/speed");
+    // prescribed kinematics: the coordinate values and speeds are not states (MocoProblemRep.cpp:546-560)
+    const bool prescribed = !M.positionMotion.empty();
+    std::vector<const PiecewisePoly*> motionOf(nq, nullptr);
+    if (prescribed) {
+        for (const auto& kv : M.positionMotion)
+            for (int q = 0; q < nq; ++q) if (coordPath[q] == kv.first) motionOf[q] = &kv.second;
+        for (int q = 0; q < nq; ++q)
+            if (!motionOf[q]) throw std::runtime_error("PositionMotion has no function for coordinate '" + coordPath[q] + "'");
+    }
+    const int nqStates = prescribed ? 0 : nq;
+    for (int q = 0; q < nqStates; ++q) sn.push_back(coordPath[q] + "/value");
+    for (int q = 0; q < nqStates; ++q) sn.push_back(coordPath[q] + "/speed");
     std::vector<int> musAct(M.muscles.size(), -1), musTen(M.muscles.size(), -1), musDeriv(M.muscles.size(), -1);
     int nz = 0, nda = 0;
     for (size_t m = 0; m < M.muscles.size(); ++m) {
@@ -956,8 +971,8 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
         ctlB.push_back(resolve(P.controlInfos, cn[c], dflt));
     }
     T.o_bounds = (int)D.size();
-    for (int q = 0; q < nq; ++q) { auto o = resolve(P.stateInfos, sn[q], Bounds(coordRange[q][0], coordRange[q][1])); D.insert(D.end(), o.begin(), o.end()); }
-    for (int q = 0; q < nq; ++q) { auto o = resolve(P.stateInfos, sn[nq + q], P.defaultSpeedBounds); D.insert(D.end(), o.begin(), o.end()); }
+    for (int q = 0; q < nqStates; ++q) { auto o = resolve(P.stateInfos, sn[q], Bounds(coordRange[q][0], coordRange[q][1])); D.insert(D.end(), o.begin(), o.end()); }
+    for (int q = 0; q < nqStates; ++q) { auto o = resolve(P.stateInfos, sn[nq + q], P.defaultSpeedBounds); D.insert(D.end(), o.begin(), o.end()); }
     for (size_t m = 0; m < M.muscles.size(); ++m) {
         if (musAct[m] >= 0) {
             Bounds dflt(-inf, inf);
@@ -988,6 +1003,14 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
         ppolyData.insert(ppolyData.end(), pp.coef.begin(), pp.coef.end());
         return id;
     };
+    T.prescribed = prescribed ? 1 : 0;
+    T.o_presc_i = 0;
+    if (prescribed) {
+        std::vector<int> ids;
+        for (int q = 0; q < nq; ++q) ids.push_back(addPPoly(*motionOf[q]));
+        T.o_presc_i = (int)I.size();
+        I.insert(I.end(), ids.begin(), ids.end());
+    }
     // ---- external forces (ExternalForce.cpp:330-355): functions of time in the piecewise-polynomial table
     {
         std::vector<int> xfI;
@@ -1011,6 +1034,9 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
     std::vector<double> goalD;
     for (const GoalSpec& g : P.goals) {
         int mode = g.mode;
+        if (prescribed && (g.kind == MOCOB200_GOAL_AVERAGE_SPEED || g.kind == MOCOB200_GOAL_INITIAL_VELOCITY_EQUILIBRIUM_DGF ||
+                           (g.kind == MOCOB200_GOAL_CONTROL && g.divideByDisplacement)))
+            throw std::runtime_error("goal '" + g.name + "' evaluates the model's kinematics at the end points: not supported with prescribed kinematics");
         const bool defaultEC = g.kind == MOCOB200_GOAL_AVERAGE_SPEED || g.kind == MOCOB200_GOAL_PERIODICITY ||
                                g.kind == MOCOB200_GOAL_INITIAL_ACTIVATION;
         if (mode == MOCOB200_MODE_PATH_CONSTRAINT && g.kind != MOCOB200_PATHCON_CONTROL_BOUND)
@@ -1100,7 +1126,7 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
         case MOCOB200_GOAL_INITIAL_ACTIVATION: {
             std::vector<int> pairs;
             for (size_t m = 0; m < M.muscles.size(); ++m)
-                if (musAct[m] >= 0) { pairs.push_back(musCtl[m]); pairs.push_back(2 * nq + musAct[m]); }
+                if (musAct[m] >= 0) { pairs.push_back(musCtl[m]); pairs.push_back(2 * nqStates + musAct[m]); }
             nout = (int)pairs.size() / 2;
             goalI.push_back(nout);
             goalI.insert(goalI.end(), pairs.begin(), pairs.end());

@@ -140,6 +140,9 @@ struct ModelSpec {
     std::vector<CoordActSpec> coordActs;
     std::vector<ExternalForceSpec> externalForces;
     std::vector<CouplerSpec> couplers;
+    // PositionMotion (Components/PositionMotion.cpp): when non-empty, one function of time for EVERY coordinate, keyed by the
+    // coordinate's absolute path (createFromTable: GCVSplines of the kinematics table) - all kinematics are prescribed
+    std::vector<std::pair<std::string, PiecewisePoly>> positionMotion;
     std::vector<std::pair<int, int>> actuatorOrder; // (0 = coordinate actuator, 1 = muscle ; index) in component order
     ModelSpec() { gravity.v[1] = -9.80665; }
     int bodyIndex(const std::string& n) const;

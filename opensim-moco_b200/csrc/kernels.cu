@@ -29,15 +29,12 @@ __global__ void k_paths(DevTables T, DevLayout L, const double* __restrict__ x, 
     const int j = p0 + t / T.nmus, m = t % T.nmus;
     double in[MOCOB200_MAX_IN];
     gather_inputs(L, x, j, in);
-    const double* q = in + 1;
-    const double* u = q + T.nq;
-    const double* z = u + T.nq;
-    const double* ctl = z + T.nz;
-    const double* auxder = ctl + T.nc + T.nm + (T.implicit ? T.nq : 0);
+    double pk[3 * MOCOB200_MAXQ];
+    const PointInputs P = point_inputs(T, in, pk);
     Scratch S;
-    kinematics(T, q, u, S);
+    kinematics(T, P.q, P.u, S);
     double ls[2];
-    muscle_force(T, m, q, u, z, ctl, auxder, S, false, false, ls);
+    muscle_force(T, m, P.q, P.u, P.z, P.ctl, P.auxder, S, false, false, ls);
     out[2 * ((size_t)j * T.nmus + m)] = ls[0];
     out[2 * ((size_t)j * T.nmus + m) + 1] = ls[1];
 }
@@ -138,7 +135,7 @@ __device__ inline bool endpoint_reads(const DevTables& T, const DevLayout& L, in
     const int side = a >= half ? 1 : 0;          // 0 = initial, 1 = final
     const int k = isIntegral ? -1 : a - side * half; // 0 = time, 1.. = states, controls, derivatives
     const bool isTime = k == 0;
-    const bool isQ = k >= 1 && k <= L.nq;
+    const bool isQ = k >= 1 && k <= L.nqs;
     const bool isState = k >= 1 && k <= L.ns;
     const bool isControl = k > L.ns && k <= L.ns + L.nc;
     switch (gr[0]) {
@@ -257,20 +254,21 @@ __device__ double velcorr_fd_entry(const DevTables& T, const DevLayout& L, const
     return jv;
 }
 __device__ __forceinline__ double xdot_val(const DevLayout& L, const double* x, const double* Y, int j, int s) {
-    if (s < L.nq) return x[L.off_states + (size_t)j * L.ns + L.nq + s];                     // qdot = u (:313-314)
-    if (s < 2 * L.nq && L.implicit) return x[L.off_derivs + (size_t)j * L.nd + (s - L.nq)]; // udot = w
-    return Y[(size_t)j * L.n_out + (s - L.nq)];
+    // L.nqs = coordinate states in the NLP (0 with prescribed kinematics: every state is then an auxiliary one)
+    if (s < L.nqs) return x[L.off_states + (size_t)j * L.ns + L.nqs + s];                     // qdot = u (:313-314)
+    if (s < 2 * L.nqs && L.implicit) return x[L.off_derivs + (size_t)j * L.nd + (s - L.nqs)]; // udot = w
+    return Y[(size_t)j * L.n_out + L.nq + (s - 2 * L.nqs)];
 }
 __device__ __forceinline__ double dxdot(const DevLayout& L, const double* J, int j, int s, const ColMetaD& c) {
     if (c.kind == COL_SLACK_D) return 0.0; // enters through the velocity correction only (k_assemble_jac_velcorr)
-    if (s < L.nq) return (c.kind == COL_STATE_D && c.k == L.nq + s) ? 1.0 : 0.0;
-    if (s < 2 * L.nq && L.implicit) return (c.kind == COL_DERIV_D && c.k == s - L.nq) ? 1.0 : 0.0;
-    return J[((size_t)j * L.n_out + (s - L.nq)) * L.n_in + c.in];
+    if (s < L.nqs) return (c.kind == COL_STATE_D && c.k == L.nqs + s) ? 1.0 : 0.0;
+    if (s < 2 * L.nqs && L.implicit) return (c.kind == COL_DERIV_D && c.k == s - L.nqs) ? 1.0 : 0.0;
+    return J[((size_t)j * L.n_out + L.nq + (s - 2 * L.nqs)) * L.n_in + c.in];
 }
 __device__ __forceinline__ double dxdot_dt(const DevLayout& L, const double* J, int j, int s) {
-    if (s < L.nq) return 0.0;
-    if (s < 2 * L.nq && L.implicit) return 0.0;
-    return time_col(L, J, j, s - L.nq);
+    if (s < L.nqs) return 0.0;
+    if (s < 2 * L.nqs && L.implicit) return 0.0;
+    return time_col(L, J, j, L.nq + (s - 2 * L.nqs));
 }
 __global__ void k_pack_time_column(DevLayout L, const double* __restrict__ J, double* __restrict__ Jt, int p0, int np) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -424,9 +422,10 @@ __global__ void k_assemble_f(DevTables T, DevLayout L, const double* __restrict_
         total += s;
     }
     for (int which = 0; which < 2; ++which) {
-        const bool on = which == 0 ? (L.minimize_accel && L.implicit) : (L.minimize_auxderiv && L.n_auxres > 0);
+        const int nacc = L.nd - L.n_auxres; // acceleration variables (none in explicit mode or with prescribed kinematics)
+        const bool on = which == 0 ? (L.minimize_accel && nacc > 0) : (L.minimize_auxderiv && L.n_auxres > 0);
         if (!on) continue;
-        const int lo = which == 0 ? 0 : (L.implicit ? L.nq : 0), hi = which == 0 ? L.nq : L.nd;
+        const int lo = which == 0 ? 0 : nacc, hi = which == 0 ? nacc : L.nd;
         double acc = 0;
         for (int j = 0; j < L.n_grid; ++j) {
             double sq = 0;
@@ -564,9 +563,10 @@ __global__ void k_assemble_grad(DevTables T, DevLayout L, const double* __restri
         }
     }
     for (int which = 0; which < 2; ++which) {
-        const bool on = which == 0 ? (L.minimize_accel && L.implicit) : (L.minimize_auxderiv && L.n_auxres > 0);
+        const int nacc = L.nd - L.n_auxres; // acceleration variables (none in explicit mode or with prescribed kinematics)
+        const bool on = which == 0 ? (L.minimize_accel && nacc > 0) : (L.minimize_auxderiv && L.n_auxres > 0);
         if (!on) continue;
-        const int lo = which == 0 ? 0 : (L.implicit ? L.nq : 0), hi = which == 0 ? L.nq : L.nd;
+        const int lo = which == 0 ? 0 : nacc, hi = which == 0 ? nacc : L.nd;
         const double w = which == 0 ? L.accel_weight : L.auxderiv_weight;
         if (c.kind == COL_DERIV_D && c.k >= lo && c.k < hi) v += 2.0 * w * dur * L.quad[c.point] * x[vi];
         if (c.kind == COL_T0_D || c.kind == COL_TF_D) {

@@ -37,6 +37,7 @@ struct ColMetaD { int kind, point, k, in; };
 
 struct DevLayout {
     int scheme, implicit, nq, nz, ns, nc, nd, n_in, n_auxres, n_integrand, n_dyn_out, n_out;
+    int prescribed, nqs; // prescribed kinematics; coordinate value states in the NLP (nq, or 0 when prescribed)
     int n_mesh, n_grid, n_intervals, n_var, n_con, nnz;
     int off_states, off_controls, off_derivs;
     int nm, nsl, n_kc, off_mult, off_slacks;   // kinematic constraints: multipliers per point, slacks per midpoint, rows per mesh point

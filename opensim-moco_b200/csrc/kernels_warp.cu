@@ -89,6 +89,7 @@ __device__ __forceinline__ void blob_load(const WarpAux& A, double* ws, const do
 // 0 = nothing (a coordinate), 1 = poses / path geometry / mass-matrix factor (a speed, or an acceleration variable in
 // implicit mode), 2 = velocities and contact forces as well (time, auxiliary states, controls, auxiliary derivatives)
 __device__ __forceinline__ int reuse_level(const DevLayout& L, int dir) {
+    if (L.prescribed) return dir == 0 ? 0 : 2; // time moves every coordinate; no coordinate, speed or acceleration inputs exist
     if (dir >= 1 && dir <= L.nq) return 0;
     if (dir > L.nq && dir <= 2 * L.nq) return 1;
     if (L.implicit && dir >= 1 + L.ns + L.nc + L.nm && dir < 1 + L.ns + L.nc + L.nm + L.nq) return 1;

@@ -14,14 +14,18 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
     Layout L{};
     L.scheme = R.scheme;
     L.implicit = R.dynamics_mode == MOCOB200_DYNAMICS_IMPLICIT;
-    L.nq = T.nq; L.nz = T.nz; L.ns = 2 * T.nq + T.nz; L.nc = T.nc;
-    L.nd = (L.implicit ? T.nq : 0) + T.nderiv_aux;
+    // prescribed kinematics (PositionMotion): no coordinate value / speed states, no acceleration variables (MocoProblemRep.cpp:546-560,
+    // CasOCProblem.h:485-517); the multibody residual rows stay (one per mobility)
+    L.prescribed = T.prescribed ? 1 : 0;
+    if (L.prescribed && !L.implicit) throw std::runtime_error("Prescribed kinematics (PositionMotion) requires implicit dynamics mode.");
+    L.nq = T.nq; L.nqs = L.prescribed ? 0 : T.nq; L.nz = T.nz; L.ns = 2 * L.nqs + T.nz; L.nc = T.nc;
+    L.nd = (L.implicit && !L.prescribed ? T.nq : 0) + T.nderiv_aux;
     const bool hsScheme = R.scheme == MOCOB200_SCHEME_HERMITE_SIMPSON;
     // kinematic constraints (CasOCProblem.h:473-524): one multiplier per holonomic equation; with enforce_constraint_derivatives
     // the velocity- and acceleration-level equations are rows too and every Hermite-Simpson midpoint gets one slack per equation
     L.nm = T.ncoupler;
-    L.enforce_derivs = (L.nm > 0 && R.enforce_constraint_derivatives) ? 1 : 0;
-    L.n_kc = L.enforce_derivs ? 3 * L.nm : L.nm;
+    L.enforce_derivs = (L.nm > 0 && R.enforce_constraint_derivatives && !L.prescribed) ? 1 : 0;
+    L.n_kc = L.prescribed ? 0 : (L.enforce_derivs ? 3 * L.nm : L.nm); // prescribed kinematics are assumed to obey the constraints (CasOCProblem.h:511-515)
     L.nsl = (L.enforce_derivs && hsScheme) ? L.nm : 0;
     L.n_in = 1 + L.ns + L.nc + L.nm + L.nd;
     L.n_auxres = T.nderiv_aux;
@@ -150,11 +154,11 @@ Layout buildLayout(const mocob200_tables& T, const mocob200_transcription& R, bo
     auto residOutRow = [&](int o) { return (L.implicit && o < L.nq) ? o : L.nq + L.nz + (o - (L.implicit ? L.nq : 0)); };
     // does xdot_s (state s) at a point depend on input `in` of the same point?
     auto xdotDepends = [&](int s, const ColMeta& c) -> bool {
-        if (s < L.nq && L.nsl > 0 && hs && c.point % 2 == 1 && c.kind == COL_STATE && c.k < 2 * L.nq)
+        if (s < L.nqs && L.nsl > 0 && hs && c.point % 2 == 1 && c.kind == COL_STATE && c.k < 2 * L.nqs)
             return true; // qdot_mid = u_mid + velocity correction(multibody states of the midpoint, slacks): dense callback block
-        if (s < L.nq) return c.kind == COL_STATE && c.k == L.nq + s; // qdot = u
-        if (s < 2 * L.nq && L.implicit) return c.kind == COL_DERIV && c.k == s - L.nq; // udot = w
-        return maskAt(s - L.nq, c.in); // the callback block: dense unless a detected mask is given
+        if (s < L.nqs) return c.kind == COL_STATE && c.k == L.nqs + s; // qdot = u
+        if (s < 2 * L.nqs && L.implicit) return c.kind == COL_DERIV && c.k == s - L.nqs; // udot = w
+        return maskAt(L.nq + (s - 2 * L.nqs), c.in); // zdot rows of the callback block: dense unless a detected mask is given
     };
     L.colptr.assign(L.n_var + 1, 0);
     L.rowidx.clear();
@@ -277,7 +281,7 @@ void layoutBounds(const mocob200_tables& T, const mocob200_transcription& R, con
                 xhi[L.off_mult + j * L.nm + k] = R.multiplier_bounds[1];
             }
             for (int k = 0; k < L.nd; ++k) {
-                const bool accel = L.implicit && k < L.nq;
+                const bool accel = L.implicit && !L.prescribed && k < L.nq;
                 xlo[L.off_derivs + j * L.nd + k] = accel ? R.accel_bounds[0] : R.auxderiv_bounds[0];
                 xhi[L.off_derivs + j * L.nd + k] = accel ? R.accel_bounds[1] : R.auxderiv_bounds[1];
             }

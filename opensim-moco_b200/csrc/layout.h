@@ -22,6 +22,7 @@ struct ColMeta { int kind, point, k, in; }; // in = index into the point-functio
 struct Layout {
     int scheme, implicit;
     int nq, nz, ns, nc, nd, n_in;
+    int prescribed, nqs;                       // prescribed kinematics; coordinate value states in the NLP (nq, or 0 when prescribed)
     int nm, nsl, n_kc;                         // multipliers per grid point, slacks per interior grid point, kinematic rows per mesh point
     int enforce_derivs;                        // enforce_constraint_derivatives (and kinematic constraints exist)
     int off_mult, off_slacks;

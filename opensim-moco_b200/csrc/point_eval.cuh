@@ -46,6 +46,7 @@ struct DevTables { // mocob200_tables with device (or shared-memory) pool pointe
     int ncoupler, o_cc_i, o_cc_d;           // coordinate-coupler kinematic constraints
     int nm, n_kc, enforce_derivs;           // multipliers per point, kinematic-constraint outputs, their derivatives enforced
     int implicit; // multibody dynamics mode
+    int prescribed, o_presc_i; // prescribed kinematics: idx[o_presc_i + k] = piecewise polynomial of coordinate k
     int n_auxres;
     int n_integrand; // goals with an integrand, in goal order
 };
@@ -206,6 +207,54 @@ __device__ inline double ppoly_eval(const DevTables& T, int id, double t) {
     double v = c[order - 1];
     for (int j = order - 2; j >= 0; --j) v = v * s + c[j];
     return v;
+}
+
+// value and first two derivatives (prescribed kinematics: Function::calcValue / calcDerivative({0}) / ({0,0}),
+// Components/PositionMotion.cpp:44-75)
+__device__ inline void ppoly_eval2(const DevTables& T, int id, double t, double& v, double& d1, double& d2) {
+    const int* rec = T.idx + T.o_ppoly_i + id * MOCOB200_PPOLY_ISTRIDE;
+    const int np = rec[1], order = rec[2];
+    const double* br = T.dblP + T.o_ppoly_data + rec[0];
+    const double* co = br + np + 1;
+    int k = 0;
+    if (t >= br[np]) k = np - 1;
+    else if (t > br[0]) {
+        k = (int)((t - br[0]) / (br[np] - br[0]) * (double)np);
+        k = max(0, min(k, np - 1));
+        while (k > 0 && t < br[k]) --k;
+        while (k < np - 1 && t >= br[k + 1]) ++k;
+    }
+    const double s = t - br[k];
+    const double* c = co + (size_t)k * order;
+    v = 0; d1 = 0; d2 = 0;
+    for (int j = order - 1; j >= 0; --j) { // Horner on the value and both derivatives
+        d2 = d2 * s + 2.0 * d1;
+        d1 = d1 * s + v;
+        v = v * s + c[j];
+    }
+}
+
+// The inputs of one point-function evaluation, in = [time, q(nqs), u(nqs), z(nz), controls(nc), multipliers(nm), udot, auxder]:
+// with prescribed kinematics (nqs = 0, no udot inputs) q, u and udot are the coordinates' functions of time, evaluated into pk.
+struct PointInputs {
+    const double *q, *u, *z, *ctl, *mult, *udot, *auxder;
+};
+__device__ inline PointInputs point_inputs(const DevTables& T, const double* in, double* pk /* [3 nq], used when prescribed */) {
+    PointInputs P;
+    const int nq = T.nq, nqs = T.prescribed ? 0 : nq;
+    P.q = in + 1;
+    P.u = P.q + nqs;
+    P.z = P.u + nqs;
+    P.ctl = P.z + T.nz;
+    P.mult = P.ctl + T.nc;
+    const double* der = P.mult + T.nm;
+    P.udot = (T.implicit && !T.prescribed) ? der : nullptr;
+    P.auxder = der + ((T.implicit && !T.prescribed) ? nq : 0);
+    if (T.prescribed) {
+        for (int k = 0; k < nq; ++k) ppoly_eval2(T, T.idx[T.o_presc_i + k], in[0], pk[k], pk[nq + k], pk[2 * nq + k]);
+        P.q = pk; P.u = pk + nq; P.udot = pk + 2 * nq;
+    }
+    return P;
 }
 
 // ---- De Groote–Fregly 2016 curves (Components/DeGrooteFregly2016Muscle.h:332-474, constants :769-815)
@@ -878,15 +927,15 @@ __device__ inline V3 mass_center(const DevTables& T, const ScratchT<SZ>& S) {
 // (udot|residual, zdot, aux residuals), bit 1+k = integrand k. Unselected outputs are left untouched.
 template <class SZ = SizeLarge>
 __device__ inline void eval_point(const DevTables& T, const double* in, double* out, unsigned mask) {
-    const int nq = T.nq, nz = T.nz, nc = T.nc;
+    const int nq = T.nq, nz = T.nz;
     const double time = in[0];
-    const double* q = in + 1;
-    const double* u = q + nq;
-    const double* z = u + nq;
-    const double* ctl = z + nz;
-    const double* mult = ctl + nc; // Lagrange multipliers of the kinematic constraints
-    const double* der = mult + T.nm; // implicit: udot[nq] then aux derivatives
-    const double* auxder = der + (T.implicit ? nq : 0);
+    double pk[3 * SZ::NQ]; // q, u, udot of prescribed kinematics
+    const PointInputs P = point_inputs(T, in, pk);
+    const double* states = in + 1; // the NLP's state vector at this point (goals index into it)
+    const double *q = P.q, *u = P.u, *z = P.z, *ctl = P.ctl;
+    const double* mult = P.mult;     // Lagrange multipliers of the kinematic constraints
+    const double* der = P.udot;      // implicit: udot[nq]
+    const double* auxder = P.auxder; // implicit auxiliary derivatives
     const bool dyn_on = mask & 1u;
     // which integrands are wanted, and do any of them need kinematics + contact forces?
     bool need_contacts = dyn_on;
@@ -958,7 +1007,8 @@ __device__ inline void eval_point(const DevTables& T, const double* in, double* 
         if (T.implicit) inverse_dynamics_residual(T, u, der, S, dyn);
         else forward_dynamics(T, u, S, dyn);
         double* kc = auxres + T.n_auxres;
-        for (int k = 0; k < T.ncoupler; ++k) coupler_errors(T, k, q, u, T.implicit ? der : dyn, kc);
+        if (T.n_kc > 0)
+            for (int k = 0; k < T.ncoupler; ++k) coupler_errors(T, k, q, u, T.implicit ? der : dyn, kc);
     }
     // goal integrands (MocoGoal::calcIntegrand; MocoControlGoal.cpp:121-131,
     // MocoStateTrackingGoal.cpp:103-117, MocoContactTrackingGoal.cpp:240-287)
@@ -983,7 +1033,7 @@ __device__ inline void eval_point(const DevTables& T, const double* in, double* 
         case MOCOB200_GOAL_STATE_TRACKING: {
             const int n = ip[0];
             for (int k = 0; k < n; ++k) {
-                const double e = q[ip[1 + 2 * k]] - ppoly_eval(T, ip[2 + 2 * k], time);
+                const double e = states[ip[1 + 2 * k]] - ppoly_eval(T, ip[2 + 2 * k], time);
                 val += dp[3 + k] * (e * e);
             }
         } break;
@@ -997,7 +1047,7 @@ __device__ inline void eval_point(const DevTables& T, const double* in, double* 
         case MOCOB200_GOAL_SUM_SQUARED_STATE: {
             const int n = ip[0];
             for (int k = 0; k < n; ++k) {
-                const double e = q[ip[1 + 2 * k]];
+                const double e = states[ip[1 + 2 * k]];
                 val += dp[3 + k] * e * e;
             }
         } break;

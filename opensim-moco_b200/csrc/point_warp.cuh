@@ -54,6 +54,7 @@ struct WarpAux {
     int o_mlen, o_mspd, o_mout, o_Rm;
     int o_cjs; // per custom joint (position-dependent): 6 axis vectors in ground (18), df[6], d2f[6]
     int lockstep;
+    int o_pk; // prescribed kinematics: q, u, udot at the point's time
     int poison; // development switch (MOCOB200_POISON_SCRATCH=1): every evaluation starts from NaN-filled scratch
     int ws_doubles;
     int wpb; // warps (= evaluations in flight) per block, chosen at create from the scratch size

@@ -238,13 +238,22 @@ __device__ __forceinline__ void warp_eval_point_t(const DevTables& T, const Warp
     const double* in = ws + A.o_in;
     double* out = ws + A.o_out;
     const double time = in[0];
+    const int nqs = T.prescribed ? 0 : nq; // coordinate states among the inputs (none with prescribed kinematics)
+    const double* states = in + 1;         // the NLP's state vector at this point (goals index into it)
     const double* q = in + 1;
-    const double* u = q + nq;
-    const double* z = u + nq;
+    const double* u = q + nqs;
+    const double* z = u + nqs;
     const double* ctl = z + nz;
     const double* mult = ctl + nc;
     const double* der = mult + T.nm;
-    const double* auxder = der + (T.implicit ? nq : 0);
+    const double* auxder = der + ((T.implicit && !T.prescribed) ? nq : 0);
+    if (T.prescribed) { // q, u, udot = the coordinates' functions of time (Components/PositionMotion.cpp:44-75)
+        double* pk = ws + A.o_pk;
+        if (reuse == 0 || time_moved)
+            for (int k = lane; k < nq; k += 32) ppoly_eval2(T, T.idx[T.o_presc_i + k], time, pk[k], pk[nq + k], pk[2 * nq + k]);
+        __syncwarp();
+        q = pk; u = pk + nq; der = pk + 2 * nq;
+    }
     const bool dyn = mask & 1u;
     bool need_contacts = dyn;
     {
@@ -338,7 +347,8 @@ __device__ __forceinline__ void warp_eval_point_t(const DevTables& T, const Warp
             wk_ldlt_solve(C, nq, ws + A.o_tau, out);
         }
         __syncwarp();
-        for (int k = lane; k < T.ncoupler; k += 32) coupler_errors(T, k, q, u, T.implicit ? der : out, out + nq + nz + T.n_auxres);
+        if (T.n_kc > 0)
+            for (int k = lane; k < T.ncoupler; k += 32) coupler_errors(T, k, q, u, T.implicit ? der : out, out + nq + nz + T.n_auxres);
         __syncwarp();
     }
     PHASE_MARK(9);
@@ -363,7 +373,7 @@ __device__ __forceinline__ void warp_eval_point_t(const DevTables& T, const Warp
         } break;
         case MOCOB200_GOAL_STATE_TRACKING:
             for (int k = lane; k < ip[0]; k += 32) {
-                const double e = q[ip[1 + 2 * k]] - ws[A.o_ref + ip[2 + 2 * k]];
+                const double e = states[ip[1 + 2 * k]] - ws[A.o_ref + ip[2 + 2 * k]];
                 val += dp[3 + k] * (e * e);
             }
             break;
@@ -375,7 +385,7 @@ __device__ __forceinline__ void warp_eval_point_t(const DevTables& T, const Warp
             break;
         case MOCOB200_GOAL_SUM_SQUARED_STATE:
             for (int k = lane; k < ip[0]; k += 32) {
-                const double e = q[ip[1 + 2 * k]];
+                const double e = states[ip[1 + 2 * k]];
                 val += dp[3 + k] * (e * e);
             }
             break;

@@ -91,8 +91,8 @@ __device__ inline double wk_integrand_term_delta(const DevTables& T, const WarpA
                                                  double v1) {
     const int* ip = T.idx + gr[4];
     const double* dp = T.dblG + gr[5];
-    const int ns = 2 * T.nq + T.nz;
-    const int state = (dir >= 1 && dir <= ns) ? dir - 1 : -1;               // index relative to q
+    const int ns = (T.prescribed ? 0 : 2 * T.nq) + T.nz;
+    const int state = (dir >= 1 && dir <= ns) ? dir - 1 : -1;               // index into the state vector
     const int control = (dir > ns && dir <= ns + T.nc) ? dir - 1 - ns : -1;
     double d = 0.0;
     switch (gr[0]) {
@@ -133,9 +133,9 @@ struct LocalMuscleEval { double F, nfDeriv, residual, actDot; };
 __device__ inline LocalMuscleEval wk_local_muscle(const DevTables& T, const WarpAux& A, const double* ws, int m, int role, double v) {
     const int nq = T.nq;
     const double* in = ws + A.o_in;
-    const double* z = in + 1 + 2 * nq;
+    const double* z = in + 1 + (T.prescribed ? 0 : 2 * nq);
     const double* ctl = z + T.nz;
-    const double* auxder = ctl + T.nc + T.nm + (T.implicit ? nq : 0);
+    const double* auxder = ctl + T.nc + T.nm + ((T.implicit && !T.prescribed) ? nq : 0);
     const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
     const double* md = T.dbl + T.o_mus_d + m * MOCOB200_MUS_DSTRIDE;
     const int flags = mi[5];

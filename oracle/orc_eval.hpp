@@ -185,10 +185,22 @@ template <class S>
 void evalPoint(const Model& M, const S* in, S* out, unsigned mask = 0xffffffffu) {
     const int nq = M.nq, nz = M.nz, nc = M.nc;
     const S time = in[0];
-    const S* q = in + 1; const S* u = q + nq; const S* z = u + nq; const S* ctl = z + nz;
+    const int nqs = M.nqs;
+    const S* states = in + 1; // the NLP's state vector at this point (goals index into it)
+    const S* q = in + 1; const S* u = q + nqs; const S* z = u + nqs; const S* ctl = z + nz;
     const S* mult = ctl + nc;
     const S* der = mult + M.nm;
-    const S* auxDeriv = der + (M.implicit ? nq : 0);
+    const S* auxDeriv = der + ((M.implicit && !M.prescribed) ? nq : 0);
+    S presc[3 * kMaxDof];
+    if (M.prescribed) { // q, qdot, qdotdot of every coordinate from its function of time (Components/PositionMotion.cpp:44-75)
+        for (int k = 0; k < nq; ++k) {
+            const int id = M.T->idx[M.T->o_presc_i + k];
+            presc[k] = piecewisePoly(M, id, time);
+            presc[nq + k] = piecewisePolyDeriv(M, id, time, 1);
+            presc[2 * nq + k] = piecewisePolyDeriv(M, id, time, 2);
+        }
+        q = presc; u = presc + nq; der = presc + 2 * nq;
+    }
     const bool dyn = mask & 1u;
     bool needContact = dyn;
     for (int s = 0; s < M.n_integrand; ++s)
@@ -280,7 +292,7 @@ void evalPoint(const Model& M, const S* in, S* out, unsigned mask = 0xffffffffu)
         // solved for; implicit: the acceleration variables)
         S* kc = out + nq + nz + M.n_auxres;
         const S* udotUsed = M.implicit ? der : out;
-        for (int k = 0; k < M.nm; ++k) {
+        for (int k = 0; k < (M.n_kc > 0 ? M.nm : 0); ++k) {
             S e, d1, d2;
             couplerFunction(M, k, q, e, d1, d2);
             const int* ci = M.couplerI(k);
@@ -310,7 +322,7 @@ void evalPoint(const Model& M, const S* in, S* out, unsigned mask = 0xffffffffu)
         } break;
         case MOCOB200_GOAL_STATE_TRACKING:
             for (int k = 0; k < ip[0]; ++k) {
-                const S e = q[ip[1 + 2 * k]] - piecewisePoly(M, ip[2 + 2 * k], time);
+                const S e = states[ip[1 + 2 * k]] - piecewisePoly(M, ip[2 + 2 * k], time);
                 v += S(dp[3 + k]) * (e * e);
             }
             break;
@@ -321,7 +333,7 @@ void evalPoint(const Model& M, const S* in, S* out, unsigned mask = 0xffffffffu)
             }
             break;
         case MOCOB200_GOAL_SUM_SQUARED_STATE:
-            for (int k = 0; k < ip[0]; ++k) { const S e = q[ip[1 + 2 * k]]; v += S(dp[3 + k]) * (e * e); }
+            for (int k = 0; k < ip[0]; ++k) { const S e = states[ip[1 + 2 * k]]; v += S(dp[3 + k]) * (e * e); }
             break;
         case MOCOB200_GOAL_CONTACT_TRACKING: {
             const int proj = ip[0], ng = ip[1];
@@ -360,7 +372,7 @@ void evalPathConstraint(const Model& M, int g, const S* in, S* errors) {
     const int* gr = M.goalRec(g);
     const int* ip = M.T->idx + gr[4];
     const S time = in[0];
-    const S* controls = in + 1 + 2 * M.nq + M.nz;
+    const S* controls = in + 1 + 2 * M.nqs + M.nz;
     for (int e = 0; e < gr[2]; ++e) errors[e] = controls[ip[2 * e]] - piecewisePoly(M, ip[2 * e + 1], time);
 }
 
@@ -370,7 +382,7 @@ void evalEndpoint(const Model& M, int g, const S* ein, S* vals) {
     const int* gr = M.goalRec(g);
     const int* ip = M.T->idx + gr[4];
     const double* dp = M.T->dbl + gr[5];
-    const int ns = 2 * M.nq + M.nz, nc = M.nc, nd = M.nd, nq = M.nq;
+    const int ns = 2 * M.nqs + M.nz, nc = M.nc, nd = M.nd, nq = M.nq;
     const int half = 1 + ns + nc + M.nm + nd;
     const S t0 = ein[0], tf = ein[half];
     const S* x0 = ein + 1; const S* c0 = x0 + ns; const S* d0 = c0 + nc + M.nm;

@@ -65,10 +65,10 @@ struct JacBuilder {
     }
     const double* xptr = nullptr;
     void addXdotRow(SparseRow& r, const double* J, int j, int s, double coef, bool structural) const {
-        if (s < P.nq && P.corrected(j)) addVelocityCorrectionRow(r, xptr, j, s, coef, structural);
-        if (s < P.nq) { if (structural) r.mark(P.offStates + j * P.ns + P.nq + s); else r.add(P.offStates + j * P.ns + P.nq + s, coef); return; }
-        if (s < 2 * P.nq && P.M.implicit) { const int c = P.offDerivs + j * P.nd + (s - P.nq); if (structural) r.mark(c); else r.add(c, coef); return; }
-        addCallbackRow(r, J, j, s - P.nq, coef, structural);
+        if (s < P.nqs && P.corrected(j)) addVelocityCorrectionRow(r, xptr, j, s, coef, structural);
+        if (s < P.nqs) { if (structural) r.mark(P.offStates + j * P.ns + P.nqs + s); else r.add(P.offStates + j * P.ns + P.nqs + s, coef); return; }
+        if (s < 2 * P.nqs && P.M.implicit) { const int c = P.offDerivs + j * P.nd + (s - P.nqs); if (structural) r.mark(c); else r.add(c, coef); return; }
+        addCallbackRow(r, J, j, P.nq + (s - 2 * P.nqs), coef, structural);
     }
     // d(goal output o)/d(everything): endpoint FD block E[nout][nEin] + chain through the integral
     void addEndpointRow(SparseRow& r, const double* x, const double* J, const double* E, int g, int o, double coef,
@@ -280,8 +280,8 @@ struct JacBuilder {
             r.add(0, -w * acc);
             r.add(1, w * acc);
         }
-        if (P.M.implicit && P.R.minimize_accelerations) pen(0, P.nq, P.R.accelerations_weight);
-        if (P.M.n_auxres && P.R.minimize_auxiliary_derivatives) pen(P.M.implicit ? P.nq : 0, P.nd, P.R.auxiliary_derivatives_weight);
+        if (P.M.implicit && !P.M.prescribed && P.R.minimize_accelerations) pen(0, P.nq, P.R.accelerations_weight);
+        if (P.M.n_auxres && P.R.minimize_auxiliary_derivatives) pen(P.nd - P.M.n_auxres, P.nd, P.R.auxiliary_derivatives_weight);
         for (int c = 0; c < P.nVar; ++c) grad[c] = r.v[c];
     }
 };

@@ -16,6 +16,8 @@
 #include <cmath>
 #include <vector>
 
+#include <stdexcept>
+
 #include "orc_eval.hpp"
 
 namespace orc {
@@ -74,6 +76,7 @@ struct Nlp {
     FdOptions fd;
     bool hs = true;
     int nMesh = 0, nIntervals = 0, nGrid = 0, ns = 0, nc = 0, nd = 0, nq = 0, nIn = 0, nOut = 0;
+    int nqs = 0; // coordinate value states in the NLP (nq, or 0 with prescribed kinematics)
     int offStates = 2, offControls = 0, offMult = 0, offSlacks = 0, offDerivs = 0, nVar = 0, nCon = 0, nEin = 0;
     int nm = 0, nsl = 0, nKc = 0;       // multipliers per grid point, slacks per interior point, kinematic rows per mesh point
     std::vector<int> kinRow;            // first kinematic-constraint row per mesh point
@@ -106,7 +109,8 @@ struct Nlp {
             if (hs) { quad[2 * i] += dm / 6.0; quad[2 * i + 1] += 2.0 * dm / 3.0; quad[2 * i + 2] += dm / 6.0; }
             else { quad[i] += 0.5 * dm; quad[i + 1] += 0.5 * dm; }
         }
-        nq = M.nq; ns = 2 * M.nq + M.nz; nc = M.nc; nd = M.nd; nIn = M.n_in; nOut = M.n_out;
+        if (M.prescribed && !M.implicit) throw std::runtime_error("Prescribed kinematics (PositionMotion) requires implicit dynamics mode.");
+        nq = M.nq; nqs = M.nqs; ns = 2 * M.nqs + M.nz; nc = M.nc; nd = M.nd; nIn = M.n_in; nOut = M.n_out;
         // x = [t0, tf, states, controls, multipliers, slacks (Hermite-Simpson midpoints, with enforced derivatives), derivatives]
         nm = M.nm; nKc = M.n_kc;
         nsl = (M.enforceDerivs && hs) ? nm : 0;
@@ -209,14 +213,14 @@ struct Nlp {
     // ---- state derivatives used by the defects: qdot = u, udot = callback (explicit) or the
     // acceleration variables (implicit), zdot = callback (CasOCTranscription.cpp:313-411)
     double xdot(const double* x, const double* Y, int j, int s) const {
-        if (s < nq && corrected(j)) {
+        if (s < nqs && corrected(j)) {
             std::vector<double> corr(nq);
             velocityCorrection<double>(M, x + offStates + (size_t)j * ns, slacksAt(x, j), corr.data());
             return x[offStates + (size_t)j * ns + nq + s] + corr[s];
         }
-        if (s < nq) return x[offStates + (size_t)j * ns + nq + s];
-        if (s < 2 * nq && M.implicit) return x[offDerivs + (size_t)j * nd + (s - nq)];
-        return Y[(size_t)j * nOut + (s - nq)];
+        if (s < nqs) return x[offStates + (size_t)j * ns + nqs + s];
+        if (s < 2 * nqs && M.implicit) return x[offDerivs + (size_t)j * nd + (s - nqs)];
+        return Y[(size_t)j * nOut + nq + (s - 2 * nqs)]; // auxiliary state: its zdot follows the nq multibody outputs
     }
     double integral(const double* x, const double* Y, int slot) const {
         double acc = 0;
@@ -336,13 +340,13 @@ struct Nlp {
             if (terms) terms[t] = s;
             ++t; total += s;
         }
-        if (M.implicit && R.minimize_accelerations) {
+        if (M.implicit && !M.prescribed && R.minimize_accelerations) {
             const double s = penalty(x, 0, nq, R.accelerations_weight);
             if (terms) terms[t] = s;
             ++t; total += s;
         }
         if (M.n_auxres && R.minimize_auxiliary_derivatives) {
-            const double s = penalty(x, M.implicit ? nq : 0, nd, R.auxiliary_derivatives_weight);
+            const double s = penalty(x, nd - M.n_auxres, nd, R.auxiliary_derivatives_weight);
             if (terms) terms[t] = s;
             ++t; total += s;
         }

@@ -21,18 +21,22 @@ struct Model {
     const mocob200_tables* T = nullptr;
     bool implicit = false;
     int nq = 0, nz = 0, nc = 0, nb = 0, n_auxres = 0, n_integrand = 0, nd = 0, n_in = 0, n_dyn_out = 0, n_out = 0;
+    bool prescribed = false;  // PositionMotion: every coordinate is a function of time (no coordinate states, no acceleration variables)
+    int nqs = 0;              // coordinate value states among the inputs: nq, or 0 when prescribed (MocoProblemRep.cpp:546-560)
     int nm = 0, n_kc = 0;     // Lagrange multipliers per grid point ; kinematic-constraint equations (3 nm with their derivatives, else nm)
     bool enforceDerivs = false;
     std::vector<int> integrandGoals; // goal index of each integrand slot
     void init(const mocob200_tables* t, bool implicitMode, bool enforceConstraintDerivatives = false) {
         T = t; implicit = implicitMode;
         nq = t->nq; nz = t->nz; nc = t->nc; nb = t->nb; n_auxres = t->nderiv_aux;
-        nd = (implicit ? nq : 0) + t->nderiv_aux;
+        prescribed = t->prescribed != 0;
+        nqs = prescribed ? 0 : nq;
+        nd = ((implicit && !prescribed) ? nq : 0) + t->nderiv_aux; // CasOCProblem.h:485-493
         // CasOCProblem.h:473-524: one multiplier per holonomic equation; 3 rows per equation when the derivatives are enforced
         nm = t->ncoupler;
-        enforceDerivs = nm > 0 && enforceConstraintDerivatives;
-        n_kc = enforceDerivs ? 3 * nm : nm;
-        n_in = 1 + 2 * nq + nz + nc + nm + nd;
+        enforceDerivs = nm > 0 && enforceConstraintDerivatives && !prescribed;
+        n_kc = prescribed ? 0 : (enforceDerivs ? 3 * nm : nm); // prescribed kinematics are taken to obey the constraints (CasOCProblem.h:511-515)
+        n_in = 1 + 2 * nqs + nz + nc + nm + nd;
         integrandGoals.clear();
         for (int g = 0; g < t->ngoal; ++g) if (goalRec(g)[3]) integrandGoals.push_back(g);
         n_integrand = (int)integrandGoals.size();
@@ -104,6 +108,29 @@ S piecewisePoly(const Model& M, int id, S t) {
     const S s = t - S(br[k]);
     S v(co[(size_t)k * order + order - 1]);
     for (int j = order - 2; j >= 0; --j) v = v * s + S(co[(size_t)k * order + j]);
+    return v;
+}
+
+// k-th derivative (k = 1, 2) of the same function, term by term (PositionMotion's calcPrescribedPositionDot / DotDot,
+// Components/PositionMotion.cpp:53-75)
+template <class S>
+S piecewisePolyDeriv(const Model& M, int id, S t, int deriv) {
+    const int* rec = M.T->idx + M.T->o_ppoly_i + id * MOCOB200_PPOLY_ISTRIDE;
+    const int np = rec[1], order = rec[2];
+    const double* br = M.T->dbl + M.T->o_ppoly_data + rec[0];
+    const double* co = br + np + 1;
+    const double tv = val(t);
+    int k = 0;
+    while (k + 1 < np && tv >= br[k + 1]) ++k;
+    if (tv < br[0]) k = 0;
+    const S s = t - S(br[k]);
+    S v(0.0), p(1.0); // p = s^(j - deriv)
+    for (int j = deriv; j < order; ++j) {
+        double f = 1.0;
+        for (int i = 0; i < deriv; ++i) f *= (double)(j - i);
+        v = v + S(f * co[(size_t)k * order + j]) * p;
+        p = p * s;
+    }
     return v;
 }
 

@@ -30,6 +30,10 @@ CASES = {
     "point_mass_coupler_implicit": ("planar_point_mass_coupler", "multibody_dynamics_mode=implicit"),
     "double_pendulum_coupler": ("double_pendulum_coupler", None),
     "double_pendulum_coupler_noderiv_trap": ("double_pendulum_coupler", "enforce_constraint_derivatives=0;transcription_scheme=trapezoidal;num_mesh_intervals=8"),
+    # MocoInverse on the 2D gait model: prescribed kinematics (PositionMotion), and the same problem with free coordinates
+    "gait2d_inverse": ("gait2d_inverse", None),
+    "gait2d_inverse_free": ("gait2d_inverse_free", None),
+    "gait2d_inverse_trap_central": ("gait2d_inverse", "transcription_scheme=trapezoidal;num_mesh_intervals=12;optim_finite_difference_scheme=central"),
     "gait2d_tracking": ("gait2d_tracking", None),
     "gait2d_prediction": ("gait2d_prediction", None),
 }

@@ -42,4 +42,6 @@ FIXTURES = ["sliding_mass", "sliding_mass_trap", "hanging_muscle", "hanging_musc
             "pendulum3_implicit", "gait2d_tracking", "gait2d_prediction", "pendulum_cb_lower", "pendulum_cb_upper_trap",
             "pendulum_cb_equality", "pendulum_cb_both",
             # kinematic constraints: multipliers, slacks, velocity correction
-            "point_mass_coupler", "point_mass_coupler_implicit", "double_pendulum_coupler", "double_pendulum_coupler_noderiv_trap"]
+            "point_mass_coupler", "point_mass_coupler_implicit", "double_pendulum_coupler", "double_pendulum_coupler_noderiv_trap",
+            # prescribed kinematics (PositionMotion, MocoInverse on the 2D gait model) and its free-coordinate twin
+            "gait2d_inverse", "gait2d_inverse_trap_central", "gait2d_inverse_free"]
