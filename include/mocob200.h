@@ -75,6 +75,12 @@ enum { MOCOB200_POINTS_OUTPUTS = 0 /* [n_grid][n_out] */, MOCOB200_POINTS_JACOBI
        MOCOB200_POINTS_PATHS = 2 };
 
 /* Layout of per-entity records inside the pools.  All strides are in elements. */
+/* wrap cylinder: dbl = [R_BW row-major (wrap frame in its body: xyz_body_rotation, body-fixed X-Y-Z), p_BW (translation),
+ * radius, length, 0, 0]; idx = [body (-1 ground), wrap axis (0 x, 1 y), wrap sign (+-1; 0 = all quadrants), active] */
+#define MOCOB200_WO_DSTRIDE 16
+#define MOCOB200_WO_ISTRIDE 4
+/* PathWrap: idx = [wrap object, range start, range end (1-based path-point numbers, < 1 = first / last), 0] */
+#define MOCOB200_PW_ISTRIDE 4
 #define MOCOB200_BODY_DSTRIDE 34   /* X_PF R(9) p(3) | X_BM R(9) p(3) | mass | com(3) | inertia about origin xx yy zz xy xz yz (6) */
 #define MOCOB200_BODY_ISTRIDE 4    /* parent (-1 ground) | joint kind | first q | ndof */
 #define MOCOB200_PP_DSTRIDE 5      /* loc(3) in body frame | range lo | range hi */
@@ -139,7 +145,12 @@ typedef struct mocob200_tables {
      * value / speed states and no acceleration variables, no kinematic-constraint rows, and nq multibody residual rows per grid
      * point (implicit mode is required, MocoCasADiSolver.cpp:147-151); multipliers stay variables and their forces are applied */
     int prescribed, o_presc_i;
-    int reserved[5];
+    /* cylinder wrapping (Simulation/Wrap/WrapCylinder.cpp, Model/GeometryPath.cpp:868-1094 applyWrapObjects):
+     * nwrapobj wrap cylinders fixed on bodies, npathwrap (muscle, cylinder) pairings in PathWrapSet order.
+     * idx[o_pw_i + 2 m], idx[o_pw_i + 2 m + 1] = first pairing and number of pairings of muscle m; the pairing records follow
+     * at idx[o_pw_i + 2 nmus + k MOCOB200_PW_ISTRIDE]. */
+    int nwrapobj, o_wo_d, o_wo_i;
+    int npathwrap, o_pw_i;
 } mocob200_tables;
 
 /* Solver-side settings: mirrors the properties of MocoDirectCollocationSolver /

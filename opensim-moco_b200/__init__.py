@@ -119,7 +119,7 @@ class Tables(C.Structure):
                 [(n, C.c_int) for n in ("nb nq nz nc nderiv_aux nmus npp nspline ncontact ncact ngoal nppoly o_body_d o_gravity o_pp_d "
                                         "o_mus_d o_contact_d o_cact_d o_spline_data o_ppoly_data o_bounds o_time_bounds o_body_i o_pp_i "
                                         "o_mus_i o_contact_i o_cact_i o_spline_i o_goal_i o_ppoly_i ncustom o_cj_d o_cj_i o_body_cj nxforce "
-                                        "o_xforce_i ncoupler o_cc_i o_cc_d prescribed o_presc_i").split()] + [("reserved", C.c_int * 5)])
+                                        "o_xforce_i ncoupler o_cc_i o_cc_d prescribed o_presc_i nwrapobj o_wo_d o_wo_i npathwrap o_pw_i").split()])
 
 
 def _vptr(a):

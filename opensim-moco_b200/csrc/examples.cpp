@@ -485,6 +485,26 @@ std::unique_ptr<FlatProblem> gait10dofReplay(const std::string& dir, const std::
     return flatten(P, S);
 }
 
+// Replay of the reference's CMC run on the full-body Rajagopal model (opensim-models/Pipelines/Rajagopal, model
+// outputReference/subject01_RRA_Adjusted.osim: 22 bodies, 39 coordinates, 80 muscles, 40 wrap cylinders, document Version
+// 30000): the muscles become path actuators driven by the recorded tensions; used by the tests to pin cylinder wrapping
+// (path lengths and lengthening speeds) against what the reference printed (Results_CMC/cmc_MuscleAnalysis_Length.sto,
+// cmc_Actuation_speed.sto). Locked coordinates are read as free ones (they stay constant in the recorded states).
+std::unique_ptr<FlatProblem> rajagopalReplay(const std::string& dir, const std::string& options) {
+    Problem P;
+    P.model = loadOsim(dir + "/outputReference/subject01_RRA_Adjusted.osim", /*musclesAsPathActuators=*/true, /*lockedAsFree=*/true);
+    P.setTimeBounds(Bounds(0.87), Bounds(1.13));
+    P.defaultSpeedBounds = Bounds(-50, 50);
+    for (auto& a : P.model.coordActs) P.setControlInfo(a.path, Bounds(-1e4, 1e4));
+    for (auto& m : P.model.muscles) P.setControlInfo(m.path, Bounds(0, 1e4));
+    P.addGoal(MOCOB200_GOAL_CONTROL, "effort");
+    SolverSettings S;
+    S.num_mesh_intervals = 10;
+    S.transcription_scheme = "trapezoidal";
+    S.applyOptions(options);
+    return flatten(P, S);
+}
+
 // MocoInverse (Moco/Moco/MocoInverse.cpp:44-140) on the example2DWalking model: the kinematics of referenceCoordinates.sto are
 // prescribed (PositionMotion::createFromTable, Components/PositionMotion.cpp:121-150: GCVSplines of the value columns), reserve
 // actuators of optimal force 1 on every coordinate without an actuator (ModelFactory.cpp:265-320, ModOpAddReserves(1.0)),
@@ -550,6 +570,7 @@ std::unique_ptr<FlatProblem> buildExample(const std::string& name, const std::st
     if (name == "gait2d_tracking") return gaitTracking(dataDir, options);
     if (name == "gait2d_prediction") return gaitPrediction(dataDir, options);
     if (name == "gait10dof_replay") return gait10dofReplay(dataDir, options);
+    if (name == "rajagopal_replay") return rajagopalReplay(dataDir, options);
     if (name == "gait2d_inverse") return gaitInverse(dataDir, options);
     if (name == "gait2d_inverse_free") return gaitInverse(dataDir, options, false);
     if (name == "planar_point_mass_coupler") return planarPointMassCoupler(options);

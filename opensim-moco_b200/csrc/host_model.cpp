@@ -189,6 +189,24 @@ void validateTables(const mocob200_tables& T) {
     intRange(T.o_ppoly_i, (long)T.nppoly * MOCOB200_PPOLY_ISTRIDE, "piecewise polynomials");
     intRange(T.o_goal_i, (long)T.ngoal * MOCOB200_GOAL_ISTRIDE, "goals");
     dblRange(T.o_bounds, 6L * ((T.prescribed ? 0 : 2 * T.nq) + T.nz + T.nc), "bounds");
+    if (T.nwrapobj < 0 || T.npathwrap < 0) bad("negative count");
+    if (T.npathwrap > 0) {
+        dblRange(T.o_wo_d, (long)T.nwrapobj * MOCOB200_WO_DSTRIDE, "wrap objects");
+        intRange(T.o_wo_i, (long)T.nwrapobj * MOCOB200_WO_ISTRIDE, "wrap objects");
+        intRange(T.o_pw_i, 2L * T.nmus + (long)T.npathwrap * MOCOB200_PW_ISTRIDE, "path wraps");
+        for (int w = 0; w < T.nwrapobj; ++w) {
+            const int* wi = T.idx + T.o_wo_i + w * MOCOB200_WO_ISTRIDE;
+            if (wi[0] < -1 || wi[0] >= T.nb || wi[1] < 0 || wi[1] > 1 || wi[2] < -1 || wi[2] > 1) bad("wrap object record");
+            if (!(T.dbl[T.o_wo_d + w * MOCOB200_WO_DSTRIDE + 12] > 0)) bad("wrap cylinder radius");
+        }
+        for (int m = 0; m < T.nmus; ++m) {
+            const int first = T.idx[T.o_pw_i + 2 * m], count = T.idx[T.o_pw_i + 2 * m + 1];
+            if (first < 0 || count < 0 || first + count > T.npathwrap) bad("path wrap range of a muscle");
+        }
+        for (int k = 0; k < T.npathwrap; ++k)
+            if (T.idx[T.o_pw_i + 2 * T.nmus + k * MOCOB200_PW_ISTRIDE] < 0 || T.idx[T.o_pw_i + 2 * T.nmus + k * MOCOB200_PW_ISTRIDE] >= T.nwrapobj)
+                bad("path wrap object");
+    }
     if (T.prescribed) {
         intRange(T.o_presc_i, T.nq, "prescribed kinematics");
         for (int k = 0; k < T.nq; ++k)
@@ -940,6 +958,43 @@ std::unique_ptr<FlatProblem> flatten(const Problem& P, const SolverSettings& S) 
     if (T.ncoupler > 0) {
         T.o_cc_i = (int)I.size(); I.insert(I.end(), ccI.begin(), ccI.end());
         T.o_cc_d = (int)D.size(); D.insert(D.end(), ccD.begin(), ccD.end());
+    }
+
+    // ---- wrap cylinders and the (muscle, cylinder) pairings (WrapObject.cpp:97-141, PathWrap.cpp)
+    {
+        std::vector<int> woIndex(M.wrapObjects.size(), -1), woI, pwHead, pwRec;
+        std::vector<double> woD;
+        int nwo = 0;
+        for (size_t w = 0; w < M.wrapObjects.size(); ++w) {
+            const WrapCylinderSpec& W = M.wrapObjects[w];
+            bool used = false;
+            for (const MuscleSpec& mu : M.muscles) for (const auto& pw : mu.wraps) used = used || pw.object == W.name;
+            if (!used) continue;
+            if (!W.supported) throw std::runtime_error("wrap object '" + W.name + "': only WrapCylinder is supported (SURVEY §8 a18)");
+            if (W.wrapAxis == 2 && W.wrapSign != 0) throw std::runtime_error("wrap cylinder '" + W.name + "': a z quadrant is meaningless for a cylinder");
+            woIndex[w] = nwo++;
+            for (int k = 0; k < 9; ++k) woD.push_back(W.X.R.m[k]);
+            for (int a = 0; a < 3; ++a) woD.push_back(W.X.p.v[a]);
+            woD.push_back(W.radius); woD.push_back(W.length); woD.push_back(0.0); woD.push_back(0.0);
+            woI.push_back(mapBody(W.body)); woI.push_back(W.wrapAxis); woI.push_back(W.wrapSign); woI.push_back(W.active ? 1 : 0);
+        }
+        for (const MuscleSpec& mu : M.muscles) {
+            pwHead.push_back((int)pwRec.size() / MOCOB200_PW_ISTRIDE);
+            pwHead.push_back((int)mu.wraps.size());
+            for (const auto& pw : mu.wraps) {
+                int wo = -1;
+                for (size_t w = 0; w < M.wrapObjects.size(); ++w) if (M.wrapObjects[w].name == pw.object) wo = woIndex[w];
+                pwRec.push_back(wo); pwRec.push_back(pw.rangeStart); pwRec.push_back(pw.rangeEnd); pwRec.push_back(0);
+            }
+        }
+        T.nwrapobj = nwo;
+        T.npathwrap = (int)pwRec.size() / MOCOB200_PW_ISTRIDE;
+        T.o_wo_d = T.o_wo_i = T.o_pw_i = 0;
+        if (T.npathwrap > 0) {
+            T.o_wo_d = (int)D.size(); D.insert(D.end(), woD.begin(), woD.end());
+            T.o_wo_i = (int)I.size(); I.insert(I.end(), woI.begin(), woI.end());
+            T.o_pw_i = (int)I.size(); I.insert(I.end(), pwHead.begin(), pwHead.end()); I.insert(I.end(), pwRec.begin(), pwRec.end());
+        }
     }
 
     // ---- variable bounds (MocoProblemRep.cpp:300-430 ; CasOCProblem.h:603-606)

@@ -95,6 +95,11 @@ struct MuscleSpec { // DeGrooteFregly2016Muscle properties (Components/DeGrooteF
     // PathActuator (Actuators/PathActuator.cpp:156-197): tension = optimal_force (maxIsometricForce here) x control, no states
     bool pathActuator = false;
     std::vector<PathPointSpec> points;
+    struct PathWrapSpec { // Simulation/Wrap/PathWrap.cpp: one (path, wrap object) pairing, in PathWrapSet order
+        std::string object;
+        int rangeStart = -1, rangeEnd = -1; // 1-based path-point numbers, < 1 = first / last
+    };
+    std::vector<PathWrapSpec> wraps;
 };
 struct ContactSpec { // SmoothSphereHalfSpaceForce + its ContactSphere / ContactHalfSpace
     std::string name;
@@ -130,8 +135,18 @@ struct CouplerSpec {
     TransformAxisSpec fn; // kind / c0 / c1 / spline (axis unused)
     double scaleFactor = 1;
 };
+struct WrapCylinderSpec { // Simulation/Wrap/WrapCylinder.cpp + WrapObject.cpp:97-141 (pose, quadrant)
+    std::string name;
+    int body = -1;
+    Xform X;                 // wrap frame in the body: xyz_body_rotation (body-fixed X-Y-Z), translation
+    double radius = 0, length = 0;
+    int wrapAxis = 0, wrapSign = 0; // quadrant "x" / "-x" / "y" / "-y" -> axis 0/1, sign +-1; "all" -> sign 0
+    bool active = true;
+    bool supported = true;   // false: a wrap object of another kind (an error only when a path refers to it)
+};
 struct ModelSpec {
     std::string name;
+    std::vector<WrapCylinderSpec> wrapObjects;
     Vec3 gravity;
     std::vector<BodySpec> bodies;
     std::vector<JointSpec> joints;
@@ -151,7 +166,8 @@ struct ModelSpec {
 // .osim: document Version 40000 subset and the Version 30000 layout (joints nested in bodies) of the
 // opensim-models pipelines. musclesAsPathActuators: every muscle of any class is read as a PathActuator with
 // optimal_force 1 on its GeometryPath (its tension becomes the control) - used to replay recorded actuator forces.
-ModelSpec loadOsim(const std::string& path, bool musclesAsPathActuators = false);
+// lockedAsFree: read locked coordinates as ordinary ones (enough for replaying recorded states, where they stay constant)
+ModelSpec loadOsim(const std::string& path, bool musclesAsPathActuators = false, bool lockedAsFree = false);
 // ForceSet file (e.g. reserve actuators) appended to a model: CoordinateActuators only; other classes are returned by name
 std::vector<std::string> appendForceSetFile(ModelSpec& M, const std::string& path);
 // ExternalLoads .xml (+ its data file, resolved relative to the .xml) -> M.externalForces (ExternalLoads.cpp, ExternalForce.cpp:200-317)

@@ -45,6 +45,7 @@ struct Ctx {
     ModelSpec& M;
     bool v3 = false; // document Version < 40000: frames are bodies referenced by bare name
     bool asPathActuators = false;
+    bool lockedAsFree = false;
     // resolve "/bodyset/x", "/ground", "ground", and (Version 30000) a bare body name
     bool baseFrame(const std::string& path, int& body) const {
         if (path == "/ground" || path == "ground") { body = -1; return true; }
@@ -189,8 +190,22 @@ int jointKindOf(const std::string& tag, const std::string& name) {
     if (tag == "PlanarJoint") return MOCOB200_JOINT_PLANAR;
     if (tag == "WeldJoint") return MOCOB200_JOINT_WELD;
     if (tag == "CustomJoint") return MOCOB200_JOINT_CUSTOM;
+    if (tag == "UniversalJoint") return MOCOB200_JOINT_CUSTOM; // two rotations, about X then about the rotated Y (universalAxes below)
     throw std::runtime_error("unsupported joint type '" + tag + "' (" + name + ")");
 }
+// SimTK::MobilizedBody::Universal (UniversalJoint.cpp:60-80): rotation about the parent frame's X by the first coordinate, then
+// about the rotated Y by the second - the function-based mobilizer with axes X, Y (linear) and everything else constant
+void universalAxes(JointSpec& J) {
+    if (J.coords.size() != 2) throw std::runtime_error("UniversalJoint '" + J.name + "' needs two coordinates");
+    const double ax[6][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}, {1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+    for (int k = 0; k < 6; ++k) {
+        TransformAxisSpec& A = J.axes[k];
+        for (int a = 0; a < 3; ++a) A.axis.v[a] = ax[k][a];
+        if (k < 2) { A.fnKind = MOCOB200_FN_LINEAR; A.c0 = 1; A.c1 = 0; A.coord = J.coords[k].name; }
+        else { A.fnKind = MOCOB200_FN_CONSTANT; A.c1 = 0; A.coord.clear(); }
+    }
+}
+bool g_lockedAsFree = false; // set for the duration of one loadOsim call
 void readCoordinates(const XmlNode* holder, JointSpec& J) {
     if (!holder) return;
     for (auto& c : holder->children) {
@@ -199,7 +214,7 @@ void readCoordinates(const XmlNode* holder, JointSpec& J) {
         C.name = c->name();
         auto r = parseDoubles(c->childText("range", "-10 10"));
         if (r.size() == 2) { C.lo = r[0]; C.hi = r[1]; }
-        if (boolOf(c->childText("locked"), false) || boolOf(c->childText("prescribed"), false))
+        if ((boolOf(c->childText("locked"), false) && !g_lockedAsFree) || boolOf(c->childText("prescribed"), false))
             throw std::runtime_error("coordinate '" + C.name + "': locked/prescribed coordinates are unsupported");
         J.coords.push_back(C);
     }
@@ -210,8 +225,24 @@ void readPath(const Ctx& cx, const XmlNode& n, MuscleSpec& mu) {
     if (!gp) throw std::runtime_error("'" + mu.path + "' has no GeometryPath");
     if (const XmlNode* ws = gp->child("PathWrapSet"))
         if (const XmlNode* wo = ws->child("objects"))
-            if (!wo->children.empty())
-                throw std::runtime_error("muscle '" + mu.path + "': PathWrap objects are unsupported (SURVEY §8 a18)");
+            for (auto& w : wo->children) {
+                if (w->tag != "PathWrap") continue;
+                MuscleSpec::PathWrapSpec pw;
+                pw.object = trim(w->childText("wrap_object"));
+                auto r = parseDoubles(w->childText("range", "-1 -1"));
+                if (r.size() == 2) { pw.rangeStart = (int)r[0]; pw.rangeEnd = (int)r[1]; }
+                const std::string method = trim(w->childText("method", "hybrid"));
+                // the method only matters for ellipsoids (WrapEllipsoid.cpp); cylinders ignore it
+                bool found = false;
+                for (const WrapCylinderSpec& o : cx.M.wrapObjects)
+                    if (o.name == pw.object) {
+                        found = true;
+                        if (!o.supported)
+                            throw std::runtime_error("muscle '" + mu.path + "' wraps over '" + pw.object + "': only WrapCylinder is supported (SURVEY §8 a18)");
+                    }
+                if (!found) throw std::runtime_error("muscle '" + mu.path + "': no wrap object named '" + pw.object + "'");
+                mu.wraps.push_back(pw);
+            }
     const XmlNode* pps = gp->child("PathPointSet");
     const XmlNode* objs = pps ? pps->child("objects") : nullptr;
     if (!objs) throw std::runtime_error("muscle '" + mu.path + "' has no path points");
@@ -346,7 +377,9 @@ void readForceLike(const Ctx& cx, const XmlNode& n, const std::string& prefix, c
 
 } // namespace
 
-ModelSpec loadOsim(const std::string& path, bool musclesAsPathActuators) {
+ModelSpec loadOsim(const std::string& path, bool musclesAsPathActuators, bool lockedAsFree) {
+    struct Restore { bool old; ~Restore() { g_lockedAsFree = old; } } restore{g_lockedAsFree};
+    g_lockedAsFree = lockedAsFree;
     auto doc = parseXmlFile(path);
     if (doc->tag != "OpenSimDocument") throw std::runtime_error(path + ": not an OpenSimDocument");
     const std::string* ver = doc->attr("Version");
@@ -375,14 +408,35 @@ ModelSpec loadOsim(const std::string& path, bool musclesAsPathActuators) {
         if (cx.v3) {
             const char* tags[6] = {"inertia_xx", "inertia_yy", "inertia_zz", "inertia_xy", "inertia_xz", "inertia_yz"};
             for (int i = 0; i < 6; ++i) B.inertiaCom[i] = dblOf(*b, tags[i], 0.0);
-            if (const XmlNode* ws = b->child("WrapObjectSet"))
-                if (const XmlNode* wo = ws->child("objects"))
-                    if (!wo->children.empty()) { /* wrap objects matter only when a path refers to them (refused there) */ }
         } else {
             auto in = parseDoubles(b->childText("inertia", "0 0 0 0 0 0"));
             if (in.size() != 6) throw std::runtime_error("body '" + B.name + "': inertia needs 6 numbers");
             for (int i = 0; i < 6; ++i) B.inertiaCom[i] = in[i];
         }
+        if (const XmlNode* ws = b->child("WrapObjectSet"))
+            if (const XmlNode* wo = ws->child("objects"))
+                for (auto& w : wo->children) {
+                    WrapCylinderSpec W;
+                    W.name = w->name();
+                    W.body = (int)M.bodies.size();
+                    W.supported = w->tag == "WrapCylinder";
+                    const Vec3 rot = vec3Of(w->childText("xyz_body_rotation", "0 0 0"), "xyz_body_rotation");
+                    W.X.R = rotXYZ(rot.v[0], rot.v[1], rot.v[2]);
+                    W.X.p = vec3Of(w->childText("translation", "0 0 0"), "translation");
+                    W.active = boolOf(w->childText("active"), true);
+                    W.radius = dblOf(*w, "radius", 0.0);
+                    W.length = dblOf(*w, "length", 0.0);
+                    const std::string qd = trim(w->childText("quadrant", "all"));
+                    if (qd == "x" || qd == "+x" || qd == "X" || qd == "+X") { W.wrapAxis = 0; W.wrapSign = 1; }
+                    else if (qd == "-x" || qd == "-X") { W.wrapAxis = 0; W.wrapSign = -1; }
+                    else if (qd == "y" || qd == "+y" || qd == "Y" || qd == "+Y") { W.wrapAxis = 1; W.wrapSign = 1; }
+                    else if (qd == "-y" || qd == "-Y") { W.wrapAxis = 1; W.wrapSign = -1; }
+                    else if (qd == "z" || qd == "+z" || qd == "Z" || qd == "+Z") { W.wrapAxis = 2; W.wrapSign = 1; }
+                    else if (qd == "-z" || qd == "-Z") { W.wrapAxis = 2; W.wrapSign = -1; }
+                    else if (qd == "all" || qd == "ALL" || qd == "All" || qd == "Unassigned") { W.wrapAxis = 0; W.wrapSign = 0; }
+                    else throw std::runtime_error("wrap object '" + W.name + "': bad quadrant '" + qd + "'");
+                    M.wrapObjects.push_back(W);
+                }
         M.bodies.push_back(B);
         bodyNodes.push_back(b.get());
     }
@@ -408,7 +462,8 @@ ModelSpec loadOsim(const std::string& path, bool musclesAsPathActuators) {
             J.child.X.R = rotXYZ(o.v[0], o.v[1], o.v[2]);
             J.child.X.p = vec3Of(j->childText("location", "0 0 0"), "location");
             if (const XmlNode* cs = j->child("CoordinateSet")) readCoordinates(cs->child("objects"), J);
-            if (J.kind == MOCOB200_JOINT_CUSTOM) readSpatialTransform(*j, J);
+            if (j->tag == "UniversalJoint") universalAxes(J);
+            else if (J.kind == MOCOB200_JOINT_CUSTOM) readSpatialTransform(*j, J);
             M.joints.push_back(J);
         }
     } else {
@@ -422,7 +477,8 @@ ModelSpec loadOsim(const std::string& path, bool musclesAsPathActuators) {
             J.parent = cx.jointFrame(*j, j->childText("socket_parent_frame"));
             J.child = cx.jointFrame(*j, j->childText("socket_child_frame"));
             readCoordinates(j->child("coordinates"), J);
-            if (J.kind == MOCOB200_JOINT_CUSTOM) readSpatialTransform(*j, J);
+            if (j->tag == "UniversalJoint") universalAxes(J);
+            else if (J.kind == MOCOB200_JOINT_CUSTOM) readSpatialTransform(*j, J);
             M.joints.push_back(J);
         }
     }

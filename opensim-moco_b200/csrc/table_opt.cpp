@@ -145,6 +145,16 @@ int mergeWeldedBodies(const mocob200_tables& T, std::vector<double>& dbl, std::v
         int* xi = idx.data() + T.o_xforce_i + f * MOCOB200_XFORCE_ISTRIDE;
         for (int k = 0; k < 3; ++k) xi[k] = remap(xi[k]);
     }
+    for (int w = 0; w < (T.npathwrap > 0 ? T.nwrapobj : 0); ++w) { // wrap cylinders: frame in the host body
+        int* wi = idx.data() + T.o_wo_i + w * MOCOB200_WO_ISTRIDE;
+        double* wd = dbl.data() + T.o_wo_d + w * MOCOB200_WO_DSTRIDE;
+        if (wi[0] >= 0 && !keep[wi[0]]) {
+            const M3 R = mulM(Rh[wi[0]].m, wd);
+            std::memcpy(wd, R.m, sizeof R.m);
+            moveStation(wi[0], wd + 9);
+        }
+        wi[0] = remap(wi[0]);
+    }
     // kept bodies whose parent was removed hang on the parent's host: X_PF' = X_host,parent X_PF
     std::vector<double> newD((size_t)nb2 * MOCOB200_BODY_DSTRIDE);
     std::vector<int> newI((size_t)nb2 * MOCOB200_BODY_ISTRIDE), newCj(nb2, -1);

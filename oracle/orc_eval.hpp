@@ -1,7 +1,10 @@
 // TEST INFRASTRUCTURE ONLY — CPU oracle: applied forces, the fused point function and the endpoint
 // (goal) functions.
 #pragma once
+#include <stdexcept>
+
 #include "orc_dynamics.hpp"
+#include "orc_wrap.hpp"
 
 namespace orc {
 
@@ -48,10 +51,11 @@ Vec3<S> contactForce(const Model& M, int ci, const Frames<S>& K, Vec3<S>& applic
 }
 
 // Path geometry of one muscle (GeometryPath.cpp:817-864, 1117-1145; Point.cpp:130-140;
-// ConditionalPathPoint.cpp:160-169; MovingPathPoint.cpp:216-315, 374-392).
+// ConditionalPathPoint.cpp:160-169; MovingPathPoint.cpp:216-315, 374-392), with wrap cylinders
+// (GeometryPath.cpp:868-1094 applyWrapObjects, :1095-1110 calcPathLengthChange, :1117-1145; orc_wrap.hpp).
 template <class S>
 struct PathState {
-    static constexpr int kMaxPts = 32;
+    static constexpr int kMaxPts = 40;
     int n = 0;
     Vec3<S> pos[kMaxPts], dPdq[kMaxPts]; // ground
     int body[kMaxPts], movingCoord[kMaxPts];
@@ -60,8 +64,10 @@ struct PathState {
 template <class S>
 void pathGeometry(const Model& M, int m, const S* q, const S* u, const Frames<S>& K, PathState<S>& P) {
     const int* mi = M.musI(m);
-    P.n = 0; P.length = S(0.0); P.speed = S(0.0);
-    Vec3<S> prevP, prevV;
+    constexpr int kMax = PathState<S>::kMaxPts;
+    // ---- the active path points, in PathPointSet order
+    int nA = 0, orig[kMax], bodyA[kMax], mcA[kMax];
+    Vec3<S> posA[kMax], velA[kMax], dpA[kMax];
     for (int k = 0; k < mi[1]; ++k) {
         const int* pi = M.ppI(mi[0] + k);
         const double* pd = M.ppD(mi[0] + k);
@@ -87,14 +93,142 @@ void pathGeometry(const Model& M, int m, const S* q, const S* u, const Frames<S>
             if (b >= 0) { vG = vG + K.R[b] * vloc; dp = K.R[b] * dp; }
             else vG = vG + vloc;
         }
+        orig[nA] = k; bodyA[nA] = b; mcA[nA] = mc; posA[nA] = pG; velA[nA] = vG; dpA[nA] = dp;
+        ++nA;
+    }
+    // ---- the current path: indices >= 0 are active points, -(2 w + 1) / -(2 w + 2) the two wrap points of pairing w
+    int path[kMax], np = nA;
+    for (int k = 0; k < nA; ++k) path[k] = k;
+    const int nW = M.T->npathwrap > 0 ? M.pathWrapCount(m) : 0;
+    constexpr int kMaxW = 8;
+    struct WrapPts { bool on = false; wrap::V r1, r2; double arc = 0; } W[kMaxW]; // tangent points in the wrap object's BODY frame
+    auto groundOf = [&](int b, const wrap::V& local) -> wrap::V { // double-precision station position
+        if (b < 0) return local;
+        const Vec3<S> g = stationPosition(K, b, Vec3<S>(S(local[0]), S(local[1]), S(local[2])));
+        return {val(g.x), val(g.y), val(g.z)};
+    };
+    auto bodyFrameOf = [&](int b, const wrap::V& g) -> wrap::V { // ground point expressed in body b
+        if (b < 0) return g;
+        const Vec3<S> d{S(g[0]) - K.origin[b].x, S(g[1]) - K.origin[b].y, S(g[2]) - K.origin[b].z};
+        const Vec3<S> l = transpose(K.R[b]) * d;
+        return {val(l.x), val(l.y), val(l.z)};
+    };
+    auto woOfPath = [&](int e) { return e >= 0 ? -1 : M.pathWrapI(m, (-e - 1) / 2)[0]; }; // wrap object of a path entry (-1: none)
+    auto groundPoint = [&](int e) -> wrap::V {
+        if (e >= 0) return {val(posA[e].x), val(posA[e].y), val(posA[e].z)};
+        const int w = (-e - 1) / 2;
+        return groundOf(M.wrapObjI(M.pathWrapI(m, w)[0])[0], ((-e - 1) % 2 == 0) ? W[w].r1 : W[w].r2);
+    };
+    auto dist = [](const wrap::V& a, const wrap::V& b) { return std::sqrt(wrap::dist2(a, b)); };
+    auto removeWrap = [&](int w) {
+        for (int j = 0; j < np; ++j)
+            if (path[j] == -(2 * w + 1)) { for (int k = j; k + 2 < np; ++k) path[k] = path[k + 2]; np -= 2; return; }
+    };
+    auto totalLength = [&]() {
+        double len = 0;
+        for (int k = 0; k + 1 < np; ++k) {
+            const int a = path[k], b = path[k + 1];
+            if (a < 0 && b < 0 && woOfPath(a) == woOfPath(b)) len += W[(-b - 1) / 2].arc;
+            else len += dist(groundPoint(a), groundPoint(b));
+        }
+        return len;
+    };
+    if (nW > kMaxW) throw std::runtime_error("oracle: more path wraps on one muscle than kMaxW");
+    if (nW > 0) {
+        int order[kMaxW], result[kMaxW];
+        for (int i = 0; i < nW; ++i) order[i] = i;
+        const int maxIterations = nW < 2 ? 1 : 8;
+        double lastLength = INFINITY;
+        bool abort = false;
+        for (int kk = 0; kk < maxIterations && !abort; ++kk) {
+            for (int i = 0; i < nW && !abort; ++i) {
+                result[i] = wrap::NoWrap;
+                const int w = order[i];
+                const int* pw = M.pathWrapI(m, w);
+                const int* wi = M.wrapObjI(pw[0]);
+                const double* wd = M.wrapObjD(pw[0]);
+                bool haveBest = false;
+                wrap::CylinderWrap best;
+                int bestEnd = -1;
+                double minChange = INFINITY;
+                removeWrap(w);
+                W[w].on = false;
+                if (!wi[3]) continue; // inactive wrap object
+                const int wrapStart = pw[1] < 1 ? 0 : pw[1] - 1, wrapEnd = pw[2] < 1 ? mi[1] - 1 : pw[2] - 1;
+                int first = -1, last = -1; // active points (indices into the active list) at the ends of the range
+                for (int k = 0; k < nA; ++k) if (orig[k] >= wrapStart && orig[k] <= wrapEnd) { if (first < 0) first = k; last = k; }
+                if (first < 0) { abort = true; break; }
+                int start = -1, end = -1;
+                for (int j = 0; j < np; ++j) { if (path[j] == first) start = j; if (path[j] == last) end = j; }
+                if (start < 0 || end < 0) { abort = true; break; }
+                auto toWrapFrame = [&](const wrap::V& g) {
+                    const wrap::V b = bodyFrameOf(wi[0], g);
+                    const wrap::V d{b[0] - wd[9], b[1] - wd[10], b[2] - wd[11]};
+                    return wrap::V{wd[0] * d[0] + wd[3] * d[1] + wd[6] * d[2], wd[1] * d[0] + wd[4] * d[1] + wd[7] * d[2],
+                                   wd[2] * d[0] + wd[5] * d[1] + wd[8] * d[2]}; // R_BW^T d
+                };
+                for (int pt1 = start; pt1 < end; ++pt1) {
+                    const int pt2 = pt1 + 1;
+                    const int wa = woOfPath(path[pt1]), wb = woOfPath(path[pt2]);
+                    if (wa >= 0 && wb >= 0 && wa == wb) continue;
+                    const wrap::V g1 = groundPoint(path[pt1]), g2 = groundPoint(path[pt2]);
+                    wrap::CylinderWrap cw;
+                    const wrap::V a1 = toWrapFrame(g1), a2 = toWrapFrame(g2);
+                    result[i] = wrap::cylinderWrapLine(wd[12], wd[13], wi[1], wi[2], a1, a2, cw);
+                    if (result[i] == wrap::MandatoryWrap) { best = cw; bestEnd = pt2; haveBest = true; break; }
+                    if (result[i] == wrap::Wrapped) {
+                        const double change = dist(a1, cw.r1) + cw.arc + dist(a2, cw.r2) - dist(g1, g2);
+                        if (change < minChange) { best = cw; bestEnd = pt2; haveBest = true; minChange = change; }
+                    }
+                }
+                if (!haveBest) continue;
+                auto toBody = [&](const wrap::V& r) { // wrap frame -> the wrap object's body frame
+                    return wrap::V{wd[0] * r[0] + wd[1] * r[1] + wd[2] * r[2] + wd[9], wd[3] * r[0] + wd[4] * r[1] + wd[5] * r[2] + wd[10],
+                                   wd[6] * r[0] + wd[7] * r[1] + wd[8] * r[2] + wd[11]};
+                };
+                W[w].on = true; W[w].r1 = toBody(best.r1); W[w].r2 = toBody(best.r2); W[w].arc = best.arc;
+                if (np + 2 > kMax) throw std::runtime_error("oracle: path longer than kMaxPts");
+                for (int k = np - 1; k >= bestEnd; --k) path[k + 2] = path[k];
+                path[bestEnd] = -(2 * w + 1);
+                path[bestEnd + 1] = -(2 * w + 2);
+                np += 2;
+            }
+            if (abort) break;
+            const double len = totalLength();
+            if (std::fabs(len - lastLength) < 0.0005) break;
+            lastLength = len;
+            if (kk == 0 && nW > 1 && result[0] == wrap::NoWrap && result[1] == wrap::InsideRadius) {
+                order[0] = 1; order[1] = 0;
+                removeWrap(0);
+                W[0].on = false;
+            }
+        }
+    }
+    // ---- length, lengthening speed and the point list the tension is applied through
+    P.n = 0; P.length = S(0.0); P.speed = S(0.0);
+    Vec3<S> prevP, prevV;
+    int prevEntry = 0;
+    for (int j = 0; j < np; ++j) {
+        const int e = path[j];
+        Vec3<S> pG, vG, dp;
+        int b, mc = -1;
+        if (e >= 0) { pG = posA[e]; vG = velA[e]; dp = dpA[e]; b = bodyA[e]; mc = mcA[e]; }
+        else { // a wrap point: a station of the wrap object's body (PathWrapPoint)
+            const int w = (-e - 1) / 2;
+            const wrap::V& r = ((-e - 1) % 2 == 0) ? W[w].r1 : W[w].r2;
+            b = M.wrapObjI(M.pathWrapI(m, w)[0])[0];
+            pG = stationPosition(K, b, Vec3<S>(S(r[0]), S(r[1]), S(r[2])));
+            vG = pointVelocity(K, b, pG);
+        }
         if (P.n > 0) {
             const Vec3<S> r = prevP - pG, dv = prevV - vG;
             const S d = norm(r);
-            P.length += d;
+            if (e < 0 && prevEntry < 0 && woOfPath(e) == woOfPath(prevEntry)) P.length += S(W[(-e - 1) / 2].arc); // over the surface
+            else P.length += d;
             if (val(d) < 2.220446049250313e-16) P.speed += norm(dv);
             else P.speed += dot(dv, (S(1.0) / d) * r);
         }
-        prevP = pG; prevV = vG;
+        prevP = pG; prevV = vG; prevEntry = e;
         P.pos[P.n] = pG; P.body[P.n] = b; P.movingCoord[P.n] = mc; P.dPdq[P.n] = dp;
         ++P.n;
     }

@@ -58,6 +58,11 @@ struct Model {
     const int* cjI(int cj) const { return T->idx + T->o_cj_i + cj * MOCOB200_CJ_ISTRIDE; }
     const int* xforceI(int f) const { return T->idx + T->o_xforce_i + f * MOCOB200_XFORCE_ISTRIDE; }
     const int* couplerI(int k) const { return T->idx + T->o_cc_i + k * MOCOB200_CC_ISTRIDE; }
+    // wrap cylinders and the (muscle, cylinder) pairings
+    const double* wrapObjD(int w) const { return T->dbl + T->o_wo_d + w * MOCOB200_WO_DSTRIDE; }
+    const int* wrapObjI(int w) const { return T->idx + T->o_wo_i + w * MOCOB200_WO_ISTRIDE; }
+    int pathWrapCount(int m) const { return T->idx[T->o_pw_i + 2 * m + 1]; }
+    const int* pathWrapI(int m, int k) const { return T->idx + T->o_pw_i + 2 * T->nmus + (T->idx[T->o_pw_i + 2 * m] + k) * MOCOB200_PW_ISTRIDE; }
     const double* couplerD(int k) const { return T->dbl + T->o_cc_d + k * MOCOB200_CC_DSTRIDE; }
 };
 
