@@ -90,6 +90,8 @@ struct mocob200_handle {
     bool useWarp = true;
     int kernelMode = 0; // 0 auto, 1 warp, 2 thread
     long warpMaxEvals = 30000;
+    bool beyondThreadKernels = false;
+    bool wrapInWarpKernels = false; // set once the warp kernels evaluate wrap cylinders
     bool warpFor(long evals) const { return kernelMode == 1 || (kernelMode == 0 && evals <= warpMaxEvals); }
     std::vector<void*> owned;
     double* d_cfg = nullptr; // per-point blobs of the nominal evaluation (warp kernels)
@@ -374,7 +376,17 @@ void recTiming(cudaEvent_t e, cudaStream_t s) {
 }
 
 // stages shared by the pipelines; x must already be in d_x
+// Wrap cylinders are evaluated by the path kernel (mocob200_eval_points(..., MOCOB200_POINTS_PATHS)) and by the point functions'
+// thread-level muscle code; the warp kernels' staged path geometry does not carry them yet: refuse rather than ignore them
+bool dynamicsSupported(mocob200_handle* h) {
+    if (h->DT.npathwrap > 0 && !h->wrapInWarpKernels) {
+        h->err = "models with wrap cylinders: only path lengths / speeds (MOCOB200_POINTS_PATHS) are available on the device so far (SURVEY 8 a18)";
+        return false;
+    }
+    return true;
+}
 bool runNominal(mocob200_handle* h) {
+    if (!dynamicsSupported(h)) return false;
     if (h->rank >= h->eff) return true; // idle rank
     if (h->warpFor(h->p1 - h->p0)) launch_wpoints_nominal(h->DT, h->WA, h->DL, h->d_x, h->d_Y, nullptr, h->p0, h->p1 - h->p0, h->stream);
     else launch_points_nominal(h->DT, h->DL, h->d_x, h->d_Y, h->p0, h->p1 - h->p0, h->stream);
@@ -428,6 +440,7 @@ void launchFdKernels(mocob200_handle* h, cudaEvent_t after_nominal) {
 // beside its assembly kernel and the caller joins on h->evI afterwards. Returns through *deferred whether that happened.
 bool runFd(mocob200_handle* h, bool deferIntegralDerivs = false, bool* deferred = nullptr) {
     if (deferred) *deferred = false;
+    if (!dynamicsSupported(h)) return false;
     recTiming(h->ev[0], h->stream);
     if (h->rank >= h->eff) { recTiming(h->ev[1], h->stream); return true; } // idle rank
     const bool overlap = h->eff == 1; // single rank: Y is complete as soon as the nominal evaluations are
@@ -578,8 +591,17 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
         const double k = 0.5 * std::pow(cd[16], 2.0 / 3.0);
         cd[DEV_CONTACT_HERTZ] = (4.0 / 3.0) * k * std::sqrt(cd[3] * k);
     }
-    if (T->nb > MOCOB200_MAXB || T->nq > MOCOB200_MAXQ || T->ncontact > MOCOB200_MAXCONTACT)
+    if (T->nb > SizeHuge::NB || T->nq > SizeHuge::NQ || T->ncontact > MOCOB200_MAXCONTACT)
         return fail(MOCOB200_ERR_UNSUPPORTED, "model exceeds the compiled limits (bodies/coordinates/contacts)");
+    // beyond the thread-per-evaluation kernels' arrays (16 bodies / 16 coordinates / 160 inputs) only the warp kernels apply
+    h->beyondThreadKernels = T->nb > MOCOB200_MAXB || T->nq > MOCOB200_MAXQ || L.n_in > SizeLarge::NIN || T->npathwrap > 0;
+    if (h->beyondThreadKernels)
+        for (int g = 0; g < T->ngoal; ++g) {
+            const int* gr = T->idx + T->o_goal_i + g * MOCOB200_GOAL_ISTRIDE;
+            const bool disp = gr[0] == MOCOB200_GOAL_AVERAGE_SPEED || gr[0] == MOCOB200_GOAL_INITIAL_VELOCITY_EQUILIBRIUM_DGF ||
+                              (gr[0] == MOCOB200_GOAL_CONTROL && T->idx[gr[4] + 1]);
+            if (disp) return fail(MOCOB200_ERR_UNSUPPORTED, "goals that evaluate the model's kinematics at the end points are limited to 16 bodies / 16 coordinates");
+        }
     DevTables& D = h->DT;
     D.dbl = (const double*)own(devUpload(dbl));
     D.idx = (const int*)own(devUpload(idx));
@@ -596,6 +618,7 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     D.ncoupler = T->ncoupler; D.o_cc_i = T->o_cc_i; D.o_cc_d = T->o_cc_d;
     D.nm = L.nm; D.n_kc = L.n_kc; D.enforce_derivs = L.enforce_derivs;
     D.prescribed = L.prescribed; D.o_presc_i = T->o_presc_i;
+    D.nwrapobj = T->nwrapobj; D.o_wo_d = T->o_wo_d; D.o_wo_i = T->o_wo_i; D.npathwrap = T->npathwrap; D.o_pw_i = T->o_pw_i;
     D.implicit = L.implicit; D.n_auxres = L.n_auxres; D.n_integrand = L.n_integrand;
     // layout
     DevLayout& G = h->DL;
@@ -645,8 +668,9 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
         const char* k = devEnv("MOCOB200_KERNEL");
         h->kernelMode = (k && std::string(k) == "thread") ? 2 : (k && std::string(k) == "warp") ? 1 : 0;
         // the thread-per-evaluation dynamics handle the constant-axis joints only: function-based joints run on the warp kernels
-        if (T->ncustom > 0) {
-            if (h->kernelMode == 2) return fail(MOCOB200_ERR_UNSUPPORTED, "the thread-per-evaluation kernels do not support custom joints");
+        if (T->ncustom > 0 || h->beyondThreadKernels) {
+            if (h->kernelMode == 2)
+                return fail(MOCOB200_ERR_UNSUPPORTED, "the thread-per-evaluation kernels do not support custom joints or models beyond 16 bodies / 16 coordinates / 160 inputs");
             h->kernelMode = 1;
         }
         std::string e;
@@ -923,6 +947,7 @@ int mocob200_eval_grad_f(mocob200_handle* h, const double* x, double* grad) {
 // goals here read x alone, so every rank evaluates them itself (the caller routes problems whose endpoint constraints carry an
 // integral through the gather-everything pipeline instead).
 static bool jacPipelineSharded(mocob200_handle* h, double* d_vals) {
+    if (!dynamicsSupported(h)) return false;
     recTiming(h->ev[0], h->stream);
     if (h->rank >= h->eff) { recTiming(h->ev[1], h->stream); return true; } // idle rank
     const Layout& L = h->L;
@@ -1222,6 +1247,7 @@ inline size_t roundUp32(size_t n) { return (n + 31) / 32 * 32; } // 256-byte sec
 extern "C" int mocob200_eval_g_static(mocob200_handle* h, const double* d_x, double* d_g, void* cuda_stream) {
     if (!h || !d_x || !d_g) return MOCOB200_ERR_ARG;
     if (h->world != 1 || h->eff != 1) { h->err = "eval_g_static: single-rank handles only"; return MOCOB200_ERR_UNSUPPORTED; }
+    if (!dynamicsSupported(h)) return MOCOB200_ERR_UNSUPPORTED;
     const Layout& L = h->L;
     const size_t nY = roundUp32((size_t)L.n_grid * L.n_out), nI = roundUp32(3 * (size_t)L.n_integrand + 1),
                  nG = roundUp32((size_t)h->DL.n_eout_total + 1), nE = roundUp32((size_t)(h->DL.n_eout_total + 1) * L.n_ein);

@@ -23,15 +23,16 @@ __global__ void k_points_nominal(DevTables T, DevLayout L, const double* __restr
 // Muscle-tendon path length and lengthening speed of every path at every grid point: out[j][m] = (length, speed).
 // What GeometryPath::getLength / getLengtheningSpeed report (GeometryPath.cpp:848-864, 1117-1145) - the quantities the
 // reference's MuscleAnalysis / Actuation analyses print; one thread per (grid point, muscle).
+template <class SZ>
 __global__ void k_paths(DevTables T, DevLayout L, const double* __restrict__ x, double* __restrict__ out, int p0, int np) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= np * T.nmus) return;
     const int j = p0 + t / T.nmus, m = t % T.nmus;
-    double in[MOCOB200_MAX_IN];
+    double in[SZ::NIN];
     gather_inputs(L, x, j, in);
-    double pk[3 * MOCOB200_MAXQ];
+    double pk[3 * SZ::NQ];
     const PointInputs P = point_inputs(T, in, pk);
-    Scratch S;
+    ScratchT<SZ> S;
     kinematics(T, P.q, P.u, S);
     double ls[2];
     muscle_force(T, m, P.q, P.u, P.z, P.ctl, P.auxder, S, false, false, ls);
@@ -41,7 +42,8 @@ __global__ void k_paths(DevTables T, DevLayout L, const double* __restrict__ x, 
 void launch_paths(const DevTables& T, const DevLayout& L, const double* d_x, double* d_out, int p0, int np, cudaStream_t s) {
     const int n = np * T.nmus;
     if (n <= 0) return;
-    k_paths<<<(n + 63) / 64, 64, 0, s>>>(T, L, d_x, d_out, p0, np);
+    if (T.npathwrap > 0 || T.nb > SizeLarge::NB || T.nq > SizeLarge::NQ || L.n_in > SizeLarge::NIN) k_paths<SizeHuge><<<(n + 63) / 64, 64, 0, s>>>(T, L, d_x, d_out, p0, np);
+    else k_paths<SizeLarge><<<(n + 63) / 64, 64, 0, s>>>(T, L, d_x, d_out, p0, np);
 }
 
 // block = one grid point; thread t < ndirs = FD direction dirs[t] (all n_in inputs when dirs == nullptr); thread ndirs =

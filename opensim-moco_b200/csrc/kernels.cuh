@@ -17,7 +17,7 @@ inline const char* devEnv(const char* name) {
     return on ? std::getenv(name) : nullptr;
 }
 
-#define MOCOB200_MAX_IN 160
+#define MOCOB200_MAX_IN 200
 #define MOCOB200_MAX_OUT 72
 #define MOCOB200_MAX_EOUT 64 /* outputs of one endpoint goal */
 

@@ -28,8 +28,12 @@ namespace mocob200 {
 #define MOCOB200_MAXPPM 12 /* path points per muscle */
 // The thread-per-evaluation code keeps its scratch in thread-local memory, whose traffic bounds it: every array
 // is sized by a size class chosen at launch, so that a 8-body / 58-input model does not carry 16-body / 160-input frames.
-struct SizeLarge { static constexpr int NB = MOCOB200_MAXB, NQ = MOCOB200_MAXQ, NPPM = MOCOB200_MAXPPM, NIN = 160, NOUT = 72; };
-struct SizeSmall { static constexpr int NB = 8, NQ = 12, NPPM = 8, NIN = 64, NOUT = 32; };
+// WRAP: the muscle code of this instantiation evaluates wrap cylinders (kept out of the FD kernels' instantiations: the mere
+// presence of the call costs the config-5 kernels 10 % through register allocation; models with wrap cylinders do not run there)
+struct SizeLarge { static constexpr int NB = MOCOB200_MAXB, NQ = MOCOB200_MAXQ, NPPM = MOCOB200_MAXPPM, NIN = 160, NOUT = 72; static constexpr bool WRAP = false; };
+struct SizeSmall { static constexpr int NB = 8, NQ = 12, NPPM = 8, NIN = 64, NOUT = 32; static constexpr bool WRAP = false; };
+// full-body models (Rajagopal: 22 bodies, 39 coordinates): kinematics / path kernels only; their dynamics run on the warp kernels
+struct SizeHuge { static constexpr int NB = 24, NQ = 40, NPPM = MOCOB200_MAXPPM, NIN = 200, NOUT = 72; static constexpr bool WRAP = true; };
 
 struct DevTables { // mocob200_tables with device (or shared-memory) pool pointers
     const double* dbl;
@@ -47,6 +51,7 @@ struct DevTables { // mocob200_tables with device (or shared-memory) pool pointe
     int nm, n_kc, enforce_derivs;           // multipliers per point, kinematic-constraint outputs, their derivatives enforced
     int implicit; // multibody dynamics mode
     int prescribed, o_presc_i; // prescribed kinematics: idx[o_presc_i + k] = piecewise polynomial of coordinate k
+    int nwrapobj, o_wo_d, o_wo_i, npathwrap, o_pw_i; // wrap cylinders and (muscle, cylinder) pairings
     int n_auxres;
     int n_integrand; // goals with an integrand, in goal order
 };
@@ -68,6 +73,9 @@ __device__ __forceinline__ V3 rmul(const double* R, V3 v) {
 __device__ __forceinline__ V3 rtmul(const double* R, V3 v) {
     return mk(R[0] * v.x + R[3] * v.y + R[6] * v.z, R[1] * v.x + R[4] * v.y + R[7] * v.z, R[2] * v.x + R[5] * v.y + R[8] * v.z);
 }
+} // namespace mocob200
+#include "point_wrap.cuh"
+namespace mocob200 {
 __device__ __forceinline__ void mm3(const double* A, const double* B, double* C) { // C = A B
 #pragma unroll
     for (int i = 0; i < 3; ++i)
@@ -579,10 +587,206 @@ __device__ inline V3 contact_force(const DevTables& T, int ci, ScratchT<SZ>& S, 
 // Muscle path geometry + muscle model + equivalent forces for muscle m
 // (GeometryPath.cpp:306-432, 817-864, 1117-1145; Point.cpp:130-140; ConditionalPathPoint.cpp:160-169;
 //  MovingPathPoint.cpp:216-315, 374-392; PathActuator.cpp:170-197).
+// ---- a muscle path with wrap cylinders (GeometryPath.cpp:868-1094 applyWrapObjects, :1095-1110 calcPathLengthChange,
+// :1117-1145): the active path points in `pos/body` (ground positions), `orig` their numbers in the PathPointSet. Builds the
+// current path in `path` (entries >= 0: active point; -(2 w + 1), -(2 w + 2): the two tangent points of the muscle's pairing w,
+// stations of the wrap object's body held in wr1 / wr2 in that body's frame, with the helix length in warc).
+#define MOCOB200_MAXWRAP 4 /* pairings per muscle */
+template <class SZ>
+__device__ __noinline__ void apply_wrap_objects(const DevTables& T, int m, const ScratchT<SZ>& S, int nA, int nSet, const int* orig,
+                                                const V3* pos, int* path, int& np, V3* wr1, V3* wr2, double* warc) {
+    const int pw0 = T.idx[T.o_pw_i + 2 * m], nW = min(T.idx[T.o_pw_i + 2 * m + 1], MOCOB200_MAXWRAP);
+    const int* pwBase = T.idx + T.o_pw_i + 2 * T.nmus + pw0 * MOCOB200_PW_ISTRIDE;
+    auto wobj = [&](int e) { return e >= 0 ? -1 : pwBase[((-e - 1) >> 1) * MOCOB200_PW_ISTRIDE]; }; // wrap object of a path entry
+    auto ground = [&](int e) -> V3 {
+        if (e >= 0) return pos[e];
+        const int w = (-e - 1) >> 1;
+        const int b = T.idx[T.o_wo_i + wobj(e) * MOCOB200_WO_ISTRIDE];
+        const V3 r = ((-e - 1) & 1) ? wr2[w] : wr1[w];
+        return b >= 0 ? S.p[b] + rmul(S.R[b], r) : r;
+    };
+    auto removeWrap = [&](int w) {
+        for (int j = 0; j < np; ++j)
+            if (path[j] == -(2 * w + 1)) { for (int k = j; k + 2 < np; ++k) path[k] = path[k + 2]; np -= 2; return; }
+    };
+    int order[MOCOB200_MAXWRAP], result[MOCOB200_MAXWRAP];
+    for (int i = 0; i < nW; ++i) order[i] = i;
+    const int maxIterations = nW < 2 ? 1 : 8;
+    double lastLength = INFINITY;
+    for (int kk = 0; kk < maxIterations; ++kk) {
+        for (int i = 0; i < nW; ++i) {
+            result[i] = WRAP_NONE;
+            const int w = order[i];
+            const int* pw = pwBase + w * MOCOB200_PW_ISTRIDE;
+            const int* wi = T.idx + T.o_wo_i + pw[0] * MOCOB200_WO_ISTRIDE;
+            const double* wd = T.dbl + T.o_wo_d + pw[0] * MOCOB200_WO_DSTRIDE;
+            removeWrap(w);
+            if (!wi[3]) continue;
+            const int wrapStart = pw[1] < 1 ? 0 : pw[1] - 1, wrapEnd = pw[2] < 1 ? nSet - 1 : pw[2] - 1;
+            int first = -1, last = -1;
+            for (int k = 0; k < nA; ++k) if (orig[k] >= wrapStart && orig[k] <= wrapEnd) { if (first < 0) first = k; last = k; }
+            if (first < 0) return;
+            int start = -1, end = -1;
+            for (int j = 0; j < np; ++j) { if (path[j] == first) start = j; if (path[j] == last) end = j; }
+            if (start < 0 || end < 0) return;
+            const int wb = wi[0];
+            auto toWrapFrame = [&](V3 g) { // ground -> wrap object's body -> wrap frame
+                const V3 b = wb >= 0 ? rtmul(S.R[wb], g - S.p[wb]) : g;
+                return rtmul(wd, b - ld3(wd + 9));
+            };
+            bool haveBest = false;
+            CylWrap best;
+            int bestEnd = -1;
+            double minChange = INFINITY;
+            for (int pt1 = start; pt1 < end; ++pt1) {
+                const int pt2 = pt1 + 1;
+                const int wa = wobj(path[pt1]), wc = wobj(path[pt2]);
+                if (wa >= 0 && wc >= 0 && wa == wc) continue;
+                const V3 g1 = ground(path[pt1]), g2 = ground(path[pt2]);
+                const V3 a1 = toWrapFrame(g1), a2 = toWrapFrame(g2);
+                CylWrap cw;
+                result[i] = wr_cylinder(wd[12], wd[13], wi[1], wi[2], a1, a2, cw);
+                if (result[i] == WRAP_MANDATORY) { best = cw; bestEnd = pt2; haveBest = true; break; }
+                if (result[i] == WRAP_WRAPPED) {
+                    const double change = wr_norm(a1 - cw.r1) + cw.arc + wr_norm(a2 - cw.r2) - wr_norm(g1 - g2);
+                    if (change < minChange) { best = cw; bestEnd = pt2; haveBest = true; minChange = change; }
+                }
+            }
+            if (!haveBest) continue;
+            wr1[w] = rmul(wd, best.r1) + ld3(wd + 9);
+            wr2[w] = rmul(wd, best.r2) + ld3(wd + 9);
+            warc[w] = best.arc;
+            for (int k = np - 1; k >= bestEnd; --k) path[k + 2] = path[k];
+            path[bestEnd] = -(2 * w + 1);
+            path[bestEnd + 1] = -(2 * w + 2);
+            np += 2;
+        }
+        double len = 0;
+        for (int k = 0; k + 1 < np; ++k) {
+            const int a = path[k], b = path[k + 1];
+            if (a < 0 && b < 0 && wobj(a) == wobj(b)) len += warc[(-b - 1) >> 1];
+            else len += wr_norm(ground(a) - ground(b));
+        }
+        if (fabs(len - lastLength) < 0.0005) break;
+        lastLength = len;
+        if (kk == 0 && nW > 1 && result[0] == WRAP_NONE && result[1] == WRAP_INSIDE_RADIUS) {
+            order[0] = 1; order[1] = 0;
+            removeWrap(0);
+        }
+    }
+}
+
+// muscle_force for a muscle that has wrap-cylinder pairings (same contract)
+template <class SZ>
+__device__ __noinline__ MuscleOut muscle_force_wrapped(const DevTables& T, int m, const double* q, const double* u, const double* z,
+                                                       const double* ctl, const double* deriv, ScratchT<SZ>& S, bool apply,
+                                                       bool wantStiffness, double* lengthSpeed) {
+    const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
+    const double* md = T.dbl + T.o_mus_d + m * MOCOB200_MUS_DSTRIDE;
+    const int first = mi[0], count = mi[1], flags = mi[5];
+    constexpr int NP = SZ::NPPM, NPATH = SZ::NPPM + 2 * MOCOB200_MAXWRAP;
+    V3 pos[NP], vel[NP], dPdq[NP];
+    int body[NP], mcoord[NP], orig[NP];
+    int na = 0;
+    for (int k = 0; k < count && na < NP; ++k) {
+        const int* pi = T.idx + T.o_pp_i + (first + k) * MOCOB200_PP_ISTRIDE;
+        const double* pd = T.dbl + T.o_pp_d + (first + k) * MOCOB200_PP_DSTRIDE;
+        const int b = pi[0], kind = pi[1];
+        V3 loc = ld3(pd), vloc = mk(0, 0, 0), dp = mk(0, 0, 0);
+        int mc = -1;
+        if (kind == MOCOB200_PP_CONDITIONAL) {
+            const double val = q[pi[2]];
+            if (!(val >= pd[3] - 1e-5 && val <= pd[4] + 1e-5)) continue;
+        } else if (kind == MOCOB200_PP_MOVING) {
+            mc = pi[6];
+            const double qv = q[mc];
+            const double qc = fmin(fmax(qv, pd[3]), pd[4]);
+            loc = mk(simm_spline(T, pi[3], qc, 0), simm_spline(T, pi[4], qc, 0), simm_spline(T, pi[5], qc, 0));
+            dp = mk(simm_spline(T, pi[3], qv, 1), simm_spline(T, pi[4], qv, 1), simm_spline(T, pi[5], qv, 1));
+            vloc = u[mc] * dp;
+        }
+        V3 pG, vG;
+        if (b >= 0) {
+            const V3 r = rmul(S.R[b], loc);
+            pG = S.p[b] + r;
+            vG = S.v[b] + cross(S.w[b], r);
+            if (mc >= 0) { vG = vG + rmul(S.R[b], vloc); dp = rmul(S.R[b], dp); }
+        } else {
+            pG = loc;
+            vG = vloc;
+        }
+        pos[na] = pG; vel[na] = vG; body[na] = b; mcoord[na] = mc; dPdq[na] = dp; orig[na] = k;
+        ++na;
+    }
+    int path[NPATH], np = na;
+    for (int k = 0; k < na; ++k) path[k] = k;
+    V3 wr1[MOCOB200_MAXWRAP], wr2[MOCOB200_MAXWRAP];
+    double warc[MOCOB200_MAXWRAP];
+    apply_wrap_objects<SZ>(T, m, S, na, count, orig, pos, path, np, wr1, wr2, warc);
+    const int pw0 = T.idx[T.o_pw_i + 2 * m];
+    const int* pwBase = T.idx + T.o_pw_i + 2 * T.nmus + pw0 * MOCOB200_PW_ISTRIDE;
+    // the entries of the current path as (ground position, velocity, body); tangent points are stations of the wrap object's body
+    auto entry = [&](int e, V3& pG, V3& vG, int& b, int& wo) {
+        if (e >= 0) { pG = pos[e]; vG = vel[e]; b = body[e]; wo = -1; return; }
+        const int w = (-e - 1) >> 1;
+        wo = pwBase[w * MOCOB200_PW_ISTRIDE];
+        b = T.idx[T.o_wo_i + wo * MOCOB200_WO_ISTRIDE];
+        const V3 r = ((-e - 1) & 1) ? wr2[w] : wr1[w];
+        if (b >= 0) { const V3 rg = rmul(S.R[b], r); pG = S.p[b] + rg; vG = S.v[b] + cross(S.w[b], rg); }
+        else { pG = r; vG = mk(0, 0, 0); }
+    };
+    double length = 0, speed = 0;
+    {
+        V3 prevP = mk(0, 0, 0), prevV = mk(0, 0, 0);
+        int prevWo = -1;
+        for (int j = 0; j < np; ++j) {
+            V3 pG, vG;
+            int b, wo;
+            entry(path[j], pG, vG, b, wo);
+            if (j > 0) {
+                const V3 r = prevP - pG, dv = prevV - vG;
+                const double d = sqrt(dot(r, r));
+                length += (wo >= 0 && wo == prevWo) ? warc[(-path[j] - 1) >> 1] : d; // over the surface: the helix length
+                speed += (d < 2.220446049250313e-16) ? sqrt(dot(dv, dv)) : dot(dv, (1.0 / d) * r);
+            }
+            prevP = pG; prevV = vG; prevWo = wo;
+        }
+    }
+    if (lengthSpeed) { lengthSpeed[0] = length; lengthSpeed[1] = speed; }
+    double activation = (flags & MOCOB200_MUS_FLAG_IGNORE_ACTIVATION_DYNAMICS) ? ctl[mi[2]] : z[mi[3]];
+    const double ntf = (mi[4] >= 0) ? z[mi[4]] : NAN;
+    const double ntfd = (mi[6] >= 0) ? deriv[mi[6]] : NAN;
+    MuscleOut o = dgf_muscle(md, flags, length, speed, activation, ntf, ntfd, wantStiffness);
+    if (apply) {
+        const double tension = o.tendonForce;
+        for (int k = 0; k + 1 < np; ++k) {
+            V3 pa, va, pb, vb;
+            int ba, bb, woa, wob;
+            entry(path[k], pa, va, ba, woa);
+            entry(path[k + 1], pb, vb, bb, wob);
+            if (ba == bb) continue;
+            V3 dir = pb - pa;
+            const double nn = sqrt(dot(dir, dir));
+            dir = (nn < 1.9984014443252818e-14) ? (NAN * dir) : ((1.0 / nn) * dir);
+            const V3 f = tension * dir;
+            apply_point_force(S, ba, pa, f);
+            apply_point_force(S, bb, pb, -1.0 * f);
+            const int ea = path[k], eb = path[k + 1];
+            if (ea >= 0 && mcoord[ea] >= 0) S.tau[mcoord[ea]] += dot(dPdq[ea], f);
+            if (eb >= 0 && mcoord[eb] >= 0) S.tau[mcoord[eb]] -= dot(dPdq[eb], f);
+        }
+    }
+    return o;
+}
+
 template <class SZ>
 __device__ inline MuscleOut muscle_force(const DevTables& T, int m, const double* q, const double* u, const double* z,
                                         const double* ctl, const double* deriv, ScratchT<SZ>& S, bool apply, bool wantStiffness,
                                         double* lengthSpeed = nullptr) {
+    if constexpr (SZ::WRAP) {
+        if (T.npathwrap > 0 && T.idx[T.o_pw_i + 2 * m + 1] > 0) // the path runs over wrap cylinders
+            return muscle_force_wrapped<SZ>(T, m, q, u, z, ctl, deriv, S, apply, wantStiffness, lengthSpeed);
+    }
     const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
     const double* md = T.dbl + T.o_mus_d + m * MOCOB200_MUS_DSTRIDE;
     const int first = mi[0], count = mi[1], flags = mi[5];

@@ -88,3 +88,58 @@ def test_wrapping_changes_the_lengths_it_should(pkg, orc, rows):
     assert np.abs(d[:, nw == 0]).max() == 0.0
     assert d[:, nw > 0].max() > 5e-3 and d.min() > -1e-12  # wrapping never shortens a path
     assert (np.abs(d[:, nw > 0]).max(axis=0) > 1e-6).sum() >= 20  # most wrapped muscles do wrap somewhere in the trial
+
+
+def replay_problem(pkg, times):
+    """The replay problem on a mesh whose grid points sit at the given times (trapezoidal: grid = mesh)."""
+    mesh = (times - times[0]) / (times[-1] - times[0])
+    mesh[0], mesh[-1] = 0.0, 1.0
+    opts = "transcription_scheme=trapezoidal;mesh=" + " ".join("%.17g" % v for v in mesh)
+    return pkg.Problem.load(golden("rajagopal_replay.mb20"), opts)
+
+
+def iterate_at(p, times, q, u):
+    d = p.dims()
+    nq = q.shape[1]
+    x = np.zeros(d.n_var)
+    x[0], x[1] = times[0], times[-1]
+    st = np.zeros((d.n_grid, d.ns))
+    st[:, :nq] = q
+    st[:, nq:2 * nq] = u
+    x[2:2 + d.n_grid * d.ns] = st.ravel()
+    return x
+
+
+@pytest.mark.gpu
+def test_gpu_path_lengths_and_speeds_match_the_reference(pkg, orc, rows):
+    p = replay_problem(pkg, rows["time"].copy())
+    ev = pkg.Evaluator(p)
+    paths = ev.eval_paths(iterate_at(p, rows["time"], rows["q"], rows["u"]))
+    assert np.abs(paths[:, :, 0] - rows["lengths"]).max() < LENGTH_TOL
+    pv = replay_problem(pkg, rows["time_v"].copy())
+    evv = pkg.Evaluator(pv)
+    xv = iterate_at(pv, rows["time_v"], rows["q_v"], rows["u_v"])
+    pathsv = evv.eval_paths(xv)
+    assert np.abs(pathsv[:, :, 1] - rows["speeds"]).max() < SPEED_TOL
+    # and the kernel against the oracle (same procedure, separately written): 1e-10
+    o = orc.Oracle(pv)
+    out = np.zeros(2)
+    worst = 0.0
+    for r in range(0, len(rows["time_v"]), 6):
+        qq, uu = np.ascontiguousarray(rows["q_v"][r]), np.ascontiguousarray(rows["u_v"][r])
+        for m in range(pathsv.shape[1]):
+            orc.lib().orc_path(o._h, m, orc._d(qq), orc._d(uu), orc._d(out))
+            worst = max(worst, abs(out[0] - pathsv[r, m, 0]) / out[0], abs(out[1] - pathsv[r, m, 1]))
+    assert worst < 1e-10, worst
+
+
+@pytest.mark.gpu
+def test_gpu_refuses_dynamics_with_wrap_cylinders_loudly(pkg, rows):
+    """Until the warp kernels carry the wrap points, a model with wrap cylinders must not silently evaluate without them."""
+    p = replay_problem(pkg, rows["time_v"][:4].copy())
+    ev = pkg.Evaluator(p)
+    x = iterate_at(p, rows["time_v"][:4], rows["q_v"][:4], rows["u_v"][:4])
+    with pytest.raises(RuntimeError, match="wrap cylinders"):
+        ev.eval_points(x)
+    with pytest.raises(RuntimeError, match="wrap cylinders"):
+        ev.eval_jac_g(x)
