@@ -91,7 +91,7 @@ struct mocob200_handle {
     int kernelMode = 0; // 0 auto, 1 warp, 2 thread
     long warpMaxEvals = 30000;
     bool beyondThreadKernels = false;
-    bool wrapInWarpKernels = false; // set once the warp kernels evaluate wrap cylinders
+    bool wrapInWarpKernels = true; // the warp kernels carry the wrap tangent points (point_warp.cuh: wk_muscle_wraps)
     bool warpFor(long evals) const { return kernelMode == 1 || (kernelMode == 0 && evals <= warpMaxEvals); }
     std::vector<void*> owned;
     double* d_cfg = nullptr; // per-point blobs of the nominal evaluation (warp kernels)
@@ -167,6 +167,11 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     for (int b = 0; b < nb; ++b) {
         bodyPpStart[b] = (int)bodyPpList.size();
         for (int p = 0; p < npp; ++p) if (T.idx[T.o_pp_i + p * MOCOB200_PP_ISTRIDE] == b) bodyPpList.push_back(p);
+        // the two tangent points of every (muscle, wrap cylinder) pairing are stations of the cylinder's body: slots npp + 2 k, + 1
+        for (int k = 0; k < T.npathwrap; ++k) {
+            const int wo = T.idx[T.o_pw_i + 2 * T.nmus + k * MOCOB200_PW_ISTRIDE];
+            if (T.idx[T.o_wo_i + wo * MOCOB200_WO_ISTRIDE] == b) { bodyPpList.push_back(npp + 2 * k); bodyPpList.push_back(npp + 2 * k + 1); }
+        }
     }
     bodyPpStart[nb] = (int)bodyPpList.size();
     for (int p = 0; p < npp; ++p) {
@@ -296,7 +301,11 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     // position-dependent block (saved/reloaded as one range)
     A.blob_begin = o;
     A.o_R = take(9 * nb); A.o_p = take(3 * nb); A.o_oM = take(3 * nb); A.o_a = take(3 * nq); A.o_l = take(3 * nq);
-    A.o_cg = take(3 * nb); A.o_Io = take(6 * nb); A.o_ppos = take(3 * npp); A.o_prel = take(3 * npp);
+    const int nppx = npp + 2 * T.npathwrap; // path points + wrap tangent points
+    A.npp_ext = nppx;
+    A.o_cg = take(3 * nb); A.o_Io = take(6 * nb); A.o_ppos = take(3 * nppx); A.o_prel = take(3 * nppx);
+    A.o_warc = take(T.npathwrap);                       // helix length of each pairing
+    A.o_mpath = take(T.npathwrap > 0 ? 4 * T.nmus : 0); // current path of each muscle: 32 bytes = count + up to 31 entries
     A.o_dpl = take(3 * A.nmpp); A.o_mloc = take(3 * A.nmpp); A.o_ref = take(T.nppoly); A.o_mact = take(T.nmus); A.o_M = take(nq * nq);
     A.o_cjs = take(30 * T.ncustom);
     A.o_pk = take(L.prescribed ? 3 * nq : 0); // q, u, udot of prescribed kinematics
@@ -309,7 +318,7 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     // per-evaluation scratch
     A.o_F = take(3 * nb); A.o_N = take(3 * nb); A.o_cm = take(nb); A.o_ch = take(3 * nb); A.o_cJ = take(6 * nb);
     A.o_tau = take(nq); A.o_taub = take(nq); A.o_lin = take(3 * nq); A.o_ang = take(3 * nq);
-    A.o_pf = take(3 * npp); A.o_dp = take(3 * A.nmpp);
+    A.o_pf = take(3 * nppx); A.o_dp = take(3 * A.nmpp);
     // right-hand sides / solutions of the local columns: reuse the wrench + composite-inertia scratch, dead by then
     A.o_Rm = ((T.nmus + T.ncact) * nq <= A.o_tau - A.o_F) ? A.o_F : take((T.nmus + T.ncact) * nq);
     A.ws_doubles = o;
@@ -549,7 +558,7 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
         h->L = buildLayout(*T, *R, true);
     } catch (const std::exception& e) { return fail(MOCOB200_ERR_UNSUPPORTED, e.what()); }
     Layout& L = h->L;
-    if (L.n_in > MOCOB200_MAX_IN || L.n_out > MOCOB200_MAX_OUT || L.n_in + 1 > 256 || L.n_ein + 1 > 1024)
+    if (L.n_in > MOCOB200_MAX_IN || L.n_out > MOCOB200_MAX_OUT || L.n_in + 1 > 256 || L.n_ein + 1 > 512)
         return fail(MOCOB200_ERR_UNSUPPORTED, "point function exceeds the compiled input/output limits");
     for (int m = 0; m < T->nmus; ++m)
         if (T->idx[T->o_mus_i + m * MOCOB200_MUS_ISTRIDE + 1] > MOCOB200_MAXPPM)
@@ -594,7 +603,7 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     if (T->nb > SizeHuge::NB || T->nq > SizeHuge::NQ || T->ncontact > MOCOB200_MAXCONTACT)
         return fail(MOCOB200_ERR_UNSUPPORTED, "model exceeds the compiled limits (bodies/coordinates/contacts)");
     // beyond the thread-per-evaluation kernels' arrays (16 bodies / 16 coordinates / 160 inputs) only the warp kernels apply
-    h->beyondThreadKernels = T->nb > MOCOB200_MAXB || T->nq > MOCOB200_MAXQ || L.n_in > SizeLarge::NIN || T->npathwrap > 0;
+    h->beyondThreadKernels = T->nb > MOCOB200_MAXB || T->nq > MOCOB200_MAXQ || L.n_in > SizeLarge::NIN || L.n_out > SizeLarge::NOUT || T->npathwrap > 0;
     if (h->beyondThreadKernels)
         for (int g = 0; g < T->ngoal; ++g) {
             const int* gr = T->idx + T->o_goal_i + g * MOCOB200_GOAL_ISTRIDE;

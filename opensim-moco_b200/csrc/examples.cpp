@@ -505,6 +505,84 @@ std::unique_ptr<FlatProblem> rajagopalReplay(const std::string& dir, const std::
     return flatten(P, S);
 }
 
+// BASELINE config 4: exampleMocoInverse (Moco/Examples/C++/example3DWalking/exampleMocoInverse.cpp:34-77) - MocoInverse
+// (MocoInverse.cpp:44-140) on the armless full-body Rajagopal model, 80 muscles, kinematics of coordinates.sto prescribed.
+// Model operators, in the example's order: ModOpAddExternalLoads(grf_walk.xml), ModOpIgnoreTendonCompliance,
+// ModOpReplaceMusclesWithDeGrooteFregly2016 (copies the path POINTS only: the DeGrooteFregly2016 muscles of this problem have
+// no wrap surfaces, in the reference too - DeGrooteFregly2016Muscle.cpp:1009-1021), ModOpIgnorePassiveFiberForcesDGF,
+// ModOpScaleActiveFiberForceCurveWidthDGF(1.5), ModOpAddReserves(1.0).
+// Kinematics: the table is in degrees; OpenSim converts the columns of Rotational coordinates only (SimbodyEngine.cpp:905-945;
+// a CustomJoint coordinate is Rotational when a rotation axis follows it with slope +-1, CustomJoint.cpp:150-200), and
+// StatesTrajectory::createFromStatesStorage(assemble = true) then moves the coordinates that are free to satisfy constraints -
+// the patella's knee_angle_*_beta - onto their coupler functions; the value columns are splined (GCVSplineSet, degree 5).
+std::unique_ptr<FlatProblem> rajagopalInverse(const std::string& dir, const std::string& options) {
+    Problem P;
+    P.model = loadOsim(dir + "/subject_walk_armless.osim", false, false, /*musclesAsDGF=*/true);
+    appendExternalLoads(P.model, dir + "/grf_walk.xml");
+    for (MuscleSpec& mu : P.model.muscles) {
+        mu.ignoreTendonCompliance = true;
+        mu.ignorePassiveFiberForce = true;
+        mu.activeForceWidthScale = 1.5;
+    }
+    const StoTable tab = readSto(dir + "/coordinates.sto");
+    const double deg = tab.inDegrees ? kPi / 180.0 : 1.0;
+    std::map<std::string, std::vector<double>> values; // coordinate name -> column (radians / metres)
+    for (const JointSpec& J : P.model.joints)
+        for (const CoordSpec& c : J.coords) {
+            const std::string path = J.container + J.name + "/" + c.name;
+            const int ci = tab.col(path + "/value");
+            if (ci < 0) throw std::runtime_error("coordinates.sto lacks " + path + "/value");
+            bool rotational = J.kind == MOCOB200_JOINT_PIN;
+            if (J.kind == MOCOB200_JOINT_CUSTOM)
+                for (int a = 0; a < 3; ++a)
+                    rotational = rotational || (J.axes[a].coord == c.name && J.axes[a].fnKind == MOCOB200_FN_LINEAR && std::fabs(J.axes[a].c0) == 1.0);
+            std::vector<double> v = tab.cols[ci];
+            if (rotational) for (double& x : v) x *= deg;
+            values[c.name] = v;
+        }
+    for (const CouplerSpec& C : P.model.couplers) { // assembly: the dependent coordinate follows its coupler function
+        if (C.fn.fnKind == MOCOB200_FN_SIMMSPLINE) throw std::runtime_error("coupler '" + C.name + "': spline-coupled kinematics are unsupported here");
+        const std::vector<double>& qi = values.at(C.independent);
+        std::vector<double>& qd = values.at(C.dependent);
+        for (size_t r = 0; r < qd.size(); ++r)
+            qd[r] = C.scaleFactor * (C.fn.fnKind == MOCOB200_FN_LINEAR ? C.fn.c0 * qi[r] + C.fn.c1 : C.fn.c1);
+    }
+    for (const JointSpec& J : P.model.joints)
+        for (const CoordSpec& c : J.coords) {
+            const std::string path = J.container + J.name + "/" + c.name;
+            P.model.positionMotion.emplace_back(path, fitNaturalSpline(tab.time, values.at(c.name), 5));
+            bool has = false;
+            for (const CoordActSpec& a : P.model.coordActs) has = has || a.coord == c.name;
+            if (has) continue;
+            bool constrained = false; // ModelFactory.cpp:294: no reserve on a coordinate a constraint determines
+            for (const CouplerSpec& C : P.model.couplers) constrained = constrained || C.dependent == c.name;
+            if (constrained) continue;
+            CoordActSpec a;
+            std::string n = path;
+            for (char& ch : n) if (ch == '/') ch = '_';
+            a.path = "/forceset/reserve" + n;
+            a.coord = c.name;
+            a.optimalForce = 1.0;
+            P.model.actuatorOrder.emplace_back(0, (int)P.model.coordActs.size());
+            P.model.coordActs.push_back(a);
+        }
+    P.setTimeBounds(Bounds(0.81), Bounds(1.79));
+    P.addGoal(MOCOB200_GOAL_CONTROL, "excitation_effort", 1.0);
+    P.addGoal(MOCOB200_GOAL_INITIAL_ACTIVATION, "initial_activation");
+    SolverSettings S;
+    S.num_mesh_intervals = 49; // mesh_interval 0.02 s over [0.81, 1.79]
+    S.multibody_dynamics_mode = "implicit";
+    S.interpolate_control_midpoints = false;
+    S.minimize_implicit_auxiliary_derivatives = true;
+    S.implicit_auxiliary_derivatives_weight = 0.01;
+    S.optim_finite_difference_scheme = "forward";
+    // (MocoInverse also sets optim_sparsity_detection = "random": a property of the evaluator handle here, mocob200_set_sparsity_detection)
+    S.optim_convergence_tolerance = 1e-3;
+    S.optim_constraint_tolerance = 1e-3;
+    S.applyOptions(options);
+    return flatten(P, S);
+}
+
 // MocoInverse (Moco/Moco/MocoInverse.cpp:44-140) on the example2DWalking model: the kinematics of referenceCoordinates.sto are
 // prescribed (PositionMotion::createFromTable, Components/PositionMotion.cpp:121-150: GCVSplines of the value columns), reserve
 // actuators of optimal force 1 on every coordinate without an actuator (ModelFactory.cpp:265-320, ModOpAddReserves(1.0)),
@@ -571,6 +649,7 @@ std::unique_ptr<FlatProblem> buildExample(const std::string& name, const std::st
     if (name == "gait2d_prediction") return gaitPrediction(dataDir, options);
     if (name == "gait10dof_replay") return gait10dofReplay(dataDir, options);
     if (name == "rajagopal_replay") return rajagopalReplay(dataDir, options);
+    if (name == "rajagopal_inverse") return rajagopalInverse(dataDir, options);
     if (name == "gait2d_inverse") return gaitInverse(dataDir, options);
     if (name == "gait2d_inverse_free") return gaitInverse(dataDir, options, false);
     if (name == "planar_point_mass_coupler") return planarPointMassCoupler(options);

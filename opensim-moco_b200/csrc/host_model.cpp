@@ -305,7 +305,9 @@ StoTable readSto(const std::string& path) {
     StoTable t;
     while (std::getline(f, line)) {
         if (header) {
-            if (trim(line).rfind("endheader", 0) == 0) header = false;
+            const std::string hl = trim(line);
+            if (hl.rfind("endheader", 0) == 0) header = false;
+            else if (hl.rfind("inDegrees", 0) == 0) t.inDegrees = hl.find("yes") != std::string::npos;
             continue;
         }
         std::string tl = trim(line);

@@ -167,7 +167,10 @@ struct ModelSpec {
 // opensim-models pipelines. musclesAsPathActuators: every muscle of any class is read as a PathActuator with
 // optimal_force 1 on its GeometryPath (its tension becomes the control) - used to replay recorded actuator forces.
 // lockedAsFree: read locked coordinates as ordinary ones (enough for replaying recorded states, where they stay constant)
-ModelSpec loadOsim(const std::string& path, bool musclesAsPathActuators = false, bool lockedAsFree = false);
+// musclesAsDGF: Millard2012EquilibriumMuscle / Thelen2003Muscle are replaced by DeGrooteFregly2016Muscles the way
+// ModOpReplaceMusclesWithDeGrooteFregly2016 does (DeGrooteFregly2016Muscle.cpp:933-1050) - which copies the path POINTS only:
+// the replaced muscles lose their PathWraps, in the reference too
+ModelSpec loadOsim(const std::string& path, bool musclesAsPathActuators = false, bool lockedAsFree = false, bool musclesAsDGF = false);
 // ForceSet file (e.g. reserve actuators) appended to a model: CoordinateActuators only; other classes are returned by name
 std::vector<std::string> appendForceSetFile(ModelSpec& M, const std::string& path);
 // ExternalLoads .xml (+ its data file, resolved relative to the .xml) -> M.externalForces (ExternalLoads.cpp, ExternalForce.cpp:200-317)
@@ -313,6 +316,7 @@ struct StoTable {
     std::vector<std::string> labels; // without "time"
     std::vector<double> time;
     std::vector<std::vector<double>> cols; // [label][row]
+    bool inDegrees = false;                // header "inDegrees=yes": rotational coordinates are in degrees
     int col(const std::string& l) const;
 };
 StoTable readSto(const std::string& path);

@@ -156,7 +156,7 @@ __device__ inline bool endpoint_reads(const DevTables& T, const DevLayout& L, in
 
 // one block per goal; thread a < n_ein = FD direction, thread n_ein = nominal evaluation.
 // which: 0 = every goal, 1 = only goals without an integrand (functions of x alone), 2 = only goals with one.
-__global__ void k_endpoint(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ x, const double* __restrict__ I,
+__global__ void __launch_bounds__(512) k_endpoint(DevTables T, DevLayout L, FdSettings fd, const double* __restrict__ x, const double* __restrict__ I,
                            double* __restrict__ G, double* __restrict__ E, int withFd, int which) {
     extern __shared__ double sh[]; // [n_ein] nominal inputs, then [nout] nominal outputs
     const int g = blockIdx.x;

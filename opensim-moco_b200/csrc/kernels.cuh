@@ -18,8 +18,8 @@ inline const char* devEnv(const char* name) {
 }
 
 #define MOCOB200_MAX_IN 200
-#define MOCOB200_MAX_OUT 72
-#define MOCOB200_MAX_EOUT 64 /* outputs of one endpoint goal */
+#define MOCOB200_MAX_OUT 128
+#define MOCOB200_MAX_EOUT 128 /* outputs of one endpoint goal */
 
 struct FdSettings {
     int scheme;    // MOCOB200_FD_*

@@ -97,6 +97,7 @@ __device__ __forceinline__ int reuse_level(const DevLayout& L, int dir) {
 }
 
 // nominal evaluation of every grid point in [p0, p0+np): Y[j][:] (+ the blob of each point when cfg != nullptr)
+template <bool WRAP>
 __global__ void k_wpoints_nominal(DevTables Tg, WarpAux Ag, DevLayout L, const double* __restrict__ x, double* __restrict__ Y,
                                   double* __restrict__ cfg, int p0, int np) {
     extern __shared__ double smem[];
@@ -115,7 +116,7 @@ __global__ void k_wpoints_nominal(DevTables Tg, WarpAux Ag, DevLayout L, const d
 #endif
     poison_scratch(A, ws, lane);
     warp_gather_inputs(L, x, j, ws + A.o_in, lane);
-    warp_eval_point_t<0>(T, A, ws, 0xffffffffu, false, false);
+    warp_eval_point_t<0, WRAP>(T, A, ws, 0xffffffffu, false, false);
     for (int o = lane; o < L.n_out; o += 32) Y[(size_t)j * L.n_out + o] = ws[A.o_out + o];
     if (cfg) blob_save(A, ws, cfg, j, lane);
 }
@@ -131,7 +132,7 @@ __global__ void k_wpoints_nominal(DevTables Tg, WarpAux Ag, DevLayout L, const d
 // KIND 1-3 run side by side once KIND 0 is done and write finished difference quotients. The coordinate evaluations of
 // KIND 0 run beside the nominal one, so they leave their RAW outputs in J[j][o][dir]; the first KIND 2 item of each grid
 // point (or k_fd1_finalize when there is none) turns those columns into quotients.
-template <int KIND>
+template <int KIND, bool WRAP = false>
 __global__ void k_wpoints_fd1(DevTables Tg, WarpAux Ag, DevLayout L, FdSettings fd, const double* __restrict__ x, double* __restrict__ Y,
                               double* __restrict__ J, double* __restrict__ cfg, int p0, int np) {
     extern __shared__ double smem[];
@@ -167,7 +168,7 @@ __global__ void k_wpoints_fd1(DevTables Tg, WarpAux Ag, DevLayout L, FdSettings 
         mask = 0xfffffffeu;
         for (int o = lane; o < L.n_dyn_out; o += 32) ws[A.o_out + o] = Y[(size_t)j * L.n_out + o];
     }
-    warp_eval_point_t<KIND>(T, A, ws, mask, KIND == 2 && dir == 0, false);
+    warp_eval_point_t<KIND, WRAP>(T, A, ws, mask, KIND == 2 && dir == 0, false);
     const double inv = (fd.scheme == MOCOB200_FD_FORWARD) ? 1.0 / fd.h : -1.0 / fd.h;
     if (dir < 0) {
         for (int o = lane; o < L.n_out; o += 32) Y[(size_t)j * L.n_out + o] = ws[A.o_out + o];
@@ -202,6 +203,7 @@ __global__ void k_fd1_finalize(DevLayout L, FdSettings fd, const int* __restrict
 
 // central differences with CasADi's step refinement; item = (point, dir, callback group). Needs Y and the blobs of
 // the nominal evaluation.
+template <bool WRAP>
 __global__ void k_wpoints_central(DevTables Tg, WarpAux Ag, DevLayout L, FdSettings fd, const double* __restrict__ x,
                                   const double* __restrict__ Y, double* __restrict__ J, const double* __restrict__ cfg, int p0, int np) {
     extern __shared__ double smem[];
@@ -236,7 +238,7 @@ __global__ void k_wpoints_central(DevTables Tg, WarpAux Ag, DevLayout L, FdSetti
         for (int side = 0; side < 2; ++side) { // one copy of the evaluation code serves both sides
             if (lane == 0) ws[A.o_in + dir] = side ? x0 + h : x0 - h;
             __syncwarp();
-            warp_eval_point(T, A, ws, mask, reuse, dir == 0);
+            warp_eval_point<WRAP>(T, A, ws, mask, reuse, dir == 0);
             if (side == 0) for (int o = lo + lane; o < hi; o += 32) yb[o] = yf[o];
         }
         double u = 0;
@@ -308,13 +310,16 @@ bool warp_kernels_configure(WarpAux& A, std::string& err) {
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 8 && bytes <= g_maxBytes[dev]) return true;
     cudaError_t e;
-    if ((e = cudaFuncSetAttribute(k_wpoints_nominal, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
-        (e = cudaFuncSetAttribute(k_wpoints_fd1<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
+    if ((e = cudaFuncSetAttribute(k_wpoints_nominal<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_wpoints_nominal<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_wpoints_fd1<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_wpoints_fd1<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(k_wpoints_central<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
         (e = cudaFuncSetAttribute(k_wpoints_fd1<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
         (e = cudaFuncSetAttribute(k_wpoints_fd1<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
         (e = cudaFuncSetAttribute(k_wpoints_fd1<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
         (e = cudaFuncSetAttribute(k_wlocal_central, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess ||
-        (e = cudaFuncSetAttribute(k_wpoints_central, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess) {
+        (e = cudaFuncSetAttribute(k_wpoints_central<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes)) != cudaSuccess) {
         err = std::string("cudaFuncSetAttribute: ") + cudaGetErrorString(e);
         return false;
     }
@@ -332,7 +337,8 @@ void launch_wpoints_nominal(const DevTables& T, const WarpAux& A, const DevLayou
         else { float a = 0; if (cudaEventElapsedTime(&a, ne[0], ne[1]) == cudaSuccess) fprintf(stderr, "[mocob200 timing] nominal %.1f us (%d points)\n", 1e3 * a, np); }
         cudaEventRecord(ne[0], s);
     }
-    k_wpoints_nominal<<<(np + A.wpb - 1) / A.wpb, A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, d_x, d_Y, d_cfg, p0, np);
+    if (T.npathwrap > 0) k_wpoints_nominal<true><<<(np + A.wpb - 1) / A.wpb, A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, d_x, d_Y, d_cfg, p0, np);
+    else k_wpoints_nominal<false><<<(np + A.wpb - 1) / A.wpb, A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, d_x, d_Y, d_cfg, p0, np);
     if (timing) cudaEventRecord(ne[1], s);
 }
 // returns the number of kernels launched
@@ -353,7 +359,8 @@ int launch_wpoints_fd(const DevTables& T, const WarpAux& A, const DevLayout& L, 
             }
             cudaEventRecord(te[0], s);
         }
-        k_wpoints_fd1<0><<<(unsigned)((items0 + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
+        if (T.npathwrap > 0) k_wpoints_fd1<0, true><<<(unsigned)((items0 + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
+        else k_wpoints_fd1<0, false><<<(unsigned)((items0 + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
         if (after_nominal) cudaEventRecord(after_nominal, s);
         if (timing) cudaEventRecord(te[1], s);
         int launched = 1;
@@ -409,7 +416,8 @@ int launch_wpoints_fd(const DevTables& T, const WarpAux& A, const DevLayout& L, 
     }
     const long items = (long)np * A.n_cd * (1 + L.n_integrand);
     if (items > 0)
-        k_wpoints_central<<<(unsigned)((items + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
+        if (T.npathwrap > 0) k_wpoints_central<true><<<(unsigned)((items + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
+        else k_wpoints_central<false><<<(unsigned)((items + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
     if (fork) cudaStreamWaitEvent(s, side->join[0], 0);
     return launched;
 }

@@ -46,6 +46,7 @@ struct Ctx {
     bool v3 = false; // document Version < 40000: frames are bodies referenced by bare name
     bool asPathActuators = false;
     bool lockedAsFree = false;
+    bool musclesAsDGF = false;
     // resolve "/bodyset/x", "/ground", "ground", and (Version 30000) a bare body name
     bool baseFrame(const std::string& path, int& body) const {
         if (path == "/ground" || path == "ground") { body = -1; return true; }
@@ -220,10 +221,10 @@ void readCoordinates(const XmlNode* holder, JointSpec& J) {
     }
 }
 
-void readPath(const Ctx& cx, const XmlNode& n, MuscleSpec& mu) {
+void readPath(const Ctx& cx, const XmlNode& n, MuscleSpec& mu, bool dropWraps = false) {
     const XmlNode* gp = n.child("GeometryPath");
     if (!gp) throw std::runtime_error("'" + mu.path + "' has no GeometryPath");
-    if (const XmlNode* ws = gp->child("PathWrapSet"))
+    if (const XmlNode* ws = dropWraps ? nullptr : gp->child("PathWrapSet"))
         if (const XmlNode* wo = ws->child("objects"))
             for (auto& w : wo->children) {
                 if (w->tag != "PathWrap") continue;
@@ -305,6 +306,47 @@ void readMuscle(const Ctx& cx, const XmlNode& n, const std::string& prefix) {
     cx.M.muscles.push_back(std::move(mu));
 }
 
+// DeGrooteFregly2016Muscle::replaceMuscles (DeGrooteFregly2016Muscle.cpp:933-1050): what a Millard2012EquilibriumMuscle or a
+// Thelen2003Muscle becomes under ModOpReplaceMusclesWithDeGrooteFregly2016. Properties absent from the file take the source
+// class's defaults (Millard2012EquilibriumMuscle.cpp:58-75, Thelen2003Muscle.cpp:62-80). Only the path points are copied.
+void readMuscleAsDGF(const Ctx& cx, const XmlNode& n, const std::string& prefix) {
+    const bool millard = n.tag == "Millard2012EquilibriumMuscle";
+    MuscleSpec mu;
+    mu.path = prefix + n.name();
+    mu.minControl = dblOf(n, "min_control", 0.0); // Muscle::constructProperties
+    mu.maxControl = dblOf(n, "max_control", 1.0);
+    mu.maxIsometricForce = dblOf(n, "max_isometric_force", 1000.0);
+    mu.optimalFiberLength = dblOf(n, "optimal_fiber_length", 0.1);
+    mu.tendonSlackLength = dblOf(n, "tendon_slack_length", 0.2);
+    mu.pennationAngleAtOptimal = dblOf(n, "pennation_angle_at_optimal", 0.0);
+    mu.maxContractionVelocity = dblOf(n, "max_contraction_velocity", 10.0);
+    mu.ignoreTendonCompliance = boolOf(n.childText("ignore_tendon_compliance"), false);
+    mu.ignoreActivationDynamics = boolOf(n.childText("ignore_activation_dynamics"), false);
+    mu.defaultActivation = dblOf(n, "default_activation", 0.05);
+    mu.activationTimeConstant = dblOf(n, "activation_time_constant", millard ? 0.010 : 0.015);
+    mu.deactivationTimeConstant = dblOf(n, "deactivation_time_constant", millard ? 0.040 : 0.050);
+    if (millard) {
+        mu.fiberDamping = dblOf(n, "fiber_damping", 0.1);
+        auto curveStrain = [&](const char* curve, double dflt) {
+            if (const XmlNode* c = n.child(curve)) {
+                const XmlNode* inner = c->children.empty() ? c : c->children[0].get();
+                if (inner->has("strain_at_one_norm_force")) return dblOf(*inner, "strain_at_one_norm_force", dflt);
+                if (c->has("strain_at_one_norm_force")) return dblOf(*c, "strain_at_one_norm_force", dflt);
+            }
+            return dflt;
+        };
+        mu.passiveFiberStrainAtOneNormForce = curveStrain("FiberForceLengthCurve", 0.7);
+        mu.tendonStrainAtOneNormForce = curveStrain("TendonForceLengthCurve", 0.049);
+    } else {
+        mu.fiberDamping = 0.0;
+        mu.passiveFiberStrainAtOneNormForce = dblOf(n, "FmaxMuscleStrain", 0.6);
+        mu.tendonStrainAtOneNormForce = dblOf(n, "FmaxTendonStrain", 0.033);
+    }
+    readPath(cx, n, mu, /*dropWraps=*/true);
+    cx.M.actuatorOrder.emplace_back(1, (int)cx.M.muscles.size());
+    cx.M.muscles.push_back(std::move(mu));
+}
+
 // PathActuator (Actuators/PathActuator.cpp:156-197), or — with musclesAsPathActuators — any force that carries a GeometryPath
 void readPathActuator(const Ctx& cx, const XmlNode& n, const std::string& prefix, bool isPathActuator) {
     MuscleSpec mu;
@@ -335,6 +377,8 @@ void readForceLike(const Ctx& cx, const XmlNode& n, const std::string& prefix, c
     if (boolOf(n.childText("isDisabled"), false) || !boolOf(n.childText("appliesForce"), true)) return;
     if (cx.asPathActuators && n.child("GeometryPath")) {
         readPathActuator(cx, n, prefix, n.tag == "PathActuator");
+    } else if (cx.musclesAsDGF && (n.tag == "Millard2012EquilibriumMuscle" || n.tag == "Thelen2003Muscle")) {
+        readMuscleAsDGF(cx, n, prefix);
     } else if (n.tag == "DeGrooteFregly2016Muscle") {
         readMuscle(cx, n, prefix);
     } else if (n.tag == "PathActuator") {
@@ -377,7 +421,7 @@ void readForceLike(const Ctx& cx, const XmlNode& n, const std::string& prefix, c
 
 } // namespace
 
-ModelSpec loadOsim(const std::string& path, bool musclesAsPathActuators, bool lockedAsFree) {
+ModelSpec loadOsim(const std::string& path, bool musclesAsPathActuators, bool lockedAsFree, bool musclesAsDGF) {
     struct Restore { bool old; ~Restore() { g_lockedAsFree = old; } } restore{g_lockedAsFree};
     g_lockedAsFree = lockedAsFree;
     auto doc = parseXmlFile(path);
@@ -393,6 +437,7 @@ ModelSpec loadOsim(const std::string& path, bool musclesAsPathActuators, bool lo
     Ctx cx{M};
     cx.v3 = version < 40000;
     cx.asPathActuators = musclesAsPathActuators;
+    cx.musclesAsDGF = musclesAsDGF;
 
     const XmlNode* bs = model->child("BodySet");
     const XmlNode* bobjs = bs ? bs->child("objects") : nullptr;

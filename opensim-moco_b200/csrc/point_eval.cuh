@@ -592,8 +592,10 @@ __device__ inline V3 contact_force(const DevTables& T, int ci, ScratchT<SZ>& S, 
 // current path in `path` (entries >= 0: active point; -(2 w + 1), -(2 w + 2): the two tangent points of the muscle's pairing w,
 // stations of the wrap object's body held in wr1 / wr2 in that body's frame, with the helix length in warc).
 #define MOCOB200_MAXWRAP 4 /* pairings per muscle */
-template <class SZ>
-__device__ __noinline__ void apply_wrap_objects(const DevTables& T, int m, const ScratchT<SZ>& S, int nA, int nSet, const int* orig,
+// FR: where the body frames live (R(b): row-major rotation, p(b): origin) - the thread kernels' scratch or the warp kernels'
+// shared-memory scratch
+template <class FR>
+__device__ __noinline__ void apply_wrap_objects(const DevTables& T, int m, const FR& S, int nA, int nSet, const int* orig,
                                                 const V3* pos, int* path, int& np, V3* wr1, V3* wr2, double* warc) {
     const int pw0 = T.idx[T.o_pw_i + 2 * m], nW = min(T.idx[T.o_pw_i + 2 * m + 1], MOCOB200_MAXWRAP);
     const int* pwBase = T.idx + T.o_pw_i + 2 * T.nmus + pw0 * MOCOB200_PW_ISTRIDE;
@@ -603,7 +605,7 @@ __device__ __noinline__ void apply_wrap_objects(const DevTables& T, int m, const
         const int w = (-e - 1) >> 1;
         const int b = T.idx[T.o_wo_i + wobj(e) * MOCOB200_WO_ISTRIDE];
         const V3 r = ((-e - 1) & 1) ? wr2[w] : wr1[w];
-        return b >= 0 ? S.p[b] + rmul(S.R[b], r) : r;
+        return b >= 0 ? S.p(b) + rmul(S.R(b), r) : r;
     };
     auto removeWrap = [&](int w) {
         for (int j = 0; j < np; ++j)
@@ -631,7 +633,7 @@ __device__ __noinline__ void apply_wrap_objects(const DevTables& T, int m, const
             if (start < 0 || end < 0) return;
             const int wb = wi[0];
             auto toWrapFrame = [&](V3 g) { // ground -> wrap object's body -> wrap frame
-                const V3 b = wb >= 0 ? rtmul(S.R[wb], g - S.p[wb]) : g;
+                const V3 b = wb >= 0 ? rtmul(S.R(wb), g - S.p(wb)) : g;
                 return rtmul(wd, b - ld3(wd + 9));
             };
             bool haveBest = false;
@@ -722,7 +724,12 @@ __device__ __noinline__ MuscleOut muscle_force_wrapped(const DevTables& T, int m
     for (int k = 0; k < na; ++k) path[k] = k;
     V3 wr1[MOCOB200_MAXWRAP], wr2[MOCOB200_MAXWRAP];
     double warc[MOCOB200_MAXWRAP];
-    apply_wrap_objects<SZ>(T, m, S, na, count, orig, pos, path, np, wr1, wr2, warc);
+    struct Frames {
+        const ScratchT<SZ>& S;
+        __device__ const double* R(int b) const { return S.R[b]; }
+        __device__ V3 p(int b) const { return S.p[b]; }
+    };
+    apply_wrap_objects(T, m, Frames{S}, na, count, orig, pos, path, np, wr1, wr2, warc);
     const int pw0 = T.idx[T.o_pw_i + 2 * m];
     const int* pwBase = T.idx + T.o_pw_i + 2 * T.nmus + pw0 * MOCOB200_PW_ISTRIDE;
     // the entries of the current path as (ground position, velocity, body); tangent points are stations of the wrap object's body

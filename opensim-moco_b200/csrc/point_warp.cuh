@@ -55,6 +55,7 @@ struct WarpAux {
     int o_cjs; // per custom joint (position-dependent): 6 axis vectors in ground (18), df[6], d2f[6]
     int lockstep;
     int o_pk; // prescribed kinematics: q, u, udot at the point's time
+    int npp_ext, o_warc, o_mpath; // wrap cylinders: path points + tangent-point slots; helix lengths; per-muscle current path
     int poison; // development switch (MOCOB200_POISON_SCRATCH=1): every evaluation starts from NaN-filled scratch
     int ws_doubles;
     int wpb; // warps (= evaluations in flight) per block, chosen at create from the scratch size
@@ -298,9 +299,78 @@ __device__ inline void wk_moving_point_spline(const WarpCtx& C, int t, const dou
     else C.at(A.o_dpl)[3 * j + c - 3] = simm_spline(T, pi[c], qv, 1);
 }
 
+// ---- wrap cylinders. The two tangent points of pairing k (global number) are stations of the cylinder's body in
+// slots npp + 2 k and npp + 2 k + 1 of ppos / prel / pf; the muscle's current path (GeometryPath "current_path") is kept as
+// bytes in o_mpath: [count, entries...], entry >= 0 = the muscle's path point number, entry < 0 = -(2 w + 1 + which) for
+// pairing w of the muscle.
+__device__ __forceinline__ int wk_muscle_wrap_count(const WarpCtx& C, int m) {
+    return C.T.npathwrap > 0 ? C.T.idx[C.T.o_pw_i + 2 * m + 1] : 0;
+}
+// global slot (into ppos / prel / pf) and body of a path entry of muscle m
+__device__ __forceinline__ int wk_path_slot(const WarpCtx& C, int m, int entry, int& body, int& wrapObj) {
+    const DevTables& T = C.T;
+    if (entry >= 0) {
+        const int pp = T.idx[T.o_mus_i + m * MOCOB200_MUS_ISTRIDE] + entry;
+        body = T.idx[T.o_pp_i + pp * MOCOB200_PP_ISTRIDE];
+        wrapObj = -1;
+        return pp;
+    }
+    const int w = (-entry - 1) >> 1, which = (-entry - 1) & 1;
+    const int k = T.idx[T.o_pw_i + 2 * m] + w; // global pairing
+    wrapObj = T.idx[T.o_pw_i + 2 * T.nmus + k * MOCOB200_PW_ISTRIDE];
+    body = T.idx[T.o_wo_i + wrapObj * MOCOB200_WO_ISTRIDE];
+    return T.npp + 2 * k + which;
+}
+__device__ inline void wk_muscle_wraps(const WarpCtx& C, int m, unsigned active) {
+    const DevTables& T = C.T;
+    const WarpAux& A = C.A;
+    signed char* mp = reinterpret_cast<signed char*>(C.at(A.o_mpath) + 4 * m);
+    const int nW = T.idx[T.o_pw_i + 2 * m + 1];
+    if (nW == 0) { mp[0] = 0; return; }
+    for (int w = 0; w < 2 * nW; ++w) { // tangent points not on the path keep a finite position: the per-body gather multiplies it by a zero force
+        const int slot = T.npp + 2 * T.idx[T.o_pw_i + 2 * m] + w;
+        stv(C.at(A.o_prel) + 3 * slot, mk(0, 0, 0));
+        stv(C.at(A.o_ppos) + 3 * slot, mk(0, 0, 0));
+    }
+    const int* mi = T.idx + T.o_mus_i + m * MOCOB200_MUS_ISTRIDE;
+    const int first = mi[0], count = mi[1];
+    V3 pos[MOCOB200_MAXPPM];
+    int orig[MOCOB200_MAXPPM], na = 0;
+    for (int k = 0; k < count && na < MOCOB200_MAXPPM; ++k)
+        if ((active >> k) & 1u) { pos[na] = ldv(C.at(A.o_ppos) + 3 * (first + k)); orig[na] = k; ++na; }
+    int path[MOCOB200_MAXPPM + 2 * MOCOB200_MAXWRAP], np = na;
+    for (int k = 0; k < na; ++k) path[k] = k;
+    V3 wr1[MOCOB200_MAXWRAP], wr2[MOCOB200_MAXWRAP];
+    double warc[MOCOB200_MAXWRAP];
+    struct Frames {
+        const WarpCtx& C;
+        __device__ const double* R(int b) const { return C.at(C.A.o_R) + 9 * b; }
+        __device__ V3 p(int b) const { return ldv(C.at(C.A.o_p) + 3 * b); }
+    };
+    apply_wrap_objects(T, m, Frames{C}, na, count, orig, pos, path, np, wr1, wr2, warc);
+    // store: path entries (active-list indices -> path point numbers), tangent points as stations of their bodies, helix lengths
+    const int pw0 = T.idx[T.o_pw_i + 2 * m];
+    mp[0] = (signed char)np;
+    for (int j = 0; j < np && j < 31; ++j) mp[1 + j] = (signed char)(path[j] >= 0 ? orig[path[j]] : path[j]);
+    for (int j = 0; j < np; ++j) {
+        if (path[j] >= 0) continue;
+        const int w = (-path[j] - 1) >> 1, which = (-path[j] - 1) & 1;
+        int body, wo;
+        const int slot = wk_path_slot(C, m, path[j], body, wo);
+        V3 r = which ? wr2[w] : wr1[w], pG = r;
+        if (body >= 0) { r = rmul(C.at(A.o_R) + 9 * body, r); pG = ldv(C.at(A.o_p) + 3 * body) + r; }
+        stv(C.at(A.o_prel) + 3 * slot, r);
+        stv(C.at(A.o_ppos) + 3 * slot, pG);
+        if (which) C.at(A.o_warc)[pw0 + w] = warc[w];
+    }
+}
+
 // ---- phase 2b: path geometry of one muscle (one lane): active points, their offsets from the body origin (prel),
 // ground positions (ppos) and, for moving points, dP/dq in the body frame (dpl). Position-dependent only.
 // (GeometryPath.cpp:817-846; ConditionalPathPoint.cpp:160-169; MovingPathPoint.cpp:216-315)
+// WRAP: this instantiation evaluates wrap cylinders (kept out of the kernels of models without them: the wrap procedure nearly
+// doubles their register count and costs config 3 10 %)
+template <bool WRAP>
 __device__ inline void wk_muscle_geometry(const WarpCtx& C, int m, const double* q) {
     const DevTables& T = C.T;
     const WarpAux& A = C.A;
@@ -331,6 +401,7 @@ __device__ inline void wk_muscle_geometry(const WarpCtx& C, int m, const double*
         if (on) active |= 1u << k;
     }
     C.at(A.o_mact)[m] = (double)active;
+    if constexpr (WRAP) { if (T.npathwrap > 0) wk_muscle_wraps(C, m, active); }
 }
 // ---- phase 2c: one muscle (one lane) from its stored geometry: point velocities, length, lengthening speed, muscle
 // model, per-point forces (GeometryPath.cpp:848-864, 1117-1145, 306-432; Point.cpp:130-140)
@@ -343,15 +414,22 @@ __device__ inline MuscleOut wk_muscle_dynamics(const WarpCtx& C, int m, const do
     const int first = mi[0], count = mi[1], flags = mi[5];
     const unsigned active = (unsigned)C.at(A.o_mact)[m];
     const double* ppos = C.at(A.o_ppos);
+    const bool wrapped = wk_muscle_wrap_count(C, m) > 0;
+    const signed char* mp = wrapped ? reinterpret_cast<const signed char*>(C.at(A.o_mpath) + 4 * m) : nullptr;
+    const int nent = wrapped ? mp[0] : count; // wrapped: walk the stored current path; otherwise the path points in order
     double length = 0, speed = 0;
     V3 prevP = mk(0, 0, 0), prevV = mk(0, 0, 0);
-    int na = 0;
-    for (int k = 0; k < count; ++k) {
-        if (!((active >> k) & 1u)) continue;
-        const int pp = first + k;
-        const int* pi = T.idx + T.o_pp_i + pp * MOCOB200_PP_ISTRIDE;
-        const int b = pi[0];
-        const int mc = (pi[1] == MOCOB200_PP_MOVING) ? pi[6] : -1;
+    int na = 0, prevWo = -1;
+    for (int k = 0; k < nent; ++k) {
+        int pp, b, wo = -1;
+        if (wrapped) pp = wk_path_slot(C, m, mp[1 + k], b, wo);
+        else {
+            if (!((active >> k) & 1u)) continue;
+            pp = first + k;
+            b = T.idx[T.o_pp_i + pp * MOCOB200_PP_ISTRIDE];
+        }
+        const int* pi = T.idx + T.o_pp_i + (pp < T.npp ? pp : 0) * MOCOB200_PP_ISTRIDE;
+        const int mc = (pp < T.npp && pi[1] == MOCOB200_PP_MOVING) ? pi[6] : -1;
         const V3 pG = ldv(ppos + 3 * pp);
         V3 vG = mk(0, 0, 0);
         if (b >= 0) vG = ldv(C.at(A.o_v) + 3 * b) + cross(ldv(C.at(A.o_w) + 3 * b), ldv(C.at(A.o_prel) + 3 * pp));
@@ -366,11 +444,13 @@ __device__ inline MuscleOut wk_muscle_dynamics(const WarpCtx& C, int m, const do
         if (na > 0) {
             const V3 r = prevP - pG, dv = prevV - vG;
             const double d = sqrt(dot(r, r));
-            length += d;
+            // between the two tangent points of one cylinder the path runs over the surface: the helix length
+            length += (wo >= 0 && wo == prevWo) ? C.at(A.o_warc)[(pp - T.npp) >> 1] : d;
             speed += (d < 2.220446049250313e-16) ? sqrt(dot(dv, dv)) : dot(dv, (1.0 / d) * r);
         }
         prevP = pG;
         prevV = vG;
+        prevWo = wo;
         ++na;
     }
     C.at(A.o_mlen)[m] = length;
@@ -383,12 +463,16 @@ __device__ inline MuscleOut wk_muscle_dynamics(const WarpCtx& C, int m, const do
         // net force of the path on the body at every active point: +T dir at the start of a segment, -T dir at its
         // end; segments between points of the same body carry no force
         double* pf = C.at(A.o_pf);
-        int prev = -1;
-        for (int k = 0; k < count; ++k) {
-            if (!((active >> k) & 1u)) continue;
+        int prev = -1, pa = -1, ba = -1;
+        for (int k = 0; k < nent; ++k) {
+            int pb, bb, wo;
+            if (wrapped) pb = wk_path_slot(C, m, mp[1 + k], bb, wo);
+            else {
+                if (!((active >> k) & 1u)) continue;
+                pb = first + k;
+                bb = T.idx[T.o_pp_i + pb * MOCOB200_PP_ISTRIDE];
+            }
             if (prev >= 0) {
-                const int pa = first + prev, pb = first + k;
-                const int ba = T.idx[T.o_pp_i + pa * MOCOB200_PP_ISTRIDE], bb = T.idx[T.o_pp_i + pb * MOCOB200_PP_ISTRIDE];
                 if (ba != bb) {
                     V3 dir = ldv(ppos + 3 * pb) - ldv(ppos + 3 * pa);
                     const double nn = sqrt(dot(dir, dir));
@@ -398,7 +482,7 @@ __device__ inline MuscleOut wk_muscle_dynamics(const WarpCtx& C, int m, const do
                     stv(pf + 3 * pb, ldv(pf + 3 * pb) - f);
                 }
             }
-            prev = k;
+            prev = k; pa = pb; ba = bb;
         }
     }
     return o;

@@ -229,7 +229,7 @@ __device__ __forceinline__ double warp_sum(double v) { // fixed butterfly order 
 // time_moved: the evaluation's time differs from the one whose tracking-reference values sit in the scratch.
 // lockstep: every warp of the block runs the same kind of evaluation (same mask and reuse), so they meet at a block
 // barrier between phases and share their instruction fetches (the code is long and mostly straight-line).
-template <int reuse>
+template <int reuse, bool WRAP = false>
 __device__ __forceinline__ void warp_eval_point_t(const DevTables& T, const WarpAux& A, double* ws, unsigned mask, bool time_moved,
                                                   bool lockstep) {
     const WarpCtx C{T, A, ws, (int)(threadIdx.x & 31)};
@@ -288,10 +288,10 @@ __device__ __forceinline__ void warp_eval_point_t(const DevTables& T, const Warp
         if (reuse == 0) {
             for (int b = lane; b < nb; b += 32) wk_body_inertia(C, b);
             PHASE_MARK(2);
-            if (dyn) for (int m = lane; m < T.nmus; m += 32) wk_muscle_geometry(C, m, q);
+            if (dyn) for (int m = lane; m < T.nmus; m += 32) wk_muscle_geometry<WRAP>(C, m, q);
         }
         PHASE_MARK(3);
-        for (int k = lane; k < 3 * T.npp; k += 32) ws[A.o_pf + k] = 0.0;
+        for (int k = lane; k < 3 * A.npp_ext; k += 32) ws[A.o_pf + k] = 0.0;
         __syncwarp();
         const int nent = (dyn ? T.nmus : 0) + (reuse < 2 ? T.ncontact : 0);
         for (int e = lane; e < nent; e += 32) {
@@ -427,9 +427,10 @@ __device__ __forceinline__ void warp_eval_point_t(const DevTables& T, const Warp
     PHASE_MARK(10);
 }
 // run-time reuse level: one specialised copy of the evaluation per level
+template <bool WRAP = false>
 __device__ inline void warp_eval_point(const DevTables& T, const WarpAux& A, double* ws, unsigned mask, int reuse, bool time_moved,
                                        bool lockstep = false) {
-    if (reuse == 0) warp_eval_point_t<0>(T, A, ws, mask, time_moved, lockstep);
+    if (reuse == 0) warp_eval_point_t<0, WRAP>(T, A, ws, mask, time_moved, lockstep);
     else if (reuse == 1) warp_eval_point_t<1>(T, A, ws, mask, time_moved, lockstep);
     else warp_eval_point_t<2>(T, A, ws, mask, time_moved, lockstep);
 }

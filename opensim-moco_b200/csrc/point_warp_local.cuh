@@ -34,14 +34,23 @@ __device__ inline void wk_unit_tension_force(const WarpCtx& C, int m, double* Rm
     const unsigned active = (unsigned)C.at(A.o_mact)[m];
     const double* ppos = C.at(A.o_ppos);
     for (int k = 0; k < nq; ++k) Rm[k] = 0.0;
-    int prev = -1;
-    for (int k = 0; k < count; ++k) {
-        if (!((active >> k) & 1u)) continue;
+    const bool wrapped = wk_muscle_wrap_count(C, m) > 0; // then walk the stored current path (tangent points are stations of the cylinders' bodies)
+    const signed char* mp = wrapped ? reinterpret_cast<const signed char*>(C.at(A.o_mpath) + 4 * m) : nullptr;
+    const int nent = wrapped ? mp[0] : count;
+    const int fixedRec[MOCOB200_PP_ISTRIDE] = {-1, MOCOB200_PP_FIXED, -1, -1, -1, -1, -1, -1};
+    int prev = -1, pa = -1, bodyA = -1;
+    const int* ia = fixedRec;
+    for (int k = 0; k < nent; ++k) {
+        int pb, bodyB, wo;
+        if (wrapped) pb = wk_path_slot(C, m, mp[1 + k], bodyB, wo);
+        else {
+            if (!((active >> k) & 1u)) continue;
+            pb = first + k;
+            bodyB = T.idx[T.o_pp_i + pb * MOCOB200_PP_ISTRIDE];
+        }
+        const int* ib = pb < T.npp ? T.idx + T.o_pp_i + pb * MOCOB200_PP_ISTRIDE : fixedRec; // a tangent point is never a moving point
         if (prev >= 0) {
-            const int pa = first + prev, pb = first + k;
-            const int* ia = T.idx + T.o_pp_i + pa * MOCOB200_PP_ISTRIDE;
-            const int* ib = T.idx + T.o_pp_i + pb * MOCOB200_PP_ISTRIDE;
-            if (ia[0] != ib[0]) {
+            if (bodyA != bodyB) {
                 V3 dir = ldv(ppos + 3 * pb) - ldv(ppos + 3 * pa);
                 const double nn = sqrt(dot(dir, dir));
                 dir = (nn < 1.9984014443252818e-14) ? (NAN * dir) : ((1.0 / nn) * dir);
@@ -59,7 +68,7 @@ __device__ inline void wk_unit_tension_force(const WarpCtx& C, int m, double* Rm
                         Rm[pi[6]] += side ? -dot(dpg, dir) : dot(dpg, dir);
                     }
                 }
-                int ba = ia[0], bb = ib[0];
+                int ba = bodyA, bb = bodyB;
                 while (ba != bb) {
                     const bool sideB = bb > ba;
                     const int b = sideB ? bb : ba;
@@ -74,7 +83,7 @@ __device__ inline void wk_unit_tension_force(const WarpCtx& C, int m, double* Rm
                 }
             }
         }
-        prev = k;
+        prev = k; pa = pb; bodyA = bodyB; ia = ib;
     }
 }
 

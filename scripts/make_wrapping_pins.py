@@ -70,3 +70,8 @@ np.savez_compressed(os.path.join(OUT, "rajagopal_cmc_rows.npz"), time=time, q=q,
                     time_v=time_v, q_v=q_v, u_v=u_v, speeds=speeds, muscles=np.array(mnames), coords=np.array(coords),
                     control_index=np.array(order))
 print(len(rows), "length rows,", len(srow), "speed rows", os.path.getsize(os.path.join(OUT, "rajagopal_cmc_rows.npz")))
+
+# BASELINE config 4 (exampleMocoInverse on the armless Rajagopal model): the flattened problem for the tests and the bench
+p4 = m.Problem.example("rajagopal_inverse", os.path.join(REF, "Moco/Examples/C++/example3DWalking"), None)
+p4.save(os.path.join(OUT, "rajagopal_inverse.mb20"))
+print("rajagopal_inverse", p4.dims().asdict(), os.path.getsize(os.path.join(OUT, "rajagopal_inverse.mb20")))

@@ -90,6 +90,35 @@ def test_wrapping_changes_the_lengths_it_should(pkg, orc, rows):
     assert (np.abs(d[:, nw > 0]).max(axis=0) > 1e-6).sum() >= 20  # most wrapped muscles do wrap somewhere in the trial
 
 
+def test_tension_through_the_tangent_points_is_consistent_with_the_path_length(pkg, orc, rows):
+    """Forces are applied through the tangent points as stations of the cylinders' bodies (GeometryPath.cpp:306-432 with
+    PathWrapPoints). Implementation-independent check: the generalized force of a unit tension equals -dL/dq - exactly for
+    straight paths, and to the 0.1 degree tangency tolerance of the reference's heuristic (about 1e-4 m of moment arm) for
+    wrapped ones."""
+    p = pkg.Problem.load(golden("rajagopal_replay.mb20"))
+    o = orc.Oracle(p)
+    nw = wraps_per_muscle(p)
+    nq = p.table_sizes().nq
+    out, tau, u = np.zeros(2), np.zeros(nq), np.zeros(nq)
+    worst = {0: 0.0, 1: 0.0, 2: 0.0}
+    q = np.ascontiguousarray(rows["q"][40])
+    for m in range(len(nw)):
+        orc.lib().orc_path_generalized_force(o._h, m, orc._d(q), 1.0, orc._d(tau))
+        g = np.zeros(nq)
+        for k in range(nq):
+            h = 1e-6
+            qa, qb = q.copy(), q.copy()
+            qa[k] += h
+            qb[k] -= h
+            orc.lib().orc_path(o._h, m, orc._d(qa), orc._d(u), orc._d(out))
+            la = out[0]
+            orc.lib().orc_path(o._h, m, orc._d(qb), orc._d(u), orc._d(out))
+            g[k] = -(la - out[0]) / (2 * h)
+        worst[int(nw[m])] = max(worst[int(nw[m])], float(np.abs(g - tau).max()))
+    assert worst[0] < 2e-9
+    assert 1e-7 < max(worst[1], worst[2]) < 5e-4  # moment arms are centimetres: a few parts in a thousand
+
+
 def replay_problem(pkg, times):
     """The replay problem on a mesh whose grid points sit at the given times (trapezoidal: grid = mesh)."""
     mesh = (times - times[0]) / (times[-1] - times[0])
@@ -134,12 +163,67 @@ def test_gpu_path_lengths_and_speeds_match_the_reference(pkg, orc, rows):
 
 
 @pytest.mark.gpu
-def test_gpu_refuses_dynamics_with_wrap_cylinders_loudly(pkg, rows):
-    """Until the warp kernels carry the wrap points, a model with wrap cylinders must not silently evaluate without them."""
-    p = replay_problem(pkg, rows["time_v"][:4].copy())
-    ev = pkg.Evaluator(p)
-    x = iterate_at(p, rows["time_v"][:4], rows["q_v"][:4], rows["u_v"][:4])
-    with pytest.raises(RuntimeError, match="wrap cylinders"):
-        ev.eval_points(x)
-    with pytest.raises(RuntimeError, match="wrap cylinders"):
-        ev.eval_jac_g(x)
+def test_gpu_dynamics_with_wrap_cylinders_match_the_oracle(pkg, orc, rows):
+    """The full-body model through the point functions (explicit forward dynamics of 39 coordinates, 80 path actuators over
+    their wrap cylinders, 2 coupler constraints): kernels against the oracle, values 1e-10 and FD Jacobian blocks 1e-7."""
+    sel = np.arange(0, len(rows["time_v"]), 8)
+    p = replay_problem(pkg, rows["time_v"][sel].copy())
+    ev, o = pkg.Evaluator(p), orc.Oracle(p)
+    x = iterate_at(p, rows["time_v"][sel], rows["q_v"][sel], rows["u_v"][sel])
+    d = p.dims()
+    rng = np.random.default_rng(0)
+    N = d.n_grid
+    ctl = x[2 + N * d.ns:2 + N * (d.ns + d.nc)].reshape(N, d.nc)
+    ctl[:] = rng.uniform(0.0, 300.0, ctl.shape)  # tensions (N) and actuator controls
+    x[2 + N * (d.ns + d.nc):2 + N * (d.ns + d.nc + d.nm)] = rng.uniform(-50, 50, N * d.nm)
+    Y, Yo = ev.eval_points(x), o.eval_points(x)
+    assert np.isfinite(Yo).all()
+    assert np.max(np.abs(Y - Yo) / (np.abs(Yo) + 1e-6 * np.abs(Yo).max())) < 1e-10
+    assert np.max(np.abs(ev.eval_g(x) - o.eval_g(x))) < 1e-10 * np.abs(o.eval_g(x)).max()
+    # the mass matrix of the full-body model has a condition number of 7e5 (wrists against the trunk), so the accelerations of
+    # the light segments carry 1e-10 of round-off and a forward quotient with h = 1e-4 differs by 1e-6 between ANY two
+    # implementations (measured: the mismatch scales with 1/h and sits in one wrist row); h = 1e-3 keeps it below the bar
+    ev.set_fd(0, 1e-3, 0)
+    o.set_fd(0, 1e-3, 0)
+    J = ev.eval_points(x, jacobian=True)
+    _, Jo = o.eval_point_jacobians(x)
+    scale = np.abs(Yo)[:, :, None] + np.abs(Jo) + 1e-4 * np.abs(Yo).max()
+    assert np.max(np.abs(J - Jo) / scale) < 1e-7
+
+
+
+# ---- BASELINE config 4: exampleMocoInverse on the armless Rajagopal model (80 DeGrooteFregly2016 muscles, prescribed kinematics)
+def test_config4_layout(pkg):
+    """exampleMocoInverse.cpp:34-77 through MocoInverse.cpp:44-140: 80 activation states, 80 excitations + 6 residual and 10
+    reserve actuators, 2 multipliers (the patella couplers; no constraint rows with prescribed kinematics), no derivative
+    variables (rigid tendons), 18 multibody residual rows per grid point, 80 initial-activation rows."""
+    p = pkg.Problem.load(golden("rajagopal_inverse.mb20"))
+    d, t = p.dims(), p.table_sizes()
+    assert (t.nb, t.nq, t.nmus, t.prescribed, t.npathwrap, t.ncoupler, t.nxforce) == (14, 18, 80, 1, 0, 2, 2)
+    assert (d.n_mesh, d.n_grid, d.ns, d.nc, d.nd, d.nm, d.n_kc) == (50, 99, 80, 96, 0, 2, 0)
+    assert d.n_in == 1 + 80 + 96 + 2 and d.n_out == 18 + 80 + 1
+    assert d.n_var == 2 + 99 * (80 + 96 + 2)
+    assert d.n_con == 80 + 99 * 18 + 49 * 2 * 80
+
+
+@pytest.mark.gpu
+def test_config4_gpu_matches_oracle(pkg, orc):
+    p = pkg.Problem.load(golden("rajagopal_inverse.mb20"), "num_mesh_intervals=6")
+    ev, o = pkg.Evaluator(p), orc.Oracle(p)
+    x = p.make_iterate(seed=2, spread=0.3)
+    Y, Yo = ev.eval_points(x), o.eval_points(x)
+    assert np.isfinite(Yo).all()
+    assert np.max(np.abs(Y - Yo) / (np.abs(Yo) + 1e-6 * np.abs(Yo).max())) < 1e-10
+    g, go = ev.eval_g(x), o.eval_g(x)
+    assert np.max(np.abs(g - go)) < 1e-10 * np.abs(go).max()
+    f, fo = ev.eval_f(x), o.eval_f(x)
+    assert abs(f - fo) < 1e-10 * abs(fo)
+    ev.set_fd(0, 1e-4, 0)
+    o.set_fd(0, 1e-4, 0)
+    v, vo = ev.eval_jac_g(x), o.eval_jac_g(x)
+    _, rowidx = o.structure()
+    rowmax = np.zeros(o.n_con)
+    np.maximum.at(rowmax, rowidx, np.abs(vo))
+    assert np.max(np.abs(v - vo) / (np.abs(vo) + rowmax[rowidx] + 1e-300)) < 5e-7
+    gr, gro = ev.eval_grad_f(x), o.eval_grad_f(x)
+    assert np.max(np.abs(gr - gro)) <= 1e-7 * max(1.0, np.abs(gro).max(), abs(fo))
