@@ -44,6 +44,10 @@ WORKLOADS = {
                 "example2DWalking gaitTracking: 2D_gait.osim, Hermite-Simpson, 50 intervals (101 grid points), forward FD"),
     "config5": ("gait2d_prediction.mb20", "num_mesh_intervals=800", 1,
                 "example2DWalking gaitPrediction at 800 intervals (1601 grid points), central FD"),
+    # BASELINE config 4 (--workload config4): exampleMocoInverse, the armless full-body Rajagopal model, 80 muscles, kinematics prescribed
+    "config4": ("rajagopal_inverse.mb20", None, 0,
+                "exampleMocoInverse: Rajagopal 3D model, 80 DeGrooteFregly2016 muscles, prescribed kinematics, Hermite-Simpson, "
+                "49 intervals (99 grid points), implicit mode, forward FD"),
 }
 METRIC = "NLP Jacobian evals/s (2D gait, 101 mesh pts)"
 UNIT = "jacobian evals/s"
@@ -102,7 +106,7 @@ def make_iterates(m, prob, n, kind):
     coordinate and speed; activations and excitations U(0.01, 1); the lumbar actuator U(-10, 10); t0 = 0, tf = 0.47008941; the feet
     are in contact with the ground as in a solve. kind "bounds": bounds midpoint + 0.1 U(-1, 1) half-range (round 1's iterates)."""
     d = prob.dims()
-    if kind == "bounds":
+    if kind == "bounds" or prob.table_sizes().prescribed:  # (prescribed kinematics: no coordinate states to put on a trajectory)
         return np.stack([prob.make_iterate(seed=k, spread=0.1) for k in range(n)])
     track = m.Problem.load(os.path.join(DATA, "gait2d_tracking.mb20"))
     t, dbl, idx = _pools(m, track)
@@ -152,7 +156,7 @@ def config_dict(workload, desc, dims, fd, sparsity, iterates_kind):
             "nnz_jac": int(dims["nnz_jac"]), "sparsity_detection": sparsity, "fd": FD_NAMES[fd],
             "iterates": ("seeded iterates: reference walking trajectory (referenceCoordinates.sto splines) + U(-0.02,0.02)*(upper-lower) "
                          "on coordinates and speeds, activations/excitations U(0.01,1), lumbar U(-10,10), tf = 0.47008941"
-                         if iterates_kind == "trajectory" else
+                         if iterates_kind == "trajectory" and not workload.startswith("config4") else
                          "seeded iterates: bounds midpoint + 0.1*U(-1,1)*half-range")}
 
 
