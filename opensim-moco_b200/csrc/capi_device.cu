@@ -92,7 +92,15 @@ struct mocob200_handle {
     long warpMaxEvals = 30000;
     bool beyondThreadKernels = false;
     bool wrapInWarpKernels = true; // the warp kernels carry the wrap tangent points (point_warp.cuh: wk_muscle_wraps)
-    bool warpFor(long evals) const { return kernelMode == 1 || (kernelMode == 0 && evals <= warpMaxEvals); }
+    // Central differences: every direction costs 2 x (1 + h_iter) evaluations and the warp kernels run them one after the
+    // other, while the paired thread kernel runs the two sides on adjacent lanes - measured on gait prediction (B200, ms per
+    // Jacobian, thread / warp): 101 grid points 0.47 / 0.70, 201: 0.49 / 1.28, 401: 0.71 / 2.40, 1601: 1.24 / 8.81
+    // (scripts/gpu_kernel_crossover.py). So the warp kernels are chosen for one-sided schemes only.
+    bool warpFor(long evals) const {
+        return kernelMode == 1 || (kernelMode == 0 && evals <= warpMaxEvals && fd.scheme != MOCOB200_FD_CENTRAL);
+    }
+    // the nominal evaluations alone (eval_f / eval_g / eval_points): one evaluation per grid point, whatever the FD scheme
+    bool warpForValues(long evals) const { return kernelMode == 1 || (kernelMode == 0 && evals <= warpMaxEvals); }
     std::vector<void*> owned;
     double* d_cfg = nullptr; // per-point blobs of the nominal evaluation (warp kernels)
     double *d_x = nullptr, *d_Y = nullptr, *d_J = nullptr, *d_I = nullptr, *d_G = nullptr, *d_E = nullptr;
@@ -397,7 +405,7 @@ bool dynamicsSupported(mocob200_handle* h) {
 bool runNominal(mocob200_handle* h) {
     if (!dynamicsSupported(h)) return false;
     if (h->rank >= h->eff) return true; // idle rank
-    if (h->warpFor(h->p1 - h->p0)) launch_wpoints_nominal(h->DT, h->WA, h->DL, h->d_x, h->d_Y, nullptr, h->p0, h->p1 - h->p0, h->stream);
+    if (h->warpForValues(h->p1 - h->p0)) launch_wpoints_nominal(h->DT, h->WA, h->DL, h->d_x, h->d_Y, nullptr, h->p0, h->p1 - h->p0, h->stream);
     else launch_points_nominal(h->DT, h->DL, h->d_x, h->d_Y, h->p0, h->p1 - h->p0, h->stream);
     h->launches++;
     if (!gatherBlocks(h, h->d_Y, (size_t)h->L.n_out)) return false;
@@ -1275,7 +1283,7 @@ extern "C" int mocob200_eval_g_static(mocob200_handle* h, const double* d_x, dou
     // the array keeps the previous call's contents: clear the part this call uses
     if (!h->ck(cudaMemsetAsync(base, 0, need, s), "clear static scratch")) return MOCOB200_ERR_CUDA;
     const int np = h->p1 - h->p0;
-    if (h->warpFor(np)) launch_wpoints_nominal(h->DT, h->WA, h->DL, d_x, sY, nullptr, h->p0, np, s);
+    if (h->warpForValues(np)) launch_wpoints_nominal(h->DT, h->WA, h->DL, d_x, sY, nullptr, h->p0, np, s);
     else launch_points_nominal(h->DT, h->DL, d_x, sY, h->p0, np, s);
     launch_integrals(h->DL, d_x, sY, nullptr, sI, false, s);
     launch_endpoint(h->DT, h->DL, h->fd, d_x, sI, sG, sE, false, s);
