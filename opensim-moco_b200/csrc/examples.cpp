@@ -505,33 +505,20 @@ std::unique_ptr<FlatProblem> rajagopalReplay(const std::string& dir, const std::
     return flatten(P, S);
 }
 
-// BASELINE config 4: exampleMocoInverse (Moco/Examples/C++/example3DWalking/exampleMocoInverse.cpp:34-77) - MocoInverse
-// (MocoInverse.cpp:44-140) on the armless full-body Rajagopal model, 80 muscles, kinematics of coordinates.sto prescribed.
-// Model operators, in the example's order: ModOpAddExternalLoads(grf_walk.xml), ModOpIgnoreTendonCompliance,
-// ModOpReplaceMusclesWithDeGrooteFregly2016 (copies the path POINTS only: the DeGrooteFregly2016 muscles of this problem have
-// no wrap surfaces, in the reference too - DeGrooteFregly2016Muscle.cpp:1009-1021), ModOpIgnorePassiveFiberForcesDGF,
-// ModOpScaleActiveFiberForceCurveWidthDGF(1.5), ModOpAddReserves(1.0).
-// Kinematics: the table is in degrees; OpenSim converts the columns of Rotational coordinates only (SimbodyEngine.cpp:905-945;
-// a CustomJoint coordinate is Rotational when a rotation axis follows it with slope +-1, CustomJoint.cpp:150-200), and
-// StatesTrajectory::createFromStatesStorage(assemble = true) then moves the coordinates that are free to satisfy constraints -
-// the patella's knee_angle_*_beta - onto their coupler functions; the value columns are splined (GCVSplineSet, degree 5).
-std::unique_ptr<FlatProblem> rajagopalInverse(const std::string& dir, const std::string& options) {
-    Problem P;
-    P.model = loadOsim(dir + "/subject_walk_armless.osim", false, false, /*musclesAsDGF=*/true);
-    appendExternalLoads(P.model, dir + "/grf_walk.xml");
-    for (MuscleSpec& mu : P.model.muscles) {
-        mu.ignoreTendonCompliance = true;
-        mu.ignorePassiveFiberForce = true;
-        mu.activeForceWidthScale = 1.5;
-    }
-    const StoTable tab = readSto(dir + "/coordinates.sto");
+// ---- pieces of MocoInverse / TableProcessor shared by the full-body inverse problems
+// The value columns of a coordinates table as OpenSim reads them for a model: labels are state paths (".../value") or bare
+// coordinate names (older files; TableProcessor::process -> updateStateLabels40); with inDegrees = yes only the columns of
+// Rotational coordinates are converted (SimbodyEngine.cpp:905-945; a CustomJoint coordinate is Rotational when a rotation axis
+// follows it with slope +-1, CustomJoint.cpp:150-200).
+std::map<std::string, std::vector<double>> coordinateColumns(const ModelSpec& M, const StoTable& tab) {
     const double deg = tab.inDegrees ? kPi / 180.0 : 1.0;
-    std::map<std::string, std::vector<double>> values; // coordinate name -> column (radians / metres)
-    for (const JointSpec& J : P.model.joints)
+    std::map<std::string, std::vector<double>> values;
+    for (const JointSpec& J : M.joints)
         for (const CoordSpec& c : J.coords) {
             const std::string path = J.container + J.name + "/" + c.name;
-            const int ci = tab.col(path + "/value");
-            if (ci < 0) throw std::runtime_error("coordinates.sto lacks " + path + "/value");
+            int ci = tab.col(path + "/value");
+            if (ci < 0) ci = tab.col(c.name);
+            if (ci < 0) throw std::runtime_error("the coordinates table lacks '" + c.name + "'");
             bool rotational = J.kind == MOCOB200_JOINT_PIN;
             if (J.kind == MOCOB200_JOINT_CUSTOM)
                 for (int a = 0; a < 3; ++a)
@@ -540,7 +527,57 @@ std::unique_ptr<FlatProblem> rajagopalInverse(const std::string& dir, const std:
             if (rotational) for (double& x : v) x *= deg;
             values[c.name] = v;
         }
-    for (const CouplerSpec& C : P.model.couplers) { // assembly: the dependent coordinate follows its coupler function
+    return values;
+}
+// TabOpLowPassFilter (Common/TableProcessor.h:160-175 -> MocoUtilities.cpp:199-208): Storage::pad(rows / 2) - the signal
+// continued at both ends by its reflection through the end point (Signal.cpp:418-450) - then a third-order Butterworth
+// filter run forwards and backwards (Signal::LowpassIIR, Signal.cpp:160-245). The padded rows stay in the table.
+void lowpassFilter(std::vector<double>& time, std::map<std::string, std::vector<double>>& values, double cutoff) {
+    const int n = (int)time.size(), pad = n / 2;
+    auto padded = [&](const std::vector<double>& s) {
+        std::vector<double> r(n + 2 * pad);
+        for (int i = 0, j = pad; i < pad; ++i, --j) r[i] = 2.0 * s[0] - s[j];
+        for (int i = 0; i < n; ++i) r[pad + i] = s[i];
+        for (int i = pad + n, j = n - 2; i < 2 * pad + n; ++i, --j) r[i] = 2.0 * s[n - 1] - s[j];
+        return r;
+    };
+    time = padded(time);
+    const int N = (int)time.size();
+    double dt = time[1] - time[0];
+    for (int i = 1; i + 1 < N; ++i) dt = std::min(dt, time[i + 1] - time[i]); // Storage::getMinTimeStep (uniform tables: no resampling)
+    const double wa = std::tan(2.0 * kPi * cutoff * dt / 2.0), wa2 = wa * wa, wa3 = wa2 * wa;
+    const double denom = (wa + 1) * (wa * wa + wa + 1.0);
+    const double a[4] = {wa3 / denom, 3 * wa3 / denom, 3 * wa3 / denom, wa3 / denom};
+    const double b[4] = {1, (3 * wa3 + 2 * wa2 - 2 * wa - 3) / denom, (3 * wa3 - 2 * wa2 - 2 * wa + 3) / denom, (wa - 1) * (wa2 - wa + 1) / denom};
+    auto pass = [&](const std::vector<double>& in) {
+        std::vector<double> out(N);
+        for (int i = 0; i <= 3 && i < N; ++i) out[i] = in[i];
+        for (int i = 3; i < N; ++i)
+            out[i] = a[0] * in[i] + a[1] * in[i - 1] + a[2] * in[i - 2] + a[3] * in[i - 3] - b[1] * out[i - 1] - b[2] * out[i - 2] - b[3] * out[i - 3];
+        return std::vector<double>(out.rbegin(), out.rend());
+    };
+    for (auto& kv : values) kv.second = pass(pass(padded(kv.second)));
+}
+// ModOpReplaceJointsWithWelds (ModelFactory.cpp: replaceJointWithWeldJoint): same frames, no coordinates
+void replaceJointsWithWelds(ModelSpec& M, const std::vector<std::string>& names) {
+    for (const std::string& n : names) {
+        bool found = false;
+        for (JointSpec& J : M.joints)
+            if (J.name == n) {
+                found = true;
+                J.kind = MOCOB200_JOINT_WELD;
+                J.coords.clear();
+                for (auto& A : J.axes) A = TransformAxisSpec();
+            }
+        if (!found) throw std::runtime_error("no joint named '" + n + "'");
+    }
+}
+// MocoInverse::initializeInternal (MocoInverse.cpp:44-140) from here on: dependent coordinates follow their coupler functions
+// (StatesTrajectory::createFromStatesStorage with assemble = true moves the coordinates that are free to satisfy constraints),
+// PositionMotion from GCV splines (degree 5) of the value columns, MocoControlGoal + MocoInitialActivationGoal, solver settings.
+std::unique_ptr<FlatProblem> finishInverse(Problem& P, const std::vector<double>& time, std::map<std::string, std::vector<double>>& values,
+                                           bool addReserves, double t0, double tf, int intervals, const std::string& options) {
+    for (const CouplerSpec& C : P.model.couplers) {
         if (C.fn.fnKind == MOCOB200_FN_SIMMSPLINE) throw std::runtime_error("coupler '" + C.name + "': spline-coupled kinematics are unsupported here");
         const std::vector<double>& qi = values.at(C.independent);
         std::vector<double>& qd = values.at(C.dependent);
@@ -550,13 +587,12 @@ std::unique_ptr<FlatProblem> rajagopalInverse(const std::string& dir, const std:
     for (const JointSpec& J : P.model.joints)
         for (const CoordSpec& c : J.coords) {
             const std::string path = J.container + J.name + "/" + c.name;
-            P.model.positionMotion.emplace_back(path, fitNaturalSpline(tab.time, values.at(c.name), 5));
-            bool has = false;
+            P.model.positionMotion.emplace_back(path, fitNaturalSpline(time, values.at(c.name), 5));
+            if (!addReserves) continue;
+            bool has = false; // ModOpAddReserves(1.0): ModelFactory.cpp:265-320
             for (const CoordActSpec& a : P.model.coordActs) has = has || a.coord == c.name;
+            for (const CouplerSpec& C : P.model.couplers) has = has || C.dependent == c.name; // constrained: no reserve (:294)
             if (has) continue;
-            bool constrained = false; // ModelFactory.cpp:294: no reserve on a coordinate a constraint determines
-            for (const CouplerSpec& C : P.model.couplers) constrained = constrained || C.dependent == c.name;
-            if (constrained) continue;
             CoordActSpec a;
             std::string n = path;
             for (char& ch : n) if (ch == '/') ch = '_';
@@ -566,11 +602,11 @@ std::unique_ptr<FlatProblem> rajagopalInverse(const std::string& dir, const std:
             P.model.actuatorOrder.emplace_back(0, (int)P.model.coordActs.size());
             P.model.coordActs.push_back(a);
         }
-    P.setTimeBounds(Bounds(0.81), Bounds(1.79));
+    P.setTimeBounds(Bounds(t0), Bounds(tf));
     P.addGoal(MOCOB200_GOAL_CONTROL, "excitation_effort", 1.0);
     P.addGoal(MOCOB200_GOAL_INITIAL_ACTIVATION, "initial_activation");
     SolverSettings S;
-    S.num_mesh_intervals = 49; // mesh_interval 0.02 s over [0.81, 1.79]
+    S.num_mesh_intervals = intervals;
     S.multibody_dynamics_mode = "implicit";
     S.interpolate_control_midpoints = false;
     S.minimize_implicit_auxiliary_derivatives = true;
@@ -581,6 +617,47 @@ std::unique_ptr<FlatProblem> rajagopalInverse(const std::string& dir, const std:
     S.optim_constraint_tolerance = 1e-3;
     S.applyOptions(options);
     return flatten(P, S);
+}
+
+// BASELINE config 4: exampleMocoInverse (Moco/Examples/C++/example3DWalking/exampleMocoInverse.cpp:34-77) - MocoInverse
+// on the armless full-body Rajagopal model, 80 muscles, kinematics of coordinates.sto prescribed.
+// Model operators, in the example's order: ModOpAddExternalLoads(grf_walk.xml), ModOpIgnoreTendonCompliance,
+// ModOpReplaceMusclesWithDeGrooteFregly2016 (copies the path POINTS only: the DeGrooteFregly2016 muscles of this problem have
+// no wrap surfaces, in the reference too - DeGrooteFregly2016Muscle.cpp:1009-1021), ModOpIgnorePassiveFiberForcesDGF,
+// ModOpScaleActiveFiberForceCurveWidthDGF(1.5), ModOpAddReserves(1.0). Time range [0.81, 1.79], mesh interval 0.02 s.
+std::unique_ptr<FlatProblem> rajagopalInverse(const std::string& dir, const std::string& options) {
+    Problem P;
+    P.model = loadOsim(dir + "/subject_walk_armless.osim", false, false, /*musclesAsDGF=*/true);
+    appendExternalLoads(P.model, dir + "/grf_walk.xml");
+    for (MuscleSpec& mu : P.model.muscles) {
+        mu.ignoreTendonCompliance = true;
+        mu.ignorePassiveFiberForce = true;
+        mu.activeForceWidthScale = 1.5;
+    }
+    const StoTable tab = readSto(dir + "/coordinates.sto");
+    auto values = coordinateColumns(P.model, tab);
+    return finishInverse(P, tab.time, values, /*addReserves=*/true, 0.81, 1.79, 49, options);
+}
+
+// The reference's regression test of MocoInverse (Moco/Tests/testMocoInverse.cpp:118-148, "MocoInverse Rajagopal2016, 18
+// muscles"), whose SOLUTION the reference ships (std_testMocoInverse_subject_18musc_solution.sto: objective 1.087741 after 52
+// IPOPT iterations): subject_walk_armless_18musc.osim with the subtalar and toe joints welded, DeGrooteFregly2016 muscles
+// without passive fibre force and with implicit tendon dynamics where the tendon is compliant, external loads; coordinates
+// low-pass filtered at 6 Hz; time range [0.45, 1.0], mesh interval 0.05 s. The tests evaluate f and g at the shipped solution.
+std::unique_ptr<FlatProblem> inverse18Muscles(const std::string& dir, const std::string& options) {
+    Problem P;
+    P.model = loadOsim(dir + "/subject_walk_armless_18musc.osim", false, /*lockedAsFree=*/true, /*musclesAsDGF=*/true);
+    replaceJointsWithWelds(P.model, {"subtalar_r", "subtalar_l", "mtp_r", "mtp_l"});
+    for (MuscleSpec& mu : P.model.muscles) {
+        mu.ignorePassiveFiberForce = true;
+        mu.tendonImplicit = true;
+    }
+    appendExternalLoads(P.model, dir + "/subject_walk_armless_external_loads.xml");
+    const StoTable tab = readSto(dir + "/subject_walk_armless_coordinates.mot");
+    auto values = coordinateColumns(P.model, tab);
+    std::vector<double> time = tab.time;
+    lowpassFilter(time, values, 6.0);
+    return finishInverse(P, time, values, /*addReserves=*/false, 0.45, 1.0, 11, options);
 }
 
 // MocoInverse (Moco/Moco/MocoInverse.cpp:44-140) on the example2DWalking model: the kinematics of referenceCoordinates.sto are
@@ -650,6 +727,7 @@ std::unique_ptr<FlatProblem> buildExample(const std::string& name, const std::st
     if (name == "gait10dof_replay") return gait10dofReplay(dataDir, options);
     if (name == "rajagopal_replay") return rajagopalReplay(dataDir, options);
     if (name == "rajagopal_inverse") return rajagopalInverse(dataDir, options);
+    if (name == "moco_inverse_18musc") return inverse18Muscles(dataDir, options);
     if (name == "gait2d_inverse") return gaitInverse(dataDir, options);
     if (name == "gait2d_inverse_free") return gaitInverse(dataDir, options, false);
     if (name == "planar_point_mass_coupler") return planarPointMassCoupler(options);

@@ -249,7 +249,9 @@ void readPath(const Ctx& cx, const XmlNode& n, MuscleSpec& mu, bool dropWraps = 
     if (!objs) throw std::runtime_error("muscle '" + mu.path + "' has no path points");
     for (auto& pn : objs->children) {
         PathPointSpec pt;
-        std::string frame = cx.v3 ? pn->childText("body") : pn->childText("socket_parent_frame");
+        // (files between Version 30000 and 40000 mix the two layouts: take whichever the point carries)
+        std::string frame = pn->childText("socket_parent_frame");
+        if (frame.empty()) frame = pn->childText("body");
         if (!cx.baseFrame(frame, pt.body))
             throw std::runtime_error("path point '" + pn->name() + "': parent frame '" + frame + "' must be a body");
         if (pn->tag == "PathPoint") {
