@@ -571,6 +571,10 @@ int mocob200_create(const mocob200_tables* T, const mocob200_transcription* R, i
     for (int m = 0; m < T->nmus; ++m)
         if (T->idx[T->o_mus_i + m * MOCOB200_MUS_ISTRIDE + 1] > MOCOB200_MAXPPM)
             return fail(MOCOB200_ERR_UNSUPPORTED, "a muscle has more path points than the compiled limit");
+    if (T->npathwrap > 0)
+        for (int m = 0; m < T->nmus; ++m)
+            if (T->idx[T->o_pw_i + 2 * m + 1] > MOCOB200_MAXWRAP)
+                return fail(MOCOB200_ERR_UNSUPPORTED, "a muscle wraps over more cylinders than the compiled limit (4)");
     for (int g = 0; g < T->ngoal; ++g)
         if (T->idx[T->o_goal_i + g * MOCOB200_GOAL_ISTRIDE + 2] > MOCOB200_MAX_EOUT)
             return fail(MOCOB200_ERR_UNSUPPORTED, "a goal has more outputs than the compiled limit");
