@@ -490,9 +490,16 @@ std::unique_ptr<FlatProblem> gait10dofReplay(const std::string& dir, const std::
 // 30000): the muscles become path actuators driven by the recorded tensions; used by the tests to pin cylinder wrapping
 // (path lengths and lengthening speeds) against what the reference printed (Results_CMC/cmc_MuscleAnalysis_Length.sto,
 // cmc_Actuation_speed.sto). Locked coordinates are read as free ones (they stay constant in the recorded states).
-std::unique_ptr<FlatProblem> rajagopalReplay(const std::string& dir, const std::string& options) {
+// withLoads: also the CMC actuator set (Actuators_CMC.xml: reserve CoordinateActuators; its pelvis Point / Torque actuators are
+// left out - they load the six pelvis rows only) and the measured ground reactions (externalLoads_run.xml), for the replay of
+// the recorded accelerations through the implicit multibody residuals.
+std::unique_ptr<FlatProblem> rajagopalReplay(const std::string& dir, const std::string& options, bool withLoads = false) {
     Problem P;
     P.model = loadOsim(dir + "/outputReference/subject01_RRA_Adjusted.osim", /*musclesAsPathActuators=*/true, /*lockedAsFree=*/true);
+    if (withLoads) {
+        appendForceSetFile(P.model, dir + "/Actuators_CMC.xml");
+        appendExternalLoads(P.model, dir + "/externalLoads_run.xml", 0.75, 1.25);
+    }
     P.setTimeBounds(Bounds(0.87), Bounds(1.13));
     P.defaultSpeedBounds = Bounds(-50, 50);
     for (auto& a : P.model.coordActs) P.setControlInfo(a.path, Bounds(-1e4, 1e4));
@@ -726,6 +733,7 @@ std::unique_ptr<FlatProblem> buildExample(const std::string& name, const std::st
     if (name == "gait2d_prediction") return gaitPrediction(dataDir, options);
     if (name == "gait10dof_replay") return gait10dofReplay(dataDir, options);
     if (name == "rajagopal_replay") return rajagopalReplay(dataDir, options);
+    if (name == "rajagopal_replay_loads") return rajagopalReplay(dataDir, options, true);
     if (name == "rajagopal_inverse") return rajagopalInverse(dataDir, options);
     if (name == "moco_inverse_18musc") return inverse18Muscles(dataDir, options);
     if (name == "gait2d_inverse") return gaitInverse(dataDir, options);

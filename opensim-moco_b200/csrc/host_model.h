@@ -174,7 +174,9 @@ ModelSpec loadOsim(const std::string& path, bool musclesAsPathActuators = false,
 // ForceSet file (e.g. reserve actuators) appended to a model: CoordinateActuators only; other classes are returned by name
 std::vector<std::string> appendForceSetFile(ModelSpec& M, const std::string& path);
 // ExternalLoads .xml (+ its data file, resolved relative to the .xml) -> M.externalForces (ExternalLoads.cpp, ExternalForce.cpp:200-317)
-void appendExternalLoads(ModelSpec& M, const std::string& xmlPath);
+// [tmin, tmax]: only the data rows inside the window are splined (a window that overhangs the times of interest by 100 rows
+// changes the interior of an interpolating cubic spline by less than round-off; it keeps the flattened problem small)
+void appendExternalLoads(ModelSpec& M, const std::string& xmlPath, double tmin = -1e300, double tmax = 1e300);
 
 // ---- the optimal control problem (MocoProblem / MocoPhase surface) ----
 struct Bounds {

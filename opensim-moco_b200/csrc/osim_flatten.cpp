@@ -596,7 +596,7 @@ std::vector<std::string> appendForceSetFile(ModelSpec& M, const std::string& pat
 
 // ExternalLoads (Simulation/Model/ExternalLoads.cpp) + ExternalForce::setDataSource (ExternalForce.cpp:200-317): the three
 // columns whose labels start with the force / point / torque identifier become functions of time.
-void appendExternalLoads(ModelSpec& M, const std::string& xmlPath) {
+void appendExternalLoads(ModelSpec& M, const std::string& xmlPath, double tmin, double tmax) {
     auto doc = parseXmlFile(xmlPath);
     const XmlNode* el = doc->child("ExternalLoads");
     const XmlNode* objs = el ? el->child("objects") : nullptr;
@@ -607,7 +607,20 @@ void appendExternalLoads(ModelSpec& M, const std::string& xmlPath) {
         size_t sl = xmlPath.rfind('/');
         datafile = (sl == std::string::npos ? std::string() : xmlPath.substr(0, sl + 1)) + datafile;
     }
-    const StoTable tab = readSto(datafile);
+    StoTable tab = readSto(datafile);
+    if (tmin > -1e299 || tmax < 1e299) {
+        StoTable w;
+        w.labels = tab.labels;
+        w.inDegrees = tab.inDegrees;
+        w.cols.resize(tab.cols.size());
+        for (size_t r = 0; r < tab.time.size(); ++r)
+            if (tab.time[r] >= tmin && tab.time[r] <= tmax) {
+                w.time.push_back(tab.time[r]);
+                for (size_t c = 0; c < tab.cols.size(); ++c) w.cols[c].push_back(tab.cols[c][r]);
+            }
+        if (w.time.size() < 4) throw std::runtime_error(xmlPath + ": fewer than 4 data rows inside the requested time window");
+        tab = std::move(w);
+    }
     Ctx cx{M};
     cx.v3 = true;
     auto functionsOf = [&](const std::string& id, PiecewisePoly* out) {

@@ -130,7 +130,8 @@ __device__ inline double simm_spline(const DevTables& T, int id, double ax, int 
 //   omega = th0' A0 + th1' R0 A1 + th2' R0 R1 A2 ,  v = sum_i Ai fi'          (thi' = dfi/dq u)
 // so the motion axis of coordinate k collects the terms whose function reads q_k, and the velocity-product acceleration
 // (what remains of d/dt(omega, v) at zero udot) is
-//   b_omega = w0 x w1 + (w0 + w1) x w2 + sum_i Wi fi'' u^2 ,  b_v = sum_i Ai fi'' u^2     (wi = thi' Wi).
+//   b_omega = w0 x w1 + (w0 + w1) x w2 + sum_i Wi fi'' u^2 ,  b_v = sum_i Ai fi'' u^2     (wi = thi' Wi)
+// - except that one-coordinate joints follow the reference in dropping w1 x w2 (see custom_joint_bias).
 struct CustomJointEval {
     double R[9];     // R_FM
     V3 p;            // p_FM (in F)
@@ -172,6 +173,21 @@ __device__ inline void custom_joint_eval(const DevTables& T, int cj, const doubl
     E.p = mk(0, 0, 0);
     for (int a = 3; a < 6; ++a) { E.g[a] = ld3(d + 5 * a); E.p = E.p + f[a] * E.g[a]; }
 }
+// One-coordinate joints (every axis function reads the same coordinate, e.g. a knee whose secondary rotations are splines
+// of the flexion angle): the reference's mobilizer (SimTK::MobilizedBody::FunctionBased, Simbody 3.7 - a dependency whose
+// source is not under /root/reference) leaves w1 x w2 out of the velocity-product term. Pinned on the reference's own RRA
+// and CMC records of the Rajagopal model (tests/test_reference_dynamics_pins.py: with the term 0.8 N m off at the hip, without
+// it 1e-4 N m); joints whose rotation axes have a coordinate each (hips, shoulders) match those records with the full
+// expression, and no record here covers other sharing patterns, which keep it too.
+__device__ inline bool cj_one_coordinate(const int* rec) { // rec: 6 x { function kind | q index | spline id }
+    int q = -1;
+    for (int i = 0; i < 6; ++i) {
+        if (rec[3 * i] == MOCOB200_FN_CONSTANT) continue;
+        if (q >= 0 && rec[3 * i + 1] != q) return false;
+        q = rec[3 * i + 1];
+    }
+    return q >= 0;
+}
 // velocity-product acceleration of the joint (in F) for the speeds u
 __device__ inline void custom_joint_bias(const CustomJointEval& E, const double* u, V3& bw, V3& bv) {
     V3 w[3];
@@ -182,7 +198,9 @@ __device__ inline void custom_joint_bias(const CustomJointEval& E, const double*
         w[i] = (E.df[i] * ui) * E.g[i];
         bw = bw + (E.d2f[i] * ui * ui) * E.g[i];
     }
-    bw = bw + cross(w[0], w[1]) + cross(w[0] + w[1], w[2]);
+    bool one = true; // E.qi is -1 for constant functions
+    for (int i = 0, q = -1; i < 6; ++i) if (E.qi[i] >= 0) { one = one && (q < 0 || q == E.qi[i]); q = E.qi[i]; }
+    bw = bw + cross(w[0], w[1]) + cross(one ? w[0] : w[0] + w[1], w[2]);
     for (int i = 3; i < 6; ++i) {
         const double ui = E.qi[i] >= 0 ? u[E.qi[i]] : 0.0;
         bv = bv + (E.d2f[i] * ui * ui) * E.g[i];

@@ -63,7 +63,7 @@ __device__ inline void eval_point_vel(const DevTables& T, const WarpAux& A, cons
                 ww[i] = (cs[18 + i] * ui) * g;
                 bw = bw + (cs[24 + i] * ui * ui) * g;
             }
-            bw = bw + cross(ww[0], ww[1]) + cross(ww[0] + ww[1], ww[2]);
+            bw = bw + cross(ww[0], ww[1]) + cross(cj_one_coordinate(rec) ? ww[0] : ww[0] + ww[1], ww[2]); // point_eval.cuh: custom_joint_bias
             for (int i = 3; i < 6; ++i) {
                 const double ui = rec[3 * i] != MOCOB200_FN_CONSTANT ? u[rec[3 * i + 1]] : 0.0;
                 bv = bv + (cs[24 + i] * ui * ui) * ldv(cs + 3 * i);

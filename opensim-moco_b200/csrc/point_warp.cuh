@@ -191,7 +191,7 @@ __device__ inline void wk_body_velocity(const WarpCtx& C, int b, const double* u
             w[i] = (cs[18 + i] * ui) * g;
             bw = bw + (cs[24 + i] * ui * ui) * g;
         }
-        bw = bw + cross(w[0], w[1]) + cross(w[0] + w[1], w[2]);
+        bw = bw + cross(w[0], w[1]) + cross(cj_one_coordinate(rec) ? w[0] : w[0] + w[1], w[2]); // point_eval.cuh: custom_joint_bias
         for (int i = 3; i < 6; ++i) {
             const double ui = rec[3 * i] != MOCOB200_FN_CONSTANT ? u[rec[3 * i + 1]] : 0.0;
             bv = bv + (cs[24 + i] * ui * ui) * ldv(cs + 3 * i);
