@@ -13,4 +13,7 @@ MOCOB200_GRAPH=0 ncu --set full --clock-control none --import-source on \
     -k regex:"k_points_fd_flat_pair|k_points_fd_vel_pair|k_wlocal_central|k_wpoints_nominal|k_assemble_jac" -c 5 -o /tmp/c5 \
     python bench.py --steps 1 --warmup 3 --workload config5 > gpurun_out/ncu_c5.log 2>&1
 ncu -i /tmp/c5.ncu-rep --page raw --csv > gpurun_out/ncu_r02_config5_raw.csv 2>/dev/null
+MOCOB200_GRAPH=0 ncu --set full --clock-control none --import-source on -k regex:"k_wpoints|k_wlocal|k_assemble_jac" -c 5 -o /tmp/c4 \
+    python bench.py --steps 1 --warmup 3 --workload config4 > gpurun_out/ncu_c4.log 2>&1
+ncu -i /tmp/c4.ncu-rep --page raw --csv > gpurun_out/ncu_r02_config4_raw.csv 2>/dev/null
 ls -la gpurun_out/*.csv
