@@ -17,9 +17,10 @@ inline const char* devEnv(const char* name) {
     return on ? std::getenv(name) : nullptr;
 }
 
-#define MOCOB200_MAX_IN 200
+#define MOCOB200_MAX_IN 240
 #define MOCOB200_MAX_OUT 128
 #define MOCOB200_MAX_EOUT 128 /* outputs of one endpoint goal */
+static_assert(SizeHuge::NIN == MOCOB200_MAX_IN, "the largest size class takes every point function the library accepts");
 
 struct FdSettings {
     int scheme;    // MOCOB200_FD_*

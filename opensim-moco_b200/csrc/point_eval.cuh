@@ -33,7 +33,7 @@ namespace mocob200 {
 struct SizeLarge { static constexpr int NB = MOCOB200_MAXB, NQ = MOCOB200_MAXQ, NPPM = MOCOB200_MAXPPM, NIN = 160, NOUT = 72; static constexpr bool WRAP = false; };
 struct SizeSmall { static constexpr int NB = 8, NQ = 12, NPPM = 8, NIN = 64, NOUT = 32; static constexpr bool WRAP = false; };
 // full-body models (Rajagopal: 22 bodies, 39 coordinates): kinematics / path kernels only; their dynamics run on the warp kernels
-struct SizeHuge { static constexpr int NB = 24, NQ = 40, NPPM = MOCOB200_MAXPPM, NIN = 200, NOUT = 72; static constexpr bool WRAP = true; };
+struct SizeHuge { static constexpr int NB = 24, NQ = 40, NPPM = MOCOB200_MAXPPM, NIN = 240, NOUT = 72; static constexpr bool WRAP = true; };
 
 struct DevTables { // mocob200_tables with device (or shared-memory) pool pointers
     const double* dbl;

@@ -1,5 +1,8 @@
 // TEST INFRASTRUCTURE ONLY — CPU oracle: multibody kinematics / dynamics and applied forces.
 // See orc_point.hpp for the formulation; reference call sites are cited per function.
+// PINNED to numbers the reference produced (Simbody's own source is not under /root/reference): accelerations of the planar
+// gait model along the reference's CMC run (tests/test_reference_pins.py), and the accelerations / actuator forces of the
+// full-body RRA and CMC runs through the implicit residuals (tests/test_reference_dynamics_pins.py: 3e-6 ... 2.3e-4 N m).
 #pragma once
 #include <cstring>
 
