@@ -507,7 +507,10 @@ def main():
                    % (r["n_x"], r["n_x"] * 8e-6 * d["n_var"], r["n_v"], r["n_v"] * 8e-6 * d["nnz_jac"])) if args.l2 == "rotate" else
                   "256 MiB device fill between steps (outside the per-step CUDA events): cold code and tables",
             "point_evals_per_step": n_exec,
-            "sharding": "grid points over %d of %d rank(s); per-rank FD blocks and CSC column runs, NCCL to rank 0" % (workers, world)})
+            "sharding": "grid points over %d of %d rank(s); per-rank FD blocks and CSC column runs, %s" % (
+                workers, world, "n/a (one rank works)" if workers <= 1 else
+                "stored by each rank's assembly kernel straight into rank 0's value array over NVLink (CUDA IPC peer memory, flag words)"
+                if ev.peer_gather() else "NCCL send/recv to rank 0")})
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": r["dev_ms"] / args.steps, "higher_is_better": True, "scaling": "strong" if workload == "config5" else "weak",

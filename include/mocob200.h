@@ -297,6 +297,10 @@ long mocob200_point_evals_per_jacobian(const mocob200_handle*); /* credited: wha
 /* executed: evaluations one eval_jac_g launches over all ranks: whole | pose-reusing | pose+velocity-reusing | local-column warps */
 int mocob200_executed_evals(const mocob200_handle*, long out[4]);
 int mocob200_working_ranks(const mocob200_handle*);      /* ranks that own grid points */
+/* 1 once a sharded Jacobian has been evaluated with the other ranks storing their CSC runs straight into rank 0's value
+ * array over NVLink (CUDA IPC mappings, set up at the first sharded Jacobian); 0: single rank, not yet evaluated, or the
+ * NCCL send / recv gather is in use because a rank could not map rank 0's memory. No counterpart in the reference. */
+int mocob200_peer_gather(const mocob200_handle*);
 int mocob200_uses_warp_kernels(const mocob200_handle*);  /* 1: warp-per-evaluation FD kernels, 0: thread-per-evaluation */
 /* FP64 FMA saturation microbenchmark: returns measured TFLOP/s (the FP64 roofline peak). */
 int mocob200_measure_fp64_peak(int device, double* tflops);

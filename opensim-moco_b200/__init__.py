@@ -27,7 +27,7 @@ ABI_SYMBOLS = [
     "mocob200_eval_g_static",
     "mocob200_eval_jac_g_batch",
     "mocob200_sync", "mocob200_mark", "mocob200_elapsed_ms", "mocob200_launch_count", "mocob200_last_kernel_ms",
-    "mocob200_point_evals_per_jacobian", "mocob200_executed_evals", "mocob200_working_ranks", "mocob200_uses_warp_kernels",
+    "mocob200_point_evals_per_jacobian", "mocob200_executed_evals", "mocob200_working_ranks", "mocob200_peer_gather", "mocob200_uses_warp_kernels",
     "mocob200_measure_fp64_peak", "mocob200_shard_range", "mocob200_effective_world", "mocob200_set_min_points_per_rank", "mocob200_set_sparsity_detection",
     "mocob200_iterate_write_sto", "mocob200_iterate_read_sto",
 ]
@@ -102,6 +102,7 @@ def lib():
         L.mocob200_measure_fp64_peak.argtypes = [C.c_int, dp]
         L.mocob200_executed_evals.argtypes = [vp, C.POINTER(C.c_long)]
         L.mocob200_working_ranks.argtypes = [vp]
+        L.mocob200_peer_gather.argtypes = [vp]
         L.mocob200_uses_warp_kernels.argtypes = [vp]
         L.mocob200_iterate_write_sto.argtypes = [vp, dp, C.c_char_p]
         L.mocob200_iterate_read_sto.argtypes = [vp, C.c_char_p, dp, C.c_char_p, C.c_int]
@@ -350,6 +351,9 @@ class Evaluator:
 
     def working_ranks(self):
         return lib().mocob200_working_ranks(self._h)
+
+    def peer_gather(self):
+        return bool(lib().mocob200_peer_gather(self._h))
 
     def uses_warp_kernels(self):
         return bool(lib().mocob200_uses_warp_kernels(self._h))

@@ -124,6 +124,18 @@ struct mocob200_handle {
     cudaEvent_t evCaller = nullptr; // ordering against a caller-supplied stream (*_device entry points)
     cudaEvent_t marks[2] = {nullptr, nullptr}; // mocob200_mark stopwatch (per handle: handles may sit on different devices)
     bool ecHasIntegrand = false; // some endpoint-constraint goal has an integrand: jac_g needs dI/dt0, dI/dtf
+    // Peer-memory gather of the sharded Jacobian (one node, one process per GPU): the working ranks other than 0 map rank 0's
+    // value array, point outputs, time columns and flag words (CUDA IPC) and their assembly kernels store straight into
+    // them over NVLink - no staging copy, no collective on the data path. See peerGatherSetup / jacPipelineSharded.
+    struct PeerGather {
+        bool tried = false, on = false;
+        double *vals = nullptr, *Y = nullptr, *Jt = nullptr; // rank > 0: rank 0's buffers in this process's address space
+        unsigned long long* flags = nullptr; // rank 0: its flag words ([0] consumed, [r] done of rank r); rank > 0: their mapping
+        unsigned long long seq = 0;          // Jacobians evaluated through the peer path since the setup
+        double* d_msg = nullptr;             // setup exchange (NCCL send / recv)
+        cudaEvent_t trace[8] = {};           // MOCOB200_PEER_TRACE=1 (development): segment stopwatch of the last Jacobian
+        bool tracing = false;
+    } peer;
     double* d_I2 = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     long launches = 0;
@@ -142,6 +154,8 @@ struct mocob200_handle {
 };
 
 extern "C" long mocob200_point_evals_per_jacobian(const mocob200_handle* h);
+
+extern "C" { static void peerGatherClose(mocob200_handle* h); } // defined with the sharded pipeline
 
 namespace {
 
@@ -529,6 +543,7 @@ int mocob200_nccl_unique_id(void* id128) {
 void mocob200_destroy(mocob200_handle* h) {
     if (!h) return;
     cudaSetDevice(h->device);
+    peerGatherClose(h);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     for (void* p : h->owned) cudaFree(p);
     for (auto& e : h->ev) if (e) cudaEventDestroy(e);
@@ -862,6 +877,7 @@ int mocob200_set_sparsity_detection(mocob200_handle* h, int mode, int n_iterates
     h->owned.push_back(c); h->owned.push_back(r); h->owned.push_back(n); h->owned.push_back(v);
     h->DL.colptr = c; h->DL.rowidx = r; h->DL.nnzcol = n; h->DL.nnz = L.nnz;
     h->d_vals = v;
+    peerGatherClose(h); // the value array the other ranks had mapped is no longer the one in use: set up again at the next Jacobian
     if (h->jacGraph) { cudaGraphExecDestroy(h->jacGraph); h->jacGraph = nullptr; }
     h->x_cached.clear();
     return MOCOB200_OK;
@@ -960,6 +976,135 @@ int mocob200_eval_grad_f(mocob200_handle* h, const double* x, double* grad) {
     return MOCOB200_OK;
 }
 
+// ---- peer-memory gather -------------------------------------------------------------------------------------------------
+// Flag words live in rank 0's memory. flags[0] = s - 1 is stored by rank 0 when it STARTS Jacobian s (stream-ordered after
+// whatever consumed Jacobian s - 1): from then on the other ranks may overwrite its buffers. flags[r] = s is stored by rank r
+// after its last store of Jacobian s (a kernel boundary and a system-scope fence precede it); rank 0 waits for all of them
+// before it reads what they wrote. Waits are bounded (10 s): a rank that never arrives traps the context - loud, not a hang.
+__global__ void k_peer_signal(unsigned long long* flag, unsigned long long v) {
+    __threadfence_system();
+    *(volatile unsigned long long*)flag = v;
+    __threadfence_system();
+}
+__global__ void k_peer_wait(const unsigned long long* flags, int first, int count, unsigned long long v) {
+    const int i = threadIdx.x;
+    if (i < count) {
+        const volatile unsigned long long* f = flags + first + i;
+        unsigned long long t0, t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        while (*f < v) {
+            __nanosleep(200);
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > 10000000000ull) __trap();
+        }
+    }
+    __threadfence_system();
+}
+static void peerGatherClose(mocob200_handle* h) {
+    auto& P = h->peer;
+    if (P.tracing) { // segments of the last Jacobian on this rank
+        cudaStreamSynchronize(h->stream);
+        const char* name[6] = {"FD stage", "wait for rank 0", "pack + endpoint join + own runs", "rank 0: wait for the others / rank r: Y copy + signal", "t0 / tf columns", "D2D of the others' runs"};
+        for (int k = 0; k < 6; ++k) {
+            float ms = 0;
+            if (cudaEventElapsedTime(&ms, P.trace[k], P.trace[k + 1]) == cudaSuccess) fprintf(stderr, "[peer trace] rank %d  %-58s %.4f ms\n", h->rank, name[k], ms);
+            else cudaGetLastError();
+        }
+        for (auto& e : P.trace) cudaEventDestroy(e);
+    }
+    if (h->rank > 0) {
+        if (P.vals) cudaIpcCloseMemHandle(P.vals);
+        if (P.Y) cudaIpcCloseMemHandle(P.Y);
+        if (P.Jt) cudaIpcCloseMemHandle(P.Jt);
+        if (P.flags) cudaIpcCloseMemHandle(P.flags);
+    } else if (P.flags) cudaFree(P.flags);
+    if (P.d_msg) cudaFree(P.d_msg);
+    P = mocob200_handle::PeerGather{};
+}
+// Collective over the working ranks (rank < eff), once per handle and value array: rank 0 exports its buffers, the others map
+// them, and all agree on the outcome (if any rank cannot, every rank keeps the NCCL gather). MOCOB200_P2P=0 (development
+// switch) declines on the rank that reads it, hence on all.
+static bool peerGatherSetup(mocob200_handle* h) {
+    auto& P = h->peer;
+    P.tried = true;
+    P.on = false;
+    P.seq = 0;
+    const int MSG = 40; // doubles per message: 4 IPC handles (4 x 64 bytes = 32 doubles), [32] = the sender's verdict
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    if (!P.d_msg && cudaMalloc(&P.d_msg, sizeof(double) * MSG * (size_t)(h->world + 1)) != cudaSuccess) { cudaGetLastError(); P.d_msg = nullptr; }
+    const char* e = devEnv("MOCOB200_P2P");
+    bool mine = P.d_msg && !(e && e[0] == '0');
+    if (!P.d_msg) { h->err = "peer gather: device allocation failed"; return false; } // the exchange itself needs the buffer
+    std::vector<double> host((size_t)MSG * (h->world + 1), 0.0);
+    auto exchange = [&](bool fromZero, int count) { // rank 0 <-> every other working rank, `count` doubles of slot r (rank 0: slot 0 out)
+        if (!ncclOk(h, g_nccl.GroupStart(), "ncclGroupStart")) return false;
+        int rc = 0;
+        if (h->rank == 0) {
+            for (int r = 1; r < h->eff && rc == 0; ++r)
+                rc = fromZero ? g_nccl.Send(P.d_msg, (size_t)count, kNcclDouble, r, h->comm, h->stream)
+                              : g_nccl.Recv(P.d_msg + (size_t)MSG * r, (size_t)count, kNcclDouble, r, h->comm, h->stream);
+        } else {
+            rc = fromZero ? g_nccl.Recv(P.d_msg, (size_t)count, kNcclDouble, 0, h->comm, h->stream)
+                          : g_nccl.Send(P.d_msg + (size_t)MSG * h->rank, (size_t)count, kNcclDouble, 0, h->comm, h->stream);
+        }
+        const int rcEnd = g_nccl.GroupEnd();
+        return ncclOk(h, rc, "ncclSend/ncclRecv(peer setup)") && ncclOk(h, rcEnd, "ncclGroupEnd") &&
+               h->ck(cudaStreamSynchronize(h->stream), "peer setup sync");
+    };
+    // 1. rank 0 -> all: handles of d_vals, d_Y, d_Jt, flags
+    if (h->rank == 0) {
+        if (mine && !P.flags) {
+            if (cudaMalloc(&P.flags, 64 * sizeof(unsigned long long)) != cudaSuccess) { cudaGetLastError(); P.flags = nullptr; mine = false; }
+        }
+        if (P.flags) cudaMemsetAsync(P.flags, 0, 64 * sizeof(unsigned long long), h->stream);
+        cudaIpcMemHandle_t hd[4];
+        void* ptrs[4] = {h->d_vals, h->d_Y, h->d_Jt, P.flags};
+        for (int k = 0; k < 4 && mine; ++k)
+            if (!ptrs[k] || cudaIpcGetMemHandle(&hd[k], ptrs[k]) != cudaSuccess) { cudaGetLastError(); mine = false; }
+        if (mine) std::memcpy(host.data(), hd, sizeof hd);
+        host[32] = mine ? 1.0 : 0.0;
+        if (!h->ck(cudaMemcpyAsync(P.d_msg, host.data(), sizeof(double) * MSG, cudaMemcpyHostToDevice, h->stream), "peer setup H2D")) return false;
+    }
+    if (!exchange(true, MSG)) return false;
+    // 2. the others map them and report
+    if (h->rank > 0) {
+        if (!h->ck(cudaMemcpy(host.data(), P.d_msg, sizeof(double) * MSG, cudaMemcpyDeviceToHost), "peer setup D2H")) return false;
+        mine = mine && host[32] == 1.0;
+        if (mine) {
+            cudaIpcMemHandle_t hd[4];
+            std::memcpy(hd, host.data(), sizeof hd);
+            void* ptrs[4] = {nullptr, nullptr, nullptr, nullptr};
+            for (int k = 0; k < 4 && mine; ++k)
+                if (cudaIpcOpenMemHandle(&ptrs[k], hd[k], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ptrs[k] = nullptr; mine = false; }
+            P.vals = (double*)ptrs[0]; P.Y = (double*)ptrs[1]; P.Jt = (double*)ptrs[2]; P.flags = (unsigned long long*)ptrs[3];
+        }
+        host[(size_t)MSG * h->rank] = mine ? 1.0 : 0.0;
+        if (!h->ck(cudaMemcpy(P.d_msg + (size_t)MSG * h->rank, host.data() + (size_t)MSG * h->rank, sizeof(double), cudaMemcpyHostToDevice), "peer setup H2D")) return false;
+    }
+    if (!exchange(false, 1)) return false;
+    // 3. rank 0 -> all: the common verdict
+    if (h->rank == 0) {
+        if (!h->ck(cudaMemcpy(host.data(), P.d_msg, sizeof(double) * MSG * (size_t)h->world, cudaMemcpyDeviceToHost), "peer setup D2H")) return false;
+        for (int r = 1; r < h->eff; ++r) mine = mine && host[(size_t)MSG * r] == 1.0;
+        host[0] = mine ? 1.0 : 0.0;
+        if (!h->ck(cudaMemcpy(P.d_msg, host.data(), sizeof(double), cudaMemcpyHostToDevice), "peer setup H2D")) return false;
+    }
+    if (!exchange(true, 1)) return false;
+    if (h->rank > 0) {
+        if (!h->ck(cudaMemcpy(host.data(), P.d_msg, sizeof(double), cudaMemcpyDeviceToHost), "peer setup D2H")) return false;
+        mine = host[0] == 1.0;
+    }
+    P.on = mine;
+    if (!P.on && h->rank > 0) { // leave nothing mapped
+        if (P.vals) cudaIpcCloseMemHandle(P.vals);
+        if (P.Y) cudaIpcCloseMemHandle(P.Y);
+        if (P.Jt) cudaIpcCloseMemHandle(P.Jt);
+        if (P.flags) cudaIpcCloseMemHandle(P.flags);
+        P.vals = P.Y = P.Jt = nullptr; P.flags = nullptr;
+    }
+    return true;
+}
+
 // Sharded Jacobian (eff > 1). Every working rank differences its own grid points and assembles the CSC entries of
 // the columns that belong to them — a column's entries need the FD block of the column's own grid point only, and CasADi's
 // column order (CasOCTranscription.h:192-199: states of all points, controls, derivatives) makes them three contiguous runs of
@@ -979,22 +1124,65 @@ static bool jacPipelineSharded(mocob200_handle* h, double* d_vals) {
         cudaEventRecord(h->evE, h->stream2);
         h->launches++;
     }
+    if (!h->peer.tried && !peerGatherSetup(h)) return false;
+    const bool peer = h->peer.on;
+    if (peer && !h->peer.tracing && devEnv("MOCOB200_PEER_TRACE")) {
+        for (auto& e : h->peer.trace) cudaEventCreate(&e);
+        h->peer.tracing = true;
+    }
+    auto trace = [&](int k) { if (h->peer.tracing) cudaEventRecord(h->peer.trace[k], h->stream); };
+    trace(0);
+    const size_t no = (size_t)L.n_out;
+    const int np = h->p1 - h->p0;
+    if (peer) { // rank 0 releases its buffers to the writers of this Jacobian (see k_peer_signal)
+        h->peer.seq++;
+        if (h->rank == 0) { k_peer_signal<<<1, 1, 0, h->stream>>>(h->peer.flags, h->peer.seq - 1); h->launches++; }
+    }
     launchFdKernels(h, nullptr);
     recTiming(h->ev[1], h->stream);
-    const int np = h->p1 - h->p0;
-    launch_pack_time_column(h->DL, h->d_J, h->d_Jt, h->p0, np, h->stream);
+    trace(1);
+    if (peer && h->rank > 0) { // from here on this rank stores into rank 0's memory
+        k_peer_wait<<<1, 32, 0, h->stream>>>(h->peer.flags, 0, 1, h->peer.seq - 1);
+        h->launches++;
+    }
+    trace(2);
+    launch_pack_time_column(h->DL, h->d_J, peer && h->rank > 0 ? h->peer.Jt : h->d_Jt, h->p0, np, h->stream);
     h->launches++;
     if (h->DL.n_eout_total > 0) cudaStreamWaitEvent(h->stream, h->evE, 0);
     recTiming(h->ev[2], h->stream);
-    double* mine = h->rank == 0 ? d_vals : h->d_vals;
+    // with the peer path the other ranks' runs land in rank 0's own value array (the one they have mapped)
+    double* mine = h->rank == 0 ? d_vals : (peer ? h->peer.vals : h->d_vals);
     for (int k = 0; k < 3; ++k) {
         const int k0 = h->runs[6 * h->rank + 2 * k], k1 = h->runs[6 * h->rank + 2 * k + 1];
         if (k1 > k0) { launch_assemble_jac(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_I, h->d_E, mine, h->stream, k0, k1); h->launches += 1 + (h->DL.n_path_rows > 0); }
     }
+    trace(3);
+    if (peer) {
+        if (h->rank > 0) {
+            if (np > 0 && !h->ck(cudaMemcpyAsync(h->peer.Y + (size_t)h->p0 * no, h->d_Y + (size_t)h->p0 * no, sizeof(double) * np * no,
+                                                 cudaMemcpyDeviceToDevice, h->stream), "point outputs to rank 0")) return false;
+            k_peer_signal<<<1, 1, 0, h->stream>>>(h->peer.flags + h->rank, h->peer.seq);
+            h->launches++;
+        } else {
+            k_peer_wait<<<1, 32, 0, h->stream>>>(h->peer.flags, 1, h->eff - 1, h->peer.seq);
+            trace(4);
+            launch_assemble_jac(h->DT, h->DLt, h->fd, h->d_x, h->d_Y, h->d_J, h->d_I, h->d_E, d_vals, h->stream, 0, L.colptr[2]);
+            trace(5);
+            h->launches += 2 + (h->DL.n_path_rows > 0);
+            if (d_vals != h->d_vals) // a caller-supplied destination: the other ranks' runs (adjacent within each block) follow
+                for (int k = 0; k < 3; ++k) {
+                    const int k0 = h->runs[6 * 1 + 2 * k], k1 = h->runs[6 * (h->eff - 1) + 2 * k + 1];
+                    if (k1 > k0 && !h->ck(cudaMemcpyAsync(d_vals + k0, h->d_vals + k0, sizeof(double) * (size_t)(k1 - k0),
+                                                          cudaMemcpyDeviceToDevice, h->stream), "D2D values")) return false;
+                }
+        }
+        trace(6);
+        recTiming(h->ev[3], h->stream);
+        return h->ck(cudaGetLastError(), "peer gather launches");
+    }
     // one NCCL group: point outputs + time columns + value runs to rank 0
     if (!ncclOk(h, g_nccl.GroupStart(), "ncclGroupStart")) return false;
     int rc = 0;
-    const size_t no = (size_t)L.n_out;
     if (h->rank == 0) {
         for (int r = 1; r < h->eff && rc == 0; ++r) {
             const size_t a = h->shard[r], n = (size_t)(h->shard[r + 1] - h->shard[r]) * no;
@@ -1224,6 +1412,7 @@ int mocob200_executed_evals(const mocob200_handle* h, long out[4]) {
     return MOCOB200_OK;
 }
 int mocob200_working_ranks(const mocob200_handle* h) { return h ? h->eff : 0; }
+int mocob200_peer_gather(const mocob200_handle* h) { return h && h->peer.on ? 1 : 0; }
 int mocob200_uses_warp_kernels(const mocob200_handle* h) {
     return h && h->warpFor(mocob200_point_evals_per_jacobian(h) / h->eff) ? 1 : 0;
 }
