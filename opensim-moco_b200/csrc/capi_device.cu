@@ -343,6 +343,8 @@ bool buildWarpAux(mocob200_handle* h, const mocob200_tables& T, std::string& err
     A.o_pf = take(3 * nppx); A.o_dp = take(3 * A.nmpp);
     // right-hand sides / solutions of the local columns: reuse the wrench + composite-inertia scratch, dead by then
     A.o_Rm = ((T.nmus + T.ncact) * nq <= A.o_tau - A.o_F) ? A.o_F : take((T.nmus + T.ncact) * nq);
+    A.n_lparts = std::max(1, (T.nmus + T.ncact + 31) / 32);
+    { const char* e = devEnv("MOCOB200_LOCAL_PARTS"); if (e && atoi(e) > 0) A.n_lparts = std::min(A.n_lparts, atoi(e)); }
     A.ws_doubles = o;
     { const char* e = devEnv("MOCOB200_POISON_SCRATCH"); A.poison = (e && e[0] == '1') ? 1 : 0; }
     return warp_kernels_configure(A, err);
@@ -1387,7 +1389,7 @@ long mocob200_point_evals_per_jacobian(const mocob200_handle* h) {
 
 // Evaluations of the point function that one eval_jac_g launches on all ranks together, by kind:
 // out[0] whole evaluations, out[1] evaluations that reload the nominal poses (speeds, implicit-mode accelerations),
-// out[2] evaluations that reload poses and velocities (time, unclassified inputs), out[3] local-column warps (one per grid point).
+// out[2] evaluations that reload poses and velocities (time, unclassified inputs), out[3] local-column warps (per grid point: one for central differences, one per 32 owners of local inputs otherwise).
 int mocob200_executed_evals(const mocob200_handle* h, long out[4]) {
     if (!h || !out) return MOCOB200_ERR_ARG;
     const Layout& L = h->L;
@@ -1401,7 +1403,7 @@ int mocob200_executed_evals(const mocob200_handle* h, long out[4]) {
         out[0] = N * (1 + per * A.n_p0);
         out[1] = N * per * A.n_p1;
         out[2] = N * per * A.n_p2;
-        out[3] = A.n_local > 0 ? N : 0;
+        out[3] = A.n_local > 0 ? N * A.n_lparts : 0;
     } else if (A.n_local > 0 && h->side.s[0]) {
         if (h->velKernel && A.n_p1 > 0 && h->side.s[1]) { out[0] = N * (1 + per * A.n_cw); out[1] = N * per * A.n_p1; }
         else out[0] = N * (1 + per * A.n_cd); // the thread kernels evaluate every non-local direction whole

@@ -128,7 +128,8 @@ __global__ void k_wpoints_nominal(DevTables Tg, WarpAux Ag, DevLayout L, const d
 //           coordinate p0_dirs[k-1] (a full evaluation);
 //   KIND 1  item = point * n_p1 + t perturbs p1_dirs[t] (speeds, implicit-mode accelerations): reloads the poses;
 //   KIND 2  item = point * n_p2 + t perturbs p2_dirs[t] (time, unclassified inputs): reloads poses and velocities;
-//   KIND 3  item = point: the columns of all "local" inputs (point_warp_local.cuh) from the reloaded blob.
+//   KIND 3  item = point * n_lparts + part: the columns of the "local" inputs (point_warp_local.cuh) of 32 owners
+//           (muscles, coordinate actuators) from the reloaded blob.
 // KIND 1-3 run side by side once KIND 0 is done and write finished difference quotients. The coordinate evaluations of
 // KIND 0 run beside the nominal one, so they leave their RAW outputs in J[j][o][dir]; the first KIND 2 item of each grid
 // point (or k_fd1_finalize when there is none) turns those columns into quotients.
@@ -141,7 +142,7 @@ __global__ void k_wpoints_fd1(DevTables Tg, WarpAux Ag, DevLayout L, FdSettings 
     double* scratch = stage_tables(Tg, Ag, smem, T, A);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long item = (long)blockIdx.x * (blockDim.x >> 5) + warp;
-    const int per = KIND == 0 ? 1 + A.n_p0 : KIND == 1 ? A.n_p1 : KIND == 2 ? A.n_p2 : 1;
+    const int per = KIND == 0 ? 1 + A.n_p0 : KIND == 1 ? A.n_p1 : KIND == 2 ? A.n_p2 : A.n_lparts;
     if (item >= (long)np * per) return;
     double* ws = scratch + (size_t)warp * A.ws_doubles;
     const int j = p0 + (int)(item / per), t = (int)(item % per);
@@ -155,7 +156,7 @@ __global__ void k_wpoints_fd1(DevTables Tg, WarpAux Ag, DevLayout L, FdSettings 
     warp_gather_inputs(L, x, j, ws + A.o_in, lane);
     if (KIND == 3) {
         blob_load(A, ws, cfg, j, lane, 2);
-        wk_local_columns(T, A, ws, ws + A.o_Rm, fd.h, fd.scheme == MOCOB200_FD_FORWARD, Jp, Y + (size_t)j * L.n_out, L.n_in, L.n_out);
+        wk_local_columns(T, A, ws, ws + A.o_Rm, fd.h, fd.scheme == MOCOB200_FD_FORWARD, Jp, Y + (size_t)j * L.n_out, L.n_in, L.n_out, t, per);
         return;
     }
     const int dir = KIND == 0 ? (t == 0 ? -1 : A.p0_dirs[t - 1]) : KIND == 1 ? A.p1_dirs[t] : A.p2_dirs[t];
@@ -382,7 +383,7 @@ int launch_wpoints_fd(const DevTables& T, const WarpAux& A, const DevLayout& L, 
             ++launched;
         }
         if (A.n_local > 0) {
-            k_wpoints_fd1<3><<<(unsigned)((np + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s3>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
+            k_wpoints_fd1<3><<<(unsigned)(((long)np * A.n_lparts + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s3>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
             ++launched;
         }
         if (fork) {
@@ -429,7 +430,7 @@ int launch_wlocal(const DevTables& T, const WarpAux& A, const DevLayout& L, cons
     if (fd.scheme == MOCOB200_FD_CENTRAL)
         k_wlocal_central<<<(np + A.wpb - 1) / A.wpb, A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
     else
-        k_wpoints_fd1<3><<<(np + A.wpb - 1) / A.wpb, A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
+        k_wpoints_fd1<3><<<(unsigned)(((long)np * A.n_lparts + A.wpb - 1) / A.wpb), A.wpb * 32, warpSmemBytes(A), s>>>(T, A, L, fd, d_x, d_Y, d_J, d_cfg, p0, np);
     return 1;
 }
 

@@ -52,6 +52,7 @@ struct WarpAux {
     const int* loc_dir; const int* loc_kind; const int* loc_owner; const int* loc_role;
     const int* dir_class;
     int o_mlen, o_mspd, o_mout, o_Rm;
+    int n_lparts; // one-sided local columns: warps per grid point, each taking the columns of 32 owners (muscles, actuators)
     int o_cjs; // per custom joint (position-dependent): 6 axis vectors in ground (18), df[6], d2f[6]
     int lockstep;
     int o_pk; // prescribed kinematics: q, u, udot at the point's time

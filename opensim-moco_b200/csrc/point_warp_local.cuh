@@ -161,13 +161,15 @@ __device__ inline LocalMuscleEval wk_local_muscle(const DevTables& T, const Warp
     return r;
 }
 
-// right-hand sides of the local columns: M^-1 R_m (explicit) or R_m (implicit) per muscle, then per coordinate actuator
-__device__ inline void wk_local_rhs(const WarpCtx& C, double* Rm) {
+// right-hand sides of the local columns: M^-1 R_m (explicit) or R_m (implicit) per muscle, then per coordinate actuator.
+// base < 0: all owners, owner r at Rm + r nq; base >= 0: the 32 owners from `base` on, owner r at Rm + (r - base) nq.
+__device__ inline void wk_local_rhs(const WarpCtx& C, double* Rm, int base = -1) {
     const DevTables& T = C.T;
     const WarpAux& A = C.A;
     const int nq = T.nq;
-    for (int r = C.lane; r < T.nmus + T.ncact; r += 32) {
-        double* x = Rm + r * nq;
+    const int r0 = base < 0 ? 0 : base, r1 = base < 0 ? T.nmus + T.ncact : min(T.nmus + T.ncact, base + 32);
+    for (int r = r0 + C.lane; r < r1; r += 32) {
+        double* x = Rm + (r - r0) * nq;
         if (r < T.nmus) wk_unit_tension_force(C, r, x);
         else {
             const int a = r - T.nmus;
@@ -281,22 +283,30 @@ __device__ inline void wk_local_columns_central(const DevTables& T, const WarpAu
     __syncwarp();
 }
 
-// The columns J[:, dir] of every "local" input of one grid point (whole warp; the scratch holds the nominal
-// evaluation or its reloaded blob, y0 its outputs, Rm is (nmus + ncact) * nq doubles of scratch that the evaluation no longer needs).
+// The columns J[:, dir] of the "local" inputs of one grid point that belong to this warp's owners (whole warp; the scratch
+// holds the reloaded blob of the nominal evaluation, y0 its outputs, Rm is scratch the evaluation no longer needs). The
+// owners (muscles, then coordinate actuators) are dealt to the `nparts` warps of the grid point in chunks of 32: a warp
+// forms the right-hand sides of its chunk, one owner per lane, and then the columns whose owner is in the chunk, one column
+// per lane. On a full-body model (107 owners, 176 local inputs) that is one right-hand-side pass and two column passes per
+// warp instead of four and six in a row.
 __device__ inline void wk_local_columns(const DevTables& T, const WarpAux& A, double* ws, double* Rm, double h, bool forward,
-                                        double* __restrict__ Jp, const double* __restrict__ y0, int n_in, int n_out) {
+                                        double* __restrict__ Jp, const double* __restrict__ y0, int n_in, int n_out, int part, int nparts) {
     const WarpCtx C{T, A, ws, (int)(threadIdx.x & 31)};
     const int lane = C.lane, nq = T.nq, nz = T.nz;
     const double* in = ws + A.o_in;
-    wk_local_rhs(C, Rm);
     const double step = forward ? h : -h;
+    const int nown = T.nmus + T.ncact;
+    for (int base = part * 32; base < nown; base += 32 * nparts) {
+    wk_local_rhs(C, Rm, base);
     for (int t = lane; t < A.n_local; t += 32) {
         const int dir = A.loc_dir[t], kind = A.loc_kind[t], owner = A.loc_owner[t], role = A.loc_role[t];
+        const int row = (kind == MOCOB200_LOCAL_MUSCLE ? owner : T.nmus + owner) - base;
+        if (row < 0 || row >= 32) continue;
         const double v0 = in[dir], v1 = v0 + step;
         const double inv = forward ? 1.0 / h : -1.0 / h; // (f(x+h) - f(x)) / h or (f(x) - f(x-h)) / h
         double* col = Jp + dir;
         for (int o = 0; o < n_out; ++o) col[(size_t)o * n_in] = 0.0;
-        const double* c = Rm + (kind == MOCOB200_LOCAL_MUSCLE ? owner : T.nmus + owner) * nq;
+        const double* c = Rm + row * nq;
         if (kind == MOCOB200_LOCAL_ACTUATOR) {
             // force = optimal_force * control (CoordinateActuator.cpp:185-204): c already carries optimal_force
             const double dctl = (v1 - v0) * inv;
@@ -325,6 +335,7 @@ __device__ inline void wk_local_columns(const DevTables& T, const WarpAux& A, do
             if (!isfinite(y0[o])) col[(size_t)o * n_in] = NAN;
     }
     __syncwarp();
+    }
 }
 
 } // namespace mocob200
