@@ -452,6 +452,78 @@ std::unique_ptr<FlatProblem> doublePendulumCoupler(const std::string& options) {
     return flatten(P, S);
 }
 
+// A three-link leg whose middle joint is a function-based joint driven by ONE coordinate, shaped like the knee of the
+// full-body models (primary rotation linear in the coordinate, two secondary rotations and two translations SimmSplines of
+// it): small enough for the thread-per-evaluation kernels, so that the one-coordinate case of the joint's velocity-product
+// term (point_eval.cuh: custom_joint_bias) is exercised on both kernel families. Torque-driven, effort goal.
+std::unique_ptr<FlatProblem> kneeChain(const std::string& options) {
+    Problem P;
+    ModelSpec& M = P.model;
+    M.name = "knee_chain";
+    const double mass[3] = {8.0, 3.5, 1.2}, len[3] = {0.42, 0.40, 0.15};
+    for (int i = 0; i < 3; ++i) {
+        const std::string is = std::to_string(i);
+        BodySpec b;
+        b.name = "seg" + is;
+        b.mass = mass[i];
+        b.com = Vec3{0.01 * (i + 1), -0.45 * len[i], 0.005 * (2 - i)};
+        b.inertiaCom[0] = 0.08 * mass[i] * len[i] * len[i] + 0.001;
+        b.inertiaCom[1] = 0.02 * mass[i] * len[i] * len[i] + 0.0005;
+        b.inertiaCom[2] = 0.085 * mass[i] * len[i] * len[i] + 0.001;
+        b.inertiaCom[3] = 0.0004 * (i + 1); // products of inertia: a general tensor
+        b.inertiaCom[4] = -0.0003;
+        b.inertiaCom[5] = 0.0002 * (i + 1);
+        M.bodies.push_back(b);
+        JointSpec j;
+        j.name = "j" + is;
+        j.parent.body = i - 1;
+        j.child.body = i;
+        if (i > 0) j.parent.X.p.v[1] = -len[i - 1];
+        j.coords.push_back({"q" + is, -3, 3});
+        if (i == 1) {
+            j.kind = MOCOB200_JOINT_CUSTOM;
+            const double xs[7] = {0, 0.35, 0.70, 1.05, 1.40, 1.75, 2.10};
+            const double r2[7] = {0, 0.0227, 0.0332, 0.0309, 0.0189, 0.0044, -0.0017};
+            const double r3[7] = {0, -0.1094, -0.1839, -0.2300, -0.2540, -0.2624, -0.2617};
+            const double t1[7] = {0, 0.000835, 0.001251, 0.001391, 0.0014, 0.001421, 0.001599};
+            const double t2[7] = {0, -0.001899, -0.003492, -0.004777, -0.005756, -0.006427, -0.006792};
+            auto spline = [&](TransformAxisSpec& a, const double* y, double scale) {
+                a.fnKind = MOCOB200_FN_SIMMSPLINE;
+                a.spline.x.assign(xs, xs + 7);
+                a.spline.y.assign(y, y + 7);
+                a.spline.scale = scale;
+                a.coord = "q1";
+            };
+            j.axes[0].axis = Vec3{1, 0, 0}; j.axes[0].fnKind = MOCOB200_FN_LINEAR; j.axes[0].c0 = 1; j.axes[0].coord = "q1";
+            j.axes[1].axis = Vec3{0, 0, 1}; spline(j.axes[1], r2, 1.0);
+            j.axes[2].axis = Vec3{0, 1, 0}; spline(j.axes[2], r3, 1.0);
+            j.axes[3].axis = Vec3{0, 1, 0}; spline(j.axes[3], t1, 1.1);
+            j.axes[4].axis = Vec3{0, 0, 1}; spline(j.axes[4], t2, 1.1);
+            j.axes[5].axis = Vec3{1, 0, 0}; // constant 0
+        } else j.kind = MOCOB200_JOINT_PIN;
+        M.joints.push_back(j);
+        CoordActSpec a;
+        a.path = "/tau" + is;
+        a.coord = "q" + is;
+        a.optimalForce = 20;
+        M.coordActs.push_back(a);
+        M.actuatorOrder.emplace_back(0, i);
+    }
+    P.setTimeBounds(Bounds(0), Bounds(0.6));
+    const double q0[3] = {0.3, 0.2, -0.1}, q1[3] = {-0.4, 1.3, 0.3};
+    for (int i = 0; i < 3; ++i) {
+        const std::string is = std::to_string(i), base = "/jointset/j" + is + "/q" + is;
+        P.setStateInfo(base + "/value", Bounds(-2.5, 2.5), Bounds(q0[i]), Bounds(q1[i]));
+        P.setStateInfo(base + "/speed", Bounds(-20, 20), Bounds(0), Bounds());
+        P.setControlInfo("/tau" + is, Bounds(-5, 5));
+    }
+    P.addGoal(MOCOB200_GOAL_CONTROL, "effort");
+    SolverSettings S;
+    S.num_mesh_intervals = 12;
+    S.applyOptions(options);
+    return flatten(P, S);
+}
+
 // Replay model for the reference-held CMC / ID results of opensim-models/Pipelines/Gait10dof18musc/OutputReference
 // (CMC/walk_Setup_CMC.xml): CMC/subject01_metabolics.osim - the variant of subject01.osim (document Version 30000, CustomJoint
 // pelvis and knees; its gluteus maximus path differs) whose path speeds reproduce ResultsCMC/walk_subject_Actuation_speed.sto
@@ -740,6 +812,7 @@ std::unique_ptr<FlatProblem> buildExample(const std::string& name, const std::st
     if (name == "gait2d_inverse_free") return gaitInverse(dataDir, options, false);
     if (name == "planar_point_mass_coupler") return planarPointMassCoupler(options);
     if (name == "double_pendulum_coupler") return doublePendulumCoupler(options);
+    if (name == "knee_chain") return kneeChain(options);
     throw std::runtime_error("unknown example '" + name + "'");
 }
 

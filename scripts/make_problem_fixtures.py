@@ -34,6 +34,9 @@ CASES = {
     "gait2d_inverse": ("gait2d_inverse", None),
     "gait2d_inverse_free": ("gait2d_inverse_free", None),
     "gait2d_inverse_trap_central": ("gait2d_inverse", "transcription_scheme=trapezoidal;num_mesh_intervals=12;optim_finite_difference_scheme=central"),
+    # three-link leg with a knee-like function-based joint (one coordinate, spline secondary rotations and translations)
+    "knee_chain": ("knee_chain", None),
+    "knee_chain_implicit_trap": ("knee_chain", "multibody_dynamics_mode=implicit;transcription_scheme=trapezoidal;optim_finite_difference_scheme=central"),
     "gait2d_tracking": ("gait2d_tracking", None),
     "gait2d_prediction": ("gait2d_prediction", None),
 }

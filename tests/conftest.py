@@ -44,4 +44,7 @@ FIXTURES = ["sliding_mass", "sliding_mass_trap", "hanging_muscle", "hanging_musc
             # kinematic constraints: multipliers, slacks, velocity correction
             "point_mass_coupler", "point_mass_coupler_implicit", "double_pendulum_coupler", "double_pendulum_coupler_noderiv_trap",
             # prescribed kinematics (PositionMotion, MocoInverse on the 2D gait model) and its free-coordinate twin
-            "gait2d_inverse", "gait2d_inverse_trap_central", "gait2d_inverse_free"]
+            "gait2d_inverse", "gait2d_inverse_trap_central", "gait2d_inverse_free",
+            # function-based joint driven by one coordinate (the knee of the full-body models) on a model small enough for both
+            # kernel families: the reference's velocity-product term of that case (tests/test_reference_dynamics_pins.py)
+            "knee_chain", "knee_chain_implicit_trap"]

@@ -163,6 +163,8 @@ def test_local_columns_central_scheme(pkg, name, kernel, monkeypatch):
     whole-function central differences, fixed step (no refinement) so that both use the same h."""
     monkeypatch.setenv("MOCOB200_KERNEL", kernel)
     p = load(pkg, name)
+    if kernel == "thread" and p.table_sizes().ncustom > 0:
+        pytest.skip("function-based joints run on the warp kernels only (the library refuses the forced thread mode)")
     x = p.make_iterate(seed=10, spread=0.4)
     ev = pkg.Evaluator(p)
     ev.set_fd(FD_CENTRAL, 1e-3, 0)
