@@ -219,9 +219,11 @@ int mocob200_layout_structure(const mocob200_tables*, const mocob200_transcripti
 int mocob200_make_iterate(const mocob200_tables*, const mocob200_transcription*, long seed, double spread, double* x);
 
 /* Guesses and solutions as MocoTrajectory tables (.sto; Moco/Moco/MocoTrajectory.cpp:610-860, setGuessFile of
- * MocoCasADiSolver.h:162-202): write = one row per grid point, columns time | states | controls | derivatives with the num_*
- * metadata; read = columns matched by name and resampled onto this problem's grid with the interpolating spline
- * MocoTrajectory::resample uses (degree min(rows-1, 5)); t0/tf from the first/last row. Host only; the problem must carry
+ * MocoCasADiSolver.h:162-202): write = one row per grid point, columns time | states | controls | multipliers | derivatives |
+ * slacks with the num_* metadata (MocoTrajectory.cpp:793-829; the midpoint-only slacks stretched over the grid times as
+ * MocoCasOCProblem.h:170-185 does); read = columns matched by name and resampled onto this problem's grid with the interpolating spline
+ * MocoTrajectory::resample uses (degree min(rows-1, 5)); t0/tf from the first/last row; slack columns keep their midpoint
+ * entries (CasOCTranscription.cpp:601-618). Host only; the problem must carry
  * variable names (created from a model, not loaded from a .mb20 file). */
 int mocob200_iterate_write_sto(const mocob200_problem*, const double* x, const char* path);
 int mocob200_iterate_read_sto(const mocob200_problem*, const char* path, double* x, char* err, int errlen);

@@ -149,6 +149,9 @@ std::vector<std::string> derivativeNamesOf(const FlatProblem& fp) {
 
 // MocoTrajectory::write (MocoTrajectory.cpp:780-860): one row per grid point, columns time | states | controls |
 // [multipliers: none] | derivatives | [slacks, parameters: none], metadata num_* in the header.
+// index of grid point j among the interval midpoints of a Hermite-Simpson grid (-1: a mesh point)
+static int hsMid(const Layout& L, int j) { return (L.n_grid != L.n_mesh && j % 2 == 1) ? j / 2 : -1; }
+
 int mocob200_iterate_write_sto(const mocob200_problem* p, const double* x, const char* path) {
     if (!p || !x || !path) return MOCOB200_ERR_ARG;
     const FlatProblem& fp = *p->fp;
@@ -159,17 +162,34 @@ int mocob200_iterate_write_sto(const mocob200_problem* p, const double* x, const
         if ((int)dn.size() != L.nd) return MOCOB200_ERR_UNSUPPORTED;
         FILE* f = std::fopen(path, "w");
         if (!f) return MOCOB200_ERR_IO;
-        std::fprintf(f, "inDegrees=no\nnum_controls=%d\nnum_derivatives=%d\nnum_multipliers=0\nnum_parameters=0\nnum_slacks=0\n"
-                        "num_states=%d\nDataType=double\nversion=3\nOpenSimVersion=mocob200\nendheader\ntime", L.nc, L.nd, L.ns);
+        if ((int)fp.multiplierNames.size() != L.nm || (L.nsl && (int)fp.slackNames.size() != L.nsl)) { std::fclose(f); return MOCOB200_ERR_UNSUPPORTED; }
+        // column order of MocoTrajectory::convertToTable (MocoTrajectory.cpp:793-829): states, controls, multipliers, derivatives, slacks
+        std::fprintf(f, "inDegrees=no\nnum_controls=%d\nnum_derivatives=%d\nnum_multipliers=%d\nnum_parameters=0\nnum_slacks=%d\n"
+                        "num_states=%d\nDataType=double\nversion=3\nOpenSimVersion=mocob200\nendheader\ntime", L.nc, L.nd, L.nm, L.nsl, L.ns);
         for (auto& n : fp.stateNames) std::fprintf(f, "\t%s", n.c_str());
         for (auto& n : fp.controlNames) std::fprintf(f, "\t%s", n.c_str());
+        for (int k = 0; k < L.nm; ++k) std::fprintf(f, "\t%s", fp.multiplierNames[k].c_str());
         for (auto& n : dn) std::fprintf(f, "\t%s", n.c_str());
+        for (int k = 0; k < L.nsl; ++k) std::fprintf(f, "\t%s", fp.slackNames[k].c_str());
         std::fprintf(f, "\n");
+        // Slacks live on the interval midpoints only; the reference stretches those values over linspace(t0, tf) and
+        // interpolates them piecewise-linearly onto every grid time (MocoCasOCProblem.h:170-185, MocoUtilities.cpp:104-141).
+        const int nInt = L.n_grid - L.n_mesh;
+        auto slackAt = [&](int k, int j) {
+            if (nInt == 1) return j == 0 ? x[L.off_slacks + k] : std::nan("");
+            const double u = L.grid[j] * (nInt - 1);
+            int i = (int)std::floor(u);
+            if (i >= nInt - 1) i = nInt - 2;
+            const double w = u - i;
+            return (1.0 - w) * x[L.off_slacks + (size_t)i * L.nsl + k] + w * x[L.off_slacks + (size_t)(i + 1) * L.nsl + k];
+        };
         for (int j = 0; j < L.n_grid; ++j) {
             std::fprintf(f, "%.17g", x[0] + (x[1] - x[0]) * L.grid[j]);
             for (int k = 0; k < L.ns; ++k) std::fprintf(f, "\t%.17g", x[L.off_states + (size_t)j * L.ns + k]);
             for (int k = 0; k < L.nc; ++k) std::fprintf(f, "\t%.17g", x[L.off_controls + (size_t)j * L.nc + k]);
+            for (int k = 0; k < L.nm; ++k) std::fprintf(f, "\t%.17g", x[L.off_mult + (size_t)j * L.nm + k]);
             for (int k = 0; k < L.nd; ++k) std::fprintf(f, "\t%.17g", x[L.off_derivs + (size_t)j * L.nd + k]);
+            for (int k = 0; k < L.nsl; ++k) std::fprintf(f, "\t%.17g", slackAt(k, j));
             std::fprintf(f, "\n");
         }
         std::fclose(f);
@@ -194,6 +214,11 @@ int mocob200_iterate_read_sto(const mocob200_problem* p, const char* path, doubl
         names.insert(names.end(), fp.controlNames.begin(), fp.controlNames.end());
         const std::vector<std::string> dn = derivativeNamesOf(fp);
         names.insert(names.end(), dn.begin(), dn.end());
+        if ((int)fp.multiplierNames.size() != L.nm || (L.nsl && (int)fp.slackNames.size() != L.nsl))
+            throw std::runtime_error("the problem carries no multiplier / slack names");
+        const int kMult = L.ns + L.nc + L.nd, kSlack = kMult + L.nm; // appended after the round-1 blocks
+        names.insert(names.end(), fp.multiplierNames.begin(), fp.multiplierNames.begin() + L.nm);
+        names.insert(names.end(), fp.slackNames.begin(), fp.slackNames.begin() + L.nsl);
         std::vector<int> col(names.size());
         for (size_t k = 0; k < names.size(); ++k) {
             col[k] = t.col(names[k]);
@@ -223,7 +248,10 @@ int mocob200_iterate_read_sto(const mocob200_problem* p, const char* path, doubl
                 const int kk = (int)k;
                 if (kk < L.ns) x[L.off_states + (size_t)j * L.ns + kk] = v;
                 else if (kk < L.ns + L.nc) x[L.off_controls + (size_t)j * L.nc + (kk - L.ns)] = v;
-                else x[L.off_derivs + (size_t)j * L.nd + (kk - L.ns - L.nc)] = v;
+                else if (kk < kMult) x[L.off_derivs + (size_t)j * L.nd + (kk - L.ns - L.nc)] = v;
+                else if (kk < kSlack) x[L.off_mult + (size_t)j * L.nm + (kk - kMult)] = v;
+                else if (hsMid(L, j) >= 0) // a slack column given on every grid time keeps its midpoint entries (CasOCTranscription.cpp:601-618)
+                    x[L.off_slacks + (size_t)hsMid(L, j) * L.nsl + (kk - kSlack)] = std::isnan(v) ? 0.0 : v;
             }
         }
         return MOCOB200_OK;

@@ -114,3 +114,46 @@ def test_incompatible_or_nameless_guesses_are_refused(pkg, tmp_path):
         loaded.read_sto(golden("moco_trajectory_head.sto"))
     with pytest.raises(RuntimeError):
         p.read_sto(os.path.join(str(tmp_path), "does_not_exist.sto"))
+
+
+def test_multiplier_and_slack_columns(pkg, tmp_path):
+    """Kinematic constraints: the table carries the multipliers (one row per grid time) between the controls and the
+    derivatives and the velocity-correction slacks last (MocoTrajectory.cpp:793-829). The slacks exist on the interval
+    midpoints only; the reference stretches those values over linspace(t0, tf) and interpolates them piecewise-linearly onto
+    every grid time when it builds the table (MocoCasOCProblem.h:170-185), and a guess whose slack column has one value per
+    grid time keeps the entries of the midpoints (CasOCTranscription.cpp:601-618)."""
+    p = pkg.Problem.example("double_pendulum_coupler", ".", "num_mesh_intervals=6")
+    d = p.dims()
+    assert d.nm == 1 and d.nsl == 1 and d.n_grid == 13
+    x = p.make_iterate(seed=5, spread=0.5)
+    n_int = d.n_grid - d.n_mesh
+    off_m = 2 + (d.ns + d.nc) * d.n_grid
+    off_s = off_m + d.nm * d.n_grid
+    off_d = off_s + d.nsl * n_int
+    assert off_d + d.nd * d.n_grid == d.n_var
+    path = tmp_path / "constrained.sto"
+    p.write_sto(x, path)
+    head, body = open(path).read().split("endheader\n")
+    assert "num_multipliers=1" in head and "num_slacks=1" in head
+    labels = body.split("\n")[0].split("\t")
+    assert labels[1 + d.ns + d.nc] == p.names(3)[0] == "lambda_cid0_p0"
+    assert labels[-1] == p.names(4)[0] == "gamma_cid0_p0"
+    assert len(labels) == 1 + d.ns + d.nc + d.nm + d.nd + d.nsl
+    table = np.array([[float(v) for v in row.split("\t")] for row in body.split("\n")[1:] if row])
+    assert table.shape == (d.n_grid, len(labels))
+    assert np.array_equal(table[:, 1 + d.ns + d.nc], x[off_m:off_m + d.n_grid])
+    slack = x[off_s:off_s + n_int]
+    expect = np.interp(np.linspace(0, 1, d.n_grid), np.linspace(0, 1, n_int), slack)
+    assert np.abs(table[:, -1] - expect).max() < 1e-15
+    # read back: everything but the slacks is the identity; the slacks are the file's column at the midpoints
+    xr = p.read_sto(path)
+    keep = np.ones(d.n_var, bool)
+    keep[off_s:off_d] = False
+    assert np.array_equal(xr[keep], x[keep])
+    assert np.array_equal(xr[off_s:off_d], table[1::2, -1])
+    # a file without the multiplier column is not a compatible guess
+    q = pkg.Problem.example("pendulum:2", ".", "num_mesh_intervals=6")
+    plain = tmp_path / "plain.sto"
+    q.write_sto(q.make_iterate(seed=1, spread=0.2), plain)
+    with pytest.raises(Exception):
+        p.read_sto(plain)
