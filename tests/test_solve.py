@@ -80,3 +80,39 @@ def test_gpu_solve_of_muscle_and_pendulum_problems_converges_like_the_cpu_solve(
     assert res_o.success and res_g.success, (res_o.message, res_g.message)
     assert abs(res_g.fun - res_o.fun) < 1e-6 * max(1.0, abs(res_o.fun))
     assert abs(st_g["iterations"] - st_o["iterations"]) <= max(1, round(0.05 * st_o["iterations"]))
+
+
+def test_interior_point_loop_solves_the_sliding_mass(pkg, orc):
+    """The barrier-method stand-in (tests/ip_solve.py: the algorithm family of IPOPT, which the reference drives through
+    CasADi's nlpsol, CasOCTranscription.cpp:630-689) on the reference's known answer."""
+    from ip_solve import solve as ip_solve
+
+    p = _problem(pkg, "trapezoidal")
+    nthreads = orc.max_threads()
+    orc.set_threads(1)
+    try:
+        res, stats = ip_solve(p, orc.Oracle(p), tol=1e-6, maxiter=400)
+    finally:
+        orc.set_threads(nthreads)
+    assert res.success, res.message
+    assert res.constraint_violation < 1e-8
+    _check_bang_bang(p, res.x, 1e-2)
+    assert abs(res.fun - res.x[1]) < 1e-12
+    assert stats["jac"] == stats["iterations"] + 2  # one eval_jac_g per iterate (as in the reference's loop) + one for the scaling
+
+
+@pytest.mark.gpu
+def test_gpu_interior_point_solve_converges_like_the_cpu_solve(pkg, orc):
+    from ip_solve import solve as ip_solve
+
+    p = _problem(pkg, "trapezoidal")
+    nthreads = orc.max_threads()
+    orc.set_threads(1)
+    try:
+        res_o, st_o = ip_solve(p, orc.Oracle(p), tol=1e-6, maxiter=400)
+    finally:
+        orc.set_threads(nthreads)
+    res_g, st_g = ip_solve(p, pkg.Evaluator(p), tol=1e-6, maxiter=400)
+    assert res_o.success and res_g.success, (res_o.message, res_g.message)
+    assert abs(res_g.fun - res_o.fun) < 1e-6
+    assert abs(st_g["iterations"] - st_o["iterations"]) <= max(1, round(0.05 * st_o["iterations"]))
