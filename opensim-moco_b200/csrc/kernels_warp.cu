@@ -169,7 +169,7 @@ __global__ void k_wpoints_fd1(DevTables Tg, WarpAux Ag, DevLayout L, FdSettings 
         mask = 0xfffffffeu;
         for (int o = lane; o < L.n_dyn_out; o += 32) ws[A.o_out + o] = Y[(size_t)j * L.n_out + o];
     }
-    warp_eval_point_t<KIND, WRAP>(T, A, ws, mask, KIND == 2 && dir == 0, false);
+    warp_eval_point_t<KIND, WRAP>(T, A, ws, mask, KIND == 2 && dir == 0, KIND <= 1 && A.lockstep != 0);
     const double inv = (fd.scheme == MOCOB200_FD_FORWARD) ? 1.0 / fd.h : -1.0 / fd.h;
     if (dir < 0) {
         for (int o = lane; o < L.n_out; o += 32) Y[(size_t)j * L.n_out + o] = ws[A.o_out + o];
