@@ -48,7 +48,7 @@ def main():
     from ip_solve import solve
 
     m = ge.package()
-    prob = m.Problem.load(os.path.join(ROOT, "tests", "golden", "gait2d_tracking.mb20"), "num_mesh_intervals=%d" % a.intervals)
+    prob = m.Problem.load(os.path.join(ROOT, "opensim-moco_b200", "data", "gait2d_tracking.mb20"), "num_mesh_intervals=%d" % a.intervals)
     d = prob.dims()
     x0 = quiet_guess(bench, m, prob)
     rec = {"problem": "example2DWalking gaitTracking, Hermite-Simpson, %d intervals (%d grid points), n_var %d, n_con %d, forward FD"
