@@ -23,6 +23,10 @@ Workloads
             grid point) — the work the stage delivers. Algorithmic FLOPs from profiles/flop_counts.json (oracle op counts).
 `cpu_baseline` / `--impl reference`: the CPU oracle (oracle/, a from-scratch restatement pinned to reference-produced data —
             the reference itself cannot be built without Simbody/CasADi/IPOPT) on all host threads.
+`solve`   : (config 3, one GPU, after the timed region; `--solve-iters 0` skips it) a stand-in for BASELINE's second metric,
+            IPOPT time-to-solve, which cannot be measured here (no IPOPT): a fixed number of iterations of an interior-point
+            loop (scripts/ip_solve.py) on 10-interval gait tracking with the GPU callbacks and with the oracle's callbacks —
+            callback seconds of both arms and the distance between the two optimisation paths. Not a converged solve.
 """
 import argparse
 import ctypes
@@ -423,6 +427,44 @@ def roofline(m, r, args, local_rank, workload, peak):
             "traffic": traffic, "traffic_source": traffic_src}, n_exec
 
 
+def solve_leg(m, iters):
+    """BASELINE metric (ii) stand-in, outside the timed region: `iters` iterations of an interior-point loop (scripts/ip_solve.py,
+    NOT IPOPT - absent from this image) on 10-interval gait tracking, once with the GPU library's four TNLP callbacks and once
+    with the CPU oracle's, from the same starting guess. A fixed iteration budget, not a converged solve: it reports callback
+    seconds of both arms and how far apart the two optimisation paths are. Failures are reported, never raised."""
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "scripts"))
+        from ip_solve import solve
+        from solve_standin import quiet_guess
+
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import oracle_py as o
+
+        prob = m.Problem.load(os.path.join(DATA, "gait2d_tracking.mb20"), "num_mesh_intervals=10")
+        x0 = quiet_guess(sys.modules[__name__], m, prob)
+        out = {"what": "interior-point stand-in (scripts/ip_solve.py), not IPOPT; fixed iteration budget, not converged; "
+                       "example2DWalking gaitTracking at 10 intervals, forward FD", "iterations": iters}
+        paths = {}
+        for arm in ("gpu", "cpu"):
+            if arm == "gpu":
+                ev = m.Evaluator(prob, device=0)
+            else:
+                o.lib().orc_set_threads(host_threads())
+                ev = o.Oracle(prob)
+            t0 = time.perf_counter()
+            res, st = solve(prob, ev, x0=x0, maxiter=iters)
+            out[arm] = {"objective": float(res.fun), "constraint_violation": float(res.constraint_violation), "iterations": st["iterations"],
+                        "callbacks": st["f"] + st["grad"] + st["g"] + st["jac"], "callback_seconds": st["t_eval"],
+                        "total_seconds": time.perf_counter() - t0}
+            paths[arm] = [h[1] for h in st["history"]]
+        n = min(len(paths["gpu"]), len(paths["cpu"]))
+        out["objective_path_max_rel_diff"] = float(max(abs(a - b) / max(1e-300, abs(b)) for a, b in zip(paths["gpu"][:n], paths["cpu"][:n])))
+        out["callback_speedup"] = out["cpu"]["callback_seconds"] / max(1e-12, out["gpu"]["callback_seconds"])
+        return out
+    except Exception as e:  # the stand-in is a side record: it must not take the bench line with it
+        return {"error": "%s: %s" % (type(e).__name__, e)}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -439,6 +481,8 @@ def main():
                     help="rotate: every step reads a different iterate out of a set larger than L2 and writes a different "
                          "output buffer (also > L2 in total); flush: 10 iterates, 256 MiB fill between steps (cold code too)")
     ap.add_argument("--iterates", default="trajectory", choices=["trajectory", "bounds"])
+    ap.add_argument("--solve-iters", type=int, default=40,
+                    help="iterations of the interior-point stand-in run with each callback arm after the timed region (config 3, one GPU; 0 = skip)")
     ap.add_argument("--no-subrecords", action="store_true", help="skip the config3 / n1 sub-records of a distributed run")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -526,6 +570,8 @@ def main():
         val, n, dt, threads, _ = cpu_oracle_rate(m, r["prob"], r["fd"], r["xs_host"], args.cpu_seconds)
         line["cpu_baseline"] = {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
                                 "sample": "%d full eval_jac_g calls of the same workload in %.1f s wall" % (n, dt)}
+        if world == 1 and workload == "config3" and args.solve_iters > 0:
+            line["solve"] = solve_leg(m, args.solve_iters)
         print(json.dumps(line))
     if world > 1:
         dist.barrier()

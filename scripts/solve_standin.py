@@ -1,5 +1,5 @@
 """BASELINE metric (ii) stand-in: time-to-solve of 2D gait tracking with the GPU callbacks and with the CPU oracle's callbacks
-inside the same host interior-point loop (tests/ip_solve.py — NOT IPOPT, which is absent from this image; the reference's
+inside the same host interior-point loop (scripts/ip_solve.py — NOT IPOPT, which is absent from this image; the reference's
 loop is CasOCTranscription.cpp:630-721). Both solves start from the same guess: the reference walking trajectory
 (referenceCoordinates.sto, as the tracking goal's splines hold it) with activations and excitations at 0.05.
 
@@ -16,7 +16,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "scripts"))
 sys.path.insert(0, os.path.join(ROOT, "oracle"))
 
 
@@ -53,7 +53,7 @@ def main():
     x0 = quiet_guess(bench, m, prob)
     rec = {"problem": "example2DWalking gaitTracking, Hermite-Simpson, %d intervals (%d grid points), n_var %d, n_con %d, forward FD"
                       % (a.intervals, d.n_grid, d.n_var, d.n_con),
-           "solver": "tests/ip_solve.py: primal-dual barrier method, damped BFGS, filter line search - a stand-in, not IPOPT",
+           "solver": "scripts/ip_solve.py: primal-dual barrier method, damped BFGS, filter line search - a stand-in, not IPOPT",
            "tol": a.tol, "maxiter": a.maxiter, "arms": {}}
     sols = {}
     for arm in a.arms.split(","):

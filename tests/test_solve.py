@@ -3,10 +3,15 @@
 callbacks. The problem is exampleSlidingMass.cpp's (mass 2 kg, |force| <= 50 N, 1 m): final time 2*sqrt(m*d/F) = 0.4 s.
 BASELINE.json's second metric asks for identical convergence of the GPU and the CPU path: final objective within 1e-6 and
 iteration count within 5 %."""
+import os
+import sys
+
 import numpy as np
 import pytest
 
 from nlp_solve import solve
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts"))  # ip_solve.py
 
 T_EXACT = 2.0 * np.sqrt(2.0 * 1.0 / 50.0)
 
@@ -83,7 +88,7 @@ def test_gpu_solve_of_muscle_and_pendulum_problems_converges_like_the_cpu_solve(
 
 
 def test_interior_point_loop_solves_the_sliding_mass(pkg, orc):
-    """The barrier-method stand-in (tests/ip_solve.py: the algorithm family of IPOPT, which the reference drives through
+    """The barrier-method stand-in (scripts/ip_solve.py: the algorithm family of IPOPT, which the reference drives through
     CasADi's nlpsol, CasOCTranscription.cpp:630-689) on the reference's known answer."""
     from ip_solve import solve as ip_solve
 
