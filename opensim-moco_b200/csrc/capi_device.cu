@@ -1274,8 +1274,8 @@ int mocob200_eval_jac_g(mocob200_handle* h, const double* x, double* values) {
     }
     if (h->rank == 0 && values)
         cudaMemcpyAsync(values, h->d_vals, sizeof(double) * h->L.nnz, cudaMemcpyDeviceToHost, h->stream);
-    if (!finish(h, "eval_jac_g")) return MOCOB200_ERR_CUDA;
-    rememberX(h, x, true);
+    rememberX(h, x, true); // the host copy of x (same-x memoisation) overlaps the device work instead of following the sync
+    if (!finish(h, "eval_jac_g")) { h->x_cached.clear(); h->haveJ = false; return MOCOB200_ERR_CUDA; }
     return MOCOB200_OK;
 }
 
