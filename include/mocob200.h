@@ -265,6 +265,18 @@ int mocob200_eval_f(mocob200_handle*, const double* x, double* f, double* f_term
 int mocob200_eval_g(mocob200_handle*, const double* x, double* g);
 int mocob200_eval_grad_f(mocob200_handle*, const double* x, double* grad);
 int mocob200_eval_jac_g(mocob200_handle*, const double* x, double* values);
+/* Optional delivery of the values into a PINNED (page-locked) caller buffer, single rank (masked = 1; default 0 = the plain
+ * device-to-host copy): the entries of the dense-block structure that are +0.0 at every iterate seen so far (CasADi keeps them
+ * in the structure under optim_sparsity_detection = "none", MocoCasADiSolver.cpp:39, CasOCFunction.cpp:25-74) do not cross
+ * PCIe - the host zero-fills their runs while the device computes and a kernel stores the other entries straight into the
+ * buffer. A kernel-side check of every skipped entry makes the call fall back to the plain copy (and widen the kept set) when
+ * one of them is not +0.0, so the buffer is bit-identical to the plain copy in every case. Pageable buffers, sharded handles
+ * and problems with path-constraint / velocity-correction rows always take the plain copy. Off by default because what it
+ * gains depends on the host: config 3 on two B200 boxes, 175 us against 183 us per call on one, 270 us against 185 us on the
+ * other, where the host's zero-fill (2.2 MB in 16 k runs, one core) outlasted the device work (profiles/experiments_r02.md).
+ * mocob200_host_push_stats: calls delivered each way; kept: entries that cross PCIe (0: not in use). */
+int mocob200_set_host_delivery(mocob200_handle*, int masked);
+int mocob200_host_push_stats(const mocob200_handle*, long* pushed, long* fallbacks, long* kept);
 /* Same evaluations with x already resident on the device and results left there (device pointers; used by bench.py's
  * device-resident timing and by callers that chain kernels). The work runs on the handle's own stream. cuda_stream != NULL: that
  * stream is ordered around the call - the handle's stream first waits for everything already queued on cuda_stream (the

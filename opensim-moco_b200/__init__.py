@@ -23,7 +23,7 @@ ABI_SYMBOLS = [
     "mocob200_layout", "mocob200_layout_bounds", "mocob200_layout_structure", "mocob200_make_iterate",
     "mocob200_create", "mocob200_nccl_unique_id", "mocob200_destroy", "mocob200_last_error", "mocob200_get_dims",
     "mocob200_set_fd", "mocob200_jac_g_structure", "mocob200_eval_points", "mocob200_eval_f", "mocob200_eval_g",
-    "mocob200_eval_grad_f", "mocob200_eval_jac_g", "mocob200_eval_jac_g_device", "mocob200_eval_g_device",
+    "mocob200_eval_grad_f", "mocob200_eval_jac_g", "mocob200_set_host_delivery", "mocob200_host_push_stats", "mocob200_eval_jac_g_device", "mocob200_eval_g_device",
     "mocob200_eval_g_static",
     "mocob200_eval_jac_g_batch",
     "mocob200_sync", "mocob200_mark", "mocob200_elapsed_ms", "mocob200_launch_count", "mocob200_last_kernel_ms",
@@ -87,6 +87,8 @@ def lib():
         L.mocob200_eval_g.argtypes = [vp, vp, vp]
         L.mocob200_eval_grad_f.argtypes = [vp, vp, vp]
         L.mocob200_eval_jac_g.argtypes = [vp, vp, vp]
+        L.mocob200_set_host_delivery.argtypes = [vp, C.c_int]
+        L.mocob200_host_push_stats.argtypes = [vp, C.POINTER(C.c_long), C.POINTER(C.c_long), C.POINTER(C.c_long)]
         L.mocob200_eval_jac_g_device.argtypes = [vp, vp, vp, vp]
         L.mocob200_eval_g_device.argtypes = [vp, vp, vp, vp]
         L.mocob200_eval_g_static.argtypes = [vp, vp, vp, vp]
@@ -303,6 +305,15 @@ class Evaluator:
         return v
 
     # raw-pointer variants (pinned host buffers / device pointers from torch)
+    def set_host_delivery(self, masked):
+        self._ck(lib().mocob200_set_host_delivery(self._h, 1 if masked else 0), "set_host_delivery")
+
+    def host_push_stats(self):
+        """(calls delivered by the masked push, calls that fell back to the plain copy, entries crossing PCIe)"""
+        a, b, c = C.c_long(), C.c_long(), C.c_long()
+        lib().mocob200_host_push_stats(self._h, C.byref(a), C.byref(b), C.byref(c))
+        return a.value, b.value, c.value
+
     def eval_jac_g_ptr(self, x_ptr, vals_ptr):
         self._ck(lib().mocob200_eval_jac_g(self._h, C.c_void_p(x_ptr), C.c_void_p(vals_ptr)), "eval_jac_g")
 

@@ -1,5 +1,6 @@
 // Device half of the C ABI: handle life cycle, evaluation pipelines, NCCL gather of the point blocks.
 #include <cuda_runtime.h>
+#include <emmintrin.h> // SSE2 stores of the host zero-fill (x86-64 baseline)
 #include <dlfcn.h>
 
 #include <algorithm>
@@ -70,6 +71,17 @@ T* devUpload(const std::vector<T>& v) {
 
 } // namespace
 
+// Zero-fill of runs [i0, i1) of a (start, length) run list: two doubles per store
+static void fillZeroRuns(double* values, const unsigned* r, size_t i0, size_t i1) {
+    const __m128d z = _mm_setzero_pd();
+    for (size_t i = i0; i < i1; i += 2) {
+        double* p = values + r[i];
+        const unsigned n = r[i + 1];
+        unsigned k = 0;
+        for (; k + 2 <= n; k += 2) _mm_storeu_pd(p + k, z);
+        if (k < n) p[k] = 0.0;
+    }
+}
 struct mocob200_handle {
     std::string err;
     int device = 0, rank = 0, world = 1;
@@ -128,6 +140,7 @@ struct mocob200_handle {
     // value array, point outputs, time columns and flag words (CUDA IPC) and their assembly kernels store straight into
     // them over NVLink - no staging copy, no collective on the data path. See peerGatherSetup / jacPipelineSharded.
     struct PeerGather {
+        bool wanted = false; // mocob200_set_host_delivery: off unless the caller asks for it
         bool tried = false, on = false;
         double *vals = nullptr, *Y = nullptr, *Jt = nullptr; // rank > 0: rank 0's buffers in this process's address space
         unsigned long long* flags = nullptr; // rank 0: its flag words ([0] consumed, [r] done of rank r); rank > 0: their mapping
@@ -145,6 +158,40 @@ struct mocob200_handle {
     // host-side memo: IPOPT asks for grad_f and jac_g at the same x
     std::vector<double> x_cached;
     bool haveJ = false;
+    // Host delivery of the CSC values into a PINNED caller buffer without the structural zeros crossing PCIe (pushSetup /
+    // pushValues below): byte mask over the value array (1 = the entry was not +0.0 at one of the detection iterates), a flag
+    // word in mapped host memory the kernel raises when an entry outside the mask is not +0.0 (then the call falls back to
+    // the plain copy, so the caller's buffer is bit-identical either way).
+    struct HostPush {
+        bool wanted = false; // mocob200_set_host_delivery: off unless the caller asks for it
+        bool tried = false, on = false;
+        unsigned char* d_mask = nullptr;
+        int* flag_h = nullptr;
+        int* flag_d = nullptr;
+        const void* lastHost = nullptr; // last caller buffer that was looked up ...
+        double* lastDev = nullptr;      // ... and its device alias (nullptr: not pinned)
+        long pushed = 0, fallbacks = 0;
+        size_t kept = 0;
+        std::vector<unsigned char> mask; // host copy (extended when a call finds a new non-zero entry)
+        std::vector<unsigned> zeroRuns;  // (start, length) of the runs of entries outside the mask: what the host zero-fills
+        std::vector<unsigned char> devMask; // mask + the entries of zero runs too short to be worth a host loop iteration
+        size_t sent = 0;                    // entries of devMask: what crosses PCIe
+        int shortRun = 8;                   // zero runs shorter than this go with the kernel's stores (MOCOB200_PUSH_SHORT_RUN: A-B)
+        void buildRuns() {
+            zeroRuns.clear();
+            devMask = mask;
+            const size_t n = mask.size();
+            for (size_t e = 0; e < n;) {
+                if (mask[e]) { ++e; continue; }
+                size_t b = e;
+                while (e < n && !mask[e]) ++e;
+                if (e - b < (size_t)shortRun) { for (size_t k = b; k < e; ++k) devMask[k] = 1; }
+                else { zeroRuns.push_back((unsigned)b); zeroRuns.push_back((unsigned)(e - b)); }
+            }
+            sent = 0;
+            for (unsigned char m : devMask) sent += m;
+        }
+    } push;
 
     bool ck(cudaError_t e, const char* what) {
         if (e == cudaSuccess) return true;
@@ -515,6 +562,16 @@ bool runFd(mocob200_handle* h, bool deferIntegralDerivs = false, bool* deferred 
     }
     return true;
 }
+// values[k] -> host[k] for the entries the mask keeps (stores into the caller's pinned buffer over PCIe); any other entry that is
+// not +0.0 raises the flag in host memory
+__global__ void k_push_masked(const double* __restrict__ vals, const unsigned char* __restrict__ mask, double* __restrict__ host,
+                              int* __restrict__ flag, int nnz) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nnz) return;
+    const double v = vals[k];
+    if (mask[k]) host[k] = v;
+    else if (__double_as_longlong(v) != 0) *flag = 1;
+}
 bool finish(mocob200_handle* h, const char* what) {
     if (!h->ck(cudaStreamSynchronize(h->stream), what)) return false;
     return h->ck(cudaGetLastError(), what);
@@ -546,6 +603,7 @@ void mocob200_destroy(mocob200_handle* h) {
     if (!h) return;
     cudaSetDevice(h->device);
     peerGatherClose(h);
+    if (h->push.flag_h) cudaFreeHost(h->push.flag_h);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     for (void* p : h->owned) cudaFree(p);
     for (auto& e : h->ev) if (e) cudaEventDestroy(e);
@@ -800,6 +858,7 @@ int mocob200_set_fd(mocob200_handle* h, int scheme, double step, int h_iter, dou
     if (u_aim > 0) h->fd.u_aim = u_aim;
     if (h->jacGraph) { cudaSetDevice(h->device); cudaStreamSynchronize(h->stream); cudaGraphExecDestroy(h->jacGraph); h->jacGraph = nullptr; }
     h->x_cached.clear();
+    h->push.tried = h->push.on = false; // the sign of a zero quotient depends on the scheme: find the mask again
     return MOCOB200_OK;
 }
 
@@ -882,6 +941,7 @@ int mocob200_set_sparsity_detection(mocob200_handle* h, int mode, int n_iterates
     peerGatherClose(h); // the value array the other ranks had mapped is no longer the one in use: set up again at the next Jacobian
     if (h->jacGraph) { cudaGraphExecDestroy(h->jacGraph); h->jacGraph = nullptr; }
     h->x_cached.clear();
+    h->push.tried = h->push.on = false; // another value array: the mask of the host delivery is found again at the next call
     return MOCOB200_OK;
 }
 
@@ -1261,9 +1321,76 @@ static bool jacPipeline(mocob200_handle* h, double* d_vals) {
     return true;
 }
 
+// Device alias of a caller buffer in pinned (page-locked, mapped) host memory, or nullptr.
+static double* pinnedAlias(mocob200_handle* h, const double* values) {
+    auto& P = h->push;
+    if (values == P.lastHost) return P.lastDev;
+    cudaPointerAttributes at;
+    double* dev = nullptr;
+    if (cudaPointerGetAttributes(&at, values) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer) dev = (double*)at.devicePointer;
+    else cudaGetLastError();
+    P.lastHost = values; P.lastDev = dev;
+    return dev;
+}
+// Once per handle: which entries of the value array can differ from +0.0? The Jacobian at four seeded iterates within the bounds
+// (the iterates of optim_sparsity_detection = "random", CasOCFunction.cpp:25-74, here applied to the assembled values and
+// bitwise). Worth it only when the dense-block structure carries enough zeros. Single rank, no path-constraint or
+// velocity-correction rows (their kernels patch the value array after the main assembly).
+static void pushSetup(mocob200_handle* h, const double* x_caller) {
+    auto& P = h->push;
+    P.tried = true;
+    const size_t nnz = (size_t)h->L.nnz;
+    if (h->eff != 1 || h->rank != 0 || h->DL.n_path_rows > 0 || h->L.nsl > 0 || nnz < 65536) return;
+    std::vector<double> x(h->L.n_var), v(nnz);
+    std::vector<unsigned char> mask(nnz, 0);
+    for (int k = 0; k < 5; ++k) { // four seeded iterates and the caller's own
+        if (k < 4) mocob200_make_iterate(&h->hostT, &h->hostR, k, k == 0 ? 0.3 : 1.0, x.data());
+        else if (x_caller) std::memcpy(x.data(), x_caller, sizeof(double) * x.size());
+        else break;
+        if (!stageX(h, x.data()) || !jacPipeline(h, h->d_vals) ||
+            !h->ck(cudaMemcpyAsync(v.data(), h->d_vals, sizeof(double) * nnz, cudaMemcpyDeviceToHost, h->stream), "D2H values") ||
+            !finish(h, "host push setup")) { h->err.clear(); cudaGetLastError(); return; }
+        for (size_t e = 0; e < nnz; ++e) {
+            long long bits;
+            std::memcpy(&bits, &v[e], sizeof bits);
+            if (bits != 0) mask[e] = 1;
+        }
+    }
+    h->x_cached.clear(); h->haveJ = false;
+    size_t kept = 0;
+    for (unsigned char m : mask) kept += m;
+    if (kept * 10 > nnz * 6) return; // fewer than 40 % zeros: the plain copy is as good
+    if (cudaMalloc(&P.d_mask, nnz) != cudaSuccess) { cudaGetLastError(); P.d_mask = nullptr; return; }
+    h->owned.push_back(P.d_mask);
+    P.mask.swap(mask);
+    if (const char* e = devEnv("MOCOB200_PUSH_SHORT_RUN")) { if (atoi(e) > 0) P.shortRun = atoi(e); }
+    P.buildRuns();
+    if (cudaMemcpy(P.d_mask, P.devMask.data(), nnz, cudaMemcpyHostToDevice) != cudaSuccess ||
+        (!P.flag_h && cudaHostAlloc((void**)&P.flag_h, sizeof(int), cudaHostAllocMapped) != cudaSuccess)) { cudaGetLastError(); P.flag_h = nullptr; return; }
+    if (cudaHostGetDevicePointer((void**)&P.flag_d, P.flag_h, 0) != cudaSuccess) { cudaGetLastError(); return; }
+    P.kept = kept;
+    P.on = true;
+}
+
+int mocob200_set_host_delivery(mocob200_handle* h, int masked) {
+    if (!h || masked < 0 || masked > 1) return MOCOB200_ERR_ARG;
+    h->push.wanted = masked != 0;
+    return MOCOB200_OK;
+}
+
+int mocob200_host_push_stats(const mocob200_handle* h, long* pushed, long* fallbacks, long* kept) {
+    if (!h) return MOCOB200_ERR_ARG;
+    if (pushed) *pushed = h->push.pushed;
+    if (fallbacks) *fallbacks = h->push.fallbacks;
+    if (kept) *kept = h->push.on ? (long)h->push.sent : 0;
+    return MOCOB200_OK;
+}
+
 int mocob200_eval_jac_g(mocob200_handle* h, const double* x, double* values) {
     if (!h) return MOCOB200_ERR_ARG;
     cudaSetDevice(h->device);
+    double* hostAlias = (h->rank == 0 && values && h->eff == 1) ? pinnedAlias(h, values) : nullptr;
+    if (hostAlias && h->push.wanted && !h->push.tried) pushSetup(h, x);
     const bool reuse = h->eff == 1 && h->haveJ && sameX(h, x);
     if (!reuse) {
         if (!stageX(h, x) || !bcastX(h, h->d_x)) return MOCOB200_ERR_CUDA;
@@ -1272,10 +1399,38 @@ int mocob200_eval_jac_g(mocob200_handle* h, const double* x, double* values) {
         launch_assemble_jac(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_I, h->d_E, h->d_vals, h->stream);
         h->launches += 1 + (h->DL.n_path_rows > 0);
     }
-    if (h->rank == 0 && values)
+    const bool push = hostAlias && h->push.wanted && h->push.on;
+    if (push) {
+        // a kernel stores the entries of the mask straight into the caller's buffer; the others are written here, by the
+        // host, while the device computes
+        *h->push.flag_h = 0;
+        k_push_masked<<<(h->L.nnz + 255) / 256, 256, 0, h->stream>>>(h->d_vals, h->push.d_mask, hostAlias, h->push.flag_d, h->L.nnz);
+        static const int noFill = (devEnv("MOCOB200_HOST_PUSH") && devEnv("MOCOB200_HOST_PUSH")[0] == '2') ? 1 : 0; // timing diagnostic only
+        if (!noFill) { // disjoint from what the kernel stores, so it needs no ordering against it: it overlaps the device work
+            const unsigned* r = h->push.zeroRuns.data();
+            fillZeroRuns(values, r, 0, h->push.zeroRuns.size());
+        }
+        h->launches++;
+    } else if (h->rank == 0 && values)
         cudaMemcpyAsync(values, h->d_vals, sizeof(double) * h->L.nnz, cudaMemcpyDeviceToHost, h->stream);
     rememberX(h, x, true); // the host copy of x (same-x memoisation) overlaps the device work instead of following the sync
     if (!finish(h, "eval_jac_g")) { h->x_cached.clear(); h->haveJ = false; return MOCOB200_ERR_CUDA; }
+    if (push) {
+        if (*h->push.flag_h) { // an entry outside the mask was not +0.0 at this x: deliver the plain copy and widen the mask
+            auto& P = h->push;
+            P.fallbacks++;
+            if (!h->ck(cudaMemcpyAsync(values, h->d_vals, sizeof(double) * h->L.nnz, cudaMemcpyDeviceToHost, h->stream), "D2H values") ||
+                !finish(h, "eval_jac_g")) { h->x_cached.clear(); h->haveJ = false; return MOCOB200_ERR_CUDA; }
+            for (size_t e = 0; e < P.mask.size(); ++e) {
+                long long bits;
+                std::memcpy(&bits, &values[e], sizeof bits);
+                if (bits != 0 && !P.mask[e]) { P.mask[e] = 1; P.kept++; }
+            }
+            P.buildRuns();
+            if (P.kept * 10 > P.mask.size() * 6 || P.fallbacks > 64 ||
+                cudaMemcpy(P.d_mask, P.devMask.data(), P.devMask.size(), cudaMemcpyHostToDevice) != cudaSuccess) { cudaGetLastError(); P.on = false; }
+        } else h->push.pushed++;
+    }
     return MOCOB200_OK;
 }
 
