@@ -1389,8 +1389,8 @@ int mocob200_host_push_stats(const mocob200_handle* h, long* pushed, long* fallb
 int mocob200_eval_jac_g(mocob200_handle* h, const double* x, double* values) {
     if (!h) return MOCOB200_ERR_ARG;
     cudaSetDevice(h->device);
-    double* hostAlias = (h->rank == 0 && values && h->eff == 1) ? pinnedAlias(h, values) : nullptr;
-    if (hostAlias && h->push.wanted && !h->push.tried) pushSetup(h, x);
+    double* hostAlias = (h->push.wanted && h->rank == 0 && values && h->eff == 1) ? pinnedAlias(h, values) : nullptr; // default: untouched path
+    if (hostAlias && !h->push.tried) pushSetup(h, x);
     const bool reuse = h->eff == 1 && h->haveJ && sameX(h, x);
     if (!reuse) {
         if (!stageX(h, x) || !bcastX(h, h->d_x)) return MOCOB200_ERR_CUDA;
@@ -1399,7 +1399,7 @@ int mocob200_eval_jac_g(mocob200_handle* h, const double* x, double* values) {
         launch_assemble_jac(h->DT, h->DL, h->fd, h->d_x, h->d_Y, h->d_J, h->d_I, h->d_E, h->d_vals, h->stream);
         h->launches += 1 + (h->DL.n_path_rows > 0);
     }
-    const bool push = hostAlias && h->push.wanted && h->push.on;
+    const bool push = hostAlias && h->push.on;
     if (push) {
         // a kernel stores the entries of the mask straight into the caller's buffer; the others are written here, by the
         // host, while the device computes
